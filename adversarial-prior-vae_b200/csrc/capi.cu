@@ -1,0 +1,397 @@
+// extern "C" surface declared in include/apvae.h.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include <mutex>
+#include "../../include/apvae.h"
+#include "kernels.h"
+#include "model.h"
+
+using namespace apvae;
+
+struct apvae_handle {
+    Model m;
+};
+struct apvae_plan {
+    OpPlan plan;
+};
+
+static std::string g_err;
+static std::mutex g_err_mu;
+static int set_global_err(const std::string& m, int code) {
+    std::lock_guard<std::mutex> l(g_err_mu);
+    g_err = m;
+    return code;
+}
+
+static_assert((int)kPerImageRows + 1 == (int)APVAE_PER_IMAGE_ROWS, "per-image row tables out of sync");
+
+extern "C" {
+
+const char* apvae_version(void) { return "apvae-b200 0.1 (sm_100a, tcgen05/TMEM/TMA)"; }
+
+const char* apvae_last_error(const apvae_handle* h) {
+    if (h) return h->m.err.c_str();
+    std::lock_guard<std::mutex> l(g_err_mu);
+    static thread_local std::string copy;
+    copy = g_err;
+    return copy.c_str();
+}
+
+int apvae_default_config(int arch, int celeba, apvae_config* c) {
+    if (!c) return set_global_err("null config", APVAE_ERR_INVALID);
+    memset(c, 0, sizeof(*c));
+    c->arch = arch;
+    c->epsilon = -20.f;
+    c->max_batch = 64;
+    c->max_chunk = 512;
+    c->enable_grad = 0;
+    switch (arch) {
+        case APVAE_ARCH_A:   // dmm_cifar10.py:27-91
+            c->x_h = 32; c->x_w = 32; c->x_c = 3; c->z_dim = 1024;
+            c->pull_back_energy_weight = 1000.f; c->min_logstd_of_q = -3.f;
+            c->smallest_step = 5e-5f; c->len_train = 50000;
+            break;
+        case APVAE_ARCH_B:   // dmm_for_sampling.py:28-92
+            c->celeba = celeba ? 1 : 0;
+            c->x_h = c->x_w = celeba ? 64 : 32; c->x_c = 3; c->z_dim = 128;
+            c->pull_back_energy_weight = 1000.f; c->min_logstd_of_q = -3.f; c->uniform_scale = 1;
+            c->smallest_step = 5e-5f; c->len_train = celeba ? 162770 : 50000;
+            break;
+        case APVAE_ARCH_M:   // dmm_bernouli_fashion.py ExpConfig
+            c->x_h = 28; c->x_w = 28; c->x_c = 1; c->z_dim = 40;
+            c->pull_back_energy_weight = 20.f; c->min_logstd_of_q = -5.f; c->use_truncated = 1; c->bernoulli = 1;
+            c->smallest_step = 5e-6f; c->len_train = 50000;
+            break;
+        default:
+            return set_global_err("arch must be 0 (A), 1 (B) or 2 (M)", APVAE_ERR_INVALID);
+    }
+    return APVAE_OK;
+}
+
+int apvae_weight_count(const apvae_config* cfg, int* count) {
+    std::string e;
+    if (!cfg || !count) return set_global_err("null argument", APVAE_ERR_INVALID);
+    if (!validate_config(*cfg, &e)) return set_global_err(e, APVAE_ERR_INVALID);
+    *count = (int)weight_schema(*cfg).size();
+    return APVAE_OK;
+}
+
+int apvae_weight_info(const apvae_config* cfg, int index, char* name, int name_cap, int64_t shape[4], int* ndim) {
+    std::string e;
+    if (!cfg || !name || !shape || !ndim) return set_global_err("null argument", APVAE_ERR_INVALID);
+    if (!validate_config(*cfg, &e)) return set_global_err(e, APVAE_ERR_INVALID);
+    const std::vector<WeightInfo> s = weight_schema(*cfg);
+    if (index < 0 || index >= (int)s.size()) return set_global_err("weight index out of range", APVAE_ERR_INVALID);
+    if ((int)s[index].name.size() + 1 > name_cap) return set_global_err("name buffer too small", APVAE_ERR_INVALID);
+    strcpy(name, s[index].name.c_str());
+    *ndim = (int)s[index].shape.size();
+    for (int i = 0; i < 4; ++i) shape[i] = i < *ndim ? s[index].shape[i] : 1;
+    return APVAE_OK;
+}
+
+int apvae_create(const apvae_config* cfg, int device, apvae_handle** out) {
+    std::string e;
+    if (!cfg || !out) return set_global_err("null argument", APVAE_ERR_INVALID);
+    if (!validate_config(*cfg, &e)) return set_global_err(e, APVAE_ERR_INVALID);
+    DeviceInfo dev;
+    if (!device_open(device, &dev, &e)) return set_global_err(e, APVAE_ERR_NO_DEVICE);
+    apvae_handle* h = new apvae_handle();
+    h->m.cfg = *cfg;
+    h->m.dev = dev;
+    *out = h;
+    return APVAE_OK;
+}
+
+int apvae_destroy(apvae_handle* h) {
+    if (h) {
+        cudaSetDevice(h->m.dev.device);
+        cudaDeviceSynchronize();
+        delete h;
+    }
+    return APVAE_OK;
+}
+
+int apvae_load_weights(apvae_handle* h, int n, const char* const* names, const float* const* data,
+                       const int64_t* const* shapes, const int* ndims) {
+    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
+    Model& m = h->m;
+    if (m.built) { m.err = "weights already loaded"; return APVAE_ERR_STATE; }
+    for (int i = 0; i < n; ++i) {
+        HostArr a;
+        size_t cnt = 1;
+        for (int j = 0; j < ndims[i]; ++j) { a.shape.push_back(shapes[i][j]); cnt *= (size_t)shapes[i][j]; }
+        a.v.assign(data[i], data[i] + cnt);
+        m.weights[names[i]] = std::move(a);
+    }
+    for (const WeightInfo& w : weight_schema(m.cfg)) {
+        auto it = m.weights.find(w.name);
+        if (it == m.weights.end()) { m.err = "missing variable '" + w.name + "'"; return APVAE_ERR_WEIGHTS; }
+        if (it->second.shape != w.shape) { m.err = "variable '" + w.name + "' has the wrong shape"; return APVAE_ERR_WEIGHTS; }
+    }
+    if (!m.build()) return APVAE_ERR_CUDA;
+    return APVAE_OK;
+}
+
+int apvae_set_scalars(apvae_handle* h, float xi_raw, float beta, float log_Z) {
+    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
+    h->m.xi_raw = xi_raw; h->m.beta = beta; h->m.log_Z = log_Z;
+    return APVAE_OK;
+}
+
+#define REQUIRE_BUILT(h)                                                              \
+    if (!(h)) return set_global_err("null handle", APVAE_ERR_INVALID);                \
+    Model& m = (h)->m;                                                                \
+    if (!m.built) { m.err = "weights not loaded (apvae_load_weights)"; return APVAE_ERR_STATE; } \
+    if (cudaSetDevice(m.dev.device) != cudaSuccess) { m.err = "cudaSetDevice failed"; return APVAE_ERR_CUDA; }
+
+#define LCHECK(call, what)                                                                         \
+    do {                                                                                           \
+        const int _e = (call);                                                                     \
+        ++m.launches;                                                                              \
+        if (_e != 0) { m.err = std::string(what) + ": " + cudaGetErrorString((cudaError_t)_e); return APVAE_ERR_CUDA; } \
+    } while (0)
+
+int apvae_encode(apvae_handle* h, const float* x_dev, int B, float* mu_dev, float* logstd_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (B <= 0 || !x_dev) { m.err = "encode: empty batch"; return APVAE_ERR_INVALID; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t per = (size_t)m.HW() * m.C();
+    for (int b0 = 0; b0 < B; b0 += m.cfg.max_batch) {
+        const int n = std::min(m.cfg.max_batch, B - b0);
+        if (!m.run_encoder(x_dev + b0 * per, n, stream)) return APVAE_ERR_CUDA;
+        const size_t bytes = (size_t)n * m.cfg.z_dim * sizeof(float);
+        if (mu_dev) cudaMemcpyAsync(mu_dev + (size_t)b0 * m.cfg.z_dim, m.q_mu, bytes, cudaMemcpyDeviceToDevice, st);
+        if (logstd_dev) cudaMemcpyAsync(logstd_dev + (size_t)b0 * m.cfg.z_dim, m.q_logstd, bytes, cudaMemcpyDeviceToDevice, st);
+    }
+    return APVAE_OK;
+}
+
+// z fp32 [n, d] -> decoder input tensors (no noise: mu = z, eps unused)
+static int stage_latents(Model& m, const float* z_dev, int n, void* stream) {
+    return launch_sample_z(nullptr, nullptr, z_dev, n, 0, 1, m.cfg.z_dim, 0.f, 0, nullptr, m.g_in.raw.ptr,
+                           m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, nullptr, stream);
+}
+
+int apvae_decode(apvae_handle* h, const float* z_dev, int N, float* x_mean_dev, float* x_logstd_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (N <= 0 || !z_dev) { m.err = "decode: empty batch"; return APVAE_ERR_INVALID; }
+    if (x_logstd_dev && m.head_ld() != 2 * m.C()) { m.err = "this architecture's G_theta has no x_logstd head"; return APVAE_ERR_INVALID; }
+    const int Cx = m.C(), ld = m.head_ld();
+    for (int s0 = 0; s0 < N; s0 += m.cfg.max_chunk) {
+        const int n = std::min(m.cfg.max_chunk, N - s0);
+        LCHECK(stage_latents(m, z_dev + (size_t)s0 * m.cfg.z_dim, n, stream), "stage_latents");
+        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
+        const long long rows = (long long)n * m.HW();
+        if (x_mean_dev) LCHECK(launch_gather_cols(m.head_f32, ld, 0, Cx, rows, x_mean_dev + (size_t)s0 * m.HW() * Cx, stream), "gather");
+        if (x_logstd_dev) LCHECK(launch_gather_cols(m.head_f32, ld, Cx, Cx, rows, x_logstd_dev + (size_t)s0 * m.HW() * Cx, stream), "gather");
+    }
+    return APVAE_OK;
+}
+
+int apvae_energy(apvae_handle* h, const float* x_dev, const float* z_dev, int N, float* d_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (N <= 0 || !d_dev || (!x_dev == !z_dev)) { m.err = "energy: pass exactly one of x_dev / z_dev"; return APVAE_ERR_INVALID; }
+    if (x_dev) return m.critic_of_images(x_dev, N, d_dev, stream) ? APVAE_OK : APVAE_ERR_CUDA;
+    for (int s0 = 0; s0 < N; s0 += m.cfg.max_chunk) {
+        const int n = std::min(m.cfg.max_chunk, N - s0);
+        LCHECK(stage_latents(m, z_dev + (size_t)s0 * m.cfg.z_dim, n, stream), "stage_latents");
+        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
+        if (!m.run_critic_chunk(n, d_dev + s0, stream)) return APVAE_ERR_CUDA;
+    }
+    return APVAE_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev, int B, int K,
+                 const float* eps_dev, uint64_t seed, float* per_image_dev, float* per_sample_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (B <= 0 || K <= 0 || !x_dev || !per_image_dev) { m.err = "is_nll: bad arguments"; return APVAE_ERR_INVALID; }
+    if (B > m.cfg.max_batch) { m.err = "is_nll: B exceeds max_batch"; return APVAE_ERR_INVALID; }
+    if (!x_origin_dev) x_origin_dev = x_dev;
+    const int d = m.cfg.z_dim;
+    const long long S = (long long)K * B;
+    if (!m.ensure_sample_buffers((size_t)S)) return APVAE_ERR_CUDA;
+    cudaStream_t st = (cudaStream_t)stream;
+    // q(z|x): q_net reads input_origin_x in arch M (dmm_bernouli_fashion.py:888), input_x otherwise
+    if (!m.run_encoder(m.cfg.arch == APVAE_ARCH_M ? x_origin_dev : x_dev, B, stream)) return APVAE_ERR_CUDA;
+    const float* eps = eps_dev;
+    if (!eps) {
+        LCHECK(launch_fill_normal(m.eps_buf, S * d, seed, 0, m.cfg.use_truncated, stream), "fill_normal");
+        eps = m.eps_buf;
+    }
+    for (long long s0 = 0; s0 < S; s0 += m.cfg.max_chunk) {
+        const int n = (int)std::min<long long>(m.cfg.max_chunk, S - s0);
+        LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps + s0 * d, n, (int)(s0 % B), B, d, m.cfg.min_logstd_of_q,
+                               m.cfg.use_truncated, nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(),
+                               m.z_cpad(), 0.2f, m.log_q + s0, m.log_pn + s0, stream), "sample_z");
+        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
+        LCHECK(launch_pixel_logprob(m.head_f32, m.head_ld(), x_dev, n, (int)(s0 % B), B, m.HW(), m.C(), m.cfg.bernoulli,
+                                    m.cfg.uniform_scale, m.beta, m.cfg.epsilon, m.log_px + s0, stream), "pixel_logprob");
+        if (!m.run_critic_chunk(n, m.d_g + s0, stream)) return APVAE_ERR_CUDA;
+    }
+    LCHECK(launch_is_reduce(m.log_px, m.log_q, m.log_pn, m.d_g, nullptr, K, B, d, m.w_xi(), m.log_Z, per_image_dev, stream),
+           "is_reduce");
+    if (!m.critic_of_images(x_origin_dev, B, per_image_dev + (size_t)APVAE_ROW_REAL_E * B, stream)) return APVAE_ERR_CUDA;
+    if (per_sample_dev) {
+        const size_t bytes = (size_t)S * sizeof(float);
+        cudaMemcpyAsync(per_sample_dev + APVAE_SROW_LOG_PX * S, m.log_px, bytes, cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(per_sample_dev + APVAE_SROW_LOG_Q * S, m.log_q, bytes, cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(per_sample_dev + APVAE_SROW_LOG_PN * S, m.log_pn, bytes, cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(per_sample_dev + APVAE_SROW_DG * S, m.d_g, bytes, cudaMemcpyDeviceToDevice, st);
+    }
+    return APVAE_OK;
+}
+
+int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t seed, float* d_g_dev,
+                      float* log_pn_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (Kp <= 0 || !d_g_dev || !log_pn_dev) { m.err = "prior_stats: bad arguments"; return APVAE_ERR_INVALID; }
+    const int d = m.cfg.z_dim;
+    if (!m.ensure_sample_buffers((size_t)Kp)) return APVAE_ERR_CUDA;
+    const float* eps = eps_dev;
+    if (!eps) {
+        LCHECK(launch_fill_normal(m.eps_buf, (long long)Kp * d, seed, 1ull << 48, 0, stream), "fill_normal");
+        eps = m.eps_buf;
+    }
+    for (int s0 = 0; s0 < Kp; s0 += m.cfg.max_chunk) {
+        const int n = std::min(m.cfg.max_chunk, Kp - s0);
+        LCHECK(launch_sample_z(nullptr, nullptr, eps + (size_t)s0 * d, n, 0, 1, d, 0.f, 0, nullptr, m.g_in.raw.ptr,
+                               m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, log_pn_dev + s0,
+                               stream), "sample_z");
+        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
+        if (!m.run_critic_chunk(n, d_g_dev + s0, stream)) return APVAE_ERR_CUDA;
+    }
+    return APVAE_OK;
+}
+
+int apvae_sample_images(apvae_handle* h, const float* z_dev, int n_total, uint8_t* out_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (n_total <= 0 || !z_dev || !out_dev) { m.err = "sample_images: bad arguments"; return APVAE_ERR_INVALID; }
+    const size_t per = (size_t)m.HW() * m.C();
+    for (int s0 = 0; s0 < n_total; s0 += m.cfg.max_chunk) {
+        const int n = std::min(m.cfg.max_chunk, n_total - s0);
+        LCHECK(stage_latents(m, z_dev + (size_t)s0 * m.cfg.z_dim, n, stream), "stage_latents");
+        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
+        LCHECK(launch_quantize_images(m.head_f32, m.head_ld(), (long long)n * m.HW(), m.C(), out_dev + s0 * per, stream),
+               "quantize");
+    }
+    return APVAE_OK;
+}
+
+int apvae_fill_normal(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, int truncated, void* stream) {
+    const int e = launch_fill_normal(out_dev, n, seed, offset, truncated, stream);
+    return e == 0 ? APVAE_OK : set_global_err(cudaGetErrorString((cudaError_t)e), APVAE_ERR_CUDA);
+}
+int apvae_fill_uniform(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, void* stream) {
+    const int e = launch_fill_uniform(out_dev, n, seed, offset, stream);
+    return e == 0 ? APVAE_OK : set_global_err(cudaGetErrorString((cudaError_t)e), APVAE_ERR_CUDA);
+}
+
+int apvae_launch_count(const apvae_handle* h, int64_t* launches) {
+    if (!h || !launches) return set_global_err("null argument", APVAE_ERR_INVALID);
+    *launches = h->m.launches;
+    return APVAE_OK;
+}
+int apvae_macs(const apvae_handle* h, double* q, double* g, double* d) {
+    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
+    if (q) *q = h->m.macs_q;
+    if (g) *g = h->m.macs_g;
+    if (d) *d = h->m.macs_d;
+    return APVAE_OK;
+}
+
+// ---------------------------------------------------------------- layer-level interface
+int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, apvae_plan** out) {
+    if (!terms || nterms <= 0 || !out || capacity_n <= 0) return set_global_err("plan_create: bad arguments", APVAE_ERR_INVALID);
+    std::vector<TermSpec> ts;
+    for (int i = 0; i < nterms; ++i) {
+        TermSpec t;
+        t.src = terms[i].src; t.transpose = terms[i].transpose; t.k = terms[i].k; t.stride = terms[i].stride;
+        t.cin = terms[i].cin; t.cout = terms[i].cout; t.in_h = terms[i].in_h; t.in_w = terms[i].in_w;
+        t.in_cp = terms[i].in_cp; t.kernel = terms[i].kernel; t.bias = terms[i].bias;
+        ts.push_back(t);
+    }
+    apvae_plan* p = new apvae_plan();
+    std::string e;
+    if (!plan_op(ts, capacity_n, &p->plan, &e)) { delete p; return set_global_err(e, APVAE_ERR_UNSUPPORTED); }
+    *out = p;
+    return APVAE_OK;
+}
+
+int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
+    if (!p || !info) return set_global_err("null argument", APVAE_ERR_INVALID);
+    const OpPlan& P = p->plan;
+    memset(info, 0, sizeof(*info));
+    info->kc = P.kc; info->npad = P.npad; info->nt = P.nt; info->n_tiles = P.n_tiles; info->cout = P.cout;
+    info->num_phases = P.num_phases;
+    for (int i = 0; i < 5; ++i) info->phase_begin[i] = P.phase_begin[i];
+    info->total_steps = (int)P.steps.size();
+    info->bw = P.bw; info->bh = P.bh; info->bn = P.bn; info->rows = P.rows; info->wg = P.wg; info->hg = P.hg;
+    info->tiles_x = P.tiles_x; info->tiles_y = P.tiles_y; info->ho = P.ho; info->wo = P.wo; info->os = P.os;
+    info->nsrc = P.nsrc; info->capacity_n = P.capacity_n;
+    for (int s = 0; s < P.nsrc; ++s) {
+        for (int i = 0; i < 5; ++i) { info->src_dims[s][i] = P.src[s].dims[i]; info->src_box[s][i] = P.src[s].box[i]; }
+        for (int i = 0; i < 4; ++i) info->src_strides[s][i] = P.src[s].strides[i];
+    }
+    info->macs_per_image = P.macs_per_image;
+    return APVAE_OK;
+}
+
+int apvae_plan_copy_steps(const apvae_plan* p, int32_t* out) {
+    if (!p || !out) return set_global_err("null argument", APVAE_ERR_INVALID);
+    for (size_t i = 0; i < p->plan.steps.size(); ++i) {
+        const TapStep& s = p->plan.steps[i];
+        out[5 * i + 0] = s.src; out[5 * i + 1] = s.dx; out[5 * i + 2] = s.dy; out[5 * i + 3] = s.ph; out[5 * i + 4] = s.c0;
+    }
+    return APVAE_OK;
+}
+int apvae_plan_copy_weights(const apvae_plan* p, uint16_t* out) {
+    if (!p || !out) return set_global_err("null argument", APVAE_ERR_INVALID);
+    memcpy(out, p->plan.wpack.data(), p->plan.wpack.size() * sizeof(uint16_t));
+    return APVAE_OK;
+}
+int apvae_plan_copy_bias(const apvae_plan* p, float* out) {
+    if (!p || !out) return set_global_err("null argument", APVAE_ERR_INVALID);
+    memcpy(out, p->plan.bias.data(), p->plan.bias.size() * sizeof(float));
+    return APVAE_OK;
+}
+int apvae_plan_destroy(apvae_plan* p) { delete p; return APVAE_OK; }
+
+int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid, const apvae_epilogue* epi) {
+    if (!p || !src_dev || !epi) return set_global_err("null argument", APVAE_ERR_INVALID);
+    DeviceInfo dev;
+    std::string e;
+    if (!device_open(device, &dev, &e)) return set_global_err(e, APVAE_ERR_NO_DEVICE);
+    Epilogue ep;
+    ep.out_raw = epi->out_raw_dev; ep.out_act = epi->out_act_dev; ep.ldo = epi->ldo;
+    ep.bf16_zero_from = epi->bf16_zero_from > 0 ? epi->bf16_zero_from : (1 << 30);
+    ep.out_f32 = epi->out_f32_dev; ep.ld_f32 = epi->ld_f32; ep.f32_cols = epi->f32_cols;
+    ep.res = epi->res_dev; ep.res_mode = epi->res_mode; ep.ld_res = epi->ld_res;
+    ep.mask = epi->mask_dev; ep.ld_mask = epi->ld_mask; ep.tanh_cols = epi->tanh_cols;
+    DevOp op;
+    op.name = "plan_run";
+    if (!devop_create(dev, p->plan, src_dev, ep, &op, &e)) return set_global_err(e, APVAE_ERR_CUDA);
+    int err = devop_launch(dev, op, n_valid, nullptr);
+    if (err == 0) err = (int)cudaDeviceSynchronize();
+    if (err != 0) return set_global_err(std::string("plan_run: ") + cudaGetErrorString((cudaError_t)err), APVAE_ERR_CUDA);
+    return APVAE_OK;
+}
+
+// ---------------------------------------------------------------- sampler (input-gradient programs)
+int apvae_energy_grad(apvae_handle* h, const float*, int, float*, float*, float*, void*) {
+    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
+    h->m.err = "energy_grad: input-gradient programs are not built in this version";
+    return APVAE_ERR_UNSUPPORTED;
+}
+int apvae_mala(apvae_handle* h, float*, int, int, float, const float*, const float*, uint64_t, float*, float*, float*, void*) {
+    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
+    h->m.err = "mala: input-gradient programs are not built in this version";
+    return APVAE_ERR_UNSUPPORTED;
+}
+
+}  // extern "C"

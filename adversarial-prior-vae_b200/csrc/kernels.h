@@ -1,0 +1,84 @@
+// Fused HBM-bound kernels of the estimator tail and the sampler (launchers).
+// All pointers are device pointers; every launcher returns a cudaError_t value.
+#pragma once
+#include <stdint.h>
+
+namespace apvae {
+
+// x fp32 [pixels, c] -> bf16 [pixels, cp] raw and leaky_relu(x) (cp = 16 k, zero padded).
+int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out_raw, void* out_act,
+                      float alpha, void* stream);
+
+// Reparameterised draw + log q(z|x) + log N(z;0,I)   (reference: zd.Normal sample/log_prob via
+// tfsnippet/distributions/wrapper.py:112,127-129; truncated_normal.py:142-149; dmm_cifar10.py:449-450,601-603)
+//   z[s,j] = mu[b,j] + exp(max(logstd[b,j], min_logstd)) * eps[s,j],  b = (s0 + s) % B
+//   (all per-sample pointers are already offset to the chunk; s0 = global index of its first sample)
+//   log_q[s], log_pn[s]; z written as fp32 [S,d] and as bf16 into the decoder input layout
+//   idx = s*zstride + (j / zc)*cpad + (j % zc)  (raw and, if z_act != null, leaky_relu).
+// mu == null: prior draw z = eps (log_q not written).
+int launch_sample_z(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
+                    float min_logstd, int truncated, float* z_f32, void* z_raw, void* z_act,
+                    long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn,
+                    void* stream);
+
+// log p(x|z) summed over pixels (reference: distributions/discretized.py:198-259 with the
+// dmm_cifar10.py:612-619 parameters; Bernoulli variant dmm_bernouli_fashion.py:619-626).
+//   head fp32 [S*HW, ld]: columns [0,C) = x_mean, [C,2C) = x_logstd (unless uniform_scale / bernoulli)
+//   x fp32 [B, HW*C]; local sample s scores image b = (s0 + s) % B.
+int launch_pixel_logprob(const float* head, int ld, const float* x, int S, int s0, int B, int HW, int C,
+                         int bernoulli, int uniform_scale, float beta, float min_log_scale,
+                         float* log_px, void* stream);
+
+// out[s] = dot(h[s, 0:n], w) + b     (D_psi's level_-1 dense, dmm_cifar10.py:561)
+int launch_rowdot(const float* h, int ld, const float* w, const float* b, int n, long long S, float* out,
+                  void* stream);
+
+// Per-image importance-sampling reductions over K (reference: variational/evaluation.py:9-39,
+// ops/misc.py:71-107, variational/objectives.py:9-42, dmm_cifar10.py:164-177,896-924).
+// per_image is [kPerImageRows][B] fp32.
+enum PerImageRow {
+    ROW_LL = 0,        // log-mean-exp_k (log px + log pN - log q)
+    ROW_LB = 1,        // mean_k of the same
+    ROW_ADV_LL = 2,    // log-mean-exp_k (log px - energy - max(logZ,-20) - log q)
+    ROW_ADV_LB = 3,
+    ROW_RECON = 4,     // mean_k log px
+    ROW_DG = 5,        // mean_k D(G(z))
+    ROW_LZ_MAX = 6,    // max_k (-energy - log q)
+    ROW_LZ_SUM = 7,    // sum_k exp(-energy - log q - max)
+    kPerImageRows = 8
+};
+int launch_is_reduce(const float* log_px, const float* log_q, const float* log_pn, const float* d_g,
+                     const float* z_f32, int K, int B, int d, float w_xi, float log_Z, float* per_image,
+                     void* stream);
+
+// Philox4x32-10 + Box-Muller standard normals (timed runs; parity runs feed eps).
+// truncated != 0: resample into [-2, 2] (tf.truncated_normal, truncated_normal.py:103).
+int launch_fill_normal(float* out, long long n, unsigned long long seed, unsigned long long offset,
+                       int truncated, void* stream);
+int launch_fill_uniform(float* out, long long n, unsigned long long seed, unsigned long long offset,
+                        void* stream);
+
+// MALA (reference: dmm_cifar10.py:197-226,241-252).
+//   propose : z' = z - alpha g + sqrt(2 alpha) eps  (fp32 + bf16 decoder-input copies)
+//   accept  : ratio, u < ratio select, history rows
+int launch_mala_propose(const float* z, const float* g, const float* eps, int n, int d, float alpha,
+                        float* z_prime, void* zp_raw, void* zp_act, long long zstride, int zc, int cpad,
+                        float lrelu_alpha, void* stream);
+int launch_mala_accept(float* z, float* e, float* g, float* pure, const float* z_prime, const float* e_prime,
+                       const float* g_prime, const float* pure_prime, const float* u, int n, int d,
+                       float alpha, float* hist_e, float* hist_pure, float* hist_ratio, void* stream);
+
+// energy E = w_xi * D + 0.5 |z|^2 and grad = w_xi * gz + z
+int launch_energy_combine(const float* d_g, const float* gz, const float* z, int n, int d, float w_xi,
+                          float* energy, float* grad, void* stream);
+
+// uint8 = round(clip(256 * x_mean / 2 + 127.5, 0, 255))   (dmm_cifar10.py:976-977,990,1067)
+int launch_quantize_images(const float* head, int ld, long long pixels, int C, uint8_t* out, void* stream);
+
+// v = max(v, lo)
+int launch_clip_min(float* v, long long n, float lo, void* stream);
+
+// copy the first `cols` columns of fp32 [rows, ld] into dense [rows, cols]; optional tanh not applied.
+int launch_gather_cols(const float* src, int ld, int col0, int cols, long long rows, float* dst, void* stream);
+
+}  // namespace apvae

@@ -1,0 +1,196 @@
+#include "model.h"
+
+#include <cuda_runtime.h>
+#include <string.h>
+#include "kernels.h"
+
+namespace apvae {
+
+Model::~Model() {
+    q_prog.clear(); g_prog.clear(); d_prog.clear();
+    for (void* p : allocs) cudaFree(p);
+    for (float* p : {eps_buf, log_px, log_q, log_pn, d_g})
+        if (p) cudaFree(p);
+}
+
+long long Model::z_stride() const {
+    if (cfg.arch == APVAE_ARCH_A) return (long long)g_base_h() * g_base_w() * pad16(zc());
+    return pad16(cfg.z_dim);
+}
+int Model::z_group() const { return cfg.arch == APVAE_ARCH_A ? zc() : cfg.z_dim; }
+int Model::z_cpad() const { return cfg.arch == APVAE_ARCH_A ? pad16(zc()) : pad16(cfg.z_dim); }
+float Model::w_xi() const { return cfg.pull_back_energy_weight * (1.f / (1.f + expf(-xi_raw))); }
+
+Tensor Model::alloc_act(int n, int h, int w, int c) {
+    Tensor t;
+    t.n = n; t.h = h; t.w = w; t.c = c; t.cp = pad16(c);
+    const size_t bytes = t.elems() * 2;
+    if (cudaMalloc(&t.ptr, bytes) != cudaSuccess) { t.ptr = nullptr; err = "cudaMalloc failed (activation arena)"; return t; }
+    cudaMemset(t.ptr, 0, bytes);
+    allocs.push_back(t.ptr);
+    return t;
+}
+
+float* Model::alloc_f32(size_t n) {
+    float* p = nullptr;
+    if (cudaMalloc(&p, n * sizeof(float)) != cudaSuccess) { err = "cudaMalloc failed (fp32 buffer)"; return nullptr; }
+    cudaMemset(p, 0, n * sizeof(float));
+    allocs.push_back(p);
+    return p;
+}
+
+const HostArr* Model::W_(const std::string& name, std::initializer_list<int64_t> shape) {
+    auto it = weights.find(name);
+    if (it == weights.end()) { err = "missing variable '" + name + "'"; return nullptr; }
+    if (it->second.shape != std::vector<int64_t>(shape)) { err = "variable '" + name + "' has the wrong shape"; return nullptr; }
+    return &it->second;
+}
+
+bool Model::add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms,
+                   const std::vector<const void*>& srcs, const Epilogue& epi, int cap, double* macs) {
+    OpPlan plan;
+    std::string perr;
+    if (!plan_op(terms, cap, &plan, &perr)) return fail("plan " + name + ": " + perr);
+    if ((int)srcs.size() != plan.nsrc) return fail("plan " + name + ": source count mismatch");
+    std::unique_ptr<DevOp> op(new DevOp());
+    op->name = name;
+    if (!devop_create(dev, plan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
+    if (macs) *macs += plan.macs_per_image;
+    prog.push_back(std::move(op));
+    return true;
+}
+
+static TermSpec term(int src, bool transpose, int k, int stride, int cin, int cout, const Tensor& in,
+                     const HostArr* kernel, const HostArr* bias) {
+    TermSpec t;
+    t.src = src; t.transpose = transpose ? 1 : 0; t.k = k; t.stride = stride; t.cin = cin; t.cout = cout;
+    t.in_h = in.h; t.in_w = in.w; t.in_cp = in.cp;
+    t.kernel = kernel->v.data();
+    t.bias = bias ? bias->v.data() : nullptr;
+    return t;
+}
+
+// resnet_conv2d_block (resnet.py:272-364, resize_at_exit=True):
+//   op1: r = lrelu(conv_k,1(lrelu(x)) + b0)                       [Cin -> Cin]
+//   op2: out = conv_k,s(r) + b1 + (shortcut: conv_1,s(x) + bs | x) [Cin -> Cout]
+bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
+                       bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape) {
+    const std::string pre = root + "/" + b.scope + "/";
+    const int cin = in.c(), cout = b.cout, k = b.k, s = b.stride, H = in.h(), Wd = in.w();
+    const bool use_sc = (s != 1) || (cin != cout);
+    const HostArr *k0 = W_(pre + "residual/conv_0/kernel", {k, k, cin, cin}), *b0 = W_(pre + "residual/conv_0/bias", {cin});
+    const HostArr *k1 = W_(pre + "residual/conv_1/kernel", {k, k, cin, cout}), *b1 = W_(pre + "residual/conv_1/bias", {cout});
+    if (!k0 || !b0 || !k1 || !b1) return false;
+    Tensor r = alloc_act(cap, H, Wd, cin);
+    if (!r.ptr) return false;
+    {
+        Epilogue e; e.out_act = r.ptr; e.ldo = r.cp;
+        if (!add_op(prog, pre + "conv_0", {term(0, false, k, 1, cin, cin, in.act, k0, b0)}, {in.act.ptr}, e, cap, macs)) return false;
+    }
+    const int Ho = (H + s - 1) / s, Wo = (Wd + s - 1) / s;
+    Pair o;
+    if (need_raw) { o.raw = alloc_act(cap, Ho, Wo, cout); if (!o.raw.ptr) return false; }
+    if (need_act) { o.act = alloc_act(cap, Ho, Wo, cout); if (!o.act.ptr) return false; }
+    Epilogue e;
+    e.out_raw = o.raw.ptr; e.out_act = o.act.ptr; e.ldo = pad16(cout);
+    std::vector<TermSpec> terms = {term(0, false, k, s, cin, cout, r, k1, b1)};
+    std::vector<const void*> srcs = {r.ptr};
+    if (use_sc) {
+        const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cin, cout}), *bs = W_(pre + "shortcut/bias", {cout});
+        if (!ks || !bs) return false;
+        terms.push_back(term(1, false, 1, s, cin, cout, in.raw, ks, bs));
+        srcs.push_back(in.raw.ptr);
+    } else {
+        e.res = in.raw.ptr; e.res_mode = RES_SAME; e.ld_res = in.raw.cp;
+    }
+    if (!add_op(prog, pre + "conv_1", terms, srcs, e, cap, macs)) return false;
+    if (tape) {
+        BlockTape t; t.scope = pre; t.deconv = false; t.use_shortcut = use_sc; t.k = k; t.stride = s;
+        t.cin = cin; t.cout = cout; t.in = in; t.r_act = r; t.out = o;
+        tape->push_back(t);
+    }
+    *out = o;
+    return true;
+}
+
+// resnet_deconv2d_block (resnet.py:369-485, resize_at_exit=False):
+//   op1: r = lrelu(deconv_k,s(lrelu(x)) + b0)                      [Cin -> Cout]
+//   op2: out = deconv_k,1(r) + b1 + shortcut                       [Cout -> Cout]
+// shortcut = deconv_1,s(x) + bs: fused as a second term when s == 1 and the padded channel
+// counts agree; otherwise computed by its own 1x1 op at the INPUT resolution and added in
+// op2's epilogue (for s == 2 only the even output pixels receive x W, conv2d_.py:464-471
+// semantics of a 1x1 stride-2 transpose; bs goes into op2's bias).
+bool Model::deconv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
+                         bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape) {
+    const std::string pre = root + "/" + b.scope + "/";
+    const int cin = in.c(), cout = b.cout, k = b.k, s = b.stride, H = in.h(), Wd = in.w();
+    const bool use_sc = (s != 1) || (cin != cout);
+    const HostArr *k0 = W_(pre + "residual/conv_0/kernel", {k, k, cout, cin}), *b0 = W_(pre + "residual/conv_0/bias", {cout});
+    const HostArr *k1 = W_(pre + "residual/conv_1/kernel", {k, k, cout, cout}), *b1 = W_(pre + "residual/conv_1/bias", {cout});
+    if (!k0 || !b0 || !k1 || !b1) return false;
+    const int Ho = H * s, Wo = Wd * s;
+    Tensor r = alloc_act(cap, Ho, Wo, cout);
+    if (!r.ptr) return false;
+    {
+        Epilogue e; e.out_act = r.ptr; e.ldo = r.cp;
+        if (!add_op(prog, pre + "conv_0", {term(0, true, k, s, cin, cout, in.act, k0, b0)}, {in.act.ptr}, e, cap, macs)) return false;
+    }
+    Pair o;
+    if (need_raw) { o.raw = alloc_act(cap, Ho, Wo, cout); if (!o.raw.ptr) return false; }
+    if (need_act) { o.act = alloc_act(cap, Ho, Wo, cout); if (!o.act.ptr) return false; }
+    Epilogue e;
+    e.out_raw = o.raw.ptr; e.out_act = o.act.ptr; e.ldo = pad16(cout);
+    HostArr bias_sum = *b1;
+    std::vector<TermSpec> terms = {term(0, true, k, 1, cout, cout, r, k1, &bias_sum)};
+    std::vector<const void*> srcs = {r.ptr};
+    if (use_sc) {
+        const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cout, cin}), *bs = W_(pre + "shortcut/bias", {cout});
+        if (!ks || !bs) return false;
+        if (s == 1 && in.raw.cp == r.cp) {
+            terms.push_back(term(1, true, 1, 1, cin, cout, in.raw, ks, bs));
+            srcs.push_back(in.raw.ptr);
+        } else {
+            Tensor sc = alloc_act(cap, H, Wd, cout);
+            if (!sc.ptr) return false;
+            Epilogue es; es.out_raw = sc.ptr; es.ldo = sc.cp;
+            if (!add_op(prog, pre + "shortcut", {term(0, true, 1, 1, cin, cout, in.raw, ks, nullptr)}, {in.raw.ptr}, es, cap, macs)) return false;
+            for (int i = 0; i < cout; ++i) bias_sum.v[i] += bs->v[i];
+            terms[0].bias = bias_sum.v.data();
+            e.res = sc.ptr; e.res_mode = (s == 1) ? RES_SAME : RES_EVEN; e.ld_res = sc.cp;
+        }
+    } else {
+        e.res = in.raw.ptr; e.res_mode = RES_SAME; e.ld_res = in.raw.cp;
+    }
+    if (!add_op(prog, pre + "conv_1", terms, srcs, e, cap, macs)) return false;
+    if (tape) {
+        BlockTape t; t.scope = pre; t.deconv = true; t.use_shortcut = use_sc; t.k = k; t.stride = s;
+        t.cin = cin; t.cout = cout; t.in = in; t.r_act = r; t.out = o;
+        tape->push_back(t);
+    }
+    *out = o;
+    return true;
+}
+
+// spt.layers.dense (dense_.py:142-147) over a flattened NHWC tensor: a 1x1 conv on a 1x1 image
+// with Cin = in_features.  `in_flat` must have cp == c so the flatten order matches reshape_tail.
+bool Model::dense_op(Program& prog, const std::string& name, const Tensor& in_flat, int in_features, int out_features,
+                     const Epilogue& epi, int cap, double* macs) {
+    const HostArr *kk = W_(name + "/kernel", {in_features, out_features}), *bb = W_(name + "/bias", {out_features});
+    if (!kk || !bb) return false;
+    Tensor v = in_flat;
+    v.h = 1; v.w = 1; v.c = in_features; v.cp = pad16(in_features);
+    if ((size_t)v.cp * 1 != (size_t)in_flat.h * in_flat.w * in_flat.cp)
+        return fail("dense " + name + ": flattened input has channel padding");
+    return add_op(prog, name, {term(0, false, 1, 1, in_features, out_features, v, kk, bb)}, {v.ptr}, epi, cap, macs);
+}
+
+bool Model::run_program(Program& prog, int n, void* stream) {
+    for (auto& op : prog) {
+        const int e = devop_launch(dev, *op, n, stream);
+        if (e != 0) return fail("launch " + op->name + ": " + cudaGetErrorString((cudaError_t)e));
+        ++launches;
+    }
+    return true;
+}
+
+}  // namespace apvae

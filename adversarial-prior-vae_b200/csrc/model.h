@@ -1,0 +1,137 @@
+// Network programs of the hot path: q_net, G_theta (+ likelihood heads) and
+// D_psi of the three script families, lowered to sequences of tap-GEMM ops.
+// Reference builders: experiment/dmm/dmm_cifar10.py:418-452,466-500,535-562;
+// dmm_for_sampling.py:421-460,476-514,551-576; dmm_bernouli_fashion.py:432-478,492-521,546-573.
+#pragma once
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+#include "../../include/apvae.h"
+#include "runtime.h"
+
+namespace apvae {
+
+struct HostArr {
+    std::vector<float> v;
+    std::vector<int64_t> shape;
+};
+
+struct BlockSpec {
+    const char* scope;
+    int cout, k, stride;
+};
+
+struct WeightInfo {
+    std::string name;
+    std::vector<int64_t> shape;
+};
+
+// Architecture tables (shared by the schema query and the builder).
+std::vector<BlockSpec> q_blocks(const apvae_config& c);
+std::vector<BlockSpec> g_blocks(const apvae_config& c);
+std::vector<BlockSpec> d_blocks(const apvae_config& c);
+std::vector<WeightInfo> weight_schema(const apvae_config& c);
+bool validate_config(const apvae_config& c, std::string* err);
+
+struct Tensor {
+    void* ptr = nullptr;
+    int n = 0, h = 0, w = 0, c = 0, cp = 0;
+    size_t elems() const { return (size_t)n * h * w * cp; }
+};
+struct Pair {
+    Tensor raw, act;
+    int h() const { return raw.ptr ? raw.h : act.h; }
+    int w() const { return raw.ptr ? raw.w : act.w; }
+    int c() const { return raw.ptr ? raw.c : act.c; }
+};
+
+// Saved forward state of one resnet block (for the input-gradient programs).
+struct BlockTape {
+    std::string scope;
+    bool deconv = false, use_shortcut = false;
+    int k = 3, stride = 1, cin = 0, cout = 0;
+    Pair in;        // block input (raw + act)
+    Tensor r_act;   // leaky_relu(conv_0 output)
+    Pair out;
+};
+
+typedef std::vector<std::unique_ptr<DevOp>> Program;
+
+class Model {
+public:
+    apvae_config cfg;
+    DeviceInfo dev;
+    mutable std::string err;
+    std::map<std::string, HostArr> weights;
+    float xi_raw = 0.f, beta = 0.f, log_Z = 1.f;
+    bool built = false;
+    int64_t launches = 0;
+    double macs_q = 0, macs_g = 0, macs_d = 0;
+
+    ~Model();
+    bool build();   // after weights are loaded
+
+    // forward pieces (all on `stream`)
+    bool run_encoder(const float* x_dev, int B, void* stream);                  // -> q_mu, q_logstd
+    bool run_decoder_chunk(int n, void* stream);                                // g_in -> head_f32, d_in
+    bool run_critic_chunk(int n, float* d_out, void* stream);                   // d_in -> d_out[n]
+    bool critic_of_images(const float* x_dev, int N, float* d_out, void* stream);
+    bool ensure_sample_buffers(size_t samples);
+
+    // geometry
+    int H() const { return cfg.x_h; }
+    int W() const { return cfg.x_w; }
+    int C() const { return cfg.x_c; }
+    int HW() const { return cfg.x_h * cfg.x_w; }
+    int head_ld() const { return (cfg.bernoulli || cfg.arch == APVAE_ARCH_M) ? cfg.x_c : 2 * cfg.x_c; }
+    int g_base_h() const { return cfg.arch == APVAE_ARCH_B ? 8 : cfg.x_h / 4; }
+    int g_base_w() const { return cfg.arch == APVAE_ARCH_B ? 8 : cfg.x_w / 4; }
+    int zc() const { return 16 * cfg.z_dim / cfg.x_h / cfg.x_w; }
+    // decoder-input layout of z (see kernels.h launch_sample_z)
+    long long z_stride() const;
+    int z_group() const;
+    int z_cpad() const;
+    float w_xi() const;
+
+    // device state
+    Program q_prog, g_prog, d_prog;
+    Pair q_in;                 // [max_batch, H, W, 16]
+    float* q_mu = nullptr;     // [max_batch, z_dim]
+    float* q_logstd = nullptr;
+    Pair g_in;                 // decoder input
+    float* head_f32 = nullptr; // [max_chunk*HW, head_ld]
+    Pair d_in;                 // [max_chunk, H, W, 16]
+    float* d64 = nullptr;      // [max_chunk, 64]
+    float* d_last_w = nullptr; // level_-1 kernel [64], bias [1]
+    float* d_last_b = nullptr;
+    std::vector<BlockTape> g_tape, d_tape;
+    Tensor g_head_in;          // raw trunk output feeding the heads
+    Tensor d_flat;             // raw output of D's last block
+
+    // per-call sample buffers (grow-only)
+    size_t sample_cap = 0;
+    float *eps_buf = nullptr, *log_px = nullptr, *log_q = nullptr, *log_pn = nullptr, *d_g = nullptr;
+    float* z_tmp = nullptr;    // [max_chunk, z_dim] scratch
+
+    std::vector<void*> allocs;
+    bool fail(const std::string& m) const { err = m; return false; }
+
+    Tensor alloc_act(int n, int h, int w, int c);
+    float* alloc_f32(size_t n);
+    const HostArr* W_(const std::string& name, std::initializer_list<int64_t> shape);
+    bool add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms,
+                const std::vector<const void*>& srcs, const Epilogue& epi, int cap, double* macs);
+    bool conv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
+                    bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape);
+    bool deconv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
+                      bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape);
+    bool dense_op(Program& prog, const std::string& name, const Tensor& in_flat, int in_features, int out_features,
+                  const Epilogue& epi, int cap, double* macs);
+    bool build_q();
+    bool build_g();
+    bool build_d();
+    bool run_program(Program& prog, int n, void* stream);
+};
+
+}  // namespace apvae

@@ -1,0 +1,222 @@
+// Program construction and forward drivers for q_net / G_theta / D_psi.
+#include <cuda_runtime.h>
+#include <string.h>
+#include "kernels.h"
+#include "model.h"
+
+namespace apvae {
+
+bool Model::build_q() {
+    const int cap = cfg.max_batch;
+    q_in.raw = alloc_act(cap, H(), W(), C());
+    q_in.act = alloc_act(cap, H(), W(), C());
+    q_mu = alloc_f32((size_t)cap * cfg.z_dim);
+    q_logstd = alloc_f32((size_t)cap * cfg.z_dim);
+    if (!q_in.raw.ptr || !q_in.act.ptr || !q_mu || !q_logstd) return false;
+    const std::vector<BlockSpec> blocks = q_blocks(cfg);
+    Pair h = q_in;
+    for (size_t i = 0; i < blocks.size(); ++i) {
+        const bool last = (i + 1 == blocks.size());
+        // arch A heads are resnet blocks (need raw + act); B/M heads are dense on the raw flatten
+        const bool need_act = !last || cfg.arch == APVAE_ARCH_A;
+        Pair o;
+        if (!conv_block(q_prog, "q_net", blocks[i], h, true, need_act, cap, &o, &macs_q, nullptr)) return false;
+        h = o;
+    }
+    if (cfg.arch == APVAE_ARCH_A) {          // dmm_cifar10.py:440-446
+        const int zcn = zc();
+        float* outs[2] = {q_mu, q_logstd};
+        const char* names[2] = {"z_mean", "z_logstd"};
+        for (int t = 0; t < 2; ++t) {
+            // a resnet_conv2d_block whose conv_1 output goes straight to fp32 [B, 8*8*zc] = [B, z_dim]
+            const std::string pre = std::string("q_net/") + names[t] + "/";
+            const int cin = h.c();
+            const HostArr *k0 = W_(pre + "residual/conv_0/kernel", {3, 3, cin, cin}), *b0 = W_(pre + "residual/conv_0/bias", {cin});
+            const HostArr *k1 = W_(pre + "residual/conv_1/kernel", {3, 3, cin, zcn}), *b1 = W_(pre + "residual/conv_1/bias", {zcn});
+            if (!k0 || !b0 || !k1 || !b1) return false;
+            Tensor r = alloc_act(cap, h.h(), h.w(), cin);
+            if (!r.ptr) return false;
+            Epilogue e0; e0.out_act = r.ptr; e0.ldo = r.cp;
+            TermSpec t0; t0.src = 0; t0.transpose = 0; t0.k = 3; t0.stride = 1; t0.cin = cin; t0.cout = cin;
+            t0.in_h = h.h(); t0.in_w = h.w(); t0.in_cp = h.act.cp; t0.kernel = k0->v.data(); t0.bias = b0->v.data();
+            if (!add_op(q_prog, pre + "conv_0", {t0}, {h.act.ptr}, e0, cap, &macs_q)) return false;
+            Epilogue e1; e1.out_f32 = outs[t]; e1.ld_f32 = zcn; e1.f32_cols = zcn;
+            TermSpec t1 = t0; t1.cout = zcn; t1.in_cp = r.cp; t1.kernel = k1->v.data(); t1.bias = b1->v.data();
+            std::vector<TermSpec> terms = {t1};
+            std::vector<const void*> srcs = {r.ptr};
+            if (cin != zcn) {
+                const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cin, zcn}), *bs = W_(pre + "shortcut/bias", {zcn});
+                if (!ks || !bs) return false;
+                TermSpec ts = t1; ts.src = 1; ts.k = 1; ts.in_cp = h.raw.cp; ts.kernel = ks->v.data(); ts.bias = bs->v.data();
+                terms.push_back(ts);
+                srcs.push_back(h.raw.ptr);
+            } else {
+                e1.res = h.raw.ptr; e1.res_mode = RES_SAME; e1.ld_res = h.raw.cp;
+            }
+            if (!add_op(q_prog, pre + "conv_1", terms, srcs, e1, cap, &macs_q)) return false;
+        }
+    } else {                                  // dmm_for_sampling.py:441-446
+        const int feat = h.h() * h.w() * h.c();
+        if (h.raw.cp != h.raw.c) return fail("q_net flatten has channel padding");
+        Epilogue e; e.out_f32 = q_mu; e.ld_f32 = cfg.z_dim; e.f32_cols = cfg.z_dim;
+        if (!dense_op(q_prog, "q_net/z_mean", h.raw, feat, cfg.z_dim, e, cap, &macs_q)) return false;
+        e.out_f32 = q_logstd;
+        if (!dense_op(q_prog, "q_net/z_logstd", h.raw, feat, cfg.z_dim, e, cap, &macs_q)) return false;
+    }
+    return true;
+}
+
+bool Model::build_g() {
+    const int cap = cfg.max_chunk;
+    const int gh = g_base_h(), gw = g_base_w();
+    std::vector<BlockTape>* tape = cfg.enable_grad ? &g_tape : nullptr;
+    Pair h;
+    if (cfg.arch == APVAE_ARCH_A) {           // dmm_cifar10.py:478-480: z reshaped to [8,8,zc]
+        g_in.raw = alloc_act(cap, gh, gw, zc());
+        g_in.act = alloc_act(cap, gh, gw, zc());
+        if (!g_in.raw.ptr || !g_in.act.ptr) return false;
+        h = g_in;
+    } else {                                  // dmm_for_sampling.py:486-492: dense(z, 64*8*8) -> [8,8,64]
+        g_in.raw = alloc_act(cap, 1, 1, cfg.z_dim);
+        if (!g_in.raw.ptr) return false;
+        const int feat = 64 * gh * gw;
+        h.raw = alloc_act(cap, gh, gw, 64);
+        h.act = alloc_act(cap, gh, gw, 64);
+        if (!h.raw.ptr || !h.act.ptr) return false;
+        Epilogue e; e.out_raw = h.raw.ptr; e.out_act = h.act.ptr; e.ldo = feat;
+        if (!dense_op(g_prog, "G_theta/level_0", g_in.raw, cfg.z_dim, feat, e, cap, &macs_g)) return false;
+    }
+    const std::vector<BlockSpec> blocks = g_blocks(cfg);
+    for (size_t i = 0; i < blocks.size(); ++i) {
+        const bool last = (i + 1 == blocks.size());
+        Pair o;
+        if (!deconv_block(g_prog, "G_theta", blocks[i], h, true, !last, cap, &o, &macs_g, tape)) return false;
+        h = o;
+    }
+    g_head_in = h.raw;
+    // heads (dmm_cifar10.py:489-496): one 1x1 GEMM for [x_mean | x_logstd]; tanh on the x_mean columns.
+    // The bf16 copy of x_mean (raw + leaky_relu) is D_psi's input.
+    const int cg = h.c(), Cx = C();
+    d_in.raw = alloc_act(cap, H(), W(), Cx);
+    d_in.act = alloc_act(cap, H(), W(), Cx);
+    head_f32 = alloc_f32((size_t)cap * HW() * head_ld());
+    if (!d_in.raw.ptr || !d_in.act.ptr || !head_f32) return false;
+    HostArr kcat, bcat;
+    const bool has_std = head_ld() == 2 * Cx;
+    const std::string mean_name = cfg.arch == APVAE_ARCH_M ? "G_theta/feature_map_mean_to_pixel" : "G_theta/x_mean";
+    const HostArr *km = W_(mean_name + "/kernel", {1, 1, cg, Cx}), *bm = W_(mean_name + "/bias", {Cx});
+    if (!km || !bm) return false;
+    const int nout = head_ld();
+    kcat.v.assign((size_t)cg * nout, 0.f);
+    bcat.v.assign(nout, 0.f);
+    const HostArr *ksd = nullptr, *bsd = nullptr;
+    if (has_std) {
+        ksd = W_("G_theta/x_logstd/kernel", {1, 1, cg, Cx});
+        bsd = W_("G_theta/x_logstd/bias", {Cx});
+        if (!ksd || !bsd) return false;
+    }
+    for (int ci = 0; ci < cg; ++ci)
+        for (int c = 0; c < Cx; ++c) {
+            kcat.v[(size_t)ci * nout + c] = km->v[(size_t)ci * Cx + c];
+            if (has_std) kcat.v[(size_t)ci * nout + Cx + c] = ksd->v[(size_t)ci * Cx + c];
+        }
+    for (int c = 0; c < Cx; ++c) { bcat.v[c] = bm->v[c]; if (has_std) bcat.v[Cx + c] = bsd->v[c]; }
+    TermSpec t; t.src = 0; t.transpose = 0; t.k = 1; t.stride = 1; t.cin = cg; t.cout = nout;
+    t.in_h = h.h(); t.in_w = h.w(); t.in_cp = h.raw.cp; t.kernel = kcat.v.data(); t.bias = bcat.v.data();
+    Epilogue e;
+    e.out_raw = d_in.raw.ptr; e.out_act = d_in.act.ptr; e.ldo = d_in.raw.cp; e.bf16_zero_from = Cx;
+    e.out_f32 = head_f32; e.ld_f32 = nout; e.f32_cols = nout; e.tanh_cols = Cx;
+    return add_op(g_prog, "G_theta/heads", {t}, {h.raw.ptr}, e, cap, &macs_g);
+}
+
+bool Model::build_d() {
+    const int cap = cfg.max_chunk;
+    std::vector<BlockTape>* tape = cfg.enable_grad ? &d_tape : nullptr;
+    const std::vector<BlockSpec> blocks = d_blocks(cfg);
+    Pair h = d_in;
+    for (size_t i = 0; i < blocks.size(); ++i) {
+        const bool last = (i + 1 == blocks.size());
+        Pair o;
+        if (!conv_block(d_prog, "D_psi", blocks[i], h, true, !last, cap, &o, &macs_d, tape)) return false;
+        h = o;
+    }
+    d_flat = h.raw;
+    if (h.raw.cp != h.raw.c) return fail("D_psi flatten has channel padding");
+    const int feat = h.h() * h.w() * h.c();
+    d64 = alloc_f32((size_t)cap * 64);
+    if (!d64) return false;
+    Epilogue e; e.out_f32 = d64; e.ld_f32 = 64; e.f32_cols = 64;
+    if (!dense_op(d_prog, "D_psi/level_-2", h.raw, feat, 64, e, cap, &macs_d)) return false;   // dmm_cifar10.py:559
+    const HostArr *kl = W_("D_psi/level_-1/kernel", {64, 1}), *bl = W_("D_psi/level_-1/bias", {1});
+    if (!kl || !bl) return false;
+    d_last_w = alloc_f32(64);
+    d_last_b = alloc_f32(1);
+    if (!d_last_w || !d_last_b) return false;
+    cudaMemcpy(d_last_w, kl->v.data(), 64 * sizeof(float), cudaMemcpyHostToDevice);
+    cudaMemcpy(d_last_b, bl->v.data(), sizeof(float), cudaMemcpyHostToDevice);
+    macs_d += 64;
+    return true;
+}
+
+bool Model::build() {
+    if (built) return fail("weights already loaded (create a new handle to reload)");
+    if (cudaSetDevice(dev.device) != cudaSuccess) return fail("cudaSetDevice failed");
+    if (!build_q() || !build_g() || !build_d()) return false;
+    z_tmp = alloc_f32((size_t)cfg.max_chunk * cfg.z_dim);
+    if (!z_tmp) return false;
+    if (cudaDeviceSynchronize() != cudaSuccess) return fail("device error while uploading weights");
+    built = true;
+    return true;
+}
+
+bool Model::ensure_sample_buffers(size_t samples) {
+    if (samples <= sample_cap) return true;
+    for (float** p : {&eps_buf, &log_px, &log_q, &log_pn, &d_g}) {
+        if (*p) cudaFree(*p);
+        *p = nullptr;
+    }
+    sample_cap = 0;
+    if (cudaMalloc(&eps_buf, samples * cfg.z_dim * sizeof(float)) != cudaSuccess) return fail("cudaMalloc eps");
+    for (float** p : {&log_px, &log_q, &log_pn, &d_g})
+        if (cudaMalloc(p, samples * sizeof(float)) != cudaSuccess) return fail("cudaMalloc per-sample stats");
+    sample_cap = samples;
+    return true;
+}
+
+#define KCHECK(call, what)                                                                        \
+    do {                                                                                          \
+        const int _e = (call);                                                                    \
+        ++launches;                                                                               \
+        if (_e != 0) return fail(std::string(what) + ": " + cudaGetErrorString((cudaError_t)_e)); \
+    } while (0)
+
+bool Model::run_encoder(const float* x_dev, int B, void* stream) {
+    if (B > cfg.max_batch) return fail("batch exceeds max_batch");
+    KCHECK(launch_pack_image(x_dev, (long long)B * HW(), C(), q_in.raw.cp, q_in.raw.ptr, q_in.act.ptr, 0.2f, stream),
+           "pack_image");
+    if (!run_program(q_prog, B, stream)) return false;
+    // maybe_clip_value(z_logstd, min_val=min_logstd_of_q)  (dmm_cifar10.py:449)
+    KCHECK(launch_clip_min(q_logstd, (long long)B * cfg.z_dim, cfg.min_logstd_of_q, stream), "clip_min");
+    return true;
+}
+
+bool Model::run_decoder_chunk(int n, void* stream) { return run_program(g_prog, n, stream); }
+
+bool Model::run_critic_chunk(int n, float* d_out, void* stream) {
+    if (!run_program(d_prog, n, stream)) return false;
+    KCHECK(launch_rowdot(d64, 64, d_last_w, d_last_b, 64, n, d_out, stream), "rowdot");   // dmm_cifar10.py:561-562
+    return true;
+}
+
+bool Model::critic_of_images(const float* x_dev, int N, float* d_out, void* stream) {
+    const size_t per = (size_t)HW() * C();
+    for (int s0 = 0; s0 < N; s0 += cfg.max_chunk) {
+        const int n = std::min(cfg.max_chunk, N - s0);
+        KCHECK(launch_pack_image(x_dev + (size_t)s0 * per, (long long)n * HW(), C(), d_in.raw.cp, d_in.raw.ptr,
+                                 d_in.act.ptr, 0.2f, stream), "pack_image");
+        if (!run_critic_chunk(n, d_out + s0, stream)) return false;
+    }
+    return true;
+}
+
+}  // namespace apvae

@@ -1,0 +1,201 @@
+#include "planner.h"
+
+#include <string.h>
+#include <algorithm>
+
+namespace apvae {
+
+void same_padding(int in, int k, int s, int* out, int* lo, int* hi) {
+    const int o = (in + s - 1) / s;
+    const int total = std::max((o - 1) * s + k - in, 0);
+    *out = o;
+    *lo = total / 2;
+    *hi = total - total / 2;
+}
+
+uint16_t f32_to_bf16(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7F800000u) == 0x7F800000u && (u & 0x007FFFFFu)) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7FFFu + ((u >> 16) & 1u);   // round to nearest even
+    return (uint16_t)(u >> 16);
+}
+
+float bf16_to_f32(uint16_t h) {
+    uint32_t u = (uint32_t)h << 16;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
+static int floor_div2(int t) { return (t >= 0) ? t / 2 : -((-t + 1) / 2); }
+
+namespace {
+
+struct Tap {
+    int di, dj;       // kernel tap
+    int dx, dy, ph;   // source box shift and row phase
+    int cbase;        // channel base in the innermost dim (column phase * Cp for s2d)
+};
+
+// Taps of one term for output phase (py, px) (phase only meaningful for a
+// stride-2 transposed conv).
+std::vector<Tap> enumerate_taps(const TermSpec& t, int py, int px) {
+    std::vector<Tap> taps;
+    int o, lo_h, lo_w, hi;
+    if (!t.transpose && t.stride == 1) {
+        same_padding(t.in_h, t.k, 1, &o, &lo_h, &hi);
+        same_padding(t.in_w, t.k, 1, &o, &lo_w, &hi);
+        for (int di = 0; di < t.k; ++di)
+            for (int dj = 0; dj < t.k; ++dj)
+                taps.push_back({di, dj, dj - lo_w, di - lo_h, 0, 0});
+    } else if (!t.transpose) {   // stride-2 conv through the space-to-depth view
+        same_padding(t.in_h, t.k, 2, &o, &lo_h, &hi);
+        same_padding(t.in_w, t.k, 2, &o, &lo_w, &hi);
+        for (int di = 0; di < t.k; ++di)
+            for (int dj = 0; dj < t.k; ++dj) {
+                const int ty = di - lo_h, tx = dj - lo_w;
+                const int qy = floor_div2(ty), qx = floor_div2(tx);
+                taps.push_back({di, dj, qx, qy, ty - 2 * qy, (tx - 2 * qx) * t.in_cp});
+            }
+    } else if (t.stride == 1) {  // transposed conv, stride 1: i = Y - di + pad_lo
+        same_padding(t.in_h, t.k, 1, &o, &lo_h, &hi);
+        same_padding(t.in_w, t.k, 1, &o, &lo_w, &hi);
+        for (int di = 0; di < t.k; ++di)
+            for (int dj = 0; dj < t.k; ++dj)
+                taps.push_back({di, dj, lo_w - dj, lo_h - di, 0, 0});
+    } else {                     // transposed conv, stride 2: Y = 2 i + di - pad_lo
+        same_padding(t.in_h * 2, t.k, 2, &o, &lo_h, &hi);
+        same_padding(t.in_w * 2, t.k, 2, &o, &lo_w, &hi);
+        for (int di = 0; di < t.k; ++di) {
+            if ((py + lo_h - di) & 1) continue;
+            for (int dj = 0; dj < t.k; ++dj) {
+                if ((px + lo_w - dj) & 1) continue;
+                taps.push_back({di, dj, floor_div2(px + lo_w - dj), floor_div2(py + lo_h - di), 0, 0});
+            }
+        }
+    }
+    return taps;
+}
+
+}  // namespace
+
+bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, std::string* err) {
+    auto fail = [&](const char* m) { if (err) *err = m; return false; };
+    if (terms.empty() || terms.size() > (size_t)kMaxSrc) return fail("1..3 terms expected");
+    OpPlan& P = *plan;
+    P = OpPlan();
+    P.capacity_n = capacity_n;
+    const TermSpec& t0 = terms[0];
+    const int cp = t0.in_cp;
+    P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
+    P.cout = t0.cout;
+    P.npad = pad16(t0.cout);
+    bool phased = false;
+    for (const TermSpec& t : terms) {
+        if (t.stride != 1 && t.stride != 2) return fail("stride must be 1 or 2");
+        if (t.in_cp % 16 != 0 || t.in_cp < t.cin) return fail("in_cp must be a multiple of 16 and >= cin");
+        if (t.in_cp != cp) return fail("terms of one op must share the padded channel count");
+        if (t.cout != t0.cout) return fail("terms of one op must share cout");
+        if (t.src < 0 || t.src >= kMaxSrc) return fail("bad src index");
+        if (t.transpose && t.stride == 2) phased = true;
+        if (!t.transpose && t.stride == 2 && ((t.in_h | t.in_w) & 1)) return fail("stride-2 conv needs even input size");
+        int oh, ow;
+        if (t.transpose) { oh = t.in_h * t.stride; ow = t.in_w * t.stride; }
+        else { oh = (t.in_h + t.stride - 1) / t.stride; ow = (t.in_w + t.stride - 1) / t.stride; }
+        if (&t == &t0) { P.ho = oh; P.wo = ow; }
+        else if (oh != P.ho || ow != P.wo) return fail("terms disagree on the output size");
+    }
+    if (phased && terms.size() != 1) return fail("a stride-2 transposed conv cannot be fused with other terms");
+    P.num_phases = phased ? 4 : 1;
+    P.os = phased ? 2 : 1;
+    P.hg = phased ? t0.in_h : P.ho;
+    P.wg = phased ? t0.in_w : P.wo;
+    if (P.wg > kTileM) return fail("grid width > 128 unsupported");
+    // pixel tile
+    P.bw = P.wg;
+    {
+        const int bh_max = std::max(1, std::min(P.hg, kTileM / P.bw));
+        int best = bh_max, best_tiles = (P.hg + bh_max - 1) / bh_max;
+        for (int bh = bh_max; bh >= 1; --bh) {
+            const int nt = (P.hg + bh - 1) / bh;
+            if (nt < best_tiles) { best = bh; best_tiles = nt; }
+        }
+        P.bh = best;
+        P.bn = (P.bh == P.hg) ? std::max(1, kTileM / (P.bw * P.bh)) : 1;
+        if (P.bn > 256) P.bn = 256;
+    }
+    P.rows = P.bw * P.bh * P.bn;
+    P.tiles_x = 1;
+    P.tiles_y = (P.hg + P.bh - 1) / P.bh;
+    // N tiling
+    P.nt = P.npad;
+    if (P.npad > 256) {
+        P.nt = 256;
+        while (P.npad % P.nt) P.nt -= 16;
+    }
+    P.n_tiles = P.npad / P.nt;
+    // sources
+    P.nsrc = 0;
+    for (const TermSpec& t : terms) P.nsrc = std::max(P.nsrc, t.src + 1);
+    bool seen[kMaxSrc] = {false, false, false};
+    for (const TermSpec& t : terms) {
+        SrcGeom& g = P.src[t.src];
+        const bool s2d = (!t.transpose && t.stride == 2);
+        const uint64_t C = t.in_cp, W = t.in_w, H = t.in_h;
+        SrcGeom n;
+        if (!s2d) {
+            n.dims[0] = C; n.dims[1] = W; n.dims[2] = 1; n.dims[3] = H; n.dims[4] = capacity_n;
+            n.strides[0] = C * 2; n.strides[1] = W * C * 2; n.strides[2] = W * C * 2; n.strides[3] = H * W * C * 2;
+        } else {
+            n.dims[0] = 2 * C; n.dims[1] = W / 2; n.dims[2] = 2; n.dims[3] = H / 2; n.dims[4] = capacity_n;
+            n.strides[0] = 2 * C * 2; n.strides[1] = W * C * 2; n.strides[2] = 2 * W * C * 2; n.strides[3] = H * W * C * 2;
+        }
+        n.box[0] = P.kc; n.box[1] = P.bw; n.box[2] = 1; n.box[3] = P.bh; n.box[4] = P.bn;
+        if (seen[t.src] && memcmp(&g, &n, sizeof(n)) != 0) return fail("two terms view one source differently");
+        g = n;
+        seen[t.src] = true;
+    }
+    for (int s = 0; s < P.nsrc; ++s)
+        if (!seen[s]) return fail("source indices must be dense");
+    // steps + weights + bias
+    P.bias.assign(P.npad, 0.f);
+    for (const TermSpec& t : terms)
+        if (t.bias) for (int n = 0; n < t.cout; ++n) P.bias[n] += t.bias[n];
+    const int chunks = cp / P.kc;
+    P.macs_per_image = 0;
+    for (int ph = 0; ph < P.num_phases; ++ph) {
+        P.phase_begin[ph] = (int)P.steps.size();
+        for (const TermSpec& t : terms) {
+            const std::vector<Tap> taps = enumerate_taps(t, ph >> 1, ph & 1);
+            const int used_chunks = (t.cin + P.kc - 1) / P.kc;   // skip all-padding chunks
+            for (const Tap& tap : taps) {
+                for (int c = 0; c < std::min(chunks, used_chunks); ++c) {
+                    TapStep st;
+                    st.src = (int16_t)t.src; st.dx = (int16_t)tap.dx; st.dy = (int16_t)tap.dy;
+                    st.ph = (int16_t)tap.ph; st.c0 = tap.cbase + c * P.kc;
+                    P.steps.push_back(st);
+                    const size_t base = P.wpack.size();
+                    P.wpack.resize(base + (size_t)P.npad * P.kc, 0);
+                    for (int n = 0; n < t.cout; ++n)
+                        for (int kk = 0; kk < P.kc; ++kk) {
+                            const int ci = c * P.kc + kk;
+                            if (ci >= t.cin) break;
+                            const size_t tap_off = ((size_t)tap.di * t.k + tap.dj);
+                            const float w = t.transpose
+                                ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
+                                : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
+                            P.wpack[base + (size_t)n * P.kc + kk] = f32_to_bf16(w);
+                        }
+                }
+            }
+            P.macs_per_image += (double)taps.size() * t.cin * t.cout * P.hg * P.wg;
+        }
+    }
+    for (int ph = P.num_phases; ph <= kMaxPhases; ++ph) P.phase_begin[ph] = (int)P.steps.size();
+    for (int ph = 0; ph < P.num_phases; ++ph)
+        if (P.phase_begin[ph + 1] == P.phase_begin[ph]) return fail("a phase has no taps");
+    return true;
+}
+
+}  // namespace apvae

@@ -1,0 +1,65 @@
+// Host-side planner: turns one conv2d / conv2d_transpose / dense (plus an
+// optional fused 1x1 shortcut term) into a tap-GEMM step table, a packed bf16
+// weight matrix and the TMA view geometry.  Pure C++ (no CUDA calls), so its
+// output can be dumped and checked on a machine without a GPU.
+//
+// Reference semantics restated here:
+//   conv2d  : tfsnippet/layers/convolutional/conv2d_.py:178-211, TF SAME padding
+//   deconv2d: conv2d_.py:464-471 (adjoint of the SAME conv), output = in*stride
+//             (layers/convolutional/utils.py:78-96)
+//   dense   : layers/core/dense_.py:142-147 (a 1x1 conv over a 1x1 image)
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "tapgemm.h"
+
+namespace apvae {
+
+struct TermSpec {
+    int src;            // which A source (0..2) this term reads
+    int transpose;      // 0: conv2d, kernel [kh,kw,Cin,Cout]; 1: deconv2d, kernel [kh,kw,Cout,Cin]
+    int k, stride;      // square kernel, stride 1 or 2
+    int cin, cout;      // logical channels
+    int in_h, in_w;     // source spatial size
+    int in_cp;          // source channels as stored (padded to a multiple of 16)
+    const float* kernel;
+    const float* bias;  // may be null
+};
+
+struct SrcGeom {
+    uint64_t dims[5];     // (C', W', P, H', N)
+    uint64_t strides[4];  // bytes, dims 1..4
+    uint32_t box[5];
+};
+
+struct OpPlan {
+    int kc = 0, npad = 0, nt = 0, n_tiles = 0, cout = 0;
+    int num_phases = 1;
+    int phase_begin[kMaxPhases + 1] = {0, 0, 0, 0, 0};
+    std::vector<TapStep> steps;
+    std::vector<uint16_t> wpack;   // bf16 [steps][npad][kc]
+    std::vector<float> bias;       // [npad], sum over terms
+    int bw = 0, bh = 0, bn = 0, rows = 0;
+    int wg = 0, hg = 0, tiles_x = 0, tiles_y = 0;
+    int ho = 0, wo = 0, os = 1;
+    int nsrc = 0;
+    int capacity_n = 0;
+    SrcGeom src[kMaxSrc];
+    double macs_per_image = 0;     // algorithmic multiply-accumulates (unpadded)
+};
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+inline int pad16(int c) { return round_up(c, 16); }
+
+// TF SAME padding rule.
+void same_padding(int in, int k, int s, int* out, int* lo, int* hi);
+
+uint16_t f32_to_bf16(float f);
+float bf16_to_f32(uint16_t h);
+
+// Builds the plan.  All terms must agree on the output grid and on in_cp.
+// Returns false and fills *err on unsupported shapes.
+bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, std::string* err);
+
+}  // namespace apvae

@@ -1,0 +1,146 @@
+#include "runtime.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <string.h>
+
+namespace apvae {
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+bool device_open(int device, DeviceInfo* info, std::string* err) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0) {
+        if (err) *err = std::string("no CUDA device available (") + cudaGetErrorString(e) +
+                        "); this library has no CPU fallback";
+        cudaGetLastError();
+        return false;
+    }
+    if (device < 0 || device >= count) {
+        if (err) *err = "device index out of range";
+        return false;
+    }
+    APVAE_CUDA_OK(cudaSetDevice(device), err);
+    cudaDeviceProp prop;
+    APVAE_CUDA_OK(cudaGetDeviceProperties(&prop, device), err);
+    if (prop.major != 10) {
+        if (err) *err = std::string("device '") + prop.name + "' is not sm_100 (Blackwell B200); kernels are sm_100a only";
+        return false;
+    }
+    info->device = device;
+    info->num_sms = prop.multiProcessorCount;
+    info->cc_major = prop.major;
+    info->cc_minor = prop.minor;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    APVAE_CUDA_OK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres), err);
+    if (fn == nullptr || qres != cudaDriverEntryPointSuccess) {
+        if (err) *err = "cuTensorMapEncodeTiled not available from the driver";
+        return false;
+    }
+    info->encode_fn = fn;
+    return true;
+}
+
+DevOp::~DevOp() {
+    if (d_steps) cudaFree(d_steps);
+    if (d_w) cudaFree(d_w);
+    if (d_bias) cudaFree(d_bias);
+}
+
+static CUtensorMapSwizzle swizzle_for(int kc) {
+    return kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : kc == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+}
+
+bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
+                  DevOp* op, std::string* err) {
+    EncodeTiledFn encode = reinterpret_cast<EncodeTiledFn>(dev.encode_fn);
+    const size_t nsteps = plan.steps.size();
+    APVAE_CUDA_OK(cudaMalloc(&op->d_steps, nsteps * sizeof(TapStep)), err);
+    APVAE_CUDA_OK(cudaMalloc(&op->d_w, plan.wpack.size() * sizeof(uint16_t)), err);
+    APVAE_CUDA_OK(cudaMalloc(&op->d_bias, plan.bias.size() * sizeof(float)), err);
+    APVAE_CUDA_OK(cudaMemcpy(op->d_steps, plan.steps.data(), nsteps * sizeof(TapStep), cudaMemcpyHostToDevice), err);
+    APVAE_CUDA_OK(cudaMemcpy(op->d_w, plan.wpack.data(), plan.wpack.size() * sizeof(uint16_t), cudaMemcpyHostToDevice), err);
+    APVAE_CUDA_OK(cudaMemcpy(op->d_bias, plan.bias.data(), plan.bias.size() * sizeof(float), cudaMemcpyHostToDevice), err);
+
+    TapGemmParams& p = op->params;
+    memset(&p, 0, sizeof(p));
+    const cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+    for (int s = 0; s < plan.nsrc; ++s) {
+        const SrcGeom& g = plan.src[s];
+        cuuint64_t dims[5], strides[4];
+        cuuint32_t box[5];
+        for (int i = 0; i < 5; ++i) { dims[i] = g.dims[i]; box[i] = g.box[i]; }
+        for (int i = 0; i < 4; ++i) strides[i] = g.strides[i];
+        CUresult r = encode(&p.tm_a[s], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(src_ptrs[s]), dims,
+                            strides, box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc),
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            if (err) *err = "cuTensorMapEncodeTiled(A) failed with CUresult " + std::to_string((int)r) + " for op " + op->name;
+            return false;
+        }
+    }
+    for (int s = plan.nsrc; s < kMaxSrc; ++s) p.tm_a[s] = p.tm_a[0];
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)plan.kc, (cuuint64_t)nsteps * plan.npad};
+        cuuint64_t strides[1] = {(cuuint64_t)plan.kc * 2};
+        cuuint32_t box[2] = {(cuuint32_t)plan.kc, (cuuint32_t)plan.nt};
+        CUresult r = encode(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op->d_w, dims, strides, box, ones,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            if (err) *err = "cuTensorMapEncodeTiled(B) failed with CUresult " + std::to_string((int)r) + " for op " + op->name;
+            return false;
+        }
+    }
+    p.steps = op->d_steps;
+    for (int i = 0; i <= kMaxPhases; ++i) p.phase_begin[i] = plan.phase_begin[i];
+    p.num_phases = plan.num_phases;
+    p.bw = plan.bw; p.bh = plan.bh; p.bn = plan.bn; p.rows = plan.rows;
+    p.Wg = plan.wg; p.Hg = plan.hg; p.tiles_x = plan.tiles_x; p.tiles_y = plan.tiles_y;
+    p.n_valid = 0;
+    p.Ho = plan.ho; p.Wo = plan.wo; p.os = plan.os;
+    p.Npad = plan.npad; p.NT = plan.nt; p.n_tiles = plan.n_tiles;
+    p.kc = plan.kc;
+    int min_steps = 1 << 30;
+    for (int ph = 0; ph < plan.num_phases; ++ph)
+        min_steps = std::min(min_steps, plan.phase_begin[ph + 1] - plan.phase_begin[ph]);
+    p.num_stages = tapgemm_pick_stages(plan.kc, plan.nt, std::max(2, (int)nsteps));
+    p.a_bytes = (uint32_t)plan.rows * plan.kc * 2;
+    p.b_bytes = (uint32_t)plan.nt * plan.kc * 2;
+    p.stage_bytes = (kTileM * plan.kc * 2 + plan.nt * plan.kc * 2 + 1023u) & ~1023u;
+    p.bias = op->d_bias;
+    p.out_raw = epi.out_raw; p.out_act = epi.out_act; p.ldo = epi.ldo;
+    p.bf16_zero_from = epi.bf16_zero_from;
+    p.out_f32 = epi.out_f32; p.ld_f32 = epi.ld_f32; p.f32_cols = epi.f32_cols;
+    p.res = epi.res; p.res_mode = epi.res_mode; p.ld_res = epi.ld_res;
+    p.mask = epi.mask; p.ld_mask = epi.ld_mask;
+    p.tanh_cols = epi.tanh_cols;
+    p.lrelu_alpha = 0.2f;
+    op->macs_per_image = plan.macs_per_image;
+    op->capacity_n = plan.capacity_n;
+    if ((epi.out_raw || epi.out_act) && (epi.ldo % 16 != 0 || epi.ldo < plan.npad)) {
+        if (err) *err = "epilogue: ldo must be a multiple of 16 and >= padded cout (op " + op->name + ")";
+        return false;
+    }
+    if (epi.res && (epi.ld_res % 8 != 0 || epi.ld_res < plan.npad)) {
+        if (err) *err = "epilogue: residual row too short (op " + op->name + ")";
+        return false;
+    }
+    if (epi.mask && (epi.ld_mask % 8 != 0 || epi.ld_mask < plan.npad)) {
+        if (err) *err = "epilogue: mask row too short (op " + op->name + ")";
+        return false;
+    }
+    return true;
+}
+
+int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
+    if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
+    op.params.n_valid = n_valid;
+    return launch_tapgemm(op.params, dev.num_sms, stream);
+}
+
+}  // namespace apvae

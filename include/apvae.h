@@ -1,0 +1,178 @@
+/* apvae.h — C ABI of the B200-native evaluation / sampling hot path of
+ * chenwenxiao/adversarial-prior-vae.
+ *
+ * The reference has no FFI: its hot path is a TensorFlow-1.x graph built by the
+ * experiment scripts and executed with session.run.  Each entry point below
+ * replaces one such graph fragment (file:line under /root/reference/code).
+ * Conventions: plain pointers and sizes only; `*_dev` pointers are CUDA device
+ * pointers owned by the caller; `stream` is a cudaStream_t (NULL = default);
+ * calls are asynchronous on that stream unless stated; every function returns
+ * an apvae_status (0 = OK) and apvae_last_error() gives the message.
+ * Tensors are float32, NHWC, sample axis first ([K,B,...] flattened as
+ * s = k*B + b), exactly as in the reference.
+ */
+#ifndef APVAE_H_
+#define APVAE_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    APVAE_OK = 0,
+    APVAE_ERR_INVALID = 1,      /* bad argument / shape (reference: ValueError at graph build) */
+    APVAE_ERR_CUDA = 2,         /* CUDA runtime / driver error */
+    APVAE_ERR_NO_DEVICE = 3,    /* no usable sm_100 GPU: there is NO CPU fallback */
+    APVAE_ERR_WEIGHTS = 4,      /* missing / mis-shaped variable */
+    APVAE_ERR_UNSUPPORTED = 5,
+    APVAE_ERR_STATE = 6         /* e.g. weights not loaded yet */
+} apvae_status;
+
+typedef enum { APVAE_ARCH_A = 0, APVAE_ARCH_B = 1, APVAE_ARCH_M = 2 } apvae_arch;
+
+/* Mirrors the ExpConfig fields the path reads
+ * (experiment/dmm/dmm_cifar10.py:27-91, dmm_for_sampling.py:28-92,
+ * dmm_bernouli_fashion.py ExpConfig). */
+typedef struct apvae_config {
+    int arch;                       /* apvae_arch */
+    int x_h, x_w, x_c;              /* config.x_shape */
+    int z_dim;                      /* config.z_dim */
+    int celeba;                     /* arch B: config.dataset == 'celebA' (stride-2 first/last blocks) */
+    float pull_back_energy_weight;  /* config.pull_back_energy_weight */
+    float min_logstd_of_q;          /* config.min_logstd_of_q */
+    float epsilon;                  /* config.epsilon: min of the likelihood log-scale (-20) */
+    int uniform_scale;              /* config.uniform_scale: log_scale = beta */
+    int use_truncated;              /* config.use_truncated: TruncatedNormal q(z|x) */
+    int bernoulli;                  /* arch M likelihood */
+    int max_batch;                  /* capacity: images per q_net launch */
+    int max_chunk;                  /* capacity: (image,sample) pairs per decoder/energy launch */
+    int enable_grad;                /* build the input-gradient programs (MALA, grad norms) */
+    float smallest_step;            /* config.smallest_step (default MALA alpha) */
+    int len_train;                  /* config.len_train (log-Z offset) */
+} apvae_config;
+
+typedef struct apvae_handle apvae_handle;
+typedef struct apvae_plan apvae_plan;
+
+const char* apvae_version(void);
+/* Message of the last failing call on `h` (or of the last failing handle-less call when h == NULL). */
+const char* apvae_last_error(const apvae_handle* h);
+
+/* ExpConfig defaults of the three script families. */
+int apvae_default_config(int arch, int celeba, apvae_config* out);
+
+/* TF variable schema (names as created under global_reuse scopes:
+ * conv2d_.py:147-173, dense_.py:112-137, resnet.py:215-246), e.g.
+ * "G_theta/level_3/residual/conv_0/kernel".  No GPU needed. */
+int apvae_weight_count(const apvae_config* cfg, int* count);
+int apvae_weight_info(const apvae_config* cfg, int index, char* name, int name_cap, int64_t shape[4], int* ndim);
+
+/* One handle per GPU / rank; not thread-safe.  Fails with APVAE_ERR_NO_DEVICE without a GPU. */
+int apvae_create(const apvae_config* cfg, int device, apvae_handle** out);
+int apvae_destroy(apvae_handle* h);
+
+/* Replaces tf.train.Saver restore / variable init: host float32 arrays in the
+ * reference layouts (conv [kh,kw,Cin,Cout], deconv [kh,kw,Cout,Cin], dense [in,out]).
+ * The caller keeps ownership; the library converts to bf16 and repacks. Synchronous. */
+int apvae_load_weights(apvae_handle* h, int n, const char* const* names, const float* const* data,
+                       const int64_t* const* shapes, const int* ndims);
+/* 'p_net/xi' (pre-sigmoid, dmm_cifar10.py:604-607), 'beta' (:860), 'log_Z' (:458-463). */
+int apvae_set_scalars(apvae_handle* h, float xi_raw, float beta, float log_Z);
+
+/* q_net(x) -> (z_mean, clipped z_logstd) [B, z_dim]   (dmm_cifar10.py:418-452) */
+int apvae_encode(apvae_handle* h, const float* x_dev, int B, float* mu_dev, float* logstd_dev, void* stream);
+/* G_theta(z, return_std) -> x_mean [N,H,W,C] (tanh applied) and x_logstd (may be NULL)   (:466-500) */
+int apvae_decode(apvae_handle* h, const float* z_dev, int N, float* x_mean_dev, float* x_logstd_dev, void* stream);
+/* D_psi(x) for images (z_dev == NULL) or D_psi(G_theta(z)) (x_dev == NULL) -> [N]   (:535-562, :175) */
+int apvae_energy(apvae_handle* h, const float* x_dev, const float* z_dev, int N, float* d_dev, void* stream);
+
+/* Rows of `per_image_dev` ([APVAE_PER_IMAGE_ROWS][B] float32). */
+enum {
+    APVAE_ROW_LL = 0,       /* is_loglikelihood, plain N(0,I) prior (dmm_cifar10.py:896-898) */
+    APVAE_ROW_LB = 1,       /* elbo (:899) */
+    APVAE_ROW_ADV_LL = 2,   /* is_loglikelihood with the energy prior (:901-910) */
+    APVAE_ROW_ADV_LB = 3,   /* :911 */
+    APVAE_ROW_RECON = 4,    /* mean_k log p(x|z_k) (:886-888) */
+    APVAE_ROW_DG = 5,       /* mean_k D(G(z_k)) (:914) */
+    APVAE_ROW_LZ_MAX = 6,   /* max_k(-energy - log q)          } another_log_Z_compute_op (:922-924) */
+    APVAE_ROW_LZ_SUM = 7,   /* sum_k exp(-energy - log q - max) } before the + log(len_train) */
+    APVAE_ROW_REAL_E = 8,   /* D_psi(x_origin) (:913) */
+    APVAE_PER_IMAGE_ROWS = 9
+};
+/* Rows of the optional `per_sample_dev` ([4][K*B]): log p(x|z), log q(z|x), log N(z), D(G(z)). */
+enum { APVAE_SROW_LOG_PX = 0, APVAE_SROW_LOG_Q = 1, APVAE_SROW_LOG_PN = 2, APVAE_SROW_DG = 3, APVAE_PER_SAMPLE_ROWS = 4 };
+
+/* The test graph of one Evaluator mini-batch (dmm_cifar10.py:880-927, one session.run at
+ * trainer/evaluator.py:189-191): q_net once per image, K reparameterised draws, G_theta and
+ * D_psi once per (image,sample), likelihood, per-image log-mean-exp.
+ * x: likelihood target; x_origin: q_net / real_energy input (same pointer for archs A, B).
+ * eps_dev [K,B,z_dim] N(0,1) noise, or NULL to draw in-kernel (Philox, `seed`). */
+int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev, int B, int K,
+                 const float* eps_dev, uint64_t seed, float* per_image_dev, float* per_sample_dev, void* stream);
+
+/* test_pn_net branch (:883,915-927): Kp prior draws through G and D.  Outputs [Kp] each. */
+int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t seed, float* d_g_dev,
+                      float* log_pn_dev, void* stream);
+
+/* EnergyDistribution.sample / get_sgld_proposal (:179-252): `steps` MALA iterations on n chains.
+ * z_io_dev [n, z_dim] in/out; eps_dev [steps,n,z_dim], u_dev [steps,n] or NULL (Philox);
+ * hist_* [steps, n] or NULL.  Requires enable_grad. */
+int apvae_mala(apvae_handle* h, float* z_io_dev, int n, int steps, float alpha, const float* eps_dev,
+               const float* u_dev, uint64_t seed, float* hist_e_dev, float* hist_pure_e_dev,
+               float* hist_ratio_dev, void* stream);
+/* energy, grad_z energy, pure energy at z (get_sgld_proposal :241-247). Any output may be NULL. */
+int apvae_energy_grad(apvae_handle* h, const float* z_dev, int n, float* energy_dev, float* grad_dev,
+                      float* pure_dev, void* stream);
+/* x_plots (:976-977,990) + np.round: uint8 NHWC images from latents. */
+int apvae_sample_images(apvae_handle* h, const float* z_dev, int n, uint8_t* out_dev, void* stream);
+
+/* Philox normals / uniforms the NULL-noise paths use (so tests can reproduce them). */
+int apvae_fill_normal(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, int truncated, void* stream);
+int apvae_fill_uniform(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, void* stream);
+
+/* Bookkeeping for the benchmark: kernels launched so far, algorithmic MACs per unit. */
+int apvae_launch_count(const apvae_handle* h, int64_t* launches);
+int apvae_macs(const apvae_handle* h, double* q_per_image, double* g_per_sample, double* d_per_sample);
+
+/* ---- layer-level interface (tests; mirrors spt.layers.conv2d / deconv2d / dense) ---- */
+typedef struct apvae_conv_term {
+    int src, transpose, k, stride, cin, cout, in_h, in_w, in_cp;
+    const float* kernel;   /* host */
+    const float* bias;     /* host, may be NULL */
+} apvae_conv_term;
+
+typedef struct apvae_plan_info {
+    int kc, npad, nt, n_tiles, cout, num_phases, phase_begin[5], total_steps;
+    int bw, bh, bn, rows, wg, hg, tiles_x, tiles_y, ho, wo, os, nsrc, capacity_n;
+    uint64_t src_dims[3][5];
+    uint64_t src_strides[3][4];
+    uint32_t src_box[3][5];
+    double macs_per_image;
+} apvae_plan_info;
+
+typedef struct apvae_epilogue {
+    void* out_raw_dev;  void* out_act_dev;  int ldo;  int bf16_zero_from;
+    float* out_f32_dev; int ld_f32; int f32_cols;
+    const void* res_dev; int res_mode; int ld_res;
+    const void* mask_dev; int ld_mask;
+    int tanh_cols;
+} apvae_epilogue;
+
+/* Host-only planning (no GPU needed): step table, packed bf16 weights, TMA view geometry. */
+int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, apvae_plan** out);
+int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info);
+int apvae_plan_copy_steps(const apvae_plan* p, int32_t* out /* [total_steps][5]: src,dx,dy,ph,c0 */);
+int apvae_plan_copy_weights(const apvae_plan* p, uint16_t* out /* bf16 [total_steps][npad][kc] */);
+int apvae_plan_copy_bias(const apvae_plan* p, float* out /* [npad] */);
+int apvae_plan_destroy(apvae_plan* p);
+/* Runs the plan on `device` (synchronous): src_dev[i] are bf16 NHWC tensors [capacity_n,H,W,Cp]. */
+int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,
+                   const apvae_epilogue* epi);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* APVAE_H_ */

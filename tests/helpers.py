@@ -1,0 +1,84 @@
+"""Test helpers: bf16 rounding, synthetic inputs, and a numpy emulation of the
+tap-GEMM plan (what the TMA boxes + step table + packed weights compute)."""
+import numpy as np
+
+
+def bf16_round(x):
+    """Round float32 -> bfloat16 -> float32 (round to nearest even)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    u = x.view(np.uint32).astype(np.uint64)
+    u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
+    return u.astype(np.uint32).view(np.float32).reshape(x.shape)
+
+
+def bf16_bits_to_f32(bits):
+    return (np.asarray(bits, dtype=np.uint32) << 16).view(np.float32)
+
+
+def pad_channels(x, cp):
+    out = np.zeros(x.shape[:-1] + (cp,), dtype=x.dtype)
+    out[..., :x.shape[-1]] = x
+    return out
+
+
+def emulate_plan(plan, srcs, n_valid):
+    """Evaluate a Plan on the CPU exactly as the kernel would: for every tile
+    and step, gather the 5-D TMA box (zero fill out of bounds) from the padded
+    NHWC source, multiply by the packed weight slice, accumulate; add bias.
+    srcs: list of float arrays [N, H, W, Cp].  Returns [n_valid, Ho, Wo, npad]."""
+    i = plan.info
+    steps, wts, bias = plan.steps, bf16_bits_to_f32(plan.weights).astype(np.float64), plan.bias
+    out = np.zeros((n_valid, i.ho, i.wo, i.npad), dtype=np.float64)
+    views = []
+    for s in range(i.nsrc):
+        dims = [int(v) for v in i.src_dims[s]]
+        strides = [int(v) for v in i.src_strides[s]]
+        flat = np.ascontiguousarray(srcs[s], dtype=np.float64).ravel()
+        # element strides of the 5-D view (bf16 = 2 bytes)
+        est = [1] + [st // 2 for st in strides]
+        views.append((flat, dims, est))
+
+    def gather(s, c0, x0, p0, y0, n0):
+        flat, dims, est = views[s]
+        box = [int(v) for v in i.src_box[s]]
+        a = np.zeros((box[4], box[3], box[2], box[1], box[0]), dtype=np.float64)
+        for bn in range(box[4]):
+            for by in range(box[3]):
+                for bx in range(box[1]):
+                    n, y, x, p = n0 + bn, y0 + by, x0 + bx, p0
+                    if not (0 <= n < dims[4] and 0 <= y < dims[3] and 0 <= x < dims[1] and 0 <= p < dims[2]):
+                        continue
+                    base = n * est[4] + y * est[3] + p * est[2] + x * est[1]
+                    for bc in range(box[0]):
+                        c = c0 + bc
+                        if 0 <= c < dims[0]:
+                            a[bn, by, 0, bx, bc] = flat[base + c]
+        return a.reshape(-1, box[0])      # rows ordered (n, y, x) = kernel row order
+
+    tiles_n = -(-n_valid // i.bn)
+    for tn in range(tiles_n):
+        for ty in range(i.tiles_y):
+            for tx in range(i.tiles_x):
+                n0, y0, x0 = tn * i.bn, ty * i.bh, tx * i.bw
+                for ph in range(i.num_phases):
+                    acc = np.zeros((i.rows, i.npad), dtype=np.float64)
+                    for st in range(i.phase_begin[ph], i.phase_begin[ph + 1]):
+                        src, dx, dy, p, c0 = [int(v) for v in steps[st]]
+                        a = gather(src, c0, x0 + dx, p, y0 + dy, n0)
+                        acc += a @ wts[st].T
+                    acc += bias
+                    py, px = (ph >> 1, ph & 1) if i.num_phases == 4 else (0, 0)
+                    for r in range(i.rows):
+                        x = r % i.bw
+                        y = (r // i.bw) % i.bh
+                        n = r // (i.bw * i.bh)
+                        if n0 + n >= n_valid or y0 + y >= i.hg or x0 + x >= i.wg:
+                            continue
+                        out[n0 + n, (y0 + y) * i.os + py, (x0 + x) * i.os + px] = acc[r]
+    return out
+
+
+def synthetic_images(shape, seed=0):
+    """uint8 ~ U{0..255} mapped as dmm_cifar10.py:1084-1085."""
+    u8 = np.random.RandomState(seed).randint(0, 256, size=shape)
+    return ((u8 - 127.5) / 256.0 * 2).astype(np.float32)

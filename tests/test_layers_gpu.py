@@ -1,0 +1,159 @@
+"""GPU parity of the tap-GEMM kernel against the oracle, through the C ABI
+(apvae_plan_create / apvae_plan_run).  Modelled on the reference's
+tests/layers/convolutional/test_conv2d.py (wrapper == raw op + bias + act) and
+tests/layers/core/test_dense.py (dense == np.dot + b), with the numpy oracle in
+place of TensorFlow.  Inputs and kernels are bf16-exact, so the only difference
+is fp32 accumulation order: tolerance 2e-4 relative to the output scale."""
+import numpy as np
+import pytest
+
+import oracle as O
+from helpers import bf16_round, pad_channels
+
+pytestmark = pytest.mark.gpu
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def _check(got, want, tol=2e-4):
+    scale = max(1.0, float(np.abs(want).max()))
+    err = float(np.abs(got - want).max())
+    assert err <= tol * scale, 'max err %g (scale %g)' % (err, scale)
+
+
+LAYER_CASES = [
+    # transpose, k, stride, N, H, W, cin, cout
+    (False, 3, 1, 5, 8, 8, 64, 64),        # KC=64
+    (False, 3, 1, 3, 32, 32, 96, 96),      # KC=32, N=96
+    (False, 3, 1, 3, 16, 16, 192, 192),    # N=192
+    (False, 5, 1, 2, 32, 32, 3, 96),       # KC=16, Cin=3
+    (False, 3, 2, 4, 32, 32, 64, 128),     # stride-2 through space-to-depth view
+    (False, 3, 2, 9, 8, 8, 256, 256),      # N=256, 4x4 output, 8 images per tile
+    (False, 5, 2, 2, 64, 64, 3, 32),       # celebA first block
+    (False, 1, 2, 3, 16, 16, 128, 256),    # 1x1 stride-2 shortcut
+    (False, 3, 1, 3, 28, 28, 16, 16),      # 112-row tiles
+    (False, 3, 2, 3, 14, 14, 32, 64),      # 7x7 output
+    (True, 3, 1, 5, 8, 8, 192, 192),
+    (True, 5, 1, 2, 32, 32, 96, 96),
+    (True, 3, 2, 5, 8, 8, 192, 192),       # 4 sub-pixel phases
+    (True, 3, 2, 3, 16, 16, 192, 96),
+    (True, 5, 2, 2, 32, 32, 32, 32),
+    (True, 1, 1, 130, 8, 8, 2, 192),       # ragged: 130 images, 2 per tile
+    (True, 3, 2, 3, 7, 7, 64, 64),         # arch M
+]
+
+
+@pytest.mark.parametrize('transpose,k,stride,N,H,W,cin,cout', LAYER_CASES)
+def test_conv_layers(transpose, k, stride, N, H, W, cin, cout):
+    torch = _torch()
+    import apvae
+    rs = np.random.RandomState(k + 10 * stride + cin + cout)
+    x = bf16_round(rs.normal(size=(N, H, W, cin)))
+    shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
+    kern = bf16_round(rs.normal(size=shp) / np.sqrt(k * k * cin))
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    fn = apvae.deconv2d if transpose else apvae.conv2d
+    got = fn(torch.tensor(x, device='cuda'), kern, bias, stride).cpu().numpy()
+    ofn = O.deconv2d if transpose else O.conv2d
+    want = ofn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), stride)
+    assert got.shape == want.shape
+    _check(got, want)
+
+
+@pytest.mark.parametrize('n,fin,fout', [(7, 4096, 64), (300, 128, 4096), (5, 40, 3136), (64, 8192, 128)])
+def test_dense(n, fin, fout):
+    torch = _torch()
+    import apvae
+    rs = np.random.RandomState(fin + fout)
+    x = bf16_round(rs.normal(size=(n, fin)))
+    k = bf16_round(rs.normal(size=(fin, fout)) / np.sqrt(fin))
+    b = rs.normal(size=fout).astype(np.float32)
+    got = apvae.dense(torch.tensor(x, device='cuda'), k, b).cpu().numpy()
+    _check(got, x.astype(np.float64) @ k.astype(np.float64) + b)
+
+
+def test_tanh_activation():
+    torch = _torch()
+    import apvae
+    rs = np.random.RandomState(0)
+    x = bf16_round(rs.normal(size=(2, 32, 32, 96)))
+    k = bf16_round(rs.normal(size=(1, 1, 96, 3)) * 0.2)
+    b = rs.normal(size=3).astype(np.float32)
+    got = apvae.conv2d(torch.tensor(x, device='cuda'), k, b, 1, 'tanh').cpu().numpy()
+    _check(got, O.conv2d(x.astype(np.float64), k.astype(np.float64), b.astype(np.float64), 1, np.tanh))
+
+
+def test_epilogue_residual_mask_and_bf16_outputs():
+    """v = (acc + bias) * lrelu'(mask) + res ; out_raw = bf16(v), out_act = bf16(lrelu(v));
+    columns >= bf16_zero_from stored as 0; only n_valid images written."""
+    torch = _torch()
+    from apvae.plan import Plan, pad16
+    from apvae import _lib
+    rs = np.random.RandomState(5)
+    cap, n_valid, H, cin, cout = 6, 5, 8, 32, 48
+    x = bf16_round(rs.normal(size=(cap, H, H, cin)))
+    kern = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.1)
+    bias = rs.normal(size=cout).astype(np.float32)
+    res = bf16_round(rs.normal(size=(cap, H, H, cout)))
+    msk = bf16_round(rs.normal(size=(cap, H, H, cout)))
+    plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=kern, bias=bias)], cap)
+    dev = 'cuda'
+    t = lambda a: torch.tensor(a, device=dev).to(torch.bfloat16)
+    out_raw = torch.full((cap, H, H, cout), 7.0, dtype=torch.bfloat16, device=dev)
+    out_act = torch.full((cap, H, H, cout), 7.0, dtype=torch.bfloat16, device=dev)
+    out_f32 = torch.full((cap, H, H, cout), 7.0, dtype=torch.float32, device=dev)
+    plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, out_act=out_act, out_f32=out_f32,
+             f32_cols=cout, res=t(res), res_mode=_lib.RES_SAME, mask=t(msk), bf16_zero_from=40)
+    conv = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
+    want = conv * np.where(msk > 0, 1.0, 0.2) + res
+    got = out_f32.cpu().numpy()
+    _check(got[:n_valid], want[:n_valid])
+    assert np.all(got[n_valid:] == 7.0), 'rows beyond n_valid must not be written'
+    raw = out_raw.float().cpu().numpy()
+    act = out_act.float().cpu().numpy()
+    w40 = want[:n_valid].copy(); w40[..., 40:] = 0
+    _check(raw[:n_valid], w40, tol=1e-2)
+    _check(act[:n_valid], np.where(w40 > 0, w40, 0.2 * w40), tol=1e-2)
+    assert np.all(raw[n_valid:] == 7.0)
+
+
+def test_epilogue_even_pixel_residual():
+    """RES_EVEN: the 1x1 stride-2 transposed shortcut adds x W only at even output pixels."""
+    torch = _torch()
+    from apvae.plan import Plan, pad16
+    from apvae import _lib
+    rs = np.random.RandomState(9)
+    n, H, c = 3, 8, 64
+    r = bf16_round(rs.normal(size=(n, 2 * H, 2 * H, c)))
+    kern = bf16_round(rs.normal(size=(3, 3, c, c)) * 0.05)
+    sc_low = bf16_round(rs.normal(size=(n, H, H, c)))
+    plan = Plan([dict(src=0, transpose=True, in_h=2 * H, in_w=2 * H, kernel=kern)], n)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    out = torch.zeros((n, 2 * H, 2 * H, c), dtype=torch.float32, device='cuda')
+    plan.run([t(r)], n, out_f32=out, f32_cols=c, res=t(sc_low), res_mode=_lib.RES_EVEN)
+    want = O.deconv2d(r.astype(np.float64), kern.astype(np.float64), None, 1)
+    want[:, ::2, ::2, :] += sc_low
+    _check(out.cpu().numpy(), want)
+
+
+def test_fused_shortcut_gpu():
+    torch = _torch()
+    from apvae.plan import Plan
+    rs = np.random.RandomState(7)
+    n, H, cin, cout = 4, 16, 128, 256
+    r = bf16_round(rs.normal(size=(n, H, H, cin)))
+    x = bf16_round(rs.normal(size=(n, H, H, cin)))
+    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.03)
+    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.1)
+    b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
+    plan = Plan([dict(src=0, stride=2, in_h=H, in_w=H, kernel=k1, bias=b1),
+                 dict(src=1, stride=2, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    out = torch.zeros((n, H // 2, H // 2, cout), dtype=torch.float32, device='cuda')
+    plan.run([t(r), t(x)], n, out_f32=out, f32_cols=cout)
+    want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 2) + \
+        O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
+    _check(out.cpu().numpy(), want)

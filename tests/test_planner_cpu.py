@@ -1,0 +1,90 @@
+"""Host planner vs the oracle: the step table + TMA view geometry + packed
+weights must reproduce conv2d / deconv2d / dense for every (k, stride) the
+scripts use.  Runs without a GPU (planning is host-only)."""
+import numpy as np
+import pytest
+
+import oracle as O
+from apvae.plan import Plan, pad16
+from helpers import bf16_round, emulate_plan, pad_channels
+
+CASES = [
+    # transpose, k, stride, H, W, cin, cout
+    (False, 3, 1, 8, 8, 16, 16),
+    (False, 5, 1, 8, 8, 3, 24),
+    (False, 3, 2, 8, 8, 32, 16),
+    (False, 5, 2, 8, 8, 3, 8),
+    (False, 1, 1, 4, 4, 64, 6),
+    (False, 1, 2, 8, 8, 16, 32),
+    (False, 3, 1, 7, 7, 20, 16),
+    (False, 3, 2, 14, 14, 16, 16),
+    (True, 3, 1, 8, 8, 16, 16),
+    (True, 5, 1, 4, 4, 96, 16),
+    (True, 3, 2, 4, 4, 16, 32),
+    (True, 5, 2, 4, 4, 8, 16),
+    (True, 1, 1, 8, 8, 2, 48),
+    (True, 3, 2, 7, 7, 64, 16),
+]
+
+
+@pytest.mark.parametrize('transpose,k,stride,H,W,cin,cout', CASES)
+def test_plan_matches_oracle(transpose, k, stride, H, W, cin, cout):
+    rs = np.random.RandomState(k * 100 + stride * 10 + cin)
+    n = 3
+    x = bf16_round(rs.normal(size=(n, H, W, cin)))
+    shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
+    kern = bf16_round(rs.normal(size=shp) * 0.2)
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    plan = Plan([dict(src=0, transpose=transpose, stride=stride, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
+    got = emulate_plan(plan, [pad_channels(x, pad16(cin))], n)[..., :cout]
+    fn = O.deconv2d if transpose else O.conv2d
+    want = fn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), stride)
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-9)
+    assert plan.info.macs_per_image > 0
+
+
+def test_fused_shortcut_terms():
+    """conv_1 (3x3, s2) + 1x1 s2 shortcut on another source accumulate in one op
+    (resnet.py:225-265)."""
+    rs = np.random.RandomState(7)
+    n, H, cin, cout = 2, 8, 32, 64
+    r = bf16_round(rs.normal(size=(n, H, H, cin)))
+    x = bf16_round(rs.normal(size=(n, H, H, cin)))
+    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.1)
+    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.1)
+    b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
+    plan = Plan([dict(src=0, stride=2, in_h=H, in_w=H, kernel=k1, bias=b1),
+                 dict(src=1, stride=2, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
+    got = emulate_plan(plan, [r, x], n)[..., :cout]
+    want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 2) + \
+        O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
+    # the two biases are summed in float32 by the planner
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+
+
+def test_dense_as_1x1():
+    """dense == np.dot(x, k) + b (reference tests/layers/core/test_dense.py)."""
+    rs = np.random.RandomState(3)
+    n, fin, fout = 5, 4096, 64
+    x = bf16_round(rs.normal(size=(n, 1, 1, fin)))
+    k = bf16_round(rs.normal(size=(fin, fout)) * 0.05)
+    b = rs.normal(size=fout).astype(np.float32)
+    plan = Plan([dict(src=0, in_h=1, in_w=1, kernel=k.reshape(1, 1, fin, fout), bias=b)], n)
+    assert plan.info.bn == 128 and plan.info.kc == 64
+    got = emulate_plan(plan, [x], n)[:, 0, 0, :fout]
+    np.testing.assert_allclose(got, x[:, 0, 0].astype(np.float64) @ k.astype(np.float64) + b, rtol=1e-9, atol=1e-9)
+
+
+def test_wide_n_is_tiled():
+    k = np.zeros((1, 1, 16, 3136), dtype=np.float32)
+    plan = Plan([dict(src=0, in_h=1, in_w=1, kernel=k)], 4)
+    assert plan.info.nt == 224 and plan.info.n_tiles == 14
+
+
+def test_unsupported_shapes_raise():
+    from apvae import ApvaeError
+    with pytest.raises(ApvaeError):
+        Plan([dict(src=0, stride=3, in_h=9, in_w=9, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1)
+    with pytest.raises(ApvaeError):     # stride-2 conv on an odd grid
+        Plan([dict(src=0, stride=2, in_h=7, in_w=7, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1)
