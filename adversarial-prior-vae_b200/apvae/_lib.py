@@ -18,6 +18,7 @@ PER_IMAGE_ROWS = 9
 PER_SAMPLE_ROWS = 4
 SROW_LOG_PX, SROW_LOG_Q, SROW_LOG_PN, SROW_DG = range(4)
 RES_NONE, RES_SAME, RES_EVEN = 0, 1, 2
+ACCUM_WEIGHT, ACCUM_BATCHES, ACCUM_SLOTS = 9, 10, 16
 
 
 class ApvaeError(RuntimeError):
@@ -90,6 +91,7 @@ _SYMBOLS = [
     ('apvae_decode', C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
     ('apvae_energy', C.c_int, [_P, _P, _P, C.c_int, _P, _P]),
     ('apvae_is_nll', C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
+    ('apvae_accumulate_metrics', C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
     ('apvae_prior_stats', C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     ('apvae_mala', C.c_int, [_P, _P, C.c_int, C.c_int, C.c_float, _P, _P, C.c_uint64, _P, _P, _P, _P]),
     ('apvae_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
@@ -98,6 +100,9 @@ _SYMBOLS = [
     ('apvae_fill_uniform', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, _P]),
     ('apvae_launch_count', C.c_int, [_P, C.POINTER(C.c_int64)]),
     ('apvae_macs', C.c_int, [_P, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    ('apvae_op_count', C.c_int, [_P, C.c_int, C.POINTER(C.c_int)]),
+    ('apvae_op_time', C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int,
+                                C.POINTER(C.c_double), C.POINTER(C.c_float), _P]),
     ('apvae_plan_create', C.c_int, [C.POINTER(ConvTerm), C.c_int, C.c_int, C.POINTER(_P)]),
     ('apvae_plan_get_info', C.c_int, [_P, C.POINTER(PlanInfo)]),
     ('apvae_plan_copy_steps', C.c_int, [_P, C.POINTER(C.c_int32)]),

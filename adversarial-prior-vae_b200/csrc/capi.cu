@@ -247,6 +247,14 @@ int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev,
     return APVAE_OK;
 }
 
+int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, int B, int K, double* accum_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    static_assert(APVAE_ACCUM_SLOTS == kAccumSlots, "accumulator layouts out of sync");
+    if (B <= 0 || K <= 0 || !per_image_dev || !accum_dev) { m.err = "accumulate_metrics: bad arguments"; return APVAE_ERR_INVALID; }
+    LCHECK(launch_accumulate_metrics(per_image_dev, B, K, APVAE_PER_IMAGE_ROWS, accum_dev, stream), "accumulate_metrics");
+    return APVAE_OK;
+}
+
 int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t seed, float* d_g_dev,
                       float* log_pn_dev, void* stream) {
     REQUIRE_BUILT(h);
@@ -302,6 +310,41 @@ int apvae_macs(const apvae_handle* h, double* q, double* g, double* d) {
     if (q) *q = h->m.macs_q;
     if (g) *g = h->m.macs_g;
     if (d) *d = h->m.macs_d;
+    return APVAE_OK;
+}
+
+static Program* pick_net(Model& m, int net) {
+    return net == 0 ? &m.q_prog : net == 1 ? &m.g_prog : net == 2 ? &m.d_prog : nullptr;
+}
+int apvae_op_count(const apvae_handle* h, int net, int* count) {
+    if (!h || !count) return set_global_err("null argument", APVAE_ERR_INVALID);
+    Program* p = pick_net(const_cast<Model&>(h->m), net);
+    if (!p) return set_global_err("net must be 0, 1 or 2", APVAE_ERR_INVALID);
+    *count = (int)p->size();
+    return APVAE_OK;
+}
+int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* name, int name_cap,
+                  double* macs_per_unit, float* ms_per_launch, void* stream) {
+    REQUIRE_BUILT(h);
+    Program* p = pick_net(m, net);
+    if (!p || index < 0 || index >= (int)p->size() || reps <= 0) { m.err = "op_time: bad arguments"; return APVAE_ERR_INVALID; }
+    DevOp& op = *(*p)[index];
+    if (n <= 0 || n > op.capacity_n) { m.err = "op_time: n exceeds the op's capacity"; return APVAE_ERR_INVALID; }
+    if (name && name_cap > 0) { strncpy(name, op.name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
+    if (macs_per_unit) *macs_per_unit = op.macs_per_image;
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    for (int i = 0; i < 2; ++i) LCHECK(devop_launch(m.dev, op, n, stream), "op_time warm-up");
+    cudaEventRecord(e0, st);
+    for (int i = 0; i < reps; ++i) LCHECK(devop_launch(m.dev, op, n, stream), "op_time");
+    cudaEventRecord(e1, st);
+    const cudaError_t e = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (e != cudaSuccess) { m.err = std::string("op_time: ") + cudaGetErrorString(e); return APVAE_ERR_CUDA; }
+    if (ms_per_launch) *ms_per_launch = ms / reps;
     return APVAE_OK;
 }
 

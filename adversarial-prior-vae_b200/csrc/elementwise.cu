@@ -378,6 +378,42 @@ __global__ void gather_cols_kernel(const float* __restrict__ src, int ld, int co
     }
 }
 
+// One block.  accum (double[kAccumSlots]): [r] += sum_b per_image[r][b] for the additive rows;
+// slots ROW_LZ_MAX / ROW_LZ_SUM hold a running (max, sum exp) over BATCHES of
+// lz_b = log-mean-exp over the batch's [K,B] elements (dmm_cifar10.py:922-924,1221-1222);
+// slot 9 += B (weight), slot 10 += 1 (batches).
+__global__ void accumulate_metrics_kernel(const float* __restrict__ per_image, int B, int K, int rows,
+                                          double* __restrict__ accum) {
+    for (int r = 0; r < rows; ++r) {
+        if (r == ROW_LZ_MAX || r == ROW_LZ_SUM) continue;
+        float acc = 0.f;
+        for (int b = threadIdx.x; b < B; b += blockDim.x) acc += per_image[(size_t)r * B + b];
+        acc = block_sum(acc);
+        if (threadIdx.x == 0) accum[r] += (double)acc;
+    }
+    float mx = -INFINITY;
+    for (int b = threadIdx.x; b < B; b += blockDim.x) mx = fmaxf(mx, per_image[(size_t)ROW_LZ_MAX * B + b]);
+    mx = block_max(mx);
+    float sm = 0.f;
+    for (int b = threadIdx.x; b < B; b += blockDim.x)
+        sm += per_image[(size_t)ROW_LZ_SUM * B + b] * expf(per_image[(size_t)ROW_LZ_MAX * B + b] - mx);
+    sm = block_sum(sm);
+    if (threadIdx.x == 0) {
+        const double lz_b = (double)mx + log((double)sm / ((double)K * (double)B));
+        const double nb = accum[10];
+        if (nb == 0.0) {
+            accum[ROW_LZ_MAX] = lz_b;
+            accum[ROW_LZ_SUM] = 1.0;
+        } else {
+            const double m0 = accum[ROW_LZ_MAX], m1 = fmax(m0, lz_b);
+            accum[ROW_LZ_SUM] = accum[ROW_LZ_SUM] * exp(m0 - m1) + exp(lz_b - m1);
+            accum[ROW_LZ_MAX] = m1;
+        }
+        accum[9] += (double)B;
+        accum[10] = nb + 1.0;
+    }
+}
+
 inline int grid_for(long long n, int block, int cap = 148 * 16) {
     long long g = (n + block - 1) / block;
     if (g < 1) g = 1;
@@ -469,6 +505,11 @@ int launch_energy_combine(const float* d_g, const float* gz, const float* z, int
 int launch_quantize_images(const float* head, int ld, long long pixels, int C, uint8_t* out, void* stream) {
     if (pixels <= 0) return 0;
     quantize_kernel<<<grid_for(pixels * C, 256), 256, 0, st(stream)>>>(head, ld, pixels, C, out);
+    return (int)cudaGetLastError();
+}
+int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, double* accum, void* stream) {
+    if (B <= 0) return 0;
+    accumulate_metrics_kernel<<<1, 256, 0, st(stream)>>>(per_image, B, K, rows, accum);
     return (int)cudaGetLastError();
 }
 int launch_clip_min(float* v, long long n, float lo, void* stream) {

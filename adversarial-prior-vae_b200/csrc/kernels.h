@@ -51,6 +51,11 @@ int launch_is_reduce(const float* log_px, const float* log_q, const float* log_p
                      const float* z_f32, int K, int B, int d, float w_xi, float log_Z, float* per_image,
                      void* stream);
 
+// Shard-local accumulation of the Evaluator metrics (replaces the host np.average of
+// trainer/evaluator.py:249-254 and the host logsumexp of dmm_cifar10.py:1221-1222); see elementwise.cu.
+constexpr int kAccumSlots = 16;
+int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, double* accum, void* stream);
+
 // Philox4x32-10 + Box-Muller standard normals (timed runs; parity runs feed eps).
 // truncated != 0: resample into [-2, 2] (tf.truncated_normal, truncated_normal.py:103).
 int launch_fill_normal(float* out, long long n, unsigned long long seed, unsigned long long offset,

@@ -113,6 +113,15 @@ enum { APVAE_SROW_LOG_PX = 0, APVAE_SROW_LOG_Q = 1, APVAE_SROW_LOG_PN = 2, APVAE
 int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev, int B, int K,
                  const float* eps_dev, uint64_t seed, float* per_image_dev, float* per_sample_dev, void* stream);
 
+/* Shard-local metric accumulation, replacing Evaluator.run's host np.average (trainer/evaluator.py:249-254)
+ * and the host logsumexp of the log-Z loop (dmm_cifar10.py:1215-1227).  accum_dev: double[APVAE_ACCUM_SLOTS],
+ * zero-initialised by the caller.  Slots 0-5, 8: sums over images of the per-image rows; slots 6, 7: running
+ * (max, sum exp) over BATCHES of another_log_Z_compute_op's batch value (before + log(len_train));
+ * slot 9: images seen; slot 10: batches seen.  One sum-allreduce of slots 0-5, 8, 9 over ranks gives the
+ * dataset metrics; (6, 7, 10) combine by log-sum-exp. */
+enum { APVAE_ACCUM_WEIGHT = 9, APVAE_ACCUM_BATCHES = 10, APVAE_ACCUM_SLOTS = 16 };
+int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, int B, int K, double* accum_dev, void* stream);
+
 /* test_pn_net branch (:883,915-927): Kp prior draws through G and D.  Outputs [Kp] each. */
 int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t seed, float* d_g_dev,
                       float* log_pn_dev, void* stream);
@@ -136,6 +145,14 @@ int apvae_fill_uniform(float* out_dev, int64_t n, uint64_t seed, uint64_t offset
 /* Bookkeeping for the benchmark: kernels launched so far, algorithmic MACs per unit. */
 int apvae_launch_count(const apvae_handle* h, int64_t* launches);
 int apvae_macs(const apvae_handle* h, double* q_per_image, double* g_per_sample, double* d_per_sample);
+
+/* Per-op device timing for bench.py's roofline: net 0 = q_net, 1 = G_theta (+heads), 2 = D_psi.
+ * apvae_op_time launches op `index` on the first `n` units of its (already populated) input
+ * buffers 2 + `reps` times and returns the CUDA-event average of the last `reps` launches on
+ * `stream` (synchronises that stream). */
+int apvae_op_count(const apvae_handle* h, int net, int* count);
+int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* name, int name_cap,
+                  double* macs_per_unit, float* ms_per_launch, void* stream);
 
 /* ---- layer-level interface (tests; mirrors spt.layers.conv2d / deconv2d / dense) ---- */
 typedef struct apvae_conv_term {

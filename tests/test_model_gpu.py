@@ -1,0 +1,202 @@
+"""GPU parity of the whole evaluation path against the float64 oracle, through the C ABI
+(apvae_create / apvae_load_weights / apvae_encode / apvae_decode / apvae_energy /
+apvae_is_nll / apvae_prior_stats / apvae_sample_images).
+
+Same synthetic weights (glorot-normal kernels INCLUDING the heads the reference
+zero-initialises, N(0,0.1) biases, seed 1234), same synthetic images and the same
+fed-in noise on both sides.  Tolerances are BASELINE.json's:
+per-image NLL within 1e-3 relative; energies D(.) within 1e-2 absolute (bf16 operands,
+fp32 accumulation).  The CUDA path is bf16-in / fp32-accumulate per layer, the oracle
+is float64 end to end.
+"""
+import numpy as np
+import pytest
+
+import oracle as O
+from helpers import synthetic_images
+
+pytestmark = pytest.mark.gpu
+
+NLL_RTOL = 1e-3       # BASELINE.json north_star: per-image NLL within 1e-3 nats relative
+ENERGY_ATOL = 1e-2    # energies within 1e-2 abs in bf16
+
+CASES = {
+    'A128': ('A', dict(z_dim=128), 3, 5),
+    'A1024': ('A', dict(), 2, 3),
+    'Bcifar': ('B', dict(dataset='cifar10'), 3, 5),
+    'Bceleba': ('B', dict(dataset='celebA'), 2, 3),
+    'M40': ('M', dict(), 4, 6),
+}
+
+
+def _make(arch, kw, max_chunk=8, **extra):
+    import apvae
+    from apvae.model import ExpConfig, Model
+    ocfg = O.OracleConfig(arch, **kw)
+    params = O.init_weights(ocfg)
+    cfg = ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim, max_batch=8, max_chunk=max_chunk, **extra)
+    return ocfg, params, cfg, Model(cfg, params)
+
+
+def _inputs(ocfg, B, K):
+    x = synthetic_images((B,) + tuple(ocfg.x_shape), seed=0).astype(np.float64)
+    rs = np.random.RandomState(3)
+    eps = rs.normal(size=(K, B, ocfg.z_dim))
+    if ocfg.arch == 'M':
+        u8 = np.random.RandomState(0).randint(0, 256, size=(B,) + tuple(ocfg.x_shape))
+        x_origin = u8 / 255.0                                               # grey image in [0,1]
+        x = (np.random.RandomState(1).uniform(size=x_origin.shape) < x_origin).astype(np.float64)
+        while np.any(np.abs(eps) > 2):                                      # TruncatedNormal noise
+            bad = np.abs(eps) > 2
+            eps[bad] = rs.normal(size=int(bad.sum()))
+    else:
+        x_origin = x
+    return x, x_origin, eps
+
+
+@pytest.mark.parametrize('case', sorted(CASES))
+def test_networks_match_oracle(case):
+    arch, kw, B, K = CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw)
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    mu_o, ls_o = O.q_net(ocfg, params, x_origin)
+    mu, ls = m.encode(x_origin)
+    assert np.abs(mu.cpu().numpy() - mu_o).max() < 3e-2 * max(1.0, np.abs(mu_o).max())
+    assert np.abs(ls.cpu().numpy() - ls_o).max() < 3e-2 * max(1.0, np.abs(ls_o).max())
+    z = (mu_o + np.exp(ls_o) * eps[0])
+    if arch == 'M':
+        xm_o = O.G_theta(ocfg, params, z)
+        xm = m.decode(z)
+    else:
+        xm_o, xs_o = O.G_theta(ocfg, params, z, return_std=True)
+        xm, xs = m.decode(z, return_std=True)
+        assert np.abs(xs.cpu().numpy() - xs_o).max() < 3e-2 * max(1.0, np.abs(xs_o).max())
+    assert np.abs(xm.cpu().numpy() - xm_o).max() < 2e-2
+    # energies: D(x) on images, D(G(z)) on latents
+    d_o = O.D_psi(ocfg, params, x_origin)
+    d = m.energy_of_images(x_origin).cpu().numpy()
+    assert np.abs(d - d_o).max() < ENERGY_ATOL, (d, d_o)
+    dg_o = O.D_psi(ocfg, params, xm_o)
+    dg = m.energy_of_latents(z).cpu().numpy()
+    assert np.abs(dg - dg_o).max() < ENERGY_ATOL, (dg, dg_o)
+    # uint8 samples: at most 1 grey level off where bf16 rounding crosses a .5 boundary
+    u8 = m.sample_images(z).cpu().numpy().astype(np.int32)
+    u8_o = O.sample_images(ocfg, params, z).astype(np.int32)
+    assert u8.shape == u8_o.shape
+    assert np.abs(u8 - u8_o).max() <= 2
+    assert np.mean(u8 != u8_o) < 0.2
+    m.close()
+
+
+@pytest.mark.parametrize('case', sorted(CASES))
+def test_is_nll_matches_oracle(case):
+    arch, kw, B, K = CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw)      # max_chunk=8 < K*B: exercises ragged chunking
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    xi_raw, beta, log_Z = 0.3, -0.5, 2.5
+    m.set_scalars(xi_raw, beta, log_Z)
+    want = O.eval_batch(ocfg, params, x, x_origin, eps, xi_raw=xi_raw, beta=beta, log_Z=log_Z)
+    got = m.is_nll(x, K, x_origin=x_origin, eps=eps, per_sample=True)
+    g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
+    # per-sample terms
+    assert np.abs(g['log_q'] - want['log_q']).max() < 1e-3 * np.abs(want['log_q']).max() + 1e-2
+    assert np.abs(g['log_pn'] - want['log_pn']).max() < 1e-3 * np.abs(want['log_pn']).max() + 1e-2
+    assert np.abs(g['d_g'] - want['d_g']).max() < ENERGY_ATOL
+    assert np.abs(g['log_px'] - want['log_px']).max() < NLL_RTOL * np.abs(want['log_px']).max()
+    # per-image estimators
+    for ours, theirs in (('ele_test_ll', 'ele_test_ll'), ('ele_test_lb', 'ele_test_lb'),
+                         ('ele_adv_test_ll', 'ele_adv_test_ll'), ('ele_adv_test_lb', 'ele_adv_test_lb')):
+        rel = np.abs(g[ours] - want[theirs]) / np.abs(want[theirs])
+        assert rel.max() < NLL_RTOL, (ours, g[ours], want[theirs])
+    assert np.abs(g['ele_real_energy'] - want['ele_real_energy']).max() < ENERGY_ATOL
+    assert np.abs(g['ele_reconstruct_energy'] - want['d_g'].mean(axis=0)).max() < ENERGY_ATOL
+    # another_log_Z_compute_op from the per-image (max, sumexp) pairs
+    mx, sm = g['ele_lz_max'], g['ele_lz_sum']
+    M = mx.max()
+    lz = M + np.log(np.sum(sm * np.exp(mx - M)) / (K * B)) + np.log(ocfg.len_train)
+    assert abs(lz - want['another_log_Z']) < NLL_RTOL * abs(want['another_log_Z']) + 0.5
+    m.close()
+
+
+def test_estimator_tail_exact_given_same_inputs():
+    """The fused estimator kernels alone (no bf16 conv in between): recompute the per-image
+    rows from the library's own per-sample terms in float64 -> agreement to fp32 rounding."""
+    arch, kw, B, K = CASES['Bcifar']
+    ocfg, params, cfg, m = _make(arch, kw)
+    x, x_origin, eps = _inputs(ocfg, B, 7)
+    K = 7
+    m.set_scalars(0.1, -1.0, 3.0)
+    got = m.is_nll(x, K, eps=eps, per_sample=True)
+    g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
+    z_half = -g['log_pn'] - 0.5 * ocfg.z_dim * np.log(2 * np.pi)
+    energy = ocfg.pull_back_energy_weight * O.sigmoid(0.1) * g['d_g'] + z_half
+    lj = g['log_px'] + g['log_pn']
+    lja = g['log_px'] - energy - 3.0
+    np.testing.assert_allclose(g['ele_test_ll'], O.importance_sampling_log_likelihood(lj, g['log_q'], 0), rtol=2e-6)
+    np.testing.assert_allclose(g['ele_test_lb'], O.elbo_objective(lj, g['log_q'], 0), rtol=2e-6)
+    np.testing.assert_allclose(g['ele_adv_test_ll'], O.importance_sampling_log_likelihood(lja, g['log_q'], 0), rtol=2e-6)
+    np.testing.assert_allclose(g['ele_adv_test_lb'], O.elbo_objective(lja, g['log_q'], 0), rtol=2e-6)
+    m.close()
+
+
+def test_prior_branch_matches_oracle():
+    arch, kw, _, _ = CASES['A128']
+    ocfg, params, cfg, m = _make(arch, kw)
+    Kp = 11
+    eps_p = np.random.RandomState(5).normal(size=(Kp, 1, ocfg.z_dim))
+    want = O.prior_branch(ocfg, params, eps_p)
+    dg, lpn = m.prior_stats(Kp, eps=eps_p)
+    assert np.abs(dg.cpu().numpy() - want['d_g'][:, 0]).max() < ENERGY_ATOL
+    np.testing.assert_allclose(lpn.cpu().numpy(), O.std_normal_log_prob(eps_p)[:, 0], rtol=1e-5)
+    m.close()
+
+
+def test_philox_noise_is_reproducible_and_standard():
+    """eps=None draws in-kernel Philox normals: same seed -> same NLL, moments ~ N(0,1)."""
+    import ctypes as C
+    import torch
+    from apvae import _lib
+    arch, kw, B, K = CASES['Bcifar']
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=64)
+    x, _, _ = _inputs(ocfg, B, K)
+    a = m.is_nll(x, 16, seed=7)['ele_test_ll'].cpu().numpy()
+    b = m.is_nll(x, 16, seed=7)['ele_test_ll'].cpu().numpy()
+    c = m.is_nll(x, 16, seed=8)['ele_test_ll'].cpu().numpy()
+    assert np.array_equal(a, b) and not np.array_equal(a, c)
+    n = 1 << 20
+    buf = torch.empty(n, device='cuda')
+    _lib.check(_lib.lib.apvae_fill_normal(C.c_void_p(buf.data_ptr()), n, 11, 0, 0, None))
+    v = buf.cpu().numpy().astype(np.float64)
+    assert abs(v.mean()) < 5e-3 and abs(v.std() - 1) < 5e-3 and abs((v ** 4).mean() - 3) < 5e-2
+    _lib.check(_lib.lib.apvae_fill_normal(C.c_void_p(buf.data_ptr()), n, 11, 0, 1, None))
+    t = buf.cpu().numpy()
+    assert np.abs(t).max() <= 2.0 and abs(t.std() - 0.8796) < 5e-3      # std of N(0,1) truncated at 2
+    _lib.check(_lib.lib.apvae_fill_uniform(C.c_void_p(buf.data_ptr()), n, 11, 0, None))
+    u = buf.cpu().numpy()
+    assert 0 < u.min() and u.max() < 1 and abs(u.mean() - 0.5) < 2e-3
+    m.close()
+
+
+def test_errors_are_loud():
+    from apvae import ApvaeError
+    from apvae.model import ExpConfig, Model
+    ocfg = O.OracleConfig('B', dataset='cifar10')
+    params = O.init_weights(ocfg)
+    cfg = ExpConfig('B', dataset='cifar10', max_batch=4, max_chunk=8)
+    bad = dict(params)
+    del bad['D_psi/level_-1/bias']
+    with pytest.raises(KeyError):
+        Model(cfg, bad)
+    bad = dict(params)
+    bad['q_net/level_0/shortcut/kernel'] = np.zeros((1, 1, 3, 31), np.float32)
+    with pytest.raises(ValueError):
+        Model(cfg, bad)
+    m = Model(cfg, params)
+    with pytest.raises(ApvaeError):     # B > max_batch
+        m.is_nll(np.zeros((5, 32, 32, 3), np.float32), 2)
+    m.close()
+    ocfg = O.OracleConfig('M')
+    m = Model(ExpConfig('M', max_batch=4, max_chunk=8), O.init_weights(ocfg))
+    with pytest.raises(ApvaeError):     # arch M's G_theta has a single (mean) head
+        m.decode(np.zeros((1, 40), np.float32), return_std=True)
+    m.close()
