@@ -1,0 +1,184 @@
+"""Pins the CPU oracle: (1) against the reference's own known-answer tests (fixtures in
+tests/golden/reference_kats.npz, produced by tests/golden/make_golden.py which EXECUTES the
+reference's numpy test helpers), (2) for the arithmetic the reference holds no independent
+values for (conv / deconv, gradients, MALA) against independent cross-checks: torch-CPU
+conv ops, adjoint identities and finite differences.  No GPU needed."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle as O
+
+GOLD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden', 'reference_kats.npz'))
+
+
+# ---------------------------------------------------------------- reference KATs
+def test_discretized_logistic_matches_reference_naive_pdf():
+    """tfsnippet tests/distributions/test_discretized.py:232-310 (rtol 1e-5, atol 1e-6)."""
+    x, mean, ls = GOLD['dl_x'], GOLD['dl_mean'], GOLD['dl_log_scale']
+    bin_size, lo, hi = GOLD['dl_params']
+    kw = dict(rtol=1e-5, atol=1e-6)
+    f = O.discretized_logistic_log_prob
+    np.testing.assert_allclose(f(x, mean, ls, bin_size, lo, hi, biased_edges=False), GOLD['dl_unbiased'], **kw)
+    np.testing.assert_allclose(f(x, mean, ls, bin_size, None, hi), GOLD['dl_nomin'], **kw)
+    np.testing.assert_allclose(f(x, mean, ls, bin_size, lo, None), GOLD['dl_nomax'], **kw)
+    np.testing.assert_allclose(f(x, mean, ls, bin_size, lo, hi), GOLD['dl_biased'], **kw)
+    np.testing.assert_allclose(f(x, mean, ls, bin_size, lo, hi, group_ndims=2), GOLD['dl_biased_g2'], **kw)
+
+
+def test_discretized_logistic_probabilities_sum_to_one():
+    """test_discretized.py:312-334."""
+    lp = O.discretized_logistic_log_prob(GOLD['ps_x'], GOLD['ps_mean'], GOLD['ps_log_scale'], 1 / 10., 0., 1.)
+    prob = np.exp(lp).sum(axis=0)
+    assert prob.shape == (3, 2, 5, 4)
+    np.testing.assert_allclose(prob, np.ones_like(prob), rtol=1e-5, atol=1e-6)
+
+
+def test_discretized_logistic_extreme_fallback_branch():
+    """test_discretized.py:336-363: cdf_delta < epsilon -> the PixelCNN++ log-pdf approximation.
+    The naive answer is -inf/garbage there; the reference test only requires closeness where the naive
+    value is finite, so check finiteness + the analytic mid-point density."""
+    ls = GOLD['ex_log_scale']
+    lp = O.discretized_logistic_log_prob(np.asarray(0.), np.asarray(0.), ls, 1 / 256., epsilon=1e-7)
+    assert np.all(np.isfinite(lp))
+    np.testing.assert_allclose(lp, np.log(1 / 256.) - ls - 2 * np.log(2.0), rtol=1e-6)
+    naive = GOLD['ex_naive']
+    ok = np.isfinite(naive)
+    np.testing.assert_allclose(lp[ok], naive[ok], rtol=1e-5, atol=1e-1)
+
+
+def test_log_sum_and_mean_exp():
+    """tests/ops/test_misc.py:39-87."""
+    x = GOLD['lse_x']
+    np.testing.assert_allclose(O.log_sum_exp(x, axis=-1), GOLD['lse_last'])
+    np.testing.assert_allclose(O.log_sum_exp(x, axis=(0, 2)), GOLD['lse_02'])
+    np.testing.assert_allclose(O.log_sum_exp(x), GOLD['lse_all'])
+    np.testing.assert_allclose(O.log_sum_exp(x, axis=(0, 2), keepdims=True), GOLD['lse_02'].reshape(1, 10, 1))
+    np.testing.assert_allclose(O.log_mean_exp(x, axis=-1), GOLD['lme_last'])
+    np.testing.assert_allclose(O.log_mean_exp(x, axis=(0, 2)), GOLD['lme_02'])
+    np.testing.assert_allclose(O.log_mean_exp(x), GOLD['lme_all'])
+
+
+def test_maybe_clip_value():
+    """tests/ops/test_misc.py:90-110."""
+    x = np.linspace(0, 1, 101, dtype=np.float32)
+    assert O.maybe_clip_value(x) is x
+    np.testing.assert_allclose(O.maybe_clip_value(x, min_val=.1), np.maximum(x, .1))
+    np.testing.assert_allclose(O.maybe_clip_value(x, max_val=.9), np.minimum(x, .9))
+    np.testing.assert_allclose(O.maybe_clip_value(x, .1, .9), np.maximum(np.minimum(x, .9), .1))
+
+
+def test_importance_sampling_and_elbo_payload():
+    """tests/variational/test_evaluation.py:9-47, test_objectives.py (atol 1e-4)."""
+    log_p, log_q = GOLD['vi_log_p'], GOLD['vi_log_q']
+    np.testing.assert_allclose(O.importance_sampling_log_likelihood(log_p, log_q, 0), GOLD['vi_is_ll'], atol=1e-4)
+    np.testing.assert_allclose(O.elbo_objective(log_p, log_q, 0), GOLD['vi_elbo'], atol=1e-4)
+    np.testing.assert_allclose(O.elbo_objective(log_p, log_q), log_p - log_q, atol=1e-6)
+    with pytest.raises(ValueError):
+        O.importance_sampling_log_likelihood(log_p, log_q, None)
+
+
+def test_evaluator_weighting():
+    """tests/trainer/test_evaluator.py:53-103: arange(6), batch 4 -> 2.5 weighted, 3.0 unweighted."""
+    assert abs(O.evaluator_average(GOLD['ev_batches'], GOLD['ev_weights']) - GOLD['ev_expected'][0]) < 1e-12
+    assert abs(O.evaluator_average(GOLD['ev_batches'], None) - GOLD['ev_expected'][1]) < 1e-12
+
+
+def test_conv_1x1_is_strided_matmul_and_dense_is_dot():
+    """tests/layers/convolutional/test_conv2d.py:117-137, tests/layers/core/test_dense.py."""
+    x, k, b = GOLD['c11_x'], GOLD['c11_k'], GOLD['c11_b']
+    np.testing.assert_allclose(O.conv2d(x, k, b, 1), GOLD['c11_s1'], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(O.conv2d(x, k, b, 2), GOLD['c11_s2'], rtol=1e-5, atol=1e-6)
+    rs = np.random.RandomState(0)
+    xx, kk, bb = rs.normal(size=(5, 3, 7)), rs.normal(size=(7, 4)), rs.normal(size=4)
+    np.testing.assert_allclose(O.dense(xx, kk, bb), np.dot(xx, kk) + bb)
+
+
+# ---------------------------------------------------------------- independent cross-checks (parity unpinned upstream)
+KS = [(3, 1), (5, 1), (3, 2), (5, 2), (1, 1), (1, 2)]
+
+
+def _torch_same_conv(x, kernel, s):
+    import torch
+    import torch.nn.functional as F
+    kh = kernel.shape[0]
+    n, h, w, c = x.shape
+    _, lo_h, hi_h = O.same_padding(h, kh, s)
+    _, lo_w, hi_w = O.same_padding(w, kh, s)
+    xt = torch.tensor(x).permute(0, 3, 1, 2)
+    xt = F.pad(xt, (lo_w, hi_w, lo_h, hi_h))
+    wt = torch.tensor(kernel).permute(3, 2, 0, 1)
+    return F.conv2d(xt, wt, stride=s).permute(0, 2, 3, 1).numpy()
+
+
+@pytest.mark.parametrize('k,s', KS)
+def test_conv2d_matches_torch_cpu(k, s):
+    rs = np.random.RandomState(k * 10 + s)
+    x = rs.normal(size=(2, 8, 10, 3))
+    kern = rs.normal(size=(k, k, 3, 4))
+    np.testing.assert_allclose(O.conv2d(x, kern, None, s), _torch_same_conv(x, kern, s), rtol=1e-10, atol=1e-10)
+
+
+@pytest.mark.parametrize('k,s', KS)
+def test_deconv2d_is_the_adjoint_of_same_conv(k, s):
+    """<conv(x; W), y> == <x, deconv(y; W)> with the deconv kernel laid out [kh,kw,Cout,Cin] = conv's
+    [kh,kw,Cin_conv,Cout_conv] (conv2d_.py:339,464-471: conv2d_transpose is the gradient of conv2d)."""
+    rs = np.random.RandomState(k * 10 + s + 1)
+    h = 8
+    x = rs.normal(size=(2, h, h, 3))                 # conv input (the deconv OUTPUT grid)
+    kern = rs.normal(size=(k, k, 3, 5))              # conv: 3 -> 5 ; as deconv kernel: Cout=3, Cin=5
+    y = rs.normal(size=(2, h // s, h // s, 5))
+    lhs = np.sum(O.conv2d(x, kern, None, s) * y)
+    rhs = np.sum(x * O.deconv2d(y, kern, None, s))
+    assert abs(lhs - rhs) < 1e-9 * max(1.0, abs(lhs))
+
+
+@pytest.mark.parametrize('arch,kw', [('A', dict(z_dim=64)), ('B', dict(dataset='cifar10', z_dim=24)), ('M', dict(z_dim=12))])
+def test_energy_gradient_by_finite_differences(arch, kw):
+    cfg = O.OracleConfig(arch, **kw)
+    params = O.init_weights(cfg)
+    rs = np.random.RandomState(0)
+    z = rs.normal(size=(2, 1, cfg.z_dim))
+    e, g, pure = O.energy_and_grad(cfg, params, z, xi_raw=0.2)
+    assert e.shape == (2, 1) and g.shape == z.shape and pure.shape == (2, 1)
+    for idx in [(0, 0, 0), (1, 0, cfg.z_dim - 1), (0, 0, cfg.z_dim // 2)]:
+        h = 1e-5
+        zp, zm = z.copy(), z.copy()
+        zp[idx] += h
+        zm[idx] -= h
+        ep = O.energy_and_grad(cfg, params, zp, xi_raw=0.2)[0]
+        em = O.energy_and_grad(cfg, params, zm, xi_raw=0.2)[0]
+        fd = (ep[idx[:2]] - em[idx[:2]]) / (2 * h)
+        assert abs(fd - g[idx]) < 1e-4 * max(1.0, abs(fd)), (idx, fd, g[idx])
+
+
+def test_mala_step_properties():
+    """alpha -> tiny: proposals are accepted (ratio ~ 1); rejected chains keep z exactly (dmm_cifar10.py:224-226)."""
+    cfg = O.OracleConfig('B', dataset='cifar10', z_dim=16)
+    params = O.init_weights(cfg)
+    rs = np.random.RandomState(1)
+    z = rs.normal(size=(3, 1, 16))
+    eps = rs.normal(size=z.shape)
+    z1, e, pure, ratio = O.mala_step(cfg, params, z, eps, np.zeros((3, 1)), 1e-9)
+    assert np.all(ratio > 0.99) and np.all(z1 != z)
+    z2, _, _, ratio2 = O.mala_step(cfg, params, z, eps, np.ones((3, 1)) * 2, 1e-9)     # u > 1: never accept
+    assert np.array_equal(z2, z)
+    out = O.mala_sample(cfg, params, z, rs.normal(size=(4, 3, 1, 16)), rs.uniform(size=(4, 3, 1)), alpha=1e-4)
+    assert out['history_z'].shape == (4, 3, 1, 16) and np.array_equal(out['history_z'][0], z)
+
+
+def test_eval_batch_self_consistency_and_weight_schema():
+    from apvae.model import ExpConfig, weight_schema
+    for arch, kw in (('A', dict(z_dim=128)), ('A', dict()), ('B', dict(dataset='cifar10')), ('B', dict(dataset='celebA')), ('M', dict())):
+        ocfg = O.OracleConfig(arch, **kw)
+        ours = dict(weight_schema(ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim)))
+        theirs = {k: tuple(v) for k, v in O.weight_shapes(ocfg).items()}
+        assert ours == theirs                        # the C library's TF variable schema == the oracle's
+    cfg = O.OracleConfig('M', z_dim=8)
+    params = O.init_weights(cfg)
+    rs = np.random.RandomState(0)
+    x = (rs.uniform(size=(2, 28, 28, 1)) < 0.5).astype(np.float64)
+    out = O.eval_batch(cfg, params, x, x, np.clip(rs.normal(size=(3, 2, 8)), -2, 2))
+    assert np.all(out['ele_test_lb'] <= out['ele_test_ll'] + 1e-9)       # Jensen: ELBO <= IS-LL
+    assert np.all(out['ele_adv_test_lb'] <= out['ele_adv_test_ll'] + 1e-9)
