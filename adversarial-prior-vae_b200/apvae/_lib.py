@@ -59,6 +59,9 @@ class PlanInfo(C.Structure):
         ('src_dims', (C.c_uint64 * 5) * 3), ('src_strides', (C.c_uint64 * 4) * 3),
         ('src_box', (C.c_uint32 * 5) * 3),
         ('macs_per_image', C.c_double),
+        ('patch', C.c_int), ('patch_macc', C.c_int), ('patch_cluster', C.c_int),
+        ('patch_rows_tile', C.c_int), ('patch_groups', C.c_int), ('patch_items', C.c_int),
+        ('patch_a_stages', C.c_int), ('patch_b_stages', C.c_int), ('patch_prow', C.c_int * 2),
     ]
 
 
@@ -108,6 +111,8 @@ _SYMBOLS = [
     ('apvae_plan_copy_steps', C.c_int, [_P, C.POINTER(C.c_int32)]),
     ('apvae_plan_copy_weights', C.c_int, [_P, C.POINTER(C.c_uint16)]),
     ('apvae_plan_copy_bias', C.c_int, [_P, C.POINTER(C.c_float)]),
+    ('apvae_plan_copy_patch_groups', C.c_int, [_P, C.POINTER(C.c_int32)]),
+    ('apvae_plan_copy_patch_weights', C.c_int, [_P, C.POINTER(C.c_uint16)]),
     ('apvae_plan_destroy', C.c_int, [_P]),
     ('apvae_plan_run', C.c_int, [_P, C.c_int, C.POINTER(_P), C.c_int, C.POINTER(Epilogue)]),
 ]

@@ -67,6 +67,19 @@ class Plan(object):
         return out
 
     @property
+    def patch_groups(self):
+        out = np.zeros((self.info.patch_groups, 6), dtype=np.int32)
+        check(lib.apvae_plan_copy_patch_groups(self._h, out.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out
+
+    @property
+    def patch_weights(self):
+        i = self.info
+        out = np.zeros((i.patch_items, i.npad, i.kc), dtype=np.uint16)
+        check(lib.apvae_plan_copy_patch_weights(self._h, out.ctypes.data_as(C.POINTER(C.c_uint16))))
+        return out
+
+    @property
     def bias(self):
         out = np.zeros((self.info.npad,), dtype=np.float32)
         check(lib.apvae_plan_copy_bias(self._h, out.ctypes.data_as(C.POINTER(C.c_float))))

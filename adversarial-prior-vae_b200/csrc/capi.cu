@@ -1,6 +1,7 @@
 // extern "C" surface declared in include/apvae.h.
 #include <cuda_runtime.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <mutex>
@@ -15,7 +16,18 @@ struct apvae_handle {
 };
 struct apvae_plan {
     OpPlan plan;
+    bool has_patch = false;
+    PatchPlan patch;
 };
+
+static int env_int(const char* name) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : 0;
+}
+static bool patch_enabled() {
+    const char* v = getenv("APVAE_PATCH");
+    return !(v && v[0] == '0');
+}
 
 static std::string g_err;
 static std::mutex g_err_mu;
@@ -362,6 +374,10 @@ int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, 
     apvae_plan* p = new apvae_plan();
     std::string e;
     if (!plan_op(ts, capacity_n, &p->plan, &e)) { delete p; return set_global_err(e, APVAE_ERR_UNSUPPORTED); }
+    if (patch_enabled()) {
+        std::string pe;
+        p->has_patch = plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->patch, &pe);
+    }
     *out = p;
     return APVAE_OK;
 }
@@ -382,6 +398,13 @@ int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
         for (int i = 0; i < 4; ++i) info->src_strides[s][i] = P.src[s].strides[i];
     }
     info->macs_per_image = P.macs_per_image;
+    if (p->has_patch) {
+        const PatchPlan& Q = p->patch;
+        info->patch = 1; info->patch_macc = Q.macc; info->patch_cluster = Q.cluster; info->patch_rows_tile = Q.rows_tile;
+        info->patch_groups = (int)Q.groups.size(); info->patch_items = Q.num_items;
+        info->patch_a_stages = Q.a_stages; info->patch_b_stages = Q.b_stages;
+        info->patch_prow[0] = Q.prow[0]; info->patch_prow[1] = Q.prow[1];
+    }
     return APVAE_OK;
 }
 
@@ -403,6 +426,20 @@ int apvae_plan_copy_bias(const apvae_plan* p, float* out) {
     memcpy(out, p->plan.bias.data(), p->plan.bias.size() * sizeof(float));
     return APVAE_OK;
 }
+int apvae_plan_copy_patch_groups(const apvae_plan* p, int32_t* out) {
+    if (!p || !out || !p->has_patch) return set_global_err("no patch plan", APVAE_ERR_INVALID);
+    for (size_t i = 0; i < p->patch.groups.size(); ++i) {
+        const PatchGroup& g = p->patch.groups[i];
+        out[6 * i + 0] = g.src; out[6 * i + 1] = g.dx; out[6 * i + 2] = g.py0; out[6 * i + 3] = g.k;
+        out[6 * i + 4] = g.c0; out[6 * i + 5] = g.prow;
+    }
+    return APVAE_OK;
+}
+int apvae_plan_copy_patch_weights(const apvae_plan* p, uint16_t* out) {
+    if (!p || !out || !p->has_patch) return set_global_err("no patch plan", APVAE_ERR_INVALID);
+    memcpy(out, p->patch.wpack.data(), p->patch.wpack.size() * sizeof(uint16_t));
+    return APVAE_OK;
+}
 int apvae_plan_destroy(apvae_plan* p) { delete p; return APVAE_OK; }
 
 int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid, const apvae_epilogue* epi) {
@@ -418,7 +455,9 @@ int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, 
     ep.mask = epi->mask_dev; ep.ld_mask = epi->ld_mask; ep.tanh_cols = epi->tanh_cols;
     DevOp op;
     op.name = "plan_run";
-    if (!devop_create(dev, p->plan, src_dev, ep, &op, &e)) return set_global_err(e, APVAE_ERR_CUDA);
+    const bool use_patch = p->has_patch && ep.res_mode != RES_EVEN;
+    if (!(use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, &op, &e) : devop_create(dev, p->plan, src_dev, ep, &op, &e)))
+        return set_global_err(e, APVAE_ERR_CUDA);
     int err = devop_launch(dev, op, n_valid, nullptr);
     if (err == 0) err = (int)cudaDeviceSynchronize();
     if (err != 0) return set_global_err(std::string("plan_run: ") + cudaGetErrorString((cudaError_t)err), APVAE_ERR_CUDA);

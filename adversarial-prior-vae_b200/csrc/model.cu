@@ -1,6 +1,7 @@
 #include "model.h"
 
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <string.h>
 #include "kernels.h"
 
@@ -48,12 +49,25 @@ const HostArr* Model::W_(const std::string& name, std::initializer_list<int64_t>
 
 bool Model::add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms,
                    const std::vector<const void*>& srcs, const Epilogue& epi, int cap, double* macs) {
-    OpPlan plan;
     std::string perr;
-    if (!plan_op(terms, cap, &plan, &perr)) return fail("plan " + name + ": " + perr);
-    if ((int)srcs.size() != plan.nsrc) return fail("plan " + name + ": source count mismatch");
     std::unique_ptr<DevOp> op(new DevOp());
     op->name = name;
+    // stride-1 convs on wide grids: the A-stationary kernel; everything else: the tap-GEMM kernel
+    const char* env = getenv("APVAE_PATCH");
+    PatchPlan pplan;
+    const char* em = getenv("APVAE_PATCH_MACC");
+    const char* ec = getenv("APVAE_PATCH_CLUSTER");
+    if (!(env && env[0] == '0') && epi.res_mode != RES_EVEN &&
+        plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr)) {
+        if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");
+        if (!devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
+        if (macs) *macs += pplan.macs_per_image;
+        prog.push_back(std::move(op));
+        return true;
+    }
+    OpPlan plan;
+    if (!plan_op(terms, cap, &plan, &perr)) return fail("plan " + name + ": " + perr);
+    if ((int)srcs.size() != plan.nsrc) return fail("plan " + name + ": source count mismatch");
     if (!devop_create(dev, plan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
     if (macs) *macs += plan.macs_per_image;
     prog.push_back(std::move(op));

@@ -1,0 +1,56 @@
+// Patch-GEMM: the A-stationary implicit-GEMM kernel for stride-1 conv2d / conv2d_transpose
+// (reference: tfsnippet/layers/convolutional/conv2d_.py:204-211,464-471) on image widths
+// W in {16, 32, 64, 128}.
+//
+// The tap-GEMM kernel (tapgemm.h) re-reads the shifted activation window from L2 once per
+// filter tap, which makes L2 -> SM bandwidth (about 6300 B/clk chip-wide) the limiter of the
+// wide layers.  Here a tile is `macc` x 128 consecutive output pixels (whole rows) of ONE image.
+// For every (channel chunk, horizontal tap offset dx) the producer loads ONE activation patch
+//     [rows_tile + k - 1 rows][W pixels][kc channels]
+// by TMA (box shifted by dx; the SAME-padding halo is the TMA zero fill).  All k vertical taps
+// of that dx then read the SAME patch: tap j's A operand is the patch advanced by j*W rows, i.e.
+// the UMMA shared-memory descriptor start address + j*W*kc*2 bytes (a multiple of the swizzle
+// period, so no re-swizzling).  Activations are therefore fetched ndx*(rows+k-1)/rows times
+// instead of k*ndx times.  Weight tiles stream through their own ring; with cluster size c > 1
+// each CTA fetches 1/c of every weight tile and TMA-multicasts it to the whole cluster.
+//
+// A "group" = (source tensor, channel chunk, dx); it owns k weight tiles ("items").
+#pragma once
+#include <stdint.h>
+#include <cuda.h>
+#include "tapgemm.h"
+
+namespace apvae {
+
+struct PatchGroup {
+    int16_t src;     // which A tensor map (0..1)
+    int16_t dx;      // horizontal shift of the patch box
+    int16_t py0;     // vertical shift of patch row 0 relative to the tile's first output row
+    int16_t k;       // weight tiles (vertical taps) that read this patch
+    int32_t c0;      // channel coordinate of the chunk
+    int32_t prow;    // patch rows of this source (= TMA box height)
+};
+
+constexpr int kPatchMaxSrc = 2;
+
+struct alignas(64) PatchGemmParams {
+    CUtensorMap tm_a[kPatchMaxSrc];  // 5-D (C, W, 1, H, N), box (kc, W, 1, prow_src, 1)
+    CUtensorMap tm_b;                // 2-D (kc, items*Npad), box (kc, NT / cluster)
+    const PatchGroup* groups;        // device pointer
+    int num_groups, num_items;
+    int W, H;                        // image size (stride 1: input grid == output grid)
+    int rows_tile, macc;             // output rows per tile = macc * 128 / W
+    int tiles_y;
+    int n_valid;
+    int Npad, NT;                    // NT == Npad <= 256, macc * NT <= 256
+    int kc;                          // 16, 32 or 64 channels per chunk
+    int a_stages, b_stages;
+    uint32_t a_slot_bytes, b_slot_bytes;
+    int cluster;                     // 1, 2 or 4 CTAs sharing the weight stream
+    EpilogueArgs epi;
+};
+
+int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream);
+uint32_t patchgemm_smem_bytes(const PatchGemmParams& p);
+
+}  // namespace apvae

@@ -198,4 +198,116 @@ bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, s
     return true;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Patch (A-stationary) plan.  Source shift of a tap: conv2d (dj - pad_lo, di - pad_lo);
+// conv2d_transpose stride 1 (pad_lo - dj, pad_lo - di)  [SURVEY section 9].
+bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force_macc, int force_cluster,
+                   PatchPlan* plan, std::string* err) {
+    auto fail = [&](const char* m) { if (err) *err = m; return false; };
+    if (terms.empty() || terms.size() > (size_t)kPatchMaxSrc) return fail("patch: 1..2 terms");
+    PatchPlan& P = *plan;
+    P = PatchPlan();
+    P.capacity_n = capacity_n;
+    const TermSpec& t0 = terms[0];
+    const int W = t0.in_w, H = t0.in_h, cp = t0.in_cp;
+    if (W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 16, 32, 64 or 128");
+    for (size_t i = 0; i < terms.size(); ++i) {
+        const TermSpec& t = terms[i];
+        if (t.stride != 1) return fail("patch: stride-1 terms only");
+        if (!(t.k & 1)) return fail("patch: odd kernel sizes only");
+        if (t.in_w != W || t.in_h != H) return fail("patch: terms disagree on the grid");
+        if (t.in_cp != cp || cp % 16 || cp < t.cin) return fail("patch: bad channel padding");
+        if (t.cout != t0.cout) return fail("patch: terms disagree on cout");
+        if (t.src != (int)i) return fail("patch: term i must read source i");
+    }
+    P.w = W; P.h = H; P.in_cp = cp;
+    P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
+    P.cout = t0.cout;
+    P.npad = pad16(t0.cout);
+    if (P.npad > 256) return fail("patch: cout > 256");
+    P.nsrc = (int)terms.size();
+    const int rows128 = kTileM / W;
+    if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
+    int kmax = 1;
+    for (const TermSpec& t : terms) kmax = std::max(kmax, t.k);
+    const uint32_t budget = 227u * 1024u - 2048u - 1024u;
+    P.b_slot_bytes = ((uint32_t)P.npad * P.kc * 2 + 1023u) & ~1023u;
+    auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * W * P.kc * 2 + 1023u) & ~1023u; };
+    int macc = 0;
+    for (int cand : {4, 2, 1}) {
+        if (force_macc && cand != force_macc) continue;
+        if (cand * P.npad > 256) continue;
+        const int rt = cand * rows128;
+        if (rt > H || H % rt) continue;
+        if (2 * a_slot_for(cand) + (uint32_t)std::min(kmax + 1, 4) * P.b_slot_bytes > budget) continue;
+        macc = cand;
+        break;
+    }
+    if (!macc) return fail("patch: no accumulator count fits");
+    P.macc = macc;
+    P.rows_tile = macc * rows128;
+    P.tiles_y = (H + P.rows_tile - 1) / P.rows_tile;
+    P.a_slot_bytes = a_slot_for(macc);
+    // ring depths: weights first (k+2 tiles keep one dx group ahead), then patches, then more weights
+    P.b_stages = std::min(12, kmax + 2);
+    while (P.b_stages > 2 && 2 * P.a_slot_bytes + P.b_stages * P.b_slot_bytes > budget) --P.b_stages;
+    P.a_stages = 2;
+    while (P.a_stages < 4 && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
+    while (P.b_stages < 12 && P.a_stages * P.a_slot_bytes + (P.b_stages + 1) * P.b_slot_bytes <= budget) ++P.b_stages;
+    // cluster: share the weight stream when it is heavy enough to matter
+    int c = 1;
+    if (P.npad >= 64) {
+        if ((P.npad / 4) % 8 == 0) c = 4;
+        else if ((P.npad / 2) % 8 == 0) c = 2;
+    }
+    if (force_cluster) {
+        if (force_cluster != 1 && force_cluster != 2 && force_cluster != 4) return fail("patch: cluster must be 1, 2 or 4");
+        if ((P.npad / force_cluster) % 8) return fail("patch: cout slice per cluster CTA must be a multiple of 8");
+        c = force_cluster;
+    }
+    P.cluster = c;
+    // groups + packed weights + bias
+    P.bias.assign(P.npad, 0.f);
+    for (const TermSpec& t : terms)
+        if (t.bias) for (int n = 0; n < t.cout; ++n) P.bias[n] += t.bias[n];
+    P.macs_per_image = 0;
+    for (const TermSpec& t : terms) {
+        int o, lo_h, lo_w, hi;
+        same_padding(H, t.k, 1, &o, &lo_h, &hi);
+        same_padding(W, t.k, 1, &o, &lo_w, &hi);
+        P.prow[t.src] = P.rows_tile + t.k - 1;
+        const int used_chunks = (t.cin + P.kc - 1) / P.kc;
+        for (int c0 = 0; c0 < used_chunks; ++c0) {
+            for (int g = 0; g < t.k; ++g) {            // dx ascending: dx = g - lo_w
+                const int dx = g - lo_w;
+                PatchGroup gr;
+                gr.src = (int16_t)t.src; gr.dx = (int16_t)dx; gr.py0 = (int16_t)(-lo_h); gr.k = (int16_t)t.k;
+                gr.c0 = c0 * P.kc; gr.prow = P.prow[t.src];
+                P.groups.push_back(gr);
+                for (int j = 0; j < t.k; ++j) {        // dy ascending: dy = j - lo_h
+                    const int dy = j - lo_h;
+                    const int dj = t.transpose ? lo_w - dx : dx + lo_w;
+                    const int di = t.transpose ? lo_h - dy : dy + lo_h;
+                    const size_t base = P.wpack.size();
+                    P.wpack.resize(base + (size_t)P.npad * P.kc, 0);
+                    const size_t tap_off = (size_t)di * t.k + dj;
+                    for (int n = 0; n < t.cout; ++n)
+                        for (int kk = 0; kk < P.kc; ++kk) {
+                            const int ci = c0 * P.kc + kk;
+                            if (ci >= t.cin) break;
+                            const float w = t.transpose ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
+                                                        : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
+                            P.wpack[base + (size_t)n * P.kc + kk] = f32_to_bf16(w);
+                        }
+                    ++P.num_items;
+                }
+            }
+        }
+        P.macs_per_image += (double)t.k * t.k * t.cin * t.cout * H * W;
+    }
+    if ((int)P.groups.size() > 64) return fail("patch: too many groups");
+    return true;
+}
+
 }  // namespace apvae

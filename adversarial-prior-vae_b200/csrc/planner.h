@@ -13,6 +13,7 @@
 #include <string>
 #include <vector>
 #include "tapgemm.h"
+#include "patchgemm.h"
 
 namespace apvae {
 
@@ -49,6 +50,24 @@ struct OpPlan {
     double macs_per_image = 0;     // algorithmic multiply-accumulates (unpadded)
 };
 
+// Plan of the A-stationary kernel (patchgemm.h) for stride-1 terms on widths 16..128.
+struct PatchPlan {
+    int kc = 0, npad = 0, cout = 0;
+    int w = 0, h = 0, rows_tile = 0, macc = 1, tiles_y = 0;
+    int nsrc = 0;
+    int prow[kPatchMaxSrc] = {0, 0};
+    int in_cp = 0;
+    std::vector<PatchGroup> groups;
+    int num_items = 0;
+    std::vector<uint16_t> wpack;   // bf16 [items][npad][kc]
+    std::vector<float> bias;       // [npad]
+    int a_stages = 0, b_stages = 0;
+    uint32_t a_slot_bytes = 0, b_slot_bytes = 0;
+    int cluster = 1;
+    int capacity_n = 0;
+    double macs_per_image = 0;
+};
+
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 inline int pad16(int c) { return round_up(c, 16); }
 
@@ -61,5 +80,11 @@ float bf16_to_f32(uint16_t h);
 // Builds the plan.  All terms must agree on the output grid and on in_cp.
 // Returns false and fills *err on unsupported shapes.
 bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, std::string* err);
+
+// Returns false (with *err = reason) when the op is not eligible for the patch kernel:
+// every term must be stride 1 on the same W x H grid with W in {16,32,64,128}, <= 2 terms, cout <= 256.
+// force_macc / force_cluster: 0 = choose automatically.
+bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force_macc, int force_cluster,
+                   PatchPlan* plan, std::string* err);
 
 }  // namespace apvae

@@ -45,15 +45,100 @@ bool device_open(int device, DeviceInfo* info, std::string* err) {
     return true;
 }
 
+static CUtensorMapSwizzle swizzle_for(int kc) {
+    return kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : kc == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+}
+
 DevOp::~DevOp() {
     if (d_steps) cudaFree(d_steps);
     if (d_w) cudaFree(d_w);
     if (d_bias) cudaFree(d_bias);
+    if (d_groups) cudaFree(d_groups);
 }
 
-static CUtensorMapSwizzle swizzle_for(int kc) {
-    return kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : kc == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B;
+static void fill_epilogue(EpilogueArgs& e, const Epilogue& epi, const float* bias) {
+    e.bias = bias;
+    e.out_raw = epi.out_raw; e.out_act = epi.out_act; e.ldo = epi.ldo;
+    e.bf16_zero_from = epi.bf16_zero_from;
+    e.out_f32 = epi.out_f32; e.ld_f32 = epi.ld_f32; e.f32_cols = epi.f32_cols;
+    e.res = epi.res; e.res_mode = epi.res_mode; e.ld_res = epi.ld_res;
+    e.mask = epi.mask; e.ld_mask = epi.ld_mask;
+    e.tanh_cols = epi.tanh_cols;
+    e.lrelu_alpha = 0.2f;
 }
+
+static bool check_epilogue(const Epilogue& epi, int npad, const std::string& name, std::string* err) {
+    if ((epi.out_raw || epi.out_act) && (epi.ldo % 16 != 0 || epi.ldo < npad)) {
+        if (err) *err = "epilogue: ldo must be a multiple of 16 and >= padded cout (op " + name + ")";
+        return false;
+    }
+    if (epi.res && (epi.ld_res % 8 != 0 || epi.ld_res < npad)) {
+        if (err) *err = "epilogue: residual row too short (op " + name + ")";
+        return false;
+    }
+    if (epi.mask && (epi.ld_mask % 8 != 0 || epi.ld_mask < npad)) {
+        if (err) *err = "epilogue: mask row too short (op " + name + ")";
+        return false;
+    }
+    return true;
+}
+
+bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
+                        DevOp* op, std::string* err) {
+    EncodeTiledFn encode = reinterpret_cast<EncodeTiledFn>(dev.encode_fn);
+    if (epi.res_mode == RES_EVEN) { if (err) *err = "patch kernel has no even-pixel residual mode"; return false; }
+    if (!check_epilogue(epi, plan.npad, op->name, err)) return false;
+    const size_t ngroups = plan.groups.size();
+    APVAE_CUDA_OK(cudaMalloc(&op->d_groups, ngroups * sizeof(PatchGroup)), err);
+    APVAE_CUDA_OK(cudaMalloc(&op->d_w, plan.wpack.size() * sizeof(uint16_t)), err);
+    APVAE_CUDA_OK(cudaMalloc(&op->d_bias, plan.bias.size() * sizeof(float)), err);
+    APVAE_CUDA_OK(cudaMemcpy(op->d_groups, plan.groups.data(), ngroups * sizeof(PatchGroup), cudaMemcpyHostToDevice), err);
+    APVAE_CUDA_OK(cudaMemcpy(op->d_w, plan.wpack.data(), plan.wpack.size() * sizeof(uint16_t), cudaMemcpyHostToDevice), err);
+    APVAE_CUDA_OK(cudaMemcpy(op->d_bias, plan.bias.data(), plan.bias.size() * sizeof(float), cudaMemcpyHostToDevice), err);
+    PatchGemmParams& p = op->pparams;
+    memset(&p, 0, sizeof(p));
+    const cuuint32_t ones[5] = {1, 1, 1, 1, 1};
+    const cuuint64_t C = plan.in_cp, W = plan.w, H = plan.h;
+    for (int s = 0; s < plan.nsrc; ++s) {
+        cuuint64_t dims[5] = {C, W, 1, H, (cuuint64_t)plan.capacity_n};
+        cuuint64_t strides[4] = {C * 2, W * C * 2, W * C * 2, H * W * C * 2};
+        cuuint32_t box[5] = {(cuuint32_t)plan.kc, (cuuint32_t)W, 1, (cuuint32_t)plan.prow[s], 1};
+        CUresult r = encode(&p.tm_a[s], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(src_ptrs[s]), dims, strides,
+                            box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc),
+                            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            if (err) *err = "cuTensorMapEncodeTiled(patch A) failed with CUresult " + std::to_string((int)r) + " for op " + op->name;
+            return false;
+        }
+    }
+    for (int s = plan.nsrc; s < kPatchMaxSrc; ++s) p.tm_a[s] = p.tm_a[0];
+    {
+        cuuint64_t dims[2] = {(cuuint64_t)plan.kc, (cuuint64_t)plan.num_items * plan.npad};
+        cuuint64_t strides[1] = {(cuuint64_t)plan.kc * 2};
+        cuuint32_t box[2] = {(cuuint32_t)plan.kc, (cuuint32_t)(plan.npad / plan.cluster)};
+        CUresult r = encode(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op->d_w, dims, strides, box, ones,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            if (err) *err = "cuTensorMapEncodeTiled(patch B) failed with CUresult " + std::to_string((int)r) + " for op " + op->name;
+            return false;
+        }
+    }
+    p.groups = op->d_groups;
+    p.num_groups = (int)ngroups; p.num_items = plan.num_items;
+    p.W = plan.w; p.H = plan.h; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
+    p.n_valid = 0;
+    p.Npad = plan.npad; p.NT = plan.npad; p.kc = plan.kc;
+    p.a_stages = plan.a_stages; p.b_stages = plan.b_stages;
+    p.a_slot_bytes = plan.a_slot_bytes; p.b_slot_bytes = plan.b_slot_bytes;
+    p.cluster = plan.cluster;
+    fill_epilogue(p.epi, epi, op->d_bias);
+    op->is_patch = true;
+    op->macs_per_image = plan.macs_per_image;
+    op->capacity_n = plan.capacity_n;
+    return true;
+}
+
 
 bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
                   DevOp* op, std::string* err) {
@@ -112,33 +197,19 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
     p.a_bytes = (uint32_t)plan.rows * plan.kc * 2;
     p.b_bytes = (uint32_t)plan.nt * plan.kc * 2;
     p.stage_bytes = (kTileM * plan.kc * 2 + plan.nt * plan.kc * 2 + 1023u) & ~1023u;
-    p.bias = op->d_bias;
-    p.out_raw = epi.out_raw; p.out_act = epi.out_act; p.ldo = epi.ldo;
-    p.bf16_zero_from = epi.bf16_zero_from;
-    p.out_f32 = epi.out_f32; p.ld_f32 = epi.ld_f32; p.f32_cols = epi.f32_cols;
-    p.res = epi.res; p.res_mode = epi.res_mode; p.ld_res = epi.ld_res;
-    p.mask = epi.mask; p.ld_mask = epi.ld_mask;
-    p.tanh_cols = epi.tanh_cols;
-    p.lrelu_alpha = 0.2f;
+    fill_epilogue(p.epi, epi, op->d_bias);
     op->macs_per_image = plan.macs_per_image;
     op->capacity_n = plan.capacity_n;
-    if ((epi.out_raw || epi.out_act) && (epi.ldo % 16 != 0 || epi.ldo < plan.npad)) {
-        if (err) *err = "epilogue: ldo must be a multiple of 16 and >= padded cout (op " + op->name + ")";
-        return false;
-    }
-    if (epi.res && (epi.ld_res % 8 != 0 || epi.ld_res < plan.npad)) {
-        if (err) *err = "epilogue: residual row too short (op " + op->name + ")";
-        return false;
-    }
-    if (epi.mask && (epi.ld_mask % 8 != 0 || epi.ld_mask < plan.npad)) {
-        if (err) *err = "epilogue: mask row too short (op " + op->name + ")";
-        return false;
-    }
+    if (!check_epilogue(epi, plan.npad, op->name, err)) return false;
     return true;
 }
 
 int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
     if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
+    if (op.is_patch) {
+        op.pparams.n_valid = n_valid;
+        return launch_patchgemm(op.pparams, dev.num_sms, stream);
+    }
     op.params.n_valid = n_valid;
     return launch_tapgemm(op.params, dev.num_sms, stream);
 }

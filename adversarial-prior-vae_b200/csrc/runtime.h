@@ -6,6 +6,7 @@
 #include <vector>
 #include "planner.h"
 #include "tapgemm.h"
+#include "patchgemm.h"
 
 namespace apvae {
 
@@ -39,6 +40,9 @@ struct DevOp {
     uint16_t* d_w = nullptr;
     float* d_bias = nullptr;
     TapGemmParams params;
+    bool is_patch = false;          // true: the A-stationary kernel (patchgemm.h) runs this op
+    PatchGroup* d_groups = nullptr;
+    PatchGemmParams pparams;
     double macs_per_image = 0;
     int capacity_n = 0;
     ~DevOp();
@@ -50,6 +54,8 @@ struct DevOp {
 // Uploads the plan and encodes the tensor maps against `src_ptrs` (bf16 NHWC device tensors).
 bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
                   DevOp* op, std::string* err);
+bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
+                        DevOp* op, std::string* err);
 // Launch for the first n_valid images.
 int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream);
 

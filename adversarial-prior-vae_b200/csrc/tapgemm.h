@@ -33,6 +33,24 @@ constexpr int kTileM = 128;
 
 enum ResMode { RES_NONE = 0, RES_SAME = 1, RES_EVEN = 2 };
 
+// Fused epilogue shared by the tensor-core kernels:
+//   v = acc + bias ; v *= lrelu'(mask) ; v += res ; tanh on cols < tanh_cols
+struct EpilogueArgs {
+    const float* bias;          // [Npad]
+    void* out_raw;              // bf16 [pix, ldo]   v
+    void* out_act;              // bf16 [pix, ldo]   leaky_relu(v)
+    int ldo;
+    int bf16_zero_from;         // columns >= this are stored as 0 in the bf16 outputs
+    float* out_f32;             // fp32 [pix, ld_f32], columns < f32_cols
+    int ld_f32, f32_cols;
+    const void* res;            // bf16 residual
+    int res_mode, ld_res;
+    const void* mask;           // bf16 forward tensor whose sign selects lrelu'
+    int ld_mask;
+    int tanh_cols;
+    float lrelu_alpha;
+};
+
 struct alignas(64) TapGemmParams {
     CUtensorMap tm_a[kMaxSrc];  // 5-D: (C', W', P, H', N)
     CUtensorMap tm_b;           // 2-D: (KC, total_steps * Npad)
@@ -50,20 +68,7 @@ struct alignas(64) TapGemmParams {
     int kc;                     // 16, 32 or 64 channels per step
     int num_stages;
     uint32_t a_bytes, b_bytes, stage_bytes;
-    // epilogue:  v = acc + bias ; v *= lrelu'(mask) ; v += res ; tanh on cols < tanh_cols
-    const float* bias;          // [Npad]
-    void* out_raw;              // bf16 [pix, ldo]   v
-    void* out_act;              // bf16 [pix, ldo]   leaky_relu(v)
-    int ldo;
-    int bf16_zero_from;         // columns >= this are stored as 0 in the bf16 outputs
-    float* out_f32;             // fp32 [pix, ld_f32], columns < f32_cols
-    int ld_f32, f32_cols;
-    const void* res;            // bf16 residual
-    int res_mode, ld_res;
-    const void* mask;           // bf16 forward tensor whose sign selects lrelu'
-    int ld_mask;
-    int tanh_cols;
-    float lrelu_alpha;
+    EpilogueArgs epi;
 };
 
 // Launches the kernel on `stream`.  Returns a cudaError_t value (0 = ok).

@@ -168,6 +168,9 @@ typedef struct apvae_plan_info {
     uint64_t src_strides[3][4];
     uint32_t src_box[3][5];
     double macs_per_image;
+    /* A-stationary ("patch") plan, when the op is eligible (stride 1, width 16..128) and not disabled */
+    int patch, patch_macc, patch_cluster, patch_rows_tile, patch_groups, patch_items, patch_a_stages, patch_b_stages;
+    int patch_prow[2];
 } apvae_plan_info;
 
 typedef struct apvae_epilogue {
@@ -178,12 +181,16 @@ typedef struct apvae_epilogue {
     int tanh_cols;
 } apvae_epilogue;
 
-/* Host-only planning (no GPU needed): step table, packed bf16 weights, TMA view geometry. */
+/* Host-only planning (no GPU needed): step table, packed bf16 weights, TMA view geometry.
+ * Environment (read at plan / model build time): APVAE_PATCH=0 disables the A-stationary kernel,
+ * APVAE_PATCH_MACC / APVAE_PATCH_CLUSTER force its accumulator count / cluster size. */
 int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, apvae_plan** out);
 int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info);
 int apvae_plan_copy_steps(const apvae_plan* p, int32_t* out /* [total_steps][5]: src,dx,dy,ph,c0 */);
 int apvae_plan_copy_weights(const apvae_plan* p, uint16_t* out /* bf16 [total_steps][npad][kc] */);
 int apvae_plan_copy_bias(const apvae_plan* p, float* out /* [npad] */);
+int apvae_plan_copy_patch_groups(const apvae_plan* p, int32_t* out /* [groups][6]: src,dx,py0,k,c0,prow */);
+int apvae_plan_copy_patch_weights(const apvae_plan* p, uint16_t* out /* bf16 [items][npad][kc] */);
 int apvae_plan_destroy(apvae_plan* p);
 /* Runs the plan on `device` (synchronous): src_dev[i] are bf16 NHWC tensors [capacity_n,H,W,Cp]. */
 int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,

@@ -157,3 +157,72 @@ def test_fused_shortcut_gpu():
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 2) + \
         O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
     _check(out.cpu().numpy(), want)
+
+
+PATCH_GPU_CASES = [
+    # transpose, k, N, H, W, cin, cout
+    (False, 3, 5, 16, 16, 192, 192),
+    (True, 3, 5, 16, 16, 192, 192),
+    (True, 5, 3, 32, 32, 96, 96),
+    (False, 3, 7, 32, 32, 16, 16),
+    (False, 3, 3, 32, 32, 64, 64),
+    (True, 3, 2, 64, 64, 32, 32),
+    (False, 3, 9, 16, 16, 128, 128),
+]
+
+
+@pytest.mark.parametrize('cluster', [1, 2, 4])
+@pytest.mark.parametrize('macc', [1, 2, 4])
+@pytest.mark.parametrize('transpose,k,N,H,W,cin,cout', PATCH_GPU_CASES)
+def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster, monkeypatch):
+    """A-stationary kernel (patchgemm.cu) for every accumulator count / cluster size it supports."""
+    torch = _torch()
+    import apvae
+    from apvae.plan import Plan, pad16
+    if macc * pad16(cout) > 256 or H % (macc * 128 // W) or (pad16(cout) // cluster) % 8:
+        pytest.skip('combination not supported by the planner')
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
+    monkeypatch.setenv('APVAE_PATCH_CLUSTER', str(cluster))
+    rs = np.random.RandomState(k + cin + cout + N)
+    x = bf16_round(rs.normal(size=(N, H, W, cin)))
+    shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
+    kern = bf16_round(rs.normal(size=shp) / np.sqrt(k * k * cin))
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    plan = Plan([dict(src=0, transpose=transpose, in_h=H, in_w=W, kernel=kern, bias=bias)], N)
+    assert plan.info.patch == 1 and plan.info.patch_macc == macc and plan.info.patch_cluster == cluster
+    src = torch.tensor(pad_channels(x, pad16(cin)), device='cuda').to(torch.bfloat16)
+    out = torch.zeros((N, H, W, cout), dtype=torch.float32, device='cuda')
+    plan.run([src], N, out_f32=out, f32_cols=cout)
+    ofn = O.deconv2d if transpose else O.conv2d
+    want = ofn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
+    _check(out.cpu().numpy(), want)
+
+
+def test_patch_kernel_matches_tap_kernel_bitwise_inputs(monkeypatch):
+    """Both kernels on the same op (fused 1x1 shortcut + residual-free epilogue, bf16 outputs)."""
+    torch = _torch()
+    from apvae.plan import Plan
+    rs = np.random.RandomState(21)
+    n, H, cin, cout = 6, 32, 32, 64
+    r = bf16_round(rs.normal(size=(n, H, H, cin)))
+    x = bf16_round(rs.normal(size=(n, H, H, cin)))
+    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.06)
+    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.2)
+    b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    outs = {}
+    for mode in ('0', '1'):
+        monkeypatch.setenv('APVAE_PATCH', mode)
+        plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
+        assert plan.info.patch == int(mode)
+        o32 = torch.zeros((n, H, H, cout), dtype=torch.float32, device='cuda')
+        oact = torch.zeros((n, H, H, cout), dtype=torch.bfloat16, device='cuda')
+        plan.run([t(r), t(x)], n - 1, out_f32=o32, f32_cols=cout, out_act=oact)
+        outs[mode] = (o32.cpu().numpy(), oact.float().cpu().numpy())
+    want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
+        O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 1)
+    _check(outs['1'][0][:n - 1], want[:n - 1])
+    _check(outs['1'][0], outs['0'][0], tol=1e-5)
+    assert np.all(outs['1'][0][n - 1] == 0) and np.all(outs['1'][1][n - 1] == 0)
+    _check(outs['1'][1], outs['0'][1], tol=1e-2)

@@ -88,3 +88,63 @@ def test_unsupported_shapes_raise():
         Plan([dict(src=0, stride=3, in_h=9, in_w=9, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1)
     with pytest.raises(ApvaeError):     # stride-2 conv on an odd grid
         Plan([dict(src=0, stride=2, in_h=7, in_w=7, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1)
+
+
+PATCH_CASES = [
+    # transpose, k, H, W, cin, cout
+    (False, 3, 16, 16, 16, 16),
+    (False, 5, 32, 32, 3, 24),
+    (True, 3, 16, 16, 32, 16),
+    (True, 5, 32, 32, 20, 16),
+    (False, 1, 16, 16, 64, 48),
+    (False, 3, 8, 16, 16, 200),      # one 128-pixel tile per image, wide N
+    (True, 3, 64, 64, 16, 32),       # celebA width
+]
+
+
+@pytest.mark.parametrize('transpose,k,H,W,cin,cout', PATCH_CASES)
+@pytest.mark.parametrize('macc', [0, 1])
+def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc, monkeypatch):
+    """The A-stationary plan (patchgemm.h): groups, packed weights and patch geometry reproduce
+    conv2d / deconv2d (stride 1)."""
+    from helpers import emulate_patch_plan
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
+    rs = np.random.RandomState(k * 100 + cin + cout)
+    n = 2
+    x = bf16_round(rs.normal(size=(n, H, W, cin)))
+    shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
+    kern = bf16_round(rs.normal(size=shp) * 0.2)
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    plan = Plan([dict(src=0, transpose=transpose, stride=1, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
+    assert plan.info.patch == 1
+    assert plan.info.patch_macc * plan.info.npad <= 256
+    got = emulate_patch_plan(plan, [pad_channels(x, pad16(cin))], n)[..., :cout]
+    fn = O.deconv2d if transpose else O.conv2d
+    want = fn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
+    np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-9)
+
+
+def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
+    from helpers import emulate_patch_plan
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    rs = np.random.RandomState(11)
+    n, H, cin, cout = 2, 16, 32, 64
+    r = bf16_round(rs.normal(size=(n, H, H, cin)))
+    x = bf16_round(rs.normal(size=(n, H, H, cin)))
+    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.1)
+    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.1)
+    b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
+    plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
+    assert plan.info.patch == 1 and plan.info.patch_prow[1] == plan.info.patch_rows_tile
+    got = emulate_patch_plan(plan, [r, x], n)[..., :cout]
+    want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
+        O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 1)
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+    # not eligible: stride 2, 8x8 grids, arch-M widths
+    for kw in (dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=28, in_w=28)):
+        p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1)
+        assert p.info.patch == 0
+    monkeypatch.setenv('APVAE_PATCH', '0')
+    p = Plan([dict(src=0, in_h=16, in_w=16, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1)
+    assert p.info.patch == 0
