@@ -115,6 +115,8 @@ _SYMBOLS = [
     ('apvae_plan_copy_patch_weights', C.c_int, [_P, C.POINTER(C.c_uint16)]),
     ('apvae_plan_destroy', C.c_int, [_P]),
     ('apvae_plan_run', C.c_int, [_P, C.c_int, C.POINTER(_P), C.c_int, C.POINTER(Epilogue)]),
+    ('apvae_plan_bench', C.c_int, [_P, C.c_int, C.POINTER(_P), C.c_int, C.POINTER(Epilogue), C.c_int,
+                                   C.POINTER(C.c_float)]),
 ]
 SYMBOL_NAMES = [s[0] for s in _SYMBOLS]
 

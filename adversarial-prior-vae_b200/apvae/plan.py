@@ -87,7 +87,7 @@ class Plan(object):
 
     def run(self, srcs, n_valid, out_raw=None, out_act=None, out_f32=None, f32_cols=0,
             res=None, res_mode=_lib.RES_NONE, mask=None, tanh_cols=0, bf16_zero_from=0,
-            device=0):
+            device=0, bench_reps=0):
         """srcs: bf16 CUDA tensors [capacity_n, H, W, Cp]; outputs are CUDA tensors
         whose last dim is the row pitch."""
         ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
@@ -105,6 +105,10 @@ class Plan(object):
         e.ld_mask = int(mask.shape[-1]) if mask is not None else 0
         e.tanh_cols = int(tanh_cols)
         arr = (C.c_void_p * len(srcs))(*[t.data_ptr() for t in srcs])
+        if bench_reps > 0:
+            ms = C.c_float()
+            check(lib.apvae_plan_bench(self._h, int(device), arr, int(n_valid), C.byref(e), int(bench_reps), C.byref(ms)))
+            return ms.value
         check(lib.apvae_plan_run(self._h, int(device), arr, int(n_valid), C.byref(e)))
 
 

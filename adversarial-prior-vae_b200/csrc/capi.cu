@@ -443,6 +443,11 @@ int apvae_plan_copy_patch_weights(const apvae_plan* p, uint16_t* out) {
 int apvae_plan_destroy(apvae_plan* p) { delete p; return APVAE_OK; }
 
 int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid, const apvae_epilogue* epi) {
+    return apvae_plan_bench(p, device, src_dev, n_valid, epi, 0, nullptr);
+}
+
+int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,
+                     const apvae_epilogue* epi, int reps, float* ms_per_launch) {
     if (!p || !src_dev || !epi) return set_global_err("null argument", APVAE_ERR_INVALID);
     DeviceInfo dev;
     std::string e;
@@ -459,6 +464,19 @@ int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, 
     if (!(use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, &op, &e) : devop_create(dev, p->plan, src_dev, ep, &op, &e)))
         return set_global_err(e, APVAE_ERR_CUDA);
     int err = devop_launch(dev, op, n_valid, nullptr);
+    if (err == 0 && reps > 0) {
+        cudaEvent_t e0, e1;
+        cudaEventCreate(&e0); cudaEventCreate(&e1);
+        err = devop_launch(dev, op, n_valid, nullptr);
+        cudaEventRecord(e0, nullptr);
+        for (int i = 0; i < reps && err == 0; ++i) err = devop_launch(dev, op, n_valid, nullptr);
+        cudaEventRecord(e1, nullptr);
+        if (err == 0) err = (int)cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms_per_launch) *ms_per_launch = ms / reps;
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+    }
     if (err == 0) err = (int)cudaDeviceSynchronize();
     if (err != 0) return set_global_err(std::string("plan_run: ") + cudaGetErrorString((cudaError_t)err), APVAE_ERR_CUDA);
     return APVAE_OK;

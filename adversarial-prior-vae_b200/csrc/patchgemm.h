@@ -32,11 +32,14 @@ struct PatchGroup {
 };
 
 constexpr int kPatchMaxSrc = 2;
+constexpr int kPatchMaxGroups = 48;
+// shared memory the kernel needs besides the two rings: barriers, realignment slack, epilogue staging
+constexpr uint32_t kPatchFixedSmem = 1024u + 1024u + kEpiSmemBytes;
 
 struct alignas(64) PatchGemmParams {
     CUtensorMap tm_a[kPatchMaxSrc];  // 5-D (C, W, 1, H, N), box (kc, W, 1, prow_src, 1)
     CUtensorMap tm_b;                // 2-D (kc, items*Npad), box (kc, NT / cluster)
-    const PatchGroup* groups;        // device pointer
+    PatchGroup groups[kPatchMaxGroups];   // in the kernel parameters: read through the constant bank (uniform loads)
     int num_groups, num_items;
     int W, H;                        // image size (stride 1: input grid == output grid)
     int rows_tile, macc;             // output rows per tile = macc * 128 / W
@@ -47,6 +50,7 @@ struct alignas(64) PatchGemmParams {
     int a_stages, b_stages;
     uint32_t a_slot_bytes, b_slot_bytes;
     int cluster;                     // 1, 2 or 4 CTAs sharing the weight stream
+    int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads (results are garbage)
     EpilogueArgs epi;
 };
 

@@ -1,5 +1,6 @@
 #include "planner.h"
 
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 
@@ -231,7 +232,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
     int kmax = 1;
     for (const TermSpec& t : terms) kmax = std::max(kmax, t.k);
-    const uint32_t budget = 227u * 1024u - 2048u - 1024u;
+    const uint32_t budget = 227u * 1024u - kPatchFixedSmem;
     P.b_slot_bytes = ((uint32_t)P.npad * P.kc * 2 + 1023u) & ~1023u;
     auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * W * P.kc * 2 + 1023u) & ~1023u; };
     int macc = 0;
@@ -255,6 +256,8 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.a_stages = 2;
     while (P.a_stages < 4 && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
     while (P.b_stages < 12 && P.a_stages * P.a_slot_bytes + (P.b_stages + 1) * P.b_slot_bytes <= budget) ++P.b_stages;
+    if (const char* e = getenv("APVAE_PATCH_ASTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.a_stages) P.a_stages = v; }
+    if (const char* e = getenv("APVAE_PATCH_BSTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.b_stages) P.b_stages = v; }
     // cluster: share the weight stream when it is heavy enough to matter
     int c = 1;
     if (P.npad >= 64) {
@@ -306,7 +309,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         }
         P.macs_per_image += (double)t.k * t.k * t.cin * t.cout * H * W;
     }
-    if ((int)P.groups.size() > 64) return fail("patch: too many groups");
+    if ((int)P.groups.size() > kPatchMaxGroups) return fail("patch: too many groups");
     return true;
 }
 

@@ -2,6 +2,7 @@
 
 #include <cuda.h>
 #include <cuda_runtime.h>
+#include <stdlib.h>
 #include <string.h>
 
 namespace apvae {
@@ -89,10 +90,9 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     if (epi.res_mode == RES_EVEN) { if (err) *err = "patch kernel has no even-pixel residual mode"; return false; }
     if (!check_epilogue(epi, plan.npad, op->name, err)) return false;
     const size_t ngroups = plan.groups.size();
-    APVAE_CUDA_OK(cudaMalloc(&op->d_groups, ngroups * sizeof(PatchGroup)), err);
+    if (ngroups > (size_t)kPatchMaxGroups) { if (err) *err = "patch plan has too many groups"; return false; }
     APVAE_CUDA_OK(cudaMalloc(&op->d_w, plan.wpack.size() * sizeof(uint16_t)), err);
     APVAE_CUDA_OK(cudaMalloc(&op->d_bias, plan.bias.size() * sizeof(float)), err);
-    APVAE_CUDA_OK(cudaMemcpy(op->d_groups, plan.groups.data(), ngroups * sizeof(PatchGroup), cudaMemcpyHostToDevice), err);
     APVAE_CUDA_OK(cudaMemcpy(op->d_w, plan.wpack.data(), plan.wpack.size() * sizeof(uint16_t), cudaMemcpyHostToDevice), err);
     APVAE_CUDA_OK(cudaMemcpy(op->d_bias, plan.bias.data(), plan.bias.size() * sizeof(float), cudaMemcpyHostToDevice), err);
     PatchGemmParams& p = op->pparams;
@@ -124,7 +124,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             return false;
         }
     }
-    p.groups = op->d_groups;
+    for (size_t i = 0; i < ngroups; ++i) p.groups[i] = plan.groups[i];
     p.num_groups = (int)ngroups; p.num_items = plan.num_items;
     p.W = plan.w; p.H = plan.h; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
     p.n_valid = 0;
@@ -132,6 +132,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.a_stages = plan.a_stages; p.b_stages = plan.b_stages;
     p.a_slot_bytes = plan.a_slot_bytes; p.b_slot_bytes = plan.b_slot_bytes;
     p.cluster = plan.cluster;
+    { const char* dbg = getenv("APVAE_PATCH_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
     fill_epilogue(p.epi, epi, op->d_bias);
     op->is_patch = true;
     op->macs_per_image = plan.macs_per_image;
@@ -182,6 +183,8 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
         }
     }
     p.steps = op->d_steps;
+    p.inline_steps = nsteps <= (size_t)kMaxInlineSteps ? 1 : 0;
+    if (p.inline_steps) for (size_t i = 0; i < nsteps; ++i) p.steps_inline[i] = plan.steps[i];
     for (int i = 0; i <= kMaxPhases; ++i) p.phase_begin[i] = plan.phase_begin[i];
     p.num_phases = plan.num_phases;
     p.bw = plan.bw; p.bh = plan.bh; p.bn = plan.bn; p.rows = plan.rows;

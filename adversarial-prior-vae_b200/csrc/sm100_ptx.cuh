@@ -107,6 +107,21 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
 }
 
+// One lane of the (converged) warp; the role loops run warp-uniformly and only the tcgen05 / TMA
+// instruction itself is issued under this predicate, so that ptxas keeps descriptors, coordinates
+// and barrier addresses in uniform registers (a lane-0 branch around the whole loop makes every
+// operand "divergent" and each UTCHMMA / UTMALDG gets wrapped in an ELECT + R2UR waterfall loop).
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred = 0;
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\t"
+        "elect.sync _|P1, 0xffffffff;\n\t"
+        "selp.u32 %0, 1, 0, P1;\n\t}"
+        : "=r"(pred));
+    return pred != 0;
+}
+__device__ __forceinline__ int uniform_warp_idx() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+
 __device__ __forceinline__ uint32_t cluster_ctarank() {
     uint32_t r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
@@ -143,74 +158,175 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xFFFF0000u); }
 
-// Epilogue for 16 accumulator columns [col, col+16) of one output pixel:
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+          "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+          "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+    uint4 r;
+    asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(addr) : "memory");
+    return r;
+}
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+    float4 r;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(addr) : "memory");
+    return r;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Warp-level epilogue of one 32-row x NT-column accumulator block (this warp's TMEM lane quarter).
 //   v = acc + bias ; v *= lrelu'(mask) ; v += res ; tanh on cols < tanh_cols ; fp32 / bf16 stores.
-__device__ __forceinline__ void epilogue16(const EpilogueArgs& e, const uint32_t (&v)[16], int col, size_t opix,
-                                           size_t rpix, bool has_res) {
-    float f[16];
-    const float4* b4 = reinterpret_cast<const float4*>(e.bias + col);
+// bf16 outputs (and the bf16 residual) go through a per-warp shared-memory staging block of
+// 32 rows x 64 columns so that global accesses are 128-byte row segments instead of one 32-byte
+// piece per lane: lane r owns accumulator row r, but 8 consecutive lanes move one row segment.
+// Staging row pitch = 64*2 + 16 bytes: the 16-byte lane accesses of a quarter-warp hit distinct banks.
+// (kEpiBlockCols, kEpiPitch, kEpiStageBytes, kEpiWarpBytes, kEpiSmemBytes: tapgemm.h)
+
+struct EpiRow {
+    size_t opix;     // output pixel of this lane's row
+    size_t rpix;     // residual pixel
+    bool valid;      // row is written
+    bool has_res;    // residual is added to this row
+};
+
+// `wsm`: this warp's kEpiWarpBytes of shared memory.  `bias_s`: smem address of bias[col_base ...] (NT floats).
+__device__ __forceinline__ void epilogue_block(const EpilogueArgs& e, uint32_t taddr0, int NT, int col_base,
+                                               const EpiRow& row, uint32_t wsm, uint32_t bias_s, int lane) {
+    const uint32_t stA = wsm, stB = wsm + kEpiStageBytes;
+    const bool any_res = __any_sync(0xffffffffu, row.has_res);
+    for (int cb = 0; cb < NT; cb += (int)kEpiBlockCols) {
+        const int bw = min((int)kEpiBlockCols, NT - cb);               // columns in this block (multiple of 16)
+        const int segs = bw >> 3;                                      // 16-byte segments per row
+        const int total = 32 * segs;
+        if (any_res) {                                                 // coalesced residual block -> staging A
+            const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(e.res);
+            for (int idx = lane; idx < total; idx += 32) {
+                const int r = idx / segs, sg = idx - r * segs;
+                const size_t rp = __shfl_sync(0xffffffffu, (unsigned long long)row.rpix, r);
+                const bool hr = __shfl_sync(0xffffffffu, (int)row.has_res, r);
+                uint4 val = make_uint4(0, 0, 0, 0);
+                if (hr) val = __ldg(reinterpret_cast<const uint4*>(res + rp * e.ld_res + col_base + cb) + sg);
+                st_shared_v4(stA + r * kEpiPitch + sg * 16, val.x, val.y, val.z, val.w);
+            }
+            __syncwarp();
+        }
+        for (int c = 0; c < bw; c += 32) {
+            const int cw = min(32, bw - c);                            // 16 or 32 columns
+            uint32_t v[32];
+            if (cw == 32) {
+                tmem_ld32(taddr0 + cb + c, v);
+            } else {
+                uint32_t lo[16];
+                tmem_ld16(taddr0 + cb + c, lo);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const float4 b = __ldg(b4 + i);
-        f[4 * i + 0] = __uint_as_float(v[4 * i + 0]) + b.x;
-        f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + b.y;
-        f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + b.z;
-        f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + b.w;
-    }
-    if (e.mask != nullptr) {
-        const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(e.mask) + opix * e.ld_mask + col);
+                for (int i = 0; i < 16; ++i) v[i] = lo[i];
+            }
+            tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const uint4 m = __ldg(m4 + i);
-            const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+            for (int h = 0; h < 2; ++h) {
+                if (h * 16 >= cw) break;
+                const int cc = cb + c + h * 16;                        // column within the N tile
+                const int col = col_base + cc;                         // global output column
+                float f[16];
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                f[8 * i + 2 * j + 0] *= (bf16_lo(w[j]) > 0.f) ? 1.f : e.lrelu_alpha;
-                f[8 * i + 2 * j + 1] *= (bf16_hi(w[j]) > 0.f) ? 1.f : e.lrelu_alpha;
+                for (int i = 0; i < 4; ++i) {
+                    const float4 b = ld_shared_f4(bias_s + (cc + 4 * i) * 4);
+                    f[4 * i + 0] = __uint_as_float(v[h * 16 + 4 * i + 0]) + b.x;
+                    f[4 * i + 1] = __uint_as_float(v[h * 16 + 4 * i + 1]) + b.y;
+                    f[4 * i + 2] = __uint_as_float(v[h * 16 + 4 * i + 2]) + b.z;
+                    f[4 * i + 3] = __uint_as_float(v[h * 16 + 4 * i + 3]) + b.w;
+                }
+                if (e.mask != nullptr && row.valid) {
+                    const uint4* m4 = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(e.mask) +
+                                                                     row.opix * e.ld_mask + col);
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const uint4 m = __ldg(m4 + i);
+                        const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            f[8 * i + 2 * j + 0] *= (bf16_lo(w[j]) > 0.f) ? 1.f : e.lrelu_alpha;
+                            f[8 * i + 2 * j + 1] *= (bf16_hi(w[j]) > 0.f) ? 1.f : e.lrelu_alpha;
+                        }
+                    }
+                }
+                if (any_res) {
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const uint4 m = ld_shared_v4(stA + lane * kEpiPitch + (c + h * 16) * 2 + i * 16);
+                        const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            f[8 * i + 2 * j + 0] += bf16_lo(w[j]);
+                            f[8 * i + 2 * j + 1] += bf16_hi(w[j]);
+                        }
+                    }
+                }
+                if (col < e.tanh_cols) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (col + i < e.tanh_cols) f[i] = tanhf(f[i]);
+                }
+                if (e.out_f32 != nullptr && col < e.f32_cols && row.valid) {
+                    float* o = e.out_f32 + row.opix * e.ld_f32 + col;
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (col + i < e.f32_cols) o[i] = f[i];
+                }
+                if (col + 16 > e.bf16_zero_from) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (col + i >= e.bf16_zero_from) f[i] = 0.f;
+                }
+                const uint32_t so = lane * kEpiPitch + (c + h * 16) * 2;
+                if (e.out_raw != nullptr) {
+                    st_shared_v4(stA + so, pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+                    st_shared_v4(stA + so + 16, pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+                }
+                if (e.out_act != nullptr) {
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : e.lrelu_alpha * f[i];
+                    st_shared_v4(stB + so, pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+                    st_shared_v4(stB + so + 16, pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+                }
             }
         }
-    }
-    if (has_res) {
-        const uint4* r4 = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(e.res) + rpix * e.ld_res + col);
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            const uint4 m = __ldg(r4 + i);
-            const uint32_t w[4] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                f[8 * i + 2 * j + 0] += bf16_lo(w[j]);
-                f[8 * i + 2 * j + 1] += bf16_hi(w[j]);
+        if (e.out_raw != nullptr || e.out_act != nullptr) {
+            __syncwarp();
+            __nv_bfloat16* oraw = static_cast<__nv_bfloat16*>(e.out_raw);
+            __nv_bfloat16* oact = static_cast<__nv_bfloat16*>(e.out_act);
+            for (int idx = lane; idx < total; idx += 32) {
+                const int r = idx / segs, sg = idx - r * segs;
+                const size_t op = __shfl_sync(0xffffffffu, (unsigned long long)row.opix, r);
+                const bool ok = __shfl_sync(0xffffffffu, (int)row.valid, r);
+                if (ok) {
+                    const size_t off = op * e.ldo + col_base + cb;
+                    if (oraw != nullptr) *(reinterpret_cast<uint4*>(oraw + off) + sg) = ld_shared_v4(stA + r * kEpiPitch + sg * 16);
+                    if (oact != nullptr) *(reinterpret_cast<uint4*>(oact + off) + sg) = ld_shared_v4(stB + r * kEpiPitch + sg * 16);
+                }
             }
         }
+        __syncwarp();                                                  // staging blocks are reused by the next column block
     }
-    if (col < e.tanh_cols) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            if (col + i < e.tanh_cols) f[i] = tanhf(f[i]);
+}
+
+// Copies bias[col_base, col_base + NT) into this warp's bias area (call when col_base changes).
+__device__ __forceinline__ void epilogue_load_bias(const EpilogueArgs& e, uint32_t bias_s, int NT, int col_base, int lane) {
+    for (int i = lane; i < NT; i += 32) {
+        const float b = __ldg(e.bias + col_base + i);
+        asm volatile("st.shared.f32 [%0], %1;" ::"r"(bias_s + i * 4), "f"(b) : "memory");
     }
-    if (e.out_f32 != nullptr && col < e.f32_cols) {
-        float* o = e.out_f32 + opix * e.ld_f32 + col;
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            if (col + i < e.f32_cols) o[i] = f[i];
-    }
-    if (col + 16 > e.bf16_zero_from) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i)
-            if (col + i >= e.bf16_zero_from) f[i] = 0.f;
-    }
-    if (e.out_raw != nullptr) {
-        uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(e.out_raw) + opix * e.ldo + col);
-        o[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-        o[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
-    }
-    if (e.out_act != nullptr) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : e.lrelu_alpha * f[i];
-        uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(e.out_act) + opix * e.ldo + col);
-        o[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-        o[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
-    }
+    __syncwarp();
 }
 
 }  // namespace ptx

@@ -49,7 +49,8 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
     // Dynamic smem is only guaranteed 16 B aligned by the ABI: realign to 1024 B
     // (swizzle atoms of the UMMA descriptors assume it).
     const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t bar_base = smem_base + p.num_stages * p.stage_bytes;
+    const uint32_t epi_base = smem_base + p.num_stages * p.stage_bytes;
+    const uint32_t bar_base = epi_base + kEpiSmemBytes;
     // barrier layout: full[S], empty[S], tmem_full[2], tmem_empty[2], tmem_ptr
     auto full_bar = [&](int s) { return bar_base + 8u * s; };
     auto empty_bar = [&](int s) { return bar_base + 8u * (p.num_stages + s); };
@@ -57,14 +58,14 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
     auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * p.num_stages + kAccStages + a); };
     const uint32_t tmem_ptr_smem = bar_base + 8u * (2 * p.num_stages + 2 * kAccStages);
 
-    const int warp = threadIdx.x >> 5;
+    const int warp = uniform_warp_idx();
     const int lane = threadIdx.x & 31;
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0 && elect_one_sync()) {
         prefetch_tmap(&p.tm_a[0]);
         prefetch_tmap(&p.tm_b);
     }
-    if (warp == 1 && lane == 0) {
+    if (warp == 1 && elect_one_sync()) {
         for (int s = 0; s < p.num_stages; ++s) {
             mbar_init(full_bar(s), 1);
             mbar_init(empty_bar(s), 1);
@@ -83,51 +84,55 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
+    tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
 
     const int tiles_n = (p.n_valid + p.bn - 1) / p.bn;
     const int total_tiles = tiles_n * p.tiles_y * p.tiles_x * p.num_phases * p.n_tiles;
 
+    // The role loops run with the whole warp converged; one elected lane issues the TMA / tcgen05
+    // instructions (see elect_one_sync in sm100_ptx.cuh).
     if (warp == 0) {
         // ===================== TMA producer =====================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const TileCoord t = decode_tile(p, tile);
-                const int s_begin = p.phase_begin[t.ph], s_end = p.phase_begin[t.ph + 1];
-                for (int s = s_begin; s < s_end; ++s) {
-                    const TapStep st = p.steps[s];
-                    mbar_wait(empty_bar(stage), phase ^ 1);
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile);
+            const int s_begin = p.phase_begin[t.ph], s_end = p.phase_begin[t.ph + 1];
+            for (int s = s_begin; s < s_end; ++s) {
+                TapStep st;
+                if (p.inline_steps) st = p.steps_inline[s];
+                else st = p.steps[s];
+                mbar_wait(empty_bar(stage), phase ^ 1);
+                if (elect_one_sync()) {
                     const uint32_t a_dst = smem_base + stage * p.stage_bytes;
                     const uint32_t b_dst = a_dst + kTileM * KC * 2;
                     mbar_expect_tx(full_bar(stage), p.a_bytes + p.b_bytes);
-                    tma_load_5d(a_dst, &p.tm_a[st.src], full_bar(stage), st.c0, t.x0 + st.dx,
-                                st.ph, t.y0 + st.dy, t.n0);
+                    tma_load_5d(a_dst, &p.tm_a[st.src], full_bar(stage), st.c0, t.x0 + st.dx, st.ph, t.y0 + st.dy, t.n0);
                     tma_load_2d(b_dst, &p.tm_b, full_bar(stage), 0, s * p.Npad + t.nt * p.NT);
-                    if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
                 }
+                __syncwarp();
+                if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
             }
         }
-        __syncwarp();
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_bf16(kTileM, p.NT);
-            int stage = 0, acc = 0;
-            uint32_t phase = 0, acc_phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const TileCoord t = decode_tile(p, tile);
-                const int s_begin = p.phase_begin[t.ph], s_end = p.phase_begin[t.ph + 1];
-                mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        const uint32_t idesc = make_idesc_bf16(kTileM, p.NT);
+        int stage = 0, acc = 0;
+        uint32_t phase = 0, acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile);
+            const int s_begin = p.phase_begin[t.ph], s_end = p.phase_begin[t.ph + 1];
+            mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+            tc_fence_after();
+            const uint32_t tmem_d = tmem_base + acc * kAccColStride;
+            for (int s = s_begin; s < s_end; ++s) {
+                mbar_wait(full_bar(stage), phase);
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * kAccColStride;
-                for (int s = s_begin; s < s_end; ++s) {
-                    mbar_wait(full_bar(stage), phase);
-                    tc_fence_after();
-                    const uint32_t a_src = smem_base + stage * p.stage_bytes;
-                    const uint32_t b_src = a_src + kTileM * KC * 2;
-                    const uint64_t da = make_kmajor_desc<KC>(a_src);
-                    const uint64_t db = make_kmajor_desc<KC>(b_src);
+                const uint32_t a_src = smem_base + stage * p.stage_bytes;
+                const uint32_t b_src = a_src + kTileM * KC * 2;
+                const uint64_t da = make_kmajor_desc<KC>(a_src);
+                const uint64_t db = make_kmajor_desc<KC>(b_src);
+                if (elect_one_sync()) {
 #pragma unroll
                     for (int k = 0; k < KC / 16; ++k) {
                         // +32 B per K=16 slice inside the swizzle atom (start address is >>4)
@@ -135,12 +140,12 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
                     }
                     umma_commit(empty_bar(stage));
                     if (s == s_end - 1) umma_commit(tfull_bar(acc));
-                    if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
                 }
-                if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+                __syncwarp();
+                if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
             }
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
-        __syncwarp();
     } else if (warp >= 4) {
         // ===================== epilogue =====================
         const int q = warp & 3;                 // TMEM lane quarter this warp may read
@@ -148,10 +153,13 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
         const int px_x = r % p.bw;
         const int px_y = (r / p.bw) % p.bh;
         const int px_n = r / (p.bw * p.bh);
-        int acc = 0;
+        const uint32_t wsm = epi_base + q * kEpiWarpBytes;
+        const uint32_t bias_s = wsm + 2 * kEpiStageBytes;
+        int acc = 0, bias_col = -1;
         uint32_t acc_phase = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const TileCoord t = decode_tile(p, tile);
+            if (bias_col != t.nt * p.NT) { bias_col = t.nt * p.NT; epilogue_load_bias(p.epi, bias_s, p.NT, bias_col, lane); }
             const int n = t.n0 + px_n, gy = t.y0 + px_y, gx = t.x0 + px_x;
             const bool valid = (r < p.rows) && (n < p.n_valid) && (gy < p.Hg) && (gx < p.Wg);
             const int Y = gy * p.os + (p.num_phases == 4 ? (t.ph >> 1) : 0);
@@ -166,12 +174,9 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             const uint32_t taddr0 = tmem_base + acc * kAccColStride + ((uint32_t)(q * 32) << 16);
-            for (int c = 0; c < p.NT; c += 16) {
-                uint32_t v[16];
-                tmem_ld16(taddr0 + c, v);
-                tmem_ld_wait();
-                if (valid) epilogue16(p.epi, v, t.nt * p.NT + c, opix, rpix, has_res);
-            }
+            EpiRow row;
+            row.opix = opix; row.rpix = rpix; row.valid = valid; row.has_res = has_res;
+            epilogue_block(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));
@@ -189,7 +194,7 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
 uint32_t tapgemm_smem_bytes(int kc, int NT, int stages) {
     uint32_t stage = kTileM * kc * 2 + NT * kc * 2;
     stage = (stage + 1023u) & ~1023u;
-    return stages * stage + kBarrierBytes + 1024u /* realignment slack */;
+    return stages * stage + kEpiSmemBytes + kBarrierBytes + 1024u /* realignment slack */;
 }
 
 int tapgemm_pick_stages(int kc, int NT, int max_useful) {

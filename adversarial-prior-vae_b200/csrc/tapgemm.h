@@ -30,6 +30,7 @@ struct TapStep {
 constexpr int kMaxPhases = 4;
 constexpr int kMaxSrc = 3;
 constexpr int kTileM = 128;
+constexpr int kMaxInlineSteps = 160;   // step tables up to this size travel in the kernel parameters (uniform constant-bank reads)
 
 enum ResMode { RES_NONE = 0, RES_SAME = 1, RES_EVEN = 2 };
 
@@ -54,7 +55,9 @@ struct EpilogueArgs {
 struct alignas(64) TapGemmParams {
     CUtensorMap tm_a[kMaxSrc];  // 5-D: (C', W', P, H', N)
     CUtensorMap tm_b;           // 2-D: (KC, total_steps * Npad)
-    const TapStep* steps;       // device pointer, all phases back to back
+    const TapStep* steps;       // device pointer, all phases back to back (used when the table does not fit inline)
+    int inline_steps;           // 1: read steps_inline
+    TapStep steps_inline[kMaxInlineSteps];
     int phase_begin[kMaxPhases + 1];
     int num_phases;             // 1, or 4 (py = ph >> 1, px = ph & 1)
     // pixel tile = TMA box (bw, bh, bn); rows = bw*bh*bn <= 128
@@ -70,6 +73,13 @@ struct alignas(64) TapGemmParams {
     uint32_t a_bytes, b_bytes, stage_bytes;
     EpilogueArgs epi;
 };
+
+// Per-warp shared-memory staging of the epilogue (sm100_ptx.cuh: epilogue_block).
+constexpr uint32_t kEpiBlockCols = 64;
+constexpr uint32_t kEpiPitch = kEpiBlockCols * 2 + 16;                 // bytes per staged row
+constexpr uint32_t kEpiStageBytes = 32 * kEpiPitch;                    // one 32-row staging block
+constexpr uint32_t kEpiWarpBytes = 2 * kEpiStageBytes + 1024;          // block A (residual, then raw), block B (act), bias[256]
+constexpr uint32_t kEpiSmemBytes = 4 * kEpiWarpBytes;                  // four epilogue warps
 
 // Launches the kernel on `stream`.  Returns a cudaError_t value (0 = ok).
 int launch_tapgemm(const TapGemmParams& p, int num_sms, void* stream);

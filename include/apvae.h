@@ -196,6 +196,11 @@ int apvae_plan_destroy(apvae_plan* p);
 int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,
                    const apvae_epilogue* epi);
 
+/* Like apvae_plan_run, but launches the op 2 + reps times and returns the CUDA-event average of the
+ * last `reps` launches (kernel tuning / profiling of one layer in isolation). */
+int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,
+                     const apvae_epilogue* epi, int reps, float* ms_per_launch);
+
 #ifdef __cplusplus
 }
 #endif
