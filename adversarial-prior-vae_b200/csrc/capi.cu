@@ -460,7 +460,7 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
     ep.mask = epi->mask_dev; ep.ld_mask = epi->ld_mask; ep.tanh_cols = epi->tanh_cols;
     DevOp op;
     op.name = "plan_run";
-    const bool use_patch = p->has_patch && ep.res_mode != RES_EVEN;
+    const bool use_patch = p->has_patch;
     if (!(use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, &op, &e) : devop_create(dev, p->plan, src_dev, ep, &op, &e)))
         return set_global_err(e, APVAE_ERR_CUDA);
     int err = devop_launch(dev, op, n_valid, nullptr);

@@ -57,8 +57,10 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     PatchPlan pplan;
     const char* em = getenv("APVAE_PATCH_MACC");
     const char* ec = getenv("APVAE_PATCH_CLUSTER");
-    if (!(env && env[0] == '0') && epi.res_mode != RES_EVEN &&
-        plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr)) {
+    const char* emax = getenv("APVAE_PATCH_MAXN");            // widest output the A-stationary kernel takes (tuning)
+    const int patch_max_n = emax ? atoi(emax) : 256;
+    if (!(env && env[0] == '0') &&
+        plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr) && pplan.npad <= patch_max_n) {
         if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");
         if (!devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
         if (macs) *macs += pplan.macs_per_image;

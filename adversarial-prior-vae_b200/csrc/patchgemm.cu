@@ -5,7 +5,9 @@
 //   warp 1      MMA issuer (tcgen05.mma; macc accumulators of 128 rows each)
 //   warp 2      TMEM allocator
 //   warp 3      weight-tile producer (TMA 2-D; 1/cluster of each tile, multicast to the cluster)
-//   warps 4..7  epilogue (tcgen05.ld -> bias/mask/residual/act -> global)
+//   warps 4..7  epilogue (tcgen05.ld -> bias/mask/residual/act -> global); bf16-only epilogues take the
+//               TMA path: residual boxes prefetched two blocks ahead by bulk tensor loads, outputs staged
+//               swizzled in shared memory and written by bulk tensor stores
 // Rings: patches (full/empty), weight tiles (full/empty; empty collects one arrival per cluster CTA
 // through tcgen05.commit multicast), and a 2-deep TMEM accumulator ring.
 #include <cuda_runtime.h>
@@ -37,7 +39,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     const uint32_t a_base = smem_base;
     const uint32_t b_base = a_base + p.a_stages * p.a_slot_bytes;
     const uint32_t epi_base = b_base + p.b_stages * p.b_slot_bytes;
-    const uint32_t bar_base = epi_base + kEpiSmemBytes;
+    const uint32_t bar_base = epi_base + (kPatchFixedSmem - 2048u);
     auto fullA = [&](int s) { return bar_base + 8u * s; };
     auto emptyA = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
     auto fullB = [&](int s) { return bar_base + 8u * (2 * kMaxStages + s); };
@@ -45,6 +47,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     auto tfull = [&](int a) { return bar_base + 8u * (4 * kMaxStages + a); };
     auto tempty = [&](int a) { return bar_base + 8u * (4 * kMaxStages + kAccStages + a); };
     const uint32_t tmem_ptr_smem = bar_base + 8u * (4 * kMaxStages + 2 * kAccStages);
+    auto resbar = [&](int q, int b) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 2 * q + b); };
 
     const int warp = uniform_warp_idx();
     const int lane = threadIdx.x & 31;
@@ -61,6 +64,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         for (int s = 0; s < p.a_stages; ++s) { mbar_init(fullA(s), 1); mbar_init(emptyA(s), 1); }
         for (int s = 0; s < p.b_stages; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), csize); }
         for (int a = 0; a < kAccStages; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), 4); }
+        for (int q = 0; q < 4; ++q) { mbar_init(resbar(q, 0), 1); mbar_init(resbar(q, 1), 1); }
         fence_barrier_init();
     }
     if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
@@ -109,18 +113,25 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             const int slice_rows = p.NT / csize;
             const uint32_t slice_bytes = (uint32_t)slice_rows * row_bytes;
             for (int g = cluster_id; g < rounds_total; g += num_clusters) {
-                for (int it = 0; it < p.num_items; ++it) {
-                    mbar_wait(emptyB(sb), pb ^ 1);               // every CTA of the cluster released this slot
-                    if (elect_one_sync()) {
-                        mbar_expect_tx(fullB(sb), (uint32_t)p.NT * row_bytes);
-                        const uint32_t dst = b_base + sb * p.b_slot_bytes + rank * slice_bytes;
-                        if (csize > 1)
-                            tma_load_2d_mc(dst, &p.tm_b, fullB(sb), 0, it * p.Npad + (int)rank * slice_rows, cmask);
-                        else
-                            tma_load_2d(dst, &p.tm_b, fullB(sb), 0, it * p.Npad);
+                int tap0 = 0;                                    // global tap index = row block of the packed weights
+                for (int gi = 0; gi < p.num_groups; ++gi) {
+                    const int k = p.groups[gi].k;
+                    for (int j0 = 0; j0 < k; j0 += p.tpi) {
+                        const int nt = min(p.tpi, k - j0);       // taps in this item
+                        mbar_wait(emptyB(sb), pb ^ 1);           // every CTA of the cluster released this slot
+                        if (elect_one_sync()) {
+                            mbar_expect_tx(fullB(sb), (uint32_t)nt * p.tap_bytes);
+                            for (int t = 0; t < nt; ++t) {
+                                const uint32_t dst = b_base + sb * p.b_slot_bytes + t * p.tap_bytes + rank * slice_bytes;
+                                const int row0 = (tap0 + j0 + t) * p.Npad + (int)rank * slice_rows;
+                                if (csize > 1) tma_load_2d_mc(dst, &p.tm_b, fullB(sb), 0, row0, cmask);
+                                else tma_load_2d(dst, &p.tm_b, fullB(sb), 0, row0);
+                            }
+                        }
+                        __syncwarp();
+                        if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
                     }
-                    __syncwarp();
-                    if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                    tap0 += k;
                 }
             }
         }
@@ -138,17 +149,22 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 const int k = p.groups[gi].k;
                 if (!skipA) mbar_wait(fullA(sa), pa);
                 const uint32_t a_src = a_base + sa * p.a_slot_bytes;
-                for (int j = 0; j < k; ++j) {
+                for (int j0 = 0; j0 < k; j0 += p.tpi) {
+                    const int nt = min(p.tpi, k - j0);
                     if (!skipB) mbar_wait(fullB(sb), pb);
                     tc_fence_after();
-                    const uint64_t db = make_kmajor_desc<KC>(b_base + sb * p.b_slot_bytes);
+                    const uint32_t b_src = b_base + sb * p.b_slot_bytes;
                     if (elect_one_sync()) {
-                        for (int m = 0; m < p.macc; ++m) {
-                            // tap j reads the patch advanced by j image rows; accumulator m by 128 pixels
-                            const uint64_t da = make_kmajor_desc<KC>(a_src + (uint32_t)(j * p.W + m * kTileM) * row_bytes);
+                        for (int t = 0; t < nt; ++t) {
+                            const uint64_t db = make_kmajor_desc<KC>(b_src + t * p.tap_bytes);
+                            for (int m = 0; m < p.macc; ++m) {
+                                // tap j reads the patch advanced by j image rows; accumulator m by 128 pixels
+                                const uint64_t da = make_kmajor_desc<KC>(a_src + (uint32_t)((j0 + t) * p.W + m * kTileM) * row_bytes);
 #pragma unroll
-                            for (int kk = 0; kk < KC / 16; ++kk)
-                                umma_bf16(tmem_d + m * p.NT, da + 2 * kk, db + 2 * kk, idesc, (kk == 0) ? accumulate : 1u);
+                                for (int kk = 0; kk < KC / 16; ++kk)
+                                    umma_bf16(tmem_d + m * p.NT, da + 2 * kk, db + 2 * kk, idesc, (kk == 0) ? accumulate : 1u);
+                            }
+                            accumulate = 1;
                         }
                         if (skipB) {}
                         else if (csize > 1) umma_commit_mc(emptyB(sb), cmask);
@@ -166,6 +182,159 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             __syncwarp();
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
+    } else if (warp >= 4 && p.fast_epi) {
+        // ===================== epilogue, TMA in / TMA out =====================
+        // Work unit = "block": 32 rows (this warp's TMEM lane quarter) x 64 columns of one accumulator.
+        const int q = warp & 3;
+        const uint32_t wbase = epi_base + q * kFastEpiWarpBytes;
+        const uint32_t rawbuf = wbase + 2 * kFastEpiBoxBytes, actbuf = wbase + 3 * kFastEpiBoxBytes;
+        const uint32_t bias_s = wbase + 4 * kFastEpiBoxBytes;
+        epilogue_load_bias(p.epi, bias_s, p.NT, 0, lane);
+        const bool leader = elect_one_sync();              // the one thread that owns this warp's bulk-store groups
+        const bool want_raw = p.epi.out_raw != nullptr, want_act = p.epi.out_act != nullptr;
+        const int res_mode = p.epi.res_mode;
+        const uint32_t res_bytes = (uint32_t)p.res_rows * 128u;
+        const float alpha = p.epi.lrelu_alpha;
+        const uint32_t sw = (uint32_t)(lane & 7);
+        struct Seq { int g, m, cb; };
+        auto seq_next = [&](Seq s) {
+            s.cb += 64;
+            if (s.cb >= p.NT) { s.cb = 0; if (++s.m == p.macc) { s.m = 0; s.g += num_clusters; } }
+            return s;
+        };
+        // first output pixel of this warp's rows in block s, and whether the tile exists
+        auto seq_pix0 = [&](const Seq& s, bool& ok) {
+            const int tile = s.g * csize + (int)rank;
+            ok = (s.g < rounds_total) && (tile < total_tiles);
+            const int n = tile / p.tiles_y, y0 = (tile % p.tiles_y) * p.rows_tile;
+            return ((n * p.H + y0) * p.W) + s.m * kTileM + q * 32;
+        };
+        // bulk load of the residual box of block s into buffer b; returns whether one was issued (warp-uniform)
+        auto issue_res = [&](const Seq& s, int b) {
+            if (res_mode == RES_NONE) return false;
+            bool ok;
+            const int pix0 = seq_pix0(s, ok);
+            if (!ok) return false;
+            int rp0 = pix0;
+            if (res_mode == RES_EVEN) {                    // half-resolution residual on even pixels only
+                const int x0 = pix0 % p.W, yy = pix0 / p.W;     // yy = n*H + y  (H even)
+                if (yy & 1) return false;
+                rp0 = (yy >> 1) * (p.W >> 1) + (x0 >> 1);
+            }
+            if (leader) {
+                mbar_expect_tx(resbar(q, b), res_bytes);
+                tma_load_2d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, rp0);
+            }
+            return true;
+        };
+        // this lane's residual row inside the box, and whether this lane's pixel takes a residual
+        int rrow = lane;
+        bool lane_res = true;
+        if (res_mode == RES_EVEN) {
+            const int pix = q * 32 + lane;                 // (m * 128 does not change x parity or the row split)
+            const int x = pix % p.W;
+            lane_res = !(x & 1) && !((pix / p.W) & 1);
+            rrow = (p.W >= 32) ? (lane >> 1) : ((lane & 15) >> 1);
+        }
+        const uint32_t rsw = (uint32_t)(rrow & 7);
+        Seq cur = {cluster_id, 0, 0};
+        bool iss0 = issue_res(cur, 0);
+        Seq pre = seq_next(cur);
+        bool iss1 = issue_res(pre, 1);
+        pre = seq_next(pre);
+        uint32_t ph0 = 0, ph1 = 0;
+        int kb = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int g = cluster_id; g < rounds_total; g += num_clusters) {
+            mbar_wait(tfull(acc), acc_phase);
+            tc_fence_after();
+            for (int m = 0; m < p.macc; ++m) {
+                for (int cb = 0; cb < p.NT; cb += 64) {
+                    const int bw = min(64, p.NT - cb);
+                    const uint32_t taddr = tmem_base + acc * kAccColStride + m * p.NT + cb + ((uint32_t)(q * 32) << 16);
+                    bool ok;
+                    const int pix0 = seq_pix0(cur, ok);
+                    const bool has_res = kb ? iss1 : iss0;
+                    const uint32_t rbuf = wbase + kb * kFastEpiBoxBytes;
+                    uint32_t rr[32], aa[32];               // packed bf16 pairs: raw and activated, 64 columns
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int cw = min(32, bw - 32 * h);
+                        if (cw <= 0) break;
+                        uint32_t v[32];
+                        if (cw == 32) {
+                            tmem_ld32(taddr + 32 * h, v);
+                        } else {
+                            uint32_t lo[16];
+                            tmem_ld16(taddr + 32 * h, lo);
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) v[i] = lo[i];
+                        }
+                        if (h == 0 && has_res) {
+                            if (kb) { mbar_wait(resbar(q, 1), ph1); ph1 ^= 1; }
+                            else { mbar_wait(resbar(q, 0), ph0); ph0 ^= 1; }
+                        }
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {      // 16-byte chunks (8 columns)
+                            if (j * 8 >= cw) break;
+                            const int ch = h * 4 + j;
+                            float f[8];
+                            const float4 b0 = ld_shared_f4(bias_s + (cb + ch * 8) * 4);
+                            const float4 b1 = ld_shared_f4(bias_s + (cb + ch * 8 + 4) * 4);
+                            f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
+                            f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
+                            f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
+                            f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
+                            if (has_res) {
+                                const uint4 rv = ld_shared_v4(rbuf + rrow * 128 + (((uint32_t)ch ^ rsw) << 4));
+                                if (lane_res) {
+                                    f[0] += bf16_lo(rv.x); f[1] += bf16_hi(rv.x); f[2] += bf16_lo(rv.y); f[3] += bf16_hi(rv.y);
+                                    f[4] += bf16_lo(rv.z); f[5] += bf16_hi(rv.z); f[6] += bf16_lo(rv.w); f[7] += bf16_hi(rv.w);
+                                }
+                            }
+#pragma unroll
+                            for (int i = 0; i < 4; ++i) {
+                                rr[ch * 4 + i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+                                aa[ch * 4 + i] = pack_bf16(fmaxf(f[2 * i], alpha * f[2 * i]), fmaxf(f[2 * i + 1], alpha * f[2 * i + 1]));
+                            }
+                        }
+                    }
+                    __syncwarp();                          // every lane is done with the residual box
+                    {                                      // refill it with the residual of the block two ahead
+                        const bool is = issue_res(pre, kb);
+                        if (kb) iss1 = is; else iss0 = is;
+                        pre = seq_next(pre);
+                    }
+                    if (leader) tma_store_wait_read();     // the previous block's stores have left the staging boxes
+                    __syncwarp();
+                    const int nch = bw >> 3;
+#pragma unroll
+                    for (int ch = 0; ch < 8; ++ch) {
+                        if (ch >= nch) break;
+                        const uint32_t off = lane * 128 + (((uint32_t)ch ^ sw) << 4);
+                        if (want_raw) st_shared_v4(rawbuf + off, rr[ch * 4], rr[ch * 4 + 1], rr[ch * 4 + 2], rr[ch * 4 + 3]);
+                        if (want_act) st_shared_v4(actbuf + off, aa[ch * 4], aa[ch * 4 + 1], aa[ch * 4 + 2], aa[ch * 4 + 3]);
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (leader && ok) {
+                        if (want_raw) tma_store_2d(&p.tm_raw, rawbuf, cb, pix0);
+                        if (want_act) tma_store_2d(&p.tm_act, actbuf, cb, pix0);
+                        tma_store_commit();
+                    }
+                    kb ^= 1;
+                    cur = seq_next(cur);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty(acc));
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (leader) tma_store_wait_all();
+        __syncwarp();
     } else if (warp >= 4) {
         // ===================== epilogue =====================
         const int q = warp & 3;
@@ -175,21 +344,39 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         epilogue_load_bias(p.epi, bias_s, p.NT, 0, lane);
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int g = cluster_id; g < rounds_total; g += num_clusters) {
-            const int tile = g * csize + (int)rank;
+        auto make_row = [&](int tile, int m) {
             const int n = tile / p.tiles_y;
             const int y0 = (tile % p.tiles_y) * p.rows_tile;
+            const int pix = m * kTileM + r;
+            const int y = y0 + pix / p.W, x = pix % p.W;
+            const bool valid = (n < p.n_valid) && (y < p.H);
+            const size_t opix = ((size_t)n * p.H + y) * p.W + x;
+            EpiRow row;
+            row.opix = opix; row.rpix = opix; row.valid = valid; row.has_res = valid && (p.epi.res_mode != RES_NONE);
+            if (p.epi.res_mode == RES_EVEN) {           // 1x1 stride-2 transposed shortcut: x W lands on even output pixels only
+                row.has_res = row.has_res && !((y | x) & 1);
+                row.rpix = ((size_t)n * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1);
+            }
+            return row;
+        };
+        uint4 rv[8];
+        bool pre = false;
+        EpiRow row = make_row(cluster_id * csize + (int)rank, 0);
+        if (cluster_id < rounds_total && __any_sync(0xffffffffu, row.has_res)) {     // residual of the first tile: before the accumulator is ready
+            epilogue_res_issue(p.epi, row, p.NT, 0, 0, lane, rv);
+            pre = true;
+        }
+        for (int g = cluster_id; g < rounds_total; g += num_clusters) {
+            const int tile = g * csize + (int)rank;
             mbar_wait(tfull(acc), acc_phase);
             tc_fence_after();
             for (int m = 0; m < p.macc; ++m) {
-                const int pix = m * kTileM + r;
-                const int y = y0 + pix / p.W, x = pix % p.W;
-                const bool valid = (n < p.n_valid) && (y < p.H);
-                const size_t opix = ((size_t)n * p.H + y) * p.W + x;
-                EpiRow row;
-                row.opix = opix; row.rpix = opix; row.valid = valid; row.has_res = valid && (p.epi.res_mode != RES_NONE);
+                const bool last_m = (m + 1 == p.macc);
+                const bool more = !last_m || (g + num_clusters < rounds_total);
+                const EpiRow nrow = last_m ? make_row((g + num_clusters) * csize + (int)rank, 0) : make_row(tile, m + 1);
                 const uint32_t taddr0 = tmem_base + acc * kAccColStride + m * p.NT + ((uint32_t)(q * 32) << 16);
-                epilogue_block(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane);
+                pre = epilogue_block(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
+                row = nrow;
             }
             tc_fence_before();
             __syncwarp();

@@ -14,7 +14,8 @@
 // instead of k*ndx times.  Weight tiles stream through their own ring; with cluster size c > 1
 // each CTA fetches 1/c of every weight tile and TMA-multicasts it to the whole cluster.
 //
-// A "group" = (source tensor, channel chunk, dx); it owns k weight tiles ("items").
+// A "group" = (source tensor, channel chunk, dx); it owns k weight tiles, fetched `tpi` taps at a time
+// ("items": one ring slot and one barrier round trip per item).
 #pragma once
 #include <stdint.h>
 #include <cuda.h>
@@ -33,8 +34,13 @@ struct PatchGroup {
 
 constexpr int kPatchMaxSrc = 2;
 constexpr int kPatchMaxGroups = 48;
+// TMA epilogue (bf16 outputs, optional bf16 residual, no mask / tanh / fp32 output): per epilogue warp two
+// residual boxes, one raw and one act staging box of 32 rows x 128 bytes (SWIZZLE_128B), plus the bias row
+constexpr uint32_t kFastEpiBoxBytes = 32u * 128u;
+constexpr uint32_t kFastEpiWarpBytes = 4u * kFastEpiBoxBytes + 1024u;
+constexpr uint32_t kFastEpiSmemBytes = 4u * kFastEpiWarpBytes;
 // shared memory the kernel needs besides the two rings: barriers, realignment slack, epilogue staging
-constexpr uint32_t kPatchFixedSmem = 1024u + 1024u + kEpiSmemBytes;
+constexpr uint32_t kPatchFixedSmem = 1024u + 1024u + (kFastEpiSmemBytes > kEpiSmemBytes ? kFastEpiSmemBytes : kEpiSmemBytes);
 
 struct alignas(64) PatchGemmParams {
     CUtensorMap tm_a[kPatchMaxSrc];  // 5-D (C, W, 1, H, N), box (kc, W, 1, prow_src, 1)
@@ -47,9 +53,15 @@ struct alignas(64) PatchGemmParams {
     int n_valid;
     int Npad, NT;                    // NT == Npad <= 256, macc * NT <= 256
     int kc;                          // 16, 32 or 64 channels per chunk
+    int tpi;                         // vertical taps per weight item (one barrier / ring slot per item)
+    uint32_t tap_bytes;              // NT * kc * 2: one tap's weight tile inside an item
     int a_stages, b_stages;
     uint32_t a_slot_bytes, b_slot_bytes;
     int cluster;                     // 1, 2 or 4 CTAs sharing the weight stream
+    int fast_epi;                    // 1: TMA epilogue through tm_raw / tm_act / tm_res
+    int res_rows;                    // rows of the residual box (32; 16 or 8 for RES_EVEN)
+    CUtensorMap tm_raw, tm_act;      // 2-D (Npad, pixels), box (64, 32), SWIZZLE_128B
+    CUtensorMap tm_res;              // 2-D (Npad, residual pixels), box (64, res_rows)
     int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads (results are garbage)
     EpilogueArgs epi;
 };

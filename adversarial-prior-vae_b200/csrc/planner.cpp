@@ -233,7 +233,11 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     int kmax = 1;
     for (const TermSpec& t : terms) kmax = std::max(kmax, t.k);
     const uint32_t budget = 227u * 1024u - kPatchFixedSmem;
-    P.b_slot_bytes = ((uint32_t)P.npad * P.kc * 2 + 1023u) & ~1023u;
+    P.tap_bytes = (uint32_t)P.npad * P.kc * 2;
+    // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
+    int tpi_want = std::max(1, std::min(kmax, (int)(32768u / P.tap_bytes)));
+    if (const char* e = getenv("APVAE_PATCH_TPI")) { const int v = atoi(e); if (v >= 1 && v <= kmax) tpi_want = v; }
+    auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * P.tap_bytes + 1023u) & ~1023u; };
     auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * W * P.kc * 2 + 1023u) & ~1023u; };
     int macc = 0;
     for (int cand : {4, 2, 1}) {
@@ -241,8 +245,11 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         if (cand * P.npad > 256) continue;
         const int rt = cand * rows128;
         if (rt > H || H % rt) continue;
-        if (2 * a_slot_for(cand) + (uint32_t)std::min(kmax + 1, 4) * P.b_slot_bytes > budget) continue;
+        int tpi = tpi_want;
+        while (tpi > 1 && 2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > budget) --tpi;
+        if (2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > budget) continue;
         macc = cand;
+        P.tpi = tpi;
         break;
     }
     if (!macc) return fail("patch: no accumulator count fits");
@@ -250,20 +257,19 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.rows_tile = macc * rows128;
     P.tiles_y = (H + P.rows_tile - 1) / P.rows_tile;
     P.a_slot_bytes = a_slot_for(macc);
+    P.b_slot_bytes = b_slot_for(P.tpi);
     // ring depths: weights first (k+2 tiles keep one dx group ahead), then patches, then more weights
-    P.b_stages = std::min(12, kmax + 2);
+    P.b_stages = std::min(12, (kmax + P.tpi - 1) / P.tpi + 2);
     while (P.b_stages > 2 && 2 * P.a_slot_bytes + P.b_stages * P.b_slot_bytes > budget) --P.b_stages;
     P.a_stages = 2;
     while (P.a_stages < 4 && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
     while (P.b_stages < 12 && P.a_stages * P.a_slot_bytes + (P.b_stages + 1) * P.b_slot_bytes <= budget) ++P.b_stages;
     if (const char* e = getenv("APVAE_PATCH_ASTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.a_stages) P.a_stages = v; }
     if (const char* e = getenv("APVAE_PATCH_BSTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.b_stages) P.b_stages = v; }
-    // cluster: share the weight stream when it is heavy enough to matter
+    // cluster: weight-stream multicast across 2 / 4 CTAs is available (force_cluster) but measured slower
+    // than independent CTAs on B200 for every layer of the reference models (the weights live in L2 anyway
+    // and the cluster-wide slot release adds a round trip), so the default is 1.
     int c = 1;
-    if (P.npad >= 64) {
-        if ((P.npad / 4) % 8 == 0) c = 4;
-        else if ((P.npad / 2) % 8 == 0) c = 2;
-    }
     if (force_cluster) {
         if (force_cluster != 1 && force_cluster != 2 && force_cluster != 4) return fail("patch: cluster must be 1, 2 or 4");
         if ((P.npad / force_cluster) % 8) return fail("patch: cout slice per cluster CTA must be a multiple of 8");

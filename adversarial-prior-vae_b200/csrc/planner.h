@@ -61,6 +61,8 @@ struct PatchPlan {
     int num_items = 0;
     std::vector<uint16_t> wpack;   // bf16 [items][npad][kc]
     std::vector<float> bias;       // [npad]
+    int tpi = 1;                   // taps per weight item
+    uint32_t tap_bytes = 0;
     int a_stages = 0, b_stages = 0;
     uint32_t a_slot_bytes = 0, b_slot_bytes = 0;
     int cluster = 1;

@@ -87,7 +87,6 @@ static bool check_epilogue(const Epilogue& epi, int npad, const std::string& nam
 bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
                         DevOp* op, std::string* err) {
     EncodeTiledFn encode = reinterpret_cast<EncodeTiledFn>(dev.encode_fn);
-    if (epi.res_mode == RES_EVEN) { if (err) *err = "patch kernel has no even-pixel residual mode"; return false; }
     if (!check_epilogue(epi, plan.npad, op->name, err)) return false;
     const size_t ngroups = plan.groups.size();
     if (ngroups > (size_t)kPatchMaxGroups) { if (err) *err = "patch plan has too many groups"; return false; }
@@ -129,11 +128,45 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.W = plan.w; p.H = plan.h; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
     p.n_valid = 0;
     p.Npad = plan.npad; p.NT = plan.npad; p.kc = plan.kc;
+    p.tpi = plan.tpi; p.tap_bytes = plan.tap_bytes;
     p.a_stages = plan.a_stages; p.b_stages = plan.b_stages;
     p.a_slot_bytes = plan.a_slot_bytes; p.b_slot_bytes = plan.b_slot_bytes;
     p.cluster = plan.cluster;
     { const char* dbg = getenv("APVAE_PATCH_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
     fill_epilogue(p.epi, epi, op->d_bias);
+    // bf16-only epilogues (the conv blocks' interior layers) go through bulk tensor loads / stores
+    p.fast_epi = 0;
+    p.res_rows = 32;
+    {
+        const char* fe = getenv("APVAE_FAST_EPI");
+        const bool plain = !epi.mask && !epi.out_f32 && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
+                           (epi.out_raw || epi.out_act) && (epi.res_mode == RES_NONE || epi.res != nullptr);
+        if (plain && !(fe && fe[0] == '0')) {
+            const cuuint64_t pixels = (cuuint64_t)plan.capacity_n * H * W;
+            bool ok = true;
+            auto map2d = [&](CUtensorMap* tm, const void* ptr, cuuint64_t rows, int ld, cuuint32_t box_rows) {
+                cuuint64_t dims[2] = {(cuuint64_t)plan.npad, rows};
+                cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+                cuuint32_t box[2] = {64, box_rows};
+                const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, ones,
+                                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) ok = false;
+            };
+            const void* any_out = epi.out_raw ? epi.out_raw : epi.out_act;
+            map2d(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out, pixels, epi.ldo, 32);
+            map2d(&p.tm_act, epi.out_act ? epi.out_act : any_out, pixels, epi.ldo, 32);
+            if (epi.res_mode == RES_EVEN) {
+                p.res_rows = (plan.w >= 32) ? 16 : 8;
+                map2d(&p.tm_res, epi.res, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
+            } else if (epi.res_mode == RES_SAME) {
+                map2d(&p.tm_res, epi.res, pixels, epi.ld_res, 32);
+            } else {
+                p.tm_res = p.tm_raw;
+            }
+            p.fast_epi = ok ? 1 : 0;
+        }
+    }
     op->is_patch = true;
     op->macs_per_image = plan.macs_per_image;
     op->capacity_n = plan.capacity_n;

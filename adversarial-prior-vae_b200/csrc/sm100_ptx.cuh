@@ -58,6 +58,18 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
         " [%0], [%1, {%3, %4}], [%2];"
         ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+// Bulk tensor store shared -> global (box clipped at the tensor extents).  Bulk async-groups are per
+// thread: the thread that issues and commits is the one that waits.
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                 ::"l"(map), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all committed groups have finished READING shared memory (the staging buffer may be rewritten)
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// generic-proxy writes to shared memory become visible to the async proxy (TMA)
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 // Multicast: the box lands at the same smem offset in every CTA of `mask`, and completes the
 // transaction on the mbarrier at the same offset in each of them.
 __device__ __forceinline__ void tma_load_2d_mc(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1,
@@ -199,26 +211,58 @@ struct EpiRow {
     bool has_res;    // residual is added to this row
 };
 
+// Issues (does not wait for) the coalesced loads of one 64-column residual block: lane l fetches the
+// 16-byte segments l, l + 32, ... of the 32 rows x bw columns block.  Called one block ahead of its use
+// (and for the first block before the accumulator is even ready), so the L2 latency hides behind the
+// previous block's arithmetic.
+__device__ __forceinline__ void epilogue_res_issue(const EpilogueArgs& e, const EpiRow& row, int NT, int col_base, int cb,
+                                                   int lane, uint4 (&rv)[8]) {
+    const int bw = min((int)kEpiBlockCols, NT - cb);
+    const int segs = bw >> 3;
+    const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(e.res);
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        rv[t] = make_uint4(0, 0, 0, 0);
+        if (t < segs) {                                                // idx = lane + 32 t < 32 segs  (warp-uniform)
+            const int idx = lane + 32 * t;
+            const int r = idx / segs, sg = idx - r * segs;
+            const size_t rp = __shfl_sync(0xffffffffu, (unsigned long long)row.rpix, r);
+            const bool hr = __shfl_sync(0xffffffffu, (int)row.has_res, r);
+            if (hr) rv[t] = __ldg(reinterpret_cast<const uint4*>(res + rp * e.ld_res + col_base + cb) + sg);
+        }
+    }
+}
+
 // `wsm`: this warp's kEpiWarpBytes of shared memory.  `bias_s`: smem address of bias[col_base ...] (NT floats).
-__device__ __forceinline__ void epilogue_block(const EpilogueArgs& e, uint32_t taddr0, int NT, int col_base,
-                                               const EpiRow& row, uint32_t wsm, uint32_t bias_s, int lane) {
+// `rv` / `preloaded`: residual registers, already holding block 0 of `row` when `preloaded`.  When `next` is
+// given, its residual block 0 (at next_col_base) is issued during this tile's last block and the function returns true
+// (pass that as the next call's `preloaded`).
+__device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t taddr0, int NT, int col_base,
+                                               const EpiRow& row, uint32_t wsm, uint32_t bias_s, int lane,
+                                               uint4 (&rv)[8], bool preloaded, const EpiRow* next, int next_col_base) {
     const uint32_t stA = wsm, stB = wsm + kEpiStageBytes;
     const bool any_res = __any_sync(0xffffffffu, row.has_res);
+    bool have = preloaded, next_issued = false;
     for (int cb = 0; cb < NT; cb += (int)kEpiBlockCols) {
         const int bw = min((int)kEpiBlockCols, NT - cb);               // columns in this block (multiple of 16)
         const int segs = bw >> 3;                                      // 16-byte segments per row
         const int total = 32 * segs;
         if (any_res) {                                                 // coalesced residual block -> staging A
-            const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(e.res);
-            for (int idx = lane; idx < total; idx += 32) {
-                const int r = idx / segs, sg = idx - r * segs;
-                const size_t rp = __shfl_sync(0xffffffffu, (unsigned long long)row.rpix, r);
-                const bool hr = __shfl_sync(0xffffffffu, (int)row.has_res, r);
-                uint4 val = make_uint4(0, 0, 0, 0);
-                if (hr) val = __ldg(reinterpret_cast<const uint4*>(res + rp * e.ld_res + col_base + cb) + sg);
-                st_shared_v4(stA + r * kEpiPitch + sg * 16, val.x, val.y, val.z, val.w);
+            if (!have) epilogue_res_issue(e, row, NT, col_base, cb, lane, rv);
+#pragma unroll
+            for (int t = 0; t < 8; ++t) {
+                if (t < segs) {
+                    const int idx = lane + 32 * t;
+                    const int r = idx / segs, sg = idx - r * segs;
+                    st_shared_v4(stA + r * kEpiPitch + sg * 16, rv[t].x, rv[t].y, rv[t].z, rv[t].w);
+                }
             }
             __syncwarp();
+            have = false;
+            if (cb + (int)kEpiBlockCols < NT) { epilogue_res_issue(e, row, NT, col_base, cb + (int)kEpiBlockCols, lane, rv); have = true; }
+        }
+        if (cb + (int)kEpiBlockCols >= NT && next != nullptr && e.res_mode != RES_NONE && !have) {
+            if (__any_sync(0xffffffffu, next->has_res)) { epilogue_res_issue(e, *next, NT, next_col_base, 0, lane, rv); next_issued = true; }
         }
         for (int c = 0; c < bw; c += 32) {
             const int cw = min(32, bw - c);                            // 16 or 32 columns
@@ -318,6 +362,7 @@ __device__ __forceinline__ void epilogue_block(const EpilogueArgs& e, uint32_t t
         }
         __syncwarp();                                                  // staging blocks are reused by the next column block
     }
+    return next_issued;
 }
 
 // Copies bias[col_base, col_base + NT) into this warp's bias area (call when col_base changes).

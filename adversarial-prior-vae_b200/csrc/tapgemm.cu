@@ -157,26 +157,43 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
         const uint32_t bias_s = wsm + 2 * kEpiStageBytes;
         int acc = 0, bias_col = -1;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const TileCoord t = decode_tile(p, tile);
-            if (bias_col != t.nt * p.NT) { bias_col = t.nt * p.NT; epilogue_load_bias(p.epi, bias_s, p.NT, bias_col, lane); }
+        auto make_row = [&](const TileCoord& t) {
             const int n = t.n0 + px_n, gy = t.y0 + px_y, gx = t.x0 + px_x;
             const bool valid = (r < p.rows) && (n < p.n_valid) && (gy < p.Hg) && (gx < p.Wg);
             const int Y = gy * p.os + (p.num_phases == 4 ? (t.ph >> 1) : 0);
             const int X = gx * p.os + (p.num_phases == 4 ? (t.ph & 1) : 0);
-            const size_t opix = ((size_t)n * p.Ho + Y) * p.Wo + X;
-            size_t rpix = opix;
-            bool has_res = valid && (p.epi.res_mode != RES_NONE);
+            EpiRow row;
+            row.opix = ((size_t)n * p.Ho + Y) * p.Wo + X;
+            row.rpix = row.opix;
+            row.valid = valid;
+            row.has_res = valid && (p.epi.res_mode != RES_NONE);
             if (p.epi.res_mode == RES_EVEN) {
-                has_res = has_res && ((Y & 1) == 0) && ((X & 1) == 0);
-                rpix = ((size_t)n * (p.Ho >> 1) + (Y >> 1)) * (p.Wo >> 1) + (X >> 1);
+                row.has_res = row.has_res && ((Y & 1) == 0) && ((X & 1) == 0);
+                row.rpix = ((size_t)n * (p.Ho >> 1) + (Y >> 1)) * (p.Wo >> 1) + (X >> 1);
             }
+            return row;
+        };
+        uint4 rv[8];
+        bool pre = false;
+        if ((int)blockIdx.x < total_tiles) {
+            const TileCoord t0 = decode_tile(p, blockIdx.x);
+            const EpiRow row0 = make_row(t0);
+            if (__any_sync(0xffffffffu, row0.has_res)) {       // first tile's residual: before the accumulator is ready
+                epilogue_res_issue(p.epi, row0, p.NT, t0.nt * p.NT, 0, lane, rv);
+                pre = true;
+            }
+        }
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const TileCoord t = decode_tile(p, tile);
+            if (bias_col != t.nt * p.NT) { bias_col = t.nt * p.NT; epilogue_load_bias(p.epi, bias_s, p.NT, bias_col, lane); }
+            const EpiRow row = make_row(t);
+            const bool more = tile + (int)gridDim.x < total_tiles;
+            const TileCoord tn = decode_tile(p, more ? tile + (int)gridDim.x : tile);
+            const EpiRow nrow = make_row(tn);
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             const uint32_t taddr0 = tmem_base + acc * kAccColStride + ((uint32_t)(q * 32) << 16);
-            EpiRow row;
-            row.opix = opix; row.rpix = rpix; row.valid = valid; row.has_res = has_res;
-            epilogue_block(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane);
+            pre = epilogue_block(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, tn.nt * p.NT);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));

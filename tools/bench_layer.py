@@ -15,7 +15,7 @@ import torch  # noqa: E402
 from apvae.plan import Plan, pad16  # noqa: E402
 
 
-def main():
+def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument('--transpose', action='store_true')
     ap.add_argument('--k', type=int, default=3)
@@ -27,7 +27,8 @@ def main():
     ap.add_argument('--n', type=int, default=256)
     ap.add_argument('--reps', type=int, default=10)
     ap.add_argument('--outs', default='raw,act', help='comma list of raw, act, f32')
-    a = ap.parse_args()
+    ap.add_argument('--res', default='none', help='none | same | even (residual added in the epilogue)')
+    a = ap.parse_args(argv)
     rs = np.random.RandomState(0)
     shp = (a.k, a.k, a.cout, a.cin) if a.transpose else (a.k, a.k, a.cin, a.cout)
     kern = (rs.normal(size=shp) / np.sqrt(a.k * a.k * a.cin)).astype(np.float32)
@@ -43,10 +44,15 @@ def main():
     if 'f32' in a.outs:
         kw['out_f32'] = torch.empty((a.n, i.ho, i.wo, a.cout), dtype=torch.float32, device='cuda')
         kw['f32_cols'] = a.cout
+    if a.res != 'none':
+        from apvae import _lib
+        d = 1 if a.res == 'same' else 2
+        kw['res'] = torch.randn((a.n, i.ho // d, i.wo // d, i.npad), device='cuda').to(torch.bfloat16)
+        kw['res_mode'] = _lib.RES_SAME if a.res == 'same' else _lib.RES_EVEN
     ms = plan.run([src], a.n, bench_reps=a.reps, **kw)
     tf = 2.0 * i.macs_per_image * a.n / (ms * 1e-3) / 1e12
-    print('%s k=%d s=%d %dx%d %d->%d n=%d | patch=%d macc=%d cluster=%d a_st=%d b_st=%d kc=%d | %.4f ms  %.1f TFLOP/s'
-          % ('deconv' if a.transpose else 'conv', a.k, a.stride, a.h, a.w, a.cin, a.cout, a.n, i.patch, i.patch_macc,
+    print('%s k=%d s=%d %dx%d %d->%d n=%d res=%s | patch=%d macc=%d cluster=%d a_st=%d b_st=%d kc=%d | %.4f ms  %.1f TFLOP/s'
+          % ('deconv' if a.transpose else 'conv', a.k, a.stride, a.h, a.w, a.cin, a.cout, a.n, a.res, i.patch, i.patch_macc,
              i.patch_cluster, i.patch_a_stages, i.patch_b_stages, i.kc, ms, tf))
 
 

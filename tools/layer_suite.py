@@ -1,0 +1,60 @@
+"""Runs a fixed list of layer cases (the hot layers of arch A at the bench chunk size) in ONE process, so
+a single ncu invocation can capture all of them:  python tools/layer_suite.py [--reps R] [--only substr]
+Each case = (label, environment overrides, bench_layer arguments)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import bench_layer  # noqa: E402
+
+N = '1000'
+L192 = ['--k', '3', '--h', '16', '--w', '16', '--cin', '192', '--cout', '192', '--n', N]
+L96_5 = ['--transpose', '--k', '5', '--h', '32', '--w', '32', '--cin', '96', '--cout', '96', '--n', N]
+L96_3 = ['--transpose', '--k', '3', '--h', '32', '--w', '32', '--cin', '96', '--cout', '96', '--n', N]
+L192_S2 = ['--transpose', '--k', '3', '--stride', '2', '--h', '16', '--w', '16', '--cin', '192', '--cout', '96', '--n', N]
+CASES = [
+    ('tap192', {'APVAE_PATCH': '0'}, L192),
+    ('tap192_res', {'APVAE_PATCH': '0'}, L192 + ['--res', 'same']),
+    ('patch192', {}, L192),
+    ('patch192_res', {}, L192 + ['--res', 'same']),
+    ('patch96x5', {}, L96_5),
+    ('patch96x5_res', {}, L96_5 + ['--res', 'same']),
+    ('patch96x5_tpi1', {'APVAE_PATCH_TPI': '1'}, L96_5),
+    ('patch96x5_macc1', {'APVAE_PATCH_MACC': '1'}, L96_5),
+    ('patch96x3_even', {}, L96_3 + ['--res', 'even']),
+    ('patch96x3', {}, L96_3),
+    ('tap96x3_even', {'APVAE_PATCH': '0'}, L96_3 + ['--res', 'even']),
+    ('tap192s2', {}, L192_S2),
+    ('patch192_c1', {'APVAE_PATCH_CLUSTER': '1'}, L192),
+    ('patch192_c2', {'APVAE_PATCH_CLUSTER': '2'}, L192),
+    ('patch96x5_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_5),
+    ('patch96x5_c2', {'APVAE_PATCH_CLUSTER': '2'}, L96_5),
+    ('patch96x5_res_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_5 + ['--res', 'same']),
+    ('patch96x3_even_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_3 + ['--res', 'even']),
+]
+
+
+def main():
+    reps, only = '5', None
+    av = sys.argv[1:]
+    if '--reps' in av:
+        reps = av[av.index('--reps') + 1]
+    if '--only' in av:
+        only = av[av.index('--only') + 1].split(',')
+    for label, env, args in CASES:
+        if only and not any(o == label for o in only):
+            continue
+        saved = {k: os.environ.get(k) for k in env}
+        os.environ.update(env)
+        sys.stdout.write('%-16s ' % label)
+        sys.stdout.flush()
+        bench_layer.main(args + ['--reps', reps])
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+if __name__ == '__main__':
+    main()

@@ -1,10 +1,11 @@
-"""Top stalled SASS instructions of an .ncu-rep source page (read here).  python tools/ncu_hot.py rep [N]"""
+"""Top stalled SASS instructions of an .ncu-rep source page (read here).  python tools/ncu_hot.py rep [N] [launch-index]"""
 import csv, io, subprocess, sys
-out = subprocess.run(['ncu', '-i', sys.argv[1], '--page', 'source', '--csv'], capture_output=True, text=True).stdout
+sel = ['--launch-skip', sys.argv[3], '--launch-count', '1'] if len(sys.argv) > 3 else []
+out = subprocess.run(['ncu', '-i', sys.argv[1], '--page', 'source', '--csv'] + sel, capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
 hdr = rows[1]
 ix = {h: i for i, h in enumerate(hdr)}
-body = rows[2:]
+body = [r for r in rows[2:] if len(r) >= len(hdr) - 1 and r[ix['# Samples']].isdigit()]
 tot = sum(int(r[ix['# Samples']] or 0) for r in body)
 stalls = [h for h in hdr if h.startswith('stall_') and 'Not Issued' not in h]
 N = int(sys.argv[2]) if len(sys.argv) > 2 else 25
