@@ -342,7 +342,10 @@ int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* na
     if (!p || index < 0 || index >= (int)p->size() || reps <= 0) { m.err = "op_time: bad arguments"; return APVAE_ERR_INVALID; }
     DevOp& op = *(*p)[index];
     if (n <= 0 || n > op.capacity_n) { m.err = "op_time: n exceeds the op's capacity"; return APVAE_ERR_INVALID; }
-    if (name && name_cap > 0) { strncpy(name, op.name.c_str(), name_cap - 1); name[name_cap - 1] = 0; }
+    if (name && name_cap > 0) {      // op name + which kernel runs it
+        const std::string full = op.name + (op.is_patch ? (op.pparams.fast_epi ? " [patchgemm, TMA epilogue]" : " [patchgemm]") : " [tapgemm]");
+        strncpy(name, full.c_str(), name_cap - 1); name[name_cap - 1] = 0;
+    }
     if (macs_per_unit) *macs_per_unit = op.macs_per_image;
     cudaStream_t st = (cudaStream_t)stream;
     cudaEvent_t e0, e1;

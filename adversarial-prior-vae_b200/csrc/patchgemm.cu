@@ -81,7 +81,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     const int cluster_id = blockIdx.x / csize;
     const int rounds_total = (total_tiles + csize - 1) / csize;   // tile groups; every CTA of a cluster runs the same rounds
     constexpr uint32_t row_bytes = KC * 2;
-    const bool skipA = (p.debug == 1 || p.debug == 3), skipB = (p.debug == 1 || p.debug == 2);
+    const bool skipA = (p.debug == 1 || p.debug == 3 || p.debug >= 10), skipB = (p.debug == 1 || p.debug == 2 || p.debug >= 10);
 
     if (warp == 0) {
         // ===================== activation-patch producer (whole warp, one lane issues) =====================
@@ -249,7 +249,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         for (int g = cluster_id; g < rounds_total; g += num_clusters) {
             mbar_wait(tfull(acc), acc_phase);
             tc_fence_after();
-            for (int m = 0; m < p.macc; ++m) {
+            for (int m = 0; m < ((p.debug == 4 || p.debug == 14) ? 0 : p.macc); ++m) {
                 for (int cb = 0; cb < p.NT; cb += 64) {
                     const int bw = min(64, p.NT - cb);
                     const uint32_t taddr = tmem_base + acc * kAccColStride + m * p.NT + cb + ((uint32_t)(q * 32) << 16);
@@ -319,7 +319,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
-                    if (leader && ok) {
+                    if (leader && ok && p.debug != 5 && p.debug != 15) {
                         if (want_raw) tma_store_2d(&p.tm_raw, rawbuf, cb, pix0);
                         if (want_act) tma_store_2d(&p.tm_act, actbuf, cb, pix0);
                         tma_store_commit();

@@ -62,7 +62,7 @@ struct alignas(64) PatchGemmParams {
     int res_rows;                    // rows of the residual box (32; 16 or 8 for RES_EVEN)
     CUtensorMap tm_raw, tm_act;      // 2-D (Npad, pixels), box (64, 32), SWIZZLE_128B
     CUtensorMap tm_res;              // 2-D (Npad, residual pixels), box (64, res_rows)
-    int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads (results are garbage)
+    int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
     EpilogueArgs epi;
 };
 

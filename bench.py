@@ -43,7 +43,7 @@ def parse_args():
     ap.add_argument('--z-dim', type=int, default=128)
     ap.add_argument('--n-z', type=int, default=1000, help='importance samples per image (K)')
     ap.add_argument('--batch', type=int, default=16, help='images per step per GPU')
-    ap.add_argument('--chunk', type=int, default=256, help='(image,sample) pairs per decoder/energy launch')
+    ap.add_argument('--chunk', type=int, default=1000, help='(image,sample) pairs per decoder/energy launch')
     ap.add_argument('--cpu-batch', type=int, default=2)
     ap.add_argument('--cpu-n-z', type=int, default=8)
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -297,9 +297,19 @@ def main():
         dom = max((r for r in rows if r[0] != 'q_net'), key=lambda r: r[3])
         ach = 2.0 * dom[2] * dom[4] / (dom[3] * 1e-3) / 1e12
         all_flops = sum(2.0 * r[2] * r[4] for r in rows if r[0] != 'q_net')
-        roofline = {'bound': 'tensor', 'kernel': 'tapgemm_kernel (tcgen05/TMEM/TMA implicit GEMM), op ' + dom[1],
+        traffic, traffic_src = None, None
+        try:                                   # DRAM bytes per launch from the committed ncu --set full capture
+            with open(os.path.join(ROOT, 'profiles', 'r1_traffic.json')) as f:
+                tj = json.load(f)
+            if args.chunk == 1000 and args.arch == 'A' and args.z_dim == 128:
+                traffic = tj['bytes_per_launch'].get(dom[1].split(' [')[0])
+                traffic_src = tj['source']
+        except (OSError, ValueError, KeyError):
+            pass
+        roofline = {'bound': 'tensor', 'kernel': 'tcgen05/TMEM/TMA implicit GEMM, op ' + dom[1],
+                    'traffic_unit': 'bytes of DRAM per launch', 'traffic_source': traffic_src,
                     'achieved': round(ach, 1), 'peak': peaks['bf16_tflops'], 'unit': 'TFLOP/s',
-                    'frac': round(ach / peaks['bf16_tflops'], 4), 'traffic': None,
+                    'frac': round(ach / peaks['bf16_tflops'], 4), 'traffic': traffic,
                     'peak_source': peaks['_source'] + ' burst (kernel timed alone, CUDA events)',
                     'share_of_chunk_time': round(dom[3] / tot, 4),
                     'all_ops_tflops': round(all_flops / (tot * 1e-3) / 1e12, 1),

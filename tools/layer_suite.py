@@ -32,6 +32,17 @@ CASES = [
     ('patch96x5_res_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_5 + ['--res', 'same']),
     ('patch96x3_even_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_3 + ['--res', 'even']),
 ]
+# tuning probes: APVAE_PATCH_DEBUG skips loads (results are garbage, timing only)
+for _d, _nm in ((1, 'noload'), (2, 'noB'), (3, 'noA')):
+    for _c in (1, 2):
+        CASES.append(('dbg192_%s_c%d' % (_nm, _c), {'APVAE_PATCH_DEBUG': str(_d), 'APVAE_PATCH_CLUSTER': str(_c)}, L192))
+    CASES.append(('dbg96x5_%s' % _nm, {'APVAE_PATCH_DEBUG': str(_d)}, L96_5))
+for _b in (2, 3):
+    CASES.append(('dbg192_bst%d' % _b, {'APVAE_PATCH_BSTAGES': str(_b)}, L192))
+for _d, _nm in ((4, 'noepi'), (5, 'nostore'), (14, 'noload_noepi'), (15, 'noload_nostore')):
+    CASES.append(('dbx192_%s' % _nm, {'APVAE_PATCH_DEBUG': str(_d)}, L192))
+    CASES.append(('dbx96x5_%s' % _nm, {'APVAE_PATCH_DEBUG': str(_d)}, L96_5))
+CASES.append(('dbg192_ast2', {'APVAE_PATCH_ASTAGES': '2'}, L192))
 
 
 def main():
@@ -42,7 +53,7 @@ def main():
     if '--only' in av:
         only = av[av.index('--only') + 1].split(',')
     for label, env, args in CASES:
-        if only and not any(o == label for o in only):
+        if (only and not any(label.startswith(o) for o in only)) or (not only and label.startswith('db')):
             continue
         saved = {k: os.environ.get(k) for k in env}
         os.environ.update(env)
