@@ -486,15 +486,28 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
 }
 
 // ---------------------------------------------------------------- sampler (input-gradient programs)
-int apvae_energy_grad(apvae_handle* h, const float*, int, float*, float*, float*, void*) {
-    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
-    h->m.err = "energy_grad: input-gradient programs are not built in this version";
-    return APVAE_ERR_UNSUPPORTED;
+int apvae_energy_grad(apvae_handle* h, const float* z_dev, int n, float* energy_dev, float* grad_dev, float* pure_dev,
+                      void* stream) {
+    REQUIRE_BUILT(h);
+    if (!m.cfg.enable_grad) { m.err = "energy_grad: create the handle with enable_grad = 1"; return APVAE_ERR_STATE; }
+    if (n <= 0 || !z_dev) { m.err = "energy_grad: empty batch"; return APVAE_ERR_INVALID; }
+    const int d = m.cfg.z_dim;
+    for (int s0 = 0; s0 < n; s0 += m.cfg.max_chunk) {
+        const int c = std::min(m.cfg.max_chunk, n - s0);
+        if (!m.energy_grad_chunk(z_dev + (size_t)s0 * d, c, energy_dev ? energy_dev + s0 : nullptr,
+                                 grad_dev ? grad_dev + (size_t)s0 * d : nullptr, pure_dev ? pure_dev + s0 : nullptr, stream))
+            return APVAE_ERR_CUDA;
+    }
+    return APVAE_OK;
 }
-int apvae_mala(apvae_handle* h, float*, int, int, float, const float*, const float*, uint64_t, float*, float*, float*, void*) {
-    if (!h) return set_global_err("null handle", APVAE_ERR_INVALID);
-    h->m.err = "mala: input-gradient programs are not built in this version";
-    return APVAE_ERR_UNSUPPORTED;
+int apvae_mala(apvae_handle* h, float* z_io_dev, int n, int steps, float alpha, const float* eps_dev, const float* u_dev,
+               uint64_t seed, float* hist_e_dev, float* hist_pure_e_dev, float* hist_ratio_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (!m.cfg.enable_grad) { m.err = "mala: create the handle with enable_grad = 1"; return APVAE_ERR_STATE; }
+    if (n <= 0 || steps < 0 || !z_io_dev) { m.err = "mala: empty batch"; return APVAE_ERR_INVALID; }
+    if (!(alpha > 0.f)) { m.err = "mala: alpha must be positive"; return APVAE_ERR_INVALID; }
+    return m.mala(z_io_dev, n, steps, alpha, eps_dev, u_dev, seed, hist_e_dev, hist_pure_e_dev, hist_ratio_dev, stream)
+               ? APVAE_OK : APVAE_ERR_CUDA;
 }
 
 }  // extern "C"

@@ -350,6 +350,22 @@ __global__ void energy_combine_kernel(const float* __restrict__ d_g, const float
     if (lane == 0 && energy) energy[s] = w_xi * d_g[s] + 0.5f * ss;
 }
 
+__global__ void tanh_backward_pack_kernel(const float* __restrict__ g, const float* __restrict__ head, int ld,
+                                          long long pixels, int C, int cp, __nv_bfloat16* __restrict__ out) {
+    const long long total = pixels * cp;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long p = i / cp;
+        const int c = (int)(i - p * cp);
+        float v = 0.f;
+        if (c < C) {
+            const float t = head[p * ld + c];
+            v = g[p * C + c] * (1.f - t * t);
+        }
+        out[i] = __float2bfloat16(v);
+    }
+}
+
 __global__ void quantize_kernel(const float* __restrict__ head, int ld, long long pixels, int C,
                                 uint8_t* __restrict__ out) {
     const long long total = pixels * C;
@@ -500,6 +516,13 @@ int launch_energy_combine(const float* d_g, const float* gz, const float* z, int
                           float* energy, float* grad, void* stream) {
     if (n <= 0) return 0;
     energy_combine_kernel<<<(n + 7) / 8, 256, 0, st(stream)>>>(d_g, gz, z, n, d, w_xi, energy, grad);
+    return (int)cudaGetLastError();
+}
+int launch_tanh_backward_pack(const float* g, const float* head, int ld, long long pixels, int C, int cp,
+                              void* out_bf16, void* stream) {
+    if (pixels <= 0) return 0;
+    tanh_backward_pack_kernel<<<grid_for(pixels * cp, 256), 256, 0, st(stream)>>>(g, head, ld, pixels, C, cp,
+                                                                               (__nv_bfloat16*)out_bf16);
     return (int)cudaGetLastError();
 }
 int launch_quantize_images(const float* head, int ld, long long pixels, int C, uint8_t* out, void* stream) {

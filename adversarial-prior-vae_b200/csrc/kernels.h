@@ -77,6 +77,11 @@ int launch_mala_accept(float* z, float* e, float* g, float* pure, const float* z
 int launch_energy_combine(const float* d_g, const float* gz, const float* z, int n, int d, float w_xi,
                           float* energy, float* grad, void* stream);
 
+// Backward through x_mean = tanh(pre): out[p, c] = g[p, c] * (1 - head[p*ld + c]^2) as bf16 [pixels, cp], zero padded
+// (head holds the fp32 tanh OUTPUT; g is the fp32 gradient w.r.t. x_mean, [pixels, C]).
+int launch_tanh_backward_pack(const float* g, const float* head, int ld, long long pixels, int C, int cp,
+                              void* out_bf16, void* stream);
+
 // uint8 = round(clip(256 * x_mean / 2 + 127.5, 0, 255))   (dmm_cifar10.py:976-977,990,1067)
 int launch_quantize_images(const float* head, int ld, long long pixels, int C, uint8_t* out, void* stream);
 

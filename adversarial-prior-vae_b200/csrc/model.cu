@@ -8,7 +8,9 @@
 namespace apvae {
 
 Model::~Model() {
-    q_prog.clear(); g_prog.clear(); d_prog.clear();
+    q_prog.clear(); g_prog.clear(); d_prog.clear(); gd_prog.clear(); gg_prog.clear();
+    for (float* p : {mz, mzp, mg, mgp, me, mep, mp, mpp, meps, mu})
+        if (p) cudaFree(p);
     for (void* p : allocs) cudaFree(p);
     for (float* p : {eps_buf, log_px, log_q, log_pn, d_g})
         if (p) cudaFree(p);

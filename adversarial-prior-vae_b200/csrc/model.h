@@ -76,6 +76,12 @@ public:
     bool run_encoder(const float* x_dev, int B, void* stream);                  // -> q_mu, q_logstd
     bool run_decoder_chunk(int n, void* stream);                                // g_in -> head_f32, d_in
     bool run_critic_chunk(int n, float* d_out, void* stream);                   // d_in -> d_out[n]
+    // energy E = w xi D(G(z)) + |z|^2 / 2, grad_z E and D(G(z)) for n <= max_chunk latents (fp32 [n, z_dim]);
+    // any output may be null (get_sgld_proposal, dmm_cifar10.py:241-247)
+    bool energy_grad_chunk(const float* z_dev, int n, float* energy, float* grad, float* pure, void* stream);
+    // EnergyDistribution.sample's loop (dmm_cifar10.py:197-238)
+    bool mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
+              float* hist_e, float* hist_pure, float* hist_ratio, void* stream);
     bool critic_of_images(const float* x_dev, int N, float* d_out, void* stream);
     bool ensure_sample_buffers(size_t samples);
 
@@ -96,6 +102,16 @@ public:
 
     // device state
     Program q_prog, g_prog, d_prog;
+    Program gd_prog, gg_prog;  // input-gradient programs: d D / d x_mean, then d x_mean / d z (enable_grad)
+    double macs_grad = 0;
+    Tensor d_seed;             // dD/d(flatten) = W64 w_last, one copy per sample (constant)
+    float* gx_f32 = nullptr;   // [max_chunk*HW, C] gradient w.r.t. x_mean
+    Tensor g_pre;              // gradient w.r.t. the x_mean head's pre-activation, bf16 [max_chunk,H,W,16]
+    float* gz_f32 = nullptr;   // [max_chunk, z_dim] d D(G(z)) / d z
+    // MALA state (grow-only): current / proposed z, energy, gradient, pure energy, noise
+    size_t mala_cap = 0;
+    float *mz = nullptr, *mzp = nullptr, *mg = nullptr, *mgp = nullptr, *me = nullptr, *mep = nullptr, *mp = nullptr,
+          *mpp = nullptr, *meps = nullptr, *mu = nullptr;
     Pair q_in;                 // [max_batch, H, W, 16]
     float* q_mu = nullptr;     // [max_batch, z_dim]
     float* q_logstd = nullptr;
@@ -131,6 +147,9 @@ public:
     bool build_q();
     bool build_g();
     bool build_d();
+    bool build_grad();
+    bool grad_conv_block(const BlockTape& t, const Tensor& g_out, float* out_f32, int f32_ld, Tensor* g_in_out);
+    bool grad_deconv_block(const BlockTape& t, const Tensor& g_out, float* out_f32, int f32_ld, Tensor* g_in_out);
     bool run_program(Program& prog, int n, void* stream);
 };
 

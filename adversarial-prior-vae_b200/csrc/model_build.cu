@@ -162,6 +162,7 @@ bool Model::build() {
     if (built) return fail("weights already loaded (create a new handle to reload)");
     if (cudaSetDevice(dev.device) != cudaSuccess) return fail("cudaSetDevice failed");
     if (!build_q() || !build_g() || !build_d()) return false;
+    if (cfg.enable_grad && !build_grad()) return false;
     z_tmp = alloc_f32((size_t)cfg.max_chunk * cfg.z_dim);
     if (!z_tmp) return false;
     if (cudaDeviceSynchronize() != cudaSuccess) return fail("device error while uploading weights");

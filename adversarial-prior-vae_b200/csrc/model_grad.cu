@@ -1,0 +1,241 @@
+// Input-gradient programs: grad_z of E(z) = w xi D_psi(G_theta(z)) + |z|^2 / 2, which is what
+// tf.gradients(energy, [z]) returns in get_sgld_proposal (experiment/dmm/dmm_cifar10.py:241-247),
+// and the MALA loop built on it (EnergyDistribution.sample, :179-239).
+//
+// The adjoint of every layer is again a planned op on the same two tcgen05 kernels:
+//   conv2d(K[kh,kw,Ci,Co], stride s)^T   = deconv2d with the SAME array read as [kh,kw,Cout'=Ci,Cin'=Co]
+//   deconv2d(K[kh,kw,Co,Ci], stride s)^T = conv2d   with the SAME array read as [kh,kw,Cin'=Co,Cout'=Ci]
+// (conv2d_transpose(SAME) is the exact adjoint of the SAME forward conv, conv2d_.py:464-471), biases drop
+// out, and leaky_relu'(v) = (v > 0 ? 1 : 0.2) is applied in the epilogue from the saved activation
+// (`mask`: sign(leaky_relu(v)) == sign(v)).  Pre-activation block (resnet.py:243-265):
+//   out = shortcut(x) + conv_1(act(r)),  r = conv_0(act(x)) + b0
+//   g_r = conv_1^T(g_out) * act'(r)
+//   g_x = conv_0^T(g_r) * act'(x) + shortcut^T(g_out)
+// D_psi's two dense layers have no activation between them (dmm_cifar10.py:559-561), so
+// dD/d(flatten) = W64 w_last is a constant vector, uploaded once per sample slot.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cmath>
+#include "kernels.h"
+#include "model.h"
+
+namespace apvae {
+
+static inline int pad16g(int c) { return (c + 15) & ~15; }
+
+static TermSpec gterm(bool transpose, int k, int stride, int cin, int cout, const Tensor& in, const HostArr* kernel) {
+    TermSpec t;
+    t.src = 0; t.transpose = transpose ? 1 : 0; t.k = k; t.stride = stride; t.cin = cin; t.cout = cout;
+    t.in_h = in.h; t.in_w = in.w; t.in_cp = in.cp;
+    t.kernel = kernel->v.data();
+    t.bias = nullptr;
+    return t;
+}
+
+// Backward of a resnet_conv2d_block (D_psi).  g_out: gradient w.r.t. the block output [cap, Ho, Wo, cout].
+bool Model::grad_conv_block(const BlockTape& t, const Tensor& g_out, float* out_f32, int f32_ld, Tensor* g_x_out) {
+    const int cap = cfg.max_chunk, k = t.k, s = t.stride, cin = t.cin, cout = t.cout;
+    const int H = t.in.h(), Wd = t.in.w();
+    const HostArr* k0 = W_(t.scope + "residual/conv_0/kernel", {k, k, cin, cin});
+    const HostArr* k1 = W_(t.scope + "residual/conv_1/kernel", {k, k, cin, cout});
+    if (!k0 || !k1) return false;
+    Tensor g_r = alloc_act(cap, H, Wd, cin);
+    if (!g_r.ptr) return false;
+    {   // g_r = conv_1^T(g_out) * act'(r)
+        Epilogue e; e.out_raw = g_r.ptr; e.ldo = g_r.cp; e.mask = t.r_act.ptr; e.ld_mask = t.r_act.cp;
+        if (!add_op(gd_prog, t.scope + "conv_1^T", {gterm(true, k, s, cout, cin, g_out, k1)}, {g_out.ptr}, e, cap, &macs_grad)) return false;
+    }
+    Epilogue e;
+    e.mask = t.in.act.ptr; e.ld_mask = t.in.act.cp;
+    if (t.use_shortcut) {   // shortcut^T: 1x1 transpose at the OUTPUT resolution; for s == 2 it lands on even input pixels
+        const HostArr* ks = W_(t.scope + "shortcut/kernel", {1, 1, cin, cout});
+        if (!ks) return false;
+        Tensor g_sc = alloc_act(cap, g_out.h, g_out.w, cin);
+        if (!g_sc.ptr) return false;
+        Epilogue es; es.out_raw = g_sc.ptr; es.ldo = g_sc.cp;
+        if (!add_op(gd_prog, t.scope + "shortcut^T", {gterm(true, 1, 1, cout, cin, g_out, ks)}, {g_out.ptr}, es, cap, &macs_grad)) return false;
+        e.res = g_sc.ptr; e.ld_res = g_sc.cp; e.res_mode = (s == 1) ? RES_SAME : RES_EVEN;
+    } else {
+        e.res = g_out.ptr; e.ld_res = g_out.cp; e.res_mode = RES_SAME;
+    }
+    Tensor g_x = alloc_act(cap, H, Wd, cin);
+    if (!g_x.ptr) return false;
+    e.out_raw = g_x.ptr; e.ldo = g_x.cp;
+    if (out_f32) { e.out_f32 = out_f32; e.ld_f32 = f32_ld; e.f32_cols = cin; }
+    if (!add_op(gd_prog, t.scope + "conv_0^T", {gterm(true, k, 1, cin, cin, g_r, k0)}, {g_r.ptr}, e, cap, &macs_grad)) return false;
+    *g_x_out = g_x;
+    return true;
+}
+
+// Backward of a resnet_deconv2d_block (G_theta).  g_out: [cap, H*s, W*s, cout].
+bool Model::grad_deconv_block(const BlockTape& t, const Tensor& g_out, float* out_f32, int f32_ld, Tensor* g_x_out) {
+    const int cap = cfg.max_chunk, k = t.k, s = t.stride, cin = t.cin, cout = t.cout;
+    const int H = t.in.h(), Wd = t.in.w();
+    const HostArr* k0 = W_(t.scope + "residual/conv_0/kernel", {k, k, cout, cin});
+    const HostArr* k1 = W_(t.scope + "residual/conv_1/kernel", {k, k, cout, cout});
+    if (!k0 || !k1) return false;
+    Tensor g_r = alloc_act(cap, g_out.h, g_out.w, cout);
+    if (!g_r.ptr) return false;
+    {   // g_r = deconv_1^T(g_out) * act'(r): a stride-1 conv
+        Epilogue e; e.out_raw = g_r.ptr; e.ldo = g_r.cp; e.mask = t.r_act.ptr; e.ld_mask = t.r_act.cp;
+        if (!add_op(gg_prog, t.scope + "conv_1^T", {gterm(false, k, 1, cout, cout, g_out, k1)}, {g_out.ptr}, e, cap, &macs_grad)) return false;
+    }
+    Epilogue e;
+    e.mask = t.in.act.ptr; e.ld_mask = t.in.act.cp;
+    if (t.use_shortcut) {   // shortcut^T = 1x1 conv with stride s of g_out (input resolution)
+        const HostArr* ks = W_(t.scope + "shortcut/kernel", {1, 1, cout, cin});
+        if (!ks) return false;
+        Tensor g_sc = alloc_act(cap, H, Wd, cin);
+        if (!g_sc.ptr) return false;
+        Epilogue es; es.out_raw = g_sc.ptr; es.ldo = g_sc.cp;
+        if (!add_op(gg_prog, t.scope + "shortcut^T", {gterm(false, 1, s, cout, cin, g_out, ks)}, {g_out.ptr}, es, cap, &macs_grad)) return false;
+        e.res = g_sc.ptr; e.ld_res = g_sc.cp; e.res_mode = RES_SAME;
+    } else {
+        e.res = g_out.ptr; e.ld_res = g_out.cp; e.res_mode = RES_SAME;
+    }
+    Tensor g_x = alloc_act(cap, H, Wd, cin);
+    if (!g_x.ptr) return false;
+    e.out_raw = g_x.ptr; e.ldo = g_x.cp;
+    if (out_f32) { e.out_f32 = out_f32; e.ld_f32 = f32_ld; e.f32_cols = cin; }
+    if (!add_op(gg_prog, t.scope + "conv_0^T", {gterm(false, k, s, cout, cin, g_r, k0)}, {g_r.ptr}, e, cap, &macs_grad)) return false;
+    *g_x_out = g_x;
+    return true;
+}
+
+bool Model::build_grad() {
+    const int cap = cfg.max_chunk;
+    if (d_tape.empty() || g_tape.empty()) return fail("gradient programs need the forward tapes");
+    // ---- seed: dD/d(flatten) = W64 w_last  (dense(64) then dense(1), no activation in between)
+    const int feat = d_flat.h * d_flat.w * d_flat.c;
+    const HostArr* k64 = W_("D_psi/level_-2/kernel", {feat, 64});
+    const HostArr* kl = W_("D_psi/level_-1/kernel", {64, 1});
+    if (!k64 || !kl) return false;
+    std::vector<uint16_t> seed((size_t)feat);
+    for (int i = 0; i < feat; ++i) {
+        double a = 0;
+        for (int j = 0; j < 64; ++j) a += (double)k64->v[(size_t)i * 64 + j] * kl->v[j];
+        const float f = (float)a;
+        uint32_t u; memcpy(&u, &f, 4);
+        u += 0x7fffu + ((u >> 16) & 1u);                 // round to nearest even bf16
+        seed[i] = (uint16_t)(u >> 16);
+    }
+    d_seed = alloc_act(cap, d_flat.h, d_flat.w, d_flat.c);
+    if (!d_seed.ptr) return false;
+    {
+        std::vector<uint16_t> rep((size_t)cap * feat);
+        for (int n = 0; n < cap; ++n) memcpy(rep.data() + (size_t)n * feat, seed.data(), (size_t)feat * 2);
+        if (cudaMemcpy(d_seed.ptr, rep.data(), rep.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess) return fail("upload of the gradient seed failed");
+    }
+    gx_f32 = alloc_f32((size_t)cap * HW() * C());
+    gz_f32 = alloc_f32((size_t)cap * cfg.z_dim);
+    g_pre = alloc_act(cap, H(), W(), C());
+    if (!gx_f32 || !gz_f32 || !g_pre.ptr) return false;
+    // ---- D_psi backward: blocks in reverse; the first block's input gradient is d D / d x_mean (fp32)
+    Tensor g = d_seed;
+    for (int i = (int)d_tape.size() - 1; i >= 0; --i) {
+        Tensor gx;
+        if (!grad_conv_block(d_tape[i], g, i == 0 ? gx_f32 : nullptr, C(), &gx)) return false;
+        g = gx;
+    }
+    // ---- x_mean = tanh(head): elementwise between the two programs (run_energy_grad), then the 1x1 head^T
+    const std::string mean_name = cfg.arch == APVAE_ARCH_M ? "G_theta/feature_map_mean_to_pixel" : "G_theta/x_mean";
+    const int cg = g_head_in.c;
+    const HostArr* km = W_(mean_name + "/kernel", {1, 1, cg, C()});
+    if (!km) return false;
+    Tensor g_h = alloc_act(cap, H(), W(), cg);
+    if (!g_h.ptr) return false;
+    {
+        Epilogue e; e.out_raw = g_h.ptr; e.ldo = g_h.cp;
+        if (!add_op(gg_prog, mean_name + "^T", {gterm(true, 1, 1, C(), cg, g_pre, km)}, {g_pre.ptr}, e, cap, &macs_grad)) return false;
+    }
+    // ---- G_theta backward
+    g = g_h;
+    for (int i = (int)g_tape.size() - 1; i >= 0; --i) {
+        const bool to_z = (i == 0 && cfg.arch == APVAE_ARCH_A);      // block 0's input IS z reshaped to [8,8,zc]
+        Tensor gx;
+        if (!grad_deconv_block(g_tape[i], g, to_z ? gz_f32 : nullptr, zc(), &gx)) return false;
+        g = gx;
+    }
+    if (cfg.arch != APVAE_ARCH_A) {      // dense(z, 64*8*8)^T: g_z = g_h0 W^T
+        const int feat0 = 64 * g_base_h() * g_base_w();
+        const HostArr* kd = W_("G_theta/level_0/kernel", {cfg.z_dim, feat0});
+        if (!kd) return false;
+        HostArr& kt = weights["G_theta/level_0/kernel^T"];
+        kt.shape = {feat0, cfg.z_dim};
+        kt.v.resize((size_t)feat0 * cfg.z_dim);
+        for (int a = 0; a < cfg.z_dim; ++a)
+            for (int b = 0; b < feat0; ++b) kt.v[(size_t)b * cfg.z_dim + a] = kd->v[(size_t)a * feat0 + b];
+        if (g.cp != g.c) return fail("G_theta first block input has channel padding");
+        Tensor v = g;
+        v.h = 1; v.w = 1; v.c = feat0; v.cp = pad16g(feat0);
+        Epilogue e; e.out_f32 = gz_f32; e.ld_f32 = cfg.z_dim; e.f32_cols = cfg.z_dim;
+        TermSpec t = gterm(false, 1, 1, feat0, cfg.z_dim, v, &kt);
+        if (!add_op(gg_prog, "G_theta/level_0^T", {t}, {v.ptr}, e, cap, &macs_grad)) return false;
+    }
+    return true;
+}
+
+#define GCHECK(call, what)                                                                        \
+    do {                                                                                          \
+        const int _e = (call);                                                                    \
+        ++launches;                                                                               \
+        if (_e != 0) return fail(std::string(what) + ": " + cudaGetErrorString((cudaError_t)_e)); \
+    } while (0)
+
+bool Model::energy_grad_chunk(const float* z_dev, int n, float* energy, float* grad, float* pure, void* stream) {
+    if (!cfg.enable_grad || gd_prog.empty()) return fail("this handle was created without enable_grad");
+    if (n > cfg.max_chunk) return fail("energy_grad_chunk: n exceeds max_chunk");
+    // forward (keeps every block's activations: they are the masks of the backward ops)
+    GCHECK(launch_sample_z(nullptr, nullptr, z_dev, n, 0, 1, cfg.z_dim, 0.f, 0, nullptr, g_in.raw.ptr, g_in.act.ptr,
+                           z_stride(), z_group(), z_cpad(), 0.2f, nullptr, nullptr, stream), "stage_latents");
+    if (!run_decoder_chunk(n, stream)) return false;
+    float* d_out = pure ? pure : z_tmp;                 // z_tmp: [max_chunk, z_dim] scratch, large enough for n floats
+    if (!run_critic_chunk(n, d_out, stream)) return false;
+    if (grad) {
+        if (!run_program(gd_prog, n, stream)) return false;
+        GCHECK(launch_tanh_backward_pack(gx_f32, head_f32, head_ld(), (long long)n * HW(), C(), g_pre.cp, g_pre.ptr, stream),
+               "tanh_backward");
+        if (!run_program(gg_prog, n, stream)) return false;
+    }
+    if (energy || grad)
+        GCHECK(launch_energy_combine(d_out, gz_f32, z_dev, n, cfg.z_dim, w_xi(), energy, grad, stream), "energy_combine");
+    return true;
+}
+
+bool Model::mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
+                 float* hist_e, float* hist_pure, float* hist_ratio, void* stream) {
+    const int d = cfg.z_dim;
+    if ((size_t)n > mala_cap) {
+        for (float** p : {&mz, &mzp, &mg, &mgp, &me, &mep, &mp, &mpp, &meps, &mu}) { if (*p) cudaFree(*p); *p = nullptr; }
+        mala_cap = 0;
+        for (float** p : {&mzp, &mg, &mgp, &meps})
+            if (cudaMalloc(p, (size_t)n * d * sizeof(float)) != cudaSuccess) return fail("cudaMalloc (MALA state)");
+        for (float** p : {&me, &mep, &mp, &mpp, &mu})
+            if (cudaMalloc(p, (size_t)n * sizeof(float)) != cudaSuccess) return fail("cudaMalloc (MALA state)");
+        mala_cap = (size_t)n;
+    }
+    auto eval_all = [&](const float* z, float* e, float* g, float* p) {
+        for (int s0 = 0; s0 < n; s0 += cfg.max_chunk) {
+            const int m = std::min(cfg.max_chunk, n - s0);
+            if (!energy_grad_chunk(z + (size_t)s0 * d, m, e + s0, g + (size_t)s0 * d, p + s0, stream)) return false;
+        }
+        return true;
+    };
+    // energy / gradient at the start; afterwards the accepted state's values are carried over (the
+    // reference recomputes them every step, :197-199; the values are the same)
+    if (!eval_all(z_io, me, mg, mp)) return false;
+    for (int i = 0; i < steps; ++i) {
+        const float* eps_i = eps ? eps + (size_t)i * n * d : meps;
+        const float* u_i = u ? u + (size_t)i * n : mu;
+        if (!eps) GCHECK(launch_fill_normal(meps, (long long)n * d, seed, (unsigned long long)i * 2 * n * d, 0, stream), "fill_normal");
+        if (!u) GCHECK(launch_fill_uniform(mu, n, seed ^ 0x9e3779b97f4a7c15ull, (unsigned long long)i * n, stream), "fill_uniform");
+        GCHECK(launch_mala_propose(z_io, mg, eps_i, n, d, alpha, mzp, nullptr, nullptr, 0, 1, 0, 0.2f, stream), "mala_propose");
+        if (!eval_all(mzp, mep, mgp, mpp)) return false;
+        GCHECK(launch_mala_accept(z_io, me, mg, mp, mzp, mep, mgp, mpp, u_i, n, d, alpha,
+                                  hist_e ? hist_e + (size_t)i * n : nullptr, hist_pure ? hist_pure + (size_t)i * n : nullptr,
+                                  hist_ratio ? hist_ratio + (size_t)i * n : nullptr, stream), "mala_accept");
+    }
+    return true;
+}
+
+}  // namespace apvae

@@ -216,3 +216,87 @@ def test_errors_are_loud():
     with pytest.raises(ApvaeError):     # arch M's G_theta has a single (mean) head
         m.decode(np.zeros((1, 40), np.float32), return_std=True)
     m.close()
+
+
+# ----------------------------------------------------------------------------- sampler
+GRAD_CASES = {
+    'A128': ('A', dict(z_dim=128), 5),
+    'Bcifar': ('B', dict(dataset='cifar10'), 5),
+    'Bceleba': ('B', dict(dataset='celebA'), 3),
+    'M40': ('M', dict(), 5),
+}
+
+
+@pytest.mark.parametrize('case', sorted(GRAD_CASES))
+def test_energy_gradient_matches_oracle(case):
+    """get_sgld_proposal's energy / tf.gradients(energy, [z]) / pure energy (dmm_cifar10.py:241-247)
+    through apvae_energy_grad: dgrad programs of D_psi o G_theta on the same tcgen05 kernels."""
+    arch, kw, n = GRAD_CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=3, enable_grad=True)      # n > max_chunk: ragged chunks
+    xi_raw = 0.4
+    m.set_scalars(xi_raw=xi_raw, beta=0.0, log_Z=1.0)
+    z = np.random.RandomState(11).normal(size=(n, ocfg.z_dim))
+    e_o, g_o, p_o = O.energy_and_grad(ocfg, params, z, xi_raw=xi_raw)
+    e, g, p = [t.cpu().numpy().astype(np.float64) for t in m.energy_grad(z)]
+    w_xi = ocfg.pull_back_energy_weight / (1 + np.exp(-xi_raw))
+    _energy_close(p, p_o)
+    assert np.abs(e - e_o).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
+    # the D(G(z)) part (the z part is exact) as a relative L2 error per chain.  With random-init weights the gradient is
+    # dominated by leaky-relu sign patterns: rounding ONLY the kernels to bf16 already moves the float64 oracle's
+    # gradient by ~6 % (arch A), so the comparison that isolates the kernels is against the oracle run on the
+    # bf16-rounded kernels the library actually holds.
+    from helpers import bf16_round
+    pb = {k: (bf16_round(v) if k.endswith('kernel') else v) for k, v in params.items()}
+    _, g_b, _ = O.energy_and_grad(ocfg, pb, z, xi_raw=xi_raw)
+    gz, gz_b, gz_o = (g - z) / w_xi, (g_b - z) / w_xi, (g_o - z) / w_xi
+    rel_b = np.linalg.norm(gz - gz_b, axis=-1) / np.linalg.norm(gz_b, axis=-1)
+    rel_o = np.linalg.norm(gz - gz_o, axis=-1) / np.linalg.norm(gz_o, axis=-1)
+    assert rel_b.max() < 1e-1, (rel_b, rel_o)         # measured 3-7 % (bf16 activations and gradients through ~60 layers)
+    assert rel_o.max() < 1.5e-1, (rel_b, rel_o)
+    m.close()
+
+
+@pytest.mark.parametrize('case', ['A128', 'Bceleba'])
+def test_mala_matches_oracle(case):
+    """EnergyDistribution.sample (dmm_cifar10.py:179-239) with fed-in noise.  The uniform draws are chosen with a
+    margin around the oracle's acceptance ratios so that no accept / reject decision is borderline; both outcomes
+    occur.  north_star: samples within 1e-2 abs.
+    bf16 operands leave ~5e-3 of error on D(G(z)); the acceptance ratio sees it multiplied by
+    pull_back_energy_weight * xi (500 at the reference default), so this bf16 test runs the chain at weight 2
+    (same code path; the reference-default weight is covered by the split-precision mode)."""
+    arch, kw, _ = GRAD_CASES[case]
+    ocfg, params, cfg, m = _make(arch, dict(kw, pull_back_energy_weight=2.0), max_chunk=4, enable_grad=True,
+                                 pull_back_energy_weight=2.0)
+    n, steps, alpha, xi_raw = 6, 3, 2e-2, 0.0
+    rs = np.random.RandomState(5)
+    z0 = rs.normal(size=(n, 1, ocfg.z_dim))
+    eps = rs.normal(size=(steps, n, 1, ocfg.z_dim))
+    u = np.zeros((steps, n, 1))
+    z = z0
+    he, hp, hr = [], [], []
+    for i in range(steps):                       # oracle chain; pick u_i away from ratio_i
+        _, _, _, ratio = O.mala_step(ocfg, params, z, eps[i], np.zeros((n, 1)), alpha, xi_raw)
+        want_accept = (np.arange(n) + i) % 3 != 0
+        u[i] = np.where(want_accept[:, None], ratio * 0.5, np.minimum(ratio + 0.5 * (1 - ratio) + 1e-3, 0.999))
+        u[i] = np.where((ratio > 0.97) | want_accept[:, None], ratio * 0.5, u[i])      # ratio ~ 1 cannot be rejected
+        z, e_z, pure, ratio = O.mala_step(ocfg, params, z, eps[i], u[i], alpha, xi_raw)
+        he.append(e_z), hp.append(pure), hr.append(ratio)
+    out = m.mala(z0, steps, alpha=alpha, eps=eps, u=u)
+    got_z = out['z'].cpu().numpy().reshape(z.shape)
+    assert np.abs(got_z - z).max() < 1e-2, np.abs(got_z - z).max()
+    w_xi = ocfg.pull_back_energy_weight * 0.5
+    ge = out['history_e_z'].cpu().numpy().reshape(steps, n)
+    gp = out['history_pure_e_z'].cpu().numpy().reshape(steps, n)
+    gr = out['history_ratio'].cpu().numpy().reshape(steps, n)
+    assert np.abs(gp - np.stack(hp).reshape(steps, n)).max() < ENERGY_MAX_ATOL
+    assert np.abs(ge - np.stack(he).reshape(steps, n)).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(np.stack(he)).max()
+    assert np.abs(gr - np.stack(hr).reshape(steps, n)).max() < 0.1
+    m.close()
+
+
+def test_energy_grad_requires_enable_grad():
+    import apvae
+    ocfg, params, cfg, m = _make('M', {})
+    with pytest.raises(apvae.ApvaeError):
+        m.energy_grad(np.zeros((2, ocfg.z_dim)))
+    m.close()
