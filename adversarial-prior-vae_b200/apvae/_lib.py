@@ -35,7 +35,7 @@ class Config(C.Structure):
         ('epsilon', C.c_float),
         ('uniform_scale', C.c_int), ('use_truncated', C.c_int), ('bernoulli', C.c_int),
         ('max_batch', C.c_int), ('max_chunk', C.c_int), ('enable_grad', C.c_int),
-        ('smallest_step', C.c_float), ('len_train', C.c_int),
+        ('smallest_step', C.c_float), ('len_train', C.c_int), ('precise', C.c_int),
     ]
 
 

@@ -46,6 +46,7 @@ class ExpConfig(object):
         self.max_batch = 64
         self.max_chunk = 512
         self.enable_grad = False
+        self.precise = False       # split-precision G_theta / D_psi (fp32-class energies for the sampler, 3x MMA work)
         for k, v in kw.items():
             if not hasattr(self, k):
                 raise AttributeError('ExpConfig has no field %r' % (k,))
@@ -67,6 +68,7 @@ class ExpConfig(object):
         c.enable_grad = int(self.enable_grad)
         c.smallest_step = float(self.smallest_step)
         c.len_train = int(self.len_train)
+        c.precise = int(self.precise)
         return c
 
 

@@ -183,7 +183,8 @@ int apvae_encode(apvae_handle* h, const float* x_dev, int B, float* mu_dev, floa
 // z fp32 [n, d] -> decoder input tensors (no noise: mu = z, eps unused)
 static int stage_latents(Model& m, const float* z_dev, int n, void* stream) {
     return launch_sample_z(nullptr, nullptr, z_dev, n, 0, 1, m.cfg.z_dim, 0.f, 0, nullptr, m.g_in.raw.ptr,
-                           m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, nullptr, stream);
+                           m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, nullptr, stream,
+                           m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr);
 }
 
 int apvae_decode(apvae_handle* h, const float* z_dev, int N, float* x_mean_dev, float* x_logstd_dev, void* stream) {
@@ -240,7 +241,8 @@ int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev,
         const int n = (int)std::min<long long>(m.cfg.max_chunk, S - s0);
         LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps + s0 * d, n, (int)(s0 % B), B, d, m.cfg.min_logstd_of_q,
                                m.cfg.use_truncated, nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(),
-                               m.z_cpad(), 0.2f, m.log_q + s0, m.log_pn + s0, stream), "sample_z");
+                               m.z_cpad(), 0.2f, m.log_q + s0, m.log_pn + s0, stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
+               "sample_z");
         if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
         LCHECK(launch_pixel_logprob(m.head_f32, m.head_ld(), x_dev, n, (int)(s0 % B), B, m.HW(), m.C(), m.cfg.bernoulli,
                                     m.cfg.uniform_scale, m.beta, m.cfg.epsilon, m.log_px + s0, stream), "pixel_logprob");
@@ -282,7 +284,7 @@ int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t se
         const int n = std::min(m.cfg.max_chunk, Kp - s0);
         LCHECK(launch_sample_z(nullptr, nullptr, eps + (size_t)s0 * d, n, 0, 1, d, 0.f, 0, nullptr, m.g_in.raw.ptr,
                                m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, log_pn_dev + s0,
-                               stream), "sample_z");
+                               stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr), "sample_z");
         if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
         if (!m.run_critic_chunk(n, d_g_dev + s0, stream)) return APVAE_ERR_CUDA;
     }

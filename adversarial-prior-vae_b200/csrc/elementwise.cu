@@ -59,7 +59,8 @@ __device__ float block_max(float v) {
 }
 
 __global__ void pack_image_kernel(const float* __restrict__ x, long long pixels, int c, int cp,
-                                  __nv_bfloat16* __restrict__ raw, __nv_bfloat16* __restrict__ act, float alpha) {
+                                  __nv_bfloat16* __restrict__ raw, __nv_bfloat16* __restrict__ act, float alpha,
+                                  __nv_bfloat16* __restrict__ raw_lo, __nv_bfloat16* __restrict__ act_lo) {
     const long long total = pixels * cp;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -68,6 +69,8 @@ __global__ void pack_image_kernel(const float* __restrict__ x, long long pixels,
         const float v = ch < c ? x[p * c + ch] : 0.f;
         if (raw) raw[i] = __float2bfloat16(v);
         if (act) act[i] = __float2bfloat16(lrelu(v, alpha));
+        if (raw_lo) raw_lo[i] = __float2bfloat16(v - __bfloat162float(__float2bfloat16(v)));
+        if (act_lo) { const float a = lrelu(v, alpha); act_lo[i] = __float2bfloat16(a - __bfloat162float(__float2bfloat16(a))); }
     }
 }
 
@@ -76,7 +79,8 @@ __global__ void sample_z_kernel(const float* __restrict__ mu, const float* __res
                                 const float* __restrict__ eps, int S, int s0, int B, int d, float min_logstd,
                                 int truncated, float* __restrict__ z_f32, __nv_bfloat16* __restrict__ z_raw,
                                 __nv_bfloat16* __restrict__ z_act, long long zstride, int zc, int cpad,
-                                float alpha, float* __restrict__ log_q, float* __restrict__ log_pn) {
+                                float alpha, float* __restrict__ log_q, float* __restrict__ log_pn,
+                                __nv_bfloat16* __restrict__ z_raw_lo, __nv_bfloat16* __restrict__ z_act_lo) {
     const int lane = threadIdx.x & 31;
     const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (s >= S) return;
@@ -101,6 +105,8 @@ __global__ void sample_z_kernel(const float* __restrict__ mu, const float* __res
         const size_t idx = (size_t)s * zstride + (size_t)(j / zc) * cpad + (j % zc);
         if (z_raw) z_raw[idx] = __float2bfloat16(z);
         if (z_act) z_act[idx] = __float2bfloat16(lrelu(z, alpha));
+        if (z_raw_lo) z_raw_lo[idx] = __float2bfloat16(z - __bfloat162float(__float2bfloat16(z)));
+        if (z_act_lo) { const float a = lrelu(z, alpha); z_act_lo[idx] = __float2bfloat16(a - __bfloat162float(__float2bfloat16(a))); }
     }
     lq = warp_sum(lq);
     lp = warp_sum(lp);
@@ -440,21 +446,22 @@ inline cudaStream_t st(void* s) { return static_cast<cudaStream_t>(s); }
 }  // namespace
 
 int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out_raw, void* out_act,
-                      float alpha, void* stream) {
+                      float alpha, void* stream, void* raw_lo, void* act_lo) {
     if (pixels <= 0) return 0;
     pack_image_kernel<<<grid_for(pixels * cp, 256), 256, 0, st(stream)>>>(
-        x, pixels, c, cp, (__nv_bfloat16*)out_raw, (__nv_bfloat16*)out_act, alpha);
+        x, pixels, c, cp, (__nv_bfloat16*)out_raw, (__nv_bfloat16*)out_act, alpha, (__nv_bfloat16*)raw_lo, (__nv_bfloat16*)act_lo);
     return (int)cudaGetLastError();
 }
 
 int launch_sample_z(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
                     float min_logstd, int truncated, float* z_f32, void* z_raw, void* z_act,
                     long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn,
-                    void* stream) {
+                    void* stream, void* z_raw_lo, void* z_act_lo) {
     if (S <= 0) return 0;
     sample_z_kernel<<<(S + 7) / 8, 256, 0, st(stream)>>>(mu, logstd, eps, S, s0, B, d, min_logstd, truncated,
                                                         z_f32, (__nv_bfloat16*)z_raw, (__nv_bfloat16*)z_act,
-                                                        zstride, zc, cpad, alpha, log_q, log_pn);
+                                                        zstride, zc, cpad, alpha, log_q, log_pn,
+                                                        (__nv_bfloat16*)z_raw_lo, (__nv_bfloat16*)z_act_lo);
     return (int)cudaGetLastError();
 }
 

@@ -6,8 +6,9 @@
 namespace apvae {
 
 // x fp32 [pixels, c] -> bf16 [pixels, cp] raw and leaky_relu(x) (cp = 16 k, zero padded).
+// raw_lo / act_lo: optional low halves (v - bf16(v)) for the split-precision mode.
 int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out_raw, void* out_act,
-                      float alpha, void* stream);
+                      float alpha, void* stream, void* raw_lo = nullptr, void* act_lo = nullptr);
 
 // Reparameterised draw + log q(z|x) + log N(z;0,I)   (reference: zd.Normal sample/log_prob via
 // tfsnippet/distributions/wrapper.py:112,127-129; truncated_normal.py:142-149; dmm_cifar10.py:449-450,601-603)
@@ -19,7 +20,7 @@ int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out
 int launch_sample_z(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
                     float min_logstd, int truncated, float* z_f32, void* z_raw, void* z_act,
                     long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn,
-                    void* stream);
+                    void* stream, void* z_raw_lo = nullptr, void* z_act_lo = nullptr);
 
 // log p(x|z) summed over pixels (reference: distributions/discretized.py:198-259 with the
 // dmm_cifar10.py:612-619 parameters; Bernoulli variant dmm_bernouli_fashion.py:619-626).

@@ -61,7 +61,8 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     const char* ec = getenv("APVAE_PATCH_CLUSTER");
     const char* emax = getenv("APVAE_PATCH_MAXN");            // widest output the A-stationary kernel takes (tuning)
     const int patch_max_n = emax ? atoi(emax) : 256;
-    if (!(env && env[0] == '0') &&
+    const bool split_epi = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;     // split precision: tap-GEMM only
+    if (!(env && env[0] == '0') && !split_epi &&
         plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr) && pplan.npad <= patch_max_n) {
         if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");
         if (!devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
@@ -88,38 +89,93 @@ static TermSpec term(int src, bool transpose, int k, int stride, int cin, int co
     return t;
 }
 
+static float bf16_round_host(float f) {
+    uint32_t u; memcpy(&u, &f, 4);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    u &= 0xffff0000u;
+    float r; memcpy(&r, &u, 4);
+    return r;
+}
+
+bool Model::push_terms(std::vector<TermSpec>& terms, std::vector<const void*>& srcs, bool split, const Tensor& hi,
+                       const Tensor& lo, bool transpose, int k, int stride, int cin, int cout, const std::string& wname,
+                       const HostArr* kernel, const HostArr* bias) {
+    const int s0 = (int)srcs.size();
+    if (!split) {
+        terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, kernel, bias));
+        srcs.push_back(hi.ptr);
+        return true;
+    }
+    if (!lo.ptr) return fail("split-precision op " + wname + " has no low-half input");
+    HostArr& whi = weights[wname + "#hi"];
+    HostArr& wlo = weights[wname + "#lo"];
+    if (whi.v.empty()) {
+        whi.shape = kernel->shape; wlo.shape = kernel->shape;
+        whi.v.resize(kernel->v.size()); wlo.v.resize(kernel->v.size());
+        for (size_t i = 0; i < kernel->v.size(); ++i) {
+            whi.v[i] = bf16_round_host(kernel->v[i]);
+            wlo.v[i] = bf16_round_host(kernel->v[i] - whi.v[i]);
+        }
+    }
+    terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, &whi, bias));
+    terms.push_back(term(s0 + 1, transpose, k, stride, cin, cout, lo, &whi, nullptr));
+    terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, &wlo, nullptr));
+    srcs.push_back(hi.ptr);
+    srcs.push_back(lo.ptr);
+    return true;
+}
+
 // resnet_conv2d_block (resnet.py:272-364, resize_at_exit=True):
 //   op1: r = lrelu(conv_k,1(lrelu(x)) + b0)                       [Cin -> Cin]
 //   op2: out = conv_k,s(r) + b1 + (shortcut: conv_1,s(x) + bs | x) [Cin -> Cout]
+// The shortcut is a second source term of op2 (bf16 mode) or its own 1x1 op whose output is op2's residual
+// (split-precision mode, where op2 already has three terms).
 bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
                        bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape) {
     const std::string pre = root + "/" + b.scope + "/";
+    const bool sp = split_mode;
     const int cin = in.c(), cout = b.cout, k = b.k, s = b.stride, H = in.h(), Wd = in.w();
     const bool use_sc = (s != 1) || (cin != cout);
     const HostArr *k0 = W_(pre + "residual/conv_0/kernel", {k, k, cin, cin}), *b0 = W_(pre + "residual/conv_0/bias", {cin});
     const HostArr *k1 = W_(pre + "residual/conv_1/kernel", {k, k, cin, cout}), *b1 = W_(pre + "residual/conv_1/bias", {cout});
     if (!k0 || !b0 || !k1 || !b1) return false;
-    Tensor r = alloc_act(cap, H, Wd, cin);
+    Tensor r = alloc_act(cap, H, Wd, cin), r_lo;
     if (!r.ptr) return false;
+    if (sp) { r_lo = alloc_act(cap, H, Wd, cin); if (!r_lo.ptr) return false; }
     {
-        Epilogue e; e.out_act = r.ptr; e.ldo = r.cp;
-        if (!add_op(prog, pre + "conv_0", {term(0, false, k, 1, cin, cin, in.act, k0, b0)}, {in.act.ptr}, e, cap, macs)) return false;
+        Epilogue e; e.out_act = r.ptr; e.out_act_lo = r_lo.ptr; e.ldo = r.cp;
+        std::vector<TermSpec> terms; std::vector<const void*> srcs;
+        if (!push_terms(terms, srcs, sp, in.act, in.act_lo, false, k, 1, cin, cin, pre + "residual/conv_0/kernel", k0, b0)) return false;
+        if (!add_op(prog, pre + "conv_0", terms, srcs, e, cap, macs)) return false;
     }
     const int Ho = (H + s - 1) / s, Wo = (Wd + s - 1) / s;
     Pair o;
     if (need_raw) { o.raw = alloc_act(cap, Ho, Wo, cout); if (!o.raw.ptr) return false; }
     if (need_act) { o.act = alloc_act(cap, Ho, Wo, cout); if (!o.act.ptr) return false; }
+    if (sp && need_raw) { o.raw_lo = alloc_act(cap, Ho, Wo, cout); if (!o.raw_lo.ptr) return false; }
+    if (sp && need_act) { o.act_lo = alloc_act(cap, Ho, Wo, cout); if (!o.act_lo.ptr) return false; }
     Epilogue e;
-    e.out_raw = o.raw.ptr; e.out_act = o.act.ptr; e.ldo = pad16(cout);
-    std::vector<TermSpec> terms = {term(0, false, k, s, cin, cout, r, k1, b1)};
-    std::vector<const void*> srcs = {r.ptr};
+    e.out_raw = o.raw.ptr; e.out_act = o.act.ptr; e.out_raw_lo = o.raw_lo.ptr; e.out_act_lo = o.act_lo.ptr; e.ldo = pad16(cout);
+    std::vector<TermSpec> terms;
+    std::vector<const void*> srcs;
+    if (!push_terms(terms, srcs, sp, r, r_lo, false, k, s, cin, cout, pre + "residual/conv_1/kernel", k1, b1)) return false;
     if (use_sc) {
         const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cin, cout}), *bs = W_(pre + "shortcut/bias", {cout});
         if (!ks || !bs) return false;
-        terms.push_back(term(1, false, 1, s, cin, cout, in.raw, ks, bs));
-        srcs.push_back(in.raw.ptr);
+        if (!sp) {
+            terms.push_back(term(1, false, 1, s, cin, cout, in.raw, ks, bs));
+            srcs.push_back(in.raw.ptr);
+        } else {
+            Tensor sc = alloc_act(cap, Ho, Wo, cout), sc_lo = alloc_act(cap, Ho, Wo, cout);
+            if (!sc.ptr || !sc_lo.ptr) return false;
+            Epilogue es; es.out_raw = sc.ptr; es.out_raw_lo = sc_lo.ptr; es.ldo = sc.cp;
+            std::vector<TermSpec> ts; std::vector<const void*> ss;
+            if (!push_terms(ts, ss, true, in.raw, in.raw_lo, false, 1, s, cin, cout, pre + "shortcut/kernel", ks, bs)) return false;
+            if (!add_op(prog, pre + "shortcut", ts, ss, es, cap, macs)) return false;
+            e.res = sc.ptr; e.res_lo = sc_lo.ptr; e.res_mode = RES_SAME; e.ld_res = sc.cp;
+        }
     } else {
-        e.res = in.raw.ptr; e.res_mode = RES_SAME; e.ld_res = in.raw.cp;
+        e.res = in.raw.ptr; e.res_lo = in.raw_lo.ptr; e.res_mode = RES_SAME; e.ld_res = in.raw.cp;
     }
     if (!add_op(prog, pre + "conv_1", terms, srcs, e, cap, macs)) return false;
     if (tape) {
@@ -141,43 +197,53 @@ bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& 
 bool Model::deconv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
                          bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape) {
     const std::string pre = root + "/" + b.scope + "/";
+    const bool sp = split_mode;
     const int cin = in.c(), cout = b.cout, k = b.k, s = b.stride, H = in.h(), Wd = in.w();
     const bool use_sc = (s != 1) || (cin != cout);
     const HostArr *k0 = W_(pre + "residual/conv_0/kernel", {k, k, cout, cin}), *b0 = W_(pre + "residual/conv_0/bias", {cout});
     const HostArr *k1 = W_(pre + "residual/conv_1/kernel", {k, k, cout, cout}), *b1 = W_(pre + "residual/conv_1/bias", {cout});
     if (!k0 || !b0 || !k1 || !b1) return false;
     const int Ho = H * s, Wo = Wd * s;
-    Tensor r = alloc_act(cap, Ho, Wo, cout);
+    Tensor r = alloc_act(cap, Ho, Wo, cout), r_lo;
     if (!r.ptr) return false;
+    if (sp) { r_lo = alloc_act(cap, Ho, Wo, cout); if (!r_lo.ptr) return false; }
     {
-        Epilogue e; e.out_act = r.ptr; e.ldo = r.cp;
-        if (!add_op(prog, pre + "conv_0", {term(0, true, k, s, cin, cout, in.act, k0, b0)}, {in.act.ptr}, e, cap, macs)) return false;
+        Epilogue e; e.out_act = r.ptr; e.out_act_lo = r_lo.ptr; e.ldo = r.cp;
+        std::vector<TermSpec> terms; std::vector<const void*> srcs;
+        if (!push_terms(terms, srcs, sp, in.act, in.act_lo, true, k, s, cin, cout, pre + "residual/conv_0/kernel", k0, b0)) return false;
+        if (!add_op(prog, pre + "conv_0", terms, srcs, e, cap, macs)) return false;
     }
     Pair o;
     if (need_raw) { o.raw = alloc_act(cap, Ho, Wo, cout); if (!o.raw.ptr) return false; }
     if (need_act) { o.act = alloc_act(cap, Ho, Wo, cout); if (!o.act.ptr) return false; }
+    if (sp && need_raw) { o.raw_lo = alloc_act(cap, Ho, Wo, cout); if (!o.raw_lo.ptr) return false; }
+    if (sp && need_act) { o.act_lo = alloc_act(cap, Ho, Wo, cout); if (!o.act_lo.ptr) return false; }
     Epilogue e;
-    e.out_raw = o.raw.ptr; e.out_act = o.act.ptr; e.ldo = pad16(cout);
+    e.out_raw = o.raw.ptr; e.out_act = o.act.ptr; e.out_raw_lo = o.raw_lo.ptr; e.out_act_lo = o.act_lo.ptr; e.ldo = pad16(cout);
     HostArr bias_sum = *b1;
-    std::vector<TermSpec> terms = {term(0, true, k, 1, cout, cout, r, k1, &bias_sum)};
-    std::vector<const void*> srcs = {r.ptr};
+    std::vector<TermSpec> terms;
+    std::vector<const void*> srcs;
+    if (!push_terms(terms, srcs, sp, r, r_lo, true, k, 1, cout, cout, pre + "residual/conv_1/kernel", k1, &bias_sum)) return false;
     if (use_sc) {
         const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cout, cin}), *bs = W_(pre + "shortcut/bias", {cout});
         if (!ks || !bs) return false;
-        if (s == 1 && in.raw.cp == r.cp) {
+        if (!sp && s == 1 && in.raw.cp == r.cp) {
             terms.push_back(term(1, true, 1, 1, cin, cout, in.raw, ks, bs));
             srcs.push_back(in.raw.ptr);
         } else {
-            Tensor sc = alloc_act(cap, H, Wd, cout);
+            Tensor sc = alloc_act(cap, H, Wd, cout), sc_lo;
             if (!sc.ptr) return false;
-            Epilogue es; es.out_raw = sc.ptr; es.ldo = sc.cp;
-            if (!add_op(prog, pre + "shortcut", {term(0, true, 1, 1, cin, cout, in.raw, ks, nullptr)}, {in.raw.ptr}, es, cap, macs)) return false;
+            if (sp) { sc_lo = alloc_act(cap, H, Wd, cout); if (!sc_lo.ptr) return false; }
+            Epilogue es; es.out_raw = sc.ptr; es.out_raw_lo = sc_lo.ptr; es.ldo = sc.cp;
+            std::vector<TermSpec> ts; std::vector<const void*> ss;
+            if (!push_terms(ts, ss, sp, in.raw, in.raw_lo, true, 1, 1, cin, cout, pre + "shortcut/kernel", ks, nullptr)) return false;
+            if (!add_op(prog, pre + "shortcut", ts, ss, es, cap, macs)) return false;
             for (int i = 0; i < cout; ++i) bias_sum.v[i] += bs->v[i];
             terms[0].bias = bias_sum.v.data();
-            e.res = sc.ptr; e.res_mode = (s == 1) ? RES_SAME : RES_EVEN; e.ld_res = sc.cp;
+            e.res = sc.ptr; e.res_lo = sc_lo.ptr; e.res_mode = (s == 1) ? RES_SAME : RES_EVEN; e.ld_res = sc.cp;
         }
     } else {
-        e.res = in.raw.ptr; e.res_mode = RES_SAME; e.ld_res = in.raw.cp;
+        e.res = in.raw.ptr; e.res_lo = in.raw_lo.ptr; e.res_mode = RES_SAME; e.ld_res = in.raw.cp;
     }
     if (!add_op(prog, pre + "conv_1", terms, srcs, e, cap, macs)) return false;
     if (tape) {
@@ -192,14 +258,18 @@ bool Model::deconv_block(Program& prog, const std::string& root, const BlockSpec
 // spt.layers.dense (dense_.py:142-147) over a flattened NHWC tensor: a 1x1 conv on a 1x1 image
 // with Cin = in_features.  `in_flat` must have cp == c so the flatten order matches reshape_tail.
 bool Model::dense_op(Program& prog, const std::string& name, const Tensor& in_flat, int in_features, int out_features,
-                     const Epilogue& epi, int cap, double* macs) {
+                     const Epilogue& epi, int cap, double* macs, const Tensor* in_flat_lo) {
     const HostArr *kk = W_(name + "/kernel", {in_features, out_features}), *bb = W_(name + "/bias", {out_features});
     if (!kk || !bb) return false;
-    Tensor v = in_flat;
+    Tensor v = in_flat, vlo;
     v.h = 1; v.w = 1; v.c = in_features; v.cp = pad16(in_features);
     if ((size_t)v.cp * 1 != (size_t)in_flat.h * in_flat.w * in_flat.cp)
         return fail("dense " + name + ": flattened input has channel padding");
-    return add_op(prog, name, {term(0, false, 1, 1, in_features, out_features, v, kk, bb)}, {v.ptr}, epi, cap, macs);
+    const bool sp = split_mode && in_flat_lo && in_flat_lo->ptr;
+    if (sp) { vlo = v; vlo.ptr = in_flat_lo->ptr; }
+    std::vector<TermSpec> terms; std::vector<const void*> srcs;
+    if (!push_terms(terms, srcs, sp, v, vlo, false, 1, 1, in_features, out_features, name + "/kernel", kk, bb)) return false;
+    return add_op(prog, name, terms, srcs, epi, cap, macs);
 }
 
 bool Model::run_program(Program& prog, int n, void* stream) {

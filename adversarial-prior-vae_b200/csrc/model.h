@@ -41,6 +41,7 @@ struct Tensor {
 };
 struct Pair {
     Tensor raw, act;
+    Tensor raw_lo, act_lo;   // split-precision mode: v = hi + lo with both halves bf16 (empty otherwise)
     int h() const { return raw.ptr ? raw.h : act.h; }
     int w() const { return raw.ptr ? raw.w : act.w; }
     int c() const { return raw.ptr ? raw.c : act.c; }
@@ -136,6 +137,13 @@ public:
     Tensor alloc_act(int n, int h, int w, int c);
     float* alloc_f32(size_t n);
     const HostArr* W_(const std::string& name, std::initializer_list<int64_t> shape);
+    // Terms of one (source, kernel) product.  bf16 mode: one term.  Split-precision mode (`split`): activations
+    // and kernels are hi + lo bf16 pairs and the product is A_hi W_hi + A_lo W_hi + A_hi W_lo (the lo*lo term,
+    // 2^-16 relative, is dropped) accumulated in the same fp32 TMEM accumulator.
+    bool push_terms(std::vector<TermSpec>& terms, std::vector<const void*>& srcs, bool split, const Tensor& hi,
+                    const Tensor& lo, bool transpose, int k, int stride, int cin, int cout, const std::string& wname,
+                    const HostArr* kernel, const HostArr* bias);
+    bool split_mode = false;   // set while building G_theta / D_psi of a `precise` handle
     bool add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms,
                 const std::vector<const void*>& srcs, const Epilogue& epi, int cap, double* macs);
     bool conv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
@@ -143,7 +151,7 @@ public:
     bool deconv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,
                       bool need_act, int cap, Pair* out, double* macs, std::vector<BlockTape>* tape);
     bool dense_op(Program& prog, const std::string& name, const Tensor& in_flat, int in_features, int out_features,
-                  const Epilogue& epi, int cap, double* macs);
+                  const Epilogue& epi, int cap, double* macs, const Tensor* in_flat_lo = nullptr);
     bool build_q();
     bool build_g();
     bool build_d();

@@ -70,21 +70,34 @@ bool Model::build_g() {
     const int cap = cfg.max_chunk;
     const int gh = g_base_h(), gw = g_base_w();
     std::vector<BlockTape>* tape = cfg.enable_grad ? &g_tape : nullptr;
+    const bool sp = cfg.precise != 0;
+    split_mode = sp;
     Pair h;
     if (cfg.arch == APVAE_ARCH_A) {           // dmm_cifar10.py:478-480: z reshaped to [8,8,zc]
         g_in.raw = alloc_act(cap, gh, gw, zc());
         g_in.act = alloc_act(cap, gh, gw, zc());
         if (!g_in.raw.ptr || !g_in.act.ptr) return false;
+        if (sp) {
+            g_in.raw_lo = alloc_act(cap, gh, gw, zc());
+            g_in.act_lo = alloc_act(cap, gh, gw, zc());
+            if (!g_in.raw_lo.ptr || !g_in.act_lo.ptr) return false;
+        }
         h = g_in;
     } else {                                  // dmm_for_sampling.py:486-492: dense(z, 64*8*8) -> [8,8,64]
         g_in.raw = alloc_act(cap, 1, 1, cfg.z_dim);
         if (!g_in.raw.ptr) return false;
+        if (sp) { g_in.raw_lo = alloc_act(cap, 1, 1, cfg.z_dim); if (!g_in.raw_lo.ptr) return false; }
         const int feat = 64 * gh * gw;
         h.raw = alloc_act(cap, gh, gw, 64);
         h.act = alloc_act(cap, gh, gw, 64);
         if (!h.raw.ptr || !h.act.ptr) return false;
-        Epilogue e; e.out_raw = h.raw.ptr; e.out_act = h.act.ptr; e.ldo = feat;
-        if (!dense_op(g_prog, "G_theta/level_0", g_in.raw, cfg.z_dim, feat, e, cap, &macs_g)) return false;
+        if (sp) {
+            h.raw_lo = alloc_act(cap, gh, gw, 64);
+            h.act_lo = alloc_act(cap, gh, gw, 64);
+            if (!h.raw_lo.ptr || !h.act_lo.ptr) return false;
+        }
+        Epilogue e; e.out_raw = h.raw.ptr; e.out_act = h.act.ptr; e.out_raw_lo = h.raw_lo.ptr; e.out_act_lo = h.act_lo.ptr; e.ldo = feat;
+        if (!dense_op(g_prog, "G_theta/level_0", g_in.raw, cfg.z_dim, feat, e, cap, &macs_g, &g_in.raw_lo)) return false;
     }
     const std::vector<BlockSpec> blocks = g_blocks(cfg);
     for (size_t i = 0; i < blocks.size(); ++i) {
@@ -101,6 +114,11 @@ bool Model::build_g() {
     d_in.act = alloc_act(cap, H(), W(), Cx);
     head_f32 = alloc_f32((size_t)cap * HW() * head_ld());
     if (!d_in.raw.ptr || !d_in.act.ptr || !head_f32) return false;
+    if (sp) {
+        d_in.raw_lo = alloc_act(cap, H(), W(), Cx);
+        d_in.act_lo = alloc_act(cap, H(), W(), Cx);
+        if (!d_in.raw_lo.ptr || !d_in.act_lo.ptr) return false;
+    }
     HostArr kcat, bcat;
     const bool has_std = head_ld() == 2 * Cx;
     const std::string mean_name = cfg.arch == APVAE_ARCH_M ? "G_theta/feature_map_mean_to_pixel" : "G_theta/x_mean";
@@ -121,18 +139,25 @@ bool Model::build_g() {
             if (has_std) kcat.v[(size_t)ci * nout + Cx + c] = ksd->v[(size_t)ci * Cx + c];
         }
     for (int c = 0; c < Cx; ++c) { bcat.v[c] = bm->v[c]; if (has_std) bcat.v[Cx + c] = bsd->v[c]; }
-    TermSpec t; t.src = 0; t.transpose = 0; t.k = 1; t.stride = 1; t.cin = cg; t.cout = nout;
-    t.in_h = h.h(); t.in_w = h.w(); t.in_cp = h.raw.cp; t.kernel = kcat.v.data(); t.bias = bcat.v.data();
+    HostArr& kc = weights["G_theta/heads/kernel"];      // [1,1,cg,nout]: x_mean | x_logstd side by side
+    kc.shape = {1, 1, cg, nout};
+    kc.v = kcat.v;
     Epilogue e;
-    e.out_raw = d_in.raw.ptr; e.out_act = d_in.act.ptr; e.ldo = d_in.raw.cp; e.bf16_zero_from = Cx;
+    e.out_raw = d_in.raw.ptr; e.out_act = d_in.act.ptr; e.out_raw_lo = d_in.raw_lo.ptr; e.out_act_lo = d_in.act_lo.ptr;
+    e.ldo = d_in.raw.cp; e.bf16_zero_from = Cx;
     e.out_f32 = head_f32; e.ld_f32 = nout; e.f32_cols = nout; e.tanh_cols = Cx;
-    return add_op(g_prog, "G_theta/heads", {t}, {h.raw.ptr}, e, cap, &macs_g);
+    std::vector<TermSpec> terms; std::vector<const void*> srcs;
+    if (!push_terms(terms, srcs, sp, h.raw, h.raw_lo, false, 1, 1, cg, nout, "G_theta/heads/kernel", &kc, &bcat)) return false;
+    const bool ok = add_op(g_prog, "G_theta/heads", terms, srcs, e, cap, &macs_g);
+    split_mode = false;
+    return ok;
 }
 
 bool Model::build_d() {
     const int cap = cfg.max_chunk;
     std::vector<BlockTape>* tape = cfg.enable_grad ? &d_tape : nullptr;
     const std::vector<BlockSpec> blocks = d_blocks(cfg);
+    split_mode = cfg.precise != 0;
     Pair h = d_in;
     for (size_t i = 0; i < blocks.size(); ++i) {
         const bool last = (i + 1 == blocks.size());
@@ -146,7 +171,8 @@ bool Model::build_d() {
     d64 = alloc_f32((size_t)cap * 64);
     if (!d64) return false;
     Epilogue e; e.out_f32 = d64; e.ld_f32 = 64; e.f32_cols = 64;
-    if (!dense_op(d_prog, "D_psi/level_-2", h.raw, feat, 64, e, cap, &macs_d)) return false;   // dmm_cifar10.py:559
+    if (!dense_op(d_prog, "D_psi/level_-2", h.raw, feat, 64, e, cap, &macs_d, &h.raw_lo)) return false;   // dmm_cifar10.py:559
+    split_mode = false;
     const HostArr *kl = W_("D_psi/level_-1/kernel", {64, 1}), *bl = W_("D_psi/level_-1/bias", {1});
     if (!kl || !bl) return false;
     d_last_w = alloc_f32(64);
@@ -214,7 +240,7 @@ bool Model::critic_of_images(const float* x_dev, int N, float* d_out, void* stre
     for (int s0 = 0; s0 < N; s0 += cfg.max_chunk) {
         const int n = std::min(cfg.max_chunk, N - s0);
         KCHECK(launch_pack_image(x_dev + (size_t)s0 * per, (long long)n * HW(), C(), d_in.raw.cp, d_in.raw.ptr,
-                                 d_in.act.ptr, 0.2f, stream), "pack_image");
+                                 d_in.act.ptr, 0.2f, stream, d_in.raw_lo.ptr, d_in.act_lo.ptr), "pack_image");
         if (!run_critic_chunk(n, d_out + s0, stream)) return false;
     }
     return true;

@@ -187,7 +187,8 @@ bool Model::energy_grad_chunk(const float* z_dev, int n, float* energy, float* g
     if (n > cfg.max_chunk) return fail("energy_grad_chunk: n exceeds max_chunk");
     // forward (keeps every block's activations: they are the masks of the backward ops)
     GCHECK(launch_sample_z(nullptr, nullptr, z_dev, n, 0, 1, cfg.z_dim, 0.f, 0, nullptr, g_in.raw.ptr, g_in.act.ptr,
-                           z_stride(), z_group(), z_cpad(), 0.2f, nullptr, nullptr, stream), "stage_latents");
+                           z_stride(), z_group(), z_cpad(), 0.2f, nullptr, nullptr, stream, g_in.raw_lo.ptr, g_in.act_lo.ptr),
+           "stage_latents");
     if (!run_decoder_chunk(n, stream)) return false;
     float* d_out = pure ? pure : z_tmp;                 // z_tmp: [max_chunk, z_dim] scratch, large enough for n floats
     if (!run_critic_chunk(n, d_out, stream)) return false;

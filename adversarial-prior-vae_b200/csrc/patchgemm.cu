@@ -375,7 +375,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 const bool more = !last_m || (g + num_clusters < rounds_total);
                 const EpiRow nrow = last_m ? make_row((g + num_clusters) * csize + (int)rank, 0) : make_row(tile, m + 1);
                 const uint32_t taddr0 = tmem_base + acc * kAccColStride + m * p.NT + ((uint32_t)(q * 32) << 16);
-                pre = epilogue_block(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
+                pre = epilogue_block<false>(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
                 row = nrow;
             }
             tc_fence_before();

@@ -107,7 +107,10 @@ bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, s
         if (&t == &t0) { P.ho = oh; P.wo = ow; }
         else if (oh != P.ho || ow != P.wo) return fail("terms disagree on the output size");
     }
-    if (phased && terms.size() != 1) return fail("a stride-2 transposed conv cannot be fused with other terms");
+    if (phased)      // sub-pixel phases: every term must be the same stride-2 transposed geometry (split-precision terms are)
+        for (const TermSpec& t : terms)
+            if (!t.transpose || t.stride != 2 || t.k != t0.k || t.in_h != t0.in_h || t.in_w != t0.in_w)
+                return fail("a stride-2 transposed conv can only be fused with terms of the same geometry");
     P.num_phases = phased ? 4 : 1;
     P.os = phased ? 2 : 1;
     P.hg = phased ? t0.in_h : P.ho;

@@ -66,6 +66,7 @@ static void fill_epilogue(EpilogueArgs& e, const Epilogue& epi, const float* bia
     e.mask = epi.mask; e.ld_mask = epi.ld_mask;
     e.tanh_cols = epi.tanh_cols;
     e.lrelu_alpha = 0.2f;
+    e.out_raw_lo = epi.out_raw_lo; e.out_act_lo = epi.out_act_lo; e.res_lo = epi.res_lo;
 }
 
 static bool check_epilogue(const Epilogue& epi, int npad, const std::string& name, std::string* err) {
@@ -139,7 +140,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.res_rows = 32;
     {
         const char* fe = getenv("APVAE_FAST_EPI");
-        const bool plain = !epi.mask && !epi.out_f32 && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
+        const bool plain = !epi.mask && !epi.out_f32 && !epi.out_raw_lo && !epi.out_act_lo && !epi.res_lo && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
                            (epi.out_raw || epi.out_act) && (epi.res_mode == RES_NONE || epi.res != nullptr);
         if (plain && !(fe && fe[0] == '0')) {
             const cuuint64_t pixels = (cuuint64_t)plan.capacity_n * H * W;

@@ -22,6 +22,9 @@ struct Epilogue {
     const void* mask = nullptr;
     int ld_mask = 0;
     int tanh_cols = 0;
+    void* out_raw_lo = nullptr;      // split-precision low halves (see tapgemm.h)
+    void* out_act_lo = nullptr;
+    const void* res_lo = nullptr;
 };
 
 struct DeviceInfo {

@@ -219,17 +219,28 @@ __device__ __forceinline__ void epilogue_res_issue(const EpilogueArgs& e, const 
                                                    int lane, uint4 (&rv)[8]) {
     const int bw = min((int)kEpiBlockCols, NT - cb);
     const int segs = bw >> 3;
-    const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(e.res);
+    const int sh = (segs == 8) ? 3 : (segs == 4) ? 2 : (segs == 2) ? 1 : -1;      // segs is even; 6 (48 columns) divides
+    const __nv_bfloat16* res = static_cast<const __nv_bfloat16*>(e.res) + col_base + cb;
+    const uint32_t rmask = __ballot_sync(0xffffffffu, row.has_res);
+    const uint32_t my_rp = (uint32_t)row.rpix;
+    // all addresses first, then all loads back to back: a shuffle between two loads would wait on the scoreboard the
+    // previous load holds and serialise the eight L2 round trips
+    const uint4* ptr[8];
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+        ptr[t] = nullptr;
+        if (t < segs) {                                                // idx = lane + 32 t < 32 segs  (warp-uniform)
+            const int idx = lane + 32 * t;
+            const int r = sh >= 0 ? (idx >> sh) : (idx / segs);
+            const int sg = idx - r * segs;
+            const uint32_t rp = __shfl_sync(0xffffffffu, my_rp, r);
+            if ((rmask >> r) & 1u) ptr[t] = reinterpret_cast<const uint4*>(res + (size_t)rp * e.ld_res) + sg;
+        }
+    }
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
         rv[t] = make_uint4(0, 0, 0, 0);
-        if (t < segs) {                                                // idx = lane + 32 t < 32 segs  (warp-uniform)
-            const int idx = lane + 32 * t;
-            const int r = idx / segs, sg = idx - r * segs;
-            const size_t rp = __shfl_sync(0xffffffffu, (unsigned long long)row.rpix, r);
-            const bool hr = __shfl_sync(0xffffffffu, (int)row.has_res, r);
-            if (hr) rv[t] = __ldg(reinterpret_cast<const uint4*>(res + rp * e.ld_res + col_base + cb) + sg);
-        }
+        if (t < segs && ptr[t] != nullptr) rv[t] = __ldg(ptr[t]);
     }
 }
 
@@ -237,6 +248,7 @@ __device__ __forceinline__ void epilogue_res_issue(const EpilogueArgs& e, const 
 // `rv` / `preloaded`: residual registers, already holding block 0 of `row` when `preloaded`.  When `next` is
 // given, its residual block 0 (at next_col_base) is issued during this tile's last block and the function returns true
 // (pass that as the next call's `preloaded`).
+template <bool kSplit>
 __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t taddr0, int NT, int col_base,
                                                const EpiRow& row, uint32_t wsm, uint32_t bias_s, int lane,
                                                uint4 (&rv)[8], bool preloaded, const EpiRow* next, int next_col_base) {
@@ -253,7 +265,8 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
             for (int t = 0; t < 8; ++t) {
                 if (t < segs) {
                     const int idx = lane + 32 * t;
-                    const int r = idx / segs, sg = idx - r * segs;
+                    const int r = (segs == 8) ? (idx >> 3) : (segs == 4) ? (idx >> 2) : (segs == 2) ? (idx >> 1) : (idx / segs);
+                    const int sg = idx - r * segs;
                     st_shared_v4(stA + r * kEpiPitch + sg * 16, rv[t].x, rv[t].y, rv[t].z, rv[t].w);
                 }
             }
@@ -316,6 +329,20 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                         }
                     }
                 }
+                if (kSplit && e.res_lo != nullptr && row.has_res) {              // low half of a split-precision residual (this lane's row)
+                    const uint4* r4 = reinterpret_cast<const uint4*>(static_cast<const __nv_bfloat16*>(e.res_lo) +
+                                                                     row.rpix * e.ld_res + col);
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) {
+                        const uint4 m = __ldg(r4 + i);
+                        const uint32_t w[4] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            f[8 * i + 2 * j + 0] += bf16_lo(w[j]);
+                            f[8 * i + 2 * j + 1] += bf16_hi(w[j]);
+                        }
+                    }
+                }
                 if (col < e.tanh_cols) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i)
@@ -333,6 +360,30 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                         if (col + i >= e.bf16_zero_from) f[i] = 0.f;
                 }
                 const uint32_t so = lane * kEpiPitch + (c + h * 16) * 2;
+                if (kSplit && e.out_raw_lo != nullptr && row.valid) {            // v - bf16(v), written straight from registers
+                    uint32_t lo[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const uint32_t hi = pack_bf16(f[2 * i], f[2 * i + 1]);
+                        lo[i] = pack_bf16(f[2 * i] - bf16_lo(hi), f[2 * i + 1] - bf16_hi(hi));
+                    }
+                    uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(e.out_raw_lo) + row.opix * e.ldo + col);
+                    o[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    o[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                }
+                if (kSplit && e.out_act_lo != nullptr && row.valid) {
+                    uint32_t lo[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float a0 = f[2 * i] > 0.f ? f[2 * i] : e.lrelu_alpha * f[2 * i];
+                        const float a1 = f[2 * i + 1] > 0.f ? f[2 * i + 1] : e.lrelu_alpha * f[2 * i + 1];
+                        const uint32_t hi = pack_bf16(a0, a1);
+                        lo[i] = pack_bf16(a0 - bf16_lo(hi), a1 - bf16_hi(hi));
+                    }
+                    uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(e.out_act_lo) + row.opix * e.ldo + col);
+                    o[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                    o[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+                }
                 if (e.out_raw != nullptr) {
                     st_shared_v4(stA + so, pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
                     st_shared_v4(stA + so + 16, pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
@@ -349,14 +400,18 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
             __syncwarp();
             __nv_bfloat16* oraw = static_cast<__nv_bfloat16*>(e.out_raw);
             __nv_bfloat16* oact = static_cast<__nv_bfloat16*>(e.out_act);
+            const int sh = (segs == 8) ? 3 : (segs == 4) ? 2 : (segs == 2) ? 1 : -1;
+            const uint32_t vmask = __ballot_sync(0xffffffffu, row.valid);
+            const uint32_t my_op = (uint32_t)row.opix;
             for (int idx = lane; idx < total; idx += 32) {
-                const int r = idx / segs, sg = idx - r * segs;
-                const size_t op = __shfl_sync(0xffffffffu, (unsigned long long)row.opix, r);
-                const bool ok = __shfl_sync(0xffffffffu, (int)row.valid, r);
-                if (ok) {
-                    const size_t off = op * e.ldo + col_base + cb;
-                    if (oraw != nullptr) *(reinterpret_cast<uint4*>(oraw + off) + sg) = ld_shared_v4(stA + r * kEpiPitch + sg * 16);
-                    if (oact != nullptr) *(reinterpret_cast<uint4*>(oact + off) + sg) = ld_shared_v4(stB + r * kEpiPitch + sg * 16);
+                const int r = sh >= 0 ? (idx >> sh) : (idx / segs);
+                const int sg = idx - r * segs;
+                const uint32_t op = __shfl_sync(0xffffffffu, my_op, r);
+                if ((vmask >> r) & 1u) {
+                    const size_t off = (size_t)op * e.ldo + col_base + cb;
+                    const uint32_t sa = r * kEpiPitch + sg * 16;
+                    if (oraw != nullptr) *(reinterpret_cast<uint4*>(oraw + off) + sg) = ld_shared_v4(stA + sa);
+                    if (oact != nullptr) *(reinterpret_cast<uint4*>(oact + off) + sg) = ld_shared_v4(stB + sa);
                 }
             }
         }

@@ -42,7 +42,7 @@ __device__ __forceinline__ TileCoord decode_tile(const TapGemmParams& p, int til
 
 }  // namespace
 
-template <int KC>
+template <int KC, bool kSplit>
 __global__ void __launch_bounds__(kThreads, 1)
 tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -193,7 +193,7 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             const uint32_t taddr0 = tmem_base + acc * kAccColStride + ((uint32_t)(q * 32) << 16);
-            pre = epilogue_block(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, tn.nt * p.NT);
+            pre = epilogue_block<kSplit>(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, tn.nt * p.NT);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar(acc));
@@ -229,10 +229,11 @@ int launch_tapgemm(const TapGemmParams& p, int num_sms, void* stream) {
     const uint32_t smem = tapgemm_smem_bytes(p.kc, p.NT, p.num_stages);
     cudaError_t err;
     void (*kern)(TapGemmParams) = nullptr;
+    const bool split = p.epi.out_raw_lo != nullptr || p.epi.out_act_lo != nullptr || p.epi.res_lo != nullptr;
     switch (p.kc) {
-        case 16: kern = tapgemm_kernel<16>; break;
-        case 32: kern = tapgemm_kernel<32>; break;
-        case 64: kern = tapgemm_kernel<64>; break;
+        case 16: kern = split ? tapgemm_kernel<16, true> : tapgemm_kernel<16, false>; break;
+        case 32: kern = split ? tapgemm_kernel<32, true> : tapgemm_kernel<32, false>; break;
+        case 64: kern = split ? tapgemm_kernel<64, true> : tapgemm_kernel<64, false>; break;
         default: return (int)cudaErrorInvalidValue;
     }
     err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

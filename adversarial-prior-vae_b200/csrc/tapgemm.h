@@ -50,6 +50,10 @@ struct EpilogueArgs {
     int ld_mask;
     int tanh_cols;
     float lrelu_alpha;
+    // split-precision mode (activations carried as hi + lo bf16 pairs, see model.h `precise`): low halves
+    void* out_raw_lo;           // bf16(v - bf16(v))
+    void* out_act_lo;           // bf16(leaky_relu(v) - bf16(leaky_relu(v)))
+    const void* res_lo;         // low half of the residual (same indexing as res)
 };
 
 struct alignas(64) TapGemmParams {

@@ -52,6 +52,9 @@ typedef struct apvae_config {
     int enable_grad;                /* build the input-gradient programs (MALA, grad norms) */
     float smallest_step;            /* config.smallest_step (default MALA alpha) */
     int len_train;                  /* config.len_train (log-Z offset) */
+    int precise;                    /* 1: split-precision G_theta / D_psi (activations and kernels as hi + lo bf16 pairs,
+                                     * three tensor-core products per term, fp32 accumulate): fp32-class energies for the
+                                     * sampler at 3x the MMA work.  0: plain bf16 operands (evaluation default). */
 } apvae_config;
 
 typedef struct apvae_handle apvae_handle;

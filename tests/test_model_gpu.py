@@ -300,3 +300,60 @@ def test_energy_grad_requires_enable_grad():
     with pytest.raises(apvae.ApvaeError):
         m.energy_grad(np.zeros((2, ocfg.z_dim)))
     m.close()
+
+
+# ----------------------------------------------------------------------------- split-precision mode
+PRECISE_ATOL = 1e-4     # north_star: energies / samples within 1e-4 abs "in fp32"
+
+
+@pytest.mark.parametrize('case', ['A128', 'Bceleba', 'M40'])
+def test_precise_mode_reaches_fp32_class_energies(case):
+    """ExpConfig.precise: activations and kernels as hi + lo bf16 pairs (A_hi W_hi + A_lo W_hi + A_hi W_lo on the
+    tensor cores, fp32 accumulate).  D(G(z)), D(x) and x_mean must match the float64 oracle (full-precision
+    weights) to the fp32 tolerance of north_star."""
+    arch, kw, n = GRAD_CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=3, precise=True)
+    z = np.random.RandomState(11).normal(size=(n, ocfg.z_dim))
+    xm_o = O.G_theta(ocfg, params, z)
+    xm = m.decode(z).cpu().numpy()
+    assert np.abs(xm - xm_o).max() < PRECISE_ATOL, np.abs(xm - xm_o).max()
+    dg = m.energy_of_latents(z).cpu().numpy()
+    dg_o = O.D_psi(ocfg, params, xm_o)
+    assert np.abs(dg - dg_o).max() < PRECISE_ATOL, np.abs(dg - dg_o).max()
+    x, x_origin, _ = _inputs(ocfg, 3, 1)
+    d = m.energy_of_images(x_origin).cpu().numpy()
+    assert np.abs(d - O.D_psi(ocfg, params, x_origin)).max() < PRECISE_ATOL
+    m.close()
+
+
+@pytest.mark.parametrize('case', ['A128', 'Bceleba'])
+def test_precise_mala_at_the_reference_energy_weight(case):
+    """MALA with pull_back_energy_weight = 1000 (reference default): the acceptance ratio sees 500 x the error of
+    D(G(z)), which needs the split-precision forward.  Accept / reject decisions and samples must match the oracle."""
+    arch, kw, _ = GRAD_CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=4, enable_grad=True, precise=True)
+    assert ocfg.pull_back_energy_weight == 1000.0
+    n, steps, alpha, xi_raw = 6, 3, ocfg.smallest_step, 0.0
+    rs = np.random.RandomState(5)
+    z0 = rs.normal(size=(n, 1, ocfg.z_dim))
+    eps = rs.normal(size=(steps, n, 1, ocfg.z_dim))
+    u = np.zeros((steps, n, 1))
+    z = z0
+    he, hp, hr, acc = [], [], [], []
+    for i in range(steps):
+        _, _, _, ratio = O.mala_step(ocfg, params, z, eps[i], np.zeros((n, 1)), alpha, xi_raw)
+        want_accept = ((np.arange(n) + i) % 3 != 0)[:, None] | (ratio > 0.8)
+        u[i] = np.where(want_accept, ratio * 0.5, np.minimum(ratio + 0.5 * (1 - ratio), 0.999))
+        acc.append(u[i] < ratio)
+        z, e_z, pure, ratio = O.mala_step(ocfg, params, z, eps[i], u[i], alpha, xi_raw)
+        he.append(e_z), hp.append(pure), hr.append(ratio)
+    out = m.mala(z0, steps, alpha=alpha, eps=eps, u=u)
+    got_z = out['z'].cpu().numpy().reshape(z.shape)
+    assert np.abs(got_z - z).max() < 1e-3, np.abs(got_z - z).max()      # alpha * (bf16 gradient error) ~ 1e-4
+    gp = out['history_pure_e_z'].cpu().numpy().reshape(steps, n)
+    ge = out['history_e_z'].cpu().numpy().reshape(steps, n)
+    gr = out['history_ratio'].cpu().numpy().reshape(steps, n)
+    assert np.abs(gp - np.stack(hp).reshape(steps, n)).max() < PRECISE_ATOL
+    assert np.abs(ge - np.stack(he).reshape(steps, n)).max() < 500 * PRECISE_ATOL + 1e-5 * np.abs(np.stack(he)).max()
+    assert np.abs(gr - np.stack(hr).reshape(steps, n)).max() < 0.25, (gr, np.stack(hr).reshape(steps, n))
+    m.close()
