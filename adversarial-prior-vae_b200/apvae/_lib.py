@@ -94,6 +94,7 @@ _SYMBOLS = [
     ('apvae_decode', C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
     ('apvae_energy', C.c_int, [_P, _P, _P, C.c_int, _P, _P]),
     ('apvae_is_nll', C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
+    ('apvae_sample_z', C.c_int, [_P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P, _P]),
     ('apvae_accumulate_metrics', C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
     ('apvae_prior_stats', C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     ('apvae_mala', C.c_int, [_P, _P, C.c_int, C.c_int, C.c_float, _P, _P, C.c_uint64, _P, _P, _P, _P]),

@@ -1,0 +1,196 @@
+"""The experiment scripts' call surface (experiment/dmm/dmm_cifar10.py, dmm_for_sampling.py,
+dmm_bernouli_fashion.py) over one `Model`: same builder names, arguments and attribute paths, eager
+instead of graph-building.  A script's test section
+
+    test_q_net = q_net(input_origin_x, posterior_flow, n_z=config.test_n_qz)
+    test_chain = test_q_net.chain(p_net, latent_axis=0, observed={'x': input_x}, n_z=..., beta=beta, log_Z=...)
+    ele_test_ll = test_chain.vi.evaluation.is_loglikelihood()             # :896-898
+    test_recon  = tf.reduce_mean(test_chain.model['x'].log_prob())        # :886-888
+    adv_test_nll via test_chain.model['z'].log_prob().energy / .log_energy_prob    # :901-910
+
+reads the same here with `s = Script(model)` and `s.q_net(...)`, `s.p_net`, `s.G_theta`, `s.D_psi`.
+Everything is computed by the library (apvae_sample_z / apvae_is_nll / apvae_decode / apvae_energy /
+apvae_mala); torch only holds the buffers.  Reductions over the sample axis that the reference writes as
+tf.reduce_mean(..) on the returned tensors are the caller's, as in the reference."""
+import math
+
+
+class _Lazy(object):
+    """Evaluates the mini-batch once (one apvae_is_nll call with per-sample rows) on first use."""
+
+    def __init__(self, model, x, x_origin, K, eps, seed, beta, log_Z):
+        self.model, self.x, self.x_origin, self.K, self.eps, self.seed = model, x, x_origin, K, eps, seed
+        self.beta, self.log_Z = beta, log_Z
+        self._out = None
+
+    def get(self):
+        if self._out is None:
+            m = self.model
+            if self.beta is not None or self.log_Z is not None:
+                m.set_scalars(m.xi_raw, m.beta if self.beta is None else self.beta,
+                              m.log_Z if self.log_Z is None else self.log_Z)
+            self._out = m.is_nll(self.x, self.K, x_origin=self.x_origin, eps=self.eps, seed=self.seed, per_sample=True)
+        return self._out
+
+
+class _LogProb(object):
+    """What EnergyDistribution.log_prob returns (dmm_cifar10.py:164-177): the Gaussian log p_N(z) as a tensor with
+    .energy, .log_energy_prob and .pure_energy attached."""
+
+    def __init__(self, log_pn, d_g, w_xi, log_Z, z_dim):
+        self.tensor = log_pn
+        self.pure_energy = d_g                                                        # :175
+        half_sq = -log_pn - 0.5 * z_dim * math.log(2 * math.pi)                       # 0.5 |z|^2
+        self.energy = w_xi * d_g + half_sq                                            # :169-171
+        self.log_energy_prob = -self.energy - max(float(log_Z), -20.0)                # :135,173
+
+
+class _StochasticTensor(object):
+    def __init__(self, tensor=None, log_prob=None, distribution=None):
+        self.tensor, self._log_prob, self.distribution = tensor, log_prob, distribution
+
+    def log_prob(self, group_ndims=None):
+        return self._log_prob() if callable(self._log_prob) else self._log_prob
+
+
+class _Distribution(object):
+    def __init__(self, mean=None, sample=None):
+        self.mean = mean
+        self._sample = sample
+
+    def sample(self, n_samples=None):
+        return self._sample(n_samples)
+
+
+class _Evaluation(object):
+    def __init__(self, lazy):
+        self._lazy = lazy
+
+    def is_loglikelihood(self):
+        """variational/evaluation.py:9-39 on log_joint = log p(x|z) + log p_N(z), latent log q(z|x)."""
+        return self._lazy.get()['ele_test_ll']
+
+    importance_sampling_log_likelihood = is_loglikelihood
+
+
+class _LowerBound(object):
+    def __init__(self, lazy):
+        self._lazy = lazy
+
+    def elbo(self):
+        """variational/objectives.py:9-42, averaged over the sample axis as the scripts do (:899)."""
+        return self._lazy.get()['ele_test_lb']
+
+
+class _VI(object):
+    def __init__(self, lazy):
+        self.evaluation = _Evaluation(lazy)
+        self.lower_bound = _LowerBound(lazy)
+
+
+class Chain(object):
+    """q_net(...).chain(p_net, ...) (bayes.py:347-417, variational/chain.py:25-68)."""
+
+    def __init__(self, script, lazy):
+        m = script.model
+        self.vi = _VI(lazy)
+        g = lazy.get
+
+        def z_log_prob():
+            o = g()
+            return _LogProb(o['log_pn'], o['d_g'], script.w_xi(), m.log_Z, m.config.z_dim)
+        self.model = {
+            'x': _StochasticTensor(log_prob=lambda: g()['log_px']),
+            'z': _StochasticTensor(log_prob=z_log_prob),
+        }
+        self.variational = {'z': _StochasticTensor(log_prob=lambda: g()['log_q'])}
+        self._lazy = lazy
+
+    # the adversarial-prior estimators the scripts assemble by hand (:901-911)
+    def adv_is_loglikelihood(self):
+        return self._lazy.get()['ele_adv_test_ll']
+
+    def adv_elbo(self):
+        return self._lazy.get()['ele_adv_test_lb']
+
+
+class QNet(object):
+    """BayesianNet returned by q_net (dmm_cifar10.py:418-452)."""
+
+    def __init__(self, script, x, n_z, eps, seed):
+        if n_z is None or int(n_z) < 1:
+            raise ValueError('`n_z` (the number of latent samples) must be a positive integer')
+        self._script, self._x, self.n_z, self._eps, self._seed = script, x, int(n_z), eps, seed
+        self._z = None
+
+    def _draw(self):
+        if self._z is None:
+            self._z = self._script.model.sample_z(self._x, self.n_z, eps=self._eps, seed=self._seed)
+        return self._z
+
+    def __getitem__(self, name):
+        if name != 'z':
+            raise KeyError(name)
+        return _StochasticTensor(tensor=self._draw()[0], log_prob=lambda: self._draw()[1])
+
+    def chain(self, model_builder, latent_axis=0, observed=None, n_z=None, beta=None, log_Z=None, **kw):
+        if latent_axis not in (0, None):
+            raise ValueError('only latent_axis=0 (sample axis first) is used by the scripts')
+        if not observed or 'x' not in observed:
+            raise ValueError("chain() needs observed={'x': ...}")
+        K = self.n_z if n_z is None else int(n_z)
+        lazy = _Lazy(self._script.model, observed['x'], self._x, K, self._eps, self._seed, beta, log_Z)
+        return Chain(self._script, lazy)
+
+
+class PNet(object):
+    """BayesianNet returned by p_net (dmm_cifar10.py:596-620)."""
+
+    def __init__(self, script, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed):
+        self._script, self._z = script, z
+        m = script.model
+        if z is None:
+            if initial_z is None:
+                raise ValueError('p_net without observed z needs initial_z (the reference feeds G_omega samples)')
+            steps = int(mcmc_iterator)
+            out = m.mala(initial_z, steps, alpha=mcmc_alpha, seed=seed) if steps > 0 else {'z': m._f32(initial_z)}
+            self._z = out['z']
+            self.history = out
+        self._xm = None
+
+    def __getitem__(self, name):
+        m = self._script.model
+        if name == 'z':
+            return _StochasticTensor(tensor=self._z)
+        if name == 'x':
+            if self._xm is None:
+                self._xm = m.decode(self._z)
+            return _StochasticTensor(tensor=None, distribution=_Distribution(mean=self._xm))
+        raise KeyError(name)
+
+
+class Script(object):
+    """Namespace of one experiment script bound to a Model: q_net / p_net / G_theta / D_psi."""
+
+    def __init__(self, model):
+        self.model = model
+        self.config = model.config
+
+    def w_xi(self):
+        return self.config.pull_back_energy_weight / (1.0 + math.exp(-self.model.xi_raw))
+
+    def q_net(self, x, posterior_flow=None, observed=None, n_z=None, eps=None, seed=0):
+        if posterior_flow is not None:
+            raise NotImplementedError('posterior flows (use_flow=True) are outside the built path')
+        return QNet(self, x, n_z, eps, seed)
+
+    def p_net(self, observed=None, n_z=None, beta=1.0, mcmc_iterator=0, log_Z=0.0, initial_z=None, mcmc_alpha=None,
+              seed=0):
+        z = None if not observed else observed.get('z')
+        return PNet(self, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed)
+
+    def G_theta(self, z, return_std=False):
+        return self.model.decode(z, return_std=return_std)
+
+    def D_psi(self, x, y=None):
+        return self.model.energy_of_images(x)

@@ -191,6 +191,16 @@ class Model(object):
         check(lib.apvae_energy(self._h, None, _ptr(z2), z2.shape[0], _ptr(out), _stream()), self._h)
         return out.reshape(lead)
 
+    def sample_z(self, x_origin, K, eps=None, seed=0):
+        """q_net(x, n_z=K)['z'] (dmm_cifar10.py:418-452): returns (z [K,B,d], log q(z|x) [K,B], log N(z) [K,B])."""
+        x = self._f32(x_origin)
+        B = x.shape[0]
+        e = self._f32(eps, (K, B, self.config.z_dim)) if eps is not None else None
+        z, lq, lpn = self._empty(K, B, self.config.z_dim), self._empty(K, B), self._empty(K, B)
+        check(lib.apvae_sample_z(self._h, _ptr(x), B, int(K), _ptr(e), int(seed), _ptr(z), _ptr(lq), _ptr(lpn),
+                                 _stream()), self._h)
+        return z, lq, lpn
+
     # ------------------------------------------------------------------ estimator
     def is_nll(self, x, K, x_origin=None, eps=None, seed=0, per_sample=False):
         """The test graph of one mini-batch (dmm_cifar10.py:880-927).  Returns a dict of

@@ -261,6 +261,27 @@ int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev,
     return APVAE_OK;
 }
 
+int apvae_sample_z(apvae_handle* h, const float* x_origin_dev, int B, int K, const float* eps_dev, uint64_t seed,
+                   float* z_dev, float* log_q_dev, float* log_pn_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (B <= 0 || K <= 0 || !x_origin_dev || !z_dev) { m.err = "sample_z: empty batch"; return APVAE_ERR_INVALID; }
+    if (B > m.cfg.max_batch) { m.err = "sample_z: batch exceeds max_batch"; return APVAE_ERR_INVALID; }
+    const long long S = (long long)K * B;
+    const int d = m.cfg.z_dim;
+    if (!m.run_encoder(x_origin_dev, B, stream)) return APVAE_ERR_CUDA;
+    const float* eps = eps_dev;
+    if (!eps) {
+        if (!m.ensure_sample_buffers((size_t)S)) return APVAE_ERR_CUDA;
+        LCHECK(launch_fill_normal(m.eps_buf, S * d, seed, 0, m.cfg.use_truncated, stream), "fill_normal");
+        eps = m.eps_buf;
+    }
+    float* lq = log_q_dev;
+    if (!lq) { if (!m.ensure_sample_buffers((size_t)S)) return APVAE_ERR_CUDA; lq = m.log_q; }
+    LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps, (int)S, 0, B, d, m.cfg.min_logstd_of_q, m.cfg.use_truncated, z_dev,
+                           nullptr, nullptr, 0, 1, 0, 0.2f, lq, log_pn_dev, stream), "sample_z");
+    return APVAE_OK;
+}
+
 int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, int B, int K, double* accum_dev, void* stream) {
     REQUIRE_BUILT(h);
     static_assert(APVAE_ACCUM_SLOTS == kAccumSlots, "accumulator layouts out of sync");

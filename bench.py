@@ -232,6 +232,7 @@ def main():
     accum = torch.zeros(_lib.ACCUM_SLOTS, dtype=torch.float64, device=model.device)
     for i in range(W):
         ev.run_shard(x_dev[i * B:(i + 1) * B], accum=accum.clone())
+        combine_accumulators(accum.clone())                      # warm-up of the collective path too (NCCL lazy init)
     barrier()
     launches0 = model.launch_count()
     sampler = ClockSampler(local)
@@ -328,8 +329,8 @@ def main():
         'e2e': {'value': e2e_value, 'unit': UNIT, 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h},
         'gpu_launches': int(launches),
         'roofline': roofline,
-        'step_tensor': {'algorithmic_tflops_per_gpu': round(step_tflops / world, 1),
-                        'frac_of_sustained_peak': round(step_tflops / world / peaks['bf16_tflops_sustained'], 4),
+        'step_tensor': {'algorithmic_tflops_per_gpu': round(step_tflops, 1),      # flops_per_step is per rank
+                        'frac_of_sustained_peak': round(step_tflops / peaks['bf16_tflops_sustained'], 4),
                         'gflop_per_image': round(flops_per_step / B / 1e9, 1)},
         'cpu_baseline': cpu,
         'nll': {k: metrics.get(k) for k in ('test_nll', 'adv_test_nll')},

@@ -116,6 +116,11 @@ enum { APVAE_SROW_LOG_PX = 0, APVAE_SROW_LOG_Q = 1, APVAE_SROW_LOG_PN = 2, APVAE
 int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev, int B, int K,
                  const float* eps_dev, uint64_t seed, float* per_image_dev, float* per_sample_dev, void* stream);
 
+/* q_net(x, n_z=K)['z'] and its log-densities (dmm_cifar10.py:418-452): z = mu + exp(logstd) * eps, [K,B,z_dim];
+ * log q(z|x) and log N(z;0,I), [K,B] each (either may be NULL).  eps_dev NULL: Philox draw with `seed`. */
+int apvae_sample_z(apvae_handle* h, const float* x_origin_dev, int B, int K, const float* eps_dev, uint64_t seed,
+                   float* z_dev, float* log_q_dev, float* log_pn_dev, void* stream);
+
 /* Shard-local metric accumulation, replacing Evaluator.run's host np.average (trainer/evaluator.py:249-254)
  * and the host logsumexp of the log-Z loop (dmm_cifar10.py:1215-1227).  accum_dev: double[APVAE_ACCUM_SLOTS],
  * zero-initialised by the caller.  Slots 0-5, 8: sums over images of the per-image rows; slots 6, 7: running

@@ -357,3 +357,42 @@ def test_precise_mala_at_the_reference_energy_weight(case):
     assert np.abs(ge - np.stack(he).reshape(steps, n)).max() < 500 * PRECISE_ATOL + 1e-5 * np.abs(np.stack(he)).max()
     assert np.abs(gr - np.stack(hr).reshape(steps, n)).max() < 0.25, (gr, np.stack(hr).reshape(steps, n))
     m.close()
+
+
+# ----------------------------------------------------------------------------- the scripts' call surface
+def test_script_call_surface_reads_like_the_reference():
+    """apvae.dmm.Script: the test section of dmm_cifar10.py (:880-927) written with the reference's own names
+    (q_net(...).chain(p_net, ...).vi.evaluation.is_loglikelihood(), .model['x'].log_prob(),
+    .model['z'].log_prob().energy ...), checked against the oracle's eval_batch."""
+    from apvae.dmm import Script
+    arch, kw, B, K = CASES['A128']
+    ocfg, params, cfg, m = _make(arch, kw)
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    xi_raw, beta, log_Z = 0.3, -0.5, 2.5
+    m.set_scalars(xi_raw, beta, log_Z)
+    want = O.eval_batch(ocfg, params, x, x_origin, eps, xi_raw=xi_raw, beta=beta, log_Z=log_Z)
+    s = Script(m)
+    q_net, p_net = s.q_net, s.p_net
+    test_q_net = q_net(x_origin, n_z=K, eps=eps)
+    test_chain = test_q_net.chain(p_net, latent_axis=0, observed={'x': x}, n_z=K, beta=beta, log_Z=log_Z)
+    npf = lambda t: t.cpu().numpy().astype(np.float64)
+    z = npf(test_q_net['z'].tensor)
+    assert z.shape == (K, B, ocfg.z_dim) and np.abs(z - want['z']).max() < 3e-2 * max(1.0, np.abs(want['z']).max())
+    ll = npf(test_chain.vi.evaluation.is_loglikelihood())
+    assert (np.abs(ll - want['ele_test_ll']) / np.abs(want['ele_test_ll'])).max() < NLL_RTOL
+    lb = npf(test_chain.vi.lower_bound.elbo())
+    assert (np.abs(lb - want['ele_test_lb']) / np.abs(want['ele_test_lb'])).max() < NLL_RTOL
+    recon = npf(test_chain.model['x'].log_prob())
+    assert np.abs(recon - want['log_px']).max() < NLL_RTOL * np.abs(want['log_px']).max()
+    lp = test_chain.model['z'].log_prob()
+    w_xi = ocfg.pull_back_energy_weight * O.sigmoid(xi_raw)
+    assert np.abs(npf(lp.energy) - want['energy']).max() < w_xi * ENERGY_MAX_ATOL + 1e-3 * np.abs(want['energy']).max()
+    _energy_close(npf(lp.pure_energy), want['d_g'])
+    adv = npf(test_chain.adv_is_loglikelihood())
+    assert (np.abs(adv - want['ele_adv_test_ll']) / np.abs(want['ele_adv_test_ll'])).max() < NLL_RTOL
+    _energy_close(npf(s.D_psi(x_origin)), want['ele_real_energy'])
+    xm = npf(s.G_theta(want['z'][0]))
+    assert np.abs(xm - want['x_mean'][0]).max() < 6e-2
+    with pytest.raises(ValueError):
+        q_net(x_origin, n_z=None)
+    m.close()
