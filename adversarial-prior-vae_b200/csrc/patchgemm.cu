@@ -11,6 +11,7 @@
 // Rings: patches (full/empty), weight tiles (full/empty; empty collects one arrival per cluster CTA
 // through tcgen05.commit multicast), and a 2-deep TMEM accumulator ring.
 #include <cuda_runtime.h>
+#include <type_traits>
 #include <string.h>
 #include "patchgemm.h"
 #include "sm100_ptx.cuh"
@@ -30,7 +31,7 @@ constexpr int kMaxStages = 12;
 
 }  // namespace
 
-template <int KC>
+template <int KC, bool kTwo>
 __global__ void __launch_bounds__(kThreads, 1)
 patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -54,6 +55,9 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     const int csize = p.cluster;
     const uint32_t rank = csize > 1 ? cluster_ctarank() : 0u;
     const uint16_t cmask = (uint16_t)((1u << csize) - 1u);
+    constexpr bool two = kTwo;                  // CTA pair: one cta_group::2 MMA per pair, issued by rank 0 (its own
+                                                // instantiation: a kernel containing cta_group::2 code cannot be launched
+                                                // without a cluster of 2)
 
     if (warp == 0 && elect_one_sync()) {
         prefetch_tmap(&p.tm_a[0]);
@@ -62,12 +66,12 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     }
     if (warp == 1 && elect_one_sync()) {
         for (int s = 0; s < p.a_stages; ++s) { mbar_init(fullA(s), 1); mbar_init(emptyA(s), 1); }
-        for (int s = 0; s < p.b_stages; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), csize); }
-        for (int a = 0; a < kAccStages; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), 4); }
+        for (int s = 0; s < p.b_stages; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), two ? 1 : csize); }
+        for (int a = 0; a < kAccStages; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), two ? 8 : 4); }
         for (int q = 0; q < 4; ++q) { mbar_init(resbar(q, 0), 1); mbar_init(resbar(q, 1), 1); }
         fence_barrier_init();
     }
-    if (warp == 2) tmem_alloc(tmem_ptr_smem, kTmemCols);
+    if (warp == 2) { if constexpr (two) tmem_alloc_2cta(tmem_ptr_smem, kTmemCols); else tmem_alloc(tmem_ptr_smem, kTmemCols); }
     tc_fence_before();
     __syncthreads();
     if (csize > 1) cluster_sync_all();      // peers' barriers are initialised before any multicast
@@ -96,9 +100,16 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                     const PatchGroup gr = p.groups[gi];
                     mbar_wait(emptyA(sa), pa ^ 1);
                     if (elect_one_sync()) {
-                        mbar_expect_tx(fullA(sa), (uint32_t)gr.prow * p.W * row_bytes);
-                        tma_load_5d(a_base + sa * p.a_slot_bytes, &p.tm_a[gr.src], fullA(sa), gr.c0, gr.dx, 0,
-                                    y0 + gr.py0, n);
+                        const uint32_t bytes = (uint32_t)gr.prow * p.W * row_bytes;
+                        if constexpr (!two) {
+                            mbar_expect_tx(fullA(sa), bytes);
+                            tma_load_5d(a_base + sa * p.a_slot_bytes, &p.tm_a[gr.src], fullA(sa), gr.c0, gr.dx, 0,
+                                        y0 + gr.py0, n);
+                        } else {                                 // both patches of the pair complete on the leader's barrier
+                            if (rank == 0) mbar_expect_tx(fullA(sa), 2 * bytes);
+                            tma_load_5d_2cta(a_base + sa * p.a_slot_bytes, &p.tm_a[gr.src], mapa_shared(fullA(sa), 0),
+                                             gr.c0, gr.dx, 0, y0 + gr.py0, n);
+                        }
                     }
                     __syncwarp();
                     if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
@@ -112,6 +123,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             uint32_t pb = 0;
             const int slice_rows = p.NT / csize;
             const uint32_t slice_bytes = (uint32_t)slice_rows * row_bytes;
+            // pair mode: each CTA keeps only ITS half of every weight tile (at the same offset in both CTAs)
+            const uint32_t tap_b = two ? p.tap_bytes / 2 : p.tap_bytes;
             for (int g = cluster_id; g < rounds_total; g += num_clusters) {
                 int tap0 = 0;                                    // global tap index = row block of the packed weights
                 for (int gi = 0; gi < p.num_groups; ++gi) {
@@ -120,12 +133,17 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                         const int nt = min(p.tpi, k - j0);       // taps in this item
                         mbar_wait(emptyB(sb), pb ^ 1);           // every CTA of the cluster released this slot
                         if (elect_one_sync()) {
-                            mbar_expect_tx(fullB(sb), (uint32_t)nt * p.tap_bytes);
+                            if (!two || rank == 0) mbar_expect_tx(fullB(sb), (uint32_t)nt * p.tap_bytes);
+                            const uint32_t bar = two ? mapa_shared(fullB(sb), 0) : fullB(sb);
                             for (int t = 0; t < nt; ++t) {
-                                const uint32_t dst = b_base + sb * p.b_slot_bytes + t * p.tap_bytes + rank * slice_bytes;
                                 const int row0 = (tap0 + j0 + t) * p.Npad + (int)rank * slice_rows;
-                                if (csize > 1) tma_load_2d_mc(dst, &p.tm_b, fullB(sb), 0, row0, cmask);
-                                else tma_load_2d(dst, &p.tm_b, fullB(sb), 0, row0);
+                                if constexpr (two) {
+                                    tma_load_2d_2cta(b_base + sb * p.b_slot_bytes + t * tap_b, &p.tm_b, bar, 0, row0);
+                                } else {
+                                    const uint32_t dst = b_base + sb * p.b_slot_bytes + t * p.tap_bytes + rank * slice_bytes;
+                                    if (csize > 1) tma_load_2d_mc(dst, &p.tm_b, bar, 0, row0, cmask);
+                                    else tma_load_2d(dst, &p.tm_b, bar, 0, row0);
+                                }
                             }
                         }
                         __syncwarp();
@@ -135,9 +153,16 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 && (!two || rank == 0)) {
         // ===================== MMA issuer (whole warp runs the loops, one lane issues) =====================
-        const uint32_t idesc = make_idesc_bf16(kTileM, p.NT);
+        const uint32_t idesc = make_idesc_bf16(two ? 2 * kTileM : kTileM, p.NT);
+        // loop invariants in registers (kernel parameters would be re-read from the constant bank after every
+        // barrier wait); descriptors advance by plain adds: the low 14 bits hold (smem address >> 4)
+        const int macc = p.macc, tpi = p.tpi, num_groups = p.num_groups, a_stages = p.a_stages, b_stages = p.b_stages;
+        const uint32_t NT = (uint32_t)p.NT, a_slot = p.a_slot_bytes, b_slot = p.b_slot_bytes;
+        const uint64_t a_tap_step = (uint64_t)(((uint32_t)p.W * row_bytes) >> 4);     // one image row of the patch
+        const uint64_t a_m_step = (uint64_t)((kTileM * row_bytes) >> 4);               // next 128-pixel accumulator
+        const uint64_t b_tap_step = (uint64_t)((two ? p.tap_bytes / 2 : p.tap_bytes) >> 4);
         int sa = 0, sb = 0, acc = 0;
         uint32_t pa = 0, pb = 0, acc_phase = 0;
         for (int g = cluster_id; g < rounds_total; g += num_clusters) {
@@ -145,40 +170,54 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             tc_fence_after();
             const uint32_t tmem_d = tmem_base + acc * kAccColStride;
             uint32_t accumulate = 0;
-            for (int gi = 0; gi < p.num_groups; ++gi) {
+            for (int gi = 0; gi < num_groups; ++gi) {
                 const int k = p.groups[gi].k;
                 if (!skipA) mbar_wait(fullA(sa), pa);
-                const uint32_t a_src = a_base + sa * p.a_slot_bytes;
-                for (int j0 = 0; j0 < k; j0 += p.tpi) {
-                    const int nt = min(p.tpi, k - j0);
+                uint64_t da_row = make_kmajor_desc<KC>(a_base + sa * a_slot);          // vertical tap 0
+                for (int j0 = 0; j0 < k; j0 += tpi) {
+                    const int nt = min(tpi, k - j0);
                     if (!skipB) mbar_wait(fullB(sb), pb);
                     tc_fence_after();
-                    const uint32_t b_src = b_base + sb * p.b_slot_bytes;
+                    const uint64_t db0 = make_kmajor_desc<KC>(b_base + sb * b_slot);
                     if (elect_one_sync()) {
-                        for (int t = 0; t < nt; ++t) {
-                            const uint64_t db = make_kmajor_desc<KC>(b_src + t * p.tap_bytes);
-                            for (int m = 0; m < p.macc; ++m) {
-                                // tap j reads the patch advanced by j image rows; accumulator m by 128 pixels
-                                const uint64_t da = make_kmajor_desc<KC>(a_src + (uint32_t)((j0 + t) * p.W + m * kTileM) * row_bytes);
+                        // tap j reads the patch advanced by j image rows; accumulator m by 128 pixels
+                        auto issue = [&](auto macc_c) {
+                            constexpr int M = decltype(macc_c)::value;
+                            uint64_t da_t = da_row, db = db0;
+                            for (int t = 0; t < nt; ++t) {
 #pragma unroll
-                                for (int kk = 0; kk < KC / 16; ++kk)
-                                    umma_bf16(tmem_d + m * p.NT, da + 2 * kk, db + 2 * kk, idesc, (kk == 0) ? accumulate : 1u);
+                                for (int m = 0; m < M; ++m) {
+#pragma unroll
+                                    for (int kk = 0; kk < KC / 16; ++kk) {
+                                        if constexpr (two) umma_bf16_2cta(tmem_d + m * NT, da_t + m * a_m_step + 2 * kk, db + 2 * kk, idesc,
+                                                                (kk == 0) ? accumulate : 1u);
+                                        else umma_bf16(tmem_d + m * NT, da_t + m * a_m_step + 2 * kk, db + 2 * kk, idesc,
+                                                       (kk == 0) ? accumulate : 1u);
+                                    }
+                                }
+                                accumulate = 1;
+                                da_t += a_tap_step;
+                                db += b_tap_step;
                             }
-                            accumulate = 1;
-                        }
+                        };
+                        if (macc == 1) issue(std::integral_constant<int, 1>{});
+                        else if (macc == 2) issue(std::integral_constant<int, 2>{});
+                        else issue(std::integral_constant<int, 4>{});
                         if (skipB) {}
+                        else if constexpr (two) umma_commit_2cta(emptyB(sb), cmask);
                         else if (csize > 1) umma_commit_mc(emptyB(sb), cmask);
                         else umma_commit(emptyB(sb));
                     }
                     __syncwarp();
                     accumulate = 1;
-                    if (++sb == p.b_stages) { sb = 0; pb ^= 1; }
+                    da_row += (uint64_t)nt * a_tap_step;
+                    if (++sb == b_stages) { sb = 0; pb ^= 1; }
                 }
-                if (!skipA && elect_one_sync()) umma_commit(emptyA(sa));
+                if (!skipA && elect_one_sync()) { if constexpr (two) umma_commit_2cta(emptyA(sa), cmask); else umma_commit(emptyA(sa)); }
                 __syncwarp();
-                if (++sa == p.a_stages) { sa = 0; pa ^= 1; }
+                if (++sa == a_stages) { sa = 0; pa ^= 1; }
             }
-            if (elect_one_sync()) umma_commit(tfull(acc));
+            if (elect_one_sync()) { if constexpr (two) umma_commit_2cta(tfull(acc), cmask); else umma_commit(tfull(acc)); }
             __syncwarp();
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
@@ -330,7 +369,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty(acc));
+            if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
         if (leader) tma_store_wait_all();
@@ -380,7 +419,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty(acc));
+            if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
     }
@@ -388,7 +427,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     tc_fence_before();
     __syncthreads();
     if (csize > 1) cluster_sync_all();      // no CTA exits while a peer may still multicast into it
-    if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+    if (warp == 2) { if constexpr (two) tmem_dealloc_2cta(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols); }
 }
 
 uint32_t patchgemm_smem_bytes(const PatchGemmParams& p) {
@@ -404,10 +443,12 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     const uint32_t smem = patchgemm_smem_bytes(p);
     if (smem > kSmemBudget) return (int)cudaErrorInvalidValue;
     void (*kern)(PatchGemmParams) = nullptr;
+    const bool two = p.two_cta != 0;
+    if (two && c != 2) return (int)cudaErrorInvalidValue;
     switch (p.kc) {
-        case 16: kern = patchgemm_kernel<16>; break;
-        case 32: kern = patchgemm_kernel<32>; break;
-        case 64: kern = patchgemm_kernel<64>; break;
+        case 16: kern = two ? patchgemm_kernel<16, true> : patchgemm_kernel<16, false>; break;
+        case 32: kern = two ? patchgemm_kernel<32, true> : patchgemm_kernel<32, false>; break;
+        case 64: kern = two ? patchgemm_kernel<64, true> : patchgemm_kernel<64, false>; break;
         default: return (int)cudaErrorInvalidValue;
     }
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -427,8 +468,8 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     // one persistent cluster per co-resident slot (GPC boundaries can leave a few SMs without a full cluster)
     int max_clusters = num_sms / c;
     if (c > 1) {
-        static int cached[3][5] = {{0}};                     // [kc index][cluster] -> max active clusters
-        const int ki = p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2;
+        static int cached[6][5] = {{0}};                     // [kc index, pair mode][cluster] -> max active clusters
+        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0);
         if (cached[ki][c] == 0) {
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki][c] = nc;

@@ -58,6 +58,7 @@ struct alignas(64) PatchGemmParams {
     int a_stages, b_stages;
     uint32_t a_slot_bytes, b_slot_bytes;
     int cluster;                     // 1, 2 or 4 CTAs sharing the weight stream
+    int two_cta;                     // 1 (cluster == 2): cta_group::2 MMAs, each CTA holds half of every weight tile
     int fast_epi;                    // 1: TMA epilogue through tm_raw / tm_act / tm_res
     int res_rows;                    // rows of the residual box (32; 16 or 8 for RES_EVEN)
     CUtensorMap tm_raw, tm_act;      // 2-D (Npad, pixels), box (64, 32), SWIZZLE_128B

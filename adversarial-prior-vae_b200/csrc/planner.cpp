@@ -240,7 +240,14 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
     int tpi_want = std::max(1, std::min(kmax, (int)(32768u / P.tap_bytes)));
     if (const char* e = getenv("APVAE_PATCH_TPI")) { const int v = atoi(e); if (v >= 1 && v <= kmax) tpi_want = v; }
-    auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * P.tap_bytes + 1023u) & ~1023u; };
+    // CTA pairs (cta_group::2): APVAE_PATCH_2CTA=1/0 overrides the default
+    // Measured on B200 (1000 samples): 96->96 5x5 @32^2 1121 -> 1436 TFLOP/s, 192->192 3x3 @16^2 1073 -> 1214, but
+    // 96->96 3x3 @32^2 859 -> 819: the pair's cross-CTA barrier round trips need enough K per tile to pay off.
+    int two = ((long long)kmax * kmax * cp >= 1500) ? 1 : 0;
+    if (const char* e = getenv("APVAE_PATCH_2CTA")) two = atoi(e) != 0;
+    if (force_cluster && force_cluster != 2) two = 0;
+    P.two_cta = two;
+    auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * (P.tap_bytes / (two ? 2 : 1)) + 1023u) & ~1023u; };
     auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * W * P.kc * 2 + 1023u) & ~1023u; };
     int macc = 0;
     for (int cand : {4, 2, 1}) {
@@ -272,7 +279,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // cluster: weight-stream multicast across 2 / 4 CTAs is available (force_cluster) but measured slower
     // than independent CTAs on B200 for every layer of the reference models (the weights live in L2 anyway
     // and the cluster-wide slot release adds a round trip), so the default is 1.
-    int c = 1;
+    int c = P.two_cta ? 2 : 1;
     if (force_cluster) {
         if (force_cluster != 1 && force_cluster != 2 && force_cluster != 4) return fail("patch: cluster must be 1, 2 or 4");
         if ((P.npad / force_cluster) % 8) return fail("patch: cout slice per cluster CTA must be a multiple of 8");

@@ -66,6 +66,7 @@ struct PatchPlan {
     int a_stages = 0, b_stages = 0;
     uint32_t a_slot_bytes = 0, b_slot_bytes = 0;
     int cluster = 1;
+    int two_cta = 0;               // cta_group::2 pairs (cluster == 2): each CTA stores half of every weight tile
     int capacity_n = 0;
     double macs_per_image = 0;
 };

@@ -133,6 +133,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.a_stages = plan.a_stages; p.b_stages = plan.b_stages;
     p.a_slot_bytes = plan.a_slot_bytes; p.b_slot_bytes = plan.b_slot_bytes;
     p.cluster = plan.cluster;
+    p.two_cta = (plan.two_cta && plan.cluster == 2) ? 1 : 0;
     { const char* dbg = getenv("APVAE_PATCH_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
     fill_epilogue(p.epi, epi, op->d_bias);
     // bf16-only epilogues (the conv blocks' interior layers) go through bulk tensor loads / stores

@@ -245,9 +245,10 @@ TMA_EPI_CASES = [
 ]
 
 
+@pytest.mark.parametrize('two_cta', [0, 1])
 @pytest.mark.parametrize('macc', [0, 1])
 @pytest.mark.parametrize('H,W,cin,cout,res,n_valid,cap', TMA_EPI_CASES)
-def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, monkeypatch):
+def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two_cta, monkeypatch):
     """bf16-only epilogue of the A-stationary kernel (bulk tensor loads of the residual, bulk tensor stores of
     out_raw / out_act): v = acc + bias (+ res on every / on even pixels); raw = bf16(v), act = bf16(lrelu(v));
     images >= n_valid stay untouched."""
@@ -255,6 +256,7 @@ def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, mon
     from apvae import _lib
     from apvae.plan import Plan, pad16
     monkeypatch.setenv('APVAE_PATCH', '1')
+    monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))     # cta_group::2 pairs: one 256-row MMA per two tiles
     if macc:
         monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
     rs = np.random.RandomState(H + cin + cout + len(res))

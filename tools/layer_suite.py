@@ -25,6 +25,11 @@ CASES = [
     ('patch96x3', {}, L96_3),
     ('tap96x3_even', {'APVAE_PATCH': '0'}, L96_3 + ['--res', 'even']),
     ('tap192s2', {}, L192_S2),
+    ('patch192_2cta', {'APVAE_PATCH_2CTA': '1'}, L192),
+    ('patch192_res_2cta', {'APVAE_PATCH_2CTA': '1'}, L192 + ['--res', 'same']),
+    ('patch96x5_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_5),
+    ('patch96x5_res_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_5 + ['--res', 'same']),
+    ('patch96x3_even_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_3 + ['--res', 'even']),
     ('patch192_c1', {'APVAE_PATCH_CLUSTER': '1'}, L192),
     ('patch192_c2', {'APVAE_PATCH_CLUSTER': '2'}, L192),
     ('patch96x5_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_5),
