@@ -99,6 +99,7 @@ _SYMBOLS = [
     ('apvae_prior_stats', C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     ('apvae_mala', C.c_int, [_P, _P, C.c_int, C.c_int, C.c_float, _P, _P, C.c_uint64, _P, _P, _P, _P]),
     ('apvae_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
+    ('apvae_image_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
     ('apvae_sample_images', C.c_int, [_P, _P, C.c_int, _P, _P]),
     ('apvae_fill_normal', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, C.c_int, _P]),
     ('apvae_fill_uniform', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, _P]),

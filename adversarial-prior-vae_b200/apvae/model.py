@@ -241,6 +241,15 @@ class Model(object):
         check(lib.apvae_energy_grad(self._h, _ptr(z2), n, _ptr(e), _ptr(g), _ptr(p), _stream()), self._h)
         return e.reshape(lead), g.reshape(lead + (self.config.z_dim,)), p.reshape(lead)
 
+    def image_energy_grad(self, x):
+        """(D_psi(x), ele_grad = dD/dx, ele_grad_norm = sum(ele_grad^2)) of evaluation/dmm_cifar.py:958-959."""
+        x = self._f32(x)
+        x4 = x.reshape((-1,) + tuple(self.config.x_shape))
+        n = x4.shape[0]
+        d, g, s = self._empty(n), self._empty(*x4.shape), self._empty(n)
+        check(lib.apvae_image_energy_grad(self._h, _ptr(x4), n, _ptr(d), _ptr(g), _ptr(s), _stream()), self._h)
+        return d, g.reshape(x.shape), s
+
     def mala(self, z0, steps, alpha=None, eps=None, u=None, seed=0, history=True):
         """EnergyDistribution.sample (dmm_cifar10.py:179-239): `steps` MALA iterations.
         z0 [n, z_dim] (or [n,1,z_dim]); eps [steps,n,z_dim], u [steps,n] optional fed-in noise."""

@@ -523,6 +523,13 @@ int apvae_energy_grad(apvae_handle* h, const float* z_dev, int n, float* energy_
     }
     return APVAE_OK;
 }
+int apvae_image_energy_grad(apvae_handle* h, const float* x_dev, int N, float* d_dev, float* grad_dev, float* grad_sqnorm_dev,
+                            void* stream) {
+    REQUIRE_BUILT(h);
+    if (!m.cfg.enable_grad) { m.err = "image_energy_grad: create the handle with enable_grad = 1"; return APVAE_ERR_STATE; }
+    if (N <= 0 || !x_dev) { m.err = "image_energy_grad: empty batch"; return APVAE_ERR_INVALID; }
+    return m.critic_grad_of_images(x_dev, N, d_dev, grad_dev, grad_sqnorm_dev, stream) ? APVAE_OK : APVAE_ERR_CUDA;
+}
 int apvae_mala(apvae_handle* h, float* z_io_dev, int n, int steps, float alpha, const float* eps_dev, const float* u_dev,
                uint64_t seed, float* hist_e_dev, float* hist_pure_e_dev, float* hist_ratio_dev, void* stream) {
     REQUIRE_BUILT(h);

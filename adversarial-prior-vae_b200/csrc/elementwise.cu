@@ -372,6 +372,22 @@ __global__ void tanh_backward_pack_kernel(const float* __restrict__ g, const flo
     }
 }
 
+// one block per row
+__global__ void row_sqnorm_kernel(const float* __restrict__ v, long long len, float* __restrict__ out) {
+    const float* p = v + (size_t)blockIdx.x * len;
+    float s = 0.f;
+    for (long long i = threadIdx.x; i < len; i += blockDim.x) { const float a = p[i]; s += a * a; }
+    s = warp_sum(s);
+    __shared__ float part[8];
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        float t = threadIdx.x < (blockDim.x >> 5) ? part[threadIdx.x] : 0.f;
+        t = warp_sum(t);
+        if (threadIdx.x == 0) out[blockIdx.x] = t;
+    }
+}
+
 __global__ void quantize_kernel(const float* __restrict__ head, int ld, long long pixels, int C,
                                 uint8_t* __restrict__ out) {
     const long long total = pixels * C;
@@ -530,6 +546,11 @@ int launch_tanh_backward_pack(const float* g, const float* head, int ld, long lo
     if (pixels <= 0) return 0;
     tanh_backward_pack_kernel<<<grid_for(pixels * cp, 256), 256, 0, st(stream)>>>(g, head, ld, pixels, C, cp,
                                                                                (__nv_bfloat16*)out_bf16);
+    return (int)cudaGetLastError();
+}
+int launch_row_sqnorm(const float* v, long long len, int rows, float* out, void* stream) {
+    if (rows <= 0) return 0;
+    row_sqnorm_kernel<<<rows, 256, 0, st(stream)>>>(v, len, out);
     return (int)cudaGetLastError();
 }
 int launch_quantize_images(const float* head, int ld, long long pixels, int C, uint8_t* out, void* stream) {

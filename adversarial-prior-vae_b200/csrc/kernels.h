@@ -83,6 +83,9 @@ int launch_energy_combine(const float* d_g, const float* gz, const float* z, int
 int launch_tanh_backward_pack(const float* g, const float* head, int ld, long long pixels, int C, int cp,
                               void* out_bf16, void* stream);
 
+// out[r] = sum_j v[r, j]^2 over `len` contiguous floats per row (ele_grad_norm, evaluation/dmm_cifar.py:958-959)
+int launch_row_sqnorm(const float* v, long long len, int rows, float* out, void* stream);
+
 // uint8 = round(clip(256 * x_mean / 2 + 127.5, 0, 255))   (dmm_cifar10.py:976-977,990,1067)
 int launch_quantize_images(const float* head, int ld, long long pixels, int C, uint8_t* out, void* stream);
 

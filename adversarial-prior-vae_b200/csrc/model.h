@@ -84,6 +84,8 @@ public:
     bool mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
               float* hist_e, float* hist_pure, float* hist_ratio, void* stream);
     bool critic_of_images(const float* x_dev, int N, float* d_out, void* stream);
+    // D_psi(x), dD/dx [N,H,W,C] and its squared norm per image (evaluation/dmm_cifar.py:958-959); outputs may be null
+    bool critic_grad_of_images(const float* x_dev, int N, float* d_out, float* grad_out, float* sqnorm_out, void* stream);
     bool ensure_sample_buffers(size_t samples);
 
     // geometry

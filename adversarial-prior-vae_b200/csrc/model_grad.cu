@@ -203,6 +203,23 @@ bool Model::energy_grad_chunk(const float* z_dev, int n, float* energy, float* g
     return true;
 }
 
+bool Model::critic_grad_of_images(const float* x_dev, int N, float* d_out, float* grad_out, float* sqnorm_out, void* stream) {
+    if (!cfg.enable_grad || gd_prog.empty()) return fail("this handle was created without enable_grad");
+    const size_t per = (size_t)HW() * C();
+    for (int s0 = 0; s0 < N; s0 += cfg.max_chunk) {
+        const int n = std::min(cfg.max_chunk, N - s0);
+        GCHECK(launch_pack_image(x_dev + (size_t)s0 * per, (long long)n * HW(), C(), d_in.raw.cp, d_in.raw.ptr, d_in.act.ptr,
+                                 0.2f, stream, d_in.raw_lo.ptr, d_in.act_lo.ptr), "pack_image");
+        if (!run_critic_chunk(n, d_out ? d_out + s0 : z_tmp, stream)) return false;
+        if (!run_program(gd_prog, n, stream)) return false;
+        if (grad_out && cudaMemcpyAsync(grad_out + (size_t)s0 * per, gx_f32, (size_t)n * per * sizeof(float),
+                                        cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)) != cudaSuccess)
+            return fail("copy of the image gradient failed");
+        if (sqnorm_out) GCHECK(launch_row_sqnorm(gx_f32, (long long)per, n, sqnorm_out + s0, stream), "row_sqnorm");
+    }
+    return true;
+}
+
 bool Model::mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
                  float* hist_e, float* hist_pure, float* hist_ratio, void* stream) {
     const int d = cfg.z_dim;

@@ -143,6 +143,11 @@ int apvae_mala(apvae_handle* h, float* z_io_dev, int n, int steps, float alpha, 
 /* energy, grad_z energy, pure energy at z (get_sgld_proposal :241-247). Any output may be NULL. */
 int apvae_energy_grad(apvae_handle* h, const float* z_dev, int n, float* energy_dev, float* grad_dev,
                       float* pure_dev, void* stream);
+/* Out-of-distribution indicators of the evaluation scripts (evaluation/dmm_cifar.py:958-959):
+ * D_psi(x) [N], ele_grad = d D_psi(x) / dx [N,H,W,C], ele_grad_norm = sum(ele_grad^2) [N].  Any output may be NULL.
+ * Requires enable_grad. */
+int apvae_image_energy_grad(apvae_handle* h, const float* x_dev, int N, float* d_dev, float* grad_dev,
+                            float* grad_sqnorm_dev, void* stream);
 /* x_plots (:976-977,990) + np.round: uint8 NHWC images from latents. */
 int apvae_sample_images(apvae_handle* h, const float* z_dev, int n, uint8_t* out_dev, void* stream);
 

@@ -396,3 +396,21 @@ def test_script_call_surface_reads_like_the_reference():
     with pytest.raises(ValueError):
         q_net(x_origin, n_z=None)
     m.close()
+
+
+@pytest.mark.parametrize('case', ['A128', 'M40'])
+def test_image_energy_gradient_ood_indicator(case):
+    """ele_grad = tf.gradients(D_psi(input_x), [input_x]); ele_grad_norm = sum(ele_grad^2)
+    (evaluation/dmm_cifar.py:958-959) through apvae_image_energy_grad."""
+    arch, kw, _ = GRAD_CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=3, enable_grad=True)
+    x, x_origin, _ = _inputs(ocfg, 5, 1)
+    d_o, g_o = O.D_psi_input_grad(ocfg, params, x_origin)
+    d, g, s = [t.cpu().numpy().astype(np.float64) for t in m.image_energy_grad(x_origin)]
+    _energy_close(d, d_o)
+    rel = np.sqrt(((g - g_o) ** 2).sum(axis=(1, 2, 3)) / (g_o ** 2).sum(axis=(1, 2, 3)))
+    assert rel.max() < 1e-1, rel                                   # bf16 operands through 12 conv layers and back
+    n_o = (g_o ** 2).sum(axis=(1, 2, 3))
+    assert np.abs(s - (g ** 2).sum(axis=(1, 2, 3))).max() < 1e-4 * n_o.max()      # the reduction itself
+    assert (np.abs(s - n_o) / n_o).max() < 2e-1, (s, n_o)
+    m.close()
