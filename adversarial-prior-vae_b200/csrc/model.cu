@@ -66,7 +66,7 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
         plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr) && pplan.npad <= patch_max_n) {
         if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");
         if (!devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
-        if (macs) *macs += pplan.macs_per_image;
+        if (macs) *macs += pplan.macs_per_image / (split_mode ? 3.0 : 1.0);
         prog.push_back(std::move(op));
         return true;
     }
@@ -74,7 +74,7 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     if (!plan_op(terms, cap, &plan, &perr)) return fail("plan " + name + ": " + perr);
     if ((int)srcs.size() != plan.nsrc) return fail("plan " + name + ": source count mismatch");
     if (!devop_create(dev, plan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
-    if (macs) *macs += plan.macs_per_image;
+    if (macs) *macs += plan.macs_per_image / (split_mode ? 3.0 : 1.0);   // split precision: 3 tensor-core terms per algorithmic product
     prog.push_back(std::move(op));
     return true;
 }

@@ -1,0 +1,55 @@
+"""BASELINE configs[3]: CelebA-shape (64x64x3, arch B = dmm_for_sampling.py) latent MALA sampling of the energy prior,
+100 steps x 1024 chains, then x = G_theta(z) -> uint8.  Prints one JSON line (chain-steps/s, algorithmic TFLOP/s).
+  python tools/bench_mala.py [--precise] [--chains 1024] [--steps 100] [--dataset celebA] [--arch B] [--chunk 512]
+Random-init weights, z0 ~ N(0, I) (stand-in for the G_omega latent GAN), in-kernel Philox noise."""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'adversarial-prior-vae_b200'))
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+from bench import synthetic_weights  # noqa: E402
+from apvae.model import ExpConfig, Model, weight_schema  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--arch', default='B')
+    ap.add_argument('--dataset', default='celebA')
+    ap.add_argument('--z-dim', type=int, default=128)
+    ap.add_argument('--chains', type=int, default=1024)
+    ap.add_argument('--steps', type=int, default=100)
+    ap.add_argument('--chunk', type=int, default=512)
+    ap.add_argument('--precise', action='store_true')
+    a = ap.parse_args()
+    cfg = ExpConfig(a.arch, dataset=a.dataset if a.arch == 'B' else None, z_dim=a.z_dim, max_batch=8, max_chunk=a.chunk,
+                    enable_grad=True, precise=a.precise)
+    m = Model(cfg, synthetic_weights(weight_schema(cfg)))
+    z0 = torch.from_numpy(np.random.RandomState(2).normal(size=(a.chains, cfg.z_dim)).astype(np.float32)).cuda()
+    m.mala(z0, 2, seed=1, history=False)                      # warm-up
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    out = m.mala(z0, a.steps, seed=7, history=True)
+    img = m.sample_images(out['z'])
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    _, mg, md = m.macs()
+    # algorithmic: one forward + one input-gradient backward of D o G per chain-step (backward ~ forward), SURVEY 8(d)
+    flops = 4.0 * (mg + md) * a.chains * a.steps
+    acc = float((out['history_ratio'] > 0.5).float().mean())
+    print(json.dumps({
+        'metric': 'MALA chain-steps/sec (%s %s, d=%d, %d chains x %d steps)' % (a.arch, a.dataset, cfg.z_dim, a.chains, a.steps),
+        'value': a.chains * a.steps / (ms / 1e3), 'unit': 'chain-steps/s', 'ms_total': ms,
+        'algorithmic_tflops': flops / (ms / 1e3) / 1e12, 'precise': bool(a.precise),
+        'mean_accept_ratio': float(out['history_ratio'].mean()), 'frac_ratio_gt_half': acc,
+        'images': list(img.shape), 'dtype': 'bf16x3 (split precision)' if a.precise else 'bf16'}))
+
+
+if __name__ == '__main__':
+    main()
