@@ -18,6 +18,7 @@ struct apvae_plan {
     OpPlan plan;
     bool has_patch = false;
     PatchPlan patch;
+    std::vector<PatchPlan> phases;   // stride-2 transposed conv: four sub-pixel phase plans (A-stationary kernel)
 };
 
 static int env_int(const char* name) {
@@ -403,6 +404,15 @@ int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, 
     if (patch_enabled()) {
         std::string pe;
         p->has_patch = plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->patch, &pe);
+        const char* eph = getenv("APVAE_PATCH_PHASES");
+        if (!p->has_patch && !(eph && eph[0] == '0') && ts.size() == 1 && ts[0].transpose && ts[0].stride == 2) {
+            p->phases.resize(4);
+            for (int ph = 0; ph < 4; ++ph)
+                if (!plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->phases[ph], &pe, ph)) {
+                    p->phases.clear();
+                    break;
+                }
+        }
     }
     *out = p;
     return APVAE_OK;
@@ -484,18 +494,39 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
     ep.out_f32 = epi->out_f32_dev; ep.ld_f32 = epi->ld_f32; ep.f32_cols = epi->f32_cols;
     ep.res = epi->res_dev; ep.res_mode = epi->res_mode; ep.ld_res = epi->ld_res;
     ep.mask = epi->mask_dev; ep.ld_mask = epi->ld_mask; ep.tanh_cols = epi->tanh_cols;
-    DevOp op;
-    op.name = "plan_run";
-    const bool use_patch = p->has_patch;
-    if (!(use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, &op, &e) : devop_create(dev, p->plan, src_dev, ep, &op, &e)))
-        return set_global_err(e, APVAE_ERR_CUDA);
-    int err = devop_launch(dev, op, n_valid, nullptr);
+    // the op, or the four phase ops of a stride-2 transposed conv (only with a bf16-only epilogue; else the tap-GEMM op)
+    std::vector<std::unique_ptr<DevOp>> ops;
+    bool phased = !p->phases.empty();
+    if (phased) {
+        for (int ph = 0; ph < 4 && phased; ++ph) {
+            std::unique_ptr<DevOp> o(new DevOp());
+            o->name = "plan_run/phase" + std::to_string(ph);
+            std::string e2;
+            phased = devop_create_patch(dev, p->phases[ph], src_dev, ep, o.get(), &e2);
+            if (phased) ops.push_back(std::move(o));
+        }
+        if (!phased) { ops.clear(); cudaGetLastError(); }
+    }
+    if (!phased) {
+        std::unique_ptr<DevOp> o(new DevOp());
+        o->name = "plan_run";
+        const bool use_patch = p->has_patch;
+        if (!(use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, o.get(), &e) : devop_create(dev, p->plan, src_dev, ep, o.get(), &e)))
+            return set_global_err(e, APVAE_ERR_CUDA);
+        ops.push_back(std::move(o));
+    }
+    auto devop_launch_all = [&](int n) {
+        int r = 0;
+        for (auto& o : ops) { r = devop_launch(dev, *o, n, nullptr); if (r != 0) break; }
+        return r;
+    };
+    int err = devop_launch_all(n_valid);
     if (err == 0 && reps > 0) {
         cudaEvent_t e0, e1;
         cudaEventCreate(&e0); cudaEventCreate(&e1);
-        err = devop_launch(dev, op, n_valid, nullptr);
+        err = devop_launch_all(n_valid);
         cudaEventRecord(e0, nullptr);
-        for (int i = 0; i < reps && err == 0; ++i) err = devop_launch(dev, op, n_valid, nullptr);
+        for (int i = 0; i < reps && err == 0; ++i) err = devop_launch_all(n_valid);
         cudaEventRecord(e1, nullptr);
         if (err == 0) err = (int)cudaEventSynchronize(e1);
         float ms = 0.f;

@@ -62,6 +62,29 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     const char* emax = getenv("APVAE_PATCH_MAXN");            // widest output the A-stationary kernel takes (tuning)
     const int patch_max_n = emax ? atoi(emax) : 256;
     const bool split_epi = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;     // split precision: tap-GEMM only
+    // stride-2 transposed conv: four sub-pixel phases, each an A-stationary stride-1 op on the input grid
+    const char* eph = getenv("APVAE_PATCH_PHASES");
+    if (!(env && env[0] == '0') && !(eph && eph[0] == '0') && !split_epi && terms.size() == 1 && terms[0].transpose &&
+        terms[0].stride == 2) {
+        std::vector<std::unique_ptr<DevOp>> ops;
+        double m = 0;
+        bool ok = true;
+        for (int ph = 0; ph < 4 && ok; ++ph) {
+            PatchPlan pp;
+            std::string e2;
+            std::unique_ptr<DevOp> o(new DevOp());
+            o->name = name + "/phase" + std::to_string(ph);
+            ok = plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pp, &e2, ph) && pp.npad <= patch_max_n &&
+                 devop_create_patch(dev, pp, srcs.data(), epi, o.get(), &e2);
+            if (ok) { m += pp.macs_per_image; ops.push_back(std::move(o)); }
+        }
+        if (ok) {
+            if (macs) *macs += m;
+            for (auto& o : ops) prog.push_back(std::move(o));
+            return true;
+        }
+        cudaGetLastError();
+    }
     if (!(env && env[0] == '0') && !split_epi &&
         plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr) && pplan.npad <= patch_max_n) {
         if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");

@@ -232,6 +232,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         const bool leader = elect_one_sync();              // the one thread that owns this warp's bulk-store groups
         const bool want_raw = p.epi.out_raw != nullptr, want_act = p.epi.out_act != nullptr;
         const int res_mode = p.epi.res_mode;
+        const bool dbl = (res_mode == RES_NONE);
+        uint32_t nblk = 0;
         const uint32_t res_bytes = (uint32_t)p.res_rows * 128u;
         const float alpha = p.epi.lrelu_alpha;
         const uint32_t sw = (uint32_t)(lane & 7);
@@ -294,6 +296,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                     const uint32_t taddr = tmem_base + acc * kAccColStride + m * p.NT + cb + ((uint32_t)(q * 32) << 16);
                     bool ok;
                     const int pix0 = seq_pix0(cur, ok);
+                    const int oy = pix0 / p.W, ox0 = pix0 - oy * p.W;      // first row of the warp on the input grid: (n*H + y, x0)
+                    const int on = oy / p.H, oyy = oy - on * p.H;
                     const bool has_res = kb ? iss1 : iss0;
                     const uint32_t rbuf = wbase + kb * kFastEpiBoxBytes;
                     uint32_t rr[32], aa[32];               // packed bf16 pairs: raw and activated, 64 columns
@@ -346,21 +350,26 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                         if (kb) iss1 = is; else iss0 = is;
                         pre = seq_next(pre);
                     }
-                    if (leader) tma_store_wait_read();     // the previous block's stores have left the staging boxes
+                    // staging boxes: without a residual the two residual boxes serve as a second (raw, act) pair, so only
+                    // the stores of the block before the previous one must have left shared memory
+                    const bool alt = dbl && (nblk & 1);
+                    const uint32_t rawb = alt ? wbase : rawbuf, actb = alt ? wbase + kFastEpiBoxBytes : actbuf;
+                    ++nblk;
+                    if (leader) { if (dbl) tma_store_wait_read1(); else tma_store_wait_read(); }
                     __syncwarp();
                     const int nch = bw >> 3;
 #pragma unroll
                     for (int ch = 0; ch < 8; ++ch) {
                         if (ch >= nch) break;
                         const uint32_t off = lane * 128 + (((uint32_t)ch ^ sw) << 4);
-                        if (want_raw) st_shared_v4(rawbuf + off, rr[ch * 4], rr[ch * 4 + 1], rr[ch * 4 + 2], rr[ch * 4 + 3]);
-                        if (want_act) st_shared_v4(actbuf + off, aa[ch * 4], aa[ch * 4 + 1], aa[ch * 4 + 2], aa[ch * 4 + 3]);
+                        if (want_raw) st_shared_v4(rawb + off, rr[ch * 4], rr[ch * 4 + 1], rr[ch * 4 + 2], rr[ch * 4 + 3]);
+                        if (want_act) st_shared_v4(actb + off, aa[ch * 4], aa[ch * 4 + 1], aa[ch * 4 + 2], aa[ch * 4 + 3]);
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (leader && ok && p.debug != 5 && p.debug != 15) {
-                        if (want_raw) tma_store_2d(&p.tm_raw, rawbuf, cb, pix0);
-                        if (want_act) tma_store_2d(&p.tm_act, actbuf, cb, pix0);
+                        if (want_raw) tma_store_4d(&p.tm_raw, rawb, cb, ox0, oyy, on);
+                        if (want_act) tma_store_4d(&p.tm_act, actb, cb, ox0, oyy, on);
                         tma_store_commit();
                     }
                     kb ^= 1;

@@ -61,7 +61,8 @@ struct alignas(64) PatchGemmParams {
     int two_cta;                     // 1 (cluster == 2): cta_group::2 MMAs, each CTA holds half of every weight tile
     int fast_epi;                    // 1: TMA epilogue through tm_raw / tm_act / tm_res
     int res_rows;                    // rows of the residual box (32; 16 or 8 for RES_EVEN)
-    CUtensorMap tm_raw, tm_act;      // 2-D (Npad, pixels), box (64, 32), SWIZZLE_128B
+    CUtensorMap tm_raw, tm_act;      // 4-D (Npad, W, H, N) over the output (strided by 2 for a sub-pixel phase),
+                                     // box (64, min(W, 32), 32 / min(W, 32), 1), SWIZZLE_128B
     CUtensorMap tm_res;              // 2-D (Npad, residual pixels), box (64, res_rows)
     int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
     EpilogueArgs epi;

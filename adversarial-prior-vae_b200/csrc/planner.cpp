@@ -207,7 +207,7 @@ bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, s
 // Patch (A-stationary) plan.  Source shift of a tap: conv2d (dj - pad_lo, di - pad_lo);
 // conv2d_transpose stride 1 (pad_lo - dj, pad_lo - di)  [SURVEY section 9].
 bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force_macc, int force_cluster,
-                   PatchPlan* plan, std::string* err) {
+                   PatchPlan* plan, std::string* err, int phase) {
     auto fail = [&](const char* m) { if (err) *err = m; return false; };
     if (terms.empty() || terms.size() > (size_t)kPatchMaxSrc) return fail("patch: 1..2 terms");
     PatchPlan& P = *plan;
@@ -218,7 +218,8 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     if (W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 16, 32, 64 or 128");
     for (size_t i = 0; i < terms.size(); ++i) {
         const TermSpec& t = terms[i];
-        if (t.stride != 1) return fail("patch: stride-1 terms only");
+        if (phase < 0 && t.stride != 1) return fail("patch: stride-1 terms only");
+        if (phase >= 0 && (terms.size() != 1 || !t.transpose || t.stride != 2)) return fail("patch: phases are for one stride-2 transposed term");
         if (!(t.k & 1)) return fail("patch: odd kernel sizes only");
         if (t.in_w != W || t.in_h != H) return fail("patch: terms disagree on the grid");
         if (t.in_cp != cp || cp % 16 || cp < t.cin) return fail("patch: bad channel padding");
@@ -235,6 +236,22 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
     int kmax = 1;
     for (const TermSpec& t : terms) kmax = std::max(kmax, t.k);
+    // a phase of a stride-2 transposed conv: taps = {dy} x {dx}, consecutive offsets on the input grid
+    std::vector<Tap> ph_taps;
+    int ph_dy0 = 0, ph_nv = 0, ph_dx0 = 0, ph_nh = 0;
+    if (phase >= 0) {
+        ph_taps = enumerate_taps(t0, phase >> 1, phase & 1);
+        if (ph_taps.empty()) return fail("patch: phase has no taps");
+        int dy1 = -1000, dx1 = -1000; ph_dy0 = 1000; ph_dx0 = 1000;
+        for (const Tap& tp : ph_taps) {
+            ph_dy0 = std::min(ph_dy0, tp.dy); dy1 = std::max(dy1, tp.dy);
+            ph_dx0 = std::min(ph_dx0, tp.dx); dx1 = std::max(dx1, tp.dx);
+        }
+        ph_nv = dy1 - ph_dy0 + 1; ph_nh = dx1 - ph_dx0 + 1;
+        if (ph_nv * ph_nh != (int)ph_taps.size()) return fail("patch: phase taps are not a product set");
+        kmax = ph_nv;
+        P.phase = phase; P.out_scale = 2;
+    }
     const uint32_t budget = 227u * 1024u - kPatchFixedSmem;
     P.tap_bytes = (uint32_t)P.npad * P.kc * 2;
     // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
@@ -243,7 +260,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // CTA pairs (cta_group::2): APVAE_PATCH_2CTA=1/0 overrides the default
     // Measured on B200 (1000 samples): 96->96 5x5 @32^2 1121 -> 1436 TFLOP/s, 192->192 3x3 @16^2 1073 -> 1214, but
     // 96->96 3x3 @32^2 859 -> 819: the pair's cross-CTA barrier round trips need enough K per tile to pay off.
-    int two = ((long long)kmax * kmax * cp >= 1500) ? 1 : 0;
+    int two = ((long long)(phase >= 0 ? ph_nv * ph_nh : kmax * kmax) * cp >= 1500) ? 1 : 0;
     if (const char* e = getenv("APVAE_PATCH_2CTA")) two = atoi(e) != 0;
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;
@@ -272,7 +289,9 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.b_stages = std::min(12, (kmax + P.tpi - 1) / P.tpi + 2);
     while (P.b_stages > 2 && 2 * P.a_slot_bytes + P.b_stages * P.b_slot_bytes > budget) --P.b_stages;
     P.a_stages = 2;
-    while (P.a_stages < 4 && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
+    int a_cap = 4;
+    if (const char* e = getenv("APVAE_PATCH_ACAP")) { const int v = atoi(e); if (v >= 2 && v <= 12) a_cap = v; }
+    while (P.a_stages < a_cap && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
     while (P.b_stages < 12 && P.a_stages * P.a_slot_bytes + (P.b_stages + 1) * P.b_slot_bytes <= budget) ++P.b_stages;
     if (const char* e = getenv("APVAE_PATCH_ASTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.a_stages) P.a_stages = v; }
     if (const char* e = getenv("APVAE_PATCH_BSTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.b_stages) P.b_stages = v; }
@@ -295,19 +314,28 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         int o, lo_h, lo_w, hi;
         same_padding(H, t.k, 1, &o, &lo_h, &hi);
         same_padding(W, t.k, 1, &o, &lo_w, &hi);
-        P.prow[t.src] = P.rows_tile + t.k - 1;
+        const int nv = phase >= 0 ? ph_nv : t.k, nh = phase >= 0 ? ph_nh : t.k;
+        const int dy0 = phase >= 0 ? ph_dy0 : -lo_h, dx0 = phase >= 0 ? ph_dx0 : -lo_w;
+        P.prow[t.src] = P.rows_tile + nv - 1;
         const int used_chunks = (t.cin + P.kc - 1) / P.kc;
         for (int c0 = 0; c0 < used_chunks; ++c0) {
-            for (int g = 0; g < t.k; ++g) {            // dx ascending: dx = g - lo_w
-                const int dx = g - lo_w;
+            for (int g = 0; g < nh; ++g) {             // dx ascending
+                const int dx = dx0 + g;
                 PatchGroup gr;
-                gr.src = (int16_t)t.src; gr.dx = (int16_t)dx; gr.py0 = (int16_t)(-lo_h); gr.k = (int16_t)t.k;
+                gr.src = (int16_t)t.src; gr.dx = (int16_t)dx; gr.py0 = (int16_t)dy0; gr.k = (int16_t)nv;
                 gr.c0 = c0 * P.kc; gr.prow = P.prow[t.src];
                 P.groups.push_back(gr);
-                for (int j = 0; j < t.k; ++j) {        // dy ascending: dy = j - lo_h
-                    const int dy = j - lo_h;
-                    const int dj = t.transpose ? lo_w - dx : dx + lo_w;
-                    const int di = t.transpose ? lo_h - dy : dy + lo_h;
+                for (int j = 0; j < nv; ++j) {         // dy ascending
+                    const int dy = dy0 + j;
+                    int di = -1, dj = -1;
+                    if (phase >= 0) {
+                        for (const Tap& tp : ph_taps)
+                            if (tp.dy == dy && tp.dx == dx) { di = tp.di; dj = tp.dj; }
+                        if (di < 0) return fail("patch: phase tap missing");
+                    } else {
+                        dj = t.transpose ? lo_w - dx : dx + lo_w;
+                        di = t.transpose ? lo_h - dy : dy + lo_h;
+                    }
                     const size_t base = P.wpack.size();
                     P.wpack.resize(base + (size_t)P.npad * P.kc, 0);
                     const size_t tap_off = (size_t)di * t.k + dj;
@@ -323,7 +351,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                 }
             }
         }
-        P.macs_per_image += (double)t.k * t.k * t.cin * t.cout * H * W;
+        P.macs_per_image += (double)nv * nh * t.cin * t.cout * H * W;
     }
     if ((int)P.groups.size() > kPatchMaxGroups) return fail("patch: too many groups");
     return true;

@@ -67,6 +67,10 @@ struct PatchPlan {
     uint32_t a_slot_bytes = 0, b_slot_bytes = 0;
     int cluster = 1;
     int two_cta = 0;               // cta_group::2 pairs (cluster == 2): each CTA stores half of every weight tile
+    // sub-pixel phase of a stride-2 transposed conv (-1: ordinary stride-1 op).  Phase (py, px) = (phase >> 1, phase & 1)
+    // is a stride-1 correlation over the INPUT grid whose results land on output pixels (2y + py, 2x + px).
+    int phase = -1;
+    int out_scale = 1;             // output grid = out_scale x input grid
     int capacity_n = 0;
     double macs_per_image = 0;
 };
@@ -87,7 +91,8 @@ bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, s
 // Returns false (with *err = reason) when the op is not eligible for the patch kernel:
 // every term must be stride 1 on the same W x H grid with W in {16,32,64,128}, <= 2 terms, cout <= 256.
 // force_macc / force_cluster: 0 = choose automatically.
+// `phase` >= 0: plan that sub-pixel phase of a single stride-2 transposed term (see PatchPlan::phase).
 bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force_macc, int force_cluster,
-                   PatchPlan* plan, std::string* err);
+                   PatchPlan* plan, std::string* err, int phase = -1);
 
 }  // namespace apvae

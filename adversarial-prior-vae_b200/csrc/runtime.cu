@@ -155,9 +155,27 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                 if (r != CUDA_SUCCESS) ok = false;
             };
+            // outputs: 4-D (C, W, H, N) view of the output tensor on the INPUT grid; a sub-pixel phase (py, px) of a stride-2
+            // transposed conv writes every second pixel of a 2H x 2W image starting at (py, px)
+            const int osc = plan.out_scale;
+            const int py = plan.phase >= 0 ? (plan.phase >> 1) : 0, px = plan.phase >= 0 ? (plan.phase & 1) : 0;
+            auto map_out = [&](CUtensorMap* tm, const void* ptr) {
+                const cuuint64_t ld = (cuuint64_t)epi.ldo * 2;                       // bytes per output pixel
+                const cuuint64_t Wo = (cuuint64_t)osc * W, Ho = (cuuint64_t)osc * H;
+                cuuint64_t dims[4] = {(cuuint64_t)plan.npad, W, H, (cuuint64_t)plan.capacity_n};
+                cuuint64_t strides[3] = {osc * ld, osc * Wo * ld, Ho * Wo * ld};
+                const cuuint32_t bx = (cuuint32_t)std::min<cuuint64_t>(W, 32);
+                cuuint32_t box[4] = {64, bx, 32 / bx, 1};
+                const cuuint32_t ones4[4] = {1, 1, 1, 1};
+                char* base = static_cast<char*>(const_cast<void*>(ptr)) + ((size_t)py * Wo + px) * ld;
+                const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, ones4,
+                                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) ok = false;
+            };
             const void* any_out = epi.out_raw ? epi.out_raw : epi.out_act;
-            map2d(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out, pixels, epi.ldo, 32);
-            map2d(&p.tm_act, epi.out_act ? epi.out_act : any_out, pixels, epi.ldo, 32);
+            map_out(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out);
+            map_out(&p.tm_act, epi.out_act ? epi.out_act : any_out);
             if (epi.res_mode == RES_EVEN) {
                 p.res_rows = (plan.w >= 32) ? 16 : 8;
                 map2d(&p.tm_res, epi.res, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
@@ -168,6 +186,10 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             }
             p.fast_epi = ok ? 1 : 0;
         }
+    }
+    if (plan.phase >= 0 && (!p.fast_epi || epi.res_mode != RES_NONE)) {
+        if (err) *err = "a sub-pixel phase op needs the bf16-only epilogue without residual (op " + op->name + ")";
+        return false;
     }
     op->is_patch = true;
     op->macs_per_image = plan.macs_per_image;
@@ -208,7 +230,14 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
     {
         cuuint64_t dims[2] = {(cuuint64_t)plan.kc, (cuuint64_t)nsteps * plan.npad};
         cuuint64_t strides[1] = {(cuuint64_t)plan.kc * 2};
-        cuuint32_t box[2] = {(cuuint32_t)plan.kc, (cuuint32_t)plan.nt};
+        // CTA pairs (cta_group::2): each CTA keeps half of every weight tile.  Pays off once the weight tile is wide
+        // enough for the shared-memory traffic to matter; APVAE_TAP_2CTA=0/1 overrides.
+        const bool split_epi = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;
+        bool two = false;    // measured: no gain for this kernel (1062 vs 1070 TFLOP/s at 192 wide, slower for short K): it is bound by the
+                             // per-stage barrier round trip and the epilogue, not by shared-memory traffic; kept for experiments
+        if (const char* e = getenv("APVAE_TAP_2CTA")) two = atoi(e) != 0 && !split_epi;
+        p.two_cta = two ? 1 : 0;
+        cuuint32_t box[2] = {(cuuint32_t)plan.kc, (cuuint32_t)(two ? plan.nt / 2 : plan.nt)};
         CUresult r = encode(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op->d_w, dims, strides, box, ones,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc), CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);

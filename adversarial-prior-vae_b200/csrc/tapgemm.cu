@@ -40,11 +40,26 @@ __device__ __forceinline__ TileCoord decode_tile(const TapGemmParams& p, int til
     return t;
 }
 
+// Pair mode: round g of a CTA pair = (N tile, phase, pair of pixel tiles); rank r takes pixel tile 2*pp + r.
+// A pixel tile beyond the grid (odd count) decodes to n0 >= n_valid: its loads are harmless, its rows are masked.
+__device__ __forceinline__ TileCoord decode_pair_tile(const TapGemmParams& p, int g, int rank, int tiles_n) {
+    TileCoord t;
+    t.nt = g % p.n_tiles;  g /= p.n_tiles;
+    t.ph = g % p.num_phases;  g /= p.num_phases;
+    int tile = 2 * g + rank;
+    t.x0 = (tile % p.tiles_x) * p.bw;  tile /= p.tiles_x;
+    t.y0 = (tile % p.tiles_y) * p.bh;  tile /= p.tiles_y;
+    t.n0 = tile * p.bn;                                   // tile >= tiles_n: out of range
+    (void)tiles_n;
+    return t;
+}
+
 }  // namespace
 
-template <int KC, bool kSplit>
+template <int KC, bool kSplit, bool kTwo>
 __global__ void __launch_bounds__(kThreads, 1)
 tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
+    constexpr bool two = kTwo;
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // Dynamic smem is only guaranteed 16 B aligned by the ABI: realign to 1024 B
     // (swizzle atoms of the UMMA descriptors assume it).
@@ -72,22 +87,29 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
         }
         for (int a = 0; a < kAccStages; ++a) {
             mbar_init(tfull_bar(a), 1);
-            mbar_init(tempty_bar(a), 4);
+            mbar_init(tempty_bar(a), two ? 8 : 4);
         }
         fence_barrier_init();
     }
     if (warp == 2) {
-        tmem_alloc(tmem_ptr_smem, kTmemCols);
+        if constexpr (two) tmem_alloc_2cta(tmem_ptr_smem, kTmemCols); else tmem_alloc(tmem_ptr_smem, kTmemCols);
     }
     tc_fence_before();
     __syncthreads();
+    if constexpr (two) cluster_sync_all();      // the peer's barriers exist before anything is signalled across the pair
     tc_fence_after();
+    const uint32_t rank = two ? cluster_ctarank() : 0u;
     uint32_t tmem_base;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_ptr_smem));
     tmem_base = __shfl_sync(0xffffffffu, tmem_base, 0);
 
     const int tiles_n = (p.n_valid + p.bn - 1) / p.bn;
-    const int total_tiles = tiles_n * p.tiles_y * p.tiles_x * p.num_phases * p.n_tiles;
+    const int pix_tiles = tiles_n * p.tiles_y * p.tiles_x;
+    // work items of this CTA: tiles (one per CTA) or, in pair mode, rounds of a CTA pair
+    const int total_tiles = (two ? (pix_tiles + 1) / 2 : pix_tiles) * p.num_phases * p.n_tiles;
+    const int w_first = two ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+    const int w_step = two ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    auto decode = [&](int w) { return two ? decode_pair_tile(p, w, (int)rank, tiles_n) : decode_tile(p, w); };
 
     // The role loops run with the whole warp converged; one elected lane issues the TMA / tcgen05
     // instructions (see elect_one_sync in sm100_ptx.cuh).
@@ -95,8 +117,8 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
         // ===================== TMA producer =====================
         int stage = 0;
         uint32_t phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const TileCoord t = decode_tile(p, tile);
+        for (int tile = w_first; tile < total_tiles; tile += w_step) {
+            const TileCoord t = decode(tile);
             const int s_begin = p.phase_begin[t.ph], s_end = p.phase_begin[t.ph + 1];
             for (int s = s_begin; s < s_end; ++s) {
                 TapStep st;
@@ -106,21 +128,28 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
                 if (elect_one_sync()) {
                     const uint32_t a_dst = smem_base + stage * p.stage_bytes;
                     const uint32_t b_dst = a_dst + kTileM * KC * 2;
-                    mbar_expect_tx(full_bar(stage), p.a_bytes + p.b_bytes);
-                    tma_load_5d(a_dst, &p.tm_a[st.src], full_bar(stage), st.c0, t.x0 + st.dx, st.ph, t.y0 + st.dy, t.n0);
-                    tma_load_2d(b_dst, &p.tm_b, full_bar(stage), 0, s * p.Npad + t.nt * p.NT);
+                    if constexpr (!two) {
+                        mbar_expect_tx(full_bar(stage), p.a_bytes + p.b_bytes);
+                        tma_load_5d(a_dst, &p.tm_a[st.src], full_bar(stage), st.c0, t.x0 + st.dx, st.ph, t.y0 + st.dy, t.n0);
+                        tma_load_2d(b_dst, &p.tm_b, full_bar(stage), 0, s * p.Npad + t.nt * p.NT);
+                    } else {       // both CTAs' boxes complete on the leader's barrier; each CTA keeps half of the weight tile
+                        const uint32_t bar = mapa_shared(full_bar(stage), 0);
+                        if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * p.a_bytes + p.b_bytes);
+                        tma_load_5d_2cta(a_dst, &p.tm_a[st.src], bar, st.c0, t.x0 + st.dx, st.ph, t.y0 + st.dy, t.n0);
+                        tma_load_2d_2cta(b_dst, &p.tm_b, bar, 0, s * p.Npad + t.nt * p.NT + (int)rank * (p.NT / 2));
+                    }
                 }
                 __syncwarp();
                 if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == 1) {
-        // ===================== MMA issuer =====================
-        const uint32_t idesc = make_idesc_bf16(kTileM, p.NT);
+    } else if (warp == 1 && (!two || rank == 0)) {
+        // ===================== MMA issuer (pair mode: the leader CTA only) =====================
+        const uint32_t idesc = make_idesc_bf16(two ? 2 * kTileM : kTileM, p.NT);
         int stage = 0, acc = 0;
         uint32_t phase = 0, acc_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const TileCoord t = decode_tile(p, tile);
+        for (int tile = w_first; tile < total_tiles; tile += w_step) {
+            const TileCoord t = decode(tile);
             const int s_begin = p.phase_begin[t.ph], s_end = p.phase_begin[t.ph + 1];
             mbar_wait(tempty_bar(acc), acc_phase ^ 1);
             tc_fence_after();
@@ -136,10 +165,16 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
 #pragma unroll
                     for (int k = 0; k < KC / 16; ++k) {
                         // +32 B per K=16 slice inside the swizzle atom (start address is >>4)
-                        umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (s > s_begin || k > 0) ? 1u : 0u);
+                        if constexpr (two) umma_bf16_2cta(tmem_d, da + 2 * k, db + 2 * k, idesc, (s > s_begin || k > 0) ? 1u : 0u);
+                        else umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (s > s_begin || k > 0) ? 1u : 0u);
                     }
-                    umma_commit(empty_bar(stage));
-                    if (s == s_end - 1) umma_commit(tfull_bar(acc));
+                    if constexpr (two) {
+                        umma_commit_2cta(empty_bar(stage), 3);
+                        if (s == s_end - 1) umma_commit_2cta(tfull_bar(acc), 3);
+                    } else {
+                        umma_commit(empty_bar(stage));
+                        if (s == s_end - 1) umma_commit(tfull_bar(acc));
+                    }
                 }
                 __syncwarp();
                 if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
@@ -175,20 +210,20 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
         };
         uint4 rv[8];
         bool pre = false;
-        if ((int)blockIdx.x < total_tiles) {
-            const TileCoord t0 = decode_tile(p, blockIdx.x);
+        if (w_first < total_tiles) {
+            const TileCoord t0 = decode(w_first);
             const EpiRow row0 = make_row(t0);
             if (__any_sync(0xffffffffu, row0.has_res)) {       // first tile's residual: before the accumulator is ready
                 epilogue_res_issue(p.epi, row0, p.NT, t0.nt * p.NT, 0, lane, rv);
                 pre = true;
             }
         }
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const TileCoord t = decode_tile(p, tile);
+        for (int tile = w_first; tile < total_tiles; tile += w_step) {
+            const TileCoord t = decode(tile);
             if (bias_col != t.nt * p.NT) { bias_col = t.nt * p.NT; epilogue_load_bias(p.epi, bias_s, p.NT, bias_col, lane); }
             const EpiRow row = make_row(t);
-            const bool more = tile + (int)gridDim.x < total_tiles;
-            const TileCoord tn = decode_tile(p, more ? tile + (int)gridDim.x : tile);
+            const bool more = tile + w_step < total_tiles;
+            const TileCoord tn = decode(more ? tile + w_step : tile);
             const EpiRow nrow = make_row(tn);
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
@@ -196,15 +231,16 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
             pre = epilogue_block<kSplit>(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, tn.nt * p.NT);
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(tempty_bar(acc));
+            if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0)); else mbar_arrive(tempty_bar(acc)); }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
     }
 
     tc_fence_before();
     __syncthreads();
+    if constexpr (two) cluster_sync_all();
     if (warp == 2) {
-        tmem_dealloc(tmem_base, kTmemCols);
+        if constexpr (two) tmem_dealloc_2cta(tmem_base, kTmemCols); else tmem_dealloc(tmem_base, kTmemCols);
     }
 }
 
@@ -223,23 +259,51 @@ int tapgemm_pick_stages(int kc, int NT, int max_useful) {
 
 int launch_tapgemm(const TapGemmParams& p, int num_sms, void* stream) {
     const int tiles_n = (p.n_valid + p.bn - 1) / p.bn;
-    const long long total = (long long)tiles_n * p.tiles_y * p.tiles_x * p.num_phases * p.n_tiles;
+    const long long pix_tiles = (long long)tiles_n * p.tiles_y * p.tiles_x;
+    const bool two = p.two_cta != 0;
+    const long long total = (two ? (pix_tiles + 1) / 2 : pix_tiles) * p.num_phases * p.n_tiles;
     if (total <= 0) return 0;
-    const int grid = (int)(total < num_sms ? total : num_sms);
     const uint32_t smem = tapgemm_smem_bytes(p.kc, p.NT, p.num_stages);
     cudaError_t err;
     void (*kern)(TapGemmParams) = nullptr;
     const bool split = p.epi.out_raw_lo != nullptr || p.epi.out_act_lo != nullptr || p.epi.res_lo != nullptr;
+    if (two && split) return (int)cudaErrorInvalidValue;
     switch (p.kc) {
-        case 16: kern = split ? tapgemm_kernel<16, true> : tapgemm_kernel<16, false>; break;
-        case 32: kern = split ? tapgemm_kernel<32, true> : tapgemm_kernel<32, false>; break;
-        case 64: kern = split ? tapgemm_kernel<64, true> : tapgemm_kernel<64, false>; break;
+        case 16: kern = two ? tapgemm_kernel<16, false, true> : split ? tapgemm_kernel<16, true, false> : tapgemm_kernel<16, false, false>; break;
+        case 32: kern = two ? tapgemm_kernel<32, false, true> : split ? tapgemm_kernel<32, true, false> : tapgemm_kernel<32, false, false>; break;
+        case 64: kern = two ? tapgemm_kernel<64, false, true> : split ? tapgemm_kernel<64, true, false> : tapgemm_kernel<64, false, false>; break;
         default: return (int)cudaErrorInvalidValue;
     }
     err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
-    kern<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
-    return (int)cudaGetLastError();
+    if (!two) {
+        const int grid = (int)(total < num_sms ? total : num_sms);
+        kern<<<grid, kThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
+        return (int)cudaGetLastError();
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = static_cast<cudaStream_t>(stream);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cfg.gridDim = dim3((num_sms / 2) * 2);
+    static int cached[3] = {0, 0, 0};                        // [kc index] -> max co-resident pairs
+    const int ki = p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2;
+    if (cached[ki] == 0) {
+        int nc = 0;
+        if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki] = nc;
+        else { cached[ki] = num_sms / 2; cudaGetLastError(); }
+    }
+    const long long pairs = total < cached[ki] ? total : cached[ki];
+    cfg.gridDim = dim3((unsigned)(pairs * 2));
+    err = cudaLaunchKernelEx(&cfg, kern, p);
+    return (int)err;
 }
 
 }  // namespace apvae

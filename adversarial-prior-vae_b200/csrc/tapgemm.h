@@ -75,6 +75,8 @@ struct alignas(64) TapGemmParams {
     int kc;                     // 16, 32 or 64 channels per step
     int num_stages;
     uint32_t a_bytes, b_bytes, stage_bytes;
+    int two_cta;                // 1: launched as 2-CTA clusters, one cta_group::2 MMA per pair of pixel tiles
+                                // (each CTA loads its own A tile and HALF of every weight tile; tm_b's box is NT / 2 rows)
     EpilogueArgs epi;
 };
 

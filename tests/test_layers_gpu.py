@@ -288,3 +288,45 @@ def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two
     assert np.abs(act[:n_valid, ..., :cout] - O.leaky_relu(want[:n_valid])).max() <= 2 ** -7 * scale
     assert np.all(raw[:n_valid, ..., cout:] == 0) and np.all(act[:n_valid, ..., cout:] == 0)   # padding columns stay zero
     assert np.all(raw[n_valid:] == 7.0) and np.all(act[n_valid:] == 7.0)
+
+
+PHASE_CASES = [
+    # k, H, W, cin, cout, n_valid, cap
+    (3, 16, 16, 192, 96, 3, 4),        # arch A G_theta/level_8/conv_0
+    (3, 16, 16, 64, 64, 5, 5),
+    (5, 32, 32, 32, 32, 2, 2),         # arch B celebA
+    (3, 32, 32, 64, 32, 2, 3),
+    (5, 16, 16, 16, 48, 3, 3),
+    (3, 64, 64, 16, 16, 1, 1),
+]
+
+
+@pytest.mark.parametrize('outs', ['act', 'raw+act'])
+@pytest.mark.parametrize('k,H,W,cin,cout,n_valid,cap', PHASE_CASES)
+def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, outs, monkeypatch):
+    """conv2d_transpose(stride 2, SAME) (conv2d_.py:464-471) as four sub-pixel phase ops of the A-stationary kernel:
+    phase (py, px) is a stride-1 correlation on the input grid written to output pixels (2y + py, 2x + px) by strided
+    bulk tensor stores."""
+    torch = _torch()
+    from apvae.plan import Plan, pad16
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    rs = np.random.RandomState(k + H + cin + cout)
+    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
+    kern = bf16_round(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], cap)
+    npad = pad16(cout)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    out_act = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    out_raw = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=torch.bfloat16, device='cuda') if outs != 'act' else None
+    plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, out_act=out_act)
+    torch.cuda.synchronize()
+    want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
+    scale = max(1.0, float(np.abs(want).max()))
+    act = out_act.float().cpu().numpy()
+    assert np.abs(act[:n_valid, ..., :cout] - O.leaky_relu(want[:n_valid])).max() <= 2 ** -7 * scale
+    assert np.all(act[n_valid:] == 7.0)
+    if out_raw is not None:
+        raw = out_raw.float().cpu().numpy()
+        assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
+        assert np.all(raw[n_valid:] == 7.0)

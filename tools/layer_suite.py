@@ -12,6 +12,11 @@ L192 = ['--k', '3', '--h', '16', '--w', '16', '--cin', '192', '--cout', '192', '
 L96_5 = ['--transpose', '--k', '5', '--h', '32', '--w', '32', '--cin', '96', '--cout', '96', '--n', N]
 L96_3 = ['--transpose', '--k', '3', '--h', '32', '--w', '32', '--cin', '96', '--cout', '96', '--n', N]
 L192_S2 = ['--transpose', '--k', '3', '--stride', '2', '--h', '16', '--w', '16', '--cin', '192', '--cout', '96', '--n', N]
+D00 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '3', '--cout', '3', '--n', N, '--outs', 'act']
+D01 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '3', '--cout', '16', '--n', N]
+D10 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '16', '--cout', '16', '--n', N, '--outs', 'act']
+D20 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '32', '--cout', '32', '--n', N, '--outs', 'act']
+D30 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '64', '--cout', '64', '--n', N, '--outs', 'act']
 CASES = [
     ('tap192', {'APVAE_PATCH': '0'}, L192),
     ('tap192_res', {'APVAE_PATCH': '0'}, L192 + ['--res', 'same']),
@@ -24,13 +29,27 @@ CASES = [
     ('patch96x3_even', {}, L96_3 + ['--res', 'even']),
     ('patch96x3', {}, L96_3),
     ('tap96x3_even', {'APVAE_PATCH': '0'}, L96_3 + ['--res', 'even']),
-    ('tap192s2', {}, L192_S2),
+    ('tap192s2', {'APVAE_PATCH_PHASES': '0'}, L192_S2 + ['--outs', 'act']),
+    ('phase192s2', {}, L192_S2 + ['--outs', 'act']),
     ('patch192_2cta', {'APVAE_PATCH_2CTA': '1'}, L192),
     ('patch192_res_2cta', {'APVAE_PATCH_2CTA': '1'}, L192 + ['--res', 'same']),
     ('patch96x5_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_5),
     ('patch96x5_res_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_5 + ['--res', 'same']),
     ('patch96x3_even_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_3 + ['--res', 'even']),
     ('patch192_c1', {'APVAE_PATCH_CLUSTER': '1'}, L192),
+    ('nar_D00_a4', {'APVAE_PATCH_ACAP': '4'}, D00),
+    ('nar_D00_a8', {'APVAE_PATCH_ACAP': '8'}, D00),
+    ('nar_D01_a4', {'APVAE_PATCH_ACAP': '4'}, D01),
+    ('nar_D01_a8', {'APVAE_PATCH_ACAP': '8'}, D01),
+    ('nar_D10_a4', {'APVAE_PATCH_ACAP': '4'}, D10),
+    ('nar_D10_a8', {'APVAE_PATCH_ACAP': '8'}, D10),
+    ('nar_D20_a4', {'APVAE_PATCH_ACAP': '4'}, D20),
+    ('nar_D20_a8', {'APVAE_PATCH_ACAP': '8'}, D20),
+    ('nar_D30_a4', {'APVAE_PATCH_ACAP': '4'}, D30),
+    ('nar_D30_a8', {'APVAE_PATCH_ACAP': '8'}, D30),
+    ('nar_96x3_a8', {'APVAE_PATCH_ACAP': '8'}, L96_3 + ['--res', 'even']),
+    ('nar_96x3_a4', {'APVAE_PATCH_ACAP': '4'}, L96_3 + ['--res', 'even']),
+
     ('patch192_c2', {'APVAE_PATCH_CLUSTER': '2'}, L192),
     ('patch96x5_c1', {'APVAE_PATCH_CLUSTER': '1'}, L96_5),
     ('patch96x5_c2', {'APVAE_PATCH_CLUSTER': '2'}, L96_5),
