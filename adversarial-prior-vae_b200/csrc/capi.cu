@@ -535,6 +535,20 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
         cudaEventDestroy(e0); cudaEventDestroy(e1);
     }
     if (err == 0) err = (int)cudaDeviceSynchronize();
+    if (err == 0) {
+        for (auto& o : ops) {
+            if (!o->d_trace) continue;
+            std::vector<unsigned long long> t(64 * 16);
+            cudaMemcpy(t.data(), o->d_trace, t.size() * sizeof(unsigned long long), cudaMemcpyDeviceToHost);
+            const unsigned long long t0 = t[0];
+            fprintf(stderr, "trace %s (cycles since the first stamp; 16 slots per tile)\n", o->name.c_str());
+            for (int i = 0; i < 64 && t[i * 16] != 0; ++i) {
+                fprintf(stderr, "tile %2d:", i);
+                for (int j = 0; j < 16; ++j) fprintf(stderr, " %7lld", t[i * 16 + j] ? (long long)(t[i * 16 + j] - t0) : -1LL);
+                fprintf(stderr, "\n");
+            }
+        }
+    }
     if (err != 0) return set_global_err(std::string("plan_run: ") + cudaGetErrorString((cudaError_t)err), APVAE_ERR_CUDA);
     return APVAE_OK;
 }

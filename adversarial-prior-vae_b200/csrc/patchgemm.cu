@@ -85,6 +85,9 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     const int cluster_id = blockIdx.x / csize;
     const int rounds_total = (total_tiles + csize - 1) / csize;   // tile groups; every CTA of a cluster runs the same rounds
     constexpr uint32_t row_bytes = KC * 2;
+    // tuning only: clock stamps of CTA 0's first 64 tiles, slot layout in tools/trace_layer.py
+    unsigned long long* const trace = (blockIdx.x == 0) ? p.trace : nullptr;
+    auto stamp = [&](int it, int slot) { if (trace && it < 64) trace[it * 16 + slot] = (unsigned long long)clock64(); };
     const bool skipA = (p.debug == 1 || p.debug == 3 || p.debug >= 10), skipB = (p.debug == 1 || p.debug == 2 || p.debug >= 10);
 
     if (warp == 0) {
@@ -92,7 +95,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         if (!skipA) {
             int sa = 0;
             uint32_t pa = 0;
-            for (int g = cluster_id; g < rounds_total; g += num_clusters) {
+            int it = 0;
+            for (int g = cluster_id; g < rounds_total; g += num_clusters, ++it) {
                 const int tile = g * csize + (int)rank;
                 const int n = tile / p.tiles_y;                  // tile >= total_tiles -> n >= n_valid: zero-filled / masked
                 const int y0 = (tile % p.tiles_y) * p.rows_tile;
@@ -100,6 +104,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                     const PatchGroup gr = p.groups[gi];
                     mbar_wait(emptyA(sa), pa ^ 1);
                     if (elect_one_sync()) {
+                        if (gi == 0) stamp(it, 14);
+                        if (gi == p.num_groups - 1) stamp(it, 15);
                         const uint32_t bytes = (uint32_t)gr.prow * p.W * row_bytes;
                         if constexpr (!two) {
                             mbar_expect_tx(fullA(sa), bytes);
@@ -165,14 +171,18 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         const uint64_t b_tap_step = (uint64_t)((two ? p.tap_bytes / 2 : p.tap_bytes) >> 4);
         int sa = 0, sb = 0, acc = 0;
         uint32_t pa = 0, pb = 0, acc_phase = 0;
-        for (int g = cluster_id; g < rounds_total; g += num_clusters) {
+        int it = 0;
+        for (int g = cluster_id; g < rounds_total; g += num_clusters, ++it) {
+            if (lane == 0) stamp(it, 0);
             mbar_wait(tempty(acc), acc_phase ^ 1);
             tc_fence_after();
+            if (lane == 0) stamp(it, 1);
             const uint32_t tmem_d = tmem_base + acc * kAccColStride;
             uint32_t accumulate = 0;
             for (int gi = 0; gi < num_groups; ++gi) {
                 const int k = p.groups[gi].k;
                 if (!skipA) mbar_wait(fullA(sa), pa);
+                if (gi == 0 && lane == 0) stamp(it, 2);
                 uint64_t da_row = make_kmajor_desc<KC>(a_base + sa * a_slot);          // vertical tap 0
                 for (int j0 = 0; j0 < k; j0 += tpi) {
                     const int nt = min(tpi, k - j0);
@@ -200,7 +210,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                                 db += b_tap_step;
                             }
                         };
-                        if (macc == 1) issue(std::integral_constant<int, 1>{});
+                        if (p.debug == 6 || p.debug == 16) {}
+                        else if (macc == 1) issue(std::integral_constant<int, 1>{});
                         else if (macc == 2) issue(std::integral_constant<int, 2>{});
                         else issue(std::integral_constant<int, 4>{});
                         if (skipB) {}
@@ -217,13 +228,16 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 __syncwarp();
                 if (++sa == a_stages) { sa = 0; pa ^= 1; }
             }
+            if (lane == 0) stamp(it, 3);
             if (elect_one_sync()) { if constexpr (two) umma_commit_2cta(tfull(acc), cmask); else umma_commit(tfull(acc)); }
             __syncwarp();
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
     } else if (warp >= 4 && p.fast_epi) {
         // ===================== epilogue, TMA in / TMA out =====================
-        // Work unit = "block": 32 rows (this warp's TMEM lane quarter) x 64 columns of one accumulator.
+        // Work unit = "block": 32 rows (this warp's TMEM lane quarter) x up to 64 columns of one accumulator.
+        // Everything that positions a block is warp-uniform and advances by adds / shifts (W is a power of two);
+        // the block body is compiled once per column count so that it is straight-line code.
         const int q = warp & 3;
         const uint32_t wbase = epi_base + q * kFastEpiWarpBytes;
         const uint32_t rawbuf = wbase + 2 * kFastEpiBoxBytes, actbuf = wbase + 3 * kFastEpiBoxBytes;
@@ -233,34 +247,37 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         const bool want_raw = p.epi.out_raw != nullptr, want_act = p.epi.out_act != nullptr;
         const int res_mode = p.epi.res_mode;
         const bool dbl = (res_mode == RES_NONE);
-        uint32_t nblk = 0;
+        const bool do_store = (p.debug != 5 && p.debug != 15), do_work = (p.debug != 4 && p.debug != 14);
         const uint32_t res_bytes = (uint32_t)p.res_rows * 128u;
         const float alpha = p.epi.lrelu_alpha;
         const uint32_t sw = (uint32_t)(lane & 7);
-        struct Seq { int g, m, cb; };
-        auto seq_next = [&](Seq s) {
+        const int W = p.W, H = p.H, NT = p.NT, macc = p.macc, tiles_y = p.tiles_y, rows_tile = p.rows_tile, n_valid = p.n_valid;
+        const int lgW = 31 - __clz(W);
+        const int tile_step = num_clusters * csize;
+        const int dn = tile_step / tiles_y, dty = tile_step - dn * tiles_y;
+        // a block's place in the work sequence: round g, accumulator m, first column cb; (n, ty) = image and row-tile of
+        // this CTA's tile in round g, advanced incrementally
+        struct Seq { int g, m, cb, n, ty; };
+        auto seq_next = [&](Seq& s) {
             s.cb += 64;
-            if (s.cb >= p.NT) { s.cb = 0; if (++s.m == p.macc) { s.m = 0; s.g += num_clusters; } }
-            return s;
+            if (s.cb >= NT) {
+                s.cb = 0;
+                if (++s.m == macc) {
+                    s.m = 0; s.g += num_clusters; s.n += dn; s.ty += dty;
+                    if (s.ty >= tiles_y) { s.ty -= tiles_y; ++s.n; }
+                }
+            }
         };
-        // first output pixel of this warp's rows in block s, and whether the tile exists
-        auto seq_pix0 = [&](const Seq& s, bool& ok) {
-            const int tile = s.g * csize + (int)rank;
-            ok = (s.g < rounds_total) && (tile < total_tiles);
-            const int n = tile / p.tiles_y, y0 = (tile % p.tiles_y) * p.rows_tile;
-            return ((n * p.H + y0) * p.W) + s.m * kTileM + q * 32;
-        };
+        auto seq_ok = [&](const Seq& s) { return s.g < rounds_total && s.n < n_valid; };
         // bulk load of the residual box of block s into buffer b; returns whether one was issued (warp-uniform)
         auto issue_res = [&](const Seq& s, int b) {
-            if (res_mode == RES_NONE) return false;
-            bool ok;
-            const int pix0 = seq_pix0(s, ok);
-            if (!ok) return false;
-            int rp0 = pix0;
-            if (res_mode == RES_EVEN) {                    // half-resolution residual on even pixels only
-                const int x0 = pix0 % p.W, yy = pix0 / p.W;     // yy = n*H + y  (H even)
-                if (yy & 1) return false;
-                rp0 = (yy >> 1) * (p.W >> 1) + (x0 >> 1);
+            if (!seq_ok(s)) return false;
+            const int po = s.m * kTileM + q * 32;          // first pixel of this warp's rows inside the tile
+            const int gy = s.n * H + s.ty * rows_tile + (po >> lgW), x0 = po & (W - 1);
+            int rp0 = gy * W + x0;
+            if (res_mode == RES_EVEN) {                    // half-resolution residual on even pixels only (H is even)
+                if (gy & 1) return false;
+                rp0 = (gy >> 1) * (W >> 1) + (x0 >> 1);
             }
             if (leader) {
                 mbar_expect_tx(resbar(q, b), res_bytes);
@@ -273,112 +290,145 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         bool lane_res = true;
         if (res_mode == RES_EVEN) {
             const int pix = q * 32 + lane;                 // (m * 128 does not change x parity or the row split)
-            const int x = pix % p.W;
-            lane_res = !(x & 1) && !((pix / p.W) & 1);
-            rrow = (p.W >= 32) ? (lane >> 1) : ((lane & 15) >> 1);
+            const int x = pix & (W - 1);
+            lane_res = !(x & 1) && !((pix >> lgW) & 1);
+            rrow = (W >= 32) ? (lane >> 1) : ((lane & 15) >> 1);
         }
-        const uint32_t rsw = (uint32_t)(rrow & 7);
-        Seq cur = {cluster_id, 0, 0};
-        bool iss0 = issue_res(cur, 0);
-        Seq pre = seq_next(cur);
-        bool iss1 = issue_res(pre, 1);
-        pre = seq_next(pre);
-        uint32_t ph0 = 0, ph1 = 0;
+        const uint32_t res_off = (uint32_t)rrow * 128u, rsw = (uint32_t)(rrow & 7);
+        const uint32_t st_off = (uint32_t)lane * 128u;
+        Seq cur;
+        {
+            const int tile0 = cluster_id * csize + (int)rank;
+            cur.g = cluster_id; cur.m = 0; cur.cb = 0; cur.n = tile0 / tiles_y; cur.ty = tile0 - cur.n * tiles_y;
+        }
+        Seq pre = cur;
+        bool iss0 = false, iss1 = false;
+        if (!dbl) {
+            iss0 = issue_res(pre, 0); seq_next(pre);
+            iss1 = issue_res(pre, 1); seq_next(pre);
+        }
+        uint32_t ph0 = 0, ph1 = 0, nblk = 0;
         int kb = 0;
         int acc = 0;
         uint32_t acc_phase = 0;
-        for (int g = cluster_id; g < rounds_total; g += num_clusters) {
-            mbar_wait(tfull(acc), acc_phase);
-            tc_fence_after();
-            for (int m = 0; m < ((p.debug == 4 || p.debug == 14) ? 0 : p.macc); ++m) {
-                for (int cb = 0; cb < p.NT; cb += 64) {
-                    const int bw = min(64, p.NT - cb);
-                    const uint32_t taddr = tmem_base + acc * kAccColStride + m * p.NT + cb + ((uint32_t)(q * 32) << 16);
-                    bool ok;
-                    const int pix0 = seq_pix0(cur, ok);
-                    const int oy = pix0 / p.W, ox0 = pix0 - oy * p.W;      // first row of the warp on the input grid: (n*H + y, x0)
-                    const int on = oy / p.H, oyy = oy - on * p.H;
-                    const bool has_res = kb ? iss1 : iss0;
-                    const uint32_t rbuf = wbase + kb * kFastEpiBoxBytes;
-                    uint32_t rr[32], aa[32];               // packed bf16 pairs: raw and activated, 64 columns
+        int tit = 0, tblk = 0;                             // trace only
+
+        // one block of BW columns: TMEM -> registers -> (+bias, +residual, leaky-relu) -> swizzled staging -> bulk stores
+        auto block = [&](auto bw_c, uint32_t taddr, bool last_of_tile) {
+            constexpr int BW = decltype(bw_c)::value;
+            constexpr int NCH = BW / 8;                    // 16-byte chunks per row
+            uint32_t v[(BW + 31) / 32 * 32];
+            {
+                uint32_t (&v0)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[0]);
+                if constexpr (BW >= 32) tmem_ld32(taddr, v0);
+                else { uint32_t (&l0)[16] = *reinterpret_cast<uint32_t (*)[16]>(&v[0]); tmem_ld16(taddr, l0); }
+                if constexpr (BW == 64) { uint32_t (&v1)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[32]); tmem_ld32(taddr + 32, v1); }
+                if constexpr (BW == 48) { uint32_t (&l1)[16] = *reinterpret_cast<uint32_t (*)[16]>(&v[32]); tmem_ld16(taddr + 32, l1); }
+            }
+            const bool has_res = kb ? iss1 : iss0;
+            if (has_res) {
+                if (kb) { mbar_wait(resbar(q, 1), ph1); ph1 ^= 1; }
+                else { mbar_wait(resbar(q, 0), ph0); ph0 ^= 1; }
+            }
+            tmem_ld_wait();
+            if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 6);
+            if (last_of_tile) {                            // the accumulator is in registers: hand it back to the MMA warp now
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
+            }
+            const uint32_t rbuf = wbase + kb * kFastEpiBoxBytes + res_off;
+            const uint32_t bias_b = bias_s + cur.cb * 4;
+            uint32_t rr[NCH * 4], aa[NCH * 4];             // packed bf16 pairs: raw and activated
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const int cw = min(32, bw - 32 * h);
-                        if (cw <= 0) break;
-                        uint32_t v[32];
-                        if (cw == 32) {
-                            tmem_ld32(taddr + 32 * h, v);
-                        } else {
-                            uint32_t lo[16];
-                            tmem_ld16(taddr + 32 * h, lo);
-#pragma unroll
-                            for (int i = 0; i < 16; ++i) v[i] = lo[i];
-                        }
-                        if (h == 0 && has_res) {
-                            if (kb) { mbar_wait(resbar(q, 1), ph1); ph1 ^= 1; }
-                            else { mbar_wait(resbar(q, 0), ph0); ph0 ^= 1; }
-                        }
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int j = 0; j < 4; ++j) {      // 16-byte chunks (8 columns)
-                            if (j * 8 >= cw) break;
-                            const int ch = h * 4 + j;
-                            float f[8];
-                            const float4 b0 = ld_shared_f4(bias_s + (cb + ch * 8) * 4);
-                            const float4 b1 = ld_shared_f4(bias_s + (cb + ch * 8 + 4) * 4);
-                            f[0] = __uint_as_float(v[j * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[j * 8 + 1]) + b0.y;
-                            f[2] = __uint_as_float(v[j * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[j * 8 + 3]) + b0.w;
-                            f[4] = __uint_as_float(v[j * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[j * 8 + 5]) + b1.y;
-                            f[6] = __uint_as_float(v[j * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[j * 8 + 7]) + b1.w;
-                            if (has_res) {
-                                const uint4 rv = ld_shared_v4(rbuf + rrow * 128 + (((uint32_t)ch ^ rsw) << 4));
-                                if (lane_res) {
-                                    f[0] += bf16_lo(rv.x); f[1] += bf16_hi(rv.x); f[2] += bf16_lo(rv.y); f[3] += bf16_hi(rv.y);
-                                    f[4] += bf16_lo(rv.z); f[5] += bf16_hi(rv.z); f[6] += bf16_lo(rv.w); f[7] += bf16_hi(rv.w);
-                                }
-                            }
-#pragma unroll
-                            for (int i = 0; i < 4; ++i) {
-                                rr[ch * 4 + i] = pack_bf16(f[2 * i], f[2 * i + 1]);
-                                aa[ch * 4 + i] = pack_bf16(fmaxf(f[2 * i], alpha * f[2 * i]), fmaxf(f[2 * i + 1], alpha * f[2 * i + 1]));
-                            }
-                        }
+            for (int ch = 0; ch < NCH; ++ch) {
+                float f[8];
+                const float4 b0 = ld_shared_f4(bias_b + ch * 32);
+                const float4 b1 = ld_shared_f4(bias_b + ch * 32 + 16);
+                f[0] = __uint_as_float(v[ch * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[ch * 8 + 1]) + b0.y;
+                f[2] = __uint_as_float(v[ch * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[ch * 8 + 3]) + b0.w;
+                f[4] = __uint_as_float(v[ch * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[ch * 8 + 5]) + b1.y;
+                f[6] = __uint_as_float(v[ch * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[ch * 8 + 7]) + b1.w;
+                if (has_res) {
+                    const uint4 rv = ld_shared_v4(rbuf + (((uint32_t)ch ^ rsw) << 4));
+                    if (lane_res) {
+                        f[0] += bf16_lo(rv.x); f[1] += bf16_hi(rv.x); f[2] += bf16_lo(rv.y); f[3] += bf16_hi(rv.y);
+                        f[4] += bf16_lo(rv.z); f[5] += bf16_hi(rv.z); f[6] += bf16_lo(rv.w); f[7] += bf16_hi(rv.w);
                     }
-                    __syncwarp();                          // every lane is done with the residual box
-                    {                                      // refill it with the residual of the block two ahead
-                        const bool is = issue_res(pre, kb);
-                        if (kb) iss1 = is; else iss0 = is;
-                        pre = seq_next(pre);
-                    }
-                    // staging boxes: without a residual the two residual boxes serve as a second (raw, act) pair, so only
-                    // the stores of the block before the previous one must have left shared memory
-                    const bool alt = dbl && (nblk & 1);
-                    const uint32_t rawb = alt ? wbase : rawbuf, actb = alt ? wbase + kFastEpiBoxBytes : actbuf;
-                    ++nblk;
-                    if (leader) { if (dbl) tma_store_wait_read1(); else tma_store_wait_read(); }
-                    __syncwarp();
-                    const int nch = bw >> 3;
+                }
 #pragma unroll
-                    for (int ch = 0; ch < 8; ++ch) {
-                        if (ch >= nch) break;
-                        const uint32_t off = lane * 128 + (((uint32_t)ch ^ sw) << 4);
-                        if (want_raw) st_shared_v4(rawb + off, rr[ch * 4], rr[ch * 4 + 1], rr[ch * 4 + 2], rr[ch * 4 + 3]);
-                        if (want_act) st_shared_v4(actb + off, aa[ch * 4], aa[ch * 4 + 1], aa[ch * 4 + 2], aa[ch * 4 + 3]);
-                    }
-                    fence_proxy_async_smem();
-                    __syncwarp();
-                    if (leader && ok && p.debug != 5 && p.debug != 15) {
-                        if (want_raw) tma_store_4d(&p.tm_raw, rawb, cb, ox0, oyy, on);
-                        if (want_act) tma_store_4d(&p.tm_act, actb, cb, ox0, oyy, on);
-                        tma_store_commit();
-                    }
-                    kb ^= 1;
-                    cur = seq_next(cur);
+                for (int i = 0; i < 4; ++i) {
+                    rr[ch * 4 + i] = pack_bf16(f[2 * i], f[2 * i + 1]);
+                    aa[ch * 4 + i] = pack_bf16(fmaxf(f[2 * i], alpha * f[2 * i]), fmaxf(f[2 * i + 1], alpha * f[2 * i + 1]));
                 }
             }
-            tc_fence_before();
+            if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 7);
+            if (!dbl) {
+                __syncwarp();                              // every lane is done with the residual box:
+                const bool is = issue_res(pre, kb);        // refill it with the residual of the block two ahead
+                if (kb) iss1 = is; else iss0 = is;
+                seq_next(pre);
+            }
+            // staging boxes: without a residual the two residual boxes serve as a second (raw, act) pair, so only
+            // the stores of the block before the previous one must have left shared memory
+            const bool alt = dbl && (nblk & 1);
+            const uint32_t rawb = (alt ? wbase : rawbuf), actb = (alt ? wbase + kFastEpiBoxBytes : actbuf);
+            ++nblk;
+            if (leader) { if (dbl) tma_store_wait_read1(); else tma_store_wait_read(); }
             __syncwarp();
-            if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
+            if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 8);
+            if (want_raw) {
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch)
+                    st_shared_v4(rawb + st_off + (((uint32_t)ch ^ sw) << 4), rr[ch * 4], rr[ch * 4 + 1], rr[ch * 4 + 2], rr[ch * 4 + 3]);
+            }
+            if (want_act) {
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch)
+                    st_shared_v4(actb + st_off + (((uint32_t)ch ^ sw) << 4), aa[ch * 4], aa[ch * 4 + 1], aa[ch * 4 + 2], aa[ch * 4 + 3]);
+            }
+            if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 9);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 10);
+            if (leader && do_store && cur.n < n_valid) {
+                const int po = cur.m * kTileM + q * 32;
+                const int oyy = cur.ty * rows_tile + (po >> lgW), ox0 = po & (W - 1);
+                if (want_raw) tma_store_4d(&p.tm_raw, rawb, cur.cb, ox0, oyy, cur.n);
+                if (want_act) tma_store_4d(&p.tm_act, actb, cur.cb, ox0, oyy, cur.n);
+                tma_store_commit();
+            }
+            if (q == 0 && lane == 0) stamp(tit, tblk == 0 ? 11 : (tblk == 1 ? 12 : 13));
+            ++tblk;
+            kb ^= 1;
+        };
+
+        const int bw_last = NT - ((NT - 1) & ~63);          // columns of the last block of an accumulator: 16, 32, 48 or 64
+        for (int g = cluster_id; g < rounds_total; g += num_clusters, ++tit) {
+            if (q == 0 && lane == 0) stamp(tit, 4);
+            mbar_wait(tfull(acc), acc_phase);
+            tc_fence_after();
+            if (q == 0 && lane == 0) stamp(tit, 5);
+            tblk = 0;
+            if (do_work) {
+                for (int m = 0; m < macc; ++m) {
+                    const uint32_t tbase = tmem_base + acc * kAccColStride + m * NT + ((uint32_t)(q * 32) << 16);
+                    for (int cb = 0; cb < NT; cb += 64) {
+                        const bool last_cb = cb + 64 >= NT;
+                        const bool last = last_cb && (m + 1 == macc);
+                        const int bw = last_cb ? bw_last : 64;
+                        if (bw == 64) block(std::integral_constant<int, 64>{}, tbase + cb, last);
+                        else if (bw == 32) block(std::integral_constant<int, 32>{}, tbase + cb, last);
+                        else if (bw == 16) block(std::integral_constant<int, 16>{}, tbase + cb, last);
+                        else block(std::integral_constant<int, 48>{}, tbase + cb, last);
+                        seq_next(cur);
+                    }
+                }
+            } else {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
+            }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
         if (leader) tma_store_wait_all();

@@ -65,6 +65,7 @@ struct alignas(64) PatchGemmParams {
                                      // box (64, min(W, 32), 32 / min(W, 32), 1), SWIZZLE_128B
     CUtensorMap tm_res;              // 2-D (Npad, residual pixels), box (64, res_rows)
     int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
+    unsigned long long* trace;       // tuning only (APVAE_PATCH_TRACE): per-tile clock64 stamps of CTA 0, 16 slots per tile, 64 tiles
     EpilogueArgs epi;
 };
 

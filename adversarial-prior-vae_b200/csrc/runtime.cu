@@ -54,6 +54,7 @@ DevOp::~DevOp() {
     if (d_steps) cudaFree(d_steps);
     if (d_w) cudaFree(d_w);
     if (d_bias) cudaFree(d_bias);
+    if (d_trace) cudaFree(d_trace);
     if (d_groups) cudaFree(d_groups);
 }
 
@@ -135,6 +136,11 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.cluster = plan.cluster;
     p.two_cta = (plan.two_cta && plan.cluster == 2) ? 1 : 0;
     { const char* dbg = getenv("APVAE_PATCH_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
+    if (getenv("APVAE_PATCH_TRACE")) {        // tuning only: clock stamps of CTA 0 (read back by apvae_plan_bench)
+        APVAE_CUDA_OK(cudaMalloc(&op->d_trace, 64 * 16 * sizeof(unsigned long long)), err);
+        APVAE_CUDA_OK(cudaMemset(op->d_trace, 0, 64 * 16 * sizeof(unsigned long long)), err);
+        p.trace = op->d_trace;
+    }
     fill_epilogue(p.epi, epi, op->d_bias);
     // bf16-only epilogues (the conv blocks' interior layers) go through bulk tensor loads / stores
     p.fast_epi = 0;

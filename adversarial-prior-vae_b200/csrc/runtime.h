@@ -42,6 +42,7 @@ struct DevOp {
     TapStep* d_steps = nullptr;
     uint16_t* d_w = nullptr;
     float* d_bias = nullptr;
+    unsigned long long* d_trace = nullptr;
     TapGemmParams params;
     bool is_patch = false;          // true: the A-stationary kernel (patchgemm.h) runs this op
     PatchGroup* d_groups = nullptr;

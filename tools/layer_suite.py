@@ -67,6 +67,19 @@ for _d, _nm in ((4, 'noepi'), (5, 'nostore'), (14, 'noload_noepi'), (15, 'noload
     CASES.append(('dbx192_%s' % _nm, {'APVAE_PATCH_DEBUG': str(_d)}, L192))
     CASES.append(('dbx96x5_%s' % _nm, {'APVAE_PATCH_DEBUG': str(_d)}, L96_5))
 CASES.append(('dbg192_ast2', {'APVAE_PATCH_ASTAGES': '2'}, L192))
+for _nm, _a in (('D00', D00), ('D01', D01), ('D10', D10), ('D20', D20)):
+    CASES.append(('dbn_%s_base' % _nm, {}, _a))
+    for _d, _dn in ((4, 'noepi'), (5, 'nostore'), (1, 'noload'), (15, 'noload_nostore')):
+        CASES.append(('dbn_%s_%s' % (_nm, _dn), {'APVAE_PATCH_DEBUG': str(_d)}, _a))
+for _n in (125, 250, 500, 1000, 2000, 4000):
+    _a = ['--k', '3', '--h', '32', '--w', '32', '--cin', '16', '--cout', '16', '--n', str(_n), '--outs', 'act']
+    CASES.append(('dbs_n%d_base' % _n, {}, _a))
+    CASES.append(('dbs_n%d_noepi' % _n, {'APVAE_PATCH_DEBUG': '14'}, _a))
+    CASES.append(('dbs_n%d_nomma' % _n, {'APVAE_PATCH_DEBUG': '16'}, _a))
+for _m in (1, 2):
+    _a = ['--k', '3', '--h', '32', '--w', '32', '--cin', '16', '--cout', '16', '--n', '1000', '--outs', 'act']
+    CASES.append(('dbs_macc%d_base' % _m, {'APVAE_PATCH_MACC': str(_m)}, _a))
+    CASES.append(('dbs_macc%d_noepi' % _m, {'APVAE_PATCH_MACC': str(_m), 'APVAE_PATCH_DEBUG': '14'}, _a))
 
 
 def main():
