@@ -303,7 +303,7 @@ def main():
         try:                                   # DRAM bytes per launch from the committed ncu --set full capture
             with open(os.path.join(ROOT, 'profiles', 'r1_traffic.json')) as f:
                 tj = json.load(f)
-            if args.chunk == 1000 and args.arch == 'A' and args.z_dim == 128:
+            if args.chunk == tj.get('chunk') and args.arch == 'A' and args.z_dim == 128:
                 traffic = tj['bytes_per_launch'].get(dom[1].split(' [')[0])
                 traffic_src = tj['source']
         except (OSError, ValueError, KeyError):
