@@ -87,7 +87,9 @@ def synthetic_images(n, x_shape, seed=0):
 
 
 class ClockSampler(object):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md)."""
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md).  The nvidia-smi process is
+    started BEFORE the warm-up (its start-up enumerates every GPU of the box under driver-wide locks, which stalls
+    kernel launches for tens of ms on an 8-GPU node); only rows that arrive inside the timed window are kept."""
     Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
          'clocks_event_reasons.sw_power_cap')
@@ -107,9 +109,9 @@ class ClockSampler(object):
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(',')])
+            self.rows.append((time.perf_counter(), [c.strip() for c in line.split(',')]))
 
-    def stop(self):
+    def stop(self, t0=None, t1=None):
         if self.proc is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
         self.proc.terminate()
@@ -118,7 +120,9 @@ class ClockSampler(object):
         except Exception:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        for t, r in self.rows:
+            if (t0 is not None and t < t0) or (t1 is not None and t > t1):
+                continue
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
             except Exception:
@@ -231,16 +235,18 @@ def main():
 
     # ---------------- device-resident throughput ("value")
     accum = torch.zeros(_lib.ACCUM_SLOTS, dtype=torch.float64, device=model.device)
-    for i in range(W):
-        ev.run_shard(x_dev[i * B:(i + 1) * B], accum=accum.clone())
-        combine_accumulators(accum.clone())                      # warm-up of the collective path too (NCCL lazy init)
-    barrier()
-    launches0 = model.launch_count()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for i in range(W):
+        wa = ev.run_shard(x_dev[i * B:(i + 1) * B], accum=accum.clone())
+        combine_accumulators(wa)                                 # warm-up of the collective path on a FILLED accumulator
+                                                                 # (NCCL lazy init + first use of the torch kernels it runs)
+    barrier()
+    launches0 = model.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    t_region0 = time.perf_counter()
     e0.record()
     for i in range(W, W + S):
         flush.fill_(i & 0xFF)                                    # evict L2 between timed steps
@@ -248,11 +254,14 @@ def main():
     total = combine_accumulators(accum)                          # the one allreduce of metric sums
     e1.record()
     barrier()
+    t_region1 = time.perf_counter()
+    if os.environ.get('APVAE_BENCH_DEBUG'):
+        sys.stderr.write('rank %d value-loop ms %.2f\n' % (rank, e0.elapsed_time(e1)))
     ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=model.device)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms = float(ms)
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_region0, t_region1) if rank == 0 else None
     launches = model.launch_count() - launches0
     metrics = metrics_from_accumulator(total)
     value = S * B * world / (ms / 1e3)
@@ -269,6 +278,25 @@ def main():
         r = model.is_nll(xb, K, seed=77 + i)
         out_host.copy_(r['per_image'])                                           # D2H of the step's result
         torch.cuda.synchronize()
+    if os.environ.get('APVAE_BENCH_DEBUG'):
+        sys.stderr.write('rank %d e2e-loop ms %.2f (before the closing barrier)\n' % (rank, 1e3 * (time.perf_counter() - t0)))
+        for rep in range(2):                                 # the value loop again, without flush / collective
+            barrier()
+            e0.record()
+            for i in range(W, W + S):
+                ev.run_shard(x_dev[i * B:(i + 1) * B], accum=accum, first_index=i * B)
+            e1.record()
+            torch.cuda.synchronize()
+            sys.stderr.write('rank %d value-loop again (no flush, no collective) ms %.2f\n' % (rank, e0.elapsed_time(e1)))
+        for rep in range(2):
+            barrier()
+            e0.record()
+            for i in range(W, W + S):
+                flush.fill_(i & 0xFF)
+                ev.run_shard(x_dev[i * B:(i + 1) * B], accum=accum, first_index=i * B)
+            e1.record()
+            torch.cuda.synchronize()
+            sys.stderr.write('rank %d value-loop again (flush, no collective) ms %.2f\n' % (rank, e0.elapsed_time(e1)))
     barrier()
     t_e2e = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=model.device)
     if world > 1:
