@@ -1,7 +1,9 @@
 """BASELINE configs[3]: CelebA-shape (64x64x3, arch B = dmm_for_sampling.py) latent MALA sampling of the energy prior,
 100 steps x 1024 chains, then x = G_theta(z) -> uint8.  Prints one JSON line (chain-steps/s, algorithmic TFLOP/s).
   python tools/bench_mala.py [--precise] [--chains 1024] [--steps 100] [--dataset celebA] [--arch B] [--chunk 512]
-Random-init weights, z0 ~ N(0, I) (stand-in for the G_omega latent GAN), in-kernel Philox noise."""
+Random-init weights, z0 ~ N(0, I) (stand-in for the G_omega latent GAN), in-kernel Philox noise.
+Under torchrun every rank runs `--chains` independent chains on its own GPU (the chains shard with no collective on the
+data path); rank 0 prints the aggregate over the slowest rank's device time."""
 import argparse
 import json
 import os
@@ -26,12 +28,21 @@ def main():
     ap.add_argument('--chunk', type=int, default=512)
     ap.add_argument('--precise', action='store_true')
     a = ap.parse_args()
+    rank, world, local = (int(os.environ.get(k, d)) for k, d in (('RANK', '0'), ('WORLD_SIZE', '1'), ('LOCAL_RANK', '0')))
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     cfg = ExpConfig(a.arch, dataset=a.dataset if a.arch == 'B' else None, z_dim=a.z_dim, max_batch=8, max_chunk=a.chunk,
                     enable_grad=True, precise=a.precise)
-    m = Model(cfg, synthetic_weights(weight_schema(cfg)))
-    z0 = torch.from_numpy(np.random.RandomState(2).normal(size=(a.chains, cfg.z_dim)).astype(np.float32)).cuda()
+    m = Model(cfg, synthetic_weights(weight_schema(cfg)), device=local)
+    z0 = torch.from_numpy(np.random.RandomState(2 + rank).normal(size=(a.chains, cfg.z_dim)).astype(np.float32)).cuda()
     m.mala(z0, 2, seed=1, history=False)                      # warm-up
     torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     out = m.mala(z0, a.steps, seed=7, history=True)
@@ -39,13 +50,21 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], dtype=torch.float64, device='cuda')
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+        dist.barrier()
+        if rank != 0:
+            dist.destroy_process_group()
+            return
     _, mg, md = m.macs()
     # algorithmic: one forward + one input-gradient backward of D o G per chain-step (backward ~ forward), SURVEY 8(d)
-    flops = 4.0 * (mg + md) * a.chains * a.steps
+    flops = 4.0 * (mg + md) * a.chains * a.steps * world
     acc = float((out['history_ratio'] > 0.5).float().mean())
     print(json.dumps({
         'metric': 'MALA chain-steps/sec (%s %s, d=%d, %d chains x %d steps)' % (a.arch, a.dataset, cfg.z_dim, a.chains, a.steps),
-        'value': a.chains * a.steps / (ms / 1e3), 'unit': 'chain-steps/s', 'ms_total': ms,
+        'value': world * a.chains * a.steps / (ms / 1e3), 'unit': 'chain-steps/s', 'n_gpus': world, 'ms_total': ms,
         'algorithmic_tflops': flops / (ms / 1e3) / 1e12, 'precise': bool(a.precise),
         'mean_accept_ratio': float(out['history_ratio'].mean()), 'frac_ratio_gt_half': acc,
         'images': list(img.shape), 'dtype': 'bf16x3 (split precision)' if a.precise else 'bf16'}))
