@@ -36,6 +36,7 @@ class Config(C.Structure):
         ('uniform_scale', C.c_int), ('use_truncated', C.c_int), ('bernoulli', C.c_int),
         ('max_batch', C.c_int), ('max_chunk', C.c_int), ('enable_grad', C.c_int),
         ('smallest_step', C.c_float), ('len_train', C.c_int), ('precise', C.c_int),
+        ('nf_layers', C.c_int),
     ]
 
 

@@ -42,6 +42,8 @@ class ExpConfig(object):
         self.test_n_pz = 1000                                       # :69
         self.test_batch_size = {'A': 64, 'B': 64, 'M': 1}[arch]     # :71, dmm_bernouli_fashion.py:82
         self.sample_n_z = 100
+        self.use_flow = False                                       # dmm_bernouli_fashion.py:69 ("VAEPP+Flow")
+        self.nf_layers = 20                                         # :48
         # capacities of this build (not reference fields)
         self.max_batch = 64
         self.max_chunk = 512
@@ -69,6 +71,7 @@ class ExpConfig(object):
         c.smallest_step = float(self.smallest_step)
         c.len_train = int(self.len_train)
         c.precise = int(self.precise)
+        c.nf_layers = int(self.nf_layers) if self.use_flow else 0
         return c
 
 

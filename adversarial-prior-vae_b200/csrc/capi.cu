@@ -240,6 +240,13 @@ int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev,
     }
     for (long long s0 = 0; s0 < S; s0 += m.cfg.max_chunk) {
         const int n = (int)std::min<long long>(m.cfg.max_chunk, S - s0);
+        if (m.cfg.nf_layers > 0)
+            LCHECK(launch_sample_z_flow(m.q_mu, m.q_logstd, eps + s0 * d, n, (int)(s0 % B), B, d, m.cfg.min_logstd_of_q,
+                                        m.cfg.use_truncated, m.flow_w, m.flow_uhat, m.flow_b, m.flow_wu, m.cfg.nf_layers,
+                                        nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f,
+                                        m.log_q + s0, m.log_pn + s0, stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
+                   "sample_z_flow");
+        else
         LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps + s0 * d, n, (int)(s0 % B), B, d, m.cfg.min_logstd_of_q,
                                m.cfg.use_truncated, nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(),
                                m.z_cpad(), 0.2f, m.log_q + s0, m.log_pn + s0, stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
@@ -278,6 +285,11 @@ int apvae_sample_z(apvae_handle* h, const float* x_origin_dev, int B, int K, con
     }
     float* lq = log_q_dev;
     if (!lq) { if (!m.ensure_sample_buffers((size_t)S)) return APVAE_ERR_CUDA; lq = m.log_q; }
+    if (m.cfg.nf_layers > 0)
+        LCHECK(launch_sample_z_flow(m.q_mu, m.q_logstd, eps, (int)S, 0, B, d, m.cfg.min_logstd_of_q, m.cfg.use_truncated,
+                                    m.flow_w, m.flow_uhat, m.flow_b, m.flow_wu, m.cfg.nf_layers, z_dev, nullptr, nullptr, 0, 1,
+                                    0, 0.2f, lq, log_pn_dev, stream), "sample_z_flow");
+    else
     LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps, (int)S, 0, B, d, m.cfg.min_logstd_of_q, m.cfg.use_truncated, z_dev,
                            nullptr, nullptr, 0, 1, 0, 0.2f, lq, log_pn_dev, stream), "sample_z");
     return APVAE_OK;

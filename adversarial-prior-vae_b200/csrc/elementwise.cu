@@ -116,6 +116,77 @@ __global__ void sample_z_kernel(const float* __restrict__ mu, const float* __res
     }
 }
 
+// one warp per sample, z held in registers (PL elements per lane) while the flow layers run
+template <int PL>
+__global__ void sample_z_flow_kernel(const float* __restrict__ mu, const float* __restrict__ logstd,
+                                     const float* __restrict__ eps, int S, int s0, int B, int d, float min_logstd,
+                                     int truncated, const float* __restrict__ flow_w, const float* __restrict__ flow_uhat,
+                                     const float* __restrict__ flow_b, const float* __restrict__ flow_wu, int nf,
+                                     float* __restrict__ z_f32, __nv_bfloat16* __restrict__ z_raw,
+                                     __nv_bfloat16* __restrict__ z_act, long long zstride, int zc, int cpad,
+                                     float alpha, float* __restrict__ log_q, float* __restrict__ log_pn,
+                                     __nv_bfloat16* __restrict__ z_raw_lo, __nv_bfloat16* __restrict__ z_act_lo) {
+    const int lane = threadIdx.x & 31;
+    const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (s >= S) return;
+    const int b = (s0 + s) % B;
+    float z[PL];
+    float lq = 0.f;
+#pragma unroll
+    for (int i = 0; i < PL; ++i) {
+        const int j = lane + 32 * i;
+        z[i] = 0.f;
+        if (j < d) {
+            const float e = eps[(size_t)s * d + j];
+            const float m = mu[(size_t)b * d + j];
+            const float ls = fmaxf(logstd[(size_t)b * d + j], min_logstd);
+            z[i] = m + expf(ls) * e;
+            const float t = (z[i] - m) * expf(-ls);
+            lq += -0.5f * kLog2Pi - ls - 0.5f * t * t - (truncated ? kLogTruncArea : 0.f);
+        }
+    }
+    float logdet = 0.f;
+    for (int l = 0; l < nf; ++l) {
+        const float* w = flow_w + (size_t)l * d;
+        const float* uh = flow_uhat + (size_t)l * d;
+        float dot = 0.f;
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) dot += __ldg(w + j) * z[i];
+        }
+        dot = warp_sum(dot);                                   // every lane holds the total
+        const float t = tanhf(dot + __ldg(flow_b + l));
+#pragma unroll
+        for (int i = 0; i < PL; ++i) {
+            const int j = lane + 32 * i;
+            if (j < d) z[i] += __ldg(uh + j) * t;
+        }
+        logdet += logf(fabsf(1.f + (1.f - t * t) * __ldg(flow_wu + l)));
+    }
+    float lp = 0.f;
+#pragma unroll
+    for (int i = 0; i < PL; ++i) {
+        const int j = lane + 32 * i;
+        if (j < d) {
+            const float v = z[i];
+            lp += -0.5f * kLog2Pi - 0.5f * v * v;
+            if (z_f32) z_f32[(size_t)s * d + j] = v;
+            const size_t idx = (size_t)s * zstride + (size_t)(j / zc) * cpad + (j % zc);
+            if (z_raw) z_raw[idx] = __float2bfloat16(v);
+            if (z_act) z_act[idx] = __float2bfloat16(lrelu(v, alpha));
+            if (z_raw_lo) z_raw_lo[idx] = __float2bfloat16(v - __bfloat162float(__float2bfloat16(v)));
+            if (z_act_lo) { const float a = lrelu(v, alpha); z_act_lo[idx] = __float2bfloat16(a - __bfloat162float(__float2bfloat16(a))); }
+        }
+    }
+    lq = warp_sum(lq);
+    lp = warp_sum(lp);
+    if (lane == 0) {
+        if (log_q) log_q[s] = lq - logdet;
+        if (log_pn) log_pn[s] = lp;
+    }
+}
+
 // one block per sample
 __global__ void pixel_logprob_kernel(const float* __restrict__ head, int ld, const float* __restrict__ x,
                                      int S, int s0, int B, int HW, int C, int bernoulli, int uniform_scale,
@@ -478,6 +549,26 @@ int launch_sample_z(const float* mu, const float* logstd, const float* eps, int 
                                                         z_f32, (__nv_bfloat16*)z_raw, (__nv_bfloat16*)z_act,
                                                         zstride, zc, cpad, alpha, log_q, log_pn,
                                                         (__nv_bfloat16*)z_raw_lo, (__nv_bfloat16*)z_act_lo);
+    return (int)cudaGetLastError();
+}
+
+int launch_sample_z_flow(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
+                         float min_logstd, int truncated, const float* flow_w, const float* flow_uhat,
+                         const float* flow_b, const float* flow_wu, int nf, float* z_f32, void* z_raw, void* z_act,
+                         long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn, void* stream,
+                         void* z_raw_lo, void* z_act_lo) {
+    if (S <= 0) return 0;
+    if (d > 512 || !mu || !logstd) return (int)cudaErrorInvalidValue;
+#define APVAE_FLOW_LAUNCH(PL) \
+    sample_z_flow_kernel<PL><<<(S + 7) / 8, 256, 0, st(stream)>>>(mu, logstd, eps, S, s0, B, d, min_logstd, truncated, \
+        flow_w, flow_uhat, flow_b, flow_wu, nf, z_f32, (__nv_bfloat16*)z_raw, (__nv_bfloat16*)z_act, zstride, zc, cpad, \
+        alpha, log_q, log_pn, (__nv_bfloat16*)z_raw_lo, (__nv_bfloat16*)z_act_lo)
+    if (d <= 32) APVAE_FLOW_LAUNCH(1);
+    else if (d <= 64) APVAE_FLOW_LAUNCH(2);
+    else if (d <= 128) APVAE_FLOW_LAUNCH(4);
+    else if (d <= 256) APVAE_FLOW_LAUNCH(8);
+    else APVAE_FLOW_LAUNCH(16);
+#undef APVAE_FLOW_LAUNCH
     return (int)cudaGetLastError();
 }
 

@@ -21,6 +21,14 @@ int launch_sample_z(const float* mu, const float* logstd, const float* eps, int 
                     float min_logstd, int truncated, float* z_f32, void* z_raw, void* z_act,
                     long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn,
                     void* stream, void* z_raw_lo = nullptr, void* z_act_lo = nullptr);
+// The same draw pushed through `nf` planar normalizing-flow layers (reference: layers/flows/planar_nf.py:108-135,
+// distributions/flow.py:118-150): z <- z + u_hat tanh(w.z + b), log q = log q0(z0) - sum_l log|1 + (1 - tanh^2) w.u_hat|.
+// flow_w / flow_uhat: [nf][d]; flow_b / flow_wu: [nf].  d <= 512.
+int launch_sample_z_flow(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
+                         float min_logstd, int truncated, const float* flow_w, const float* flow_uhat,
+                         const float* flow_b, const float* flow_wu, int nf, float* z_f32, void* z_raw, void* z_act,
+                         long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn, void* stream,
+                         void* z_raw_lo = nullptr, void* z_act_lo = nullptr);
 
 // log p(x|z) summed over pixels (reference: distributions/discretized.py:198-259 with the
 // dmm_cifar10.py:612-619 parameters; Bernoulli variant dmm_bernouli_fashion.py:619-626).

@@ -118,6 +118,8 @@ public:
     Pair q_in;                 // [max_batch, H, W, 16]
     float* q_mu = nullptr;     // [max_batch, z_dim]
     float* q_logstd = nullptr;
+    // planar posterior flow (nf_layers > 0): w [L][d], u_hat [L][d], b [L], w . u_hat [L]
+    float* flow_w = nullptr; float* flow_uhat = nullptr; float* flow_b = nullptr; float* flow_wu = nullptr;
     Pair g_in;                 // decoder input
     float* head_f32 = nullptr; // [max_chunk*HW, head_ld]
     Pair d_in;                 // [max_chunk, H, W, 16]

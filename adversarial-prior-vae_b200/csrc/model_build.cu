@@ -1,6 +1,9 @@
 // Program construction and forward drivers for q_net / G_theta / D_psi.
 #include <cuda_runtime.h>
 #include <string.h>
+#include <math.h>
+#include <string>
+#include <vector>
 #include "kernels.h"
 #include "model.h"
 
@@ -13,6 +16,37 @@ bool Model::build_q() {
     q_mu = alloc_f32((size_t)cap * cfg.z_dim);
     q_logstd = alloc_f32((size_t)cap * cfg.z_dim);
     if (!q_in.raw.ptr || !q_in.act.ptr || !q_mu || !q_logstd) return false;
+    if (cfg.nf_layers > 0) {
+        // u_hat = u + (m(w.u) - w.u) w / |w|^2, m(a) = -1 + softplus(a)  (planar_nf.py:104-106); the log-determinant
+        // needs only w . u_hat per layer: det = 1 + (1 - tanh^2(w.x + b)) (w . u_hat)  (:127-131)
+        const int L = cfg.nf_layers, d = cfg.z_dim;
+        std::vector<float> hw((size_t)L * d), hu((size_t)L * d), hb(L), hwu(L);
+        for (int l = 0; l < L; ++l) {
+            const std::string pre = L == 1 ? std::string("posterior_flow/") : "posterior_flow/_" + std::to_string(l) + "/";
+            const HostArr& w = weights[pre + "w"];
+            const HostArr& u = weights[pre + "u"];
+            const HostArr& b = weights[pre + "b"];
+            double wu = 0, ww = 0;
+            for (int j = 0; j < d; ++j) { wu += (double)w.v[j] * u.v[j]; ww += (double)w.v[j] * w.v[j]; }
+            const double sp = wu > 30 ? wu : log1p(exp(wu));
+            const double coef = (-1.0 + sp - wu) / ww;
+            double wuh = 0;
+            for (int j = 0; j < d; ++j) {
+                const double uh = u.v[j] + coef * w.v[j];
+                hw[(size_t)l * d + j] = w.v[j];
+                hu[(size_t)l * d + j] = (float)uh;
+                wuh += (double)w.v[j] * uh;
+            }
+            hb[l] = b.v[0];
+            hwu[l] = (float)wuh;
+        }
+        flow_w = alloc_f32(hw.size()); flow_uhat = alloc_f32(hu.size()); flow_b = alloc_f32(L); flow_wu = alloc_f32(L);
+        if (!flow_w || !flow_uhat || !flow_b || !flow_wu) return false;
+        cudaMemcpy(flow_w, hw.data(), hw.size() * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(flow_uhat, hu.data(), hu.size() * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(flow_b, hb.data(), L * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(flow_wu, hwu.data(), L * 4, cudaMemcpyHostToDevice);
+    }
     const std::vector<BlockSpec> blocks = q_blocks(cfg);
     Pair h = q_in;
     for (size_t i = 0; i < blocks.size(); ++i) {

@@ -58,6 +58,8 @@ bool validate_config(const apvae_config& c, std::string* err) {
         if (c.x_h != want || c.x_w != want) return fail("arch B: x_shape must be 64x64 (celebA) or 32x32");
     }
     if (c.max_batch <= 0 || c.max_chunk <= 0) return fail("max_batch / max_chunk must be positive");
+    if (c.nf_layers < 0 || c.nf_layers > 256) return fail("nf_layers must be in [0, 256]");
+    if (c.nf_layers > 0 && c.z_dim > 512) return fail("posterior flow: z_dim <= 512");
     return true;
 }
 
@@ -135,6 +137,14 @@ std::vector<WeightInfo> weight_schema(const apvae_config& c) {
     out.push_back({"D_psi/level_-2/bias", {64}});
     out.push_back({"D_psi/level_-1/kernel", {64, 1}});
     out.push_back({"D_psi/level_-1/bias", {1}});
+    // posterior flow: planar_normalizing_flows(config.nf_layers, name='posterior_flow') (dmm_cifar10.py:850-851;
+    // variable scopes planar_nf.py:208-221, variables w [1,d], b [1], u [1,d] :79-103)
+    for (int i = 0; i < c.nf_layers; ++i) {
+        const std::string pre = c.nf_layers == 1 ? std::string("posterior_flow/") : "posterior_flow/_" + std::to_string(i) + "/";
+        out.push_back({pre + "w", {1, d}});
+        out.push_back({pre + "b", {1}});
+        out.push_back({pre + "u", {1, d}});
+    }
     return out;
 }
 

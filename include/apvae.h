@@ -55,6 +55,10 @@ typedef struct apvae_config {
     int precise;                    /* 1: split-precision G_theta / D_psi (activations and kernels as hi + lo bf16 pairs,
                                      * three tensor-core products per term, fp32 accumulate): fp32-class energies for the
                                      * sampler at 3x the MMA work.  0: plain bf16 operands (evaluation default). */
+    int nf_layers;                  /* config.nf_layers when config.use_flow (dmm_bernouli_fashion.py:48,69,468-474): q(z|x) is
+                                     * a FlowDistribution, the base Normal / TruncatedNormal draw pushed through that many planar
+                                     * normalizing-flow layers (layers/flows/planar_nf.py); weights `posterior_flow/_i/{w,b,u}`
+                                     * (`posterior_flow/{w,b,u}` for one layer).  0: no flow (every script's default). */
 } apvae_config;
 
 typedef struct apvae_handle apvae_handle;

@@ -12,6 +12,7 @@ __all__ = [
     'normal_log_prob', 'truncated_normal_log_prob', 'std_normal_log_prob',
     'discretized_logistic_log_prob', 'bernoulli_log_prob_from_mean',
     'importance_sampling_log_likelihood', 'elbo_objective',
+    'planar_flow_u_hat', 'planar_flow_transform', 'planar_flows_transform',
     'TRUNCATED_AREA',
 ]
 
@@ -130,6 +131,43 @@ def bernoulli_log_prob_from_mean(x, x_mean, group_ndims=0):
     logits = np.log(p) - np.log1p(-p)
     lp = x * logits - softplus(logits)
     return _reduce_group(lp, group_ndims)
+
+
+def planar_flow_u_hat(w, u):
+    """u_hat = u + (m(w.u) - w.u) w / |w|^2, m(a) = -1 + log(1 + e^a)
+    (layers/flows/planar_nf.py:104-106; w, u: [1, d])."""
+    w, u = np.asarray(w, dtype=np.float64), np.asarray(u, dtype=np.float64)
+    wu = np.dot(w, u.T)                                   # [1, 1]
+    return u + (-1.0 + softplus(wu) - wu) * w / np.sum(np.square(w))
+
+
+def planar_flow_transform(x, w, b, u):
+    """One PlanarNormalizingFlow layer (planar_nf.py:112-135): x [..., d] ->
+    (y [..., d], log_det [...]):  y = x + u_hat tanh(w.x + b),
+    log_det = log|1 + ((1 - tanh^2) w) . u_hat|."""
+    u_hat = planar_flow_u_hat(w, u)
+    w = np.asarray(w, dtype=np.float64)
+    x = np.asarray(x, dtype=np.float64)
+    xf = x.reshape(-1, x.shape[-1])
+    wxb = np.dot(xf, w.T) + np.asarray(b, dtype=np.float64)   # [?, 1]
+    t = np.tanh(wxb)
+    y = xf + u_hat * t
+    phi = (1.0 - np.square(t)) * w                        # [?, d]
+    log_det = np.log(np.abs(1.0 + np.dot(phi, u_hat.T)))  # [?, 1]
+    return y.reshape(x.shape), log_det[:, 0].reshape(x.shape[:-1])
+
+
+def planar_flows_transform(x, params, n_layers, scope='posterior_flow'):
+    """planar_normalizing_flows(n_layers, name=scope) as a SequentialFlow
+    (planar_nf.py:208-221; sequential.py sums the layers' log-dets).
+    Variables scope/_i/{w,b,u}, or scope/{w,b,u} for a single layer."""
+    y = np.asarray(x, dtype=np.float64)
+    log_det = np.zeros(y.shape[:-1])
+    for i in range(n_layers):
+        pre = scope + '/' if n_layers == 1 else '%s/_%d/' % (scope, i)
+        y, ld = planar_flow_transform(y, params[pre + 'w'], params[pre + 'b'], params[pre + 'u'])
+        log_det = log_det + ld
+    return y, log_det
 
 
 def importance_sampling_log_likelihood(log_joint, latent_log_prob, axis):

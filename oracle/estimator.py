@@ -10,7 +10,7 @@ from .dists import (normal_log_prob, truncated_normal_log_prob,
                     std_normal_log_prob, discretized_logistic_log_prob,
                     bernoulli_log_prob_from_mean, log_mean_exp, log_sum_exp,
                     importance_sampling_log_likelihood, elbo_objective,
-                    maybe_clip_value, sigmoid)
+                    maybe_clip_value, sigmoid, planar_flows_transform)
 from .nets import q_net, G_theta, D_psi, G_theta_input_grad, D_psi_input_grad
 
 __all__ = ['log_px_given_z', 'energy_terms', 'eval_batch', 'prior_branch',
@@ -66,6 +66,11 @@ def eval_batch(cfg, params, x, x_origin, eps, xi_raw=0.0, beta=0.0, log_Z=1.0):
         log_q = truncated_normal_log_prob(z, mu, logstd, 1)
     else:
         log_q = normal_log_prob(z, mu, logstd, 1)
+    if cfg.use_flow:
+        # FlowDistribution(z_distribution, posterior_flow) (dmm_bernouli_fashion.py:468-474):
+        # y = flow(x), log q(y) = log q0(x) - log_det (distributions/flow.py:118-150)
+        z, log_det = planar_flows_transform(z, params, cfg.nf_layers)
+        log_q = log_q - log_det
     log_px, x_mean = log_px_given_z(cfg, params, x, z, beta)
     log_pn = std_normal_log_prob(z)
     d_g = D_psi(cfg, params, x_mean)                                # pure_energy, :175

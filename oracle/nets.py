@@ -62,6 +62,8 @@ class OracleConfig(object):
         self.epsilon = -20.0
         self.initial_xi = 0.0
         self.test_n_pz = 1000
+        self.use_flow = False                                 # dmm_bernouli_fashion.py:69
+        self.nf_layers = 20                                   # :48
         for k, v in kw.items():
             if not hasattr(self, k):
                 raise AttributeError(k)
@@ -191,6 +193,12 @@ def weight_shapes(cfg):
     shapes['D_psi/level_-2/bias'] = (64,)
     shapes['D_psi/level_-1/kernel'] = (64, 1)                # :561
     shapes['D_psi/level_-1/bias'] = (1,)
+    if cfg.use_flow:                                         # planar_nf.py:79-103,208-221
+        for i in range(cfg.nf_layers):
+            pre = 'posterior_flow/' if cfg.nf_layers == 1 else 'posterior_flow/_%d/' % i
+            shapes[pre + 'w'] = (1, cfg.z_dim)
+            shapes[pre + 'b'] = (1,)
+            shapes[pre + 'u'] = (1, cfg.z_dim)
     return shapes
 
 
@@ -212,6 +220,10 @@ def init_weights(cfg, seed=1234, dtype=np.float64, bias_std=0.1, head_gain=1.0):
                 fan_in, fan_out = shp
             std = np.sqrt(2.0 / (fan_in + fan_out))
             w = rng.normal(0.0, std, size=shp)
+        elif name.startswith('posterior_flow/'):
+            # the reference draws w, u ~ N(0, 0.01^2) (planar_nf.py:37-41), which leaves the flow at the
+            # identity to 1e-4; the synthetic test weights are larger so that the layers do something
+            w = rng.normal(0.0, 0.1 if name.endswith('/b') else 1.0 / np.sqrt(shp[-1]) * 2.0, size=shp)
         else:
             w = rng.normal(0.0, bias_std, size=shp)
         params[name] = w.astype(np.float32).astype(dtype)

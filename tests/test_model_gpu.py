@@ -414,3 +414,48 @@ def test_image_energy_gradient_ood_indicator(case):
     assert np.abs(s - (g ** 2).sum(axis=(1, 2, 3))).max() < 1e-4 * n_o.max()      # the reduction itself
     assert (np.abs(s - n_o) / n_o).max() < 2e-1, (s, n_o)
     m.close()
+
+
+@pytest.mark.parametrize('case', ['M40', 'Bcifar'])
+def test_flow_posterior_matches_oracle(case):
+    """q(z|x) as a FlowDistribution over planar normalizing flows (dmm_bernouli_fashion.py:468-474,
+    layers/flows/planar_nf.py): z, log q from apvae_sample_z and the whole estimator from apvae_is_nll."""
+    arch, kw, B, K = CASES[case]
+    kw = dict(kw, use_flow=True, nf_layers=4)
+    import apvae
+    from apvae.model import ExpConfig, Model
+    ocfg = O.OracleConfig(arch, **kw)
+    params = O.init_weights(ocfg)
+    if arch == 'M':
+        params['G_theta/feature_map_mean_to_pixel/kernel'] = params['G_theta/feature_map_mean_to_pixel/kernel'] * 0.25
+        params['G_theta/feature_map_mean_to_pixel/bias'] = params['G_theta/feature_map_mean_to_pixel/bias'] * 0 + 0.55
+    cfg = ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim, max_batch=8, max_chunk=8, use_flow=True, nf_layers=4)
+    m = Model(cfg, params)
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    m.set_scalars(0.3, -0.5, 2.5)
+    want = O.eval_batch(ocfg, params, x, x_origin, eps, xi_raw=0.3, beta=-0.5, log_Z=2.5)
+    z, lq, lpn = m.sample_z(x_origin, K, eps=eps)
+    z = z.cpu().numpy().astype(np.float64)
+    lq = lq.cpu().numpy().astype(np.float64)
+    # the flow kernel alone: the oracle's flow on OUR encoder's (mu, logstd) must agree to fp32 rounding
+    mu, ls = (t.cpu().numpy().astype(np.float64) for t in m.encode(x_origin))
+    z0 = mu + np.exp(ls) * eps
+    lq0 = (O.truncated_normal_log_prob if ocfg.use_truncated else O.normal_log_prob)(z0, mu, ls, 1)
+    zf, ld = O.planar_flows_transform(z0, params, 4)
+    assert np.abs(z - zf).max() < 1e-4 and np.abs(ld).max() > 1e-2
+    assert np.abs(lq - (lq0 - ld)).max() < 1e-3
+    assert np.abs(lpn.cpu().numpy() - O.std_normal_log_prob(zf)).max() < 1e-3
+    # end to end against the float64 oracle (its encoder differs from the bf16 one by ~1e-2 in mu)
+    assert np.abs(z - want['z']).max() < 5e-2
+    assert np.abs(lq - want['log_q']).max() < 1e-3 * np.abs(want['log_q']).max() + 2e-2
+    got = m.is_nll(x, K, x_origin=x_origin, eps=eps, per_sample=True)
+    g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
+    assert np.abs(g['log_q'] - want['log_q']).max() < 1e-3 * np.abs(want['log_q']).max() + 2e-2
+    for name in ('ele_test_ll', 'ele_test_lb', 'ele_adv_test_ll', 'ele_adv_test_lb'):
+        rel = np.abs(g[name] - want[name]) / np.abs(want[name])
+        assert rel.max() < NLL_RTOL, (name, g[name], want[name])
+    # without the flow weights the build must refuse, loudly
+    bad = {k: v for k, v in params.items() if not k.startswith('posterior_flow/_3/')}
+    with pytest.raises(Exception):
+        Model(cfg, bad)
+    m.close()

@@ -182,3 +182,77 @@ def test_eval_batch_self_consistency_and_weight_schema():
     out = O.eval_batch(cfg, params, x, x, np.clip(rs.normal(size=(3, 2, 8)), -2, 2))
     assert np.all(out['ele_test_lb'] <= out['ele_test_ll'] + 1e-9)       # Jensen: ELBO <= IS-LL
     assert np.all(out['ele_adv_test_lb'] <= out['ele_adv_test_ll'] + 1e-9)
+
+
+def test_planar_flow_follows_the_reference_test_and_its_jacobian():
+    """tests/layers/flows/test_planar_nf.py:16-71 restated: u_hat against the closed form the reference test uses, the
+    transform against the test's own numpy `transform` on x = arange(30).reshape(2, 3, 5); plus two checks the
+    reference does not have: the invertibility condition w.u_hat >= -1 and log_det against the determinant of a
+    finite-difference Jacobian."""
+    rs = np.random.RandomState(1234)
+    n = 5
+    w, u, b = rs.normal(size=(1, n)), rs.normal(size=(1, n)), rs.normal(size=(1,))
+    m = lambda a: -1 + np.log(1 + np.exp(a))
+    wu = np.dot(w, u.T)
+    u_hat = O.planar_flow_u_hat(w, u)
+    np.testing.assert_allclose(u + w * (m(wu) - wu) / np.sum(w ** 2), u_hat)           # test_u_hat
+    assert np.dot(w, u_hat.T).item() >= -1.0
+
+    def transform(x, u, w, b):                                                          # test_transform's reference
+        wxb = np.dot(x, w.T) + b
+        y = x + u * np.tanh(wxb)
+        tanh_wxb = np.tanh(wxb)
+        phi = (1 - tanh_wxb ** 2) * w
+        log_det = np.log(np.abs(1 + np.dot(phi, u.T)))
+        return y, np.squeeze(log_det, -1)
+
+    x = np.arange(30, dtype=np.float64).reshape([2, 3, n]) / 10.0
+    y, log_det = transform(x, u_hat, w, b)
+    y2, log_det2 = O.planar_flow_transform(x, w, b, u)
+    np.testing.assert_allclose(y2, y, rtol=1e-12)
+    np.testing.assert_allclose(log_det2, log_det, rtol=1e-12)
+    # finite-difference Jacobian of one row
+    x0 = x[1, 2]
+    J = np.zeros((n, n))
+    for j in range(n):
+        e = np.zeros(n); e[j] = 1e-6
+        J[:, j] = (O.planar_flow_transform(x0 + e, w, b, u)[0] - O.planar_flow_transform(x0 - e, w, b, u)[0]) / 2e-6
+    assert abs(np.log(abs(np.linalg.det(J))) - log_det2[1, 2]) < 1e-6
+    # sequential flow: log-dets add, variable scopes posterior_flow/_i/
+    params = {}
+    for i in range(3):
+        params['posterior_flow/_%d/w' % i] = rs.normal(size=(1, n))
+        params['posterior_flow/_%d/u' % i] = rs.normal(size=(1, n))
+        params['posterior_flow/_%d/b' % i] = rs.normal(size=(1,))
+    ys, lds = O.planar_flows_transform(x, params, 3)
+    yy, ld = x, 0.0
+    for i in range(3):
+        yy, l1 = O.planar_flow_transform(yy, params['posterior_flow/_%d/w' % i], params['posterior_flow/_%d/b' % i],
+                                         params['posterior_flow/_%d/u' % i])
+        ld = ld + l1
+    np.testing.assert_allclose(ys, yy)
+    np.testing.assert_allclose(lds, ld)
+
+
+def test_flow_posterior_in_the_evaluation_graph_and_schema():
+    """use_flow = True (dmm_bernouli_fashion.py:468-474): q(z|x) = FlowDistribution(TruncatedNormal, planar flows);
+    log q = log q0(z0) - sum log_det; the C library's schema lists posterior_flow/_i/{w,b,u}."""
+    from apvae.model import ExpConfig, weight_schema
+    cfg = O.OracleConfig('M', z_dim=8, use_flow=True, nf_layers=3)
+    ours = dict(weight_schema(ExpConfig('M', z_dim=8, use_flow=True, nf_layers=3)))
+    assert ours == {k: tuple(v) for k, v in O.weight_shapes(cfg).items()}
+    assert ours['posterior_flow/_2/w'] == (1, 8) and ours['posterior_flow/_0/b'] == (1,)
+    one = dict(weight_schema(ExpConfig('M', z_dim=8, use_flow=True, nf_layers=1)))
+    assert 'posterior_flow/w' in one and 'posterior_flow/_0/w' not in one
+    assert not any(k.startswith('posterior_flow') for k, _ in weight_schema(ExpConfig('M', z_dim=8)))
+    params = O.init_weights(cfg)
+    rs = np.random.RandomState(0)
+    x = (rs.uniform(size=(2, 28, 28, 1)) < 0.5).astype(np.float64)
+    eps = np.clip(rs.normal(size=(3, 2, 8)), -2, 2)
+    out = O.eval_batch(cfg, params, x, x, eps)
+    base = O.eval_batch(O.OracleConfig('M', z_dim=8), params, x, x, eps)
+    z, ld = O.planar_flows_transform(base['z'], params, 3)
+    np.testing.assert_allclose(out['z'], z)
+    np.testing.assert_allclose(out['log_q'], base['log_q'] - ld)
+    assert np.abs(out['z'] - base['z']).max() > 1e-2                                     # the synthetic flow is not the identity
+    assert np.all(out['ele_test_lb'] <= out['ele_test_ll'] + 1e-9)
