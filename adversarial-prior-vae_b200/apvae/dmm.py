@@ -169,6 +169,13 @@ class PNet(object):
         raise KeyError(name)
 
 
+class PlanarFlows(object):
+    def __init__(self, n_layers, name):
+        if n_layers < 1:
+            raise ValueError('n_layers must be positive')          # validate_positive_int_arg, planar_nf.py:200
+        self.n_layers, self.name = n_layers, name
+
+
 class Script(object):
     """Namespace of one experiment script bound to a Model: q_net / p_net / G_theta / D_psi."""
 
@@ -179,9 +186,17 @@ class Script(object):
     def w_xi(self):
         return self.config.pull_back_energy_weight / (1.0 + math.exp(-self.model.xi_raw))
 
+    def planar_normalizing_flows(self, n_layers=1, name='posterior_flow'):
+        """spt.layers.planar_normalizing_flows(config.nf_layers, name='posterior_flow') (dmm_cifar10.py:850-851): a
+        descriptor only; the flow's variables (`posterior_flow/_i/{w,b,u}`) live in the model's weight dict."""
+        return PlanarFlows(int(n_layers), name)
+
     def q_net(self, x, posterior_flow=None, observed=None, n_z=None, eps=None, seed=0):
-        if posterior_flow is not None:
-            raise NotImplementedError('posterior flows (use_flow=True) are outside the built path')
+        # like the reference (dmm_bernouli_fashion.py:468-474; dmm_cifar10.py's q_net ignores the argument), the flow is
+        # applied iff config.use_flow; the handle was then created with nf_layers flow layers
+        if self.config.use_flow and isinstance(posterior_flow, PlanarFlows) and posterior_flow.n_layers != self.config.nf_layers:
+            raise ValueError('posterior_flow has %d layers, the model was built with nf_layers=%d'
+                             % (posterior_flow.n_layers, self.config.nf_layers))
         return QNet(self, x, n_z, eps, seed)
 
     def p_net(self, observed=None, n_z=None, beta=1.0, mcmc_iterator=0, log_Z=0.0, initial_z=None, mcmc_alpha=None,
