@@ -135,6 +135,22 @@ class Model(object):
 
     __del__ = close
 
+    @classmethod
+    def from_checkpoint(cls, config, save_path, device=0):
+        """The model restored from a reference checkpoint (`tf.train.Saver` V2 files written by tfsnippet's
+        CheckpointSaver, scaffold/checkpoint.py:230-253): `save_path` is a checkpoint prefix or a directory holding a
+        `checkpoint` state file (tf.train.latest_checkpoint).  xi / beta / log_Z come from the checkpoint when present."""
+        import os
+        from . import checkpoint as ck
+        prefix = save_path
+        if os.path.isdir(save_path):
+            prefix = ck.latest_checkpoint(save_path)
+            if prefix is None:
+                raise IOError('no checkpoint state in %r' % (save_path,))
+        weights, scalars = ck.model_weights_from_checkpoint(prefix, config)
+        return cls(config, weights, device=device, xi_raw=scalars.get('xi_raw'), beta=scalars.get('beta', 0.0),
+                   log_Z=scalars.get('log_Z', 1.0))
+
     def set_scalars(self, xi_raw, beta, log_Z):
         """'p_net/xi' (pre-sigmoid), 'beta', 'log_Z' (dmm_cifar10.py:604-607,860,458-463)."""
         self.xi_raw, self.beta, self.log_Z = float(xi_raw), float(beta), float(log_Z)
