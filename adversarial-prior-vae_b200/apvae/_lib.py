@@ -36,7 +36,7 @@ class Config(C.Structure):
         ('uniform_scale', C.c_int), ('use_truncated', C.c_int), ('bernoulli', C.c_int),
         ('max_batch', C.c_int), ('max_chunk', C.c_int), ('enable_grad', C.c_int),
         ('smallest_step', C.c_float), ('len_train', C.c_int), ('precise', C.c_int),
-        ('nf_layers', C.c_int),
+        ('nf_layers', C.c_int), ('latent_gan', C.c_int),
     ]
 
 
@@ -102,6 +102,7 @@ _SYMBOLS = [
     ('apvae_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
     ('apvae_image_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
     ('apvae_sample_images', C.c_int, [_P, _P, C.c_int, _P, _P]),
+    ('apvae_latent_gan', C.c_int, [_P, _P, C.c_int, C.c_uint64, _P, _P]),
     ('apvae_fill_normal', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, C.c_int, _P]),
     ('apvae_fill_uniform', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, _P]),
     ('apvae_launch_count', C.c_int, [_P, C.POINTER(C.c_int64)]),

@@ -169,6 +169,25 @@ class PNet(object):
         raise KeyError(name)
 
 
+class POmegaNet(object):
+    """BayesianNet returned by p_omega_net (dmm_cifar10.py:623-639): 'f_z' has mean gan_z = G_omega(z_omega),
+    'x' has mean G_theta(gan_z)."""
+
+    def __init__(self, script, n_z, z_omega, seed):
+        self._script = script
+        self._fz = script.model.latent_gan(int(n_z), z_omega=z_omega, seed=seed)
+        self._xm = None
+
+    def __getitem__(self, name):
+        if name == 'f_z':
+            return _StochasticTensor(tensor=None, distribution=_Distribution(mean=self._fz))
+        if name == 'x':
+            if self._xm is None:
+                self._xm = self._script.model.decode(self._fz)
+            return _StochasticTensor(tensor=None, distribution=_Distribution(mean=self._xm))
+        raise KeyError(name)
+
+
 class PlanarFlows(object):
     def __init__(self, n_layers, name):
         if n_layers < 1:
@@ -203,6 +222,14 @@ class Script(object):
               seed=0):
         z = None if not observed else observed.get('z')
         return PNet(self, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed)
+
+    def p_omega_net(self, observed=None, n_z=None, beta=1.0, mcmc_iterator=0, log_Z=0.0, initial_z=None, z_omega=None,
+                    seed=0):
+        """gan_net = p_omega_net(n_z=sample_n_z, beta=beta); gan_z = gan_net['f_z'].distribution.mean
+        (dmm_cifar10.py:965-969).  Needs ExpConfig(latent_gan=True)."""
+        if n_z is None:
+            raise ValueError('p_omega_net needs n_z')
+        return POmegaNet(self, n_z, z_omega, seed)
 
     def G_theta(self, z, return_std=False):
         return self.model.decode(z, return_std=return_std)

@@ -44,6 +44,7 @@ class ExpConfig(object):
         self.sample_n_z = 100
         self.use_flow = False                                       # dmm_bernouli_fashion.py:69 ("VAEPP+Flow")
         self.nf_layers = 20                                         # :48
+        self.latent_gan = False    # also build G_omega (gan_z = the MALA chains' initial_z, dmm_cifar10.py:503-532,623-639)
         # capacities of this build (not reference fields)
         self.max_batch = 64
         self.max_chunk = 512
@@ -72,6 +73,7 @@ class ExpConfig(object):
         c.len_train = int(self.len_train)
         c.precise = int(self.precise)
         c.nf_layers = int(self.nf_layers) if self.use_flow else 0
+        c.latent_gan = int(self.latent_gan)
         return c
 
 
@@ -285,6 +287,14 @@ class Model(object):
         check(lib.apvae_mala(self._h, _ptr(z2), n, int(steps), float(alpha), _ptr(e), _ptr(uu), int(seed),
                              _ptr(he), _ptr(hp), _ptr(hr), _stream()), self._h)
         return dict(z=z2.reshape(shape), history_e_z=he, history_pure_e_z=hp, history_ratio=hr)
+
+    def latent_gan(self, n, z_omega=None, seed=0):
+        """gan_z = p_omega_net(n_z=n)['f_z'].distribution.mean (dmm_cifar10.py:623-635,967-969): G_omega applied to
+        z_omega ~ N(0, I_128) (fed [n,128] or drawn in-kernel) -> [n, z_dim], the `initial_z` of plot_samples' MALA loop."""
+        zo = self._f32(z_omega, (n, 128)) if z_omega is not None else None
+        out = self._empty(n, self.config.z_dim)
+        check(lib.apvae_latent_gan(self._h, _ptr(zo), int(n), int(seed), _ptr(out), _stream()), self._h)
+        return out
 
     def sample_images(self, z):
         """x_plots + np.round (dmm_cifar10.py:976-977,990,1067): uint8 [n,H,W,C]."""

@@ -325,6 +325,22 @@ int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t se
     return APVAE_OK;
 }
 
+int apvae_latent_gan(apvae_handle* h, const float* z_omega_dev, int n_total, uint64_t seed, float* z0_dev, void* stream) {
+    REQUIRE_BUILT(h);
+    if (!m.cfg.latent_gan) { m.err = "latent_gan: create the handle with latent_gan = 1"; return APVAE_ERR_STATE; }
+    if (n_total <= 0 || !z0_dev) { m.err = "latent_gan: bad arguments"; return APVAE_ERR_INVALID; }
+    for (int s0 = 0; s0 < n_total; s0 += m.cfg.max_chunk) {
+        const int n = std::min(m.cfg.max_chunk, n_total - s0);
+        const float* zo = z_omega_dev ? z_omega_dev + (size_t)s0 * 128 : nullptr;
+        if (!zo) {                                       // z ~ N(0, I_128) (dmm_cifar10.py:626-629)
+            LCHECK(launch_fill_normal(m.om_noise, (long long)n * 128, seed, (uint64_t)s0 * 128, 0, stream), "fill_normal");
+            zo = m.om_noise;
+        }
+        if (!m.latent_gan_chunk(zo, n, z0_dev + (size_t)s0 * m.cfg.z_dim, stream)) return APVAE_ERR_CUDA;
+    }
+    return APVAE_OK;
+}
+
 int apvae_sample_images(apvae_handle* h, const float* z_dev, int n_total, uint8_t* out_dev, void* stream) {
     REQUIRE_BUILT(h);
     if (n_total <= 0 || !z_dev || !out_dev) { m.err = "sample_images: bad arguments"; return APVAE_ERR_INVALID; }

@@ -31,6 +31,9 @@ struct WeightInfo {
 std::vector<BlockSpec> q_blocks(const apvae_config& c);
 std::vector<BlockSpec> g_blocks(const apvae_config& c);
 std::vector<BlockSpec> d_blocks(const apvae_config& c);
+std::vector<BlockSpec> omega_blocks(const apvae_config& c);
+int omega_base_h(const apvae_config& c);
+int omega_base_w(const apvae_config& c);
 std::vector<WeightInfo> weight_schema(const apvae_config& c);
 bool validate_config(const apvae_config& c, std::string* err);
 
@@ -83,6 +86,7 @@ public:
     // EnergyDistribution.sample's loop (dmm_cifar10.py:197-238)
     bool mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
               float* hist_e, float* hist_pure, float* hist_ratio, void* stream);
+    bool latent_gan_chunk(const float* z_omega_dev, int n, float* z0_dev, void* stream);   // n <= max_chunk
     bool critic_of_images(const float* x_dev, int N, float* d_out, void* stream);
     // D_psi(x), dD/dx [N,H,W,C] and its squared norm per image (evaluation/dmm_cifar.py:958-959); outputs may be null
     bool critic_grad_of_images(const float* x_dev, int N, float* d_out, float* grad_out, float* sqnorm_out, void* stream);
@@ -105,6 +109,11 @@ public:
 
     // device state
     Program q_prog, g_prog, d_prog;
+    Program om_prog;           // G_omega (latent_gan)
+    Tensor om_in;              // bf16 [max_chunk, 1, 1, 128]
+    float* om_out = nullptr;   // fp32 [max_chunk, z_dim]
+    float* om_noise = nullptr; // fp32 [max_chunk, 128] in-kernel z_omega draws
+    double macs_omega = 0;
     Program gd_prog, gg_prog;  // input-gradient programs: d D / d x_mean, then d x_mean / d z (enable_grad)
     double macs_grad = 0;
     Tensor d_seed;             // dD/d(flatten) = W64 w_last, one copy per sample (constant)
@@ -160,6 +169,7 @@ public:
     bool build_g();
     bool build_d();
     bool build_grad();
+    bool build_omega();
     bool grad_conv_block(const BlockTape& t, const Tensor& g_out, float* out_f32, int f32_ld, Tensor* g_in_out);
     bool grad_deconv_block(const BlockTape& t, const Tensor& g_out, float* out_f32, int f32_ld, Tensor* g_in_out);
     bool run_program(Program& prog, int n, void* stream);

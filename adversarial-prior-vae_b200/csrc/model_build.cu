@@ -9,6 +9,13 @@
 
 namespace apvae {
 
+#define KCHECK(call, what)                                                                        \
+    do {                                                                                          \
+        const int _e = (call);                                                                    \
+        ++launches;                                                                               \
+        if (_e != 0) return fail(std::string(what) + ": " + cudaGetErrorString((cudaError_t)_e)); \
+    } while (0)
+
 bool Model::build_q() {
     const int cap = cfg.max_batch;
     q_in.raw = alloc_act(cap, H(), W(), C());
@@ -187,6 +194,53 @@ bool Model::build_g() {
     return ok;
 }
 
+// G_omega (dmm_cifar10.py:503-532): dense(z_omega[128]) -> [oh, ow, 256] -> six resnet deconv blocks -> 1x1 conv to
+// z_channel at [2 oh, 2 ow]; flattened, that is gan_z = the initial_z of the MALA chains (:623-635,1061-1066).
+bool Model::build_omega() {
+    const int cap = cfg.max_chunk;
+    const int oh = omega_base_h(cfg), ow = omega_base_w(cfg);
+    const int feat = 256 * oh * ow;
+    om_in = alloc_act(cap, 1, 1, 128);
+    om_out = alloc_f32((size_t)cap * cfg.z_dim);
+    om_noise = alloc_f32((size_t)cap * 128);
+    Pair h;
+    h.raw = alloc_act(cap, oh, ow, 256);
+    h.act = alloc_act(cap, oh, ow, 256);
+    if (!om_in.ptr || !om_out || !om_noise || !h.raw.ptr || !h.act.ptr) return false;
+    {
+        Epilogue e; e.out_raw = h.raw.ptr; e.out_act = h.act.ptr; e.ldo = feat;
+        if (!dense_op(om_prog, "G_omega/level_0", om_in, 128, feat, e, cap, &macs_omega)) return false;
+    }
+    const std::vector<BlockSpec> blocks = omega_blocks(cfg);
+    for (size_t i = 0; i < blocks.size(); ++i) {
+        const bool last = (i + 1 == blocks.size());
+        Pair o;
+        if (!deconv_block(om_prog, "G_omega", blocks[i], h, true, !last, cap, &o, &macs_omega, nullptr)) return false;
+        h = o;
+    }
+    const int co = h.c(), zch = cfg.z_dim / (4 * oh * ow);
+    const HostArr* k = W_("G_omega/feature_map_mean_to_pixel/kernel", {1, 1, co, zch});
+    const HostArr* b = W_("G_omega/feature_map_mean_to_pixel/bias", {zch});
+    if (!k || !b) return false;
+    Epilogue e;
+    e.out_f32 = om_out; e.ld_f32 = zch; e.f32_cols = zch;     // [n][2oh][2ow][zch] == reshape_tail(x_mean, 3, (-1,))
+    std::vector<TermSpec> terms; std::vector<const void*> srcs;
+    if (!push_terms(terms, srcs, false, h.raw, h.raw_lo, false, 1, 1, co, zch, "G_omega/feature_map_mean_to_pixel/kernel", k, b))
+        return false;
+    return add_op(om_prog, "G_omega/feature_map_mean_to_pixel", terms, srcs, e, cap, &macs_omega);
+}
+
+bool Model::latent_gan_chunk(const float* z_omega_dev, int n, float* z0_dev, void* stream) {
+    if (om_prog.empty()) return fail("latent_gan: create the handle with latent_gan = 1");
+    KCHECK(launch_sample_z(nullptr, nullptr, z_omega_dev, n, 0, 1, 128, 0.f, 0, nullptr, om_in.ptr, nullptr, om_in.cp, 128,
+                           om_in.cp, 0.2f, nullptr, nullptr, stream), "pack z_omega");
+    if (!run_program(om_prog, n, stream)) return false;
+    const cudaError_t ce = cudaMemcpyAsync(z0_dev, om_out, (size_t)n * cfg.z_dim * sizeof(float), cudaMemcpyDeviceToDevice,
+                                           static_cast<cudaStream_t>(stream));
+    if (ce != cudaSuccess) return fail(std::string("latent_gan copy: ") + cudaGetErrorString(ce));
+    return true;
+}
+
 bool Model::build_d() {
     const int cap = cfg.max_chunk;
     std::vector<BlockTape>* tape = cfg.enable_grad ? &d_tape : nullptr;
@@ -222,6 +276,7 @@ bool Model::build() {
     if (built) return fail("weights already loaded (create a new handle to reload)");
     if (cudaSetDevice(dev.device) != cudaSuccess) return fail("cudaSetDevice failed");
     if (!build_q() || !build_g() || !build_d()) return false;
+    if (cfg.latent_gan && !build_omega()) return false;
     if (cfg.enable_grad && !build_grad()) return false;
     z_tmp = alloc_f32((size_t)cfg.max_chunk * cfg.z_dim);
     if (!z_tmp) return false;
@@ -244,12 +299,6 @@ bool Model::ensure_sample_buffers(size_t samples) {
     return true;
 }
 
-#define KCHECK(call, what)                                                                        \
-    do {                                                                                          \
-        const int _e = (call);                                                                    \
-        ++launches;                                                                               \
-        if (_e != 0) return fail(std::string(what) + ": " + cudaGetErrorString((cudaError_t)_e)); \
-    } while (0)
 
 bool Model::run_encoder(const float* x_dev, int B, void* stream) {
     if (B > cfg.max_batch) return fail("batch exceeds max_batch");

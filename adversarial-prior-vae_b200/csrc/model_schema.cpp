@@ -42,6 +42,13 @@ std::vector<BlockSpec> d_blocks(const apvae_config& c) {
             {"level_6", 64, 3, 2}};     // dmm_bernouli_fashion.py:561-565
 }
 
+std::vector<BlockSpec> omega_blocks(const apvae_config&) {      // dmm_cifar10.py:523-528 (same in dmm_for_sampling.py)
+    return {{"level_1", 256, 3, 1}, {"level_2", 256, 3, 1}, {"level_3", 128, 3, 2}, {"level_4", 64, 3, 1},
+            {"level_5", 32, 3, 1}, {"level_6", 16, 3, 1}};
+}
+int omega_base_h(const apvae_config& c) { return c.arch == APVAE_ARCH_A ? c.x_h / 8 : 4; }   // :516-521 / for_sampling :529-535
+int omega_base_w(const apvae_config& c) { return c.arch == APVAE_ARCH_A ? c.x_w / 8 : 4; }
+
 bool validate_config(const apvae_config& c, std::string* err) {
     auto fail = [&](const char* m) { if (err) *err = m; return false; };
     if (c.arch < 0 || c.arch > 2) return fail("arch must be 0 (A), 1 (B) or 2 (M)");
@@ -58,6 +65,11 @@ bool validate_config(const apvae_config& c, std::string* err) {
         if (c.x_h != want || c.x_w != want) return fail("arch B: x_shape must be 64x64 (celebA) or 32x32");
     }
     if (c.max_batch <= 0 || c.max_chunk <= 0) return fail("max_batch / max_chunk must be positive");
+    if (c.latent_gan) {
+        if (c.arch == APVAE_ARCH_M) return fail("latent_gan: arch M's weight-normalised dense G_omega is not built");
+        const int cells = 4 * omega_base_h(c) * omega_base_w(c);
+        if (c.z_dim % cells || c.z_dim / cells < 1) return fail("latent_gan: z_dim must be a multiple of the G_omega output grid");
+    }
     if (c.nf_layers < 0 || c.nf_layers > 256) return fail("nf_layers must be in [0, 256]");
     if (c.nf_layers > 0 && c.z_dim > 512) return fail("posterior flow: z_dim <= 512");
     return true;
@@ -137,6 +149,16 @@ std::vector<WeightInfo> weight_schema(const apvae_config& c) {
     out.push_back({"D_psi/level_-2/bias", {64}});
     out.push_back({"D_psi/level_-1/kernel", {64, 1}});
     out.push_back({"D_psi/level_-1/bias", {1}});
+    // G_omega (dmm_cifar10.py:503-532, dmm_for_sampling.py:519-546): dense 128 -> 256*oh*ow, six deconv blocks, 1x1 conv
+    if (c.latent_gan) {
+        const int oh = omega_base_h(c), ow = omega_base_w(c);
+        out.push_back({"G_omega/level_0/kernel", {128, (int64_t)256 * oh * ow}});
+        out.push_back({"G_omega/level_0/bias", {(int64_t)256 * oh * ow}});
+        const int co = block_schema(out, "G_omega", omega_blocks(c), 256, true);
+        const int64_t zch = c.z_dim / (4 * oh * ow);
+        out.push_back({"G_omega/feature_map_mean_to_pixel/kernel", {1, 1, co, zch}});
+        out.push_back({"G_omega/feature_map_mean_to_pixel/bias", {zch}});
+    }
     // posterior flow: planar_normalizing_flows(config.nf_layers, name='posterior_flow') (dmm_cifar10.py:850-851;
     // variable scopes planar_nf.py:208-221, variables w [1,d], b [1], u [1,d] :79-103)
     for (int i = 0; i < c.nf_layers; ++i) {

@@ -59,6 +59,9 @@ typedef struct apvae_config {
                                      * a FlowDistribution, the base Normal / TruncatedNormal draw pushed through that many planar
                                      * normalizing-flow layers (layers/flows/planar_nf.py); weights `posterior_flow/_i/{w,b,u}`
                                      * (`posterior_flow/{w,b,u}` for one layer).  0: no flow (every script's default). */
+    int latent_gan;                 /* 1: also build G_omega, the latent generator whose output `gan_z` is the initial_z of the
+                                     * MALA chains in plot_samples (dmm_cifar10.py:503-532,623-639,1061-1066; archs A and B):
+                                     * weights `G_omega/...`, entry point apvae_latent_gan. */
 } apvae_config;
 
 typedef struct apvae_handle apvae_handle;
@@ -153,6 +156,11 @@ int apvae_energy_grad(apvae_handle* h, const float* z_dev, int n, float* energy_
 int apvae_image_energy_grad(apvae_handle* h, const float* x_dev, int N, float* d_dev, float* grad_dev,
                             float* grad_sqnorm_dev, void* stream);
 /* x_plots (:976-977,990) + np.round: uint8 NHWC images from latents. */
+/* gan_z = G_omega(z_omega) (p_omega_net's 'f_z' mean, dmm_cifar10.py:623-635): z_omega_dev fp32 [n, 128] ~ N(0, I), or
+ * NULL for in-kernel Philox draws with `seed`; z0_dev fp32 [n, z_dim] receives the flattened [8, 8, z_channel] output,
+ * the `initial_z` handed to apvae_mala (:1061-1066).  Needs config.latent_gan = 1. */
+int apvae_latent_gan(apvae_handle* h, const float* z_omega_dev, int n, uint64_t seed, float* z0_dev, void* stream);
+
 int apvae_sample_images(apvae_handle* h, const float* z_dev, int n, uint8_t* out_dev, void* stream);
 
 /* Philox normals / uniforms the NULL-noise paths use (so tests can reproduce them). */

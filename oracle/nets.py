@@ -16,7 +16,7 @@ from .layers import (conv2d, deconv2d, dense, resnet_conv2d_block,
 from .dists import maybe_clip_value
 
 __all__ = ['OracleConfig', 'weight_shapes', 'init_weights', 'q_net',
-           'G_theta', 'D_psi', 'G_theta_input_grad', 'D_psi_input_grad']
+           'G_theta', 'D_psi', 'G_omega', 'G_theta_input_grad', 'D_psi_input_grad']
 
 
 class OracleConfig(object):
@@ -62,6 +62,7 @@ class OracleConfig(object):
         self.epsilon = -20.0
         self.initial_xi = 0.0
         self.test_n_pz = 1000
+        self.latent_gan = False                               # build G_omega too (dmm_cifar10.py:503-532)
         self.use_flow = False                                 # dmm_bernouli_fashion.py:69
         self.nf_layers = 20                                   # :48
         for k, v in kw.items():
@@ -100,6 +101,17 @@ def _g_blocks(cfg):
                 ('level_8', 32, 3, 1), ('level_9', 32, 5, s9)]
     return [('level_3', 64, 3, 2), ('level_5', 32, 3, 2), ('level_6', 32, 3, 1),   # M :510-514
             ('level_7', 32, 3, 1), ('level_8', 16, 3, 1)]
+
+
+def _omega_blocks(cfg):          # dmm_cifar10.py:523-528 == dmm_for_sampling.py:536-541
+    return [('level_1', 256, 3, 1), ('level_2', 256, 3, 1), ('level_3', 128, 3, 2),
+            ('level_4', 64, 3, 1), ('level_5', 32, 3, 1), ('level_6', 16, 3, 1)]
+
+
+def _omega_base_hw(cfg):
+    if cfg.arch == 'A':          # dmm_cifar10.py:516-521
+        return cfg.x_shape[0] // 8, cfg.x_shape[1] // 8
+    return 4, 4                  # dmm_for_sampling.py:529-535
 
 
 def _d_blocks(cfg):
@@ -193,6 +205,16 @@ def weight_shapes(cfg):
     shapes['D_psi/level_-2/bias'] = (64,)
     shapes['D_psi/level_-1/kernel'] = (64, 1)                # :561
     shapes['D_psi/level_-1/bias'] = (1,)
+    if cfg.latent_gan:
+        if cfg.arch == 'M':
+            raise ValueError("arch M's weight-normalised dense G_omega is not restated")
+        oh, ow = _omega_base_hw(cfg)
+        shapes['G_omega/level_0/kernel'] = (128, 256 * oh * ow)
+        shapes['G_omega/level_0/bias'] = (256 * oh * ow,)
+        co = _block_shapes(shapes, 'G_omega', _omega_blocks(cfg), 256, True)
+        zch = cfg.z_dim // (4 * oh * ow)
+        shapes['G_omega/feature_map_mean_to_pixel/kernel'] = (1, 1, co, zch)
+        shapes['G_omega/feature_map_mean_to_pixel/bias'] = (zch,)
     if cfg.use_flow:                                         # planar_nf.py:79-103,208-221
         for i in range(cfg.nf_layers):
             pre = 'posterior_flow/' if cfg.nf_layers == 1 else 'posterior_flow/_%d/' % i
@@ -261,6 +283,18 @@ def _g_trunk(cfg, params, z, tape=None):
     for scope, cout, k, s in _g_blocks(cfg):
         h = resnet_deconv2d_block(h, params, 'G_theta/' + scope, cout, k, s, tape)
     return h
+
+
+def G_omega(cfg, params, z_omega):
+    """gan_z = flatten(G_omega(z_omega, z_channel)) (dmm_cifar10.py:503-532,630-632; dmm_for_sampling.py:519-546,
+    646-648): z_omega [..., 128] -> [..., z_dim].  The 1x1 output conv has no activation."""
+    oh, ow = _omega_base_hw(cfg)
+    h = dense(z_omega, params['G_omega/level_0/kernel'], params['G_omega/level_0/bias'])
+    h = h.reshape(h.shape[:-1] + (oh, ow, 256))
+    for scope, cout, k, s in _omega_blocks(cfg):
+        h = resnet_deconv2d_block(h, params, 'G_omega/' + scope, cout, k, s)
+    x = conv2d(h, params['G_omega/feature_map_mean_to_pixel/kernel'], params['G_omega/feature_map_mean_to_pixel/bias'])
+    return x.reshape(x.shape[:-3] + (-1,))
 
 
 def G_theta(cfg, params, z, return_std=False, tape=None):

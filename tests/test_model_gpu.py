@@ -459,3 +459,32 @@ def test_flow_posterior_matches_oracle(case):
     with pytest.raises(Exception):
         Model(cfg, bad)
     m.close()
+
+
+@pytest.mark.parametrize('case', ['A128', 'Bceleba'])
+def test_latent_gan_initial_z_matches_oracle(case):
+    """gan_z = G_omega(z_omega) (dmm_cifar10.py:503-532,623-635): the initial_z of plot_samples' MALA loop."""
+    arch, kw, _, _ = CASES[case]
+    from apvae.model import ExpConfig, Model
+    ocfg = O.OracleConfig(arch, latent_gan=True, **kw)
+    params = O.init_weights(ocfg)
+    cfg = ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim, max_batch=8, max_chunk=8, latent_gan=True, enable_grad=True)
+    m = Model(cfg, params)
+    n = 11                                                           # ragged against max_chunk = 8
+    zo = np.random.RandomState(5).normal(size=(n, 128))
+    want = O.G_omega(ocfg, params, zo)
+    got = m.latent_gan(n, z_omega=zo).cpu().numpy().astype(np.float64)
+    assert got.shape == (n, ocfg.z_dim)
+    scale = np.abs(want).max()
+    assert np.abs(got - want).max() < 2e-2 * scale and np.abs(got - want).mean() < 4e-3 * scale, (np.abs(got - want).max(), scale)
+    # in-kernel draws: reproducible, seed-dependent, and usable as the chains' initial state
+    a, b, c = m.latent_gan(n, seed=3), m.latent_gan(n, seed=3), m.latent_gan(n, seed=4)
+    assert bool((a == b).all()) and not bool((a == c).all())
+    out = m.mala(a, 2, seed=1, history=False)
+    assert tuple(out['z'].shape) == (n, ocfg.z_dim) and bool(out['z'].isfinite().all())
+    # a handle without latent_gan refuses
+    m2 = Model(ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim, max_batch=8, max_chunk=8),
+               {k: v for k, v in params.items() if not k.startswith('G_omega/')})
+    with pytest.raises(Exception):
+        m2.latent_gan(4)
+    m.close(); m2.close()

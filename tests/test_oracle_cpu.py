@@ -256,3 +256,17 @@ def test_flow_posterior_in_the_evaluation_graph_and_schema():
     np.testing.assert_allclose(out['log_q'], base['log_q'] - ld)
     assert np.abs(out['z'] - base['z']).max() > 1e-2                                     # the synthetic flow is not the identity
     assert np.all(out['ele_test_lb'] <= out['ele_test_ll'] + 1e-9)
+
+
+def test_latent_gan_schema_and_shapes():
+    from apvae.model import ExpConfig, weight_schema
+    for arch, kw in (('A', dict(z_dim=128)), ('A', dict()), ('B', dict(dataset='cifar10', z_dim=64)), ('B', dict(dataset='celebA'))):
+        ocfg = O.OracleConfig(arch, latent_gan=True, **kw)
+        ours = dict(weight_schema(ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim, latent_gan=True)))
+        assert ours == {k: tuple(v) for k, v in O.weight_shapes(ocfg).items()}
+        assert ours['G_omega/level_0/kernel'] == (128, 256 * 16) and ours['G_omega/level_3/shortcut/kernel'] == (1, 1, 128, 256)
+    ocfg = O.OracleConfig('B', dataset='cifar10', z_dim=64, latent_gan=True)
+    z0 = O.G_omega(ocfg, O.init_weights(ocfg), np.random.RandomState(0).normal(size=(2, 3, 128)))
+    assert z0.shape == (2, 3, 64) and np.isfinite(z0).all()
+    with pytest.raises(Exception):
+        weight_schema(ExpConfig('M', latent_gan=True))
