@@ -468,6 +468,7 @@ int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
         info->patch_groups = (int)Q.groups.size(); info->patch_items = Q.num_items;
         info->patch_a_stages = Q.a_stages; info->patch_b_stages = Q.b_stages;
         info->patch_prow[0] = Q.prow[0]; info->patch_prow[1] = Q.prow[1];
+        info->patch_fold = Q.fold;
     }
     return APVAE_OK;
 }
@@ -539,8 +540,14 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
         std::unique_ptr<DevOp> o(new DevOp());
         o->name = "plan_run";
         const bool use_patch = p->has_patch;
-        if (!(use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, o.get(), &e) : devop_create(dev, p->plan, src_dev, ep, o.get(), &e)))
-            return set_global_err(e, APVAE_ERR_CUDA);
+        bool made = use_patch ? devop_create_patch(dev, p->patch, src_dev, ep, o.get(), &e) : devop_create(dev, p->plan, src_dev, ep, o.get(), &e);
+        if (!made && use_patch && p->patch.fold > 1) {       // folded op the A-stationary kernel cannot take: tap-GEMM
+            cudaGetLastError();
+            o.reset(new DevOp());
+            o->name = "plan_run";
+            made = devop_create(dev, p->plan, src_dev, ep, o.get(), &e);
+        }
+        if (!made) return set_global_err(e, APVAE_ERR_CUDA);
         ops.push_back(std::move(o));
     }
     auto devop_launch_all = [&](int n) {

@@ -103,4 +103,25 @@ int launch_clip_min(float* v, long long n, float lo, void* stream);
 // copy the first `cols` columns of fp32 [rows, ld] into dense [rows, cols]; optional tanh not applied.
 int launch_gather_cols(const float* src, int ld, int col0, int cols, long long rows, float* dst, void* stream);
 
+
+// G_theta's 1x1 output heads (dmm_cifar10.py:489-496: x_mean = tanh(conv 1x1), x_logstd = conv 1x1) on the CUDA cores:
+// nout <= 8 outputs per pixel are an HBM-bound stream over the trunk output, not a tensor-core shape.  One thread per
+// pixel; the pixel rows of a 128-pixel tile are staged through shared memory by coalesced 16-byte loads; the weights
+// and biases travel in the kernel parameters (constant bank operands, fp32).  Writes the fp32 heads (tanh on the first
+// tanh_cols columns) and the bf16 copy of those columns that D_psi reads (raw + leaky_relu, padding columns zero);
+// split precision: input = in + in_lo, outputs as hi + lo pairs.
+constexpr int kHeadsMaxW = 2048;          // cin * nout fp32 weights in the parameter block
+struct HeadsParams {
+    const void* in;  const void* in_lo;   // bf16 [pixels, cp]
+    int cp, cin, nout, tanh_cols;
+    long long pixels_per_image;
+    float* out_f32;  int ld_f32;          // [pixels, ld_f32], columns < nout
+    void* raw;  void* act;  void* raw_lo;  void* act_lo;   // bf16 [pixels, ldo], columns < tanh_cols, rest zero
+    int ldo;
+    float alpha;
+    float bias[8];
+    float w[kHeadsMaxW];                  // [cin][nout]
+};
+int launch_pixel_heads(const HeadsParams& p, long long pixels, void* stream);
+
 }  // namespace apvae

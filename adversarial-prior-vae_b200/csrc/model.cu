@@ -88,10 +88,17 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     if (!(env && env[0] == '0') && !split_epi &&
         plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr) && pplan.npad <= patch_max_n) {
         if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");
-        if (!devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
-        if (macs) *macs += pplan.macs_per_image / (split_mode ? 3.0 : 1.0);
-        prog.push_back(std::move(op));
-        return true;
+        const bool made = devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr);
+        if (!made && pplan.fold == 1) return fail(perr);
+        if (made) {
+            if (macs) *macs += pplan.macs_per_image / (split_mode ? 3.0 : 1.0);
+            prog.push_back(std::move(op));
+            return true;
+        }
+        // a folded (8-wide) op the A-stationary kernel cannot take (half-resolution residual): the tap-GEMM kernel runs it
+        cudaGetLastError();
+        op.reset(new DevOp());
+        op->name = name;
     }
     OpPlan plan;
     if (!plan_op(terms, cap, &plan, &perr)) return fail("plan " + name + ": " + perr);

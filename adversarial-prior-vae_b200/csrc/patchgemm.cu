@@ -253,6 +253,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         const uint32_t sw = (uint32_t)(lane & 7);
         const int W = p.W, H = p.H, NT = p.NT, macc = p.macc, tiles_y = p.tiles_y, rows_tile = p.rows_tile, n_valid = p.n_valid;
         const int lgW = 31 - __clz(W);
+        const bool fold = p.fold > 1;                      // two 8-wide images per tile row (tiles_y == 1): 5-D epilogue maps
         const int tile_step = num_clusters * csize;
         const int dn = tile_step / tiles_y, dty = tile_step - dn * tiles_y;
         // a block's place in the work sequence: round g, accumulator m, first column cb; (n, ty) = image and row-tile of
@@ -281,7 +282,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             }
             if (leader) {
                 mbar_expect_tx(resbar(q, b), res_bytes);
-                tma_load_2d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, rp0);
+                if (fold) tma_load_5d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else tma_load_2d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, rp0);
             }
             return true;
         };
@@ -394,8 +396,13 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             if (leader && do_store && cur.n < n_valid) {
                 const int po = cur.m * kTileM + q * 32;
                 const int oyy = cur.ty * rows_tile + (po >> lgW), ox0 = po & (W - 1);
-                if (want_raw) tma_store_4d(&p.tm_raw, rawb, cur.cb, ox0, oyy, cur.n);
-                if (want_act) tma_store_4d(&p.tm_act, actb, cur.cb, ox0, oyy, cur.n);
+                if (fold) {
+                    if (want_raw) tma_store_5d(&p.tm_raw, rawb, cur.cb, 0, 0, oyy, cur.n);
+                    if (want_act) tma_store_5d(&p.tm_act, actb, cur.cb, 0, 0, oyy, cur.n);
+                } else {
+                    if (want_raw) tma_store_4d(&p.tm_raw, rawb, cur.cb, ox0, oyy, cur.n);
+                    if (want_act) tma_store_4d(&p.tm_act, actb, cur.cb, ox0, oyy, cur.n);
+                }
                 tma_store_commit();
             }
             if (q == 0 && lane == 0) stamp(tit, tblk == 0 ? 11 : (tblk == 1 ? 12 : 13));
@@ -446,14 +453,19 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             const int n = tile / p.tiles_y;
             const int y0 = (tile % p.tiles_y) * p.rows_tile;
             const int pix = m * kTileM + r;
-            const int y = y0 + pix / p.W, x = pix % p.W;
-            const bool valid = (n < p.n_valid) && (y < p.H);
-            const size_t opix = ((size_t)n * p.H + y) * p.W + x;
+            int y = y0 + pix / p.W, x = pix % p.W;
+            int ni = n, wr = p.W;                       // image and row width in memory
+            bool valid = (n < p.n_valid) && (y < p.H);
+            if (p.fold > 1) {                           // x = (image of the pair, pixel): image 2 n + x / 8, 8 pixels per row
+                ni = 2 * n + (x >> 3); x &= 7; wr = 8;
+                valid = (ni < p.n_real) && (y < p.H);
+            }
+            const size_t opix = ((size_t)ni * p.H + y) * wr + x;
             EpiRow row;
             row.opix = opix; row.rpix = opix; row.valid = valid; row.has_res = valid && (p.epi.res_mode != RES_NONE);
             if (p.epi.res_mode == RES_EVEN) {           // 1x1 stride-2 transposed shortcut: x W lands on even output pixels only
                 row.has_res = row.has_res && !((y | x) & 1);
-                row.rpix = ((size_t)n * (p.H >> 1) + (y >> 1)) * (p.W >> 1) + (x >> 1);
+                row.rpix = ((size_t)ni * (p.H >> 1) + (y >> 1)) * (wr >> 1) + (x >> 1);
             }
             return row;
         };

@@ -50,7 +50,11 @@ struct alignas(64) PatchGemmParams {
     int W, H;                        // image size (stride 1: input grid == output grid)
     int rows_tile, macc;             // output rows per tile = macc * 128 / W
     int tiles_y;
-    int n_valid;
+    int n_valid;                     // images to process (folded ops: image PAIRS, see `fold`)
+    int fold;                        // 1: ordinary op.  2: 8-pixel-wide images, two per 128-pixel tile: the patch is
+                                     // [rows][2 images][8 pixels] (W = 16 here), tm_a is (C, 8, 2, H, N/2) and the epilogue
+                                     // maps tm_raw / tm_act / tm_res are 5-D (Npad, 8, 2, H, N/2) with boxes (64, 8, 2, 2, 1)
+    int n_real;                      // images to process (== n_valid unless folded)
     int Npad, NT;                    // NT == Npad <= 256, macc * NT <= 256
     int kc;                          // 16, 32 or 64 channels per chunk
     int tpi;                         // vertical taps per weight item (one barrier / ring slot per item)

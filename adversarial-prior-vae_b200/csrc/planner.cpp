@@ -215,7 +215,12 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.capacity_n = capacity_n;
     const TermSpec& t0 = terms[0];
     const int W = t0.in_w, H = t0.in_h, cp = t0.in_cp;
-    if (W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 16, 32, 64 or 128");
+    if (W != 8 && W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 8, 16, 32, 64 or 128");
+    // 8-wide images: two images side by side per tile row (PatchGemmParams::fold); needs whole pairs in the buffers
+    const int fold = (W == 8) ? 2 : 1;
+    if (fold > 1 && (capacity_n & 1)) return fail("patch: 8-wide images need an even capacity");
+    if (fold > 1) { const char* e = getenv("APVAE_PATCH_FOLD"); if (e && e[0] == '0') return fail("patch: 8-wide images disabled (APVAE_PATCH_FOLD=0)"); }
+    const int Wt = W * fold;
     for (size_t i = 0; i < terms.size(); ++i) {
         const TermSpec& t = terms[i];
         if (phase < 0 && t.stride != 1) return fail("patch: stride-1 terms only");
@@ -226,13 +231,13 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         if (t.cout != t0.cout) return fail("patch: terms disagree on cout");
         if (t.src != (int)i) return fail("patch: term i must read source i");
     }
-    P.w = W; P.h = H; P.in_cp = cp;
+    P.w = W; P.h = H; P.in_cp = cp; P.fold = fold;
     P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
     P.cout = t0.cout;
     P.npad = pad16(t0.cout);
     if (P.npad > 256) return fail("patch: cout > 256");
     P.nsrc = (int)terms.size();
-    const int rows128 = kTileM / W;
+    const int rows128 = kTileM / Wt;
     if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
     int kmax = 1;
     for (const TermSpec& t : terms) kmax = std::max(kmax, t.k);
@@ -265,7 +270,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;
     auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * (P.tap_bytes / (two ? 2 : 1)) + 1023u) & ~1023u; };
-    auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * W * P.kc * 2 + 1023u) & ~1023u; };
+    auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * Wt * P.kc * 2 + 1023u) & ~1023u; };
     int macc = 0;
     for (int cand : {4, 2, 1}) {
         if (force_macc && cand != force_macc) continue;

@@ -100,10 +100,14 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     memset(&p, 0, sizeof(p));
     const cuuint32_t ones[5] = {1, 1, 1, 1, 1};
     const cuuint64_t C = plan.in_cp, W = plan.w, H = plan.h;
+    const bool fold = plan.fold > 1;        // 8-wide images in pairs: dim 2 is the image inside the pair, dim 4 the pair
+    if (fold && (plan.fold != 2 || W != 8 || (plan.capacity_n & 1))) { if (err) *err = "patch: bad fold geometry for op " + op->name; return false; }
+    if (fold && epi.res_mode == RES_EVEN) { if (err) *err = "patch: folded ops take no half-resolution residual (op " + op->name + ")"; return false; }
+    const cuuint64_t NP = fold ? (cuuint64_t)plan.capacity_n / 2 : (cuuint64_t)plan.capacity_n;
     for (int s = 0; s < plan.nsrc; ++s) {
-        cuuint64_t dims[5] = {C, W, 1, H, (cuuint64_t)plan.capacity_n};
-        cuuint64_t strides[4] = {C * 2, W * C * 2, W * C * 2, H * W * C * 2};
-        cuuint32_t box[5] = {(cuuint32_t)plan.kc, (cuuint32_t)W, 1, (cuuint32_t)plan.prow[s], 1};
+        cuuint64_t dims[5] = {C, W, fold ? 2u : 1u, H, NP};
+        cuuint64_t strides[4] = {C * 2, (fold ? H : 1) * W * C * 2, W * C * 2, (fold ? 2 : 1) * H * W * C * 2};
+        cuuint32_t box[5] = {(cuuint32_t)plan.kc, (cuuint32_t)W, fold ? 2u : 1u, (cuuint32_t)plan.prow[s], 1};
         CUresult r = encode(&p.tm_a[s], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(src_ptrs[s]), dims, strides,
                             box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc),
                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -127,7 +131,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     }
     for (size_t i = 0; i < ngroups; ++i) p.groups[i] = plan.groups[i];
     p.num_groups = (int)ngroups; p.num_items = plan.num_items;
-    p.W = plan.w; p.H = plan.h; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
+    p.W = plan.w * plan.fold; p.H = plan.h; p.fold = plan.fold; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
     p.n_valid = 0;
     p.Npad = plan.npad; p.NT = plan.npad; p.kc = plan.kc;
     p.tpi = plan.tpi; p.tap_bytes = plan.tap_bytes;
@@ -168,12 +172,22 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             auto map_out = [&](CUtensorMap* tm, const void* ptr) {
                 const cuuint64_t ld = (cuuint64_t)epi.ldo * 2;                       // bytes per output pixel
                 const cuuint64_t Wo = (cuuint64_t)osc * W, Ho = (cuuint64_t)osc * H;
+                char* base = static_cast<char*>(const_cast<void*>(ptr)) + ((size_t)py * Wo + px) * ld;
+                if (fold) {                 // (C, 8 pixels, 2 images, H, pairs): a block's 32 rows are [2 rows][2 images][8 pixels]
+                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
+                    cuuint64_t strides4[4] = {osc * ld, Ho * Wo * ld, osc * Wo * ld, 2 * Ho * Wo * ld};
+                    cuuint32_t box5[5] = {64, 8, 2, 2, 1};
+                    const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims5, strides4, box5, ones,
+                                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    if (r != CUDA_SUCCESS) ok = false;
+                    return;
+                }
                 cuuint64_t dims[4] = {(cuuint64_t)plan.npad, W, H, (cuuint64_t)plan.capacity_n};
                 cuuint64_t strides[3] = {osc * ld, osc * Wo * ld, Ho * Wo * ld};
                 const cuuint32_t bx = (cuuint32_t)std::min<cuuint64_t>(W, 32);
                 cuuint32_t box[4] = {64, bx, 32 / bx, 1};
                 const cuuint32_t ones4[4] = {1, 1, 1, 1};
-                char* base = static_cast<char*>(const_cast<void*>(ptr)) + ((size_t)py * Wo + px) * ld;
                 const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, base, dims, strides, box, ones4,
                                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -185,6 +199,15 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             if (epi.res_mode == RES_EVEN) {
                 p.res_rows = (plan.w >= 32) ? 16 : 8;
                 map2d(&p.tm_res, epi.res, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
+            } else if (epi.res_mode == RES_SAME && fold) {
+                const cuuint64_t ld = (cuuint64_t)epi.ld_res * 2;
+                cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
+                cuuint64_t strides4[4] = {ld, H * W * ld, W * ld, 2 * H * W * ld};
+                cuuint32_t box5[5] = {64, 8, 2, 2, 1};
+                const CUresult r = encode(&p.tm_res, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(epi.res), dims5, strides4,
+                                          box5, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                if (r != CUDA_SUCCESS) ok = false;
             } else if (epi.res_mode == RES_SAME) {
                 map2d(&p.tm_res, epi.res, pixels, epi.ld_res, 32);
             } else {
@@ -280,7 +303,8 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
 int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
     if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
     if (op.is_patch) {
-        op.pparams.n_valid = n_valid;
+        op.pparams.n_real = n_valid;
+        op.pparams.n_valid = op.pparams.fold > 1 ? (n_valid + 1) / 2 : n_valid;
         return launch_patchgemm(op.pparams, dev.num_sms, stream);
     }
     op.params.n_valid = n_valid;

@@ -193,9 +193,10 @@ typedef struct apvae_plan_info {
     uint64_t src_strides[3][4];
     uint32_t src_box[3][5];
     double macs_per_image;
-    /* A-stationary ("patch") plan, when the op is eligible (stride 1, width 16..128) and not disabled */
+    /* A-stationary ("patch") plan, when the op is eligible (stride 1, width 8..128) and not disabled */
     int patch, patch_macc, patch_cluster, patch_rows_tile, patch_groups, patch_items, patch_a_stages, patch_b_stages;
     int patch_prow[2];
+    int patch_fold;   /* 2: 8-pixel-wide images are processed in pairs, side by side in one 16-wide tile row (even capacity) */
 } apvae_plan_info;
 
 typedef struct apvae_epilogue {

@@ -87,42 +87,50 @@ def synthetic_images(shape, seed=0):
 def emulate_patch_plan(plan, srcs, n_valid):
     """Evaluate the A-stationary ("patch") plan on the CPU exactly as patchgemm.cu would: per tile and
     group, one zero-filled patch [prow, W, kc]; tap j reads the patch advanced by j*W rows, accumulator
-    m by 128 rows.  srcs: float arrays [N, H, W, Cp].  Returns [n_valid, H, W, npad]."""
+    m by 128 rows.  Folded plans (8-wide images, patch_fold == 2) lay two images side by side: the patch
+    is [prow, 2 images, 8, kc] and a tile row is 16 pixels.  srcs: float arrays [N, H, W, Cp].
+    Returns [n_valid, H, W, npad]."""
     i = plan.info
     assert i.patch
     groups = plan.patch_groups
     wts = bf16_bits_to_f32(plan.patch_weights).astype(np.float64)
     bias = plan.bias
     H, W, kc, macc, rt = i.hg, i.wg, i.kc, i.patch_macc, i.patch_rows_tile
+    fold = max(1, i.patch_fold)
+    Wt = W * fold
     out = np.zeros((n_valid, H, W, i.npad), dtype=np.float64)
     tiles_y = -(-H // rt)
-    for n in range(n_valid):
+    for n0 in range(0, n_valid, fold):
         for ty in range(tiles_y):
             y0 = ty * rt
             acc = np.zeros((macc * 128, i.npad), dtype=np.float64)
             item = 0
             for src, dx, py0, k, c0, prow in groups:
                 x = np.asarray(srcs[src], dtype=np.float64)
-                patch = np.zeros((prow, W, kc))
+                patch = np.zeros((prow, fold, W, kc))
                 for py in range(prow):
                     y = y0 + py0 + py
                     if not 0 <= y < H:
                         continue
-                    for px in range(W):
-                        xx = px + dx
-                        if 0 <= xx < W:
-                            patch[py, px, :] = x[n, y, xx, c0:c0 + kc]
-                flat = patch.reshape(prow * W, kc)
+                    for f in range(fold):
+                        if n0 + f >= x.shape[0]:
+                            continue
+                        for px in range(W):
+                            xx = px + dx
+                            if 0 <= xx < W:
+                                patch[py, f, px, :] = x[n0 + f, y, xx, c0:c0 + kc]
+                flat = patch.reshape(prow * Wt, kc)
                 for j in range(k):
                     for m in range(macc):
-                        a = flat[j * W + m * 128: j * W + m * 128 + 128]
+                        a = flat[j * Wt + m * 128: j * Wt + m * 128 + 128]
                         assert a.shape[0] == 128
                         acc[m * 128:(m + 1) * 128] += a @ wts[item].T
                     item += 1
             assert item == i.patch_items
             acc += bias
             for pix in range(macc * 128):
-                y, xx = y0 + pix // W, pix % W
-                if y < H:
-                    out[n, y, xx] = acc[pix]
+                y, xt = y0 + pix // Wt, pix % Wt
+                f, xx = xt // W, xt % W
+                if y < H and n0 + f < n_valid:
+                    out[n0 + f, y, xx] = acc[pix]
     return out

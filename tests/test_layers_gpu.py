@@ -168,6 +168,9 @@ PATCH_GPU_CASES = [
     (False, 3, 3, 32, 32, 64, 64),
     (True, 3, 2, 64, 64, 32, 32),
     (False, 3, 9, 16, 16, 128, 128),
+    (False, 3, 6, 8, 8, 192, 192),         # 8-wide images run as pairs (fold): even capacity
+    (True, 3, 4, 8, 8, 64, 64),
+    (True, 1, 130, 8, 8, 2, 192),
 ]
 
 
@@ -179,7 +182,8 @@ def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster, monkeypat
     torch = _torch()
     import apvae
     from apvae.plan import Plan, pad16
-    if macc * pad16(cout) > 256 or H % (macc * 128 // W) or (pad16(cout) // cluster) % 8:
+    Wt = 16 if W == 8 else W                   # 8-wide images: two side by side per tile row
+    if macc * pad16(cout) > 256 or H % (macc * 128 // Wt) or (pad16(cout) // cluster) % 8:
         pytest.skip('combination not supported by the planner')
     monkeypatch.setenv('APVAE_PATCH', '1')
     monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
@@ -242,6 +246,13 @@ TMA_EPI_CASES = [
     (32, 32, 16, 16, 'same', 3, 3),        # narrower than one 64-column box
     (32, 32, 32, 48, 'none', 2, 3),
     (128, 128, 16, 64, 'even', 1, 1),
+    (8, 8, 192, 192, 'same', 5, 6),        # 8-wide images run as pairs: 5-D epilogue maps
+    (8, 8, 192, 192, 'none', 4, 4),
+    (8, 8, 2, 192, 'none', 3, 4),
+    (8, 8, 256, 256, 'same', 7, 8),
+    (8, 8, 64, 48, 'same', 2, 2),
+    (8, 8, 64, 64, 'even', 3, 4),          # half-resolution residual: falls back to the tap-GEMM kernel
+    (16, 8, 32, 32, 'same', 3, 4),         # 8 wide, 16 high: two row tiles per pair
 ]
 
 
@@ -251,7 +262,7 @@ TMA_EPI_CASES = [
 def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two_cta, monkeypatch):
     """bf16-only epilogue of the A-stationary kernel (bulk tensor loads of the residual, bulk tensor stores of
     out_raw / out_act): v = acc + bias (+ res on every / on even pixels); raw = bf16(v), act = bf16(lrelu(v));
-    images >= n_valid stay untouched."""
+    images >= n_valid stay untouched (a folded 8-wide op may also write the second image of its last pair)."""
     torch = _torch()
     from apvae import _lib
     from apvae.plan import Plan, pad16
@@ -287,7 +298,8 @@ def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two
     assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale       # bf16 rounding of the output
     assert np.abs(act[:n_valid, ..., :cout] - O.leaky_relu(want[:n_valid])).max() <= 2 ** -7 * scale
     assert np.all(raw[:n_valid, ..., cout:] == 0) and np.all(act[:n_valid, ..., cout:] == 0)   # padding columns stay zero
-    assert np.all(raw[n_valid:] == 7.0) and np.all(act[n_valid:] == 7.0)
+    keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 else 0)
+    assert np.all(raw[keep:] == 7.0) and np.all(act[keep:] == 7.0)
 
 
 PHASE_CASES = [
@@ -298,6 +310,9 @@ PHASE_CASES = [
     (3, 32, 32, 64, 32, 2, 3),
     (5, 16, 16, 16, 48, 3, 3),
     (3, 64, 64, 16, 16, 1, 1),
+    (3, 8, 8, 192, 192, 3, 4),         # arch A G_theta/level_3/conv_0: 8-wide inputs run as pairs
+    (3, 8, 8, 64, 32, 4, 4),
+    (5, 8, 8, 32, 32, 2, 2),
 ]
 
 
@@ -325,8 +340,9 @@ def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, o
     scale = max(1.0, float(np.abs(want).max()))
     act = out_act.float().cpu().numpy()
     assert np.abs(act[:n_valid, ..., :cout] - O.leaky_relu(want[:n_valid])).max() <= 2 ** -7 * scale
-    assert np.all(act[n_valid:] == 7.0)
+    keep = n_valid + (n_valid & 1 if W == 8 else 0)      # pairs of 8-wide images: the last pair is written whole
+    assert np.all(act[keep:] == 7.0)
     if out_raw is not None:
         raw = out_raw.float().cpu().numpy()
         assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
-        assert np.all(raw[n_valid:] == 7.0)
+        assert np.all(raw[keep:] == 7.0)

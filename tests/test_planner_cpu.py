@@ -99,6 +99,9 @@ PATCH_CASES = [
     (False, 1, 16, 16, 64, 48),
     (False, 3, 8, 16, 16, 200),      # one 128-pixel tile per image, wide N
     (True, 3, 64, 64, 16, 32),       # celebA width
+    (False, 3, 8, 8, 32, 48),        # 8-wide images: two per tile row (fold)
+    (True, 3, 8, 8, 16, 200),
+    (False, 1, 16, 8, 16, 16),       # 8 wide, two row tiles per pair
 ]
 
 
@@ -119,6 +122,7 @@ def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc, monkeypa
     plan = Plan([dict(src=0, transpose=transpose, stride=1, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
     assert plan.info.patch == 1
     assert plan.info.patch_macc * plan.info.npad <= 256
+    assert plan.info.patch_fold == (2 if W == 8 else 1)
     got = emulate_patch_plan(plan, [pad_channels(x, pad16(cin))], n)[..., :cout]
     fn = O.deconv2d if transpose else O.conv2d
     want = fn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
@@ -141,7 +145,8 @@ def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
         O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 1)
     np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
-    # not eligible: stride 2, 8x8 grids, arch-M widths
+    # not eligible: stride 2, 8x8 grids with an odd capacity (they run as image pairs), arch-M widths
+    assert Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), in_h=8, in_w=8)], 4).info.patch_fold == 2
     for kw in (dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=28, in_w=28)):
         p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1)
         assert p.info.patch == 0
