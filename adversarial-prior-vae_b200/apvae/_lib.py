@@ -62,7 +62,9 @@ class PlanInfo(C.Structure):
         ('macs_per_image', C.c_double),
         ('patch', C.c_int), ('patch_macc', C.c_int), ('patch_cluster', C.c_int),
         ('patch_rows_tile', C.c_int), ('patch_groups', C.c_int), ('patch_items', C.c_int),
-        ('patch_a_stages', C.c_int), ('patch_b_stages', C.c_int), ('patch_prow', C.c_int * 2), ('patch_fold', C.c_int),
+        ('patch_a_stages', C.c_int), ('patch_b_stages', C.c_int), ('patch_prow', C.c_int * 2),
+        ('patch_s2d', C.c_int), ('patch_nmaps', C.c_int), ('patch_map_src', C.c_int * 4), ('patch_map_ph', C.c_int * 4),
+        ('patch_map_prow', C.c_int * 4), ('patch_fold', C.c_int),
     ]
 
 

@@ -395,7 +395,7 @@ int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* na
     DevOp& op = *(*p)[index];
     if (n <= 0 || n > op.capacity_n) { m.err = "op_time: n exceeds the op's capacity"; return APVAE_ERR_INVALID; }
     if (name && name_cap > 0) {      // op name + which kernel runs it
-        const std::string full = op.name + (op.is_patch ? (op.pparams.fast_epi ? " [patchgemm, TMA epilogue]" : " [patchgemm]") : " [tapgemm]");
+        const std::string full = op.name + (op.is_heads ? " [heads, CUDA cores]" : op.is_patch ? (op.pparams.fast_epi ? " [patchgemm, TMA epilogue]" : " [patchgemm]") : " [tapgemm]");
         strncpy(name, full.c_str(), name_cap - 1); name[name_cap - 1] = 0;
     }
     if (macs_per_unit) *macs_per_unit = op.macs_per_image;
@@ -469,6 +469,8 @@ int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
         info->patch_a_stages = Q.a_stages; info->patch_b_stages = Q.b_stages;
         info->patch_prow[0] = Q.prow[0]; info->patch_prow[1] = Q.prow[1];
         info->patch_fold = Q.fold;
+        info->patch_s2d = Q.s2d; info->patch_nmaps = Q.nmaps;
+        for (int i = 0; i < 4; ++i) { info->patch_map_src[i] = Q.map_src[i]; info->patch_map_ph[i] = Q.map_ph[i]; info->patch_map_prow[i] = Q.prow[i]; }
     }
     return APVAE_OK;
 }

@@ -187,6 +187,32 @@ bool Model::build_g() {
     e.out_raw = d_in.raw.ptr; e.out_act = d_in.act.ptr; e.out_raw_lo = d_in.raw_lo.ptr; e.out_act_lo = d_in.act_lo.ptr;
     e.ldo = d_in.raw.cp; e.bf16_zero_from = Cx;
     e.out_f32 = head_f32; e.ld_f32 = nout; e.f32_cols = nout; e.tanh_cols = Cx;
+    // nout <= 8 outputs per pixel: an HBM-bound stream, run on the CUDA cores (heads.cu) with fp32 weights;
+    // APVAE_HEADS_GEMM=1 keeps the 1x1 tensor-core op (tuning / A-B only)
+    const char* hg = getenv("APVAE_HEADS_GEMM");
+    if (!(hg && hg[0] == '1') && nout <= 8 && ((cg + 7) / 8) * 8 * nout <= kHeadsMaxW && d_in.raw.cp % 8 == 0) {
+        std::unique_ptr<DevOp> op(new DevOp());
+        op->name = "G_theta/heads";
+        op->is_heads = true;
+        op->capacity_n = cap;
+        op->macs_per_image = (double)cg * nout * HW();
+        HeadsParams& hp = op->heads;
+        memset(&hp, 0, sizeof(hp));
+        hp.in = h.raw.ptr; hp.in_lo = sp ? h.raw_lo.ptr : nullptr;
+        hp.cp = h.raw.cp; hp.cin = cg; hp.nout = nout; hp.tanh_cols = Cx;
+        hp.pixels_per_image = HW();
+        hp.out_f32 = head_f32; hp.ld_f32 = nout;
+        hp.raw = d_in.raw.ptr; hp.act = d_in.act.ptr; hp.raw_lo = d_in.raw_lo.ptr; hp.act_lo = d_in.act_lo.ptr;
+        hp.ldo = d_in.raw.cp;
+        hp.alpha = 0.2f;
+        for (int c = 0; c < nout; ++c) hp.bias[c] = bcat.v[c];
+        for (int ci = 0; ci < cg; ++ci)
+            for (int c = 0; c < nout; ++c) hp.w[ci * nout + c] = kcat.v[(size_t)ci * nout + c];
+        macs_g += op->macs_per_image;
+        g_prog.push_back(std::move(op));
+        split_mode = false;
+        return true;
+    }
     std::vector<TermSpec> terms; std::vector<const void*> srcs;
     if (!push_terms(terms, srcs, sp, h.raw, h.raw_lo, false, 1, 1, cg, nout, "G_theta/heads/kernel", &kc, &bcat)) return false;
     const bool ok = add_op(g_prog, "G_theta/heads", terms, srcs, e, cap, &macs_g);

@@ -24,7 +24,7 @@
 namespace apvae {
 
 struct PatchGroup {
-    int16_t src;     // which A tensor map (0..1)
+    int16_t src;     // which A tensor map (0..kPatchMaxMaps-1)
     int16_t dx;      // horizontal shift of the patch box
     int16_t py0;     // vertical shift of patch row 0 relative to the tile's first output row
     int16_t k;       // weight tiles (vertical taps) that read this patch
@@ -33,6 +33,7 @@ struct PatchGroup {
 };
 
 constexpr int kPatchMaxSrc = 2;
+constexpr int kPatchMaxMaps = 4;     // activation tensor maps: (source, row phase of the space-to-depth view)
 constexpr int kPatchMaxGroups = 48;
 // TMA epilogue (bf16 outputs, optional bf16 residual, no mask / tanh / fp32 output): per epilogue warp two
 // residual boxes, one raw and one act staging box of 32 rows x 128 bytes (SWIZZLE_128B), plus the bias row
@@ -43,7 +44,8 @@ constexpr uint32_t kFastEpiSmemBytes = 4u * kFastEpiWarpBytes;
 constexpr uint32_t kPatchFixedSmem = 1024u + 1024u + (kFastEpiSmemBytes > kEpiSmemBytes ? kFastEpiSmemBytes : kEpiSmemBytes);
 
 struct alignas(64) PatchGemmParams {
-    CUtensorMap tm_a[kPatchMaxSrc];  // 5-D (C, W, 1, H, N), box (kc, W, 1, prow_src, 1)
+    CUtensorMap tm_a[kPatchMaxMaps]; // 5-D (C, W, 1, H, N), box (kc, W, 1, prow_src, 1); a stride-2 conv reads the
+                                     // space-to-depth view (2C, W/2, 1, H/2, N) of one row phase per map
     CUtensorMap tm_b;                // 2-D (kc, items*Npad), box (kc, NT / cluster)
     PatchGroup groups[kPatchMaxGroups];   // in the kernel parameters: read through the constant bank (uniform loads)
     int num_groups, num_items;

@@ -214,7 +214,13 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P = PatchPlan();
     P.capacity_n = capacity_n;
     const TermSpec& t0 = terms[0];
-    const int W = t0.in_w, H = t0.in_h, cp = t0.in_cp;
+    // stride-2 conv2d: the grid is the OUTPUT grid; the input is read through its space-to-depth view
+    // (row phase = one tensor map each, column phase folded into the channel coordinate)
+    bool s2c = (phase < 0);
+    for (const TermSpec& t : terms) s2c = s2c && !t.transpose && t.stride == 2;
+    if (s2c) { const char* e = getenv("APVAE_PATCH_S2"); if (e && e[0] == '0') return fail("patch: stride-2 convs disabled (APVAE_PATCH_S2=0)"); }
+    if (s2c && ((t0.in_w | t0.in_h) & 1)) return fail("patch: stride-2 conv needs an even input size");
+    const int W = s2c ? t0.in_w / 2 : t0.in_w, H = s2c ? t0.in_h / 2 : t0.in_h, cp = t0.in_cp;
     if (W != 8 && W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 8, 16, 32, 64 or 128");
     // 8-wide images: two images side by side per tile row (PatchGemmParams::fold); needs whole pairs in the buffers
     const int fold = (W == 8) ? 2 : 1;
@@ -223,15 +229,15 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     const int Wt = W * fold;
     for (size_t i = 0; i < terms.size(); ++i) {
         const TermSpec& t = terms[i];
-        if (phase < 0 && t.stride != 1) return fail("patch: stride-1 terms only");
+        if (phase < 0 && !s2c && t.stride != 1) return fail("patch: every term stride 1, or every term a stride-2 conv2d");
         if (phase >= 0 && (terms.size() != 1 || !t.transpose || t.stride != 2)) return fail("patch: phases are for one stride-2 transposed term");
         if (!(t.k & 1)) return fail("patch: odd kernel sizes only");
-        if (t.in_w != W || t.in_h != H) return fail("patch: terms disagree on the grid");
+        if (t.in_w != t0.in_w || t.in_h != t0.in_h) return fail("patch: terms disagree on the grid");
         if (t.in_cp != cp || cp % 16 || cp < t.cin) return fail("patch: bad channel padding");
         if (t.cout != t0.cout) return fail("patch: terms disagree on cout");
         if (t.src != (int)i) return fail("patch: term i must read source i");
     }
-    P.w = W; P.h = H; P.in_cp = cp; P.fold = fold;
+    P.w = W; P.h = H; P.in_cp = cp; P.fold = fold; P.s2d = s2c ? 1 : 0;
     P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
     P.cout = t0.cout;
     P.npad = pad16(t0.cout);
@@ -240,7 +246,9 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     const int rows128 = kTileM / Wt;
     if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
     int kmax = 1;
-    for (const TermSpec& t : terms) kmax = std::max(kmax, t.k);
+    for (const TermSpec& t : terms) kmax = std::max(kmax, s2c ? (t.k + 1) / 2 : t.k);     // vertical taps that share one patch
+    int ktot = 1;                                                                       // taps per output (pair-mode rule)
+    for (const TermSpec& t : terms) ktot = std::max(ktot, t.k * t.k);
     // a phase of a stride-2 transposed conv: taps = {dy} x {dx}, consecutive offsets on the input grid
     std::vector<Tap> ph_taps;
     int ph_dy0 = 0, ph_nv = 0, ph_dx0 = 0, ph_nh = 0;
@@ -265,7 +273,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // CTA pairs (cta_group::2): APVAE_PATCH_2CTA=1/0 overrides the default
     // Measured on B200 (1000 samples): 96->96 5x5 @32^2 1121 -> 1436 TFLOP/s, 192->192 3x3 @16^2 1073 -> 1214, but
     // 96->96 3x3 @32^2 859 -> 819: the pair's cross-CTA barrier round trips need enough K per tile to pay off.
-    int two = ((long long)(phase >= 0 ? ph_nv * ph_nh : kmax * kmax) * cp >= 1500) ? 1 : 0;
+    int two = ((long long)(phase >= 0 ? ph_nv * ph_nh : ktot) * cp >= 1500) ? 1 : 0;
     if (const char* e = getenv("APVAE_PATCH_2CTA")) two = atoi(e) != 0;
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;
@@ -315,20 +323,70 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     for (const TermSpec& t : terms)
         if (t.bias) for (int n = 0; n < t.cout; ++n) P.bias[n] += t.bias[n];
     P.macs_per_image = 0;
+    auto pack_tap = [&](const TermSpec& t, int c0, int di, int dj) {
+        const size_t base = P.wpack.size();
+        P.wpack.resize(base + (size_t)P.npad * P.kc, 0);
+        const size_t tap_off = (size_t)di * t.k + dj;
+        for (int n = 0; n < t.cout; ++n)
+            for (int kk = 0; kk < P.kc; ++kk) {
+                const int ci = c0 * P.kc + kk;
+                if (ci >= t.cin) break;
+                const float w = t.transpose ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
+                                            : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
+                P.wpack[base + (size_t)n * P.kc + kk] = f32_to_bf16(w);
+            }
+        ++P.num_items;
+    };
     for (const TermSpec& t : terms) {
+        const int used_chunks = (t.cin + P.kc - 1) / P.kc;
+        if (s2c) {
+            // taps by (row phase, column phase, dx); the vertical taps of one (row phase) are consecutive row shifts
+            const std::vector<Tap> taps = enumerate_taps(t, 0, 0);
+            int map_of[2] = {-1, -1}, dy0[2] = {0, 0}, nv[2] = {0, 0};
+            for (int ph = 0; ph < 2; ++ph) {
+                int lo = 1000, hi2 = -1000;
+                for (const Tap& tp : taps) if (tp.ph == ph) { lo = std::min(lo, tp.dy); hi2 = std::max(hi2, tp.dy); }
+                if (hi2 < lo) continue;
+                if (P.nmaps >= kPatchMaxMaps) return fail("patch: too many activation maps");
+                map_of[ph] = P.nmaps; dy0[ph] = lo; nv[ph] = hi2 - lo + 1;
+                P.map_src[P.nmaps] = t.src; P.map_ph[P.nmaps] = ph; P.prow[P.nmaps] = P.rows_tile + nv[ph] - 1;
+                ++P.nmaps;
+            }
+            for (int c0 = 0; c0 < used_chunks; ++c0)
+                for (int ph = 0; ph < 2; ++ph) {
+                    if (map_of[ph] < 0) continue;
+                    for (int cph = 0; cph < 2; ++cph)
+                        for (int dx = -8; dx <= 8; ++dx) {
+                            std::vector<const Tap*> col(nv[ph], nullptr);
+                            int found = 0;
+                            for (const Tap& tp : taps)
+                                if (tp.ph == ph && tp.cbase == cph * cp && tp.dx == dx) { col[tp.dy - dy0[ph]] = &tp; ++found; }
+                            if (!found) continue;
+                            if (found != nv[ph]) return fail("patch: stride-2 taps are not a product set");
+                            PatchGroup gr;
+                            gr.src = (int16_t)map_of[ph]; gr.dx = (int16_t)dx; gr.py0 = (int16_t)dy0[ph]; gr.k = (int16_t)nv[ph];
+                            gr.c0 = cph * cp + c0 * P.kc; gr.prow = P.prow[map_of[ph]];
+                            P.groups.push_back(gr);
+                            for (int j = 0; j < nv[ph]; ++j) pack_tap(t, c0, col[j]->di, col[j]->dj);
+                        }
+                }
+            P.macs_per_image += (double)t.k * t.k * t.cin * t.cout * H * W;
+            continue;
+        }
         int o, lo_h, lo_w, hi;
         same_padding(H, t.k, 1, &o, &lo_h, &hi);
         same_padding(W, t.k, 1, &o, &lo_w, &hi);
         const int nv = phase >= 0 ? ph_nv : t.k, nh = phase >= 0 ? ph_nh : t.k;
         const int dy0 = phase >= 0 ? ph_dy0 : -lo_h, dx0 = phase >= 0 ? ph_dx0 : -lo_w;
-        P.prow[t.src] = P.rows_tile + nv - 1;
-        const int used_chunks = (t.cin + P.kc - 1) / P.kc;
+        P.map_src[P.nmaps] = t.src; P.map_ph[P.nmaps] = 0;
+        P.prow[P.nmaps] = P.rows_tile + nv - 1;
+        const int map = P.nmaps++;
         for (int c0 = 0; c0 < used_chunks; ++c0) {
             for (int g = 0; g < nh; ++g) {             // dx ascending
                 const int dx = dx0 + g;
                 PatchGroup gr;
-                gr.src = (int16_t)t.src; gr.dx = (int16_t)dx; gr.py0 = (int16_t)dy0; gr.k = (int16_t)nv;
-                gr.c0 = c0 * P.kc; gr.prow = P.prow[t.src];
+                gr.src = (int16_t)map; gr.dx = (int16_t)dx; gr.py0 = (int16_t)dy0; gr.k = (int16_t)nv;
+                gr.c0 = c0 * P.kc; gr.prow = P.prow[map];
                 P.groups.push_back(gr);
                 for (int j = 0; j < nv; ++j) {         // dy ascending
                     const int dy = dy0 + j;
@@ -341,18 +399,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                         dj = t.transpose ? lo_w - dx : dx + lo_w;
                         di = t.transpose ? lo_h - dy : dy + lo_h;
                     }
-                    const size_t base = P.wpack.size();
-                    P.wpack.resize(base + (size_t)P.npad * P.kc, 0);
-                    const size_t tap_off = (size_t)di * t.k + dj;
-                    for (int n = 0; n < t.cout; ++n)
-                        for (int kk = 0; kk < P.kc; ++kk) {
-                            const int ci = c0 * P.kc + kk;
-                            if (ci >= t.cin) break;
-                            const float w = t.transpose ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
-                                                        : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
-                            P.wpack[base + (size_t)n * P.kc + kk] = f32_to_bf16(w);
-                        }
-                    ++P.num_items;
+                    pack_tap(t, c0, di, dj);
                 }
             }
         }

@@ -56,7 +56,13 @@ struct PatchPlan {
     int w = 0, h = 0, rows_tile = 0, macc = 1, tiles_y = 0;
     int fold = 1;                  // 2: 8-pixel-wide images, two per tile row (the kernel sees a 16-wide "image" per pair)
     int nsrc = 0;
-    int prow[kPatchMaxSrc] = {0, 0};
+    // activation tensor maps: one per source, or (stride-2 conv through the space-to-depth view, `s2d`) one per
+    // (source, row phase) in use; PatchGroup::src indexes this list
+    int nmaps = 0;
+    int map_src[kPatchMaxMaps] = {0, 0, 0, 0};
+    int map_ph[kPatchMaxMaps] = {0, 0, 0, 0};
+    int prow[kPatchMaxMaps] = {0, 0, 0, 0};     // patch rows (TMA box height) per map
+    int s2d = 0;                   // 1: stride-2 conv; w, h are the OUTPUT grid, the input is 2w x 2h
     int in_cp = 0;
     std::vector<PatchGroup> groups;
     int num_items = 0;
@@ -90,7 +96,7 @@ float bf16_to_f32(uint16_t h);
 bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, std::string* err);
 
 // Returns false (with *err = reason) when the op is not eligible for the patch kernel:
-// every term must be stride 1 on the same W x H grid with W in {8 (pairs of images, even capacity),16,32,64,128}, <= 2 terms, cout <= 256.
+// every term must be stride 1 (or every term a stride-2 conv2d with even input size) on the same W x H output grid with W in {8 (pairs of images, even capacity),16,32,64,128}, <= 2 terms, cout <= 256.
 // force_macc / force_cluster: 0 = choose automatically.
 // `phase` >= 0: plan that sub-pixel phase of a single stride-2 transposed term (see PatchPlan::phase).
 bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force_macc, int force_cluster,

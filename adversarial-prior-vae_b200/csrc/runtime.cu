@@ -104,11 +104,17 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     if (fold && (plan.fold != 2 || W != 8 || (plan.capacity_n & 1))) { if (err) *err = "patch: bad fold geometry for op " + op->name; return false; }
     if (fold && epi.res_mode == RES_EVEN) { if (err) *err = "patch: folded ops take no half-resolution residual (op " + op->name + ")"; return false; }
     const cuuint64_t NP = fold ? (cuuint64_t)plan.capacity_n / 2 : (cuuint64_t)plan.capacity_n;
-    for (int s = 0; s < plan.nsrc; ++s) {
-        cuuint64_t dims[5] = {C, W, fold ? 2u : 1u, H, NP};
-        cuuint64_t strides[4] = {C * 2, (fold ? H : 1) * W * C * 2, W * C * 2, (fold ? 2 : 1) * H * W * C * 2};
+    // one map per (source, row phase): a stride-2 conv reads the space-to-depth view of its 2H x 2W input, column phase
+    // folded into the channel dim (2C), row phase selected by the map's base address (planner.h: PatchPlan::s2d)
+    const cuuint64_t cs = plan.s2d ? 2 : 1;
+    const cuuint64_t row_b = cs * cs * W * C * 2, img_b = H * row_b;      // bytes per grid row (cs input rows) and per image
+    if (plan.nmaps < 1 || plan.nmaps > kPatchMaxMaps) { if (err) *err = "patch: bad map count for op " + op->name; return false; }
+    for (int s = 0; s < plan.nmaps; ++s) {
+        cuuint64_t dims[5] = {cs * C, W, fold ? 2u : 1u, H, NP};
+        cuuint64_t strides[4] = {cs * C * 2, fold ? img_b : row_b, row_b, (fold ? 2 : 1) * img_b};
         cuuint32_t box[5] = {(cuuint32_t)plan.kc, (cuuint32_t)W, fold ? 2u : 1u, (cuuint32_t)plan.prow[s], 1};
-        CUresult r = encode(&p.tm_a[s], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(src_ptrs[s]), dims, strides,
+        char* base = static_cast<char*>(const_cast<void*>(src_ptrs[plan.map_src[s]])) + (size_t)plan.map_ph[s] * (cs * W * C * 2);
+        CUresult r = encode(&p.tm_a[s], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims, strides,
                             box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc),
                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
         if (r != CUDA_SUCCESS) {
@@ -116,7 +122,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             return false;
         }
     }
-    for (int s = plan.nsrc; s < kPatchMaxSrc; ++s) p.tm_a[s] = p.tm_a[0];
+    for (int s = plan.nmaps; s < kPatchMaxMaps; ++s) p.tm_a[s] = p.tm_a[0];
     {
         cuuint64_t dims[2] = {(cuuint64_t)plan.kc, (cuuint64_t)plan.num_items * plan.npad};
         cuuint64_t strides[1] = {(cuuint64_t)plan.kc * 2};
@@ -302,6 +308,7 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
 
 int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
     if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
+    if (op.is_heads) return launch_pixel_heads(op.heads, (long long)n_valid * op.heads.pixels_per_image, stream);
     if (op.is_patch) {
         op.pparams.n_real = n_valid;
         op.pparams.n_valid = op.pparams.fold > 1 ? (n_valid + 1) / 2 : n_valid;

@@ -5,6 +5,7 @@
 #include <string>
 #include <vector>
 #include "planner.h"
+#include "kernels.h"
 #include "tapgemm.h"
 #include "patchgemm.h"
 
@@ -47,6 +48,8 @@ struct DevOp {
     bool is_patch = false;          // true: the A-stationary kernel (patchgemm.h) runs this op
     PatchGroup* d_groups = nullptr;
     PatchGemmParams pparams;
+    bool is_heads = false;          // true: G_theta's 1x1 output heads on the CUDA cores (kernels.h: HeadsParams)
+    HeadsParams heads;
     double macs_per_image = 0;
     int capacity_n = 0;
     ~DevOp();

@@ -196,6 +196,8 @@ typedef struct apvae_plan_info {
     /* A-stationary ("patch") plan, when the op is eligible (stride 1, width 8..128) and not disabled */
     int patch, patch_macc, patch_cluster, patch_rows_tile, patch_groups, patch_items, patch_a_stages, patch_b_stages;
     int patch_prow[2];
+    /* activation maps of the patch plan: (source, row phase); patch_s2d = 1: stride-2 conv through the space-to-depth view */
+    int patch_s2d, patch_nmaps, patch_map_src[4], patch_map_ph[4], patch_map_prow[4];
     int patch_fold;   /* 2: 8-pixel-wide images are processed in pairs, side by side in one 16-wide tile row (even capacity) */
 } apvae_plan_info;
 

@@ -87,7 +87,7 @@ def synthetic_images(shape, seed=0):
 def emulate_patch_plan(plan, srcs, n_valid):
     """Evaluate the A-stationary ("patch") plan on the CPU exactly as patchgemm.cu would: per tile and
     group, one zero-filled patch [prow, W, kc]; tap j reads the patch advanced by j*W rows, accumulator
-    m by 128 rows.  Folded plans (8-wide images, patch_fold == 2) lay two images side by side: the patch
+    m by 128 rows.  Stride-2 convs (patch_s2d) read the space-to-depth view of the input.  Folded plans (8-wide images, patch_fold == 2) lay two images side by side: the patch
     is [prow, 2 images, 8, kc] and a tile row is 16 pixels.  srcs: float arrays [N, H, W, Cp].
     Returns [n_valid, H, W, npad]."""
     i = plan.info
@@ -105,8 +105,11 @@ def emulate_patch_plan(plan, srcs, n_valid):
             y0 = ty * rt
             acc = np.zeros((macc * 128, i.npad), dtype=np.float64)
             item = 0
-            for src, dx, py0, k, c0, prow in groups:
-                x = np.asarray(srcs[src], dtype=np.float64)
+            for mp, dx, py0, k, c0, prow in groups:
+                x = np.asarray(srcs[i.patch_map_src[mp]], dtype=np.float64)
+                if i.patch_s2d:      # space-to-depth view of the 2H x 2W input: [N, H, row phase, W, 2 Cp], one row phase per map
+                    nn, hh, ww, cc = x.shape
+                    x = x.reshape(nn, hh // 2, 2, ww // 2, 2 * cc)[:, :, i.patch_map_ph[mp]]
                 patch = np.zeros((prow, fold, W, kc))
                 for py in range(prow):
                     y = y0 + py0 + py

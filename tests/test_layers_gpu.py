@@ -346,3 +346,59 @@ def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, o
         raw = out_raw.float().cpu().numpy()
         assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
         assert np.all(raw[keep:] == 7.0)
+
+
+S2_CASES = [
+    # k, H, W (input), cin, cout, fused 1x1 stride-2 shortcut, n_valid, cap
+    (3, 32, 32, 64, 128, True, 3, 4),      # arch A D_psi/level_3/conv_1
+    (3, 16, 16, 128, 256, True, 5, 6),     # D_psi/level_4/conv_1: 8-wide output, image pairs
+    (3, 32, 32, 96, 192, True, 2, 2),      # q_net/level_2/conv_1
+    (5, 64, 64, 3, 32, False, 2, 3),       # celebA first block
+    (3, 64, 64, 32, 64, True, 1, 2),
+    (1, 32, 32, 16, 16, False, 3, 3),
+]
+
+
+@pytest.mark.parametrize('two_cta', [0, 1])
+@pytest.mark.parametrize('k,H,W,cin,cout,shortcut,n_valid,cap', S2_CASES)
+def test_stride2_conv_on_patch_kernel(k, H, W, cin, cout, shortcut, n_valid, cap, two_cta, monkeypatch):
+    """conv2d(stride 2, SAME) (conv2d_.py:204-211) on the A-stationary kernel through the space-to-depth view of the
+    input (one tensor map per row phase), optionally with the block's 1x1 stride-2 shortcut as a second term
+    (resnet.py:234-241); bf16 raw + act outputs through the TMA epilogue."""
+    torch = _torch()
+    from apvae.plan import Plan, pad16
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))
+    rs = np.random.RandomState(k + H + cin + cout)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
+    kern = bf16_round(rs.normal(size=(k, k, cin, cout)) / np.sqrt(k * k * cin))
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    terms = [dict(src=0, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)]
+    srcs = [t(pad_channels(x, pad16(cin)))]
+    want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
+    if shortcut:
+        x2 = bf16_round(rs.normal(size=(cap, H, W, cin)))
+        ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) / np.sqrt(cin))
+        bs = rs.normal(size=(cout,)).astype(np.float32)
+        terms.append(dict(src=1, stride=2, in_h=H, in_w=W, kernel=ks, bias=bs))
+        srcs.append(t(pad_channels(x2, pad16(cin))))
+        want = want + O.conv2d(x2.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
+    plan = Plan(terms, cap)
+    assert plan.info.patch == 1 and plan.info.patch_s2d == 1
+    npad = pad16(cout)
+    out_raw = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    out_act = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    plan.run(srcs, n_valid, out_raw=out_raw, out_act=out_act)
+    torch.cuda.synchronize()
+    raw = out_raw.float().cpu().numpy()
+    act = out_act.float().cpu().numpy()
+    scale = max(1.0, float(np.abs(want).max()))
+    assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
+    assert np.abs(act[:n_valid, ..., :cout] - O.leaky_relu(want[:n_valid])).max() <= 2 ** -7 * scale
+    keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 else 0)
+    assert np.all(raw[keep:] == 7.0) and np.all(act[keep:] == 7.0)
+    # fp32 output through the generic epilogue of the same kernel
+    o32 = torch.zeros((cap, H // 2, W // 2, cout), dtype=torch.float32, device='cuda')
+    plan.run(srcs, n_valid, out_f32=o32, f32_cols=cout)
+    _check(o32.cpu().numpy()[:n_valid], want[:n_valid])

@@ -129,6 +129,46 @@ def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc, monkeypa
     np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-9)
 
 
+S2_PATCH_CASES = [
+    # k, H, W (input), cin, cout, with a fused 1x1 stride-2 shortcut term
+    (3, 32, 32, 64, 128, True),      # arch A D_psi/level_3/conv_1
+    (3, 16, 16, 32, 48, True),       # 8-wide output: image pairs
+    (5, 64, 64, 3, 32, False),       # celebA first block
+    (1, 32, 32, 16, 16, False),
+    (3, 32, 64, 16, 24, False),      # non-square
+]
+
+
+@pytest.mark.parametrize('k,H,W,cin,cout,shortcut', S2_PATCH_CASES)
+def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut, monkeypatch):
+    """Stride-2 conv2d on the A-stationary kernel: the input is read through its space-to-depth view, one tensor map
+    per row phase, column phase folded into the channel coordinate; vertical taps of one row phase share a patch."""
+    from helpers import emulate_patch_plan
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    rs = np.random.RandomState(k * 100 + cin + cout)
+    n = 2
+    x = bf16_round(rs.normal(size=(n, H, W, cin)))
+    kern = bf16_round(rs.normal(size=(k, k, cin, cout)) * 0.2)
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    terms = [dict(src=0, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)]
+    srcs = [pad_channels(x, pad16(cin))]
+    want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
+    if shortcut:
+        x2 = bf16_round(rs.normal(size=(n, H, W, cin)))
+        ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.2)
+        bs = rs.normal(size=(cout,)).astype(np.float32)
+        terms.append(dict(src=1, stride=2, in_h=H, in_w=W, kernel=ks, bias=bs))
+        srcs.append(pad_channels(x2, pad16(cin)))
+        want = want + O.conv2d(x2.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
+    plan = Plan(terms, n)
+    assert plan.info.patch == 1 and plan.info.patch_s2d == 1
+    assert plan.info.patch_fold == (2 if W == 16 else 1)
+    assert plan.info.patch_nmaps == (1 if k == 1 else 2) + (1 if shortcut else 0)
+    got = emulate_patch_plan(plan, srcs, n)[..., :cout]
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+
+
 def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     from helpers import emulate_patch_plan
     monkeypatch.setenv('APVAE_PATCH', '1')
@@ -145,9 +185,9 @@ def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
         O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 1)
     np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
-    # not eligible: stride 2, 8x8 grids with an odd capacity (they run as image pairs), arch-M widths
+    # not eligible: stride 2 onto a 4x4 grid, 8x8 grids with an odd capacity (they run as image pairs), arch-M widths
     assert Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), in_h=8, in_w=8)], 4).info.patch_fold == 2
-    for kw in (dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=28, in_w=28)):
+    for kw in (dict(stride=2, in_h=8, in_w=8), dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=28, in_w=28)):
         p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1)
         assert p.info.patch == 0
     monkeypatch.setenv('APVAE_PATCH', '0')
