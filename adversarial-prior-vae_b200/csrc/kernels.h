@@ -124,4 +124,25 @@ struct HeadsParams {
 };
 int launch_pixel_heads(const HeadsParams& p, long long pixels, void* stream);
 
+
+// A whole resnet_conv2d_block (resnet.py:272-364) with <= 3 input channels on the CUDA cores: D_psi/level_0 of the
+// CIFAR models is 3 -> 3 -> 16 channels at 32 x 32 (0.57 MMAC per image).  As implicit GEMMs its two convs pad K from 3
+// to 16 per tap and sit on the tensor pipe's per-instruction floor (3 and 18 TFLOP/s measured); here one CTA takes one
+// image through shared memory:  r = lrelu(conv_k(lrelu(x)) + b0);  out = conv_k(r) + b1 + x W_s + b_s.
+// r is rounded to bf16 (it is stored for the backward pass and that is what the unfused ops fed to conv_1).
+constexpr int kSmallBlockMaxCin = 3, kSmallBlockMaxCout = 16, kSmallBlockMaxK = 3, kSmallBlockMaxHW = 32;
+struct SmallBlockParams {
+    const void* in_raw;                   // bf16 [N, H, W, cp_in]
+    void* r_act;                          // bf16 [N, H, W, cp_in]: lrelu(conv_0 + b0), padding channels zero
+    void* out_raw;  void* out_act;        // bf16 [N, H, W, ldo]: padding channels zero (either may be null)
+    int H, W, cp_in, cin, cout, ldo, k;
+    float alpha;
+    float b0[kSmallBlockMaxCin];
+    float b1[kSmallBlockMaxCout];         // conv_1 bias + shortcut bias
+    float w0[kSmallBlockMaxK * kSmallBlockMaxK * kSmallBlockMaxCin * kSmallBlockMaxCin];      // [k][k][cin][cin]
+    float w1[kSmallBlockMaxK * kSmallBlockMaxK * kSmallBlockMaxCin * kSmallBlockMaxCout];     // [k][k][cin][cout]
+    float ws[kSmallBlockMaxCin * kSmallBlockMaxCout];                                         // [cin][cout] 1x1 shortcut
+};
+int launch_small_block(const SmallBlockParams& p, int n, void* stream);
+
 }  // namespace apvae

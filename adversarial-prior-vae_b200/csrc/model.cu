@@ -172,6 +172,46 @@ bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& 
     Tensor r = alloc_act(cap, H, Wd, cin), r_lo;
     if (!r.ptr) return false;
     if (sp) { r_lo = alloc_act(cap, H, Wd, cin); if (!r_lo.ptr) return false; }
+    // <= 3 input channels (D_psi/level_0 of the CIFAR models: 3 -> 3 -> 16 at 32 x 32): the whole block is one HBM-bound
+    // CUDA-core kernel (block0.cu) with fp32 weights; APVAE_SMALL_BLOCK=0 keeps the two tensor-core ops (tuning / A-B only)
+    const char* esb = getenv("APVAE_SMALL_BLOCK");
+    if (!sp && !(esb && esb[0] == '0') && s == 1 && k == kSmallBlockMaxK && cin <= kSmallBlockMaxCin && cout == kSmallBlockMaxCout &&
+        use_sc && H <= kSmallBlockMaxHW && Wd <= kSmallBlockMaxHW) {
+        const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cin, cout}), *bs = W_(pre + "shortcut/bias", {cout});
+        if (!ks || !bs) return false;
+        Pair o;
+        if (need_raw) { o.raw = alloc_act(cap, H, Wd, cout); if (!o.raw.ptr) return false; }
+        if (need_act) { o.act = alloc_act(cap, H, Wd, cout); if (!o.act.ptr) return false; }
+        std::unique_ptr<DevOp> op(new DevOp());
+        op->name = pre + "block";
+        op->is_small_block = true;
+        op->capacity_n = cap;
+        op->macs_per_image = ((double)k * k * cin * cin + (double)k * k * cin * cout + (double)cin * cout) * H * Wd;
+        SmallBlockParams& sb = op->sblock;
+        memset(&sb, 0, sizeof(sb));
+        sb.in_raw = in.raw.ptr; sb.r_act = r.ptr; sb.out_raw = o.raw.ptr; sb.out_act = o.act.ptr;
+        sb.H = H; sb.W = Wd; sb.cp_in = in.raw.cp; sb.cin = cin; sb.cout = cout; sb.ldo = pad16(cout); sb.k = k;
+        sb.alpha = 0.2f;
+        for (int c = 0; c < cin; ++c) sb.b0[c] = b0->v[c];
+        for (int c = 0; c < cout; ++c) sb.b1[c] = b1->v[c] + bs->v[c];
+        // kernel template is instantiated on cin (weights packed [tap][cin][cout] with that cin)
+        for (int tp = 0; tp < k * k; ++tp)
+            for (int ci = 0; ci < cin; ++ci) {
+                for (int co = 0; co < cin; ++co) sb.w0[(tp * cin + ci) * cin + co] = k0->v[((size_t)tp * cin + ci) * cin + co];
+                for (int co = 0; co < cout; ++co) sb.w1[(tp * cin + ci) * cout + co] = k1->v[((size_t)tp * cin + ci) * cout + co];
+            }
+        for (int ci = 0; ci < cin; ++ci)
+            for (int co = 0; co < cout; ++co) sb.ws[ci * cout + co] = ks->v[(size_t)ci * cout + co];
+        if (macs) *macs += op->macs_per_image;
+        prog.push_back(std::move(op));
+        if (tape) {
+            BlockTape t; t.scope = pre; t.deconv = false; t.use_shortcut = use_sc; t.k = k; t.stride = s;
+            t.cin = cin; t.cout = cout; t.in = in; t.r_act = r; t.out = o;
+            tape->push_back(t);
+        }
+        *out = o;
+        return true;
+    }
     {
         Epilogue e; e.out_act = r.ptr; e.out_act_lo = r_lo.ptr; e.ldo = r.cp;
         std::vector<TermSpec> terms; std::vector<const void*> srcs;

@@ -270,10 +270,14 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
     int tpi_want = std::max(1, std::min(kmax, (int)(32768u / P.tap_bytes)));
     if (const char* e = getenv("APVAE_PATCH_TPI")) { const int v = atoi(e); if (v >= 1 && v <= kmax) tpi_want = v; }
-    // CTA pairs (cta_group::2): APVAE_PATCH_2CTA=1/0 overrides the default
-    // Measured on B200 (1000 samples): 96->96 5x5 @32^2 1121 -> 1436 TFLOP/s, 192->192 3x3 @16^2 1073 -> 1214, but
-    // 96->96 3x3 @32^2 859 -> 819: the pair's cross-CTA barrier round trips need enough K per tile to pay off.
-    int two = ((long long)(phase >= 0 ? ph_nv * ph_nh : ktot) * cp >= 1500) ? 1 : 0;
+    // CTA pairs (cta_group::2): APVAE_PATCH_2CTA=1/0 overrides the default; APVAE_PATCH_2CTA_MINK moves the threshold.
+    // Measured on B200 (1000 samples, TFLOP/s single -> pair): 96->96 5x5 @32^2 1121 -> 1436, 192->192 3x3 @16^2
+    // 1073 -> 1214, 128->128 3x3 @16^2 967 -> 1170, 64->64 3x3 @32^2 697 -> 786, 96->96 3x3 @32^2 778 -> 808; the
+    // 16- and 32-channel layers (K < 500 per output) sit on the A-operand fetch floor either way and the whole step
+    // was best with the threshold at 500 (sweep 1 / 100 / 250 / 500 / 1500 in one call: profiles/r1_notes.md).
+    int two_min_k = 500;
+    if (const char* e = getenv("APVAE_PATCH_2CTA_MINK")) two_min_k = atoi(e);
+    int two = ((long long)(phase >= 0 ? ph_nv * ph_nh : ktot) * cp >= two_min_k) ? 1 : 0;
     if (const char* e = getenv("APVAE_PATCH_2CTA")) two = atoi(e) != 0;
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;

@@ -17,7 +17,14 @@ D01 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '3', '--cout', '16', '--n'
 D10 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '16', '--cout', '16', '--n', N, '--outs', 'act']
 D20 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '32', '--cout', '32', '--n', N, '--outs', 'act']
 D30 = ['--k', '3', '--h', '32', '--w', '32', '--cin', '64', '--cout', '64', '--n', N, '--outs', 'act']
+L128 = ['--k', '3', '--h', '16', '--w', '16', '--cin', '128', '--cout', '128', '--n', N, '--outs', 'act']
 CASES = [
+    ('pair_D30_1cta', {'APVAE_PATCH_2CTA': '0'}, D30),
+    ('pair_D30_2cta', {'APVAE_PATCH_2CTA': '1'}, D30),
+    ('pair_D40_1cta', {'APVAE_PATCH_2CTA': '0'}, L128),
+    ('pair_D40_2cta', {'APVAE_PATCH_2CTA': '1'}, L128),
+    ('pair_96x3_1cta', {'APVAE_PATCH_2CTA': '0'}, L96_3 + ['--res', 'even']),
+    ('pair_96x3_2cta', {'APVAE_PATCH_2CTA': '1'}, L96_3 + ['--res', 'even']),
     ('tap192', {'APVAE_PATCH': '0'}, L192),
     ('tap192_res', {'APVAE_PATCH': '0'}, L192 + ['--res', 'same']),
     ('patch192', {}, L192),
