@@ -188,6 +188,79 @@ class POmegaNet(object):
         raise KeyError(name)
 
 
+class _UnitNormal(object):
+    """spt.Normal(mean=0, logstd=0) as the scripts build the base p(z) (dmm_cifar10.py:600-603)."""
+    is_continuous = True
+    is_reparameterized = True
+
+
+class EnergyDistribution(object):
+    """EnergyDistribution(pz, G, D, log_Z, xi, mcmc_iterator, mcmc_alpha, initial_z) (dmm_cifar10.py:97-252):
+    p(z) proportional to exp(-w * xi * D(G(z)) - 0.5 |z|^2).  G and D must be the bound Script's G_theta / D_psi
+    (the library evaluates D(G(z)) and its gradient itself); `xi` is the sigmoid-ed weight the scripts pass
+    (`tf.nn.sigmoid(xi_node)`, :607) and must agree with the model's `xi_raw`.
+
+    log_prob(given) returns the Gaussian log p_N(z) carrying .energy / .log_energy_prob / .pure_energy (:164-177);
+    sample(n_samples) runs `mcmc_iterator` MALA steps from `initial_z` (or a N(0, I) draw) and returns a stochastic
+    tensor carrying .history_e_z / .history_pure_e_z / .history_ratio (:179-239)."""
+
+    def __init__(self, pz, G, D, log_Z=0., xi=1.0, mcmc_iterator=0, mcmc_alpha=None, mcmc_algorithm='mala',
+                 mcmc_space='z', initial_z=None, seed=0):
+        if not getattr(pz, 'is_continuous', False):
+            raise TypeError('`base_distribution` must be a continuous distribution.')         # :117-119
+        script = getattr(G, '__self__', None)
+        if not isinstance(script, Script) or getattr(D, '__self__', None) is not script:
+            raise TypeError('G and D must be the G_theta / D_psi of one apvae.dmm.Script')
+        if mcmc_algorithm != 'mala' or mcmc_space != 'z':
+            raise ValueError("only mcmc_algorithm='mala' in mcmc_space='z' exists (as in the reference)")
+        self._script, self._pz, self._G, self._D = script, pz, G, D
+        m = script.model
+        want = 1.0 / (1.0 + math.exp(-m.xi_raw))
+        if abs(float(xi) - want) > 1e-6 * max(1.0, abs(want)):
+            raise ValueError('xi = %g disagrees with sigmoid(xi_raw) = %g of the model' % (float(xi), want))
+        self._xi = float(xi)
+        self._log_Z = max(float(log_Z), -20.0)                                                # :135
+        self._mcmc_iterator = int(mcmc_iterator)
+        self._mcmc_alpha = m.config.smallest_step if mcmc_alpha is None else float(mcmc_alpha)
+        self._initial_z = initial_z
+        self._seed = seed
+
+    pz = property(lambda self: self._pz)
+    G = property(lambda self: self._G)
+    D = property(lambda self: self._D)
+    xi = property(lambda self: self._xi)
+    log_Z = property(lambda self: self._log_Z)
+
+    def set_log_Z(self, new_log_Z):
+        self._log_Z = new_log_Z
+        return new_log_Z
+
+    def log_prob(self, given, group_ndims=0, name=None, y=None):
+        m = self._script.model
+        z = m._f32(given)
+        d = m.config.z_dim
+        d_g = m.energy_of_latents(z)
+        log_pn = -0.5 * (z * z).sum(-1) - 0.5 * d * math.log(2 * math.pi)      # spt.Normal(0, 1).log_prob, group_ndims=1
+        return _LogProb(log_pn, d_g, self._script.w_xi(), self._log_Z, d)
+
+    def sample(self, n_samples=None, group_ndims=0, is_reparameterized=None, compute_density=None, name=None):
+        m = self._script.model
+        z0 = self._initial_z
+        if z0 is None:
+            if n_samples is None:
+                raise ValueError('sample() needs n_samples or an initial_z')
+            z0 = m.fill_normal((int(n_samples), m.config.z_dim), seed=self._seed)
+        if self._mcmc_iterator > 0:
+            out = m.mala(z0, self._mcmc_iterator, alpha=self._mcmc_alpha, seed=self._seed)
+        else:
+            out = {'z': m._f32(z0)}
+        t = _StochasticTensor(tensor=out['z'], distribution=self)
+        t.history_e_z = out.get('history_e_z')
+        t.history_pure_e_z = out.get('history_pure_e_z')
+        t.history_ratio = out.get('history_ratio')
+        return t
+
+
 class PlanarFlows(object):
     def __init__(self, n_layers, name):
         if n_layers < 1:
@@ -230,6 +303,12 @@ class Script(object):
         if n_z is None:
             raise ValueError('p_omega_net needs n_z')
         return POmegaNet(self, n_z, z_omega, seed)
+
+    def Normal(self, mean=0.0, logstd=0.0):
+        """The base p(z) of the scripts, spt.Normal(mean=zeros, logstd=zeros) (dmm_cifar10.py:600-603)."""
+        if mean != 0.0 or logstd != 0.0:
+            raise ValueError('the energy prior is built on N(0, I)')
+        return _UnitNormal()
 
     def G_theta(self, z, return_std=False):
         return self.model.decode(z, return_std=return_std)

@@ -288,6 +288,13 @@ class Model(object):
                              _ptr(he), _ptr(hp), _ptr(hr), _stream()), self._h)
         return dict(z=z2.reshape(shape), history_e_z=he, history_pure_e_z=hp, history_ratio=hr)
 
+    def fill_normal(self, shape, seed=0, offset=0, truncated=False):
+        """N(0, 1) draws (Philox, in-kernel) as tf.random_normal inside zd.Normal.sample; `truncated`: resampled
+        beyond 2 sigma (experiment/truncated_normal.py:96-107)."""
+        out = self._empty(*tuple(int(v) for v in shape))
+        check(lib.apvae_fill_normal(_ptr(out), out.numel(), int(seed), int(offset), int(bool(truncated)), _stream()))
+        return out
+
     def latent_gan(self, n, z_omega=None, seed=0):
         """gan_z = p_omega_net(n_z=n)['f_z'].distribution.mean (dmm_cifar10.py:623-635,967-969): G_omega applied to
         z_omega ~ N(0, I_128) (fed [n,128] or drawn in-kernel) -> [n, z_dim], the `initial_z` of plot_samples' MALA loop."""

@@ -19,6 +19,7 @@ struct apvae_plan {
     bool has_patch = false;
     PatchPlan patch;
     std::vector<PatchPlan> phases;   // stride-2 transposed conv: four sub-pixel phase plans (A-stationary kernel)
+    std::vector<PatchPlan> row_phases;   // ... or two plans, one per output row phase, both column phases merged into N
 };
 
 static int env_int(const char* name) {
@@ -440,6 +441,16 @@ int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, 
                     p->phases.clear();
                     break;
                 }
+            // both column phases per op (two ops); used by plan_run when the output rows are unpadded
+            const char* emg = getenv("APVAE_PATCH_MERGE");
+            if (!p->phases.empty() && !(emg && emg[0] == '0')) {
+                p->row_phases.resize(2);
+                for (int py = 0; py < 2; ++py)
+                    if (!plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->row_phases[py], &pe, 4 + py)) {
+                        p->row_phases.clear();
+                        break;
+                    }
+            }
         }
     }
     *out = p;
@@ -528,6 +539,19 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
     // the op, or the four phase ops of a stride-2 transposed conv (only with a bf16-only epilogue; else the tap-GEMM op)
     std::vector<std::unique_ptr<DevOp>> ops;
     bool phased = !p->phases.empty();
+    if (!p->row_phases.empty()) {            // two merged ops when the epilogue allows it
+        bool ok = true;
+        for (int py = 0; py < 2 && ok; ++py) {
+            std::unique_ptr<DevOp> o(new DevOp());
+            o->name = "plan_run/rows" + std::to_string(py);
+            std::string e2;
+            ok = devop_create_patch(dev, p->row_phases[py], src_dev, ep, o.get(), &e2);
+            if (ok) ops.push_back(std::move(o));
+        }
+        if (ok) phased = false;
+        else { ops.clear(); cudaGetLastError(); }
+    }
+    const bool merged_ok = !ops.empty();
     if (phased) {
         for (int ph = 0; ph < 4 && phased; ++ph) {
             std::unique_ptr<DevOp> o(new DevOp());
@@ -538,7 +562,7 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
         }
         if (!phased) { ops.clear(); cudaGetLastError(); }
     }
-    if (!phased) {
+    if (!phased && !merged_ok) {
         std::unique_ptr<DevOp> o(new DevOp());
         o->name = "plan_run";
         const bool use_patch = p->has_patch;

@@ -69,6 +69,27 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
         std::vector<std::unique_ptr<DevOp>> ops;
         double m = 0;
         bool ok = true;
+        // two ops, one per output row phase, each writing both column phases as one 2 * cout-wide row (needs unpadded
+        // output rows and 2 * cout <= 256); else one op per sub-pixel phase.  APVAE_PATCH_MERGE=0: always four.
+        const char* emg = getenv("APVAE_PATCH_MERGE");
+        if (!(emg && emg[0] == '0')) {
+            for (int py = 0; py < 2 && ok; ++py) {
+                PatchPlan pp;
+                std::string e2;
+                std::unique_ptr<DevOp> o(new DevOp());
+                o->name = name + "/rows" + std::to_string(py);
+                ok = plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pp, &e2, 4 + py) && pp.npad <= patch_max_n &&
+                     devop_create_patch(dev, pp, srcs.data(), epi, o.get(), &e2);
+                if (ok) { m += pp.macs_per_image; ops.push_back(std::move(o)); }
+            }
+            if (ok) {
+                if (macs) *macs += m;
+                for (auto& o : ops) prog.push_back(std::move(o));
+                return true;
+            }
+            cudaGetLastError();
+            ops.clear(); m = 0; ok = true;
+        }
         for (int ph = 0; ph < 4 && ok; ++ph) {
             PatchPlan pp;
             std::string e2;

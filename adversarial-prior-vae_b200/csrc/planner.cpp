@@ -239,8 +239,12 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     }
     P.w = W; P.h = H; P.in_cp = cp; P.fold = fold; P.s2d = s2c ? 1 : 0;
     P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
-    P.cout = t0.cout;
-    P.npad = pad16(t0.cout);
+    // phase 4 + py: both column phases of output rows 2y + py in ONE op.  Its N is [px = 0 | px = 1] x cout, i.e. the two
+    // adjacent output pixels (2x, 2x + 1) of input pixel x as one contiguous 2 * cout row (no channel padding allowed)
+    const bool merged = phase >= 4;
+    if (merged && (phase > 5 || t0.cout % 16 || 2 * t0.cout > 256)) return fail("patch: merged column phases need cout % 16 == 0 and 2 * cout <= 256");
+    P.cout = merged ? 2 * t0.cout : t0.cout;
+    P.npad = pad16(P.cout);
     if (P.npad > 256) return fail("patch: cout > 256");
     P.nsrc = (int)terms.size();
     const int rows128 = kTileM / Wt;
@@ -252,16 +256,26 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // a phase of a stride-2 transposed conv: taps = {dy} x {dx}, consecutive offsets on the input grid
     std::vector<Tap> ph_taps;
     int ph_dy0 = 0, ph_nv = 0, ph_dx0 = 0, ph_nh = 0;
+    std::vector<Tap> ph_taps1;            // merged: the taps of column phase px = 1 (ph_taps holds px = 0)
     if (phase >= 0) {
-        ph_taps = enumerate_taps(t0, phase >> 1, phase & 1);
-        if (ph_taps.empty()) return fail("patch: phase has no taps");
+        ph_taps = enumerate_taps(t0, merged ? phase - 4 : phase >> 1, merged ? 0 : phase & 1);
+        if (merged) ph_taps1 = enumerate_taps(t0, phase - 4, 1);
+        if (ph_taps.empty() || (merged && ph_taps1.empty())) return fail("patch: phase has no taps");
         int dy1 = -1000, dx1 = -1000; ph_dy0 = 1000; ph_dx0 = 1000;
-        for (const Tap& tp : ph_taps) {
-            ph_dy0 = std::min(ph_dy0, tp.dy); dy1 = std::max(dy1, tp.dy);
-            ph_dx0 = std::min(ph_dx0, tp.dx); dx1 = std::max(dx1, tp.dx);
-        }
+        for (const std::vector<Tap>* v : {&ph_taps, &ph_taps1})
+            for (const Tap& tp : *v) {
+                ph_dy0 = std::min(ph_dy0, tp.dy); dy1 = std::max(dy1, tp.dy);
+                ph_dx0 = std::min(ph_dx0, tp.dx); dx1 = std::max(dx1, tp.dx);
+            }
         ph_nv = dy1 - ph_dy0 + 1; ph_nh = dx1 - ph_dx0 + 1;
-        if (ph_nv * ph_nh != (int)ph_taps.size()) return fail("patch: phase taps are not a product set");
+        // every (dy, dx) of the bounding box must be used by at least one of the phases, and each phase's taps are distinct
+        for (int dy = ph_dy0; dy <= dy1; ++dy)
+            for (int dx = ph_dx0; dx <= dx1; ++dx) {
+                int hits = 0;
+                for (const std::vector<Tap>* v : {&ph_taps, &ph_taps1})
+                    for (const Tap& tp : *v) hits += (tp.dy == dy && tp.dx == dx);
+                if (hits < 1 || hits > (merged ? 2 : 1)) return fail("patch: phase taps are not a product set");
+            }
         kmax = ph_nv;
         P.phase = phase; P.out_scale = 2;
     }
@@ -325,11 +339,12 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // groups + packed weights + bias
     P.bias.assign(P.npad, 0.f);
     for (const TermSpec& t : terms)
-        if (t.bias) for (int n = 0; n < t.cout; ++n) P.bias[n] += t.bias[n];
+        if (t.bias) for (int n = 0; n < t.cout; ++n) { P.bias[n] += t.bias[n]; if (merged) P.bias[t.cout + n] += t.bias[n]; }
     P.macs_per_image = 0;
-    auto pack_tap = [&](const TermSpec& t, int c0, int di, int dj) {
-        const size_t base = P.wpack.size();
-        P.wpack.resize(base + (size_t)P.npad * P.kc, 0);
+    // one weight tile [npad][kc] per item; fill_tap writes kernel tap (di, dj) into rows row0 .. row0 + cout - 1 of the newest
+    auto new_item = [&]() { P.wpack.resize(P.wpack.size() + (size_t)P.npad * P.kc, 0); ++P.num_items; };
+    auto fill_tap = [&](const TermSpec& t, int c0, int di, int dj, int row0) {
+        const size_t base = P.wpack.size() - (size_t)P.npad * P.kc;
         const size_t tap_off = (size_t)di * t.k + dj;
         for (int n = 0; n < t.cout; ++n)
             for (int kk = 0; kk < P.kc; ++kk) {
@@ -337,10 +352,10 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                 if (ci >= t.cin) break;
                 const float w = t.transpose ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
                                             : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
-                P.wpack[base + (size_t)n * P.kc + kk] = f32_to_bf16(w);
+                P.wpack[base + (size_t)(row0 + n) * P.kc + kk] = f32_to_bf16(w);
             }
-        ++P.num_items;
     };
+    auto pack_tap = [&](const TermSpec& t, int c0, int di, int dj) { new_item(); fill_tap(t, c0, di, dj, 0); };
     for (const TermSpec& t : terms) {
         const int used_chunks = (t.cin + P.kc - 1) / P.kc;
         if (s2c) {
@@ -395,6 +410,12 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                 for (int j = 0; j < nv; ++j) {         // dy ascending
                     const int dy = dy0 + j;
                     int di = -1, dj = -1;
+                    if (merged) {                      // rows [0, cout): column phase 0; [cout, 2 cout): column phase 1
+                        new_item();
+                        for (const Tap& tp : ph_taps) if (tp.dy == dy && tp.dx == dx) fill_tap(t, c0, tp.di, tp.dj, 0);
+                        for (const Tap& tp : ph_taps1) if (tp.dy == dy && tp.dx == dx) fill_tap(t, c0, tp.di, tp.dj, t.cout);
+                        continue;
+                    }
                     if (phase >= 0) {
                         for (const Tap& tp : ph_taps)
                             if (tp.dy == dy && tp.dx == dx) { di = tp.di; dj = tp.dj; }
@@ -407,7 +428,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                 }
             }
         }
-        P.macs_per_image += (double)nv * nh * t.cin * t.cout * H * W;
+        P.macs_per_image += (merged ? (double)(ph_taps.size() + ph_taps1.size()) : (double)nv * nh) * t.cin * t.cout * H * W;
     }
     if ((int)P.groups.size() > kPatchMaxGroups) return fail("patch: too many groups");
     return true;

@@ -76,7 +76,7 @@ struct PatchPlan {
     int two_cta = 0;               // cta_group::2 pairs (cluster == 2): each CTA stores half of every weight tile
     // sub-pixel phase of a stride-2 transposed conv (-1: ordinary stride-1 op).  Phase (py, px) = (phase >> 1, phase & 1)
     // is a stride-1 correlation over the INPUT grid whose results land on output pixels (2y + py, 2x + px).
-    int phase = -1;
+    int phase = -1;                // 4 + py: both column phases of output rows 2y + py (N = [px 0 | px 1] x cout, see planner.cpp)
     int out_scale = 1;             // output grid = out_scale x input grid
     int capacity_n = 0;
     double macs_per_image = 0;

@@ -89,7 +89,7 @@ static bool check_epilogue(const Epilogue& epi, int npad, const std::string& nam
 bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void* const* src_ptrs, const Epilogue& epi,
                         DevOp* op, std::string* err) {
     EncodeTiledFn encode = reinterpret_cast<EncodeTiledFn>(dev.encode_fn);
-    if (!check_epilogue(epi, plan.npad, op->name, err)) return false;
+    if (!check_epilogue(epi, plan.phase >= 4 ? plan.npad / 2 : plan.npad, op->name, err)) return false;
     const size_t ngroups = plan.groups.size();
     if (ngroups > (size_t)kPatchMaxGroups) { if (err) *err = "patch plan has too many groups"; return false; }
     APVAE_CUDA_OK(cudaMalloc(&op->d_w, plan.wpack.size() * sizeof(uint16_t)), err);
@@ -174,7 +174,11 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             // outputs: 4-D (C, W, H, N) view of the output tensor on the INPUT grid; a sub-pixel phase (py, px) of a stride-2
             // transposed conv writes every second pixel of a 2H x 2W image starting at (py, px)
             const int osc = plan.out_scale;
-            const int py = plan.phase >= 0 ? (plan.phase >> 1) : 0, px = plan.phase >= 0 ? (plan.phase & 1) : 0;
+            // phase 4 + py: both column phases in one op; its 2 * cout outputs per input pixel are output pixels (2x, 2x + 1),
+            // contiguous only when the output rows carry no channel padding
+            const bool merged = plan.phase >= 4;
+            if (merged && epi.ldo * 2 != plan.npad) { if (err) *err = "patch: merged column phases need ldo == cout (op " + op->name + ")"; return false; }
+            const int py = merged ? plan.phase - 4 : plan.phase >= 0 ? (plan.phase >> 1) : 0, px = (plan.phase >= 0 && !merged) ? (plan.phase & 1) : 0;
             auto map_out = [&](CUtensorMap* tm, const void* ptr) {
                 const cuuint64_t ld = (cuuint64_t)epi.ldo * 2;                       // bytes per output pixel
                 const cuuint64_t Wo = (cuuint64_t)osc * W, Ho = (cuuint64_t)osc * H;

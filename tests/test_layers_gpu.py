@@ -316,15 +316,18 @@ PHASE_CASES = [
 ]
 
 
+@pytest.mark.parametrize('merge', ['1', '0'])
 @pytest.mark.parametrize('outs', ['act', 'raw+act'])
 @pytest.mark.parametrize('k,H,W,cin,cout,n_valid,cap', PHASE_CASES)
-def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, outs, monkeypatch):
+def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, outs, merge, monkeypatch):
     """conv2d_transpose(stride 2, SAME) (conv2d_.py:464-471) as four sub-pixel phase ops of the A-stationary kernel:
     phase (py, px) is a stride-1 correlation on the input grid written to output pixels (2y + py, 2x + px) by strided
-    bulk tensor stores."""
+    bulk tensor stores.  merge=1: two ops, one per output row phase, whose N = [px 0 | px 1] x cout is the pair of
+    adjacent output pixels (2x, 2x + 1) written as one contiguous row (when 2 * cout <= 256)."""
     torch = _torch()
     from apvae.plan import Plan, pad16
     monkeypatch.setenv('APVAE_PATCH', '1')
+    monkeypatch.setenv('APVAE_PATCH_MERGE', merge)
     rs = np.random.RandomState(k + H + cin + cout)
     x = bf16_round(rs.normal(size=(cap, H, W, cin)))
     kern = bf16_round(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))

@@ -407,6 +407,46 @@ def test_script_call_surface_reads_like_the_reference():
     m.close()
 
 
+def test_energy_distribution_class_matches_oracle():
+    """EnergyDistribution(pz, G_theta, D_psi, log_Z, xi, mcmc_iterator, mcmc_alpha, initial_z) (dmm_cifar10.py:97-252)
+    as the scripts construct it inside p_net (:606-611): log_prob attributes and sample() histories."""
+    import math
+    from apvae.dmm import Script, EnergyDistribution
+    ocfg, params, cfg, m = _make('A', dict(z_dim=128, pull_back_energy_weight=2.0), max_chunk=4, enable_grad=True,
+                                 pull_back_energy_weight=2.0)
+    xi_raw, log_Z = 0.4, -30.0                       # log_Z below the clip at -20 (:135)
+    m.set_scalars(xi_raw=xi_raw, beta=0.0, log_Z=0.0)
+    s = Script(m)
+    n, steps, alpha = 4, 2, 2e-2
+    rs = np.random.RandomState(9)
+    z0 = rs.normal(size=(n, ocfg.z_dim))
+    xi = 1.0 / (1.0 + math.exp(-xi_raw))
+    pz = EnergyDistribution(s.Normal(mean=0.0, logstd=0.0), G=s.G_theta, D=s.D_psi, log_Z=log_Z, xi=xi,
+                            mcmc_iterator=steps, mcmc_alpha=alpha, initial_z=z0, seed=7)
+    npf = lambda t: t.cpu().numpy().astype(np.float64)
+    lp = pz.log_prob(z0, group_ndims=1)
+    e_o, _, p_o = O.energy_and_grad(ocfg, params, z0, xi_raw=xi_raw)
+    _energy_close(npf(lp.pure_energy), p_o)
+    w_xi = ocfg.pull_back_energy_weight * xi
+    assert np.abs(npf(lp.energy) - e_o).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
+    assert np.abs(npf(lp.log_energy_prob) - (-e_o + 20.0)).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
+    want_pn = -0.5 * (z0 ** 2).sum(-1) - 0.5 * ocfg.z_dim * math.log(2 * math.pi)
+    assert np.abs(npf(lp.tensor) - want_pn).max() < 1e-3
+    t = pz.sample()
+    assert tuple(t.tensor.shape) == (n, ocfg.z_dim)
+    assert tuple(t.history_e_z.shape) == (steps, n) and tuple(t.history_ratio.shape) == (steps, n)
+    # step 0 starts from initial_z: its energies are the oracle's at z0
+    assert np.abs(npf(t.history_e_z)[0] - e_o).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
+    _energy_close(npf(t.history_pure_e_z)[0], p_o)
+    r = npf(t.history_ratio)
+    assert np.all(r >= 0) and np.all(r <= 1)
+    with pytest.raises(ValueError):
+        EnergyDistribution(s.Normal(), G=s.G_theta, D=s.D_psi, xi=0.123)
+    with pytest.raises(TypeError):
+        EnergyDistribution(object(), G=s.G_theta, D=s.D_psi, xi=xi)
+    m.close()
+
+
 @pytest.mark.parametrize('case', ['A128', 'M40'])
 def test_image_energy_gradient_ood_indicator(case):
     """ele_grad = tf.gradients(D_psi(input_x), [input_x]); ele_grad_norm = sum(ele_grad^2)
