@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument('--n-z', type=int, default=1000, help='importance samples per image (K)')
     ap.add_argument('--batch', type=int, default=37,
                     help='images per step per GPU (37 x 1000 samples = 125 x 296: every chunk is a whole number of 148-SM waves)')
-    ap.add_argument('--chunk', type=int, default=2368, help='(image,sample) pairs per decoder/energy launch')
+    ap.add_argument('--chunk', type=int, default=7400, help='(image,sample) pairs per decoder/energy launch')
     ap.add_argument('--cpu-batch', type=int, default=2)
     ap.add_argument('--cpu-n-z', type=int, default=8)
     ap.add_argument('--no-cpu-baseline', action='store_true')
