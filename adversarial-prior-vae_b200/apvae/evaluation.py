@@ -116,11 +116,11 @@ class Evaluator(object):
         for b0 in range(0, n, self.batch_size):
             b1 = min(n, b0 + self.batch_size)
             B = b1 - b0
-            xb = m._f32(x[b0:b1] if isinstance(x, torch.Tensor) else np.asarray(x[b0:b1], dtype=np.float32))
+            xb = m._images(x[b0:b1] if isinstance(x, torch.Tensor) else np.asarray(x[b0:b1], dtype=np.float32))
             xo = None
             if x_origin is not None:
-                xo = m._f32(x_origin[b0:b1] if isinstance(x_origin, torch.Tensor)
-                            else np.asarray(x_origin[b0:b1], dtype=np.float32))
+                xo = m._images(x_origin[b0:b1] if isinstance(x_origin, torch.Tensor)
+                               else np.asarray(x_origin[b0:b1], dtype=np.float32))
             eb = m._f32(eps[:, b0:b1]) if eps is not None else None
             view = pi.reshape(-1)[:_lib.PER_IMAGE_ROWS * B]
             check(lib.apvae_is_nll(m._h, _ptr(xb), _ptr(xo), B, self.n_z, _ptr(eb),

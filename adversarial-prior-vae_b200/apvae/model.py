@@ -168,6 +168,15 @@ class Model(object):
             raise ValueError('expected shape %r, got %r' % (tuple(shape), tuple(t.shape)))
         return t
 
+    def _images(self, x):
+        """float32 device tensor [B, H, W, C]; the trailing dims must be the model's x_shape (the reference's
+        InputSpec raises ValueError at graph-build time for a wrong static shape)."""
+        t = self._f32(x)
+        want = tuple(int(v) for v in self.config.x_shape)
+        if t.dim() != 4 or tuple(t.shape[1:]) != want:
+            raise ValueError('expected images of shape [B, %d, %d, %d], got %r' % (want + (tuple(t.shape),)))
+        return t
+
     def _empty(self, *shape, **kw):
         import torch
         return torch.empty(shape, dtype=kw.get('dtype', torch.float32), device=self.device)
@@ -175,7 +184,7 @@ class Model(object):
     # ------------------------------------------------------------------ nets
     def encode(self, x):
         """q_net(x) -> (z_mean, max(z_logstd, min_logstd_of_q)), each [B, z_dim]."""
-        x = self._f32(x)
+        x = self._images(x)
         B = x.shape[0]
         mu, ls = self._empty(B, self.config.z_dim), self._empty(B, self.config.z_dim)
         check(lib.apvae_encode(self._h, _ptr(x), B, _ptr(mu), _ptr(ls), _stream()), self._h)
@@ -196,7 +205,7 @@ class Model(object):
 
     def energy_of_images(self, x):
         """D_psi(x): x [..., H, W, C] -> [...]."""
-        x = self._f32(x)
+        x = self._images(x)
         lead = tuple(x.shape[:-3])
         x4 = x.reshape((-1,) + tuple(self.config.x_shape))
         out = self._empty(x4.shape[0])
@@ -214,7 +223,7 @@ class Model(object):
 
     def sample_z(self, x_origin, K, eps=None, seed=0):
         """q_net(x, n_z=K)['z'] (dmm_cifar10.py:418-452): returns (z [K,B,d], log q(z|x) [K,B], log N(z) [K,B])."""
-        x = self._f32(x_origin)
+        x = self._images(x_origin)
         B = x.shape[0]
         e = self._f32(eps, (K, B, self.config.z_dim)) if eps is not None else None
         z, lq, lpn = self._empty(K, B, self.config.z_dim), self._empty(K, B), self._empty(K, B)
@@ -226,7 +235,7 @@ class Model(object):
     def is_nll(self, x, K, x_origin=None, eps=None, seed=0, per_sample=False):
         """The test graph of one mini-batch (dmm_cifar10.py:880-927).  Returns a dict of
         per-image [B] tensors (and per-sample [K,B] if asked)."""
-        x = self._f32(x)
+        x = self._images(x)
         B = x.shape[0]
         xo = self._f32(x_origin, x.shape) if x_origin is not None else None
         e = self._f32(eps, (K, B, self.config.z_dim)) if eps is not None else None
@@ -264,7 +273,7 @@ class Model(object):
 
     def image_energy_grad(self, x):
         """(D_psi(x), ele_grad = dD/dx, ele_grad_norm = sum(ele_grad^2)) of evaluation/dmm_cifar.py:958-959."""
-        x = self._f32(x)
+        x = self._images(x)
         x4 = x.reshape((-1,) + tuple(self.config.x_shape))
         n = x4.shape[0]
         d, g, s = self._empty(n), self._empty(*x4.shape), self._empty(n)
