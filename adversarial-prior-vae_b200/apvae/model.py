@@ -333,13 +333,17 @@ class Model(object):
         check(lib.apvae_macs(self._h, C.byref(q), C.byref(g), C.byref(d)))
         return q.value, g.value, d.value
 
-    def op_times(self, n, reps=5):
+    def op_times(self, n, reps=5, grad=False):
         """Per-op CUDA-event timings (bench.py roofline): [(net, name, macs_per_unit, ms_per_launch)]
-        for every tap-GEMM op of q_net (n capped at max_batch), G_theta and D_psi on `n` units."""
+        for every planned op of q_net (n capped at max_batch), G_theta and D_psi on `n` units; grad=True adds the
+        adjoint programs of the sampler (model_grad.cu)."""
         out = []
         name = C.create_string_buffer(256)
         macs, ms, cnt = C.c_double(), C.c_float(), C.c_int()
-        for net, label in ((0, 'q_net'), (1, 'G_theta'), (2, 'D_psi')):
+        nets = [(0, 'q_net'), (1, 'G_theta'), (2, 'D_psi')]
+        if grad and self.config.enable_grad:
+            nets += [(3, 'D_psi^T'), (4, 'G_theta^T')]
+        for net, label in nets:
             check(lib.apvae_op_count(self._h, net, C.byref(cnt)))
             nn = min(n, self.config.max_batch) if net == 0 else min(n, self.config.max_chunk)
             for i in range(cnt.value):

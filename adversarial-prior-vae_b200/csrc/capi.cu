@@ -379,12 +379,13 @@ int apvae_macs(const apvae_handle* h, double* q, double* g, double* d) {
 }
 
 static Program* pick_net(Model& m, int net) {
-    return net == 0 ? &m.q_prog : net == 1 ? &m.g_prog : net == 2 ? &m.d_prog : nullptr;
+    return net == 0 ? &m.q_prog : net == 1 ? &m.g_prog : net == 2 ? &m.d_prog : net == 3 ? &m.gd_prog : net == 4 ? &m.gg_prog :
+           net == 5 ? &m.om_prog : nullptr;
 }
 int apvae_op_count(const apvae_handle* h, int net, int* count) {
     if (!h || !count) return set_global_err("null argument", APVAE_ERR_INVALID);
     Program* p = pick_net(const_cast<Model&>(h->m), net);
-    if (!p) return set_global_err("net must be 0, 1 or 2", APVAE_ERR_INVALID);
+    if (!p) return set_global_err("net must be 0 .. 5", APVAE_ERR_INVALID);
     *count = (int)p->size();
     return APVAE_OK;
 }

@@ -31,7 +31,7 @@ constexpr int kMaxStages = 12;
 
 }  // namespace
 
-template <int KC, bool kTwo>
+template <int KC, bool kTwo, bool kMask>
 __global__ void __launch_bounds__(kThreads, 1)
 patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -49,6 +49,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     auto tempty = [&](int a) { return bar_base + 8u * (4 * kMaxStages + kAccStages + a); };
     const uint32_t tmem_ptr_smem = bar_base + 8u * (4 * kMaxStages + 2 * kAccStages);
     auto resbar = [&](int q, int b) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 2 * q + b); };
+    auto maskbar = [&](int q) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 8 + q); };
 
     const int warp = uniform_warp_idx();
     const int lane = threadIdx.x & 31;
@@ -68,7 +69,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         for (int s = 0; s < p.a_stages; ++s) { mbar_init(fullA(s), 1); mbar_init(emptyA(s), 1); }
         for (int s = 0; s < p.b_stages; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), two ? 1 : csize); }
         for (int a = 0; a < kAccStages; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), two ? 8 : 4); }
-        for (int q = 0; q < 4; ++q) { mbar_init(resbar(q, 0), 1); mbar_init(resbar(q, 1), 1); }
+        for (int q = 0; q < 4; ++q) { mbar_init(resbar(q, 0), 1); mbar_init(resbar(q, 1), 1); mbar_init(maskbar(q), 1); }
         fence_barrier_init();
     }
     if (warp == 2) { if constexpr (two) tmem_alloc_2cta(tmem_ptr_smem, kTmemCols); else tmem_alloc(tmem_ptr_smem, kTmemCols); }
@@ -287,6 +288,19 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             }
             return true;
         };
+        // leaky-relu' mask (adjoint ops): the forward activation box of block s, one block ahead, into the act staging box
+        // (such ops write no act output); returns whether one was issued (warp-uniform)
+        constexpr bool has_mask = kMask;               // its own instantiation: the forward ops' epilogue carries none of this
+        auto issue_mask = [&](const Seq& s) {
+            if (!has_mask || !seq_ok(s)) return false;
+            const int po = s.m * kTileM + q * 32;
+            if (leader) {
+                mbar_expect_tx(maskbar(q), 32u * 128u);
+                if (fold) tma_load_5d(actbuf, &p.tm_mask, maskbar(q), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else tma_load_2d(actbuf, &p.tm_mask, maskbar(q), s.cb, (s.n * H + s.ty * rows_tile + (po >> lgW)) * W + (po & (W - 1)));
+            }
+            return true;
+        };
         // this lane's residual row inside the box, and whether this lane's pixel takes a residual
         int rrow = lane;
         bool lane_res = true;
@@ -304,6 +318,10 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             cur.g = cluster_id; cur.m = 0; cur.cb = 0; cur.n = tile0 / tiles_y; cur.ty = tile0 - cur.n * tiles_y;
         }
         Seq pre = cur;
+        Seq mseq = cur;
+        bool miss = issue_mask(mseq);                      // mask of the first block
+        seq_next(mseq);
+        uint32_t mph = 0;
         bool iss0 = false, iss1 = false;
         if (!dbl) {
             iss0 = issue_res(pre, 0); seq_next(pre);
@@ -332,6 +350,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 if (kb) { mbar_wait(resbar(q, 1), ph1); ph1 ^= 1; }
                 else { mbar_wait(resbar(q, 0), ph0); ph0 ^= 1; }
             }
+            const bool use_mask = has_mask && miss;
+            if (use_mask) { mbar_wait(maskbar(q), mph); mph ^= 1; }
             tmem_ld_wait();
             if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 6);
             if (last_of_tile) {                            // the accumulator is in registers: hand it back to the MMA warp now
@@ -351,6 +371,13 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 f[2] = __uint_as_float(v[ch * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[ch * 8 + 3]) + b0.w;
                 f[4] = __uint_as_float(v[ch * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[ch * 8 + 5]) + b1.y;
                 f[6] = __uint_as_float(v[ch * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[ch * 8 + 7]) + b1.w;
+                if (use_mask) {                            // v *= leaky-relu'(forward activation): 1 where it is positive, else alpha
+                    const uint4 mv = ld_shared_v4(actbuf + st_off + (((uint32_t)ch ^ sw) << 4));
+                    f[0] *= bf16_lo(mv.x) > 0.f ? 1.f : alpha; f[1] *= bf16_hi(mv.x) > 0.f ? 1.f : alpha;
+                    f[2] *= bf16_lo(mv.y) > 0.f ? 1.f : alpha; f[3] *= bf16_hi(mv.y) > 0.f ? 1.f : alpha;
+                    f[4] *= bf16_lo(mv.z) > 0.f ? 1.f : alpha; f[5] *= bf16_hi(mv.z) > 0.f ? 1.f : alpha;
+                    f[6] *= bf16_lo(mv.w) > 0.f ? 1.f : alpha; f[7] *= bf16_hi(mv.w) > 0.f ? 1.f : alpha;
+                }
                 if (has_res) {
                     const uint4 rv = ld_shared_v4(rbuf + (((uint32_t)ch ^ rsw) << 4));
                     if (lane_res) {
@@ -370,6 +397,11 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 const bool is = issue_res(pre, kb);        // refill it with the residual of the block two ahead
                 if (kb) iss1 = is; else iss0 = is;
                 seq_next(pre);
+            }
+            if (has_mask) {
+                __syncwarp();                              // ... and with the mask box: fetch the next block's mask
+                miss = issue_mask(mseq);
+                seq_next(mseq);
             }
             // staging boxes: without a residual the two residual boxes serve as a second (raw, act) pair, so only
             // the stores of the block before the previous one must have left shared memory
@@ -516,10 +548,14 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     void (*kern)(PatchGemmParams) = nullptr;
     const bool two = p.two_cta != 0;
     if (two && c != 2) return (int)cudaErrorInvalidValue;
+    const bool mk = p.fast_epi && p.fast_mask;
     switch (p.kc) {
-        case 16: kern = two ? patchgemm_kernel<16, true> : patchgemm_kernel<16, false>; break;
-        case 32: kern = two ? patchgemm_kernel<32, true> : patchgemm_kernel<32, false>; break;
-        case 64: kern = two ? patchgemm_kernel<64, true> : patchgemm_kernel<64, false>; break;
+        case 16: kern = two ? (mk ? patchgemm_kernel<16, true, true> : patchgemm_kernel<16, true, false>)
+                            : (mk ? patchgemm_kernel<16, false, true> : patchgemm_kernel<16, false, false>); break;
+        case 32: kern = two ? (mk ? patchgemm_kernel<32, true, true> : patchgemm_kernel<32, true, false>)
+                            : (mk ? patchgemm_kernel<32, false, true> : patchgemm_kernel<32, false, false>); break;
+        case 64: kern = two ? (mk ? patchgemm_kernel<64, true, true> : patchgemm_kernel<64, true, false>)
+                            : (mk ? patchgemm_kernel<64, false, true> : patchgemm_kernel<64, false, false>); break;
         default: return (int)cudaErrorInvalidValue;
     }
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -539,8 +575,8 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     // one persistent cluster per co-resident slot (GPC boundaries can leave a few SMs without a full cluster)
     int max_clusters = num_sms / c;
     if (c > 1) {
-        static int cached[6][5] = {{0}};                     // [kc index, pair mode][cluster] -> max active clusters
-        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0);
+        static int cached[12][5] = {{0}};                     // [kc index, pair mode][cluster] -> max active clusters
+        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (mk ? 6 : 0);
         if (cached[ki][c] == 0) {
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki][c] = nc;

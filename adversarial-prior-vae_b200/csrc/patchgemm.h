@@ -70,6 +70,10 @@ struct alignas(64) PatchGemmParams {
     CUtensorMap tm_raw, tm_act;      // 4-D (Npad, W, H, N) over the output (strided by 2 for a sub-pixel phase),
                                      // box (64, min(W, 32), 32 / min(W, 32), 1), SWIZZLE_128B
     CUtensorMap tm_res;              // 2-D (Npad, residual pixels), box (64, res_rows)
+    CUtensorMap tm_mask;             // fast_epi with epi.mask (adjoint ops, raw output only): the forward activation whose sign
+                                     // selects leaky-relu', same view and box as a same-resolution residual; it is loaded
+                                     // one block ahead into the (unused) act staging box
+    int fast_mask;                   // 1: tm_mask is valid and the TMA epilogue multiplies by leaky-relu'(mask)
     int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
     unsigned long long* trace;       // tuning only (APVAE_PATCH_TRACE): per-tile clock64 stamps of CTA 0, 16 slots per tile, 64 tiles
     EpilogueArgs epi;

@@ -157,7 +157,10 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.res_rows = 32;
     {
         const char* fe = getenv("APVAE_FAST_EPI");
-        const bool plain = !epi.mask && !epi.out_f32 && !epi.out_raw_lo && !epi.out_act_lo && !epi.res_lo && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
+        // a leaky-relu' mask (adjoint ops) rides along when the op writes no act output: its box takes the act staging box
+        const char* fm = getenv("APVAE_FAST_MASK");
+        const bool mask_ok = !epi.mask || (plan.phase < 0 && !epi.out_act && epi.out_raw && !(fm && fm[0] == '0'));   // (a phase op's mask would be a strided view)
+        const bool plain = mask_ok && !epi.out_f32 && !epi.out_raw_lo && !epi.out_act_lo && !epi.res_lo && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
                            (epi.out_raw || epi.out_act) && (epi.res_mode == RES_NONE || epi.res != nullptr);
         if (plain && !(fe && fe[0] == '0')) {
             const cuuint64_t pixels = (cuuint64_t)plan.capacity_n * H * W;
@@ -222,6 +225,24 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                 map2d(&p.tm_res, epi.res, pixels, epi.ld_res, 32);
             } else {
                 p.tm_res = p.tm_raw;
+            }
+            p.fast_mask = 0;
+            if (epi.mask) {
+                if (fold) {
+                    const cuuint64_t ld = (cuuint64_t)epi.ld_mask * 2;
+                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
+                    cuuint64_t strides4[4] = {ld, H * W * ld, W * ld, 2 * H * W * ld};
+                    cuuint32_t box5[5] = {64, 8, 2, 2, 1};
+                    const CUresult r = encode(&p.tm_mask, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(epi.mask), dims5, strides4,
+                                              box5, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    if (r != CUDA_SUCCESS) ok = false;
+                } else {
+                    map2d(&p.tm_mask, epi.mask, pixels, epi.ld_mask, 32);
+                }
+                p.fast_mask = ok ? 1 : 0;
+            } else {
+                p.tm_mask = p.tm_raw;
             }
             p.fast_epi = ok ? 1 : 0;
         }

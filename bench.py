@@ -146,6 +146,21 @@ def cpu_reference_throughput(args, steps, warmup):
     params = O.init_weights(cfg, dtype=np.float32)
     B, K = args.cpu_batch, args.cpu_n_z
     x = synthetic_images(B, cfg.x_shape).astype(np.float32)
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        cores = os.cpu_count()
+    # all the host threads the BLAS can use, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1);
+    # `cores` reports the thread count actually in effect
+    limit = None
+    try:
+        from threadpoolctl import threadpool_limits, threadpool_info
+        limit = threadpool_limits(limits=cores, user_api='blas')
+        got = [p.get('num_threads') for p in threadpool_info() if p.get('user_api') == 'blas']
+        if got:
+            cores = int(max(got))
+    except Exception:
+        pass
     times = []
     for i in range(warmup + steps):
         eps = np.random.RandomState(100 + i).normal(size=(K, B, cfg.z_dim)).astype(np.float32)
@@ -153,12 +168,10 @@ def cpu_reference_throughput(args, steps, warmup):
         O.eval_batch(cfg, params, x, x, eps)
         if i >= warmup:
             times.append(time.perf_counter() - t0)
+    if limit is not None:
+        limit.restore_original_limits()
     t = float(np.mean(times))
     samples_per_s = B * K / t
-    try:
-        cores = len(os.sched_getaffinity(0))
-    except Exception:
-        cores = os.cpu_count()
     return {'value': samples_per_s / args.n_z, 'unit': UNIT, 'cores': cores, 'kind': 'port',
             'sample': 'oracle eval_batch (numpy fp32, BLAS threads) on B=%d images x K=%d samples per step, '
                       '%.2f s/step, %.2f (image,sample)/s; images/s scaled linearly to K=%d'

@@ -171,7 +171,8 @@ int apvae_fill_uniform(float* out_dev, int64_t n, uint64_t seed, uint64_t offset
 int apvae_launch_count(const apvae_handle* h, int64_t* launches);
 int apvae_macs(const apvae_handle* h, double* q_per_image, double* g_per_sample, double* d_per_sample);
 
-/* Per-op device timing for bench.py's roofline: net 0 = q_net, 1 = G_theta (+heads), 2 = D_psi.
+/* Per-op device timing for bench.py's roofline: net 0 = q_net, 1 = G_theta (+heads), 2 = D_psi, 3 = adjoint program of
+ * D_psi, 4 = adjoint program of G_theta (both need enable_grad), 5 = G_omega (needs latent_gan).
  * apvae_op_time launches op `index` on the first `n` units of its (already populated) input
  * buffers 2 + `reps` times and returns the CUDA-event average of the last `reps` launches on
  * `stream` (synchronises that stream). */

@@ -405,3 +405,63 @@ def test_stride2_conv_on_patch_kernel(k, H, W, cin, cout, shortcut, n_valid, cap
     o32 = torch.zeros((cap, H // 2, W // 2, cout), dtype=torch.float32, device='cuda')
     plan.run(srcs, n_valid, out_f32=o32, f32_cols=cout)
     _check(o32.cpu().numpy()[:n_valid], want[:n_valid])
+
+
+MASK_CASES = [
+    # H, W, cin, cout, res ('none' | 'same' | 'even'), n_valid, cap
+    (32, 32, 96, 96, 'none', 3, 4),
+    (32, 32, 96, 96, 'same', 2, 2),
+    (16, 16, 192, 192, 'even', 3, 3),
+    (32, 32, 32, 16, 'same', 3, 3),
+    (64, 64, 32, 32, 'none', 1, 2),
+    (8, 8, 192, 192, 'same', 5, 6),        # image pairs
+    (8, 8, 64, 48, 'none', 4, 4),
+]
+
+
+@pytest.mark.parametrize('two_cta', [0, 1])
+@pytest.mark.parametrize('H,W,cin,cout,res,n_valid,cap', MASK_CASES)
+def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_cta, monkeypatch):
+    """Adjoint ops (model_grad.cu): v = (acc + bias) * leaky_relu'(mask) (+ res), raw bf16 output only, through the TMA
+    epilogue of the A-stationary kernel: the mask (the forward activation, dmm_cifar10.py:241-247 via tf.gradients of
+    tf.nn.leaky_relu) is fetched one block ahead into the unused act staging box."""
+    torch = _torch()
+    from apvae import _lib
+    from apvae.plan import Plan, pad16
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))
+    rs = np.random.RandomState(H + cin + cout + len(res))
+    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
+    kern = bf16_round(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap)
+    assert plan.info.patch == 1
+    npad = pad16(cout)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    mask = bf16_round(rs.normal(size=(cap, H, W, npad)))
+    mask[rs.uniform(size=mask.shape) < 0.1] = 0.0                 # lrelu'(0) = alpha
+    want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
+    want = want * np.where(mask[..., :cout] > 0, 1.0, 0.2)
+    kw = {}
+    if res == 'same':
+        r = bf16_round(rs.normal(size=(cap, H, W, npad)))
+        want = want + r[..., :cout]
+        kw = dict(res=t(r), res_mode=_lib.RES_SAME)
+    elif res == 'even':
+        r = bf16_round(rs.normal(size=(cap, H // 2, W // 2, npad)))
+        want[:, ::2, ::2, :] += r[..., :cout]
+        kw = dict(res=t(r), res_mode=_lib.RES_EVEN)
+    out_raw = torch.full((cap, H, W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, mask=t(mask), **kw)
+    torch.cuda.synchronize()
+    raw = out_raw.float().cpu().numpy()
+    scale = max(1.0, float(np.abs(want).max()))
+    assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
+    keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 else 0)
+    assert np.all(raw[keep:] == 7.0)
+    # same op through the generic epilogue (APVAE_FAST_MASK=0): same values up to the bf16 rounding of the output
+    monkeypatch.setenv('APVAE_FAST_MASK', '0')
+    out2 = torch.full((cap, H, W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out2, mask=t(mask), **kw)
+    torch.cuda.synchronize()
+    assert np.abs(out2.float().cpu().numpy()[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale

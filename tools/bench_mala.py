@@ -27,6 +27,7 @@ def main():
     ap.add_argument('--steps', type=int, default=100)
     ap.add_argument('--chunk', type=int, default=512)
     ap.add_argument('--precise', action='store_true')
+    ap.add_argument('--op-times', action='store_true', help='also print per-op timings of the forward and adjoint programs')
     a = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (('RANK', '0'), ('WORLD_SIZE', '1'), ('LOCAL_RANK', '0')))
     torch.cuda.set_device(local)
@@ -62,6 +63,16 @@ def main():
     # algorithmic: one forward + one input-gradient backward of D o G per chain-step (backward ~ forward), SURVEY 8(d)
     flops = 4.0 * (mg + md) * a.chains * a.steps * world
     acc = float((out['history_ratio'] > 0.5).float().mean())
+    if a.op_times and rank == 0:
+        rows = m.op_times(min(a.chunk, a.chains), reps=5, grad=True)
+        tot = sum(r[3] for r in rows if r[0] != 'q_net')
+        for net, name, macs, t_ms, nn in rows:
+            if net == 'q_net':
+                continue
+            tf = 2.0 * macs * nn / (t_ms * 1e-3) / 1e12 if t_ms > 0 else 0.0
+            print('%-9s %-64s %8.4f ms %8.1f TFLOP/s %5.1f%%' % (net, name, t_ms, tf, 100 * t_ms / tot), file=sys.stderr)
+        print('sum of ops per chunk of %d chains: %.3f ms (forward + adjoint programs; a MALA step runs them once per chunk)'
+              % (min(a.chunk, a.chains), tot), file=sys.stderr)
     print(json.dumps({
         'metric': 'MALA chain-steps/sec (%s %s, d=%d, %d chains x %d steps)' % (a.arch, a.dataset, cfg.z_dim, a.chains, a.steps),
         'value': world * a.chains * a.steps / (ms / 1e3), 'unit': 'chain-steps/s', 'n_gpus': world, 'ms_total': ms,
