@@ -145,4 +145,26 @@ struct SmallBlockParams {
 };
 int launch_small_block(const SmallBlockParams& p, int n, void* stream);
 
+
+// Stride-1 conv2d / conv2d_transpose with <= 4 input AND <= 4 output channels on the CUDA cores: the first conv of a
+// block on the raw image channels (3 -> 3, 1 -> 1) and its adjoint in the sampler's backward pass.  As implicit GEMMs
+// these pad K and N from 3 to 16 and sit on the tensor pipe's per-instruction floor (1..4 TFLOP/s measured); here a
+// 32 x 8 pixel tile with its halo goes through shared memory and the weights are constant-bank operands.
+// Epilogue = the GEMM kernels': v = acc + bias; v *= lrelu'(mask); v += res (same / even pixels); raw, act, fp32 outputs.
+constexpr int kTinyMaxC = 4, kTinyMaxK = 5;
+struct TinyConvParams {
+    const void* in;                       // bf16 [N, H, W, cp_in]
+    int H, W, cp_in, cin, cout, k;
+    int ntaps;
+    int8_t dy[kTinyMaxK * kTinyMaxK], dx[kTinyMaxK * kTinyMaxK];          // source shift of each tap
+    float w[kTinyMaxK * kTinyMaxK * kTinyMaxC * kTinyMaxC];              // [tap][ci][co] (cin x cout used, packed to kTinyMaxC)
+    float bias[kTinyMaxC];
+    void* out_raw;  void* out_act;  int ldo;                             // bf16 [N, H, W, ldo], channels >= cout zero
+    float* out_f32;  int ld_f32;                                          // fp32 [N*H*W, ld_f32], cout columns
+    const void* res;  int res_mode, ld_res;                              // bf16, RES_SAME: [N,H,W,ld_res]; RES_EVEN: [N,H/2,W/2,ld_res]
+    const void* mask;  int ld_mask;                                      // bf16 [N, H, W, ld_mask]
+    float alpha;
+};
+int launch_tiny_conv(const TinyConvParams& p, int n, void* stream);
+
 }  // namespace apvae

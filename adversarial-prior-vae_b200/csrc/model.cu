@@ -54,6 +54,45 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     std::string perr;
     std::unique_ptr<DevOp> op(new DevOp());
     op->name = name;
+    // <= 4 -> <= 4 channels, stride 1 (the first conv on the image channels and its adjoint): CUDA cores (tinyconv.cu);
+    // APVAE_TINY=0 keeps the tensor-core op (tuning / A-B only)
+    {
+        const char* et = getenv("APVAE_TINY");
+        const bool lo_parts = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;
+        if (!(et && et[0] == '0') && terms.size() == 1 && terms[0].stride == 1 && terms[0].cin <= kTinyMaxC && terms[0].cout <= kTinyMaxC &&
+            terms[0].k <= kTinyMaxK && (terms[0].k & 1) && !lo_parts && epi.tanh_cols == 0 && epi.bf16_zero_from >= terms[0].cout &&
+            terms[0].in_cp % 8 == 0 && (epi.ldo % 8 == 0 || !(epi.out_raw || epi.out_act)) &&
+            (!epi.out_f32 || epi.f32_cols == terms[0].cout) && (epi.res_mode == RES_NONE || epi.res)) {
+            const TermSpec& t = terms[0];
+            op->is_tiny = true;
+            op->capacity_n = cap;
+            TinyConvParams& tc = op->tiny;
+            memset(&tc, 0, sizeof(tc));
+            tc.in = srcs[0]; tc.H = t.in_h; tc.W = t.in_w; tc.cp_in = t.in_cp; tc.cin = t.cin; tc.cout = t.cout; tc.k = t.k;
+            const int lo = (t.k - 1) / 2;                          // SAME padding, stride 1, odd k
+            for (int di = 0; di < t.k; ++di)
+                for (int dj = 0; dj < t.k; ++dj) {
+                    const int tp = tc.ntaps++;
+                    tc.dy[tp] = (int8_t)(t.transpose ? lo - di : di - lo);
+                    tc.dx[tp] = (int8_t)(t.transpose ? lo - dj : dj - lo);
+                    const size_t tap_off = (size_t)di * t.k + dj;
+                    for (int ci = 0; ci < t.cin; ++ci)
+                        for (int co = 0; co < t.cout; ++co)
+                            tc.w[(tp * kTinyMaxC + ci) * kTinyMaxC + co] =
+                                t.transpose ? t.kernel[(tap_off * t.cout + co) * t.cin + ci] : t.kernel[(tap_off * t.cin + ci) * t.cout + co];
+                }
+            if (t.bias) for (int co = 0; co < t.cout; ++co) tc.bias[co] = t.bias[co];
+            tc.out_raw = epi.out_raw; tc.out_act = epi.out_act; tc.ldo = epi.ldo;
+            tc.out_f32 = epi.out_f32; tc.ld_f32 = epi.ld_f32;
+            tc.res = epi.res; tc.res_mode = epi.res ? epi.res_mode : RES_NONE; tc.ld_res = epi.ld_res;
+            tc.mask = epi.mask; tc.ld_mask = epi.ld_mask;
+            tc.alpha = 0.2f;
+            op->macs_per_image = (double)t.k * t.k * t.cin * t.cout * t.in_h * t.in_w;
+            if (macs) *macs += op->macs_per_image;
+            prog.push_back(std::move(op));
+            return true;
+        }
+    }
     // stride-1 convs on wide grids: the A-stationary kernel; everything else: the tap-GEMM kernel
     const char* env = getenv("APVAE_PATCH");
     PatchPlan pplan;

@@ -333,6 +333,7 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
 
 int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
     if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
+    if (op.is_tiny) return launch_tiny_conv(op.tiny, n_valid, stream);
     if (op.is_small_block) return launch_small_block(op.sblock, n_valid, stream);
     if (op.is_heads) return launch_pixel_heads(op.heads, (long long)n_valid * op.heads.pixels_per_image, stream);
     if (op.is_patch) {

@@ -50,6 +50,8 @@ struct DevOp {
     PatchGemmParams pparams;
     bool is_heads = false;          // true: G_theta's 1x1 output heads on the CUDA cores (kernels.h: HeadsParams)
     HeadsParams heads;
+    bool is_tiny = false;           // true: a <= 4 -> <= 4 channel stride-1 conv on the CUDA cores (kernels.h: TinyConvParams)
+    TinyConvParams tiny;
     bool is_small_block = false;    // true: a whole <= 3-channel-input resnet block on the CUDA cores (kernels.h: SmallBlockParams)
     SmallBlockParams sblock;
     double macs_per_image = 0;
