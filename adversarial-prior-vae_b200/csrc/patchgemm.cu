@@ -297,6 +297,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             if (leader) {
                 mbar_expect_tx(maskbar(q), 32u * 128u);
                 if (fold) tma_load_5d(actbuf, &p.tm_mask, maskbar(q), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else if (p.fast_mask == 2) tma_load_4d(actbuf, &p.tm_mask, maskbar(q), s.cb, po & (W - 1), s.ty * rows_tile + (po >> lgW), s.n);
                 else tma_load_2d(actbuf, &p.tm_mask, maskbar(q), s.cb, (s.n * H + s.ty * rows_tile + (po >> lgW)) * W + (po & (W - 1)));
             }
             return true;

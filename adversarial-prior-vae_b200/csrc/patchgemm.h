@@ -73,7 +73,8 @@ struct alignas(64) PatchGemmParams {
     CUtensorMap tm_mask;             // fast_epi with epi.mask (adjoint ops, raw output only): the forward activation whose sign
                                      // selects leaky-relu', same view and box as a same-resolution residual; it is loaded
                                      // one block ahead into the (unused) act staging box
-    int fast_mask;                   // 1: tm_mask is valid and the TMA epilogue multiplies by leaky-relu'(mask)
+    int fast_mask;                   // 1: tm_mask is valid and the TMA epilogue multiplies by leaky-relu'(mask); 2: tm_mask is the
+                                     // 4-D strided view of a sub-pixel phase, loaded at the store's coordinates
     int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
     unsigned long long* trace;       // tuning only (APVAE_PATCH_TRACE): per-tile clock64 stamps of CTA 0, 16 slots per tile, 64 tiles
     EpilogueArgs epi;

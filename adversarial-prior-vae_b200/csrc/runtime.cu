@@ -159,7 +159,8 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
         const char* fe = getenv("APVAE_FAST_EPI");
         // a leaky-relu' mask (adjoint ops) rides along when the op writes no act output: its box takes the act staging box
         const char* fm = getenv("APVAE_FAST_MASK");
-        const bool mask_ok = !epi.mask || (plan.phase < 0 && !epi.out_act && epi.out_raw && !(fm && fm[0] == '0'));   // (a phase op's mask would be a strided view)
+        // (a merged-column-phase op needs unpadded mask rows, like its output rows)
+        const bool mask_ok = !epi.mask || ((plan.phase < 4 || epi.ld_mask * 2 == plan.npad) && !epi.out_act && epi.out_raw && !(fm && fm[0] == '0'));
         const bool plain = mask_ok && !epi.out_f32 && !epi.out_raw_lo && !epi.out_act_lo && !epi.res_lo && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
                            (epi.out_raw || epi.out_act) && (epi.res_mode == RES_NONE || epi.res != nullptr);
         if (plain && !(fe && fe[0] == '0')) {
@@ -182,8 +183,8 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             const bool merged = plan.phase >= 4;
             if (merged && epi.ldo * 2 != plan.npad) { if (err) *err = "patch: merged column phases need ldo == cout (op " + op->name + ")"; return false; }
             const int py = merged ? plan.phase - 4 : plan.phase >= 0 ? (plan.phase >> 1) : 0, px = (plan.phase >= 0 && !merged) ? (plan.phase & 1) : 0;
-            auto map_out = [&](CUtensorMap* tm, const void* ptr) {
-                const cuuint64_t ld = (cuuint64_t)epi.ldo * 2;                       // bytes per output pixel
+            auto map_out = [&](CUtensorMap* tm, const void* ptr, int ld_elems) {
+                const cuuint64_t ld = (cuuint64_t)ld_elems * 2;                      // bytes per output pixel
                 const cuuint64_t Wo = (cuuint64_t)osc * W, Ho = (cuuint64_t)osc * H;
                 char* base = static_cast<char*>(const_cast<void*>(ptr)) + ((size_t)py * Wo + px) * ld;
                 if (fold) {                 // (C, 8 pixels, 2 images, H, pairs): a block's 32 rows are [2 rows][2 images][8 pixels]
@@ -207,8 +208,8 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                 if (r != CUDA_SUCCESS) ok = false;
             };
             const void* any_out = epi.out_raw ? epi.out_raw : epi.out_act;
-            map_out(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out);
-            map_out(&p.tm_act, epi.out_act ? epi.out_act : any_out);
+            map_out(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out, epi.ldo);
+            map_out(&p.tm_act, epi.out_act ? epi.out_act : any_out, epi.ldo);
             if (epi.res_mode == RES_EVEN) {
                 p.res_rows = (plan.w >= 32) ? 16 : 8;
                 map2d(&p.tm_res, epi.res, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
@@ -227,7 +228,10 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                 p.tm_res = p.tm_raw;
             }
             p.fast_mask = 0;
-            if (epi.mask) {
+            if (epi.mask && plan.phase >= 0) {            // the mask of a sub-pixel phase: the same strided view as its output
+                map_out(&p.tm_mask, epi.mask, epi.ld_mask);
+                p.fast_mask = ok ? (fold ? 1 : 2) : 0;     // 2: 4-D load at the store's coordinates
+            } else if (epi.mask) {
                 if (fold) {
                     const cuuint64_t ld = (cuuint64_t)epi.ld_mask * 2;
                     cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};

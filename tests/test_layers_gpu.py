@@ -465,3 +465,38 @@ def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out2, mask=t(mask), **kw)
     torch.cuda.synchronize()
     assert np.abs(out2.float().cpu().numpy()[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
+
+
+PHASE_MASK_CASES = [
+    # k, H, W (input), cin, cout, n_valid, cap
+    (3, 16, 16, 128, 64, 3, 4),        # merged column phases (2 * cout <= 256, unpadded rows)
+    (5, 32, 32, 32, 3, 2, 2),          # arch B D_psi/level_0/conv_1^T: 3 output channels, four phases
+    (3, 8, 8, 192, 192, 3, 4),         # image pairs, four phases
+    (3, 32, 32, 64, 48, 2, 3),
+]
+
+
+@pytest.mark.parametrize('k,H,W,cin,cout,n_valid,cap', PHASE_MASK_CASES)
+def test_stride2_deconv_phases_with_mask(k, H, W, cin, cout, n_valid, cap, monkeypatch):
+    """The adjoint of a stride-2 conv (model_grad.cu: conv_1^T of a D_psi block) = conv2d_transpose(stride 2) whose
+    epilogue multiplies by leaky_relu'(forward activation): sub-pixel phase ops whose mask is the same strided view as
+    their output, fetched by 4-D bulk tensor loads."""
+    torch = _torch()
+    from apvae.plan import Plan, pad16
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    rs = np.random.RandomState(k + H + cin + cout)
+    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
+    kern = bf16_round(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=None)], cap)
+    npad = pad16(cout)
+    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    mask = bf16_round(rs.normal(size=(cap, 2 * H, 2 * W, npad)))
+    out_raw = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, mask=t(mask))
+    torch.cuda.synchronize()
+    want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), np.zeros(cout), 2) * np.where(mask[..., :cout] > 0, 1.0, 0.2)
+    scale = max(1.0, float(np.abs(want).max()))
+    raw = out_raw.float().cpu().numpy()
+    assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
+    keep = n_valid + (n_valid & 1 if W == 8 else 0)
+    assert np.all(raw[keep:] == 7.0)

@@ -1,6 +1,6 @@
 """BASELINE configs[3]: CelebA-shape (64x64x3, arch B = dmm_for_sampling.py) latent MALA sampling of the energy prior,
 100 steps x 1024 chains, then x = G_theta(z) -> uint8.  Prints one JSON line (chain-steps/s, algorithmic TFLOP/s).
-  python tools/bench_mala.py [--precise] [--chains 1024] [--steps 100] [--dataset celebA] [--arch B] [--chunk 512]
+  python tools/bench_mala.py [--precise] [--chains 1024] [--steps 100] [--dataset celebA] [--arch B] [--chunk 1024] [--op-times]
 Random-init weights, z0 ~ N(0, I) (stand-in for the G_omega latent GAN), in-kernel Philox noise.
 Under torchrun every rank runs `--chains` independent chains on its own GPU (the chains shard with no collective on the
 data path); rank 0 prints the aggregate over the slowest rank's device time."""
@@ -25,7 +25,7 @@ def main():
     ap.add_argument('--z-dim', type=int, default=128)
     ap.add_argument('--chains', type=int, default=1024)
     ap.add_argument('--steps', type=int, default=100)
-    ap.add_argument('--chunk', type=int, default=512)
+    ap.add_argument('--chunk', type=int, default=1024)
     ap.add_argument('--precise', action='store_true')
     ap.add_argument('--op-times', action='store_true', help='also print per-op timings of the forward and adjoint programs')
     a = ap.parse_args()
