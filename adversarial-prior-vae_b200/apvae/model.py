@@ -307,7 +307,8 @@ class Model(object):
     def latent_gan(self, n, z_omega=None, seed=0):
         """gan_z = p_omega_net(n_z=n)['f_z'].distribution.mean (dmm_cifar10.py:623-635,967-969): G_omega applied to
         z_omega ~ N(0, I_128) (fed [n,128] or drawn in-kernel) -> [n, z_dim], the `initial_z` of plot_samples' MALA loop."""
-        zo = self._f32(z_omega, (n, 128)) if z_omega is not None else None
+        din = self.config.z_dim if self.config.arch == 'M' else 128        # dmm_bernouli_fashion.py:636-639: z ~ N(0, I_z_dim)
+        zo = self._f32(z_omega, (n, din)) if z_omega is not None else None
         out = self._empty(n, self.config.z_dim)
         check(lib.apvae_latent_gan(self._h, _ptr(zo), int(n), int(seed), _ptr(out), _stream()), self._h)
         return out

@@ -332,9 +332,10 @@ int apvae_latent_gan(apvae_handle* h, const float* z_omega_dev, int n_total, uin
     if (n_total <= 0 || !z0_dev) { m.err = "latent_gan: bad arguments"; return APVAE_ERR_INVALID; }
     for (int s0 = 0; s0 < n_total; s0 += m.cfg.max_chunk) {
         const int n = std::min(m.cfg.max_chunk, n_total - s0);
-        const float* zo = z_omega_dev ? z_omega_dev + (size_t)s0 * 128 : nullptr;
-        if (!zo) {                                       // z ~ N(0, I_128) (dmm_cifar10.py:626-629)
-            LCHECK(launch_fill_normal(m.om_noise, (long long)n * 128, seed, (uint64_t)s0 * 128, 0, stream), "fill_normal");
+        const int din = m.omega_in_dim();
+        const float* zo = z_omega_dev ? z_omega_dev + (size_t)s0 * din : nullptr;
+        if (!zo) {                                       // z ~ N(0, I_128) (dmm_cifar10.py:626-629); arch M: N(0, I_z_dim)
+            LCHECK(launch_fill_normal(m.om_noise, (long long)n * din, seed, (uint64_t)s0 * din, 0, stream), "fill_normal");
             zo = m.om_noise;
         }
         if (!m.latent_gan_chunk(zo, n, z0_dev + (size_t)s0 * m.cfg.z_dim, stream)) return APVAE_ERR_CUDA;

@@ -477,6 +477,12 @@ __global__ void clip_min_kernel(float* v, long long n, float lo) {
         v[i] = fmaxf(v[i], lo);
 }
 
+__global__ void leaky_relu_f32_kernel(float* v, long long n, float alpha) {
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x)
+        v[i] = fmaxf(v[i], alpha * v[i]);
+}
+
 __global__ void gather_cols_kernel(const float* __restrict__ src, int ld, int col0, int cols, long long rows,
                                    float* __restrict__ dst) {
     const long long total = rows * cols;
@@ -657,6 +663,11 @@ int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, do
 int launch_clip_min(float* v, long long n, float lo, void* stream) {
     if (n <= 0) return 0;
     clip_min_kernel<<<grid_for(n, 256), 256, 0, st(stream)>>>(v, n, lo);
+    return (int)cudaGetLastError();
+}
+int launch_leaky_relu_f32(float* v, long long n, float alpha, void* stream) {
+    if (n <= 0) return 0;
+    leaky_relu_f32_kernel<<<grid_for(n, 256), 256, 0, st(stream)>>>(v, n, alpha);
     return (int)cudaGetLastError();
 }
 int launch_gather_cols(const float* src, int ld, int col0, int cols, long long rows, float* dst, void* stream) {

@@ -99,6 +99,8 @@ int launch_quantize_images(const float* head, int ld, long long pixels, int C, u
 
 // v = max(v, lo)
 int launch_clip_min(float* v, long long n, float lo, void* stream);
+// v = max(v, alpha * v)
+int launch_leaky_relu_f32(float* v, long long n, float alpha, void* stream);
 
 // copy the first `cols` columns of fp32 [rows, ld] into dense [rows, cols]; optional tanh not applied.
 int launch_gather_cols(const float* src, int ld, int col0, int cols, long long rows, float* dst, void* stream);

@@ -97,6 +97,7 @@ public:
     int W() const { return cfg.x_w; }
     int C() const { return cfg.x_c; }
     int HW() const { return cfg.x_h * cfg.x_w; }
+    int omega_in_dim() const { return cfg.arch == APVAE_ARCH_M ? cfg.z_dim : 128; }   // z_omega: dmm_cifar10.py:626-629 / dmm_bernouli_fashion.py:636-639
     int head_ld() const { return (cfg.bernoulli || cfg.arch == APVAE_ARCH_M) ? cfg.x_c : 2 * cfg.x_c; }
     int g_base_h() const { return cfg.arch == APVAE_ARCH_B ? 8 : cfg.x_h / 4; }
     int g_base_w() const { return cfg.arch == APVAE_ARCH_B ? 8 : cfg.x_w / 4; }

@@ -224,6 +224,46 @@ bool Model::build_g() {
 // z_channel at [2 oh, 2 ow]; flattened, that is gan_z = the initial_z of the MALA chains (:623-635,1061-1066).
 bool Model::build_omega() {
     const int cap = cfg.max_chunk;
+    if (cfg.arch == APVAE_ARCH_M) {
+        // dmm_bernouli_fashion.py:526-543: h = z; six times h = leaky_relu(h W_eff + b) with the weight-normalised kernel
+        // W_eff = scale * kernel / sqrt(max(sum_in kernel^2, 1e-12)) (weight_norm_.py:76-97, tf.nn.l2_normalize over the
+        // input axis), folded here once at load time.  The last layer's activation runs on the fp32 output.
+        const int din = cfg.z_dim;
+        om_in = alloc_act(cap, 1, 1, din);
+        om_out = alloc_f32((size_t)cap * cfg.z_dim);
+        om_noise = alloc_f32((size_t)cap * din);
+        if (!om_in.ptr || !om_out || !om_noise) return false;
+        Tensor h = om_in;
+        for (int i = 0; i < 6; ++i) {
+            const std::string pre = std::string("G_omega/dense") + (i ? "_" + std::to_string(i) : "");
+            const int fin = i == 0 ? din : 40, fout = i == 5 ? cfg.z_dim : 40;
+            const HostArr *k = W_(pre + "/kernel", {fin, fout}), *sc = W_(pre + "/weight_norm/scale", {fin, fout}),
+                          *b = W_(pre + "/bias", {fout});
+            if (!k || !sc || !b) return false;
+            HostArr& we = weights[pre + "#wn/kernel"];
+            we.shape = {fin, fout};
+            we.v.resize((size_t)fin * fout);
+            for (int o = 0; o < fout; ++o) {
+                double ss = 0;
+                for (int a = 0; a < fin; ++a) ss += (double)k->v[(size_t)a * fout + o] * k->v[(size_t)a * fout + o];
+                const double inv = 1.0 / sqrt(ss > 1e-12 ? ss : 1e-12);
+                for (int a = 0; a < fin; ++a) we.v[(size_t)a * fout + o] = (float)(k->v[(size_t)a * fout + o] * inv * sc->v[(size_t)a * fout + o]);
+            }
+            weights[pre + "#wn/bias"] = *b;
+            Epilogue e;
+            Tensor o;
+            if (i < 5) {
+                o = alloc_act(cap, 1, 1, fout);
+                if (!o.ptr) return false;
+                e.out_act = o.ptr; e.ldo = o.cp;
+            } else {
+                e.out_f32 = om_out; e.ld_f32 = cfg.z_dim; e.f32_cols = cfg.z_dim;
+            }
+            if (!dense_op(om_prog, pre + "#wn", h, fin, fout, e, cap, &macs_omega)) return false;
+            h = o;
+        }
+        return true;
+    }
     const int oh = omega_base_h(cfg), ow = omega_base_w(cfg);
     const int feat = 256 * oh * ow;
     om_in = alloc_act(cap, 1, 1, 128);
@@ -258,9 +298,12 @@ bool Model::build_omega() {
 
 bool Model::latent_gan_chunk(const float* z_omega_dev, int n, float* z0_dev, void* stream) {
     if (om_prog.empty()) return fail("latent_gan: create the handle with latent_gan = 1");
-    KCHECK(launch_sample_z(nullptr, nullptr, z_omega_dev, n, 0, 1, 128, 0.f, 0, nullptr, om_in.ptr, nullptr, om_in.cp, 128,
+    const int din = omega_in_dim();
+    KCHECK(launch_sample_z(nullptr, nullptr, z_omega_dev, n, 0, 1, din, 0.f, 0, nullptr, om_in.ptr, nullptr, om_in.cp, din,
                            om_in.cp, 0.2f, nullptr, nullptr, stream), "pack z_omega");
     if (!run_program(om_prog, n, stream)) return false;
+    if (cfg.arch == APVAE_ARCH_M)      // the last dense layer's leaky_relu (dmm_bernouli_fashion.py:530-541)
+        KCHECK(launch_leaky_relu_f32(om_out, (long long)n * cfg.z_dim, 0.2f, stream), "leaky_relu");
     const cudaError_t ce = cudaMemcpyAsync(z0_dev, om_out, (size_t)n * cfg.z_dim * sizeof(float), cudaMemcpyDeviceToDevice,
                                            static_cast<cudaStream_t>(stream));
     if (ce != cudaSuccess) return fail(std::string("latent_gan copy: ") + cudaGetErrorString(ce));

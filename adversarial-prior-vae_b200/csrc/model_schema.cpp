@@ -66,9 +66,9 @@ bool validate_config(const apvae_config& c, std::string* err) {
     }
     if (c.max_batch <= 0 || c.max_chunk <= 0) return fail("max_batch / max_chunk must be positive");
     if (c.latent_gan) {
-        if (c.arch == APVAE_ARCH_M) return fail("latent_gan: arch M's weight-normalised dense G_omega is not built");
         const int cells = 4 * omega_base_h(c) * omega_base_w(c);
-        if (c.z_dim % cells || c.z_dim / cells < 1) return fail("latent_gan: z_dim must be a multiple of the G_omega output grid");
+        if (c.arch != APVAE_ARCH_M && (c.z_dim % cells || c.z_dim / cells < 1))
+            return fail("latent_gan: z_dim must be a multiple of the G_omega output grid");
     }
     if (c.nf_layers < 0 || c.nf_layers > 256) return fail("nf_layers must be in [0, 256]");
     if (c.nf_layers > 0 && c.z_dim > 512) return fail("posterior flow: z_dim <= 512");
@@ -150,7 +150,17 @@ std::vector<WeightInfo> weight_schema(const apvae_config& c) {
     out.push_back({"D_psi/level_-1/kernel", {64, 1}});
     out.push_back({"D_psi/level_-1/bias", {1}});
     // G_omega (dmm_cifar10.py:503-532, dmm_for_sampling.py:519-546): dense 128 -> 256*oh*ow, six deconv blocks, 1x1 conv
-    if (c.latent_gan) {
+    // arch M (dmm_bernouli_fashion.py:526-543): six weight-normalised dense layers z_dim -> 40 x5 -> z_dim; variables per
+    // layer (tf default scope names dense, dense_1, ...): kernel, weight_norm/scale (kernel-shaped, weight_norm_.py:84-92), bias
+    if (c.latent_gan && c.arch == APVAE_ARCH_M) {
+        for (int i = 0; i < 6; ++i) {
+            const std::string pre = std::string("G_omega/dense") + (i ? "_" + std::to_string(i) : "") + "/";
+            const int64_t fin = i == 0 ? c.z_dim : 40, fout = i == 5 ? c.z_dim : 40;
+            out.push_back({pre + "kernel", {fin, fout}});
+            out.push_back({pre + "weight_norm/scale", {fin, fout}});
+            out.push_back({pre + "bias", {fout}});
+        }
+    } else if (c.latent_gan) {
         const int oh = omega_base_h(c), ow = omega_base_w(c);
         out.push_back({"G_omega/level_0/kernel", {128, (int64_t)256 * oh * ow}});
         out.push_back({"G_omega/level_0/bias", {(int64_t)256 * oh * ow}});

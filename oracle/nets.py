@@ -16,7 +16,7 @@ from .layers import (conv2d, deconv2d, dense, resnet_conv2d_block,
 from .dists import maybe_clip_value
 
 __all__ = ['OracleConfig', 'weight_shapes', 'init_weights', 'q_net',
-           'G_theta', 'D_psi', 'G_omega', 'G_theta_input_grad', 'D_psi_input_grad']
+           'G_theta', 'D_psi', 'G_omega', 'weight_norm', 'G_theta_input_grad', 'D_psi_input_grad']
 
 
 class OracleConfig(object):
@@ -205,9 +205,14 @@ def weight_shapes(cfg):
     shapes['D_psi/level_-2/bias'] = (64,)
     shapes['D_psi/level_-1/kernel'] = (64, 1)                # :561
     shapes['D_psi/level_-1/bias'] = (1,)
-    if cfg.latent_gan:
-        if cfg.arch == 'M':
-            raise ValueError("arch M's weight-normalised dense G_omega is not restated")
+    if cfg.latent_gan and cfg.arch == 'M':       # dmm_bernouli_fashion.py:526-543: six weight-normalised dense layers
+        for i in range(6):
+            pre = 'G_omega/dense%s/' % ('_%d' % i if i else '')
+            fin, fout = (cfg.z_dim if i == 0 else 40), (cfg.z_dim if i == 5 else 40)
+            shapes[pre + 'kernel'] = (fin, fout)
+            shapes[pre + 'weight_norm/scale'] = (fin, fout)      # kernel-shaped, weight_norm_.py:84-92
+            shapes[pre + 'bias'] = (fout,)
+    elif cfg.latent_gan:
         oh, ow = _omega_base_hw(cfg)
         shapes['G_omega/level_0/kernel'] = (128, 256 * oh * ow)
         shapes['G_omega/level_0/bias'] = (256 * oh * ow,)
@@ -242,6 +247,8 @@ def init_weights(cfg, seed=1234, dtype=np.float64, bias_std=0.1, head_gain=1.0):
                 fan_in, fan_out = shp
             std = np.sqrt(2.0 / (fan_in + fan_out))
             w = rng.normal(0.0, std, size=shp)
+        elif name.endswith('/weight_norm/scale'):
+            w = 1.0 + rng.normal(0.0, 0.25, size=shp)      # the reference initialises ones (weight_norm_.py:64-65)
         elif name.startswith('posterior_flow/'):
             # the reference draws w, u ~ N(0, 0.01^2) (planar_nf.py:37-41), which leaves the flow at the
             # identity to 1e-4; the synthetic test weights are larger so that the layers do something
@@ -285,9 +292,28 @@ def _g_trunk(cfg, params, z, tape=None):
     return h
 
 
+def weight_norm(kernel, scale=None, epsilon=1e-12):
+    """tfsnippet.layers.weight_norm(kernel, axis=-1) (layers/normalization/weight_norm_.py:76-97): tf.nn.l2_normalize over
+    every axis but the last (x / sqrt(max(sum x^2, epsilon))), times the kernel-shaped `scale`.  The reference's own test
+    states it in numpy: scale * kernel / sqrt(sum(kernel ** 2, axis=all but last, keepdims=True))
+    (tests/layers/normalization/test_weight_norm.py:23-53)."""
+    kernel = np.asarray(kernel)
+    red = tuple(range(kernel.ndim - 1))
+    w = kernel / np.sqrt(np.maximum(np.sum(kernel ** 2, axis=red, keepdims=True), epsilon))
+    return w if scale is None else w * np.asarray(scale)
+
+
 def G_omega(cfg, params, z_omega):
     """gan_z = flatten(G_omega(z_omega, z_channel)) (dmm_cifar10.py:503-532,630-632; dmm_for_sampling.py:519-546,
-    646-648): z_omega [..., 128] -> [..., z_dim].  The 1x1 output conv has no activation."""
+    646-648): z_omega [..., 128] -> [..., z_dim].  The 1x1 output conv has no activation.
+    Arch M (dmm_bernouli_fashion.py:526-543,636-640): z_omega [..., z_dim]; six dense layers with weight_norm=True and
+    leaky_relu on every one of them, the last included."""
+    if cfg.arch == 'M':
+        h = np.asarray(z_omega)
+        for i in range(6):
+            pre = 'G_omega/dense%s/' % ('_%d' % i if i else '')
+            h = leaky_relu(dense(h, weight_norm(params[pre + 'kernel'], params[pre + 'weight_norm/scale']), params[pre + 'bias']))
+        return h
     oh, ow = _omega_base_hw(cfg)
     h = dense(z_omega, params['G_omega/level_0/kernel'], params['G_omega/level_0/bias'])
     h = h.reshape(h.shape[:-1] + (oh, ow, 256))

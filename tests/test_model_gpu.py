@@ -510,9 +510,10 @@ def test_flow_posterior_matches_oracle(case):
     m.close()
 
 
-@pytest.mark.parametrize('case', ['A128', 'Bceleba'])
+@pytest.mark.parametrize('case', ['A128', 'Bceleba', 'M40'])
 def test_latent_gan_initial_z_matches_oracle(case):
-    """gan_z = G_omega(z_omega) (dmm_cifar10.py:503-532,623-635): the initial_z of plot_samples' MALA loop."""
+    """gan_z = G_omega(z_omega) (dmm_cifar10.py:503-532,623-635): the initial_z of plot_samples' MALA loop.
+    M40: the six weight-normalised dense layers of dmm_bernouli_fashion.py:526-543 on z_omega ~ N(0, I_z_dim)."""
     arch, kw, _, _ = CASES[case]
     from apvae.model import ExpConfig, Model
     ocfg = O.OracleConfig(arch, latent_gan=True, **kw)
@@ -520,7 +521,7 @@ def test_latent_gan_initial_z_matches_oracle(case):
     cfg = ExpConfig(arch, dataset=kw.get('dataset'), z_dim=ocfg.z_dim, max_batch=8, max_chunk=8, latent_gan=True, enable_grad=True)
     m = Model(cfg, params)
     n = 11                                                           # ragged against max_chunk = 8
-    zo = np.random.RandomState(5).normal(size=(n, 128))
+    zo = np.random.RandomState(5).normal(size=(n, ocfg.z_dim if arch == 'M' else 128))
     want = O.G_omega(ocfg, params, zo)
     got = m.latent_gan(n, z_omega=zo).cpu().numpy().astype(np.float64)
     assert got.shape == (n, ocfg.z_dim)

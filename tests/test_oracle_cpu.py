@@ -268,5 +268,41 @@ def test_latent_gan_schema_and_shapes():
     ocfg = O.OracleConfig('B', dataset='cifar10', z_dim=64, latent_gan=True)
     z0 = O.G_omega(ocfg, O.init_weights(ocfg), np.random.RandomState(0).normal(size=(2, 3, 128)))
     assert z0.shape == (2, 3, 64) and np.isfinite(z0).all()
-    with pytest.raises(Exception):
-        weight_schema(ExpConfig('M', latent_gan=True))
+    # arch M: six weight-normalised dense layers (kernel, kernel-shaped scale, bias)
+    ocfg = O.OracleConfig('M', latent_gan=True)
+    ours = dict(weight_schema(ExpConfig('M', z_dim=ocfg.z_dim, latent_gan=True)))
+    assert ours == {k: tuple(v) for k, v in O.weight_shapes(ocfg).items()}
+    assert ours['G_omega/dense/weight_norm/scale'] == (40, 40) and ours['G_omega/dense_5/kernel'] == (40, ocfg.z_dim)
+
+
+def test_weight_norm_matches_the_reference_tests_numpy_statement():
+    """tests/layers/normalization/test_weight_norm.py:23-53 (payload arange(120) as a (2,3,4,5) kernel, axis=-1): the
+    expected values there are plain numpy; arch M's G_omega (dmm_bernouli_fashion.py:526-543) uses exactly this on its
+    dense kernels."""
+    kernel = np.reshape(np.arange(120, dtype=np.float64), (2, 3, 4, 5))
+    scale = np.random.RandomState(0).normal(size=kernel.shape)
+    want = kernel / np.sqrt(np.sum(kernel ** 2, axis=(0, 1, 2), keepdims=True))
+    np.testing.assert_allclose(O.weight_norm(kernel), want, rtol=1e-12)
+    np.testing.assert_allclose(O.weight_norm(kernel, scale), scale * want, rtol=1e-12)
+    # dense kernels [in, out]: reduce over the input axis; an all-zero column hits the epsilon floor instead of dividing by 0
+    k2 = kernel.reshape(24, 5).copy()
+    k2[:, 2] = 0.0
+    w = O.weight_norm(k2, scale.reshape(24, 5))
+    assert np.all(w[:, 2] == 0.0) and np.all(np.isfinite(w))
+    np.testing.assert_allclose(np.sum(O.weight_norm(k2)[:, [0, 1, 3, 4]] ** 2, axis=0), 1.0, rtol=1e-12)
+
+
+def test_arch_m_latent_gan_oracle_shapes():
+    cfg = O.OracleConfig('M', latent_gan=True)
+    params = O.init_weights(cfg)
+    z = np.random.RandomState(1).normal(size=(5, cfg.z_dim))
+    out = O.G_omega(cfg, params, z)
+    assert out.shape == (5, cfg.z_dim) and np.all(np.isfinite(out))
+    # every layer ends in leaky_relu (the last included): negative outputs are 0.2 x the pre-activation
+    pre = 'G_omega/dense_5/'
+    h = z
+    for i in range(5):
+        p = 'G_omega/dense%s/' % ('_%d' % i if i else '')
+        h = O.leaky_relu(h @ O.weight_norm(params[p + 'kernel'], params[p + 'weight_norm/scale']) + params[p + 'bias'])
+    last = h @ O.weight_norm(params[pre + 'kernel'], params[pre + 'weight_norm/scale']) + params[pre + 'bias']
+    np.testing.assert_allclose(out, np.where(last > 0, last, 0.2 * last), rtol=1e-12)
