@@ -64,7 +64,8 @@ class PlanInfo(C.Structure):
         ('patch_rows_tile', C.c_int), ('patch_groups', C.c_int), ('patch_items', C.c_int),
         ('patch_a_stages', C.c_int), ('patch_b_stages', C.c_int), ('patch_prow', C.c_int * 2),
         ('patch_s2d', C.c_int), ('patch_nmaps', C.c_int), ('patch_map_src', C.c_int * 4), ('patch_map_ph', C.c_int * 4),
-        ('patch_map_prow', C.c_int * 4), ('patch_fold', C.c_int),
+        ('patch_map_prow', C.c_int * 4), ('patch_phase', C.c_int), ('patch_out_scale', C.c_int), ('patch_npad', C.c_int),
+        ('patch_fold', C.c_int),
     ]
 
 
@@ -119,6 +120,8 @@ _SYMBOLS = [
     ('apvae_plan_copy_bias', C.c_int, [_P, C.POINTER(C.c_float)]),
     ('apvae_plan_copy_patch_groups', C.c_int, [_P, C.POINTER(C.c_int32)]),
     ('apvae_plan_copy_patch_weights', C.c_int, [_P, C.POINTER(C.c_uint16)]),
+    ('apvae_plan_copy_patch_bias', C.c_int, [_P, C.POINTER(C.c_float)]),
+    ('apvae_plan_select_patch', C.c_int, [_P, C.c_int]),
     ('apvae_plan_destroy', C.c_int, [_P]),
     ('apvae_plan_run', C.c_int, [_P, C.c_int, C.POINTER(_P), C.c_int, C.POINTER(Epilogue)]),
     ('apvae_plan_bench', C.c_int, [_P, C.c_int, C.POINTER(_P), C.c_int, C.POINTER(Epilogue), C.c_int,

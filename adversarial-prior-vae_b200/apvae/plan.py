@@ -72,10 +72,23 @@ class Plan(object):
         check(lib.apvae_plan_copy_patch_groups(self._h, out.ctypes.data_as(C.POINTER(C.c_int32))))
         return out
 
+    def select_patch(self, which):
+        """-1: the op's own patch plan; 0..3: sub-pixel phase plans of a stride-2 transposed conv; 4..5: its row-phase
+        plans with both column phases merged into N.  Refreshes `info`."""
+        check(lib.apvae_plan_select_patch(self._h, int(which)))
+        check(lib.apvae_plan_get_info(self._h, C.byref(self.info)))
+        return self
+
+    @property
+    def patch_bias(self):
+        out = np.zeros((self.info.patch_npad,), dtype=np.float32)
+        check(lib.apvae_plan_copy_patch_bias(self._h, out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
     @property
     def patch_weights(self):
         i = self.info
-        out = np.zeros((i.patch_items, i.npad, i.kc), dtype=np.uint16)
+        out = np.zeros((i.patch_items, i.patch_npad or i.npad, i.kc), dtype=np.uint16)
         check(lib.apvae_plan_copy_patch_weights(self._h, out.ctypes.data_as(C.POINTER(C.c_uint16))))
         return out
 

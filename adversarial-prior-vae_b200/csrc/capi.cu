@@ -19,6 +19,7 @@ struct apvae_plan {
     bool has_patch = false;
     PatchPlan patch;
     std::vector<PatchPlan> phases;   // stride-2 transposed conv: four sub-pixel phase plans (A-stationary kernel)
+    int sel = -1;                     // which patch plan the info / copy calls describe (apvae_plan_select_patch)
     std::vector<PatchPlan> row_phases;   // ... or two plans, one per output row phase, both column phases merged into N
 };
 
@@ -459,6 +460,20 @@ int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, 
     return APVAE_OK;
 }
 
+static const PatchPlan* selected_patch(const apvae_plan* p) {
+    if (p->sel < 0) return p->has_patch ? &p->patch : nullptr;
+    if (p->sel < 4) return (size_t)p->sel < p->phases.size() ? &p->phases[p->sel] : nullptr;
+    return (size_t)(p->sel - 4) < p->row_phases.size() ? &p->row_phases[p->sel - 4] : nullptr;
+}
+
+int apvae_plan_select_patch(apvae_plan* p, int which) {
+    if (!p || which < -1 || which > 5) return set_global_err("select_patch: which must be -1 (the op), 0..3 (sub-pixel phase) or 4..5 (row phase)", APVAE_ERR_INVALID);
+    const int old = p->sel;
+    p->sel = which;
+    if (!selected_patch(p)) { p->sel = old; return set_global_err("select_patch: this op has no such patch plan", APVAE_ERR_INVALID); }
+    return APVAE_OK;
+}
+
 int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
     if (!p || !info) return set_global_err("null argument", APVAE_ERR_INVALID);
     const OpPlan& P = p->plan;
@@ -475,8 +490,9 @@ int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
         for (int i = 0; i < 4; ++i) info->src_strides[s][i] = P.src[s].strides[i];
     }
     info->macs_per_image = P.macs_per_image;
-    if (p->has_patch) {
-        const PatchPlan& Q = p->patch;
+    if (const PatchPlan* qp = selected_patch(p)) {
+        const PatchPlan& Q = *qp;
+        info->patch_phase = Q.phase; info->patch_out_scale = Q.out_scale; info->patch_npad = Q.npad;
         info->patch = 1; info->patch_macc = Q.macc; info->patch_cluster = Q.cluster; info->patch_rows_tile = Q.rows_tile;
         info->patch_groups = (int)Q.groups.size(); info->patch_items = Q.num_items;
         info->patch_a_stages = Q.a_stages; info->patch_b_stages = Q.b_stages;
@@ -507,17 +523,25 @@ int apvae_plan_copy_bias(const apvae_plan* p, float* out) {
     return APVAE_OK;
 }
 int apvae_plan_copy_patch_groups(const apvae_plan* p, int32_t* out) {
-    if (!p || !out || !p->has_patch) return set_global_err("no patch plan", APVAE_ERR_INVALID);
-    for (size_t i = 0; i < p->patch.groups.size(); ++i) {
-        const PatchGroup& g = p->patch.groups[i];
+    const PatchPlan* q = p ? selected_patch(p) : nullptr;
+    if (!q || !out) return set_global_err("no patch plan", APVAE_ERR_INVALID);
+    for (size_t i = 0; i < q->groups.size(); ++i) {
+        const PatchGroup& g = q->groups[i];
         out[6 * i + 0] = g.src; out[6 * i + 1] = g.dx; out[6 * i + 2] = g.py0; out[6 * i + 3] = g.k;
         out[6 * i + 4] = g.c0; out[6 * i + 5] = g.prow;
     }
     return APVAE_OK;
 }
 int apvae_plan_copy_patch_weights(const apvae_plan* p, uint16_t* out) {
-    if (!p || !out || !p->has_patch) return set_global_err("no patch plan", APVAE_ERR_INVALID);
-    memcpy(out, p->patch.wpack.data(), p->patch.wpack.size() * sizeof(uint16_t));
+    const PatchPlan* q = p ? selected_patch(p) : nullptr;
+    if (!q || !out) return set_global_err("no patch plan", APVAE_ERR_INVALID);
+    memcpy(out, q->wpack.data(), q->wpack.size() * sizeof(uint16_t));
+    return APVAE_OK;
+}
+int apvae_plan_copy_patch_bias(const apvae_plan* p, float* out) {
+    const PatchPlan* q = p ? selected_patch(p) : nullptr;
+    if (!q || !out) return set_global_err("no patch plan", APVAE_ERR_INVALID);
+    memcpy(out, q->bias.data(), q->bias.size() * sizeof(float));
     return APVAE_OK;
 }
 int apvae_plan_destroy(apvae_plan* p) { delete p; return APVAE_OK; }

@@ -199,6 +199,7 @@ typedef struct apvae_plan_info {
     int patch_prow[2];
     /* activation maps of the patch plan: (source, row phase); patch_s2d = 1: stride-2 conv through the space-to-depth view */
     int patch_s2d, patch_nmaps, patch_map_src[4], patch_map_ph[4], patch_map_prow[4];
+    int patch_phase, patch_out_scale, patch_npad;   /* of the selected patch plan (apvae_plan_select_patch): sub-pixel phase 0..3, row phase 4..5, -1 none */
     int patch_fold;   /* 2: 8-pixel-wide images are processed in pairs, side by side in one 16-wide tile row (even capacity) */
 } apvae_plan_info;
 
@@ -220,6 +221,11 @@ int apvae_plan_copy_weights(const apvae_plan* p, uint16_t* out /* bf16 [total_st
 int apvae_plan_copy_bias(const apvae_plan* p, float* out /* [npad] */);
 int apvae_plan_copy_patch_groups(const apvae_plan* p, int32_t* out /* [groups][6]: src,dx,py0,k,c0,prow */);
 int apvae_plan_copy_patch_weights(const apvae_plan* p, uint16_t* out /* bf16 [items][npad][kc] */);
+int apvae_plan_copy_patch_bias(const apvae_plan* p, float* out /* [patch_npad] */);
+/* A stride-2 transposed conv is run as four sub-pixel phase plans (which = 0..3: phase (py, px) = (which >> 1, which & 1))
+ * or two row-phase plans with both column phases merged into N (which = 4 + py); -1 = the op's own patch plan.  Selects
+ * the plan the patch_* fields of apvae_plan_get_info and the apvae_plan_copy_patch_* calls describe (host-side tests). */
+int apvae_plan_select_patch(apvae_plan* p, int which);
 int apvae_plan_destroy(apvae_plan* p);
 /* Runs the plan on `device` (synchronous): src_dev[i] are bf16 NHWC tensors [capacity_n,H,W,Cp]. */
 int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,

@@ -94,16 +94,21 @@ def emulate_patch_plan(plan, srcs, n_valid):
     assert i.patch
     groups = plan.patch_groups
     wts = bf16_bits_to_f32(plan.patch_weights).astype(np.float64)
-    bias = plan.bias
+    npad = i.patch_npad or i.npad
+    bias = plan.patch_bias if i.patch_npad else plan.bias
     H, W, kc, macc, rt = i.hg, i.wg, i.kc, i.patch_macc, i.patch_rows_tile
     fold = max(1, i.patch_fold)
     Wt = W * fold
-    out = np.zeros((n_valid, H, W, i.npad), dtype=np.float64)
+    # a sub-pixel phase plan (Plan.select_patch) writes output pixels (2y + py, 2x + px) of a 2H x 2W image; a row-phase
+    # plan (phase 4 + py) carries both column phases side by side in N
+    ph = i.patch_phase
+    cout = i.cout
+    out = np.zeros((n_valid, H, W, npad) if ph < 0 else (n_valid, 2 * H, 2 * W, cout), dtype=np.float64)
     tiles_y = -(-H // rt)
     for n0 in range(0, n_valid, fold):
         for ty in range(tiles_y):
             y0 = ty * rt
-            acc = np.zeros((macc * 128, i.npad), dtype=np.float64)
+            acc = np.zeros((macc * 128, npad), dtype=np.float64)
             item = 0
             for mp, dx, py0, k, c0, prow in groups:
                 x = np.asarray(srcs[i.patch_map_src[mp]], dtype=np.float64)
@@ -135,5 +140,11 @@ def emulate_patch_plan(plan, srcs, n_valid):
                 y, xt = y0 + pix // Wt, pix % Wt
                 f, xx = xt // W, xt % W
                 if y < H and n0 + f < n_valid:
-                    out[n0 + f, y, xx] = acc[pix]
+                    if ph < 0:
+                        out[n0 + f, y, xx] = acc[pix]
+                    elif ph < 4:
+                        out[n0 + f, 2 * y + (ph >> 1), 2 * xx + (ph & 1)] = acc[pix, :cout]
+                    else:
+                        out[n0 + f, 2 * y + ph - 4, 2 * xx] = acc[pix, :cout]
+                        out[n0 + f, 2 * y + ph - 4, 2 * xx + 1] = acc[pix, cout:2 * cout]
     return out

@@ -169,6 +169,49 @@ def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut, mo
     np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
 
 
+PHASE_PLAN_CASES = [
+    # k, H, W (input), cin, cout
+    (3, 16, 16, 32, 48),       # 2 * cout <= 256, cout % 16 == 0: row-phase plans exist
+    (5, 16, 16, 16, 16),
+    (3, 8, 8, 32, 32),         # 8-wide input: image pairs
+    (3, 16, 16, 16, 3),        # cout % 16 != 0: four sub-pixel phases only
+    (3, 16, 32, 16, 192),      # 2 * cout > 256: four sub-pixel phases only
+]
+
+
+@pytest.mark.parametrize('k,H,W,cin,cout', PHASE_PLAN_CASES)
+def test_stride2_deconv_phase_plans_match_oracle(k, H, W, cin, cout, monkeypatch):
+    """conv2d_transpose(stride 2, SAME) (conv2d_.py:464-471) assembled from its sub-pixel phase plans: four plans (py, px),
+    or two row-phase plans whose N is [px 0 | px 1] x cout — each emulated exactly as the kernel walks it."""
+    from helpers import emulate_patch_plan
+    monkeypatch.setenv('APVAE_PATCH', '1')
+    rs = np.random.RandomState(k * 100 + cin + cout)
+    n = 2
+    x = bf16_round(rs.normal(size=(n, H, W, cin)))
+    kern = bf16_round(rs.normal(size=(k, k, cout, cin)) * 0.2)
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
+    want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
+    src = [pad_channels(x, pad16(cin))]
+    got = np.zeros_like(want)
+    for ph in range(4):
+        plan.select_patch(ph)
+        assert plan.info.patch_phase == ph and plan.info.patch_out_scale == 2
+        got += emulate_patch_plan(plan, src, n)
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+    merged_ok = cout % 16 == 0 and 2 * cout <= 256
+    if merged_ok:
+        got = np.zeros_like(want)
+        for py in range(2):
+            plan.select_patch(4 + py)
+            assert plan.info.patch_npad == 2 * cout
+            got += emulate_patch_plan(plan, src, n)
+        np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+    else:
+        with pytest.raises(Exception):
+            plan.select_patch(4)
+
+
 def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     from helpers import emulate_patch_plan
     monkeypatch.setenv('APVAE_PATCH', '1')
