@@ -47,6 +47,8 @@ def parse_args():
     ap.add_argument('--chunk', type=int, default=7400, help='(image,sample) pairs per decoder/energy launch')
     ap.add_argument('--cpu-batch', type=int, default=2)
     ap.add_argument('--cpu-n-z', type=int, default=8)
+    ap.add_argument('--cpu-steps', type=int, default=2, help='timed runs of the CPU baseline sample (after --cpu-warmup untimed ones)')
+    ap.add_argument('--cpu-warmup', type=int, default=1)
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-op-times', action='store_true')
     return ap.parse_args()
@@ -186,7 +188,7 @@ def run_reference(args):
     steps, warmup = min(args.steps, 3), min(args.warmup, 1)
     r = cpu_reference_throughput(args, steps, warmup)
     line = {
-        'impl': 'reference', 'metric': METRIC, 'value': r['value'], 'unit': UNIT, 'n_gpus': args.gpus,
+        'impl': 'reference', 'metric': metric_name(args), 'value': r['value'], 'unit': UNIT, 'n_gpus': args.gpus,
         'steps': steps, 'warmup': warmup, 'ms_per_step': r['ms_per_step'], 'higher_is_better': True,
         'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
         'config': workload_config(args, None),
@@ -197,10 +199,22 @@ def run_reference(args):
     print(json.dumps(line))
 
 
+def metric_name(args):
+    """BASELINE.json's metric for the default workload; other shapes / K (the parity configs run as benches) say so."""
+    ds = args.dataset or {'A': 'cifar10', 'B': 'cifar10', 'M': 'fashion'}[args.arch]
+    if args.n_z == 1000 and ds == 'cifar10':
+        return METRIC
+    shape = {'cifar10': 'CIFAR', 'celebA': 'CelebA', 'fashion': 'MNIST'}.get(ds, ds)
+    return 'importance-sampled NLL images/sec (K=%d, %s-shape)' % (args.n_z, shape)
+
+
 def workload_config(args, world):
     ds = args.dataset or {'A': 'cifar10', 'B': 'cifar10', 'M': 'fashion'}[args.arch]
-    return {'workload': 'BASELINE configs[1]: arch %s (%s-shape) ResNet VAE + energy prior, z_dim=%d, K=%d '
-                        'importance-sampled NLL' % (args.arch, ds, args.z_dim, args.n_z),
+    which = 'configs[1]' if (args.arch == 'A' and args.n_z == 1000) else \
+        'configs[0]' if (args.arch == 'M' and args.n_z == 100 and args.batch == 64) else \
+        'configs[4] (z_dim sweep)' if (args.arch == 'B' and ds == 'cifar10') else 'custom'
+    return {'workload': 'BASELINE %s: arch %s (%s-shape) ResNet VAE + energy prior, z_dim=%d, K=%d '
+                        'importance-sampled NLL' % (which, args.arch, ds, args.z_dim, args.n_z),
             'arch': args.arch, 'z_dim': args.z_dim, 'n_z': args.n_z, 'images_per_step_per_gpu': args.batch,
             'chunk': args.chunk, 'parallelism': ('dp%d (image shards, one allreduce of metric sums)' % world) if world else 'cpu',
             'l2': 'per-step activation working set (>1 GB) exceeds the 126 MB L2; a 256 MB buffer is also '
@@ -360,11 +374,11 @@ def main():
     step_tflops = flops_per_step * S / (ms / 1e3) / 1e12
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_reference_throughput(args, steps=2, warmup=1)
+        cpu = cpu_reference_throughput(args, steps=max(1, args.cpu_steps), warmup=max(0, args.cpu_warmup))
         cpu.pop('ms_per_step')
 
     line = {
-        'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': S, 'warmup': W,
+        'metric': metric_name(args), 'value': value, 'unit': UNIT, 'n_gpus': world, 'steps': S, 'warmup': W,
         'ms_per_step': ms / S, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'bf16', 'data': 'synthetic', 'config': workload_config(args, world),
         'clocks': clocks,
