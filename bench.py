@@ -349,8 +349,19 @@ def main():
         op_table = []
         for net, name, macs, t_ms, nn in rows:
             tf = 2.0 * macs * nn / (t_ms * 1e-3) / 1e12 if t_ms > 0 else 0.0
-            op_table.append({'op': name, 'units': nn, 'ms': round(t_ms, 4), 'tflops': round(tf, 1),
-                             'share': round(t_ms / tot, 4) if net != 'q_net' else None})
+            row = {'op': name, 'units': nn, 'ms': round(t_ms, 4), 'tflops': round(tf, 1),
+                   'share': round(t_ms / tot, 4) if net != 'q_net' else None}
+            # the HBM-bound CUDA-core ops: algorithmic bytes per unit -> achieved GB/s against the copy peak
+            H, Wd, Cx = cfg.x_shape
+            by = None
+            if '[heads' in name and args.arch == 'A':
+                by = H * Wd * (96 * 2 + 2 * Cx * 4 + 2 * 16 * 2)           # trunk row in, fp32 heads + D_psi's raw / act rows out
+            elif '[fused block' in name:
+                by = H * Wd * (16 * 2) * 4                                # x in, r, raw and act out: 16-channel bf16 rows
+            if by and t_ms > 0:
+                row['hbm_gbs'] = round(by * nn / (t_ms * 1e-3) / 1e9, 1)
+                row['hbm_frac'] = round(row['hbm_gbs'] / peaks['hbm_gbs'], 4)
+            op_table.append(row)
         dom = max((r for r in rows if r[0] != 'q_net'), key=lambda r: r[3])
         ach = 2.0 * dom[2] * dom[4] / (dom[3] * 1e-3) / 1e12
         all_flops = sum(2.0 * r[2] * r[4] for r in rows if r[0] != 'q_net')
