@@ -45,6 +45,19 @@ __global__ void __launch_bounds__(kTile) pixel_heads_kernel(const __grid_constan
         const int total = np * chunks;
         {
             const uint4* src = reinterpret_cast<const uint4*>(p.in) + p0 * chunks;
+            constexpr int U = USED > 0 ? USED : 1;
+            if (USED > 0 && np == kTile && chunks == U) {
+                // full tile, compile-time row length: all of this thread's 16-byte loads are issued before the first
+                // shared-memory store (U independent loads in flight per thread)
+                uint4 v[U];
+#pragma unroll
+                for (int i = 0; i < U; ++i) v[i] = __ldg(src + t + i * kTile);
+#pragma unroll
+                for (int i = 0; i < U; ++i) {
+                    const int c = t + i * kTile, px = c / U, ch = c - px * U;
+                    *reinterpret_cast<uint4*>(sm + px * pitch + ch * 16) = v[i];
+                }
+            } else
             for (int c = t; c < total; c += kTile) {
                 const int px = c / chunks, ch = c - px * chunks;
                 if (ch < used) *reinterpret_cast<uint4*>(sm + px * pitch + ch * 16) = __ldg(src + c);
