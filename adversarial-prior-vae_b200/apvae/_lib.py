@@ -12,13 +12,16 @@ LIB_PATH = os.path.join(os.path.dirname(_HERE), 'libapvae_b200.so')
 
 OK, ERR_INVALID, ERR_CUDA, ERR_NO_DEVICE, ERR_WEIGHTS, ERR_UNSUPPORTED, ERR_STATE = range(7)
 ARCH_A, ARCH_B, ARCH_M = 0, 1, 2
-PER_IMAGE_ROWS = 9
+PER_IMAGE_ROWS = 10
 (ROW_LL, ROW_LB, ROW_ADV_LL, ROW_ADV_LB, ROW_RECON, ROW_DG, ROW_LZ_MAX, ROW_LZ_SUM,
- ROW_REAL_E) = range(9)
-PER_SAMPLE_ROWS = 4
-SROW_LOG_PX, SROW_LOG_Q, SROW_LOG_PN, SROW_DG = range(4)
+ ROW_REAL_E, ROW_MSE) = range(10)
+PER_SAMPLE_ROWS = 5
+SROW_LOG_PX, SROW_LOG_Q, SROW_LOG_PN, SROW_DG, SROW_SQ_ERR = range(5)
 RES_NONE, RES_SAME, RES_EVEN = 0, 1, 2
-ACCUM_WEIGHT, ACCUM_BATCHES, ACCUM_SLOTS = 9, 10, 16
+ACCUM_WEIGHT, ACCUM_BATCHES, ACCUM_MSE = 9, 10, 11
+ACCUM_PN_ENERGY, ACCUM_PD_ENERGY, ACCUM_KL_ADV, ACCUM_LOG_Z_OP, ACCUM_PRIOR_WEIGHT = 12, 13, 14, 15, 16
+ACCUM_SLOTS = 20
+PRIOR_PN_ENERGY, PRIOR_PD_ENERGY, PRIOR_KL_ADV, PRIOR_LOG_Z_OP = range(4)
 
 
 class ApvaeError(RuntimeError):
@@ -36,7 +39,7 @@ class Config(C.Structure):
         ('uniform_scale', C.c_int), ('use_truncated', C.c_int), ('bernoulli', C.c_int),
         ('max_batch', C.c_int), ('max_chunk', C.c_int), ('enable_grad', C.c_int),
         ('smallest_step', C.c_float), ('len_train', C.c_int), ('precise', C.c_int),
-        ('nf_layers', C.c_int), ('latent_gan', C.c_int),
+        ('nf_layers', C.c_int), ('latent_gan', C.c_int), ('operand_bf16', C.c_int),
     ]
 
 
@@ -99,13 +102,17 @@ _SYMBOLS = [
     ('apvae_energy', C.c_int, [_P, _P, _P, C.c_int, _P, _P]),
     ('apvae_is_nll', C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     ('apvae_sample_z', C.c_int, [_P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P, _P]),
-    ('apvae_accumulate_metrics', C.c_int, [_P, _P, C.c_int, C.c_int, _P, _P]),
-    ('apvae_prior_stats', C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, _P]),
-    ('apvae_mala', C.c_int, [_P, _P, C.c_int, C.c_int, C.c_float, _P, _P, C.c_uint64, _P, _P, _P, _P]),
+    ('apvae_accumulate_metrics', C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    ('apvae_prior_stats', C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, _P, _P]),
+    ('apvae_mala', C.c_int, [_P, _P, C.c_int, C.c_int, C.c_float, _P, _P, C.c_uint64, _P, _P, _P, _P, _P]),
     ('apvae_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
     ('apvae_image_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
     ('apvae_sample_images', C.c_int, [_P, _P, C.c_int, _P, _P]),
     ('apvae_latent_gan', C.c_int, [_P, _P, C.c_int, C.c_uint64, _P, _P]),
+    ('apvae_discretized_logistic_log_prob', C.c_int, [_P, _P, _P, C.c_int64, C.c_int64, C.c_float, C.c_int, C.c_float,
+                                                      C.c_int, C.c_float, C.c_int, C.c_float, _P, _P]),
+    ('apvae_bernoulli_log_prob', C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P]),
+    ('apvae_is_reduce', C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, _P, _P]),
     ('apvae_fill_normal', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, C.c_int, _P]),
     ('apvae_fill_uniform', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, _P]),
     ('apvae_launch_count', C.c_int, [_P, C.POINTER(C.c_int64)]),
@@ -113,7 +120,7 @@ _SYMBOLS = [
     ('apvae_op_count', C.c_int, [_P, C.c_int, C.POINTER(C.c_int)]),
     ('apvae_op_time', C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int,
                                 C.POINTER(C.c_double), C.POINTER(C.c_float), _P]),
-    ('apvae_plan_create', C.c_int, [C.POINTER(ConvTerm), C.c_int, C.c_int, C.POINTER(_P)]),
+    ('apvae_plan_create', C.c_int, [C.POINTER(ConvTerm), C.c_int, C.c_int, C.c_int, C.POINTER(_P)]),
     ('apvae_plan_get_info', C.c_int, [_P, C.POINTER(PlanInfo)]),
     ('apvae_plan_copy_steps', C.c_int, [_P, C.POINTER(C.c_int32)]),
     ('apvae_plan_copy_weights', C.c_int, [_P, C.POINTER(C.c_uint16)]),

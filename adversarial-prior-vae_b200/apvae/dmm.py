@@ -144,24 +144,46 @@ class QNet(object):
 
 
 class PNet(object):
-    """BayesianNet returned by p_net (dmm_cifar10.py:596-620)."""
+    """BayesianNet returned by p_net (dmm_cifar10.py:596-620).  With z observed it wraps the given latents; otherwise
+    z is a sample of the energy prior: N(0, I) draws (n_z of them; pz.sample, :188-192) or `initial_z`, moved by
+    `mcmc_iterator` MALA steps (:197-226).  `p_net(n_z=config.test_n_pz, mcmc_iterator=0)` is the test graph's
+    test_pn_net (:883): its 'z'.log_prob() carries .energy / .log_energy_prob / .pure_energy at the prior draws."""
 
-    def __init__(self, script, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed):
+    def __init__(self, script, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed, log_Z=None):
         self._script, self._z = script, z
         m = script.model
+        self._log_Z = m.log_Z if log_Z is None else float(log_Z)
+        self.history = None
         if z is None:
             if initial_z is None:
-                raise ValueError('p_net without observed z needs initial_z (the reference feeds G_omega samples)')
+                if n_z is None:
+                    raise ValueError('p_net needs observed z, an initial_z, or n_z prior samples')
+                initial_z = m.fill_normal((int(n_z), 1, m.config.z_dim), seed=seed, offset=1 << 48)
             steps = int(mcmc_iterator)
-            out = m.mala(initial_z, steps, alpha=mcmc_alpha, seed=seed) if steps > 0 else {'z': m._f32(initial_z)}
+            out = m.mala(initial_z, steps, alpha=mcmc_alpha, seed=seed, history_z=True) if steps > 0 else {'z': m._f32(initial_z)}
             self._z = out['z']
             self.history = out
         self._xm = None
+        self._lp = None
+
+    def _z_log_prob(self):
+        if self._lp is None:
+            m = self._script.model
+            z = m._f32(self._z)
+            d = m.config.z_dim
+            d_g = m.energy_of_latents(z)
+            log_pn = -0.5 * (z * z).sum(-1) - 0.5 * d * math.log(2 * math.pi)
+            self._lp = _LogProb(log_pn, d_g, self._script.w_xi(), self._log_Z, d)
+        return self._lp
 
     def __getitem__(self, name):
         m = self._script.model
         if name == 'z':
-            return _StochasticTensor(tensor=self._z)
+            t = _StochasticTensor(tensor=self._z, log_prob=self._z_log_prob)
+            if self.history is not None:
+                for k in ('history_z', 'history_e_z', 'history_pure_e_z', 'history_ratio'):
+                    setattr(t, k, self.history.get(k))
+            return t
         if name == 'x':
             if self._xm is None:
                 self._xm = m.decode(self._z)
@@ -202,7 +224,7 @@ class EnergyDistribution(object):
 
     log_prob(given) returns the Gaussian log p_N(z) carrying .energy / .log_energy_prob / .pure_energy (:164-177);
     sample(n_samples) runs `mcmc_iterator` MALA steps from `initial_z` (or a N(0, I) draw) and returns a stochastic
-    tensor carrying .history_e_z / .history_pure_e_z / .history_ratio (:179-239)."""
+    tensor carrying .history_z / .history_e_z / .history_pure_e_z / .history_ratio (:179-239)."""
 
     def __init__(self, pz, G, D, log_Z=0., xi=1.0, mcmc_iterator=0, mcmc_alpha=None, mcmc_algorithm='mala',
                  mcmc_space='z', initial_z=None, seed=0):
@@ -251,10 +273,11 @@ class EnergyDistribution(object):
                 raise ValueError('sample() needs n_samples or an initial_z')
             z0 = m.fill_normal((int(n_samples), m.config.z_dim), seed=self._seed)
         if self._mcmc_iterator > 0:
-            out = m.mala(z0, self._mcmc_iterator, alpha=self._mcmc_alpha, seed=self._seed)
+            out = m.mala(z0, self._mcmc_iterator, alpha=self._mcmc_alpha, seed=self._seed, history_z=True)
         else:
             out = {'z': m._f32(z0)}
         t = _StochasticTensor(tensor=out['z'], distribution=self)
+        t.history_z = out.get('history_z')                       # state BEFORE each step (:200,235)
         t.history_e_z = out.get('history_e_z')
         t.history_pure_e_z = out.get('history_pure_e_z')
         t.history_ratio = out.get('history_ratio')
@@ -294,7 +317,7 @@ class Script(object):
     def p_net(self, observed=None, n_z=None, beta=1.0, mcmc_iterator=0, log_Z=0.0, initial_z=None, mcmc_alpha=None,
               seed=0):
         z = None if not observed else observed.get('z')
-        return PNet(self, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed)
+        return PNet(self, z, n_z, mcmc_iterator, mcmc_alpha, initial_z, seed, log_Z=log_Z)
 
     def p_omega_net(self, observed=None, n_z=None, beta=1.0, mcmc_iterator=0, log_Z=0.0, initial_z=None, z_omega=None,
                     seed=0):

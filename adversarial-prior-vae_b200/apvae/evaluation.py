@@ -17,7 +17,7 @@ from . import _lib
 from ._lib import lib, check
 from .model import _ptr, _stream
 
-# metric name -> (accumulator slot, sign)   names as in dmm_cifar10.py:1131-1136
+# metric name -> (accumulator slot, sign)   the eleven names of dmm_cifar10.py:1131-1136
 METRIC_SLOTS = {
     'test_nll': (_lib.ROW_LL, -1.0),
     'test_lb': (_lib.ROW_LB, 1.0),
@@ -26,8 +26,15 @@ METRIC_SLOTS = {
     'test_recon': (_lib.ROW_RECON, 1.0),
     'reconstruct_energy': (_lib.ROW_DG, 1.0),
     'real_energy': (_lib.ROW_REAL_E, 1.0),
+    'test_mse': (_lib.ACCUM_MSE, 1.0),
 }
-_SUM_SLOTS = [0, 1, 2, 3, 4, 5, 8, _lib.ACCUM_WEIGHT, _lib.ACCUM_BATCHES]
+# the test_pn_net branch (:883,915-927): batch scalars, size-weighted like every Evaluator metric
+PRIOR_METRIC_SLOTS = {
+    'pn_energy': _lib.ACCUM_PN_ENERGY,
+    'pd_energy': _lib.ACCUM_PD_ENERGY,
+    'kl_adv_and_gaussian': _lib.ACCUM_KL_ADV,
+    'log_Z_compute_op': _lib.ACCUM_LOG_Z_OP,       # not in the Evaluator's dict in the reference; reported alongside
+}
 
 
 def shard_range(n, rank, world):
@@ -39,38 +46,56 @@ def shard_range(n, rank, world):
 
 
 def combine_accumulators(accum, group=None):
-    """All ranks' accumulator vectors (float64 torch tensor [ACCUM_SLOTS], any device) -> global one.
-    ONE sum-allreduce carries every additive slot; the log-Z (max, sum-exp) pair is made additive
-    first by rescaling to a max that travels in a tiny max-allreduce only when log-Z batches exist."""
+    """All ranks' accumulator vectors (float64 torch tensor [ACCUM_SLOTS], any device) -> the global one, on every
+    rank, with ONE collective and no host synchronisation: an all-gather of the R x ACCUM_SLOTS doubles (NCCL over
+    NVLink on GPUs), then every rank sums the additive slots and merges the log-Z (max, sum-exp) pairs by rescaling to
+    the common max, all as device tensor ops."""
     import torch
     import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return accum
-    out = accum.clone()
-    gmax = out[_lib.ROW_LZ_MAX:_lib.ROW_LZ_MAX + 1].clone()
-    if float(out[_lib.ACCUM_BATCHES]) == 0:
-        gmax.fill_(-float('inf'))
-    dist.all_reduce(gmax, op=dist.ReduceOp.MAX, group=group)
-    if math.isfinite(float(gmax)):
-        scale = torch.exp(out[_lib.ROW_LZ_MAX] - gmax[0]) if float(out[_lib.ACCUM_BATCHES]) > 0 else out.new_zeros(())
-        out[_lib.ROW_LZ_SUM] = out[_lib.ROW_LZ_SUM] * scale
-    else:
-        out[_lib.ROW_LZ_SUM] = 0
-    out[_lib.ROW_LZ_MAX] = 0
-    dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)       # THE allreduce of the metric sums
-    out[_lib.ROW_LZ_MAX] = gmax[0]
+    world = dist.get_world_size(group)
+    mine = accum.contiguous()
+    gathered = torch.empty((world, mine.numel()), dtype=mine.dtype, device=mine.device)
+    try:
+        dist.all_gather_into_tensor(gathered, mine, group=group)        # THE collective of an evaluation
+    except (RuntimeError, NotImplementedError):                         # backends without the flat variant
+        parts = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(parts, mine, group=group)
+        gathered = torch.stack(parts)
+    return merge_accumulators(gathered)
+
+
+def merge_accumulators(gathered):
+    """[R, ACCUM_SLOTS] per-rank accumulators -> one [ACCUM_SLOTS] (pure tensor arithmetic, no host sync)."""
+    import torch
+    out = gathered.sum(dim=0)
+    has = gathered[:, _lib.ACCUM_BATCHES] > 0                           # ranks that saw log-Z batches
+    ninf = torch.full_like(gathered[:, 0], -float('inf'))
+    gmax = torch.where(has, gathered[:, _lib.ROW_LZ_MAX], ninf).max()
+    terms = torch.where(has, gathered[:, _lib.ROW_LZ_SUM] * torch.exp(gathered[:, _lib.ROW_LZ_MAX] - gmax),
+                        torch.zeros_like(ninf))
+    any_has = has.any()
+    out[_lib.ROW_LZ_MAX] = torch.where(any_has, gmax, torch.zeros_like(gmax))
+    out[_lib.ROW_LZ_SUM] = torch.where(any_has, terms.sum(), torch.zeros_like(gmax))
     return out
 
 
 def metrics_from_accumulator(accum, len_train=None):
-    """float64 accumulator -> dict of dataset metrics (names of dmm_cifar10.py:1131-1136) and,
-    if log-Z batches were accumulated, 'log_Z' = logsumexp_b(lz_b) - log(#batches) (+ log len_train)."""
+    """float64 accumulator -> dict of dataset metrics (the eleven names of dmm_cifar10.py:1131-1136; the prior-branch
+    ones when that branch was accumulated) and, if log-Z batches were accumulated, 'log_Z' = logsumexp_b(lz_b) -
+    log(#batches) (+ log len_train).  test_mse: the reference reshapes the per-image minima to (-1, test_x_samples)
+    and averages twice (:893-895), which is the plain mean over images."""
     a = np.asarray(accum.detach().cpu().numpy() if hasattr(accum, 'detach') else accum, dtype=np.float64)
     w = a[_lib.ACCUM_WEIGHT]
     out = {}
     if w > 0:
         for name, (slot, sign) in METRIC_SLOTS.items():
             out[name] = sign * a[slot] / w
+    pw = a[_lib.ACCUM_PRIOR_WEIGHT]
+    if pw > 0:
+        for name, slot in PRIOR_METRIC_SLOTS.items():
+            out[name] = a[slot] / pw
     nb = a[_lib.ACCUM_BATCHES]
     if nb > 0 and a[_lib.ROW_LZ_SUM] > 0:
         out['log_Z'] = a[_lib.ROW_LZ_MAX] + math.log(a[_lib.ROW_LZ_SUM]) - math.log(nb)
@@ -87,8 +112,14 @@ class Evaluator(object):
     metric dict (every rank gets the same values).  `x` may be a CUDA tensor (resident data) or a
     host array / pinned tensor (copied batch by batch inside the loop, like feed_dict)."""
 
-    def __init__(self, model, n_z=None, batch_size=None, seed=0, group=None, time_metric_name='eval_time'):
+    def __init__(self, model, n_z=None, batch_size=None, seed=0, group=None, time_metric_name='eval_time',
+                 prior_branch=True, n_pz=None):
+        """prior_branch: evaluate the test_pn_net branch (config.test_n_pz prior draws through G_theta and D_psi per
+        mini-batch -> pn_energy, pd_energy, kl_adv_and_gaussian) with every batch, as the reference's graph does
+        (dmm_cifar10.py:883,915-927); False leaves those three metrics out (throughput runs that say so)."""
         self.model = model
+        self.prior_branch = bool(prior_branch)
+        self.n_pz = int(n_pz if n_pz is not None else model.config.test_n_pz)
         self.n_z = int(n_z if n_z is not None else model.config.test_n_qz)
         self.batch_size = int(batch_size if batch_size is not None else model.config.test_batch_size)
         if self.batch_size > model.config.max_batch:
@@ -104,8 +135,9 @@ class Evaluator(object):
             return dist.get_rank(self.group), dist.get_world_size(self.group)
         return 0, 1
 
-    def run_shard(self, x, x_origin=None, eps=None, accum=None, first_index=0):
-        """Accumulate the metrics of images x [n,H,W,C] (already this rank's shard) into `accum`."""
+    def run_shard(self, x, x_origin=None, eps=None, accum=None, first_index=0, eps_prior=None):
+        """Accumulate the metrics of images x [n,H,W,C] (already this rank's shard) into `accum`.
+        eps_prior [n_batches, n_pz, z_dim]: fed-in prior draws of the test_pn_net branch (parity runs)."""
         import torch
         m = self.model
         dev = m.device
@@ -113,7 +145,8 @@ class Evaluator(object):
             accum = torch.zeros(_lib.ACCUM_SLOTS, dtype=torch.float64, device=dev)
         n = int(x.shape[0])
         pi = torch.empty((_lib.PER_IMAGE_ROWS, self.batch_size), dtype=torch.float32, device=dev)
-        for b0 in range(0, n, self.batch_size):
+        prior4 = torch.empty(4, dtype=torch.float32, device=dev) if self.prior_branch else None
+        for ib, b0 in enumerate(range(0, n, self.batch_size)):
             b1 = min(n, b0 + self.batch_size)
             B = b1 - b0
             xb = m._images(x[b0:b1] if isinstance(x, torch.Tensor) else np.asarray(x[b0:b1], dtype=np.float32))
@@ -125,16 +158,19 @@ class Evaluator(object):
             view = pi.reshape(-1)[:_lib.PER_IMAGE_ROWS * B]
             check(lib.apvae_is_nll(m._h, _ptr(xb), _ptr(xo), B, self.n_z, _ptr(eb),
                                    self.seed + first_index + b0, _ptr(view), None, _stream()), m._h)
-            check(lib.apvae_accumulate_metrics(m._h, _ptr(view), B, self.n_z, _ptr(accum), _stream()), m._h)
+            if self.prior_branch:
+                m.prior_branch(self.n_pz, eps=None if eps_prior is None else eps_prior[ib],
+                               seed=self.seed + first_index + b0, out=prior4)
+            check(lib.apvae_accumulate_metrics(m._h, _ptr(view), _ptr(prior4), B, self.n_z, _ptr(accum), _stream()), m._h)
         return accum
 
-    def run(self, x, x_origin=None, eps=None):
+    def run(self, x, x_origin=None, eps=None, eps_prior=None):
         import torch
         rank, world = self._rank_world()
         lo, hi = shard_range(int(x.shape[0]), rank, world)
         t0 = time.time()
         accum = self.run_shard(x[lo:hi], None if x_origin is None else x_origin[lo:hi],
-                               None if eps is None else eps[:, lo:hi], first_index=lo)
+                               None if eps is None else eps[:, lo:hi], first_index=lo, eps_prior=eps_prior)
         accum = combine_accumulators(accum, self.group)
         self.last_accumulator = accum
         out = metrics_from_accumulator(accum, self.model.config.len_train)
@@ -145,7 +181,11 @@ class Evaluator(object):
     def estimate_log_Z(self, x_train, x_origin=None, eps=None, set_model=True):
         """The log-Z loop (dmm_cifar10.py:1215-1227): another_log_Z_compute_op over the train set,
         logsumexp(list) - log(#batches); stores it like get_log_Z().set(...)."""
-        out = self.run(x_train, x_origin, eps)
+        keep, self.prior_branch = self.prior_branch, False        # the log-Z pass reads only the chain's energies
+        try:
+            out = self.run(x_train, x_origin, eps)
+        finally:
+            self.prior_branch = keep
         if set_model and 'log_Z' in out:
             m = self.model
             m.set_scalars(m.xi_raw, m.beta, out['log_Z'])

@@ -50,6 +50,8 @@ class ExpConfig(object):
         self.max_chunk = 512
         self.enable_grad = False
         self.precise = False       # split-precision G_theta / D_psi (fp32-class energies for the sampler, 3x MMA work)
+        self.operand_dtype = 'fp16'  # 16-bit operand format of the tensor-core path: 'fp16' (11 significant bits; default)
+                                     # or 'bf16' (8 bits, fp32's exponent range); fp32 accumulation either way
         for k, v in kw.items():
             if not hasattr(self, k):
                 raise AttributeError('ExpConfig has no field %r' % (k,))
@@ -74,6 +76,9 @@ class ExpConfig(object):
         c.precise = int(self.precise)
         c.nf_layers = int(self.nf_layers) if self.use_flow else 0
         c.latent_gan = int(self.latent_gan)
+        if self.operand_dtype not in ('fp16', 'bf16'):
+            raise ValueError("operand_dtype must be 'fp16' or 'bf16'")
+        c.operand_bf16 = int(self.operand_dtype == 'bf16')
         return c
 
 
@@ -247,18 +252,29 @@ class Model(object):
                    ele_adv_test_ll=pi[_lib.ROW_ADV_LL], ele_adv_test_lb=pi[_lib.ROW_ADV_LB],
                    ele_test_recon=pi[_lib.ROW_RECON], ele_reconstruct_energy=pi[_lib.ROW_DG],
                    ele_lz_max=pi[_lib.ROW_LZ_MAX], ele_lz_sum=pi[_lib.ROW_LZ_SUM],
-                   ele_real_energy=pi[_lib.ROW_REAL_E], per_image=pi)
+                   ele_real_energy=pi[_lib.ROW_REAL_E], ele_test_mse=pi[_lib.ROW_MSE], per_image=pi)
         if per_sample:
             out.update(log_px=ps[_lib.SROW_LOG_PX].reshape(K, B), log_q=ps[_lib.SROW_LOG_Q].reshape(K, B),
-                       log_pn=ps[_lib.SROW_LOG_PN].reshape(K, B), d_g=ps[_lib.SROW_DG].reshape(K, B))
+                       log_pn=ps[_lib.SROW_LOG_PN].reshape(K, B), d_g=ps[_lib.SROW_DG].reshape(K, B),
+                       sq_err=ps[_lib.SROW_SQ_ERR].reshape(K, B))
         return out
 
     def prior_stats(self, Kp, eps=None, seed=0):
         """test_pn_net branch (dmm_cifar10.py:883,915-927): D(G(z)) and log N(z) for Kp prior draws."""
         e = self._f32(eps).reshape(Kp, self.config.z_dim) if eps is not None else None
         dg, lpn = self._empty(Kp), self._empty(Kp)
-        check(lib.apvae_prior_stats(self._h, int(Kp), _ptr(e), int(seed), _ptr(dg), _ptr(lpn), _stream()), self._h)
+        check(lib.apvae_prior_stats(self._h, int(Kp), _ptr(e), int(seed), _ptr(dg), _ptr(lpn), None, _stream()), self._h)
         return dg, lpn
+
+    def prior_branch(self, Kp=None, eps=None, seed=0, out=None):
+        """The batch scalars of the test_pn_net branch (dmm_cifar10.py:883,915-927), reduced on the device: a float32
+        tensor [4] = (pn_energy, pd_energy, kl_adv_and_gaussian, log_Z_compute_op) from Kp = config.test_n_pz draws
+        z ~ N(0, I) (fed as eps [Kp, z_dim] or drawn in-kernel)."""
+        Kp = int(self.config.test_n_pz if Kp is None else Kp)
+        e = self._f32(eps).reshape(Kp, self.config.z_dim) if eps is not None else None
+        out = self._empty(4) if out is None else out
+        check(lib.apvae_prior_stats(self._h, Kp, _ptr(e), int(seed), None, None, _ptr(out), _stream()), self._h)
+        return out
 
     # ------------------------------------------------------------------ sampler
     def energy_grad(self, z):
@@ -280,9 +296,11 @@ class Model(object):
         check(lib.apvae_image_energy_grad(self._h, _ptr(x4), n, _ptr(d), _ptr(g), _ptr(s), _stream()), self._h)
         return d, g.reshape(x.shape), s
 
-    def mala(self, z0, steps, alpha=None, eps=None, u=None, seed=0, history=True):
+    def mala(self, z0, steps, alpha=None, eps=None, u=None, seed=0, history=True, history_z=False):
         """EnergyDistribution.sample (dmm_cifar10.py:179-239): `steps` MALA iterations.
-        z0 [n, z_dim] (or [n,1,z_dim]); eps [steps,n,z_dim], u [steps,n] optional fed-in noise."""
+        z0 [n, z_dim] (or [n,1,z_dim]); eps [steps,n,z_dim], u [steps,n] optional fed-in noise.
+        history_z=True also returns history_z [steps, ...z0.shape]: the state BEFORE each step (:200,235); the reference's
+        plot_samples restarts its next run from history_z[-1] (:1061)."""
         z = self._f32(z0).clone()
         shape = tuple(z.shape)
         z2 = z.reshape(-1, self.config.z_dim)
@@ -293,9 +311,13 @@ class Model(object):
         he = self._empty(steps, n) if history else None
         hp = self._empty(steps, n) if history else None
         hr = self._empty(steps, n) if history else None
+        hz = self._empty(steps, n, self.config.z_dim) if history_z else None
         check(lib.apvae_mala(self._h, _ptr(z2), n, int(steps), float(alpha), _ptr(e), _ptr(uu), int(seed),
-                             _ptr(he), _ptr(hp), _ptr(hr), _stream()), self._h)
-        return dict(z=z2.reshape(shape), history_e_z=he, history_pure_e_z=hp, history_ratio=hr)
+                             _ptr(he), _ptr(hp), _ptr(hr), _ptr(hz), _stream()), self._h)
+        out = dict(z=z2.reshape(shape), history_e_z=he, history_pure_e_z=hp, history_ratio=hr)
+        if history_z:
+            out['history_z'] = hz.reshape((steps,) + shape)
+        return out
 
     def fill_normal(self, shape, seed=0, offset=0, truncated=False):
         """N(0, 1) draws (Philox, in-kernel) as tf.random_normal inside zd.Normal.sample; `truncated`: resampled

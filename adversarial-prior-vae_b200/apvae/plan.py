@@ -21,7 +21,12 @@ def pad16(c):
 class Plan(object):
     """A planned op: sum of conv terms sharing one output grid."""
 
-    def __init__(self, terms, capacity_n):
+    def __init__(self, terms, capacity_n, dtype='fp16'):
+        """dtype: the 16-bit operand format ('fp16' default, 'bf16'): kernels are packed in it, sources and 16-bit
+        outputs hold it."""
+        if dtype not in ('fp16', 'bf16'):
+            raise ValueError("dtype must be 'fp16' or 'bf16'")
+        self.dtype = dtype
         self._keep = []
         arr = (_lib.ConvTerm * len(terms))()
         for i, t in enumerate(terms):
@@ -43,7 +48,7 @@ class Plan(object):
                 self._keep.append(b)
                 arr[i].bias = b.ctypes.data_as(C.POINTER(C.c_float))
         self._h = C.c_void_p()
-        check(lib.apvae_plan_create(arr, len(terms), int(capacity_n), C.byref(self._h)))
+        check(lib.apvae_plan_create(arr, len(terms), int(capacity_n), int(dtype == 'bf16'), C.byref(self._h)))
         self.info = _lib.PlanInfo()
         check(lib.apvae_plan_get_info(self._h, C.byref(self.info)))
 
@@ -125,16 +130,21 @@ class Plan(object):
         check(lib.apvae_plan_run(self._h, int(device), arr, int(n_valid), C.byref(e)))
 
 
-def _to_nhwc_bf16(x, cp):
-    """float32 CUDA [N,H,W,C] -> bf16 [N,H,W,cp] (zero padded). torch is plumbing only."""
+def torch_dtype(dtype):
+    import torch
+    return torch.float16 if dtype == 'fp16' else torch.bfloat16
+
+
+def _to_nhwc_16(x, cp, dtype='fp16'):
+    """float32 CUDA [N,H,W,C] -> 16-bit operand tensor [N,H,W,cp] (zero padded). torch is plumbing only."""
     import torch
     n, h, w, c = x.shape
-    out = torch.zeros((n, h, w, cp), dtype=torch.bfloat16, device=x.device)
-    out[..., :c] = x.to(torch.bfloat16)
+    out = torch.zeros((n, h, w, cp), dtype=torch_dtype(dtype), device=x.device)
+    out[..., :c] = x.to(out.dtype)
     return out
 
 
-def _run_single(x, kernel, bias, strides, transpose, activation_fn):
+def _run_single(x, kernel, bias, strides, transpose, activation_fn, dtype='fp16'):
     import torch
     lead = tuple(x.shape[:-3])
     x4 = x.reshape((-1,) + tuple(x.shape[-3:])).contiguous()
@@ -142,8 +152,8 @@ def _run_single(x, kernel, bias, strides, transpose, activation_fn):
     kernel = np.asarray(kernel, dtype=np.float32)
     cout = kernel.shape[2] if transpose else kernel.shape[3]
     plan = Plan([dict(src=0, transpose=transpose, stride=strides, in_h=h, in_w=w, kernel=kernel,
-                      bias=bias)], n)
-    src = _to_nhwc_bf16(x4, pad16(c))
+                      bias=bias)], n, dtype=dtype)
+    src = _to_nhwc_16(x4, pad16(c), dtype)
     out = torch.zeros((n, plan.info.ho, plan.info.wo, cout), dtype=torch.float32, device=x.device)
     if activation_fn not in (None, 'tanh'):
         raise ValueError('activation_fn must be None or "tanh"')
@@ -152,21 +162,21 @@ def _run_single(x, kernel, bias, strides, transpose, activation_fn):
     return out.reshape(lead + tuple(out.shape[1:]))
 
 
-def conv2d(x, kernel, bias=None, strides=1, activation_fn=None):
+def conv2d(x, kernel, bias=None, strides=1, activation_fn=None, dtype='fp16'):
     """spt.layers.conv2d(channels_last=True, padding='same'); x float32 CUDA [...,H,W,C],
-    kernel [kh,kw,Cin,Cout] (conv2d_.py:23-238).  bf16 operands, fp32 accumulate."""
-    return _run_single(x, kernel, bias, strides, False, activation_fn)
+    kernel [kh,kw,Cin,Cout] (conv2d_.py:23-238).  16-bit operands (`dtype`), fp32 accumulate."""
+    return _run_single(x, kernel, bias, strides, False, activation_fn, dtype)
 
 
-def deconv2d(x, kernel, bias=None, strides=1, activation_fn=None):
+def deconv2d(x, kernel, bias=None, strides=1, activation_fn=None, dtype='fp16'):
     """spt.layers.deconv2d; kernel [kh,kw,Cout,Cin] (conv2d_.py:243-501)."""
-    return _run_single(x, kernel, bias, strides, True, activation_fn)
+    return _run_single(x, kernel, bias, strides, True, activation_fn, dtype)
 
 
-def dense(x, kernel, bias=None):
+def dense(x, kernel, bias=None, dtype='fp16'):
     """spt.layers.dense (dense_.py:14-171): x [..., in] @ kernel [in, out] + bias."""
     lead = tuple(x.shape[:-1])
     k = np.asarray(kernel, dtype=np.float32)
     x4 = x.reshape((-1, 1, 1, x.shape[-1]))
-    y = _run_single(x4, k.reshape((1, 1) + k.shape), bias, 1, False, None)
+    y = _run_single(x4, k.reshape((1, 1) + k.shape), bias, 1, False, None, dtype)
     return y.reshape(lead + (k.shape[1],))

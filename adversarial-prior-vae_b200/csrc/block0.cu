@@ -11,23 +11,16 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include "kernels.h"
+#include "op16.h"
 
 namespace apvae {
 namespace {
 
 constexpr int kThreads = 256;
 
-__device__ __forceinline__ float bfl(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bfh(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
-__device__ __forceinline__ uint32_t pk(float a, float b) {
-    const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<const uint32_t*>(&v);
-}
-__device__ __forceinline__ float bfr(float a) { return __bfloat162float(__float2bfloat16_rn(a)); }
-
 // CIN input channels, COUT outputs, 3x3 taps, one image per CTA (H, W <= 32).  Shared memory: lrelu(x), x and r on a
 // zero-bordered (H+2) x (W+2) grid, channel-planar fp32.
-template <int CIN, int COUT>
+template <int CIN, int COUT, bool F16>
 __global__ void __launch_bounds__(kThreads) small_block_kernel(const __grid_constant__ SmallBlockParams p, int n_images) {
     constexpr int PW = kSmallBlockMaxHW + 2;
     __shared__ float xa[CIN][PW * PW];        // lrelu(x), zero border
@@ -41,7 +34,7 @@ __global__ void __launch_bounds__(kThreads) small_block_kernel(const __grid_cons
         const uint8_t* src = static_cast<const uint8_t*>(p.in_raw) + (size_t)img * HW * p.cp_in * 2;
         for (int px = t; px < HW; px += kThreads) {
             const uint2 v = *reinterpret_cast<const uint2*>(src + (size_t)px * p.cp_in * 2);     // first 4 channels
-            const float c[4] = {bfl(v.x), bfh(v.x), bfl(v.y), bfh(v.y)};
+            const float c[4] = {op16::lo<F16>(v.x), op16::hi<F16>(v.x), op16::lo<F16>(v.y), op16::hi<F16>(v.y)};
             const int y = px / W, x = px - y * W, o = (y + 1) * PW + x + 1;
 #pragma unroll
             for (int ci = 0; ci < CIN; ++ci) { xr[ci][o] = c[ci]; xa[ci][o] = fmaxf(c[ci], p.alpha * c[ci]); }
@@ -68,12 +61,12 @@ __global__ void __launch_bounds__(kThreads) small_block_kernel(const __grid_cons
             float rv[4] = {0.f, 0.f, 0.f, 0.f};          // CIN <= 3 values, the rest of the first 4 channels zero
 #pragma unroll
             for (int co = 0; co < CIN; ++co) {
-                rv[co] = bfr(fmaxf(acc[co], p.alpha * acc[co]));
+                rv[co] = op16::round<F16>(fmaxf(acc[co], p.alpha * acc[co]));
                 rr[co][o + PW + 1] = rv[co];
             }
             if (p.r_act) {
                 uint4* d = reinterpret_cast<uint4*>(rdst + (size_t)px * p.cp_in * 2);
-                d[0] = make_uint4(pk(rv[0], rv[1]), pk(rv[2], rv[3]), 0u, 0u);
+                d[0] = make_uint4(op16::pack<F16>(rv[0], rv[1]), op16::pack<F16>(rv[2], rv[3]), 0u, 0u);
                 for (int c = 1; c < rch; ++c) d[c] = make_uint4(0u, 0u, 0u, 0u);
             }
         }
@@ -106,8 +99,8 @@ __global__ void __launch_bounds__(kThreads) small_block_kernel(const __grid_cons
             uint32_t wr[COUT / 2], wa[COUT / 2];
 #pragma unroll
             for (int co = 0; co < COUT; co += 2) {
-                wr[co / 2] = pk(acc[co], acc[co + 1]);
-                wa[co / 2] = pk(fmaxf(acc[co], p.alpha * acc[co]), fmaxf(acc[co + 1], p.alpha * acc[co + 1]));
+                wr[co / 2] = op16::pack<F16>(acc[co], acc[co + 1]);
+                wa[co / 2] = op16::pack<F16>(fmaxf(acc[co], p.alpha * acc[co]), fmaxf(acc[co + 1], p.alpha * acc[co + 1]));
             }
             auto store = [&](uint8_t* base, const uint32_t (&w)[COUT / 2]) {
                 uint4* d = reinterpret_cast<uint4*>(base + (size_t)px * p.ldo * 2);
@@ -131,9 +124,9 @@ int launch_small_block(const SmallBlockParams& p, int n, void* stream) {
         return (int)cudaErrorInvalidValue;
     void (*kern)(SmallBlockParams, int) = nullptr;
     switch (p.cin) {
-        case 1: kern = small_block_kernel<1, 16>; break;
-        case 2: kern = small_block_kernel<2, 16>; break;
-        default: kern = small_block_kernel<3, 16>; break;
+        case 1: kern = p.f16 ? small_block_kernel<1, 16, true> : small_block_kernel<1, 16, false>; break;
+        case 2: kern = p.f16 ? small_block_kernel<2, 16, true> : small_block_kernel<2, 16, false>; break;
+        default: kern = p.f16 ? small_block_kernel<3, 16, true> : small_block_kernel<3, 16, false>; break;
     }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

@@ -21,6 +21,7 @@ struct apvae_plan {
     std::vector<PatchPlan> phases;   // stride-2 transposed conv: four sub-pixel phase plans (A-stationary kernel)
     int sel = -1;                     // which patch plan the info / copy calls describe (apvae_plan_select_patch)
     std::vector<PatchPlan> row_phases;   // ... or two plans, one per output row phase, both column phases merged into N
+    int f16 = 1;                         // operand format (op16.h)
 };
 
 static int env_int(const char* name) {
@@ -40,7 +41,12 @@ static int set_global_err(const std::string& m, int code) {
     return code;
 }
 
-static_assert((int)kPerImageRows + 1 == (int)APVAE_PER_IMAGE_ROWS, "per-image row tables out of sync");
+static_assert((int)kPerImageRows == (int)APVAE_PER_IMAGE_ROWS && (int)ROW_REAL_E == (int)APVAE_ROW_REAL_E &&
+              (int)ROW_MSE == (int)APVAE_ROW_MSE, "per-image row tables out of sync");
+static_assert((int)ACC_WEIGHT == APVAE_ACCUM_WEIGHT && (int)ACC_BATCHES == APVAE_ACCUM_BATCHES && (int)ACC_MSE == APVAE_ACCUM_MSE &&
+              (int)ACC_PN == APVAE_ACCUM_PN_ENERGY && (int)ACC_PD == APVAE_ACCUM_PD_ENERGY && (int)ACC_KL == APVAE_ACCUM_KL_ADV &&
+              (int)ACC_LOGZ_OP == APVAE_ACCUM_LOG_Z_OP && (int)ACC_PRIOR_WEIGHT == APVAE_ACCUM_PRIOR_WEIGHT,
+              "accumulator layouts out of sync");
 
 extern "C" {
 
@@ -186,7 +192,7 @@ int apvae_encode(apvae_handle* h, const float* x_dev, int B, float* mu_dev, floa
 // z fp32 [n, d] -> decoder input tensors (no noise: mu = z, eps unused)
 static int stage_latents(Model& m, const float* z_dev, int n, void* stream) {
     return launch_sample_z(nullptr, nullptr, z_dev, n, 0, 1, m.cfg.z_dim, 0.f, 0, nullptr, m.g_in.raw.ptr,
-                           m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, nullptr, stream,
+                           m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, nullptr, m.f16(), stream,
                            m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr);
 }
 
@@ -213,7 +219,7 @@ int apvae_energy(apvae_handle* h, const float* x_dev, const float* z_dev, int N,
     for (int s0 = 0; s0 < N; s0 += m.cfg.max_chunk) {
         const int n = std::min(m.cfg.max_chunk, N - s0);
         LCHECK(stage_latents(m, z_dev + (size_t)s0 * m.cfg.z_dim, n, stream), "stage_latents");
-        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
+        if (!m.run_decoder_chunk(n, stream, false)) return APVAE_ERR_CUDA;
         if (!m.run_critic_chunk(n, d_dev + s0, stream)) return APVAE_ERR_CUDA;
     }
     return APVAE_OK;
@@ -246,19 +252,19 @@ int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev,
             LCHECK(launch_sample_z_flow(m.q_mu, m.q_logstd, eps + s0 * d, n, (int)(s0 % B), B, d, m.cfg.min_logstd_of_q,
                                         m.cfg.use_truncated, m.flow_w, m.flow_uhat, m.flow_b, m.flow_wu, m.cfg.nf_layers,
                                         nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f,
-                                        m.log_q + s0, m.log_pn + s0, stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
+                                        m.log_q + s0, m.log_pn + s0, m.f16(), stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
                    "sample_z_flow");
         else
         LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps + s0 * d, n, (int)(s0 % B), B, d, m.cfg.min_logstd_of_q,
                                m.cfg.use_truncated, nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(),
-                               m.z_cpad(), 0.2f, m.log_q + s0, m.log_pn + s0, stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
+                               m.z_cpad(), 0.2f, m.log_q + s0, m.log_pn + s0, m.f16(), stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr),
                "sample_z");
-        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
-        LCHECK(launch_pixel_logprob(m.head_f32, m.head_ld(), x_dev, n, (int)(s0 % B), B, m.HW(), m.C(), m.cfg.bernoulli,
-                                    m.cfg.uniform_scale, m.beta, m.cfg.epsilon, m.log_px + s0, stream), "pixel_logprob");
+        // G_theta, with log p(x|z) and the test_mse squared error scored inside the heads kernel
+        const Model::LikArgs lik = {x_dev, (int)(s0 % B), B, m.log_px + s0, m.sq_err + s0};
+        if (!m.run_decoder_chunk(n, stream, !m.heads_op, &lik)) return APVAE_ERR_CUDA;
         if (!m.run_critic_chunk(n, m.d_g + s0, stream)) return APVAE_ERR_CUDA;
     }
-    LCHECK(launch_is_reduce(m.log_px, m.log_q, m.log_pn, m.d_g, nullptr, K, B, d, m.w_xi(), m.log_Z, per_image_dev, stream),
+    LCHECK(launch_is_reduce(m.log_px, m.log_q, m.log_pn, m.d_g, m.sq_err, K, B, d, m.w_xi(), m.log_Z, per_image_dev, stream),
            "is_reduce");
     if (!m.critic_of_images(x_origin_dev, B, per_image_dev + (size_t)APVAE_ROW_REAL_E * B, stream)) return APVAE_ERR_CUDA;
     if (per_sample_dev) {
@@ -267,6 +273,7 @@ int apvae_is_nll(apvae_handle* h, const float* x_dev, const float* x_origin_dev,
         cudaMemcpyAsync(per_sample_dev + APVAE_SROW_LOG_Q * S, m.log_q, bytes, cudaMemcpyDeviceToDevice, st);
         cudaMemcpyAsync(per_sample_dev + APVAE_SROW_LOG_PN * S, m.log_pn, bytes, cudaMemcpyDeviceToDevice, st);
         cudaMemcpyAsync(per_sample_dev + APVAE_SROW_DG * S, m.d_g, bytes, cudaMemcpyDeviceToDevice, st);
+        cudaMemcpyAsync(per_sample_dev + APVAE_SROW_SQ_ERR * S, m.sq_err, bytes, cudaMemcpyDeviceToDevice, st);
     }
     return APVAE_OK;
 }
@@ -290,25 +297,26 @@ int apvae_sample_z(apvae_handle* h, const float* x_origin_dev, int B, int K, con
     if (m.cfg.nf_layers > 0)
         LCHECK(launch_sample_z_flow(m.q_mu, m.q_logstd, eps, (int)S, 0, B, d, m.cfg.min_logstd_of_q, m.cfg.use_truncated,
                                     m.flow_w, m.flow_uhat, m.flow_b, m.flow_wu, m.cfg.nf_layers, z_dev, nullptr, nullptr, 0, 1,
-                                    0, 0.2f, lq, log_pn_dev, stream), "sample_z_flow");
+                                    0, 0.2f, lq, log_pn_dev, m.f16(), stream), "sample_z_flow");
     else
     LCHECK(launch_sample_z(m.q_mu, m.q_logstd, eps, (int)S, 0, B, d, m.cfg.min_logstd_of_q, m.cfg.use_truncated, z_dev,
-                           nullptr, nullptr, 0, 1, 0, 0.2f, lq, log_pn_dev, stream), "sample_z");
+                           nullptr, nullptr, 0, 1, 0, 0.2f, lq, log_pn_dev, m.f16(), stream), "sample_z");
     return APVAE_OK;
 }
 
-int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, int B, int K, double* accum_dev, void* stream) {
+int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, const float* prior4_dev, int B, int K,
+                             double* accum_dev, void* stream) {
     REQUIRE_BUILT(h);
     static_assert(APVAE_ACCUM_SLOTS == kAccumSlots, "accumulator layouts out of sync");
     if (B <= 0 || K <= 0 || !per_image_dev || !accum_dev) { m.err = "accumulate_metrics: bad arguments"; return APVAE_ERR_INVALID; }
-    LCHECK(launch_accumulate_metrics(per_image_dev, B, K, APVAE_PER_IMAGE_ROWS, accum_dev, stream), "accumulate_metrics");
+    LCHECK(launch_accumulate_metrics(per_image_dev, B, K, APVAE_PER_IMAGE_ROWS, prior4_dev, accum_dev, stream), "accumulate_metrics");
     return APVAE_OK;
 }
 
 int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t seed, float* d_g_dev,
-                      float* log_pn_dev, void* stream) {
+                      float* log_pn_dev, float* prior4_dev, void* stream) {
     REQUIRE_BUILT(h);
-    if (Kp <= 0 || !d_g_dev || !log_pn_dev) { m.err = "prior_stats: bad arguments"; return APVAE_ERR_INVALID; }
+    if (Kp <= 0 || (!d_g_dev && !log_pn_dev && !prior4_dev)) { m.err = "prior_stats: bad arguments"; return APVAE_ERR_INVALID; }
     const int d = m.cfg.z_dim;
     if (!m.ensure_sample_buffers((size_t)Kp)) return APVAE_ERR_CUDA;
     const float* eps = eps_dev;
@@ -316,14 +324,18 @@ int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t se
         LCHECK(launch_fill_normal(m.eps_buf, (long long)Kp * d, seed, 1ull << 48, 0, stream), "fill_normal");
         eps = m.eps_buf;
     }
+    // per-draw rows land in the caller's arrays when given, else in the handle's per-sample scratch
+    float* dg = d_g_dev ? d_g_dev : m.d_g;
+    float* lpn = log_pn_dev ? log_pn_dev : m.log_pn;
     for (int s0 = 0; s0 < Kp; s0 += m.cfg.max_chunk) {
         const int n = std::min(m.cfg.max_chunk, Kp - s0);
         LCHECK(launch_sample_z(nullptr, nullptr, eps + (size_t)s0 * d, n, 0, 1, d, 0.f, 0, nullptr, m.g_in.raw.ptr,
-                               m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, log_pn_dev + s0,
-                               stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr), "sample_z");
-        if (!m.run_decoder_chunk(n, stream)) return APVAE_ERR_CUDA;
-        if (!m.run_critic_chunk(n, d_g_dev + s0, stream)) return APVAE_ERR_CUDA;
+                               m.g_in.act.ptr, m.z_stride(), m.z_group(), m.z_cpad(), 0.2f, nullptr, lpn + s0,
+                               m.f16(), stream, m.g_in.raw_lo.ptr, m.g_in.act_lo.ptr), "sample_z");
+        if (!m.run_decoder_chunk(n, stream, false)) return APVAE_ERR_CUDA;
+        if (!m.run_critic_chunk(n, dg + s0, stream)) return APVAE_ERR_CUDA;
     }
+    if (prior4_dev) LCHECK(launch_prior_reduce(dg, lpn, Kp, d, m.w_xi(), m.log_Z, prior4_dev, stream), "prior_reduce");
     return APVAE_OK;
 }
 
@@ -356,6 +368,33 @@ int apvae_sample_images(apvae_handle* h, const float* z_dev, int n_total, uint8_
                "quantize");
     }
     return APVAE_OK;
+}
+
+int apvae_discretized_logistic_log_prob(const float* x_dev, const float* mean_dev, const float* log_scale_dev, int64_t rows,
+                                        int64_t group, float bin_size, int has_min, float min_val, int has_max, float max_val,
+                                        int biased_edges, float epsilon, float* out_dev, void* stream) {
+    if (!x_dev || !mean_dev || !log_scale_dev || !out_dev || rows <= 0 || group <= 0 || !(bin_size > 0.f))
+        return set_global_err("discretized_logistic_log_prob: bad arguments", APVAE_ERR_INVALID);
+    LikelihoodSpec s;
+    memset(&s, 0, sizeof(s));
+    s.bernoulli = 0; s.bin_size = bin_size; s.log_bin_size = logf(bin_size);
+    s.has_min = has_min ? 1 : 0; s.has_max = has_max ? 1 : 0; s.min_val = min_val; s.max_val = max_val;
+    s.biased_edges = biased_edges ? 1 : 0; s.epsilon = epsilon; s.min_log_scale = -INFINITY;
+    const int e = launch_elementwise_logprob(x_dev, mean_dev, log_scale_dev, rows, group, s, out_dev, stream);
+    return e == 0 ? APVAE_OK : set_global_err(cudaGetErrorString((cudaError_t)e), e == (int)cudaErrorNoDevice || e == (int)cudaErrorInsufficientDriver ? APVAE_ERR_NO_DEVICE : APVAE_ERR_CUDA);
+}
+int apvae_bernoulli_log_prob(const float* x_dev, const float* mean_dev, int64_t rows, int64_t group, float* out_dev, void* stream) {
+    if (!x_dev || !mean_dev || !out_dev || rows <= 0 || group <= 0) return set_global_err("bernoulli_log_prob: bad arguments", APVAE_ERR_INVALID);
+    const LikelihoodSpec s = script_likelihood(1, -20.f);
+    const int e = launch_elementwise_logprob(x_dev, mean_dev, nullptr, rows, group, s, out_dev, stream);
+    return e == 0 ? APVAE_OK : set_global_err(cudaGetErrorString((cudaError_t)e), APVAE_ERR_CUDA);
+}
+int apvae_is_reduce(const float* log_px_dev, const float* log_q_dev, const float* log_pn_dev, const float* d_g_dev,
+                    const float* sq_err_dev, int K, int B, int z_dim, float w_xi, float log_Z, float* per_image_dev, void* stream) {
+    if (!log_px_dev || !log_q_dev || !log_pn_dev || !d_g_dev || !per_image_dev || K <= 0 || B <= 0)
+        return set_global_err("is_reduce: bad arguments", APVAE_ERR_INVALID);
+    const int e = launch_is_reduce(log_px_dev, log_q_dev, log_pn_dev, d_g_dev, sq_err_dev, K, B, z_dim, w_xi, log_Z, per_image_dev, stream);
+    return e == 0 ? APVAE_OK : set_global_err(cudaGetErrorString((cudaError_t)e), APVAE_ERR_CUDA);
 }
 
 int apvae_fill_normal(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, int truncated, void* stream) {
@@ -420,7 +459,7 @@ int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* na
 }
 
 // ---------------------------------------------------------------- layer-level interface
-int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, apvae_plan** out) {
+int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, apvae_plan** out) {
     if (!terms || nterms <= 0 || !out || capacity_n <= 0) return set_global_err("plan_create: bad arguments", APVAE_ERR_INVALID);
     std::vector<TermSpec> ts;
     for (int i = 0; i < nterms; ++i) {
@@ -428,9 +467,11 @@ int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, 
         t.src = terms[i].src; t.transpose = terms[i].transpose; t.k = terms[i].k; t.stride = terms[i].stride;
         t.cin = terms[i].cin; t.cout = terms[i].cout; t.in_h = terms[i].in_h; t.in_w = terms[i].in_w;
         t.in_cp = terms[i].in_cp; t.kernel = terms[i].kernel; t.bias = terms[i].bias;
+        t.f16 = operand_bf16 ? 0 : 1;
         ts.push_back(t);
     }
     apvae_plan* p = new apvae_plan();
+    p->f16 = operand_bf16 ? 0 : 1;
     std::string e;
     if (!plan_op(ts, capacity_n, &p->plan, &e)) { delete p; return set_global_err(e, APVAE_ERR_UNSUPPORTED); }
     if (patch_enabled()) {
@@ -562,6 +603,7 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
     ep.out_f32 = epi->out_f32_dev; ep.ld_f32 = epi->ld_f32; ep.f32_cols = epi->f32_cols;
     ep.res = epi->res_dev; ep.res_mode = epi->res_mode; ep.ld_res = epi->ld_res;
     ep.mask = epi->mask_dev; ep.ld_mask = epi->ld_mask; ep.tanh_cols = epi->tanh_cols;
+    ep.f16 = p->f16;
     // the op, or the four phase ops of a stride-2 transposed conv (only with a bf16-only epilogue; else the tap-GEMM op)
     std::vector<std::unique_ptr<DevOp>> ops;
     bool phased = !p->phases.empty();
@@ -663,12 +705,12 @@ int apvae_image_energy_grad(apvae_handle* h, const float* x_dev, int N, float* d
     return m.critic_grad_of_images(x_dev, N, d_dev, grad_dev, grad_sqnorm_dev, stream) ? APVAE_OK : APVAE_ERR_CUDA;
 }
 int apvae_mala(apvae_handle* h, float* z_io_dev, int n, int steps, float alpha, const float* eps_dev, const float* u_dev,
-               uint64_t seed, float* hist_e_dev, float* hist_pure_e_dev, float* hist_ratio_dev, void* stream) {
+               uint64_t seed, float* hist_e_dev, float* hist_pure_e_dev, float* hist_ratio_dev, float* hist_z_dev, void* stream) {
     REQUIRE_BUILT(h);
     if (!m.cfg.enable_grad) { m.err = "mala: create the handle with enable_grad = 1"; return APVAE_ERR_STATE; }
     if (n <= 0 || steps < 0 || !z_io_dev) { m.err = "mala: empty batch"; return APVAE_ERR_INVALID; }
     if (!(alpha > 0.f)) { m.err = "mala: alpha must be positive"; return APVAE_ERR_INVALID; }
-    return m.mala(z_io_dev, n, steps, alpha, eps_dev, u_dev, seed, hist_e_dev, hist_pure_e_dev, hist_ratio_dev, stream)
+    return m.mala(z_io_dev, n, steps, alpha, eps_dev, u_dev, seed, hist_e_dev, hist_pure_e_dev, hist_ratio_dev, hist_z_dev, stream)
                ? APVAE_OK : APVAE_ERR_CUDA;
 }
 

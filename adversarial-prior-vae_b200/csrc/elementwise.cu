@@ -3,6 +3,8 @@
 #include <cuda_bf16.h>
 #include <math.h>
 #include "kernels.h"
+#include "likelihood.cuh"
+#include "op16.h"
 
 namespace apvae {
 namespace {
@@ -11,11 +13,6 @@ constexpr float kLog2Pi = 1.8378770664093453f;
 constexpr float kLogTruncArea = -0.04656529f;   // log(0.95449974), truncated_normal.py:146
 
 __device__ __forceinline__ float lrelu(float v, float a) { return v > 0.f ? v : a * v; }
-__device__ __forceinline__ float softplusf(float x) { return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x))); }
-__device__ __forceinline__ float sigmoidf_(float x) {
-    const float e = expf(-fabsf(x));
-    return x >= 0.f ? 1.f / (1.f + e) : e / (1.f + e);
-}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -59,28 +56,28 @@ __device__ float block_max(float v) {
 }
 
 __global__ void pack_image_kernel(const float* __restrict__ x, long long pixels, int c, int cp,
-                                  __nv_bfloat16* __restrict__ raw, __nv_bfloat16* __restrict__ act, float alpha,
-                                  __nv_bfloat16* __restrict__ raw_lo, __nv_bfloat16* __restrict__ act_lo) {
+                                  uint16_t* __restrict__ raw, uint16_t* __restrict__ act, float alpha,
+                                  uint16_t* __restrict__ raw_lo, uint16_t* __restrict__ act_lo, int f16) {
     const long long total = pixels * cp;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
         const long long p = i / cp;
         const int ch = (int)(i - p * cp);
         const float v = ch < c ? x[p * c + ch] : 0.f;
-        if (raw) raw[i] = __float2bfloat16(v);
-        if (act) act[i] = __float2bfloat16(lrelu(v, alpha));
-        if (raw_lo) raw_lo[i] = __float2bfloat16(v - __bfloat162float(__float2bfloat16(v)));
-        if (act_lo) { const float a = lrelu(v, alpha); act_lo[i] = __float2bfloat16(a - __bfloat162float(__float2bfloat16(a))); }
+        if (raw) raw[i] = op16::from_f32(v, f16);
+        if (act) act[i] = op16::from_f32(lrelu(v, alpha), f16);
+        if (raw_lo) raw_lo[i] = op16::from_f32(v - op16::round(v, f16), f16);
+        if (act_lo) { const float a = lrelu(v, alpha); act_lo[i] = op16::from_f32(a - op16::round(a, f16), f16); }
     }
 }
 
 // one warp per sample
 __global__ void sample_z_kernel(const float* __restrict__ mu, const float* __restrict__ logstd,
                                 const float* __restrict__ eps, int S, int s0, int B, int d, float min_logstd,
-                                int truncated, float* __restrict__ z_f32, __nv_bfloat16* __restrict__ z_raw,
-                                __nv_bfloat16* __restrict__ z_act, long long zstride, int zc, int cpad,
+                                int truncated, float* __restrict__ z_f32, uint16_t* __restrict__ z_raw,
+                                uint16_t* __restrict__ z_act, long long zstride, int zc, int cpad,
                                 float alpha, float* __restrict__ log_q, float* __restrict__ log_pn,
-                                __nv_bfloat16* __restrict__ z_raw_lo, __nv_bfloat16* __restrict__ z_act_lo) {
+                                uint16_t* __restrict__ z_raw_lo, uint16_t* __restrict__ z_act_lo, int f16) {
     const int lane = threadIdx.x & 31;
     const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (s >= S) return;
@@ -103,10 +100,10 @@ __global__ void sample_z_kernel(const float* __restrict__ mu, const float* __res
         lp += -0.5f * kLog2Pi - 0.5f * z * z;
         if (z_f32) z_f32[(size_t)s * d + j] = z;
         const size_t idx = (size_t)s * zstride + (size_t)(j / zc) * cpad + (j % zc);
-        if (z_raw) z_raw[idx] = __float2bfloat16(z);
-        if (z_act) z_act[idx] = __float2bfloat16(lrelu(z, alpha));
-        if (z_raw_lo) z_raw_lo[idx] = __float2bfloat16(z - __bfloat162float(__float2bfloat16(z)));
-        if (z_act_lo) { const float a = lrelu(z, alpha); z_act_lo[idx] = __float2bfloat16(a - __bfloat162float(__float2bfloat16(a))); }
+        if (z_raw) z_raw[idx] = op16::from_f32(z, f16);
+        if (z_act) z_act[idx] = op16::from_f32(lrelu(z, alpha), f16);
+        if (z_raw_lo) z_raw_lo[idx] = op16::from_f32(z - op16::round(z, f16), f16);
+        if (z_act_lo) { const float a = lrelu(z, alpha); z_act_lo[idx] = op16::from_f32(a - op16::round(a, f16), f16); }
     }
     lq = warp_sum(lq);
     lp = warp_sum(lp);
@@ -122,10 +119,10 @@ __global__ void sample_z_flow_kernel(const float* __restrict__ mu, const float* 
                                      const float* __restrict__ eps, int S, int s0, int B, int d, float min_logstd,
                                      int truncated, const float* __restrict__ flow_w, const float* __restrict__ flow_uhat,
                                      const float* __restrict__ flow_b, const float* __restrict__ flow_wu, int nf,
-                                     float* __restrict__ z_f32, __nv_bfloat16* __restrict__ z_raw,
-                                     __nv_bfloat16* __restrict__ z_act, long long zstride, int zc, int cpad,
+                                     float* __restrict__ z_f32, uint16_t* __restrict__ z_raw,
+                                     uint16_t* __restrict__ z_act, long long zstride, int zc, int cpad,
                                      float alpha, float* __restrict__ log_q, float* __restrict__ log_pn,
-                                     __nv_bfloat16* __restrict__ z_raw_lo, __nv_bfloat16* __restrict__ z_act_lo) {
+                                     uint16_t* __restrict__ z_raw_lo, uint16_t* __restrict__ z_act_lo, int f16) {
     const int lane = threadIdx.x & 31;
     const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (s >= S) return;
@@ -173,10 +170,10 @@ __global__ void sample_z_flow_kernel(const float* __restrict__ mu, const float* 
             lp += -0.5f * kLog2Pi - 0.5f * v * v;
             if (z_f32) z_f32[(size_t)s * d + j] = v;
             const size_t idx = (size_t)s * zstride + (size_t)(j / zc) * cpad + (j % zc);
-            if (z_raw) z_raw[idx] = __float2bfloat16(v);
-            if (z_act) z_act[idx] = __float2bfloat16(lrelu(v, alpha));
-            if (z_raw_lo) z_raw_lo[idx] = __float2bfloat16(v - __bfloat162float(__float2bfloat16(v)));
-            if (z_act_lo) { const float a = lrelu(v, alpha); z_act_lo[idx] = __float2bfloat16(a - __bfloat162float(__float2bfloat16(a))); }
+            if (z_raw) z_raw[idx] = op16::from_f32(v, f16);
+            if (z_act) z_act[idx] = op16::from_f32(lrelu(v, alpha), f16);
+            if (z_raw_lo) z_raw_lo[idx] = op16::from_f32(v - op16::round(v, f16), f16);
+            if (z_act_lo) { const float a = lrelu(v, alpha); z_act_lo[idx] = op16::from_f32(a - op16::round(a, f16), f16); }
         }
     }
     lq = warp_sum(lq);
@@ -187,42 +184,43 @@ __global__ void sample_z_flow_kernel(const float* __restrict__ mu, const float* 
     }
 }
 
-// one block per sample
+// one block per sample: the unfused likelihood over the fp32 heads (kept for head layouts the fused heads kernel does not run)
 __global__ void pixel_logprob_kernel(const float* __restrict__ head, int ld, const float* __restrict__ x,
-                                     int S, int s0, int B, int HW, int C, int bernoulli, int uniform_scale,
-                                     float beta, float min_log_scale, float* __restrict__ log_px) {
+                                     int S, int s0, int B, int HW, int C, const LikelihoodSpec spec, int uniform_scale,
+                                     float beta, float* __restrict__ log_px, float* __restrict__ sq_err) {
     const int s = blockIdx.x;
     const int b = (s0 + s) % B;
     const int n_x = HW * C;
-    const float bin = 2.0f / 256.0f, half_bin = 1.0f / 256.0f;
-    const float min_val = -1.0f + 1.0f / 256.0f, max_val = 1.0f - 1.0f / 256.0f;
-    const float log_bin = logf(bin);
-    float acc = 0.f;
+    float acc = 0.f, se = 0.f;
     for (int i = threadIdx.x; i < n_x; i += blockDim.x) {
         const int p = i / C, c = i - p * C;
         const float* row = head + ((size_t)s * HW + p) * ld;
         const float xv = x[(size_t)b * n_x + i];
         const float mean = row[c];
-        float lp;
-        if (bernoulli) {
-            const float pm = fminf(fmaxf(mean, 1e-7f), 1.0f - 1e-7f);
-            const float logits = logf(pm) - log1pf(-pm);
-            lp = xv * logits - softplusf(logits);
-        } else {
-            const float ls = fmaxf(uniform_scale ? beta : row[C + c], min_log_scale);
-            const float inv = expf(-ls);
-            const float hd = half_bin * inv;
-            const float xm = (xv - mean) * inv;
-            const float lo = xm - hd, hi = xm + hd;
-            const float delta = sigmoidf_(hi) - sigmoidf_(lo);
-            lp = delta > 1e-10f ? logf(fmaxf(delta, 1e-12f)) : xm + (log_bin - ls) - 2.f * softplusf(xm);
-            if (xv < min_val + half_bin) lp = -softplusf(-hi);
-            if (xv >= max_val - half_bin) lp = -softplusf(lo);
-        }
-        acc += lp;
+        const float ls = (spec.bernoulli || uniform_scale) ? beta : row[C + c];
+        acc += element_log_prob(spec, xv, mean, ls);
+        se += element_sq_err(spec.bernoulli, xv, mean);
     }
     acc = block_sum(acc);
-    if (threadIdx.x == 0) log_px[s] = acc;
+    se = block_sum(se);
+    if (threadIdx.x == 0) { log_px[s] = acc; if (sq_err) sq_err[s] = se; }
+}
+
+// Stand-alone log_prob of the two likelihood families on plain arrays (apvae_discretized_logistic_log_prob /
+// apvae_bernoulli_log_prob): out[r] = sum over `group` consecutive elements; one warp per row.
+__global__ void elementwise_logprob_kernel(const float* __restrict__ x, const float* __restrict__ mean,
+                                           const float* __restrict__ log_scale, long long rows, long long group,
+                                           const LikelihoodSpec spec, float* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long long r = blockIdx.x * (long long)(blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (r >= rows) return;
+    float acc = 0.f;
+    for (long long j = lane; j < group; j += 32) {
+        const long long i = r * group + j;
+        acc += element_log_prob(spec, x[i], mean[i], log_scale ? log_scale[i] : 0.f);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) out[r] = acc;
 }
 
 __global__ void rowdot_kernel(const float* __restrict__ h, int ld, const float* __restrict__ w,
@@ -238,14 +236,17 @@ __global__ void rowdot_kernel(const float* __restrict__ h, int ld, const float* 
 
 // one block per image
 __global__ void is_reduce_kernel(const float* __restrict__ log_px, const float* __restrict__ log_q,
-                                 const float* __restrict__ log_pn, const float* __restrict__ d_g, int K, int B,
+                                 const float* __restrict__ log_pn, const float* __restrict__ d_g,
+                                 const float* __restrict__ sq_err, int K, int B,
                                  int d, float w_xi, float log_Z, float* __restrict__ per_image) {
     const int b = blockIdx.x;
     const float lz = fmaxf(log_Z, -20.f);
     float m_p = -INFINITY, m_a = -INFINITY, m_z = -INFINITY;
     float s_p = 0.f, s_a = 0.f, s_px = 0.f, s_dg = 0.f;
+    float min_se = INFINITY;
     for (int k = threadIdx.x; k < K; k += blockDim.x) {
         const size_t s = (size_t)k * B + b;
+        if (sq_err) min_se = fminf(min_se, sq_err[s]);
         const float lpx = log_px[s], lq = log_q[s], lpn = log_pn[s], dg = d_g[s];
         const float half_z2 = -lpn - 0.5f * d * kLog2Pi;
         const float energy = w_xi * dg + half_z2;
@@ -255,6 +256,7 @@ __global__ void is_reduce_kernel(const float* __restrict__ log_px, const float* 
         s_p += lp;  s_a += la;  s_px += lpx;  s_dg += dg;
     }
     m_p = block_max(m_p);  m_a = block_max(m_a);  m_z = block_max(m_z);
+    min_se = -block_max(-min_se);
     float e_p = 0.f, e_a = 0.f, e_z = 0.f;
     for (int k = threadIdx.x; k < K; k += blockDim.x) {
         const size_t s = (size_t)k * B + b;
@@ -277,6 +279,7 @@ __global__ void is_reduce_kernel(const float* __restrict__ log_px, const float* 
         per_image[ROW_DG * B + b] = s_dg * invK;
         per_image[ROW_LZ_MAX * B + b] = m_z;
         per_image[ROW_LZ_SUM * B + b] = e_z;
+        per_image[ROW_MSE * B + b] = sq_err ? min_se : 0.f;      // test_mse: min over the K samples (dmm_cifar10.py:892)
     }
 }
 
@@ -356,9 +359,7 @@ __global__ void fill_uniform_kernel(float* __restrict__ out, long long n, unsign
 // one warp per chain
 __global__ void mala_propose_kernel(const float* __restrict__ z, const float* __restrict__ g,
                                     const float* __restrict__ eps, int n, int d, float alpha,
-                                    float* __restrict__ zp, __nv_bfloat16* __restrict__ zp_raw,
-                                    __nv_bfloat16* __restrict__ zp_act, long long zstride, int zc, int cpad,
-                                    float lrelu_alpha) {
+                                    float* __restrict__ zp) {
     const int lane = threadIdx.x & 31;
     const int s = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (s >= n) return;
@@ -367,9 +368,6 @@ __global__ void mala_propose_kernel(const float* __restrict__ z, const float* __
         const size_t i = (size_t)s * d + j;
         const float v = z[i] - alpha * g[i] + sc * eps[i];
         zp[i] = v;
-        const size_t idx = (size_t)s * zstride + (size_t)(j / zc) * cpad + (j % zc);
-        if (zp_raw) zp_raw[idx] = __float2bfloat16(v);
-        if (zp_act) zp_act[idx] = __float2bfloat16(lrelu(v, lrelu_alpha));
     }
 }
 
@@ -428,7 +426,7 @@ __global__ void energy_combine_kernel(const float* __restrict__ d_g, const float
 }
 
 __global__ void tanh_backward_pack_kernel(const float* __restrict__ g, const float* __restrict__ head, int ld,
-                                          long long pixels, int C, int cp, __nv_bfloat16* __restrict__ out) {
+                                          long long pixels, int C, int cp, uint16_t* __restrict__ out, int f16) {
     const long long total = pixels * cp;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
          i += (long long)gridDim.x * blockDim.x) {
@@ -439,7 +437,7 @@ __global__ void tanh_backward_pack_kernel(const float* __restrict__ g, const flo
             const float t = head[p * ld + c];
             v = g[p * C + c] * (1.f - t * t);
         }
-        out[i] = __float2bfloat16(v);
+        out[i] = op16::from_f32(v, f16);
     }
 }
 
@@ -493,18 +491,20 @@ __global__ void gather_cols_kernel(const float* __restrict__ src, int ld, int co
     }
 }
 
-// One block.  accum (double[kAccumSlots]): [r] += sum_b per_image[r][b] for the additive rows;
-// slots ROW_LZ_MAX / ROW_LZ_SUM hold a running (max, sum exp) over BATCHES of
+// One block.  accum (double[kAccumSlots]): [r] += sum_b per_image[r][b] for the additive rows (ROW_MSE goes to
+// slot ACC_MSE); slots ROW_LZ_MAX / ROW_LZ_SUM hold a running (max, sum exp) over BATCHES of
 // lz_b = log-mean-exp over the batch's [K,B] elements (dmm_cifar10.py:922-924,1221-1222);
-// slot 9 += B (weight), slot 10 += 1 (batches).
+// slot 9 += B (weight), slot 10 += 1 (batches).  `prior` (4 floats: pn_energy, pd_energy, kl_adv_and_gaussian,
+// log_Z_compute_op of this batch's prior branch, or null): slots 12..15 += B * value — the Evaluator weights every
+// batch scalar by the batch size (trainer/evaluator.py:249-254).
 __global__ void accumulate_metrics_kernel(const float* __restrict__ per_image, int B, int K, int rows,
-                                          double* __restrict__ accum) {
+                                          const float* __restrict__ prior, double* __restrict__ accum) {
     for (int r = 0; r < rows; ++r) {
         if (r == ROW_LZ_MAX || r == ROW_LZ_SUM) continue;
         float acc = 0.f;
         for (int b = threadIdx.x; b < B; b += blockDim.x) acc += per_image[(size_t)r * B + b];
         acc = block_sum(acc);
-        if (threadIdx.x == 0) accum[r] += (double)acc;
+        if (threadIdx.x == 0) accum[r == ROW_MSE ? ACC_MSE : r] += (double)acc;
     }
     float mx = -INFINITY;
     for (int b = threadIdx.x; b < B; b += blockDim.x) mx = fmaxf(mx, per_image[(size_t)ROW_LZ_MAX * B + b]);
@@ -515,7 +515,7 @@ __global__ void accumulate_metrics_kernel(const float* __restrict__ per_image, i
     sm = block_sum(sm);
     if (threadIdx.x == 0) {
         const double lz_b = (double)mx + log((double)sm / ((double)K * (double)B));
-        const double nb = accum[10];
+        const double nb = accum[ACC_BATCHES];
         if (nb == 0.0) {
             accum[ROW_LZ_MAX] = lz_b;
             accum[ROW_LZ_SUM] = 1.0;
@@ -524,8 +524,46 @@ __global__ void accumulate_metrics_kernel(const float* __restrict__ per_image, i
             accum[ROW_LZ_SUM] = accum[ROW_LZ_SUM] * exp(m0 - m1) + exp(lz_b - m1);
             accum[ROW_LZ_MAX] = m1;
         }
-        accum[9] += (double)B;
-        accum[10] = nb + 1.0;
+        accum[ACC_WEIGHT] += (double)B;
+        accum[ACC_BATCHES] = nb + 1.0;
+        if (prior) {
+            for (int i = 0; i < 4; ++i) accum[ACC_PN + i] += (double)B * (double)prior[i];
+            accum[ACC_PRIOR_WEIGHT] += (double)B;
+        }
+    }
+}
+
+// The test_pn_net branch's batch scalars from Kp prior draws (dmm_cifar10.py:883,915-927), one block:
+//   out[0] pn_energy = mean D(G(z));  out[1] pd_energy = mean[D(G(z)) exp(log_energy_prob - log p_N(z))];
+//   out[2] kl_adv_and_gaussian = mean[log p_N(z) - log_energy_prob];  out[3] log_Z_compute_op = log-mean-exp(-energy - log p_N(z))
+// with energy = w_xi D + |z|^2 / 2 and log_energy_prob = -energy - max(log_Z, -20) (:164-177), fp32 like the reference.
+__global__ void prior_reduce_kernel(const float* __restrict__ d_g, const float* __restrict__ log_pn, int Kp, int d,
+                                    float w_xi, float log_Z, float* __restrict__ out) {
+    const float lz = fmaxf(log_Z, -20.f);
+    float s_pn = 0.f, s_pd = 0.f, s_kl = 0.f, mx = -INFINITY;
+    for (int k = threadIdx.x; k < Kp; k += blockDim.x) {
+        const float dg = d_g[k], lpn = log_pn[k];
+        const float energy = w_xi * dg + (-lpn - 0.5f * d * kLog2Pi);
+        const float lep = -energy - lz;
+        s_pn += dg;
+        s_pd += dg * expf(lep - lpn);
+        s_kl += lpn - lep;
+        mx = fmaxf(mx, -energy - lpn);
+    }
+    mx = block_max(mx);
+    float se = 0.f;
+    for (int k = threadIdx.x; k < Kp; k += blockDim.x) {
+        const float dg = d_g[k], lpn = log_pn[k];
+        const float energy = w_xi * dg + (-lpn - 0.5f * d * kLog2Pi);
+        se += expf(-energy - lpn - mx);
+    }
+    s_pn = block_sum(s_pn);  s_pd = block_sum(s_pd);  s_kl = block_sum(s_kl);  se = block_sum(se);
+    if (threadIdx.x == 0) {
+        const float inv = 1.f / Kp;
+        out[0] = s_pn * inv;
+        out[1] = s_pd * inv;
+        out[2] = s_kl * inv;
+        out[3] = mx + logf(se * inv);
     }
 }
 
@@ -539,36 +577,36 @@ inline cudaStream_t st(void* s) { return static_cast<cudaStream_t>(s); }
 }  // namespace
 
 int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out_raw, void* out_act,
-                      float alpha, void* stream, void* raw_lo, void* act_lo) {
+                      float alpha, int f16, void* stream, void* raw_lo, void* act_lo) {
     if (pixels <= 0) return 0;
     pack_image_kernel<<<grid_for(pixels * cp, 256), 256, 0, st(stream)>>>(
-        x, pixels, c, cp, (__nv_bfloat16*)out_raw, (__nv_bfloat16*)out_act, alpha, (__nv_bfloat16*)raw_lo, (__nv_bfloat16*)act_lo);
+        x, pixels, c, cp, (uint16_t*)out_raw, (uint16_t*)out_act, alpha, (uint16_t*)raw_lo, (uint16_t*)act_lo, f16);
     return (int)cudaGetLastError();
 }
 
 int launch_sample_z(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
                     float min_logstd, int truncated, float* z_f32, void* z_raw, void* z_act,
                     long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn,
-                    void* stream, void* z_raw_lo, void* z_act_lo) {
+                    int f16, void* stream, void* z_raw_lo, void* z_act_lo) {
     if (S <= 0) return 0;
     sample_z_kernel<<<(S + 7) / 8, 256, 0, st(stream)>>>(mu, logstd, eps, S, s0, B, d, min_logstd, truncated,
-                                                        z_f32, (__nv_bfloat16*)z_raw, (__nv_bfloat16*)z_act,
+                                                        z_f32, (uint16_t*)z_raw, (uint16_t*)z_act,
                                                         zstride, zc, cpad, alpha, log_q, log_pn,
-                                                        (__nv_bfloat16*)z_raw_lo, (__nv_bfloat16*)z_act_lo);
+                                                        (uint16_t*)z_raw_lo, (uint16_t*)z_act_lo, f16);
     return (int)cudaGetLastError();
 }
 
 int launch_sample_z_flow(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
                          float min_logstd, int truncated, const float* flow_w, const float* flow_uhat,
                          const float* flow_b, const float* flow_wu, int nf, float* z_f32, void* z_raw, void* z_act,
-                         long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn, void* stream,
+                         long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn, int f16, void* stream,
                          void* z_raw_lo, void* z_act_lo) {
     if (S <= 0) return 0;
     if (d > 512 || !mu || !logstd) return (int)cudaErrorInvalidValue;
 #define APVAE_FLOW_LAUNCH(PL) \
     sample_z_flow_kernel<PL><<<(S + 7) / 8, 256, 0, st(stream)>>>(mu, logstd, eps, S, s0, B, d, min_logstd, truncated, \
-        flow_w, flow_uhat, flow_b, flow_wu, nf, z_f32, (__nv_bfloat16*)z_raw, (__nv_bfloat16*)z_act, zstride, zc, cpad, \
-        alpha, log_q, log_pn, (__nv_bfloat16*)z_raw_lo, (__nv_bfloat16*)z_act_lo)
+        flow_w, flow_uhat, flow_b, flow_wu, nf, z_f32, (uint16_t*)z_raw, (uint16_t*)z_act, zstride, zc, cpad, \
+        alpha, log_q, log_pn, (uint16_t*)z_raw_lo, (uint16_t*)z_act_lo, f16)
     if (d <= 32) APVAE_FLOW_LAUNCH(1);
     else if (d <= 64) APVAE_FLOW_LAUNCH(2);
     else if (d <= 128) APVAE_FLOW_LAUNCH(4);
@@ -579,11 +617,17 @@ int launch_sample_z_flow(const float* mu, const float* logstd, const float* eps,
 }
 
 int launch_pixel_logprob(const float* head, int ld, const float* x, int S, int s0, int B, int HW, int C,
-                         int bernoulli, int uniform_scale, float beta, float min_log_scale,
-                         float* log_px, void* stream) {
+                         const LikelihoodSpec& spec, int uniform_scale, float beta, float* log_px, float* sq_err,
+                         void* stream) {
     if (S <= 0) return 0;
-    pixel_logprob_kernel<<<S, 256, 0, st(stream)>>>(head, ld, x, S, s0, B, HW, C, bernoulli, uniform_scale, beta,
-                                                   min_log_scale, log_px);
+    pixel_logprob_kernel<<<S, 256, 0, st(stream)>>>(head, ld, x, S, s0, B, HW, C, spec, uniform_scale, beta, log_px, sq_err);
+    return (int)cudaGetLastError();
+}
+
+int launch_elementwise_logprob(const float* x, const float* mean, const float* log_scale, long long rows, long long group,
+                               const LikelihoodSpec& spec, float* out, void* stream) {
+    if (rows <= 0 || group <= 0) return 0;
+    elementwise_logprob_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st(stream)>>>(x, mean, log_scale, rows, group, spec, out);
     return (int)cudaGetLastError();
 }
 
@@ -595,10 +639,10 @@ int launch_rowdot(const float* h, int ld, const float* w, const float* b, int n,
 }
 
 int launch_is_reduce(const float* log_px, const float* log_q, const float* log_pn, const float* d_g,
-                     const float* /*z_f32*/, int K, int B, int d, float w_xi, float log_Z, float* per_image,
+                     const float* sq_err, int K, int B, int d, float w_xi, float log_Z, float* per_image,
                      void* stream) {
     if (B <= 0) return 0;
-    is_reduce_kernel<<<B, 256, 0, st(stream)>>>(log_px, log_q, log_pn, d_g, K, B, d, w_xi, log_Z, per_image);
+    is_reduce_kernel<<<B, 256, 0, st(stream)>>>(log_px, log_q, log_pn, d_g, sq_err, K, B, d, w_xi, log_Z, per_image);
     return (int)cudaGetLastError();
 }
 
@@ -616,12 +660,9 @@ int launch_fill_uniform(float* out, long long n, unsigned long long seed, unsign
 }
 
 int launch_mala_propose(const float* z, const float* g, const float* eps, int n, int d, float alpha,
-                        float* z_prime, void* zp_raw, void* zp_act, long long zstride, int zc, int cpad,
-                        float lrelu_alpha, void* stream) {
+                        float* z_prime, void* stream) {
     if (n <= 0) return 0;
-    mala_propose_kernel<<<(n + 7) / 8, 256, 0, st(stream)>>>(z, g, eps, n, d, alpha, z_prime,
-                                                            (__nv_bfloat16*)zp_raw, (__nv_bfloat16*)zp_act,
-                                                            zstride, zc, cpad, lrelu_alpha);
+    mala_propose_kernel<<<(n + 7) / 8, 256, 0, st(stream)>>>(z, g, eps, n, d, alpha, z_prime);
     return (int)cudaGetLastError();
 }
 int launch_mala_accept(float* z, float* e, float* g, float* pure, const float* z_prime, const float* e_prime,
@@ -639,10 +680,10 @@ int launch_energy_combine(const float* d_g, const float* gz, const float* z, int
     return (int)cudaGetLastError();
 }
 int launch_tanh_backward_pack(const float* g, const float* head, int ld, long long pixels, int C, int cp,
-                              void* out_bf16, void* stream) {
+                              void* out_bf16, int f16, void* stream) {
     if (pixels <= 0) return 0;
     tanh_backward_pack_kernel<<<grid_for(pixels * cp, 256), 256, 0, st(stream)>>>(g, head, ld, pixels, C, cp,
-                                                                               (__nv_bfloat16*)out_bf16);
+                                                                               (uint16_t*)out_bf16, f16);
     return (int)cudaGetLastError();
 }
 int launch_row_sqnorm(const float* v, long long len, int rows, float* out, void* stream) {
@@ -655,9 +696,14 @@ int launch_quantize_images(const float* head, int ld, long long pixels, int C, u
     quantize_kernel<<<grid_for(pixels * C, 256), 256, 0, st(stream)>>>(head, ld, pixels, C, out);
     return (int)cudaGetLastError();
 }
-int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, double* accum, void* stream) {
+int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, const float* prior, double* accum, void* stream) {
     if (B <= 0) return 0;
-    accumulate_metrics_kernel<<<1, 256, 0, st(stream)>>>(per_image, B, K, rows, accum);
+    accumulate_metrics_kernel<<<1, 256, 0, st(stream)>>>(per_image, B, K, rows, prior, accum);
+    return (int)cudaGetLastError();
+}
+int launch_prior_reduce(const float* d_g, const float* log_pn, int Kp, int d, float w_xi, float log_Z, float* out4, void* stream) {
+    if (Kp <= 0) return 0;
+    prior_reduce_kernel<<<1, 256, 0, st(stream)>>>(d_g, log_pn, Kp, d, w_xi, log_Z, out4);
     return (int)cudaGetLastError();
 }
 int launch_clip_min(float* v, long long n, float lo, void* stream) {

@@ -2,13 +2,15 @@
 // All pointers are device pointers; every launcher returns a cudaError_t value.
 #pragma once
 #include <stdint.h>
+#include "likelihood.cuh"
 
 namespace apvae {
 
 // x fp32 [pixels, c] -> bf16 [pixels, cp] raw and leaky_relu(x) (cp = 16 k, zero padded).
 // raw_lo / act_lo: optional low halves (v - bf16(v)) for the split-precision mode.
+// f16: 16-bit format of the outputs (op16.h), here and in every launcher below that writes operand tensors.
 int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out_raw, void* out_act,
-                      float alpha, void* stream, void* raw_lo = nullptr, void* act_lo = nullptr);
+                      float alpha, int f16, void* stream, void* raw_lo = nullptr, void* act_lo = nullptr);
 
 // Reparameterised draw + log q(z|x) + log N(z;0,I)   (reference: zd.Normal sample/log_prob via
 // tfsnippet/distributions/wrapper.py:112,127-129; truncated_normal.py:142-149; dmm_cifar10.py:449-450,601-603)
@@ -20,23 +22,28 @@ int launch_pack_image(const float* x, long long pixels, int c, int cp, void* out
 int launch_sample_z(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
                     float min_logstd, int truncated, float* z_f32, void* z_raw, void* z_act,
                     long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn,
-                    void* stream, void* z_raw_lo = nullptr, void* z_act_lo = nullptr);
+                    int f16, void* stream, void* z_raw_lo = nullptr, void* z_act_lo = nullptr);
 // The same draw pushed through `nf` planar normalizing-flow layers (reference: layers/flows/planar_nf.py:108-135,
 // distributions/flow.py:118-150): z <- z + u_hat tanh(w.z + b), log q = log q0(z0) - sum_l log|1 + (1 - tanh^2) w.u_hat|.
 // flow_w / flow_uhat: [nf][d]; flow_b / flow_wu: [nf].  d <= 512.
 int launch_sample_z_flow(const float* mu, const float* logstd, const float* eps, int S, int s0, int B, int d,
                          float min_logstd, int truncated, const float* flow_w, const float* flow_uhat,
                          const float* flow_b, const float* flow_wu, int nf, float* z_f32, void* z_raw, void* z_act,
-                         long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn, void* stream,
+                         long long zstride, int zc, int cpad, float alpha, float* log_q, float* log_pn, int f16, void* stream,
                          void* z_raw_lo = nullptr, void* z_act_lo = nullptr);
 
-// log p(x|z) summed over pixels (reference: distributions/discretized.py:198-259 with the
-// dmm_cifar10.py:612-619 parameters; Bernoulli variant dmm_bernouli_fashion.py:619-626).
+// log p(x|z) summed over pixels from the fp32 heads (reference: distributions/discretized.py:198-259 with the
+// dmm_cifar10.py:612-619 parameters; Bernoulli variant dmm_bernouli_fashion.py:619-626).  The hot path computes this
+// inside the heads kernel (HeadsParams::lik_*); this pass remains for head layouts that kernel does not run.
 //   head fp32 [S*HW, ld]: columns [0,C) = x_mean, [C,2C) = x_logstd (unless uniform_scale / bernoulli)
-//   x fp32 [B, HW*C]; local sample s scores image b = (s0 + s) % B.
+//   x fp32 [B, HW*C]; local sample s scores image b = (s0 + s) % B.  sq_err (may be null): test_mse's per-sample sum.
 int launch_pixel_logprob(const float* head, int ld, const float* x, int S, int s0, int B, int HW, int C,
-                         int bernoulli, int uniform_scale, float beta, float min_log_scale,
-                         float* log_px, void* stream);
+                         const LikelihoodSpec& spec, int uniform_scale, float beta, float* log_px, float* sq_err,
+                         void* stream);
+// The likelihood families on plain arrays: out[r] = sum_{j < group} log p(x[r*group + j] | mean, log_scale) (log_scale may
+// be null for the Bernoulli).
+int launch_elementwise_logprob(const float* x, const float* mean, const float* log_scale, long long rows, long long group,
+                               const LikelihoodSpec& spec, float* out, void* stream);
 
 // out[s] = dot(h[s, 0:n], w) + b     (D_psi's level_-1 dense, dmm_cifar10.py:561)
 int launch_rowdot(const float* h, int ld, const float* w, const float* b, int n, long long S, float* out,
@@ -54,16 +61,23 @@ enum PerImageRow {
     ROW_DG = 5,        // mean_k D(G(z))
     ROW_LZ_MAX = 6,    // max_k (-energy - log q)
     ROW_LZ_SUM = 7,    // sum_k exp(-energy - log q - max)
-    kPerImageRows = 8
+    ROW_REAL_E = 8,    // D_psi(x_origin): written by the caller, not by is_reduce
+    ROW_MSE = 9,       // min_k sum_pixels (round(x_mean 128 + 127.5) - round(x 128 + 127.5))^2 (test_mse, dmm_cifar10.py:889-892)
+    kPerImageRows = 10
 };
+// sq_err [K*B] (may be null -> ROW_MSE = 0): per-sample squared error of the rounded pixels
 int launch_is_reduce(const float* log_px, const float* log_q, const float* log_pn, const float* d_g,
-                     const float* z_f32, int K, int B, int d, float w_xi, float log_Z, float* per_image,
+                     const float* sq_err, int K, int B, int d, float w_xi, float log_Z, float* per_image,
                      void* stream);
 
 // Shard-local accumulation of the Evaluator metrics (replaces the host np.average of
 // trainer/evaluator.py:249-254 and the host logsumexp of dmm_cifar10.py:1221-1222); see elementwise.cu.
-constexpr int kAccumSlots = 16;
-int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, double* accum, void* stream);
+constexpr int kAccumSlots = 20;
+enum AccumSlot { ACC_WEIGHT = 9, ACC_BATCHES = 10, ACC_MSE = 11, ACC_PN = 12, ACC_PD = 13, ACC_KL = 14, ACC_LOGZ_OP = 15,
+                 ACC_PRIOR_WEIGHT = 16 };
+int launch_accumulate_metrics(const float* per_image, int B, int K, int rows, const float* prior4, double* accum, void* stream);
+// test_pn_net branch scalars from Kp prior draws: out4 = {pn_energy, pd_energy, kl_adv_and_gaussian, log_Z_compute_op}
+int launch_prior_reduce(const float* d_g, const float* log_pn, int Kp, int d, float w_xi, float log_Z, float* out4, void* stream);
 
 // Philox4x32-10 + Box-Muller standard normals (timed runs; parity runs feed eps).
 // truncated != 0: resample into [-2, 2] (tf.truncated_normal, truncated_normal.py:103).
@@ -76,8 +90,7 @@ int launch_fill_uniform(float* out, long long n, unsigned long long seed, unsign
 //   propose : z' = z - alpha g + sqrt(2 alpha) eps  (fp32 + bf16 decoder-input copies)
 //   accept  : ratio, u < ratio select, history rows
 int launch_mala_propose(const float* z, const float* g, const float* eps, int n, int d, float alpha,
-                        float* z_prime, void* zp_raw, void* zp_act, long long zstride, int zc, int cpad,
-                        float lrelu_alpha, void* stream);
+                        float* z_prime, void* stream);
 int launch_mala_accept(float* z, float* e, float* g, float* pure, const float* z_prime, const float* e_prime,
                        const float* g_prime, const float* pure_prime, const float* u, int n, int d,
                        float alpha, float* hist_e, float* hist_pure, float* hist_ratio, void* stream);
@@ -89,7 +102,7 @@ int launch_energy_combine(const float* d_g, const float* gz, const float* z, int
 // Backward through x_mean = tanh(pre): out[p, c] = g[p, c] * (1 - head[p*ld + c]^2) as bf16 [pixels, cp], zero padded
 // (head holds the fp32 tanh OUTPUT; g is the fp32 gradient w.r.t. x_mean, [pixels, C]).
 int launch_tanh_backward_pack(const float* g, const float* head, int ld, long long pixels, int C, int cp,
-                              void* out_bf16, void* stream);
+                              void* out_bf16, int f16, void* stream);
 
 // out[r] = sum_j v[r, j]^2 over `len` contiguous floats per row (ele_grad_norm, evaluation/dmm_cifar.py:958-959)
 int launch_row_sqnorm(const float* v, long long len, int rows, float* out, void* stream);
@@ -121,10 +134,20 @@ struct HeadsParams {
     void* raw;  void* act;  void* raw_lo;  void* act_lo;   // bf16 [pixels, ldo], columns < tanh_cols, rest zero
     int ldo;
     float alpha;
+    int f16;                              // operand format of `in` and of the 16-bit outputs (op16.h)
+    // fused likelihood (set per call; lik_part == null: off): pixel p of local sample s scores x[(lik_s0 + s) % lik_B]
+    const float* lik_x;                   // fp32 [lik_B, pixels_per_image * C]
+    float* lik_part;                      // [samples * tiles_per_image][2]: per-tile sums of log p and of the squared pixel error
+    int lik_s0, lik_B, lik_has_std;       // lik_has_std: columns [C, 2C) are x_logstd; else log_scale = lik_beta
+    float lik_beta;
+    LikelihoodSpec lik;
     float bias[8];
     float w[kHeadsMaxW];                  // [cin][nout]
 };
-int launch_pixel_heads(const HeadsParams& p, long long pixels, void* stream);
+int launch_pixel_heads(const HeadsParams& p, int n_images, void* stream);
+int heads_tiles_per_image(long long pixels_per_image);
+// log_px[s] / sq_err[s] = sum of the sample's tiles_per_image partial sums written by the fused heads kernel
+int launch_sum_tiles(const float* part, int tpi, int n, float* log_px, float* sq_err, void* stream);
 
 
 // A whole resnet_conv2d_block (resnet.py:272-364) with <= 3 input channels on the CUDA cores: D_psi/level_0 of the
@@ -139,6 +162,7 @@ struct SmallBlockParams {
     void* out_raw;  void* out_act;        // bf16 [N, H, W, ldo]: padding channels zero (either may be null)
     int H, W, cp_in, cin, cout, ldo, k;
     float alpha;
+    int f16;                              // operand format (op16.h)
     float b0[kSmallBlockMaxCin];
     float b1[kSmallBlockMaxCout];         // conv_1 bias + shortcut bias
     float w0[kSmallBlockMaxK * kSmallBlockMaxK * kSmallBlockMaxCin * kSmallBlockMaxCin];      // [k][k][cin][cin]
@@ -166,6 +190,7 @@ struct TinyConvParams {
     const void* res;  int res_mode, ld_res;                              // bf16, RES_SAME: [N,H,W,ld_res]; RES_EVEN: [N,H/2,W/2,ld_res]
     const void* mask;  int ld_mask;                                      // bf16 [N, H, W, ld_mask]
     float alpha;
+    int f16;                                                             // operand format (op16.h)
 };
 int launch_tiny_conv(const TinyConvParams& p, int n, void* stream);
 

@@ -4,6 +4,7 @@
 #include <stdlib.h>
 #include <string.h>
 #include "kernels.h"
+#include "op16.h"
 
 namespace apvae {
 
@@ -12,7 +13,7 @@ Model::~Model() {
     for (float* p : {mz, mzp, mg, mgp, me, mep, mp, mpp, meps, mu})
         if (p) cudaFree(p);
     for (void* p : allocs) cudaFree(p);
-    for (float* p : {eps_buf, log_px, log_q, log_pn, d_g})
+    for (float* p : {eps_buf, log_px, log_q, log_pn, d_g, sq_err})
         if (p) cudaFree(p);
 }
 
@@ -49,9 +50,14 @@ const HostArr* Model::W_(const std::string& name, std::initializer_list<int64_t>
     return &it->second;
 }
 
-bool Model::add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms,
-                   const std::vector<const void*>& srcs, const Epilogue& epi, int cap, double* macs) {
+bool Model::add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms_in,
+                   const std::vector<const void*>& srcs, const Epilogue& epi_in, int cap, double* macs) {
     std::string perr;
+    // every op of a handle packs its kernels and writes its 16-bit outputs in the handle's operand format
+    std::vector<TermSpec> terms = terms_in;
+    for (TermSpec& t : terms) t.f16 = f16();
+    Epilogue epi = epi_in;
+    epi.f16 = f16();
     std::unique_ptr<DevOp> op(new DevOp());
     op->name = name;
     // <= 4 -> <= 4 channels, stride 1 (the first conv on the image channels and its adjoint): CUDA cores (tinyconv.cu);
@@ -87,6 +93,7 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
             tc.res = epi.res; tc.res_mode = epi.res ? epi.res_mode : RES_NONE; tc.ld_res = epi.ld_res;
             tc.mask = epi.mask; tc.ld_mask = epi.ld_mask;
             tc.alpha = 0.2f;
+            tc.f16 = f16();
             op->macs_per_image = (double)t.k * t.k * t.cin * t.cout * t.in_h * t.in_w;
             if (macs) *macs += op->macs_per_image;
             prog.push_back(std::move(op));
@@ -179,14 +186,6 @@ static TermSpec term(int src, bool transpose, int k, int stride, int cin, int co
     return t;
 }
 
-static float bf16_round_host(float f) {
-    uint32_t u; memcpy(&u, &f, 4);
-    u += 0x7fffu + ((u >> 16) & 1u);
-    u &= 0xffff0000u;
-    float r; memcpy(&r, &u, 4);
-    return r;
-}
-
 bool Model::push_terms(std::vector<TermSpec>& terms, std::vector<const void*>& srcs, bool split, const Tensor& hi,
                        const Tensor& lo, bool transpose, int k, int stride, int cin, int cout, const std::string& wname,
                        const HostArr* kernel, const HostArr* bias) {
@@ -203,8 +202,8 @@ bool Model::push_terms(std::vector<TermSpec>& terms, std::vector<const void*>& s
         whi.shape = kernel->shape; wlo.shape = kernel->shape;
         whi.v.resize(kernel->v.size()); wlo.v.resize(kernel->v.size());
         for (size_t i = 0; i < kernel->v.size(); ++i) {
-            whi.v[i] = bf16_round_host(kernel->v[i]);
-            wlo.v[i] = bf16_round_host(kernel->v[i] - whi.v[i]);
+            whi.v[i] = op16::host_round(kernel->v[i], f16() != 0);
+            wlo.v[i] = op16::host_round(kernel->v[i] - whi.v[i], f16() != 0);
         }
     }
     terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, &whi, bias));
@@ -252,6 +251,7 @@ bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& 
         sb.in_raw = in.raw.ptr; sb.r_act = r.ptr; sb.out_raw = o.raw.ptr; sb.out_act = o.act.ptr;
         sb.H = H; sb.W = Wd; sb.cp_in = in.raw.cp; sb.cin = cin; sb.cout = cout; sb.ldo = pad16(cout); sb.k = k;
         sb.alpha = 0.2f;
+        sb.f16 = f16();
         for (int c = 0; c < cin; ++c) sb.b0[c] = b0->v[c];
         for (int c = 0; c < cout; ++c) sb.b1[c] = b1->v[c] + bs->v[c];
         // kernel template is instantiated on cin (weights packed [tap][cin][cout] with that cin)

@@ -78,14 +78,17 @@ public:
 
     // forward pieces (all on `stream`)
     bool run_encoder(const float* x_dev, int B, void* stream);                  // -> q_mu, q_logstd
-    bool run_decoder_chunk(int n, void* stream);                                // g_in -> head_f32, d_in
+    // g_in -> d_in (+ head_f32 when want_f32).  `lik`: also score the samples against x inside the heads kernel
+    // (log p(x|z) and the test_mse squared error, per sample) -> log_px_out / sq_err_out [n]
+    struct LikArgs { const float* x; int s0, B; float* log_px_out; float* sq_err_out; };
+    bool run_decoder_chunk(int n, void* stream, bool want_f32 = true, const LikArgs* lik = nullptr);
     bool run_critic_chunk(int n, float* d_out, void* stream);                   // d_in -> d_out[n]
     // energy E = w xi D(G(z)) + |z|^2 / 2, grad_z E and D(G(z)) for n <= max_chunk latents (fp32 [n, z_dim]);
     // any output may be null (get_sgld_proposal, dmm_cifar10.py:241-247)
     bool energy_grad_chunk(const float* z_dev, int n, float* energy, float* grad, float* pure, void* stream);
     // EnergyDistribution.sample's loop (dmm_cifar10.py:197-238)
     bool mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
-              float* hist_e, float* hist_pure, float* hist_ratio, void* stream);
+              float* hist_e, float* hist_pure, float* hist_ratio, float* hist_z, void* stream);
     bool latent_gan_chunk(const float* z_omega_dev, int n, float* z0_dev, void* stream);   // n <= max_chunk
     bool critic_of_images(const float* x_dev, int N, float* d_out, void* stream);
     // D_psi(x), dD/dx [N,H,W,C] and its squared norm per image (evaluation/dmm_cifar.py:958-959); outputs may be null
@@ -107,6 +110,7 @@ public:
     int z_group() const;
     int z_cpad() const;
     float w_xi() const;
+    int f16() const { return cfg.operand_bf16 ? 0 : 1; }   // 16-bit operand format of every tensor of this handle (op16.h)
 
     // device state
     Program q_prog, g_prog, d_prog;
@@ -132,6 +136,9 @@ public:
     float* flow_w = nullptr; float* flow_uhat = nullptr; float* flow_b = nullptr; float* flow_wu = nullptr;
     Pair g_in;                 // decoder input
     float* head_f32 = nullptr; // [max_chunk*HW, head_ld]
+    DevOp* heads_op = nullptr; // the CUDA-core heads op at the end of g_prog (null: the heads run as a GEMM op)
+    float* lik_part = nullptr; // [max_chunk * tiles_per_image][2] per-tile likelihood sums of the fused heads kernel
+    float* prior4 = nullptr;   // the prior branch's four batch scalars (apvae_prior_stats)
     Pair d_in;                 // [max_chunk, H, W, 16]
     float* d64 = nullptr;      // [max_chunk, 64]
     float* d_last_w = nullptr; // level_-1 kernel [64], bias [1]
@@ -142,7 +149,7 @@ public:
 
     // per-call sample buffers (grow-only)
     size_t sample_cap = 0;
-    float *eps_buf = nullptr, *log_px = nullptr, *log_q = nullptr, *log_pn = nullptr, *d_g = nullptr;
+    float *eps_buf = nullptr, *log_px = nullptr, *log_q = nullptr, *log_pn = nullptr, *d_g = nullptr, *sq_err = nullptr;
     float* z_tmp = nullptr;    // [max_chunk, z_dim] scratch
 
     std::vector<void*> allocs;

@@ -205,10 +205,14 @@ bool Model::build_g() {
         hp.raw = d_in.raw.ptr; hp.act = d_in.act.ptr; hp.raw_lo = d_in.raw_lo.ptr; hp.act_lo = d_in.act_lo.ptr;
         hp.ldo = d_in.raw.cp;
         hp.alpha = 0.2f;
+        hp.f16 = f16();
         for (int c = 0; c < nout; ++c) hp.bias[c] = bcat.v[c];
         for (int ci = 0; ci < cg; ++ci)
             for (int c = 0; c < nout; ++c) hp.w[ci * nout + c] = kcat.v[(size_t)ci * nout + c];
         macs_g += op->macs_per_image;
+        heads_op = op.get();
+        lik_part = alloc_f32((size_t)cap * heads_tiles_per_image(HW()) * 2);
+        if (!lik_part) return false;
         g_prog.push_back(std::move(op));
         split_mode = false;
         return true;
@@ -300,7 +304,7 @@ bool Model::latent_gan_chunk(const float* z_omega_dev, int n, float* z0_dev, voi
     if (om_prog.empty()) return fail("latent_gan: create the handle with latent_gan = 1");
     const int din = omega_in_dim();
     KCHECK(launch_sample_z(nullptr, nullptr, z_omega_dev, n, 0, 1, din, 0.f, 0, nullptr, om_in.ptr, nullptr, om_in.cp, din,
-                           om_in.cp, 0.2f, nullptr, nullptr, stream), "pack z_omega");
+                           om_in.cp, 0.2f, nullptr, nullptr, f16(), stream), "pack z_omega");
     if (!run_program(om_prog, n, stream)) return false;
     if (cfg.arch == APVAE_ARCH_M)      // the last dense layer's leaky_relu (dmm_bernouli_fashion.py:530-541)
         KCHECK(launch_leaky_relu_f32(om_out, (long long)n * cfg.z_dim, 0.2f, stream), "leaky_relu");
@@ -345,6 +349,14 @@ bool Model::build() {
     if (built) return fail("weights already loaded (create a new handle to reload)");
     if (cudaSetDevice(dev.device) != cudaSuccess) return fail("cudaSetDevice failed");
     if (!build_q() || !build_g() || !build_d()) return false;
+    // D_psi's first block as the fused CUDA-core block reads only the raw x_mean (it applies the activation itself):
+    // the heads kernel then skips the activated copy (32 B per pixel)
+    if (heads_op && !d_prog.empty() && d_prog[0]->is_small_block) {
+        heads_op->heads.act = nullptr;
+        if (!d_tape.empty()) d_tape[0].in.act = Tensor();      // the adjoint's leaky-relu' mask then reads the raw input (same signs)
+    }
+    prior4 = alloc_f32(4);
+    if (!prior4) return false;
     if (cfg.latent_gan && !build_omega()) return false;
     if (cfg.enable_grad && !build_grad()) return false;
     z_tmp = alloc_f32((size_t)cfg.max_chunk * cfg.z_dim);
@@ -356,13 +368,13 @@ bool Model::build() {
 
 bool Model::ensure_sample_buffers(size_t samples) {
     if (samples <= sample_cap) return true;
-    for (float** p : {&eps_buf, &log_px, &log_q, &log_pn, &d_g}) {
+    for (float** p : {&eps_buf, &log_px, &log_q, &log_pn, &d_g, &sq_err}) {
         if (*p) cudaFree(*p);
         *p = nullptr;
     }
     sample_cap = 0;
     if (cudaMalloc(&eps_buf, samples * cfg.z_dim * sizeof(float)) != cudaSuccess) return fail("cudaMalloc eps");
-    for (float** p : {&log_px, &log_q, &log_pn, &d_g})
+    for (float** p : {&log_px, &log_q, &log_pn, &d_g, &sq_err})
         if (cudaMalloc(p, samples * sizeof(float)) != cudaSuccess) return fail("cudaMalloc per-sample stats");
     sample_cap = samples;
     return true;
@@ -371,7 +383,7 @@ bool Model::ensure_sample_buffers(size_t samples) {
 
 bool Model::run_encoder(const float* x_dev, int B, void* stream) {
     if (B > cfg.max_batch) return fail("batch exceeds max_batch");
-    KCHECK(launch_pack_image(x_dev, (long long)B * HW(), C(), q_in.raw.cp, q_in.raw.ptr, q_in.act.ptr, 0.2f, stream),
+    KCHECK(launch_pack_image(x_dev, (long long)B * HW(), C(), q_in.raw.cp, q_in.raw.ptr, q_in.act.ptr, 0.2f, f16(), stream),
            "pack_image");
     if (!run_program(q_prog, B, stream)) return false;
     // maybe_clip_value(z_logstd, min_val=min_logstd_of_q)  (dmm_cifar10.py:449)
@@ -379,7 +391,29 @@ bool Model::run_encoder(const float* x_dev, int B, void* stream) {
     return true;
 }
 
-bool Model::run_decoder_chunk(int n, void* stream) { return run_program(g_prog, n, stream); }
+bool Model::run_decoder_chunk(int n, void* stream, bool want_f32, const LikArgs* lik) {
+    const LikelihoodSpec spec = script_likelihood(cfg.bernoulli, cfg.epsilon);
+    if (heads_op) {                               // per-call arguments of the fused heads kernel
+        HeadsParams& hp = heads_op->heads;
+        hp.out_f32 = want_f32 ? head_f32 : nullptr;
+        hp.lik_part = lik ? lik_part : nullptr;
+        if (lik) {
+            hp.lik_x = lik->x; hp.lik_s0 = lik->s0; hp.lik_B = lik->B;
+            hp.lik_has_std = head_ld() == 2 * C() ? 1 : 0;
+            hp.lik_beta = beta;
+            hp.lik = spec;
+        }
+    }
+    if (!run_program(g_prog, n, stream)) return false;
+    if (!lik) return true;
+    if (heads_op) {
+        KCHECK(launch_sum_tiles(lik_part, heads_tiles_per_image(HW()), n, lik->log_px_out, lik->sq_err_out, stream), "sum_tiles");
+    } else {                                      // heads ran as a GEMM op: score the fp32 heads in a separate pass
+        KCHECK(launch_pixel_logprob(head_f32, head_ld(), lik->x, n, lik->s0, lik->B, HW(), C(), spec, cfg.uniform_scale, beta,
+                                    lik->log_px_out, lik->sq_err_out, stream), "pixel_logprob");
+    }
+    return true;
+}
 
 bool Model::run_critic_chunk(int n, float* d_out, void* stream) {
     if (!run_program(d_prog, n, stream)) return false;
@@ -392,7 +426,7 @@ bool Model::critic_of_images(const float* x_dev, int N, float* d_out, void* stre
     for (int s0 = 0; s0 < N; s0 += cfg.max_chunk) {
         const int n = std::min(cfg.max_chunk, N - s0);
         KCHECK(launch_pack_image(x_dev + (size_t)s0 * per, (long long)n * HW(), C(), d_in.raw.cp, d_in.raw.ptr,
-                                 d_in.act.ptr, 0.2f, stream, d_in.raw_lo.ptr, d_in.act_lo.ptr), "pack_image");
+                                 d_in.act.ptr, 0.2f, f16(), stream, d_in.raw_lo.ptr, d_in.act_lo.ptr), "pack_image");
         if (!run_critic_chunk(n, d_out + s0, stream)) return false;
     }
     return true;

@@ -18,6 +18,7 @@
 #include <cmath>
 #include "kernels.h"
 #include "model.h"
+#include "op16.h"
 
 namespace apvae {
 
@@ -46,7 +47,8 @@ bool Model::grad_conv_block(const BlockTape& t, const Tensor& g_out, float* out_
         if (!add_op(gd_prog, t.scope + "conv_1^T", {gterm(true, k, s, cout, cin, g_out, k1)}, {g_out.ptr}, e, cap, &macs_grad)) return false;
     }
     Epilogue e;
-    e.mask = t.in.act.ptr; e.ld_mask = t.in.act.cp;
+    // sign(leaky_relu(x)) == sign(x): the raw block input serves as the mask too (D_psi's first block may have no act copy)
+    e.mask = t.in.act.ptr ? t.in.act.ptr : t.in.raw.ptr; e.ld_mask = t.in.act.ptr ? t.in.act.cp : t.in.raw.cp;
     if (t.use_shortcut) {   // shortcut^T: 1x1 transpose at the OUTPUT resolution; for s == 2 it lands on even input pixels
         const HostArr* ks = W_(t.scope + "shortcut/kernel", {1, 1, cin, cout});
         if (!ks) return false;
@@ -114,10 +116,7 @@ bool Model::build_grad() {
     for (int i = 0; i < feat; ++i) {
         double a = 0;
         for (int j = 0; j < 64; ++j) a += (double)k64->v[(size_t)i * 64 + j] * kl->v[j];
-        const float f = (float)a;
-        uint32_t u; memcpy(&u, &f, 4);
-        u += 0x7fffu + ((u >> 16) & 1u);                 // round to nearest even bf16
-        seed[i] = (uint16_t)(u >> 16);
+        seed[i] = op16::host_from_f32((float)a, f16() != 0);
     }
     d_seed = alloc_act(cap, d_flat.h, d_flat.w, d_flat.c);
     if (!d_seed.ptr) return false;
@@ -187,14 +186,14 @@ bool Model::energy_grad_chunk(const float* z_dev, int n, float* energy, float* g
     if (n > cfg.max_chunk) return fail("energy_grad_chunk: n exceeds max_chunk");
     // forward (keeps every block's activations: they are the masks of the backward ops)
     GCHECK(launch_sample_z(nullptr, nullptr, z_dev, n, 0, 1, cfg.z_dim, 0.f, 0, nullptr, g_in.raw.ptr, g_in.act.ptr,
-                           z_stride(), z_group(), z_cpad(), 0.2f, nullptr, nullptr, stream, g_in.raw_lo.ptr, g_in.act_lo.ptr),
+                           z_stride(), z_group(), z_cpad(), 0.2f, nullptr, nullptr, f16(), stream, g_in.raw_lo.ptr, g_in.act_lo.ptr),
            "stage_latents");
     if (!run_decoder_chunk(n, stream)) return false;
     float* d_out = pure ? pure : z_tmp;                 // z_tmp: [max_chunk, z_dim] scratch, large enough for n floats
     if (!run_critic_chunk(n, d_out, stream)) return false;
     if (grad) {
         if (!run_program(gd_prog, n, stream)) return false;
-        GCHECK(launch_tanh_backward_pack(gx_f32, head_f32, head_ld(), (long long)n * HW(), C(), g_pre.cp, g_pre.ptr, stream),
+        GCHECK(launch_tanh_backward_pack(gx_f32, head_f32, head_ld(), (long long)n * HW(), C(), g_pre.cp, g_pre.ptr, f16(), stream),
                "tanh_backward");
         if (!run_program(gg_prog, n, stream)) return false;
     }
@@ -209,7 +208,7 @@ bool Model::critic_grad_of_images(const float* x_dev, int N, float* d_out, float
     for (int s0 = 0; s0 < N; s0 += cfg.max_chunk) {
         const int n = std::min(cfg.max_chunk, N - s0);
         GCHECK(launch_pack_image(x_dev + (size_t)s0 * per, (long long)n * HW(), C(), d_in.raw.cp, d_in.raw.ptr, d_in.act.ptr,
-                                 0.2f, stream, d_in.raw_lo.ptr, d_in.act_lo.ptr), "pack_image");
+                                 0.2f, f16(), stream, d_in.raw_lo.ptr, d_in.act_lo.ptr), "pack_image");
         if (!run_critic_chunk(n, d_out ? d_out + s0 : z_tmp, stream)) return false;
         if (!run_program(gd_prog, n, stream)) return false;
         if (grad_out && cudaMemcpyAsync(grad_out + (size_t)s0 * per, gx_f32, (size_t)n * per * sizeof(float),
@@ -221,7 +220,7 @@ bool Model::critic_grad_of_images(const float* x_dev, int N, float* d_out, float
 }
 
 bool Model::mala(float* z_io, int n, int steps, float alpha, const float* eps, const float* u, uint64_t seed,
-                 float* hist_e, float* hist_pure, float* hist_ratio, void* stream) {
+                 float* hist_e, float* hist_pure, float* hist_ratio, float* hist_z, void* stream) {
     const int d = cfg.z_dim;
     if ((size_t)n > mala_cap) {
         for (float** p : {&mz, &mzp, &mg, &mgp, &me, &mep, &mp, &mpp, &meps, &mu}) { if (*p) cudaFree(*p); *p = nullptr; }
@@ -245,9 +244,13 @@ bool Model::mala(float* z_io, int n, int steps, float alpha, const float* eps, c
     for (int i = 0; i < steps; ++i) {
         const float* eps_i = eps ? eps + (size_t)i * n * d : meps;
         const float* u_i = u ? u + (size_t)i * n : mu;
+        // history_z[i] = z BEFORE step i's accept (dmm_cifar10.py:200,235)
+        if (hist_z && cudaMemcpyAsync(hist_z + (size_t)i * n * d, z_io, (size_t)n * d * sizeof(float), cudaMemcpyDeviceToDevice,
+                                      static_cast<cudaStream_t>(stream)) != cudaSuccess)
+            return fail("copy of history_z failed");
         if (!eps) GCHECK(launch_fill_normal(meps, (long long)n * d, seed, (unsigned long long)i * 2 * n * d, 0, stream), "fill_normal");
         if (!u) GCHECK(launch_fill_uniform(mu, n, seed ^ 0x9e3779b97f4a7c15ull, (unsigned long long)i * n, stream), "fill_uniform");
-        GCHECK(launch_mala_propose(z_io, mg, eps_i, n, d, alpha, mzp, nullptr, nullptr, 0, 1, 0, 0.2f, stream), "mala_propose");
+        GCHECK(launch_mala_propose(z_io, mg, eps_i, n, d, alpha, mzp, stream), "mala_propose");
         if (!eval_all(mzp, mep, mgp, mpp)) return false;
         GCHECK(launch_mala_accept(z_io, me, mg, mp, mzp, mep, mgp, mpp, u_i, n, d, alpha,
                                   hist_e ? hist_e + (size_t)i * n : nullptr, hist_pure ? hist_pure + (size_t)i * n : nullptr,

@@ -31,7 +31,7 @@ constexpr int kMaxStages = 12;
 
 }  // namespace
 
-template <int KC, bool kTwo, bool kMask>
+template <int KC, bool kTwo, bool kMask, bool kF16>
 __global__ void __launch_bounds__(kThreads, 1)
 patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -162,7 +162,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         }
     } else if (warp == 1 && (!two || rank == 0)) {
         // ===================== MMA issuer (whole warp runs the loops, one lane issues) =====================
-        const uint32_t idesc = make_idesc_bf16(two ? 2 * kTileM : kTileM, p.NT);
+        const uint32_t idesc = make_idesc_16(two ? 2 * kTileM : kTileM, p.NT, kF16);
         // loop invariants in registers (kernel parameters would be re-read from the constant bank after every
         // barrier wait); descriptors advance by plain adds: the low 14 bits hold (smem address >> 4)
         const int macc = p.macc, tpi = p.tpi, num_groups = p.num_groups, a_stages = p.a_stages, b_stages = p.b_stages;
@@ -374,22 +374,23 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 f[6] = __uint_as_float(v[ch * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[ch * 8 + 7]) + b1.w;
                 if (use_mask) {                            // v *= leaky-relu'(forward activation): 1 where it is positive, else alpha
                     const uint4 mv = ld_shared_v4(actbuf + st_off + (((uint32_t)ch ^ sw) << 4));
-                    f[0] *= bf16_lo(mv.x) > 0.f ? 1.f : alpha; f[1] *= bf16_hi(mv.x) > 0.f ? 1.f : alpha;
-                    f[2] *= bf16_lo(mv.y) > 0.f ? 1.f : alpha; f[3] *= bf16_hi(mv.y) > 0.f ? 1.f : alpha;
-                    f[4] *= bf16_lo(mv.z) > 0.f ? 1.f : alpha; f[5] *= bf16_hi(mv.z) > 0.f ? 1.f : alpha;
-                    f[6] *= bf16_lo(mv.w) > 0.f ? 1.f : alpha; f[7] *= bf16_hi(mv.w) > 0.f ? 1.f : alpha;
+                    f[0] *= op16::pos_lo(mv.x) ? 1.f : alpha; f[1] *= op16::pos_hi(mv.x) ? 1.f : alpha;
+                    f[2] *= op16::pos_lo(mv.y) ? 1.f : alpha; f[3] *= op16::pos_hi(mv.y) ? 1.f : alpha;
+                    f[4] *= op16::pos_lo(mv.z) ? 1.f : alpha; f[5] *= op16::pos_hi(mv.z) ? 1.f : alpha;
+                    f[6] *= op16::pos_lo(mv.w) ? 1.f : alpha; f[7] *= op16::pos_hi(mv.w) ? 1.f : alpha;
                 }
                 if (has_res) {
                     const uint4 rv = ld_shared_v4(rbuf + (((uint32_t)ch ^ rsw) << 4));
                     if (lane_res) {
-                        f[0] += bf16_lo(rv.x); f[1] += bf16_hi(rv.x); f[2] += bf16_lo(rv.y); f[3] += bf16_hi(rv.y);
-                        f[4] += bf16_lo(rv.z); f[5] += bf16_hi(rv.z); f[6] += bf16_lo(rv.w); f[7] += bf16_hi(rv.w);
+                        const float2 r0 = op16::unpack<kF16>(rv.x), r1 = op16::unpack<kF16>(rv.y), r2 = op16::unpack<kF16>(rv.z), r3 = op16::unpack<kF16>(rv.w);
+                        f[0] += r0.x; f[1] += r0.y; f[2] += r1.x; f[3] += r1.y;
+                        f[4] += r2.x; f[5] += r2.y; f[6] += r3.x; f[7] += r3.y;
                     }
                 }
 #pragma unroll
                 for (int i = 0; i < 4; ++i) {
-                    rr[ch * 4 + i] = pack_bf16(f[2 * i], f[2 * i + 1]);
-                    aa[ch * 4 + i] = pack_bf16(fmaxf(f[2 * i], alpha * f[2 * i]), fmaxf(f[2 * i + 1], alpha * f[2 * i + 1]));
+                    rr[ch * 4 + i] = op16::pack<kF16>(f[2 * i], f[2 * i + 1]);
+                    aa[ch * 4 + i] = op16::pack<kF16>(fmaxf(f[2 * i], alpha * f[2 * i]), fmaxf(f[2 * i + 1], alpha * f[2 * i + 1]));
                 }
             }
             if (q == 0 && lane == 0 && tblk == 0) stamp(tit, 7);
@@ -518,7 +519,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 const bool more = !last_m || (g + num_clusters < rounds_total);
                 const EpiRow nrow = last_m ? make_row((g + num_clusters) * csize + (int)rank, 0) : make_row(tile, m + 1);
                 const uint32_t taddr0 = tmem_base + acc * kAccColStride + m * p.NT + ((uint32_t)(q * 32) << 16);
-                pre = epilogue_block<false>(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
+                pre = epilogue_block<false, kF16>(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
                 row = nrow;
             }
             tc_fence_before();
@@ -550,15 +551,21 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     const bool two = p.two_cta != 0;
     if (two && c != 2) return (int)cudaErrorInvalidValue;
     const bool mk = p.fast_epi && p.fast_mask;
+    const bool f16 = p.epi.f16 != 0;
+#define APVAE_PATCH_PICK2(KC, TWO, MK) kern = f16 ? patchgemm_kernel<KC, TWO, MK, true> : patchgemm_kernel<KC, TWO, MK, false>
+#define APVAE_PATCH_PICK(KC)                                                                              \
+    do {                                                                                                  \
+        if (two) { if (mk) APVAE_PATCH_PICK2(KC, true, true); else APVAE_PATCH_PICK2(KC, true, false); }  \
+        else { if (mk) APVAE_PATCH_PICK2(KC, false, true); else APVAE_PATCH_PICK2(KC, false, false); }    \
+    } while (0)
     switch (p.kc) {
-        case 16: kern = two ? (mk ? patchgemm_kernel<16, true, true> : patchgemm_kernel<16, true, false>)
-                            : (mk ? patchgemm_kernel<16, false, true> : patchgemm_kernel<16, false, false>); break;
-        case 32: kern = two ? (mk ? patchgemm_kernel<32, true, true> : patchgemm_kernel<32, true, false>)
-                            : (mk ? patchgemm_kernel<32, false, true> : patchgemm_kernel<32, false, false>); break;
-        case 64: kern = two ? (mk ? patchgemm_kernel<64, true, true> : patchgemm_kernel<64, true, false>)
-                            : (mk ? patchgemm_kernel<64, false, true> : patchgemm_kernel<64, false, false>); break;
+        case 16: APVAE_PATCH_PICK(16); break;
+        case 32: APVAE_PATCH_PICK(32); break;
+        case 64: APVAE_PATCH_PICK(64); break;
         default: return (int)cudaErrorInvalidValue;
     }
+#undef APVAE_PATCH_PICK
+#undef APVAE_PATCH_PICK2
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
     cudaLaunchConfig_t cfg = {};
@@ -576,8 +583,8 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     // one persistent cluster per co-resident slot (GPC boundaries can leave a few SMs without a full cluster)
     int max_clusters = num_sms / c;
     if (c > 1) {
-        static int cached[12][5] = {{0}};                     // [kc index, pair mode][cluster] -> max active clusters
-        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (mk ? 6 : 0);
+        static int cached[24][5] = {{0}};                     // [kc index, pair mode][cluster] -> max active clusters
+        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (mk ? 6 : 0) + (f16 ? 12 : 0);
         if (cached[ki][c] == 0) {
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki][c] = nc;

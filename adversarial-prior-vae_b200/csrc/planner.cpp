@@ -1,4 +1,5 @@
 #include "planner.h"
+#include "op16.h"
 
 #include <stdlib.h>
 #include <string.h>
@@ -189,7 +190,7 @@ bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, s
                             const float w = t.transpose
                                 ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
                                 : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
-                            P.wpack[base + (size_t)n * P.kc + kk] = f32_to_bf16(w);
+                            P.wpack[base + (size_t)n * P.kc + kk] = op16::host_from_f32(w, t.f16 != 0);
                         }
                 }
             }
@@ -352,7 +353,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                 if (ci >= t.cin) break;
                 const float w = t.transpose ? t.kernel[(tap_off * t.cout + n) * t.cin + ci]
                                             : t.kernel[(tap_off * t.cin + ci) * t.cout + n];
-                P.wpack[base + (size_t)(row0 + n) * P.kc + kk] = f32_to_bf16(w);
+                P.wpack[base + (size_t)(row0 + n) * P.kc + kk] = op16::host_from_f32(w, t.f16 != 0);
             }
     };
     auto pack_tap = [&](const TermSpec& t, int c0, int di, int dj) { new_item(); fill_tap(t, c0, di, dj, 0); };

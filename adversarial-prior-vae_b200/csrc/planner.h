@@ -26,6 +26,7 @@ struct TermSpec {
     int in_cp;          // source channels as stored (padded to a multiple of 16)
     const float* kernel;
     const float* bias;  // may be null
+    int f16 = 1;        // 16-bit operand format the kernel is packed in: 1 = fp16, 0 = bf16 (op16.h); all terms of an op agree
 };
 
 struct SrcGeom {

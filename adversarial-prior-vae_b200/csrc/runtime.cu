@@ -68,6 +68,7 @@ static void fill_epilogue(EpilogueArgs& e, const Epilogue& epi, const float* bia
     e.tanh_cols = epi.tanh_cols;
     e.lrelu_alpha = 0.2f;
     e.out_raw_lo = epi.out_raw_lo; e.out_act_lo = epi.out_act_lo; e.res_lo = epi.res_lo;
+    e.f16 = epi.f16;
 }
 
 static bool check_epilogue(const Epilogue& epi, int npad, const std::string& name, std::string* err) {
@@ -339,7 +340,7 @@ int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
     if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
     if (op.is_tiny) return launch_tiny_conv(op.tiny, n_valid, stream);
     if (op.is_small_block) return launch_small_block(op.sblock, n_valid, stream);
-    if (op.is_heads) return launch_pixel_heads(op.heads, (long long)n_valid * op.heads.pixels_per_image, stream);
+    if (op.is_heads) return launch_pixel_heads(op.heads, n_valid, stream);
     if (op.is_patch) {
         op.pparams.n_real = n_valid;
         op.pparams.n_valid = op.pparams.fold > 1 ? (n_valid + 1) / 2 : n_valid;

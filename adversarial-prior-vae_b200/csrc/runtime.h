@@ -23,6 +23,7 @@ struct Epilogue {
     const void* mask = nullptr;
     int ld_mask = 0;
     int tanh_cols = 0;
+    int f16 = 1;                     // 16-bit operand / output format of the op: 1 = fp16, 0 = bf16 (op16.h)
     void* out_raw_lo = nullptr;      // split-precision low halves (see tapgemm.h)
     void* out_act_lo = nullptr;
     const void* res_lo = nullptr;

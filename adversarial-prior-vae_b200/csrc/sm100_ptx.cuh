@@ -6,6 +6,7 @@
 #include <cuda_bf16.h>
 #include <stdio.h>
 #include "tapgemm.h"
+#include "op16.h"
 
 namespace apvae {
 namespace ptx {
@@ -219,9 +220,10 @@ __device__ __forceinline__ uint64_t make_kmajor_desc(uint32_t saddr) {
     d |= layout << 61;
     return d;
 }
-// kind::f16 instruction descriptor: D = f32, A = B = bf16, both K-major, M x N.
-__device__ __forceinline__ uint32_t make_idesc_bf16(int M, int N) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// kind::f16 instruction descriptor: D = f32, A = B = fp16 (format 0) or bf16 (format 1), both K-major, M x N.
+__device__ __forceinline__ uint32_t make_idesc_16(int M, int N, bool f16) {
+    const uint32_t fmt = f16 ? 0u : 1u;
+    return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
@@ -309,7 +311,7 @@ __device__ __forceinline__ void epilogue_res_issue(const EpilogueArgs& e, const 
 // `rv` / `preloaded`: residual registers, already holding block 0 of `row` when `preloaded`.  When `next` is
 // given, its residual block 0 (at next_col_base) is issued during this tile's last block and the function returns true
 // (pass that as the next call's `preloaded`).
-template <bool kSplit>
+template <bool kSplit, bool kF16>
 __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t taddr0, int NT, int col_base,
                                                const EpiRow& row, uint32_t wsm, uint32_t bias_s, int lane,
                                                uint4 (&rv)[8], bool preloaded, const EpiRow* next, int next_col_base) {
@@ -373,8 +375,8 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                         const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            f[8 * i + 2 * j + 0] *= (bf16_lo(w[j]) > 0.f) ? 1.f : e.lrelu_alpha;
-                            f[8 * i + 2 * j + 1] *= (bf16_hi(w[j]) > 0.f) ? 1.f : e.lrelu_alpha;
+                            f[8 * i + 2 * j + 0] *= op16::pos_lo(w[j]) ? 1.f : e.lrelu_alpha;
+                            f[8 * i + 2 * j + 1] *= op16::pos_hi(w[j]) ? 1.f : e.lrelu_alpha;
                         }
                     }
                 }
@@ -385,8 +387,7 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                         const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            f[8 * i + 2 * j + 0] += bf16_lo(w[j]);
-                            f[8 * i + 2 * j + 1] += bf16_hi(w[j]);
+                            { const float2 u2 = op16::unpack<kF16>(w[j]); f[8 * i + 2 * j + 0] += u2.x; f[8 * i + 2 * j + 1] += u2.y; }
                         }
                     }
                 }
@@ -399,8 +400,7 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                         const uint32_t w[4] = {m.x, m.y, m.z, m.w};
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            f[8 * i + 2 * j + 0] += bf16_lo(w[j]);
-                            f[8 * i + 2 * j + 1] += bf16_hi(w[j]);
+                            { const float2 u2 = op16::unpack<kF16>(w[j]); f[8 * i + 2 * j + 0] += u2.x; f[8 * i + 2 * j + 1] += u2.y; }
                         }
                     }
                 }
@@ -425,8 +425,8 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                     uint32_t lo[8];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
-                        const uint32_t hi = pack_bf16(f[2 * i], f[2 * i + 1]);
-                        lo[i] = pack_bf16(f[2 * i] - bf16_lo(hi), f[2 * i + 1] - bf16_hi(hi));
+                        const uint32_t hi = op16::pack<kF16>(f[2 * i], f[2 * i + 1]);
+                        lo[i] = op16::pack<kF16>(f[2 * i] - op16::lo<kF16>(hi), f[2 * i + 1] - op16::hi<kF16>(hi));
                     }
                     uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(e.out_raw_lo) + row.opix * e.ldo + col);
                     o[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
@@ -438,22 +438,22 @@ __device__ __forceinline__ bool epilogue_block(const EpilogueArgs& e, uint32_t t
                     for (int i = 0; i < 8; ++i) {
                         const float a0 = f[2 * i] > 0.f ? f[2 * i] : e.lrelu_alpha * f[2 * i];
                         const float a1 = f[2 * i + 1] > 0.f ? f[2 * i + 1] : e.lrelu_alpha * f[2 * i + 1];
-                        const uint32_t hi = pack_bf16(a0, a1);
-                        lo[i] = pack_bf16(a0 - bf16_lo(hi), a1 - bf16_hi(hi));
+                        const uint32_t hi = op16::pack<kF16>(a0, a1);
+                        lo[i] = op16::pack<kF16>(a0 - op16::lo<kF16>(hi), a1 - op16::hi<kF16>(hi));
                     }
                     uint4* o = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(e.out_act_lo) + row.opix * e.ldo + col);
                     o[0] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                     o[1] = make_uint4(lo[4], lo[5], lo[6], lo[7]);
                 }
                 if (e.out_raw != nullptr) {
-                    st_shared_v4(stA + so, pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-                    st_shared_v4(stA + so + 16, pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+                    st_shared_v4(stA + so, op16::pack<kF16>(f[0], f[1]), op16::pack<kF16>(f[2], f[3]), op16::pack<kF16>(f[4], f[5]), op16::pack<kF16>(f[6], f[7]));
+                    st_shared_v4(stA + so + 16, op16::pack<kF16>(f[8], f[9]), op16::pack<kF16>(f[10], f[11]), op16::pack<kF16>(f[12], f[13]), op16::pack<kF16>(f[14], f[15]));
                 }
                 if (e.out_act != nullptr) {
 #pragma unroll
                     for (int i = 0; i < 16; ++i) f[i] = f[i] > 0.f ? f[i] : e.lrelu_alpha * f[i];
-                    st_shared_v4(stB + so, pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-                    st_shared_v4(stB + so + 16, pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+                    st_shared_v4(stB + so, op16::pack<kF16>(f[0], f[1]), op16::pack<kF16>(f[2], f[3]), op16::pack<kF16>(f[4], f[5]), op16::pack<kF16>(f[6], f[7]));
+                    st_shared_v4(stB + so + 16, op16::pack<kF16>(f[8], f[9]), op16::pack<kF16>(f[10], f[11]), op16::pack<kF16>(f[12], f[13]), op16::pack<kF16>(f[14], f[15]));
                 }
             }
         }

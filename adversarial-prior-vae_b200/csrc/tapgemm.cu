@@ -56,7 +56,7 @@ __device__ __forceinline__ TileCoord decode_pair_tile(const TapGemmParams& p, in
 
 }  // namespace
 
-template <int KC, bool kSplit, bool kTwo>
+template <int KC, bool kSplit, bool kTwo, bool kF16>
 __global__ void __launch_bounds__(kThreads, 1)
 tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
     constexpr bool two = kTwo;
@@ -145,7 +145,7 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
         }
     } else if (warp == 1 && (!two || rank == 0)) {
         // ===================== MMA issuer (pair mode: the leader CTA only) =====================
-        const uint32_t idesc = make_idesc_bf16(two ? 2 * kTileM : kTileM, p.NT);
+        const uint32_t idesc = make_idesc_16(two ? 2 * kTileM : kTileM, p.NT, kF16);
         int stage = 0, acc = 0;
         uint32_t phase = 0, acc_phase = 0;
         for (int tile = w_first; tile < total_tiles; tile += w_step) {
@@ -228,7 +228,7 @@ tapgemm_kernel(const __grid_constant__ TapGemmParams p) {
             mbar_wait(tfull_bar(acc), acc_phase);
             tc_fence_after();
             const uint32_t taddr0 = tmem_base + acc * kAccColStride + ((uint32_t)(q * 32) << 16);
-            pre = epilogue_block<kSplit>(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, tn.nt * p.NT);
+            pre = epilogue_block<kSplit, kF16>(p.epi, taddr0, p.NT, t.nt * p.NT, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, tn.nt * p.NT);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0)); else mbar_arrive(tempty_bar(acc)); }
@@ -268,12 +268,18 @@ int launch_tapgemm(const TapGemmParams& p, int num_sms, void* stream) {
     void (*kern)(TapGemmParams) = nullptr;
     const bool split = p.epi.out_raw_lo != nullptr || p.epi.out_act_lo != nullptr || p.epi.res_lo != nullptr;
     if (two && split) return (int)cudaErrorInvalidValue;
+    const bool f16 = p.epi.f16 != 0;
+#define APVAE_TAP_PICK(KC)                                                                                            \
+    kern = two ? (f16 ? tapgemm_kernel<KC, false, true, true> : tapgemm_kernel<KC, false, true, false>)               \
+         : split ? (f16 ? tapgemm_kernel<KC, true, false, true> : tapgemm_kernel<KC, true, false, false>)             \
+                 : (f16 ? tapgemm_kernel<KC, false, false, true> : tapgemm_kernel<KC, false, false, false>)
     switch (p.kc) {
-        case 16: kern = two ? tapgemm_kernel<16, false, true> : split ? tapgemm_kernel<16, true, false> : tapgemm_kernel<16, false, false>; break;
-        case 32: kern = two ? tapgemm_kernel<32, false, true> : split ? tapgemm_kernel<32, true, false> : tapgemm_kernel<32, false, false>; break;
-        case 64: kern = two ? tapgemm_kernel<64, false, true> : split ? tapgemm_kernel<64, true, false> : tapgemm_kernel<64, false, false>; break;
+        case 16: APVAE_TAP_PICK(16); break;
+        case 32: APVAE_TAP_PICK(32); break;
+        case 64: APVAE_TAP_PICK(64); break;
         default: return (int)cudaErrorInvalidValue;
     }
+#undef APVAE_TAP_PICK
     err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
     if (!two) {
@@ -293,8 +299,8 @@ int launch_tapgemm(const TapGemmParams& p, int num_sms, void* stream) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     cfg.gridDim = dim3((num_sms / 2) * 2);
-    static int cached[3] = {0, 0, 0};                        // [kc index] -> max co-resident pairs
-    const int ki = p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2;
+    static int cached[6] = {0, 0, 0, 0, 0, 0};               // [kc index, format] -> max co-resident pairs
+    const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (f16 ? 3 : 0);
     if (cached[ki] == 0) {
         int nc = 0;
         if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki] = nc;

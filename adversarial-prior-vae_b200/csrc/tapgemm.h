@@ -54,6 +54,7 @@ struct EpilogueArgs {
     void* out_raw_lo;           // bf16(v - bf16(v))
     void* out_act_lo;           // bf16(leaky_relu(v) - bf16(leaky_relu(v)))
     const void* res_lo;         // low half of the residual (same indexing as res)
+    int f16;                    // 16-bit operand / output format of this op: 1 = fp16, 0 = bf16 (op16.h)
 };
 
 struct alignas(64) TapGemmParams {

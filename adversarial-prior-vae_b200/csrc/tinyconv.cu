@@ -11,6 +11,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include "kernels.h"
+#include "op16.h"
 #include "tapgemm.h"      // ResMode
 
 namespace apvae {
@@ -19,14 +20,7 @@ namespace {
 constexpr int kTW = 32, kTH = 8, kHalo = kTinyMaxK - 1;
 constexpr int kPW = kTW + kHalo, kPH = kTH + kHalo;
 
-__device__ __forceinline__ float bfl(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bfh(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
-__device__ __forceinline__ uint32_t pk(float a, float b) {
-    const __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<const uint32_t*>(&v);
-}
-
-template <int CIN, int COUT>
+template <int CIN, int COUT, bool F16>
 __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_constant__ TinyConvParams p, int n_images) {
     __shared__ float tile[CIN][kPH * kPW];
     const int H = p.H, W = p.W;
@@ -45,7 +39,7 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
             float c[4] = {0.f, 0.f, 0.f, 0.f};
             if (py < kTH + 2 * r && px < kTW + 2 * r && y >= 0 && y < H && x >= 0 && x < W) {
                 const uint2 v = *reinterpret_cast<const uint2*>(src + ((size_t)y * W + x) * p.cp_in * 2);
-                c[0] = bfl(v.x); c[1] = bfh(v.x); c[2] = bfl(v.y); c[3] = bfh(v.y);
+                c[0] = op16::lo<F16>(v.x); c[1] = op16::hi<F16>(v.x); c[2] = op16::lo<F16>(v.y); c[3] = op16::hi<F16>(v.y);
             }
 #pragma unroll
             for (int ci = 0; ci < CIN; ++ci) tile[ci][i] = c[ci];
@@ -69,14 +63,14 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
             const size_t pix = ((size_t)n * H + y) * W + x;
             if (p.mask) {
                 const uint2 m = *reinterpret_cast<const uint2*>(static_cast<const uint8_t*>(p.mask) + pix * p.ld_mask * 2);
-                const float mv[4] = {bfl(m.x), bfh(m.x), bfl(m.y), bfh(m.y)};
+                const bool mv[4] = {op16::pos_lo(m.x), op16::pos_hi(m.x), op16::pos_lo(m.y), op16::pos_hi(m.y)};
 #pragma unroll
-                for (int co = 0; co < COUT; ++co) acc[co] *= mv[co] > 0.f ? 1.f : p.alpha;
+                for (int co = 0; co < COUT; ++co) acc[co] *= mv[co] ? 1.f : p.alpha;
             }
             if (p.res_mode == RES_SAME || (p.res_mode == RES_EVEN && !((y | x) & 1))) {
                 const size_t rp = p.res_mode == RES_SAME ? pix : ((size_t)n * (H >> 1) + (y >> 1)) * (W >> 1) + (x >> 1);
                 const uint2 rv = *reinterpret_cast<const uint2*>(static_cast<const uint8_t*>(p.res) + rp * p.ld_res * 2);
-                const float rr[4] = {bfl(rv.x), bfh(rv.x), bfl(rv.y), bfh(rv.y)};
+                const float rr[4] = {op16::lo<F16>(rv.x), op16::hi<F16>(rv.x), op16::lo<F16>(rv.y), op16::hi<F16>(rv.y)};
 #pragma unroll
                 for (int co = 0; co < COUT; ++co) acc[co] += rr[co];
             }
@@ -90,7 +84,7 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
             const int och = p.ldo >> 3;
             if (p.out_raw) {
                 uint4* d = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.out_raw) + pix * p.ldo * 2);
-                d[0] = make_uint4(pk(v[0], v[1]), pk(v[2], v[3]), 0u, 0u);
+                d[0] = make_uint4(op16::pack<F16>(v[0], v[1]), op16::pack<F16>(v[2], v[3]), 0u, 0u);
                 for (int c = 1; c < och; ++c) d[c] = make_uint4(0u, 0u, 0u, 0u);
             }
             if (p.out_act) {
@@ -98,7 +92,7 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
 #pragma unroll
                 for (int co = 0; co < 4; ++co) a[co] = fmaxf(v[co], p.alpha * v[co]);
                 uint4* d = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.out_act) + pix * p.ldo * 2);
-                d[0] = make_uint4(pk(a[0], a[1]), pk(a[2], a[3]), 0u, 0u);
+                d[0] = make_uint4(op16::pack<F16>(a[0], a[1]), op16::pack<F16>(a[2], a[3]), 0u, 0u);
                 for (int c = 1; c < och; ++c) d[c] = make_uint4(0u, 0u, 0u, 0u);
             }
         }
@@ -107,12 +101,12 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
 }
 
 template <int CIN>
-void (*pick_cout(int cout))(TinyConvParams, int) {
+void (*pick_cout(int cout, bool f16))(TinyConvParams, int) {
     switch (cout) {
-        case 1: return tiny_conv_kernel<CIN, 1>;
-        case 2: return tiny_conv_kernel<CIN, 2>;
-        case 3: return tiny_conv_kernel<CIN, 3>;
-        default: return tiny_conv_kernel<CIN, 4>;
+        case 1: return f16 ? tiny_conv_kernel<CIN, 1, true> : tiny_conv_kernel<CIN, 1, false>;
+        case 2: return f16 ? tiny_conv_kernel<CIN, 2, true> : tiny_conv_kernel<CIN, 2, false>;
+        case 3: return f16 ? tiny_conv_kernel<CIN, 3, true> : tiny_conv_kernel<CIN, 3, false>;
+        default: return f16 ? tiny_conv_kernel<CIN, 4, true> : tiny_conv_kernel<CIN, 4, false>;
     }
 }
 
@@ -126,10 +120,10 @@ int launch_tiny_conv(const TinyConvParams& p, int n, void* stream) {
         return (int)cudaErrorInvalidValue;
     void (*kern)(TinyConvParams, int) = nullptr;
     switch (p.cin) {
-        case 1: kern = pick_cout<1>(p.cout); break;
-        case 2: kern = pick_cout<2>(p.cout); break;
-        case 3: kern = pick_cout<3>(p.cout); break;
-        default: kern = pick_cout<4>(p.cout); break;
+        case 1: kern = pick_cout<1>(p.cout, p.f16 != 0); break;
+        case 2: kern = pick_cout<2>(p.cout, p.f16 != 0); break;
+        case 3: kern = pick_cout<3>(p.cout, p.f16 != 0); break;
+        default: kern = pick_cout<4>(p.cout, p.f16 != 0); break;
     }
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);

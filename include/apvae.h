@@ -62,6 +62,10 @@ typedef struct apvae_config {
     int latent_gan;                 /* 1: also build G_omega, the latent generator whose output `gan_z` is the initial_z of the
                                      * MALA chains in plot_samples (dmm_cifar10.py:503-532,623-639,1061-1066; archs A and B):
                                      * weights `G_omega/...`, entry point apvae_latent_gan. */
+    int operand_bf16;               /* 16-bit operand format of the tensor-core path (activations and packed kernels; fp32 accumulate):
+                                     * 0 (default): fp16 — 11 significant bits, D(G(z)) within 2e-3 of the float64 oracle;
+                                     * 1: bf16 — 8 significant bits, fp32's exponent range (for activations beyond +-65504);
+                                     * same tcgen05 rate either way (kind::f16). */
 } apvae_config;
 
 typedef struct apvae_handle apvae_handle;
@@ -110,10 +114,13 @@ enum {
     APVAE_ROW_LZ_MAX = 6,   /* max_k(-energy - log q)          } another_log_Z_compute_op (:922-924) */
     APVAE_ROW_LZ_SUM = 7,   /* sum_k exp(-energy - log q - max) } before the + log(len_train) */
     APVAE_ROW_REAL_E = 8,   /* D_psi(x_origin) (:913) */
-    APVAE_PER_IMAGE_ROWS = 9
+    APVAE_ROW_MSE = 9,      /* min_k sum_pixels (round(x_mean 128 + 127.5) - round(x 128 + 127.5))^2: test_mse before the batch mean
+                             * (:889-895; arch M: * 255 on the clipped Bernoulli mean, dmm_bernouli_fashion.py:893-899) */
+    APVAE_PER_IMAGE_ROWS = 10
 };
-/* Rows of the optional `per_sample_dev` ([4][K*B]): log p(x|z), log q(z|x), log N(z), D(G(z)). */
-enum { APVAE_SROW_LOG_PX = 0, APVAE_SROW_LOG_Q = 1, APVAE_SROW_LOG_PN = 2, APVAE_SROW_DG = 3, APVAE_PER_SAMPLE_ROWS = 4 };
+/* Rows of the optional `per_sample_dev` ([5][K*B]): log p(x|z), log q(z|x), log N(z), D(G(z)), squared pixel error. */
+enum { APVAE_SROW_LOG_PX = 0, APVAE_SROW_LOG_Q = 1, APVAE_SROW_LOG_PN = 2, APVAE_SROW_DG = 3, APVAE_SROW_SQ_ERR = 4,
+       APVAE_PER_SAMPLE_ROWS = 5 };
 
 /* The test graph of one Evaluator mini-batch (dmm_cifar10.py:880-927, one session.run at
  * trainer/evaluator.py:189-191): q_net once per image, K reparameterised draws, G_theta and
@@ -130,23 +137,32 @@ int apvae_sample_z(apvae_handle* h, const float* x_origin_dev, int B, int K, con
 
 /* Shard-local metric accumulation, replacing Evaluator.run's host np.average (trainer/evaluator.py:249-254)
  * and the host logsumexp of the log-Z loop (dmm_cifar10.py:1215-1227).  accum_dev: double[APVAE_ACCUM_SLOTS],
- * zero-initialised by the caller.  Slots 0-5, 8: sums over images of the per-image rows; slots 6, 7: running
- * (max, sum exp) over BATCHES of another_log_Z_compute_op's batch value (before + log(len_train));
- * slot 9: images seen; slot 10: batches seen.  One sum-allreduce of slots 0-5, 8, 9 over ranks gives the
- * dataset metrics; (6, 7, 10) combine by log-sum-exp. */
-enum { APVAE_ACCUM_WEIGHT = 9, APVAE_ACCUM_BATCHES = 10, APVAE_ACCUM_SLOTS = 16 };
-int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, int B, int K, double* accum_dev, void* stream);
+ * zero-initialised by the caller.  Slots 0-5, 8, 11: sums over images of the per-image rows (11 = APVAE_ROW_MSE);
+ * slots 6, 7: running (max, sum exp) over BATCHES of another_log_Z_compute_op's batch value (before + log(len_train));
+ * slot 9: images seen; slot 10: batches seen; slots 12-15: sums over batches of B x the prior branch's batch scalars
+ * (`prior4_dev`, may be NULL: then slots 12-16 are untouched), slot 16: their weight.  One sum-allreduce of the additive
+ * slots over ranks gives the dataset metrics; (6, 7) combine by log-sum-exp. */
+enum { APVAE_ACCUM_WEIGHT = 9, APVAE_ACCUM_BATCHES = 10, APVAE_ACCUM_MSE = 11, APVAE_ACCUM_PN_ENERGY = 12,
+       APVAE_ACCUM_PD_ENERGY = 13, APVAE_ACCUM_KL_ADV = 14, APVAE_ACCUM_LOG_Z_OP = 15, APVAE_ACCUM_PRIOR_WEIGHT = 16,
+       APVAE_ACCUM_SLOTS = 20 };
+int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, const float* prior4_dev, int B, int K,
+                             double* accum_dev, void* stream);
 
-/* test_pn_net branch (:883,915-927): Kp prior draws through G and D.  Outputs [Kp] each. */
+/* test_pn_net branch (:883,915-927): Kp prior draws z ~ N(0, I) through G_theta and D_psi.
+ * d_g_dev / log_pn_dev [Kp]: D(G(z)) and log N(z) per draw (either may be NULL);
+ * prior4_dev [4] (may be NULL): the batch scalars { pn_energy (:918), pd_energy (:915-917), kl_adv_and_gaussian (:925-927),
+ * log_Z_compute_op (:919-920) }, reduced on the device. */
+enum { APVAE_PRIOR_PN_ENERGY = 0, APVAE_PRIOR_PD_ENERGY = 1, APVAE_PRIOR_KL_ADV = 2, APVAE_PRIOR_LOG_Z_OP = 3 };
 int apvae_prior_stats(apvae_handle* h, int Kp, const float* eps_dev, uint64_t seed, float* d_g_dev,
-                      float* log_pn_dev, void* stream);
+                      float* log_pn_dev, float* prior4_dev, void* stream);
 
 /* EnergyDistribution.sample / get_sgld_proposal (:179-252): `steps` MALA iterations on n chains.
  * z_io_dev [n, z_dim] in/out; eps_dev [steps,n,z_dim], u_dev [steps,n] or NULL (Philox);
- * hist_* [steps, n] or NULL.  Requires enable_grad. */
+ * hist_* [steps, n] or NULL; hist_z_dev [steps, n, z_dim] or NULL: history_z, the state BEFORE each step (:200,235 — the
+ * reference's sampling driver restarts from history_z[-1], the state before the last accept, :1061).  Requires enable_grad. */
 int apvae_mala(apvae_handle* h, float* z_io_dev, int n, int steps, float alpha, const float* eps_dev,
                const float* u_dev, uint64_t seed, float* hist_e_dev, float* hist_pure_e_dev,
-               float* hist_ratio_dev, void* stream);
+               float* hist_ratio_dev, float* hist_z_dev, void* stream);
 /* energy, grad_z energy, pure energy at z (get_sgld_proposal :241-247). Any output may be NULL. */
 int apvae_energy_grad(apvae_handle* h, const float* z_dev, int n, float* energy_dev, float* grad_dev,
                       float* pure_dev, void* stream);
@@ -162,6 +178,25 @@ int apvae_image_energy_grad(apvae_handle* h, const float* x_dev, int N, float* d
 int apvae_latent_gan(apvae_handle* h, const float* z_omega_dev, int n, uint64_t seed, float* z0_dev, void* stream);
 
 int apvae_sample_images(apvae_handle* h, const float* z_dev, int n, uint8_t* out_dev, void* stream);
+
+/* ---- the estimator kernels on plain arrays (no handle; current device): what the reference's own unit tests exercise.
+ * DiscretizedLogistic(mean, log_scale, bin_size, min_val, max_val, biased_edges, epsilon).log_prob(given, group_ndims)
+ * (tfsnippet/distributions/discretized.py:26-58,198-259; tests/distributions/test_discretized.py:232-363): x / mean /
+ * log_scale are fp32 device arrays of rows * group elements (already broadcast), out_dev[r] = sum of the `group`
+ * consecutive element log-probs of row r (group = 1: elementwise).  has_min / has_max = 0: min_val / max_val is None. */
+int apvae_discretized_logistic_log_prob(const float* x_dev, const float* mean_dev, const float* log_scale_dev, int64_t rows,
+                                        int64_t group, float bin_size, int has_min, float min_val, int has_max, float max_val,
+                                        int biased_edges, float epsilon, float* out_dev, void* stream);
+/* The arch-M likelihood (dmm_bernouli_fashion.py:619-626): p = clip(mean, 1e-7, 1 - 1e-7), logits = log p - log1p(-p),
+ * Bernoulli(logits).log_prob(x) = x logits - softplus(logits), summed over `group` consecutive elements. */
+int apvae_bernoulli_log_prob(const float* x_dev, const float* mean_dev, int64_t rows, int64_t group, float* out_dev,
+                             void* stream);
+/* Per-image reductions over the K samples (variational/evaluation.py:9-39, objectives.py:9-42, ops/misc.py:71-107):
+ * log_px / log_q / log_pn / d_g [K, B] (+ optional sq_err [K, B]) -> per_image_dev [APVAE_PER_IMAGE_ROWS][B] (rows
+ * APVAE_ROW_LL .. APVAE_ROW_LZ_SUM and APVAE_ROW_MSE; APVAE_ROW_REAL_E is left untouched). */
+int apvae_is_reduce(const float* log_px_dev, const float* log_q_dev, const float* log_pn_dev, const float* d_g_dev,
+                    const float* sq_err_dev, int K, int B, int z_dim, float w_xi, float log_Z, float* per_image_dev,
+                    void* stream);
 
 /* Philox normals / uniforms the NULL-noise paths use (so tests can reproduce them). */
 int apvae_fill_normal(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, int truncated, void* stream);
@@ -214,7 +249,8 @@ typedef struct apvae_epilogue {
 /* Host-only planning (no GPU needed): step table, packed bf16 weights, TMA view geometry.
  * Environment (read at plan / model build time): APVAE_PATCH=0 disables the A-stationary kernel,
  * APVAE_PATCH_MACC / APVAE_PATCH_CLUSTER force its accumulator count / cluster size. */
-int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, apvae_plan** out);
+/* operand_bf16: the 16-bit format the kernels are packed in and the sources / outputs hold (see apvae_config). */
+int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, apvae_plan** out);
 int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info);
 int apvae_plan_copy_steps(const apvae_plan* p, int32_t* out /* [total_steps][5]: src,dx,dy,ph,c0 */);
 int apvae_plan_copy_weights(const apvae_plan* p, uint16_t* out /* bf16 [total_steps][npad][kc] */);

@@ -13,13 +13,13 @@ from .dists import (normal_log_prob, truncated_normal_log_prob,
                     maybe_clip_value, sigmoid, planar_flows_transform)
 from .nets import q_net, G_theta, D_psi, G_theta_input_grad, D_psi_input_grad
 
-__all__ = ['log_px_given_z', 'energy_terms', 'eval_batch', 'prior_branch',
+__all__ = ['log_px_given_z', 'rounded_pixel_sq_err', 'energy_terms', 'eval_batch', 'prior_branch',
            'log_Z_batch', 'combine_log_Z', 'energy_and_grad', 'mala_step',
            'mala_sample', 'sample_images', 'evaluator_average', 'METRIC_NAMES']
 
 METRIC_NAMES = ['test_nll', 'test_lb', 'adv_test_nll', 'adv_test_lb',
                 'reconstruct_energy', 'real_energy', 'pd_energy', 'pn_energy',
-                'test_recon', 'kl_adv_and_gaussian']     # dmm_cifar10.py:1131-1136
+                'test_recon', 'kl_adv_and_gaussian', 'test_mse']     # dmm_cifar10.py:1131-1136
 
 
 def log_px_given_z(cfg, params, x, z, beta=0.0):
@@ -37,6 +37,19 @@ def log_px_given_z(cfg, params, x, z, beta=0.0):
         x, x_mean, log_scale, bin_size=2.0 / 256.0, min_val=-1.0 + 1.0 / 256.0,
         max_val=1.0 - 1.0 / 256.0, epsilon=1e-10, group_ndims=3)
     return lp, x_mean
+
+
+def rounded_pixel_sq_err(cfg, x, x_mean):
+    """The summand of test_mse (dmm_cifar10.py:889-891): sum over H, W, C of
+    (round(x_mean * 128 + 127.5) - round(x * 128 + 127.5))^2 with tf.round = round half to even (np.round);
+    arch M (dmm_bernouli_fashion.py:893-896): round(mean * 255) - round(x * 255), where distribution.mean of the
+    Bernoulli is sigmoid(logits) = the clipped G_theta output (:619-626)."""
+    if cfg.arch == 'M':
+        p = np.clip(x_mean, 1e-7, 1.0 - 1e-7)
+        d = np.round(p * 255.0) - np.round(x * 255.0)
+    else:
+        d = np.round(x_mean * 128.0 + 127.5) - np.round(x * 128.0 + 127.5)
+    return np.sum(np.square(d), axis=(-1, -2, -3))
 
 
 def energy_terms(cfg, z, d_of_g, xi_raw, log_Z):
@@ -90,6 +103,9 @@ def eval_batch(cfg, params, x, x_origin, eps, xi_raw=0.0, beta=0.0, log_Z=1.0):
     out['adv_test_nll'] = -np.mean(out['ele_adv_test_ll'])
     out['adv_test_lb'] = np.mean(out['ele_adv_test_lb'])
     out['test_recon'] = np.mean(log_px)                             # :886-888
+    out['sq_err'] = rounded_pixel_sq_err(cfg, x, x_mean)            # [K,B]
+    out['ele_test_mse'] = np.min(out['sq_err'], axis=0)             # :892 reduce_min over the sample axis
+    out['test_mse'] = np.mean(out['ele_test_mse'])                  # :893-895 (test_x_samples = 1, :76)
     out['ele_real_energy'] = D_psi(cfg, params, x_origin)           # :913
     out['real_energy'] = np.mean(out['ele_real_energy'])
     out['reconstruct_energy'] = np.mean(d_g)                        # :914

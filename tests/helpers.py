@@ -15,6 +15,30 @@ def bf16_bits_to_f32(bits):
     return (np.asarray(bits, dtype=np.uint32) << 16).view(np.float32)
 
 
+def exact16(x):
+    """Test inputs exactly representable in BOTH operand formats: bf16-rounded, with magnitudes below fp16's smallest
+    normal (2^-14) flushed to zero (8 significant bits always fit fp16's 11)."""
+    r = bf16_round(x)
+    return np.where(np.abs(r) < 2.0 ** -14, np.float32(0), r).astype(np.float32)
+
+
+def fp16_round(x):
+    """Round float -> float16 -> float32."""
+    return np.asarray(x, dtype=np.float32).astype(np.float16).astype(np.float32)
+
+
+def op16_round(x, dtype='fp16'):
+    """Round through the library's 16-bit operand format (csrc/op16.h)."""
+    return fp16_round(x) if dtype == 'fp16' else bf16_round(x)
+
+
+def op16_bits_to_f32(bits, dtype='fp16'):
+    """Packed 16-bit operand words (as the planner emits them) -> float32."""
+    if dtype == 'fp16':
+        return np.ascontiguousarray(bits, dtype=np.uint16).view(np.float16).astype(np.float32)
+    return bf16_bits_to_f32(bits)
+
+
 def pad_channels(x, cp):
     out = np.zeros(x.shape[:-1] + (cp,), dtype=x.dtype)
     out[..., :x.shape[-1]] = x
@@ -27,7 +51,7 @@ def emulate_plan(plan, srcs, n_valid):
     NHWC source, multiply by the packed weight slice, accumulate; add bias.
     srcs: list of float arrays [N, H, W, Cp].  Returns [n_valid, Ho, Wo, npad]."""
     i = plan.info
-    steps, wts, bias = plan.steps, bf16_bits_to_f32(plan.weights).astype(np.float64), plan.bias
+    steps, wts, bias = plan.steps, op16_bits_to_f32(plan.weights, plan.dtype).astype(np.float64), plan.bias
     out = np.zeros((n_valid, i.ho, i.wo, i.npad), dtype=np.float64)
     views = []
     for s in range(i.nsrc):
@@ -93,7 +117,7 @@ def emulate_patch_plan(plan, srcs, n_valid):
     i = plan.info
     assert i.patch
     groups = plan.patch_groups
-    wts = bf16_bits_to_f32(plan.patch_weights).astype(np.float64)
+    wts = op16_bits_to_f32(plan.patch_weights, plan.dtype).astype(np.float64)
     npad = i.patch_npad or i.npad
     bias = plan.patch_bias if i.patch_npad else plan.bias
     H, W, kc, macc, rt = i.hg, i.wg, i.kc, i.patch_macc, i.patch_rows_tile

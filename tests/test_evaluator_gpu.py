@@ -68,7 +68,7 @@ def test_evaluator_ragged_batches_match_per_image_means_and_oracle():
         t = -want['energy'][:, sl] - want['log_q'][:, sl]                     # another_log_Z_compute_op, dmm_cifar10.py:922-924
         per_batch.append(O.log_mean_exp(t.reshape(-1)))
     lz_o = O.log_sum_exp(np.asarray(per_batch)) - math.log(len(per_batch)) + math.log(m.config.len_train)
-    assert abs(lz - lz_o) < 1e-3 * abs(lz_o) + w_xi * 3e-2, (lz, lz_o)
+    assert abs(lz - lz_o) < 1e-3 * abs(lz_o) + w_xi * 1e-2, (lz, lz_o)        # energies within 1e-2, times the weight
     m.close()
 
 
@@ -99,8 +99,49 @@ def test_full_size_k1000_properties():
     small.close()
     for k in ('ele_test_ll', 'ele_test_lb', 'ele_adv_test_ll', 'ele_adv_test_lb', 'ele_test_recon'):
         rel = np.abs(a[k] - b[k]) / np.abs(a[k])
-        assert rel.max() < 2e-4, (k, a[k], b[k])                   # same bf16 rounding points, different fp32 summation order
+        assert rel.max() < 2e-4, (k, a[k], b[k])                   # same 16-bit rounding points, different fp32 summation order
     assert np.abs(a['ele_reconstruct_energy'] - b['ele_reconstruct_energy']).max() < 1e-2
+
+
+def test_benchmarked_shape_against_the_oracle():
+    """The configuration bench.py times (BASELINE configs[1]: arch A, z_dim 128, K = 1000, 37 images per step, chunks of
+    7400 samples) against the oracle: the library evaluates the whole 37-image batch with fed-in noise; the oracle
+    (float32 "as-reference" mode, ~1-2 minutes of CPU) evaluates two of its images — images are independent, so those
+    per-image rows must agree.  north_star tolerances: per-image NLL 1e-3 relative, energies 1e-2 absolute."""
+    from apvae.model import ExpConfig, Model
+    B, K = 37, 1000
+    ocfg = O.OracleConfig('A', z_dim=128)
+    params = O.init_weights(ocfg)
+    m = Model(ExpConfig('A', z_dim=128, max_batch=B, max_chunk=7400), params)
+    x = synthetic_images((B,) + tuple(ocfg.x_shape), seed=0).astype(np.float32)
+    eps = np.random.RandomState(3).normal(size=(K, B, ocfg.z_dim)).astype(np.float32)
+    xi_raw, beta, log_Z = 0.0, 0.0, 1.0                             # the bench's scalars (SURVEY 8d)
+    m.set_scalars(xi_raw, beta, log_Z)
+    got = m.is_nll(x, K, x_origin=x, eps=eps, per_sample=True)
+    g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
+    m.close()
+    p32 = {k: v.astype(np.float32) for k, v in params.items()}
+    for b in (0, 36):
+        # the oracle in slices of 100 samples (the nets treat samples independently; bounds its memory), then the
+        # reference's reductions over all K (variational/evaluation.py:9-39, objectives.py:9-42)
+        parts = [O.eval_batch(ocfg, p32, x[b:b + 1], x[b:b + 1], eps[k0:k0 + 100, b:b + 1], xi_raw=xi_raw, beta=beta, log_Z=log_Z)
+                 for k0 in range(0, K, 100)]
+        cat = lambda key: np.concatenate([p[key] for p in parts], axis=0).astype(np.float64)
+        log_px, log_q, log_pn, d_g, energy, sq = (cat(k) for k in ('log_px', 'log_q', 'log_pn', 'd_g', 'energy', 'sq_err'))
+        lja = log_px - energy - max(log_Z, -20.0)
+        want = {'ele_test_ll': O.importance_sampling_log_likelihood(log_px + log_pn, log_q, 0),
+                'ele_test_lb': O.elbo_objective(log_px + log_pn, log_q, 0),
+                'ele_adv_test_ll': O.importance_sampling_log_likelihood(lja, log_q, 0),
+                'ele_adv_test_lb': O.elbo_objective(lja, log_q, 0)}
+        for name in want:
+            rel = abs(g[name][b] - float(want[name][0])) / abs(float(want[name][0]))
+            assert rel < NLL_RTOL, (b, name, g[name][b], want[name][0])
+        d_err = np.abs(g['d_g'][:, b] - d_g[:, 0])
+        assert d_err.max() < 1e-2, (b, d_err.max(), d_err.mean())           # all 1000 samples of the image
+        assert abs(g['ele_real_energy'][b] - float(parts[0]['ele_real_energy'][0])) < 1e-2
+        lp_err = np.abs(g['log_px'][:, b] - log_px[:, 0]) / np.abs(log_px[:, 0])
+        assert lp_err.max() < NLL_RTOL, (b, lp_err.max())
+        assert abs(g['ele_test_mse'][b] - sq[:, 0].min()) < 2e-2 * sq[:, 0].min()
 
 
 def test_k1_and_bad_shapes_are_rejected():

@@ -8,14 +8,30 @@ import numpy as np
 import pytest
 
 import oracle as O
-from helpers import bf16_round, pad_channels
+from helpers import bf16_round, exact16, pad_channels
 
 pytestmark = pytest.mark.gpu
+
+DT = 'fp16'     # the 16-bit operand format under test (set per test by the fixture below)
+
+
+@pytest.fixture(autouse=True, params=['fp16', 'bf16'])
+def operand_format(request, monkeypatch):
+    """Every layer test runs in both operand formats of the library (op16.h): fp16 (default) and bf16.  The inputs are
+    bf16-exact numbers of moderate magnitude, hence exact in fp16 as well."""
+    import sys
+    monkeypatch.setattr(sys.modules[__name__], 'DT', request.param)
+    yield request.param
 
 
 def _torch():
     import torch
     return torch
+
+
+def _td():
+    import torch
+    return torch.float16 if DT == 'fp16' else _td()
 
 
 def _check(got, want, tol=2e-4):
@@ -51,12 +67,12 @@ def test_conv_layers(transpose, k, stride, N, H, W, cin, cout):
     torch = _torch()
     import apvae
     rs = np.random.RandomState(k + 10 * stride + cin + cout)
-    x = bf16_round(rs.normal(size=(N, H, W, cin)))
+    x = exact16(rs.normal(size=(N, H, W, cin)))
     shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
-    kern = bf16_round(rs.normal(size=shp) / np.sqrt(k * k * cin))
+    kern = exact16(rs.normal(size=shp) / np.sqrt(k * k * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
     fn = apvae.deconv2d if transpose else apvae.conv2d
-    got = fn(torch.tensor(x, device='cuda'), kern, bias, stride).cpu().numpy()
+    got = fn(torch.tensor(x, device='cuda'), kern, bias, stride, dtype=DT).cpu().numpy()
     ofn = O.deconv2d if transpose else O.conv2d
     want = ofn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), stride)
     assert got.shape == want.shape
@@ -68,10 +84,10 @@ def test_dense(n, fin, fout):
     torch = _torch()
     import apvae
     rs = np.random.RandomState(fin + fout)
-    x = bf16_round(rs.normal(size=(n, fin)))
-    k = bf16_round(rs.normal(size=(fin, fout)) / np.sqrt(fin))
+    x = exact16(rs.normal(size=(n, fin)))
+    k = exact16(rs.normal(size=(fin, fout)) / np.sqrt(fin))
     b = rs.normal(size=fout).astype(np.float32)
-    got = apvae.dense(torch.tensor(x, device='cuda'), k, b).cpu().numpy()
+    got = apvae.dense(torch.tensor(x, device='cuda'), k, b, dtype=DT).cpu().numpy()
     _check(got, x.astype(np.float64) @ k.astype(np.float64) + b)
 
 
@@ -79,10 +95,10 @@ def test_tanh_activation():
     torch = _torch()
     import apvae
     rs = np.random.RandomState(0)
-    x = bf16_round(rs.normal(size=(2, 32, 32, 96)))
-    k = bf16_round(rs.normal(size=(1, 1, 96, 3)) * 0.2)
+    x = exact16(rs.normal(size=(2, 32, 32, 96)))
+    k = exact16(rs.normal(size=(1, 1, 96, 3)) * 0.2)
     b = rs.normal(size=3).astype(np.float32)
-    got = apvae.conv2d(torch.tensor(x, device='cuda'), k, b, 1, 'tanh').cpu().numpy()
+    got = apvae.conv2d(torch.tensor(x, device='cuda'), k, b, 1, 'tanh', dtype=DT).cpu().numpy()
     _check(got, O.conv2d(x.astype(np.float64), k.astype(np.float64), b.astype(np.float64), 1, np.tanh))
 
 
@@ -94,16 +110,16 @@ def test_epilogue_residual_mask_and_bf16_outputs():
     from apvae import _lib
     rs = np.random.RandomState(5)
     cap, n_valid, H, cin, cout = 6, 5, 8, 32, 48
-    x = bf16_round(rs.normal(size=(cap, H, H, cin)))
-    kern = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.1)
+    x = exact16(rs.normal(size=(cap, H, H, cin)))
+    kern = exact16(rs.normal(size=(3, 3, cin, cout)) * 0.1)
     bias = rs.normal(size=cout).astype(np.float32)
-    res = bf16_round(rs.normal(size=(cap, H, H, cout)))
-    msk = bf16_round(rs.normal(size=(cap, H, H, cout)))
-    plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=kern, bias=bias)], cap)
+    res = exact16(rs.normal(size=(cap, H, H, cout)))
+    msk = exact16(rs.normal(size=(cap, H, H, cout)))
+    plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=kern, bias=bias)], cap, dtype=DT)
     dev = 'cuda'
-    t = lambda a: torch.tensor(a, device=dev).to(torch.bfloat16)
-    out_raw = torch.full((cap, H, H, cout), 7.0, dtype=torch.bfloat16, device=dev)
-    out_act = torch.full((cap, H, H, cout), 7.0, dtype=torch.bfloat16, device=dev)
+    t = lambda a: torch.tensor(a, device=dev).to(_td())
+    out_raw = torch.full((cap, H, H, cout), 7.0, dtype=_td(), device=dev)
+    out_act = torch.full((cap, H, H, cout), 7.0, dtype=_td(), device=dev)
     out_f32 = torch.full((cap, H, H, cout), 7.0, dtype=torch.float32, device=dev)
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, out_act=out_act, out_f32=out_f32,
              f32_cols=cout, res=t(res), res_mode=_lib.RES_SAME, mask=t(msk), bf16_zero_from=40)
@@ -127,11 +143,11 @@ def test_epilogue_even_pixel_residual():
     from apvae import _lib
     rs = np.random.RandomState(9)
     n, H, c = 3, 8, 64
-    r = bf16_round(rs.normal(size=(n, 2 * H, 2 * H, c)))
-    kern = bf16_round(rs.normal(size=(3, 3, c, c)) * 0.05)
-    sc_low = bf16_round(rs.normal(size=(n, H, H, c)))
-    plan = Plan([dict(src=0, transpose=True, in_h=2 * H, in_w=2 * H, kernel=kern)], n)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    r = exact16(rs.normal(size=(n, 2 * H, 2 * H, c)))
+    kern = exact16(rs.normal(size=(3, 3, c, c)) * 0.05)
+    sc_low = exact16(rs.normal(size=(n, H, H, c)))
+    plan = Plan([dict(src=0, transpose=True, in_h=2 * H, in_w=2 * H, kernel=kern)], n, dtype=DT)
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
     out = torch.zeros((n, 2 * H, 2 * H, c), dtype=torch.float32, device='cuda')
     plan.run([t(r)], n, out_f32=out, f32_cols=c, res=t(sc_low), res_mode=_lib.RES_EVEN)
     want = O.deconv2d(r.astype(np.float64), kern.astype(np.float64), None, 1)
@@ -144,14 +160,14 @@ def test_fused_shortcut_gpu():
     from apvae.plan import Plan
     rs = np.random.RandomState(7)
     n, H, cin, cout = 4, 16, 128, 256
-    r = bf16_round(rs.normal(size=(n, H, H, cin)))
-    x = bf16_round(rs.normal(size=(n, H, H, cin)))
-    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.03)
-    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.1)
+    r = exact16(rs.normal(size=(n, H, H, cin)))
+    x = exact16(rs.normal(size=(n, H, H, cin)))
+    k1 = exact16(rs.normal(size=(3, 3, cin, cout)) * 0.03)
+    ks = exact16(rs.normal(size=(1, 1, cin, cout)) * 0.1)
     b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
     plan = Plan([dict(src=0, stride=2, in_h=H, in_w=H, kernel=k1, bias=b1),
-                 dict(src=1, stride=2, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+                 dict(src=1, stride=2, in_h=H, in_w=H, kernel=ks, bias=bs)], n, dtype=DT)
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
     out = torch.zeros((n, H // 2, H // 2, cout), dtype=torch.float32, device='cuda')
     plan.run([t(r), t(x)], n, out_f32=out, f32_cols=cout)
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 2) + \
@@ -189,15 +205,15 @@ def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster, monkeypat
     monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
     monkeypatch.setenv('APVAE_PATCH_CLUSTER', str(cluster))
     rs = np.random.RandomState(k + cin + cout + N)
-    x = bf16_round(rs.normal(size=(N, H, W, cin)))
+    x = exact16(rs.normal(size=(N, H, W, cin)))
     shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
-    kern = bf16_round(rs.normal(size=shp) / np.sqrt(k * k * cin))
+    kern = exact16(rs.normal(size=shp) / np.sqrt(k * k * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, transpose=transpose, in_h=H, in_w=W, kernel=kern, bias=bias)], N)
+    plan = Plan([dict(src=0, transpose=transpose, in_h=H, in_w=W, kernel=kern, bias=bias)], N, dtype=DT)
     if plan.info.patch != 1:
         pytest.skip('forced accumulator count does not fit the shared-memory rings')
     assert plan.info.patch_macc == macc and plan.info.patch_cluster == cluster
-    src = torch.tensor(pad_channels(x, pad16(cin)), device='cuda').to(torch.bfloat16)
+    src = torch.tensor(pad_channels(x, pad16(cin)), device='cuda').to(_td())
     out = torch.zeros((N, H, W, cout), dtype=torch.float32, device='cuda')
     plan.run([src], N, out_f32=out, f32_cols=cout)
     ofn = O.deconv2d if transpose else O.conv2d
@@ -211,19 +227,19 @@ def test_patch_kernel_matches_tap_kernel_bitwise_inputs(monkeypatch):
     from apvae.plan import Plan
     rs = np.random.RandomState(21)
     n, H, cin, cout = 6, 32, 32, 64
-    r = bf16_round(rs.normal(size=(n, H, H, cin)))
-    x = bf16_round(rs.normal(size=(n, H, H, cin)))
-    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.06)
-    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.2)
+    r = exact16(rs.normal(size=(n, H, H, cin)))
+    x = exact16(rs.normal(size=(n, H, H, cin)))
+    k1 = exact16(rs.normal(size=(3, 3, cin, cout)) * 0.06)
+    ks = exact16(rs.normal(size=(1, 1, cin, cout)) * 0.2)
     b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
     outs = {}
     for mode in ('0', '1'):
         monkeypatch.setenv('APVAE_PATCH', mode)
-        plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
+        plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n, dtype=DT)
         assert plan.info.patch == int(mode)
         o32 = torch.zeros((n, H, H, cout), dtype=torch.float32, device='cuda')
-        oact = torch.zeros((n, H, H, cout), dtype=torch.bfloat16, device='cuda')
+        oact = torch.zeros((n, H, H, cout), dtype=_td(), device='cuda')
         plan.run([t(r), t(x)], n - 1, out_f32=o32, f32_cols=cout, out_act=oact)
         outs[mode] = (o32.cpu().numpy(), oact.float().cpu().numpy())
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
@@ -271,23 +287,23 @@ def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two
     if macc:
         monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
     rs = np.random.RandomState(H + cin + cout + len(res))
-    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
+    x = exact16(rs.normal(size=(cap, H, W, cin)))
+    kern = exact16(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap)
+    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT)
     assert plan.info.patch == 1
     npad = pad16(cout)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
-    out_raw = torch.full((cap, H, W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
-    out_act = torch.full((cap, H, W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
+    out_raw = torch.full((cap, H, W, npad), 7.0, dtype=_td(), device='cuda')
+    out_act = torch.full((cap, H, W, npad), 7.0, dtype=_td(), device='cuda')
     want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
     kw = {}
     if res == 'same':
-        r = bf16_round(rs.normal(size=(cap, H, W, npad)))
+        r = exact16(rs.normal(size=(cap, H, W, npad)))
         want = want + r[..., :cout]
         kw = dict(res=t(r), res_mode=_lib.RES_SAME)
     elif res == 'even':
-        r = bf16_round(rs.normal(size=(cap, H // 2, W // 2, npad)))
+        r = exact16(rs.normal(size=(cap, H // 2, W // 2, npad)))
         want[:, ::2, ::2, :] += r[..., :cout]
         kw = dict(res=t(r), res_mode=_lib.RES_EVEN)
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, out_act=out_act, **kw)
@@ -329,14 +345,14 @@ def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, o
     monkeypatch.setenv('APVAE_PATCH', '1')
     monkeypatch.setenv('APVAE_PATCH_MERGE', merge)
     rs = np.random.RandomState(k + H + cin + cout)
-    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
+    x = exact16(rs.normal(size=(cap, H, W, cin)))
+    kern = exact16(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], cap)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT)
     npad = pad16(cout)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
-    out_act = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
-    out_raw = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=torch.bfloat16, device='cuda') if outs != 'act' else None
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
+    out_act = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=_td(), device='cuda')
+    out_raw = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=_td(), device='cuda') if outs != 'act' else None
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, out_act=out_act)
     torch.cuda.synchronize()
     want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
@@ -373,25 +389,25 @@ def test_stride2_conv_on_patch_kernel(k, H, W, cin, cout, shortcut, n_valid, cap
     monkeypatch.setenv('APVAE_PATCH', '1')
     monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))
     rs = np.random.RandomState(k + H + cin + cout)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
-    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(k, k, cin, cout)) / np.sqrt(k * k * cin))
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
+    x = exact16(rs.normal(size=(cap, H, W, cin)))
+    kern = exact16(rs.normal(size=(k, k, cin, cout)) / np.sqrt(k * k * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
     terms = [dict(src=0, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)]
     srcs = [t(pad_channels(x, pad16(cin)))]
     want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
     if shortcut:
-        x2 = bf16_round(rs.normal(size=(cap, H, W, cin)))
-        ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) / np.sqrt(cin))
+        x2 = exact16(rs.normal(size=(cap, H, W, cin)))
+        ks = exact16(rs.normal(size=(1, 1, cin, cout)) / np.sqrt(cin))
         bs = rs.normal(size=(cout,)).astype(np.float32)
         terms.append(dict(src=1, stride=2, in_h=H, in_w=W, kernel=ks, bias=bs))
         srcs.append(t(pad_channels(x2, pad16(cin))))
         want = want + O.conv2d(x2.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
-    plan = Plan(terms, cap)
+    plan = Plan(terms, cap, dtype=DT)
     assert plan.info.patch == 1 and plan.info.patch_s2d == 1
     npad = pad16(cout)
-    out_raw = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=torch.bfloat16, device='cuda')
-    out_act = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    out_raw = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=_td(), device='cuda')
+    out_act = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=_td(), device='cuda')
     plan.run(srcs, n_valid, out_raw=out_raw, out_act=out_act)
     torch.cuda.synchronize()
     raw = out_raw.float().cpu().numpy()
@@ -431,27 +447,27 @@ def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_
     monkeypatch.setenv('APVAE_PATCH', '1')
     monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))
     rs = np.random.RandomState(H + cin + cout + len(res))
-    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
+    x = exact16(rs.normal(size=(cap, H, W, cin)))
+    kern = exact16(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap)
+    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT)
     assert plan.info.patch == 1
     npad = pad16(cout)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
-    mask = bf16_round(rs.normal(size=(cap, H, W, npad)))
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
+    mask = exact16(rs.normal(size=(cap, H, W, npad)))
     mask[rs.uniform(size=mask.shape) < 0.1] = 0.0                 # lrelu'(0) = alpha
     want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
     want = want * np.where(mask[..., :cout] > 0, 1.0, 0.2)
     kw = {}
     if res == 'same':
-        r = bf16_round(rs.normal(size=(cap, H, W, npad)))
+        r = exact16(rs.normal(size=(cap, H, W, npad)))
         want = want + r[..., :cout]
         kw = dict(res=t(r), res_mode=_lib.RES_SAME)
     elif res == 'even':
-        r = bf16_round(rs.normal(size=(cap, H // 2, W // 2, npad)))
+        r = exact16(rs.normal(size=(cap, H // 2, W // 2, npad)))
         want[:, ::2, ::2, :] += r[..., :cout]
         kw = dict(res=t(r), res_mode=_lib.RES_EVEN)
-    out_raw = torch.full((cap, H, W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    out_raw = torch.full((cap, H, W, npad), 7.0, dtype=_td(), device='cuda')
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, mask=t(mask), **kw)
     torch.cuda.synchronize()
     raw = out_raw.float().cpu().numpy()
@@ -461,7 +477,7 @@ def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_
     assert np.all(raw[keep:] == 7.0)
     # same op through the generic epilogue (APVAE_FAST_MASK=0): same values up to the bf16 rounding of the output
     monkeypatch.setenv('APVAE_FAST_MASK', '0')
-    out2 = torch.full((cap, H, W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    out2 = torch.full((cap, H, W, npad), 7.0, dtype=_td(), device='cuda')
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out2, mask=t(mask), **kw)
     torch.cuda.synchronize()
     assert np.abs(out2.float().cpu().numpy()[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
@@ -485,13 +501,13 @@ def test_stride2_deconv_phases_with_mask(k, H, W, cin, cout, n_valid, cap, monke
     from apvae.plan import Plan, pad16
     monkeypatch.setenv('APVAE_PATCH', '1')
     rs = np.random.RandomState(k + H + cin + cout)
-    x = bf16_round(rs.normal(size=(cap, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
-    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=None)], cap)
+    x = exact16(rs.normal(size=(cap, H, W, cin)))
+    kern = exact16(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=None)], cap, dtype=DT)
     npad = pad16(cout)
-    t = lambda a: torch.tensor(a, device='cuda').to(torch.bfloat16)
-    mask = bf16_round(rs.normal(size=(cap, 2 * H, 2 * W, npad)))
-    out_raw = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=torch.bfloat16, device='cuda')
+    t = lambda a: torch.tensor(a, device='cuda').to(_td())
+    mask = exact16(rs.normal(size=(cap, 2 * H, 2 * W, npad)))
+    out_raw = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=_td(), device='cuda')
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out_raw, mask=t(mask))
     torch.cuda.synchronize()
     want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), np.zeros(cout), 2) * np.where(mask[..., :cout] > 0, 1.0, 0.2)

@@ -4,10 +4,11 @@ apvae_is_nll / apvae_prior_stats / apvae_sample_images).
 
 Same synthetic weights (glorot-normal kernels INCLUDING the heads the reference
 zero-initialises, N(0,0.1) biases, seed 1234), same synthetic images and the same
-fed-in noise on both sides.  Tolerances are BASELINE.json's:
-per-image NLL within 1e-3 relative; energies D(.) within 1e-2 absolute (bf16 operands,
-fp32 accumulation).  The CUDA path is bf16-in / fp32-accumulate per layer, the oracle
-is float64 end to end.
+fed-in noise on both sides.  Tolerances are BASELINE.json's, written literally:
+per-image NLL within 1e-3 relative; energies D(.) and samples within 1e-2 absolute (16-bit
+operands, fp32 accumulation) — asserted on the MAXIMUM error of every case.  The CUDA path
+is fp16-in / fp32-accumulate per layer by default (csrc/op16.h; `operand_dtype='bf16'` is the
+wide-range alternative, covered by test_bf16_operand_format), the oracle is float64 end to end.
 """
 import numpy as np
 import pytest
@@ -18,14 +19,12 @@ from helpers import synthetic_images
 pytestmark = pytest.mark.gpu
 
 NLL_RTOL = 1e-3       # BASELINE.json north_star: per-image NLL within 1e-3 nats relative
-ENERGY_ATOL = 1e-2    # energies within 1e-2 abs in bf16: asserted on the MEAN abs error; the MAX abs error
-ENERGY_MAX_ATOL = 3e-2  # over a case is allowed 3e-2 (measured 0.6e-2 .. 2.1e-2 with random-init weights: every
-                        # conv input AND weight is rounded to bf16, D_psi is 12 convs deep; see DESIGN.md "Parity")
+ENERGY_ATOL = 1e-2    # ... energies / samples within 1e-2 abs: every element, not the mean
 
 
-def _energy_close(got, want, mean_atol=ENERGY_ATOL):
+def _energy_close(got, want, atol=ENERGY_ATOL):
     err = np.abs(np.asarray(got, dtype=np.float64) - want)
-    assert err.mean() < mean_atol and err.max() < ENERGY_MAX_ATOL, (err.mean(), err.max(), got, want)
+    assert err.max() < atol, (err.mean(), err.max(), got, want)
 
 CASES = {
     'A128': ('A', dict(z_dim=128), 3, 5),
@@ -74,8 +73,8 @@ def test_networks_match_oracle(case):
     x, x_origin, eps = _inputs(ocfg, B, K)
     mu_o, ls_o = O.q_net(ocfg, params, x_origin)
     mu, ls = m.encode(x_origin)
-    assert np.abs(mu.cpu().numpy() - mu_o).max() < 3e-2 * max(1.0, np.abs(mu_o).max())
-    assert np.abs(ls.cpu().numpy() - ls_o).max() < 3e-2 * max(1.0, np.abs(ls_o).max())
+    assert np.abs(mu.cpu().numpy() - mu_o).max() < 5e-3 * max(1.0, np.abs(mu_o).max())
+    assert np.abs(ls.cpu().numpy() - ls_o).max() < 5e-3 * max(1.0, np.abs(ls_o).max())
     z = (mu_o + np.exp(ls_o) * eps[0])
     if arch == 'M':
         xm_o = O.G_theta(ocfg, params, z)
@@ -83,9 +82,9 @@ def test_networks_match_oracle(case):
     else:
         xm_o, xs_o = O.G_theta(ocfg, params, z, return_std=True)
         xm, xs = m.decode(z, return_std=True)
-        assert np.abs(xs.cpu().numpy() - xs_o).max() < 3e-2 * max(1.0, np.abs(xs_o).max())
-    xerr = np.abs(xm.cpu().numpy() - xm_o)          # tanh output in [-1, 1] after 16 bf16-operand conv layers
-    assert xerr.max() < 6e-2 and xerr.mean() < 6e-3, (xerr.max(), xerr.mean())
+        assert np.abs(xs.cpu().numpy() - xs_o).max() < 5e-3 * max(1.0, np.abs(xs_o).max())
+    xerr = np.abs(xm.cpu().numpy() - xm_o)          # tanh output in [-1, 1] after 16 conv layers: "samples within 1e-2"
+    assert xerr.max() < ENERGY_ATOL and xerr.mean() < 1e-3, (xerr.max(), xerr.mean())
     # energies: D(x) on images, D(G(z)) on latents
     d_o = O.D_psi(ocfg, params, x_origin)
     d = m.energy_of_images(x_origin).cpu().numpy()
@@ -93,12 +92,16 @@ def test_networks_match_oracle(case):
     dg_o = O.D_psi(ocfg, params, xm_o)
     dg = m.energy_of_latents(z).cpu().numpy()
     _energy_close(dg, dg_o)
-    # uint8 samples: 128 grey levels per unit of x_mean -> the x_mean tolerance above in grey levels
+    # uint8 samples (byte work): 128 grey levels per unit of x_mean, so the 1e-2 tolerance is 1.28 levels: at most one
+    # level apart, and only where the oracle's pre-rounding value lies within the x_mean error of a rounding boundary
     u8 = m.sample_images(z).cpu().numpy().astype(np.int32)
     u8_o = O.sample_images(ocfg, params, z).astype(np.int32)
     assert u8.shape == u8_o.shape
-    assert np.abs(u8 - u8_o).max() <= 8
-    assert np.mean(np.abs(u8 - u8_o)) < 0.8
+    assert np.abs(u8 - u8_o).max() <= 1
+    pre = np.clip(256.0 * xm_o / 2 + 127.5, 0, 255).reshape(u8.shape)
+    off = u8 != u8_o
+    assert off.mean() < 0.1
+    assert np.all(np.abs(pre[off] - np.floor(pre[off]) - 0.5) < 128 * ENERGY_ATOL)
     m.close()
 
 
@@ -134,7 +137,7 @@ def test_is_nll_matches_oracle(case):
     lz = M + np.log(np.sum(sm * np.exp(mx - M)) / (K * B)) + np.log(ocfg.len_train)
     # -energy carries w * xi * D(G(z)): the energy tolerance scaled by the pull-back weight
     w_xi = ocfg.pull_back_energy_weight * O.sigmoid(xi_raw)
-    assert abs(lz - want['another_log_Z']) < NLL_RTOL * abs(want['another_log_Z']) + w_xi * ENERGY_MAX_ATOL
+    assert abs(lz - want['another_log_Z']) < NLL_RTOL * abs(want['another_log_Z']) + w_xi * ENERGY_ATOL
     m.close()
 
 
@@ -243,25 +246,20 @@ def test_energy_gradient_matches_oracle(case):
     e_o, g_o, p_o = O.energy_and_grad(ocfg, params, z, xi_raw=xi_raw)
     e, g, p = [t.cpu().numpy().astype(np.float64) for t in m.energy_grad(z)]
     w_xi = ocfg.pull_back_energy_weight / (1 + np.exp(-xi_raw))
-    # D(G(z)) of 3-5 chains.  Rounding the KERNELS to bf16 shifts every chain's energy by a common amount (D_psi ends in
-    # two activation-free dense layers, so d D / d W is nearly the same for every input): against the float64 oracle on
-    # the exact kernels the per-case mean error measured 0.1e-2 .. 1.1e-2 (arch B celebA worst), so the mean bound here
-    # is 1.5e-2 and the 1e-2 bound is asserted against the oracle on the bf16-rounded kernels the library holds (below).
-    _energy_close(p, p_o, mean_atol=1.5e-2)
-    assert np.abs(e - e_o).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
-    # the D(G(z)) part (the z part is exact) as a relative L2 error per chain.  With random-init weights the gradient is
-    # dominated by leaky-relu sign patterns: rounding ONLY the kernels to bf16 already moves the float64 oracle's
-    # gradient by ~6 % (arch A), so the comparison that isolates the kernels is against the oracle run on the
-    # bf16-rounded kernels the library actually holds.
-    from helpers import bf16_round
-    pb = {k: (bf16_round(v) if k.endswith('kernel') else v) for k, v in params.items()}
+    # D(G(z)) of 3-5 chains against the float64 oracle on the exact kernels: north_star's 1e-2, every chain
+    _energy_close(p, p_o)
+    assert np.abs(e - e_o).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(e_o).max()
+    # the D(G(z)) part (the z part is exact) as a relative L2 error per chain, against the oracle on the exact kernels
+    # (rel_o) and on the fp16-rounded kernels the library actually holds (rel_b: isolates activation rounding)
+    from helpers import fp16_round
+    pb = {k: (fp16_round(v).astype(np.float64) if k.endswith('kernel') else v) for k, v in params.items()}
     _, g_b, p_b = O.energy_and_grad(ocfg, pb, z, xi_raw=xi_raw)
     _energy_close(p, p_b)
     gz, gz_b, gz_o = (g - z) / w_xi, (g_b - z) / w_xi, (g_o - z) / w_xi
     rel_b = np.linalg.norm(gz - gz_b, axis=-1) / np.linalg.norm(gz_b, axis=-1)
     rel_o = np.linalg.norm(gz - gz_o, axis=-1) / np.linalg.norm(gz_o, axis=-1)
-    assert rel_b.max() < 1e-1, (rel_b, rel_o)         # measured 3-7 % (bf16 activations and gradients through ~60 layers)
-    assert rel_o.max() < 1.5e-1, (rel_b, rel_o)
+    assert rel_b.max() < 2e-2, (rel_b, rel_o)         # fp16 activations and gradients through ~60 layers
+    assert rel_o.max() < 3e-2, (rel_b, rel_o)
     m.close()
 
 
@@ -270,9 +268,10 @@ def test_mala_matches_oracle(case):
     """EnergyDistribution.sample (dmm_cifar10.py:179-239) with fed-in noise.  The uniform draws are chosen with a
     margin around the oracle's acceptance ratios so that no accept / reject decision is borderline; both outcomes
     occur.  north_star: samples within 1e-2 abs.
-    bf16 operands leave ~5e-3 of error on D(G(z)); the acceptance ratio sees it multiplied by
-    pull_back_energy_weight * xi (500 at the reference default), so this bf16 test runs the chain at weight 2
-    (same code path; the reference-default weight is covered by the split-precision mode)."""
+    16-bit operands leave ~1e-3 of error on D(G(z)); the acceptance ratio sees it multiplied by
+    pull_back_energy_weight * xi (500 at the reference default), so the single-pass test runs the chain at weight 2
+    (same code path); the reference-default weight is covered by the split-precision mode
+    (test_precise_mala_at_the_reference_energy_weight)."""
     arch, kw, _ = GRAD_CASES[case]
     ocfg, params, cfg, m = _make(arch, dict(kw, pull_back_energy_weight=2.0), max_chunk=4, enable_grad=True,
                                  pull_back_energy_weight=2.0)
@@ -297,8 +296,8 @@ def test_mala_matches_oracle(case):
     ge = out['history_e_z'].cpu().numpy().reshape(steps, n)
     gp = out['history_pure_e_z'].cpu().numpy().reshape(steps, n)
     gr = out['history_ratio'].cpu().numpy().reshape(steps, n)
-    assert np.abs(gp - np.stack(hp).reshape(steps, n)).max() < ENERGY_MAX_ATOL
-    assert np.abs(ge - np.stack(he).reshape(steps, n)).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(np.stack(he)).max()
+    assert np.abs(gp - np.stack(hp).reshape(steps, n)).max() < ENERGY_ATOL
+    assert np.abs(ge - np.stack(he).reshape(steps, n)).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(np.stack(he)).max()
     assert np.abs(gr - np.stack(hr).reshape(steps, n)).max() < 0.1
     m.close()
 
@@ -386,7 +385,7 @@ def test_script_call_surface_reads_like_the_reference():
     test_chain = test_q_net.chain(p_net, latent_axis=0, observed={'x': x}, n_z=K, beta=beta, log_Z=log_Z)
     npf = lambda t: t.cpu().numpy().astype(np.float64)
     z = npf(test_q_net['z'].tensor)
-    assert z.shape == (K, B, ocfg.z_dim) and np.abs(z - want['z']).max() < 3e-2 * max(1.0, np.abs(want['z']).max())
+    assert z.shape == (K, B, ocfg.z_dim) and np.abs(z - want['z']).max() < 5e-3 * max(1.0, np.abs(want['z']).max())
     ll = npf(test_chain.vi.evaluation.is_loglikelihood())
     assert (np.abs(ll - want['ele_test_ll']) / np.abs(want['ele_test_ll'])).max() < NLL_RTOL
     lb = npf(test_chain.vi.lower_bound.elbo())
@@ -395,13 +394,13 @@ def test_script_call_surface_reads_like_the_reference():
     assert np.abs(recon - want['log_px']).max() < NLL_RTOL * np.abs(want['log_px']).max()
     lp = test_chain.model['z'].log_prob()
     w_xi = ocfg.pull_back_energy_weight * O.sigmoid(xi_raw)
-    assert np.abs(npf(lp.energy) - want['energy']).max() < w_xi * ENERGY_MAX_ATOL + 1e-3 * np.abs(want['energy']).max()
+    assert np.abs(npf(lp.energy) - want['energy']).max() < w_xi * ENERGY_ATOL + 1e-3 * np.abs(want['energy']).max()
     _energy_close(npf(lp.pure_energy), want['d_g'])
     adv = npf(test_chain.adv_is_loglikelihood())
     assert (np.abs(adv - want['ele_adv_test_ll']) / np.abs(want['ele_adv_test_ll'])).max() < NLL_RTOL
     _energy_close(npf(s.D_psi(x_origin)), want['ele_real_energy'])
     xm = npf(s.G_theta(want['z'][0]))
-    assert np.abs(xm - want['x_mean'][0]).max() < 6e-2
+    assert np.abs(xm - want['x_mean'][0]).max() < ENERGY_ATOL
     with pytest.raises(ValueError):
         q_net(x_origin, n_z=None)
     m.close()
@@ -428,15 +427,15 @@ def test_energy_distribution_class_matches_oracle():
     e_o, _, p_o = O.energy_and_grad(ocfg, params, z0, xi_raw=xi_raw)
     _energy_close(npf(lp.pure_energy), p_o)
     w_xi = ocfg.pull_back_energy_weight * xi
-    assert np.abs(npf(lp.energy) - e_o).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
-    assert np.abs(npf(lp.log_energy_prob) - (-e_o + 20.0)).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
+    assert np.abs(npf(lp.energy) - e_o).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(e_o).max()
+    assert np.abs(npf(lp.log_energy_prob) - (-e_o + 20.0)).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(e_o).max()
     want_pn = -0.5 * (z0 ** 2).sum(-1) - 0.5 * ocfg.z_dim * math.log(2 * math.pi)
     assert np.abs(npf(lp.tensor) - want_pn).max() < 1e-3
     t = pz.sample()
     assert tuple(t.tensor.shape) == (n, ocfg.z_dim)
     assert tuple(t.history_e_z.shape) == (steps, n) and tuple(t.history_ratio.shape) == (steps, n)
     # step 0 starts from initial_z: its energies are the oracle's at z0
-    assert np.abs(npf(t.history_e_z)[0] - e_o).max() < w_xi * ENERGY_MAX_ATOL + 1e-4 * np.abs(e_o).max()
+    assert np.abs(npf(t.history_e_z)[0] - e_o).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(e_o).max()
     _energy_close(npf(t.history_pure_e_z)[0], p_o)
     r = npf(t.history_ratio)
     assert np.all(r >= 0) and np.all(r <= 1)
@@ -458,10 +457,10 @@ def test_image_energy_gradient_ood_indicator(case):
     d, g, s = [t.cpu().numpy().astype(np.float64) for t in m.image_energy_grad(x_origin)]
     _energy_close(d, d_o)
     rel = np.sqrt(((g - g_o) ** 2).sum(axis=(1, 2, 3)) / (g_o ** 2).sum(axis=(1, 2, 3)))
-    assert rel.max() < 1e-1, rel                                   # bf16 operands through 12 conv layers and back
+    assert rel.max() < 2e-2, rel                                   # fp16 operands through 12 conv layers and back
     n_o = (g_o ** 2).sum(axis=(1, 2, 3))
     assert np.abs(s - (g ** 2).sum(axis=(1, 2, 3))).max() < 1e-4 * n_o.max()      # the reduction itself
-    assert (np.abs(s - n_o) / n_o).max() < 2e-1, (s, n_o)
+    assert (np.abs(s - n_o) / n_o).max() < 3e-2, (s, n_o)
     m.close()
 
 
@@ -538,3 +537,188 @@ def test_latent_gan_initial_z_matches_oracle(case):
     with pytest.raises(Exception):
         m2.latent_gan(4)
     m.close(); m2.close()
+
+
+# ----------------------------------------------------------------------------- round-2 additions
+def test_arch_m_with_the_reference_tanh_head():
+    """Arch M exactly as the script builds it (dmm_bernouli_fashion.py:517-521,619-626): the mean head is a zero-centred
+    tanh, so about half of the pixels sit on clip(x_mean, 1e-7, .) — the branch the recentred cases above never reach.
+    Where the clip is active log p is flat in x_mean; the whole-model sum is ill-conditioned only for the few pixels
+    whose mean lies within the x_mean error of the clip threshold with x = 1 (log p jumps from log(1e-7) to log(mean)),
+    hence the per-image gate is 5e-3 relative here; the clip arithmetic itself is pinned exactly by
+    test_kats_gpu.py::test_cuda_bernoulli_clip_branch."""
+    from apvae.model import ExpConfig, Model
+    ocfg = O.OracleConfig('M')
+    params = O.init_weights(ocfg)
+    cfg = ExpConfig('M', z_dim=ocfg.z_dim, max_batch=8, max_chunk=8)
+    m = Model(cfg, params)
+    B, K = 4, 6
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    want = O.eval_batch(ocfg, params, x, x_origin, eps)
+    assert (want['x_mean'] < 1e-7).mean() > 0.3                   # the clip IS active on a large share of the pixels
+    got = m.is_nll(x, K, x_origin=x_origin, eps=eps, per_sample=True)
+    g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
+    for name in ('ele_test_ll', 'ele_test_lb', 'ele_adv_test_ll', 'ele_adv_test_lb'):
+        rel = np.abs(g[name] - want[name]) / np.abs(want[name])
+        assert rel.max() < 5e-3, (name, g[name], want[name])
+    _energy_close(g['d_g'], want['d_g'])
+    m.close()
+
+
+def test_evaluator_reports_all_eleven_metrics():
+    """spt.Evaluator's metric dict (dmm_cifar10.py:1131-1136): test_nll, test_lb, adv_test_nll, adv_test_lb,
+    reconstruct_energy, real_energy, pd_energy, pn_energy, test_recon, kl_adv_and_gaussian, test_mse — the prior
+    branch (test_pn_net, :883,915-927) evaluated once per mini-batch, everything size-weighted over ragged batches
+    (trainer/evaluator.py:249-254) — against the float64 oracle with the same fed-in noise."""
+    from apvae.evaluation import Evaluator
+    arch, kw, _, _ = CASES['A128']
+    ocfg, params, cfg, m = _make(arch, kw)
+    N, K, bs, Kp = 7, 4, 3, 9                                       # batches of 3, 3, 1
+    x = synthetic_images((N,) + tuple(ocfg.x_shape), seed=0).astype(np.float64)
+    rs = np.random.RandomState(3)
+    eps = rs.normal(size=(K, N, ocfg.z_dim))
+    eps_p = rs.normal(size=(3, Kp, ocfg.z_dim))
+    # pd_energy averages D exp(log_energy_prob - log p_N) = D exp(-w xi D - log_Z + (d/2) log 2 pi): xi = sigmoid(-6)
+    # (w xi ~ 2.5) and log_Z = 110 ~ (d/2) log 2 pi keep the exponent O(1), inside float32's range like a trained model's
+    xi_raw, beta, log_Z = -6.0, -0.5, 110.0
+    m.set_scalars(xi_raw, beta, log_Z)
+    ev = Evaluator(m, n_z=K, batch_size=bs, n_pz=Kp)
+    got = ev.run(x, x_origin=x, eps=eps, eps_prior=eps_p)
+    names = ('test_nll', 'test_lb', 'adv_test_nll', 'adv_test_lb', 'reconstruct_energy', 'real_energy', 'pd_energy',
+             'pn_energy', 'test_recon', 'kl_adv_and_gaussian', 'test_mse')
+    assert all(n in got for n in names), sorted(got)
+    assert ev.time_metric_name in got
+    # oracle: per-batch scalars, then np.average weighted by the batch size
+    rows, weights = {n: [] for n in names}, []
+    for ib, b0 in enumerate(range(0, N, bs)):
+        sl = slice(b0, min(N, b0 + bs))
+        o = O.eval_batch(ocfg, params, x[sl], x[sl], eps[:, sl], xi_raw=xi_raw, beta=beta, log_Z=log_Z)
+        pb = O.prior_branch(ocfg, params, eps_p[ib][:, None, :], xi_raw=xi_raw, log_Z=log_Z)
+        for n in names:
+            rows[n].append(pb[n] if n in pb else o[n])
+        weights.append(x[sl].size)
+    want = {n: O.evaluator_average(rows[n], weights) for n in names}
+    for n in ('test_nll', 'test_lb', 'adv_test_nll', 'adv_test_lb', 'test_recon'):
+        assert abs(got[n] - want[n]) < NLL_RTOL * abs(want[n]), (n, got[n], want[n])
+    for n in ('reconstruct_energy', 'real_energy', 'pn_energy'):
+        assert abs(got[n] - want[n]) < ENERGY_ATOL, (n, got[n], want[n])
+    w_xi = ocfg.pull_back_energy_weight * O.sigmoid(xi_raw)
+    assert abs(got['kl_adv_and_gaussian'] - want['kl_adv_and_gaussian']) < w_xi * ENERGY_ATOL + 1e-5 * abs(want['kl_adv_and_gaussian'])
+    # pd_energy = mean[D exp(log_energy_prob - log p_N)]: the exponent carries w xi D, so its relative error is w xi * 1e-2
+    assert abs(got['pd_energy'] - want['pd_energy']) < (w_xi * ENERGY_ATOL * 1.5 + 1e-3) * abs(want['pd_energy']) + 1e-6, (got['pd_energy'], want['pd_energy'])
+    # test_mse: squared grey-level differences; x_mean within 1e-2 moves a rounded pixel by at most one level
+    assert abs(got['test_mse'] - want['test_mse']) < 2e-2 * want['test_mse'], (got['test_mse'], want['test_mse'])
+    # the prior branch alone, and log_Z_compute_op (:919-920)
+    p4 = m.prior_branch(Kp, eps=eps_p[0]).cpu().numpy().astype(np.float64)
+    pb = O.prior_branch(ocfg, params, eps_p[0][:, None, :], xi_raw=xi_raw, log_Z=log_Z)
+    assert abs(p4[0] - pb['pn_energy']) < ENERGY_ATOL
+    assert abs(p4[3] - pb['log_Z_compute_op']) < w_xi * ENERGY_ATOL + 1e-4 * abs(pb['log_Z_compute_op'])
+    # prior_branch=False: the three prior metrics are absent, the rest unchanged
+    got2 = Evaluator(m, n_z=K, batch_size=bs, prior_branch=False).run(x, x_origin=x, eps=eps)
+    assert 'pn_energy' not in got2 and abs(got2['test_nll'] - got['test_nll']) < 1e-6 * abs(got['test_nll'])
+    m.close()
+
+
+def test_test_mse_rows_match_the_oracle_given_the_same_x_mean():
+    """ROW_MSE / sq_err: min over K of the squared rounded-pixel error (dmm_cifar10.py:889-892), per image and per
+    sample; exact when recomputed from the library's own x_mean (decode), close to the oracle's."""
+    arch, kw, B, K = CASES['Bcifar']
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=64)
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    want = O.eval_batch(ocfg, params, x, x_origin, eps)
+    got = m.is_nll(x, K, eps=eps, per_sample=True)
+    se = got['sq_err'].cpu().numpy().astype(np.float64)
+    mse = got['ele_test_mse'].cpu().numpy().astype(np.float64)
+    np.testing.assert_allclose(mse, se.min(axis=0), rtol=1e-6)
+    # x_mean within 1e-2 moves a rounded pixel by at most one grey level: the squared-error sums agree to ~1 %
+    assert np.abs(se - want['sq_err']).max() < 2e-2 * want['sq_err'].max(), (se, want['sq_err'])
+    assert np.abs(mse - want['ele_test_mse']).max() < 2e-2 * want['ele_test_mse'].max()
+    m.close()
+
+
+def test_history_z_and_the_reference_chain_handover():
+    """EnergyDistribution.sample records history_z, the state BEFORE each step (dmm_cifar10.py:200,235), and
+    plot_samples restarts every run from batch_history_z[-1] (:1061): the state before the LAST accept, so consecutive
+    runs overlap by one step.  Checked against the oracle's mala_sample with fed-in noise (weight 2, see above)."""
+    arch, kw, _ = GRAD_CASES['A128']
+    ocfg, params, cfg, m = _make(arch, dict(kw, pull_back_energy_weight=2.0), max_chunk=4, enable_grad=True,
+                                 pull_back_energy_weight=2.0)
+    n, steps, alpha = 5, 3, 2e-2
+    rs = np.random.RandomState(5)
+    z0 = rs.normal(size=(n, 1, ocfg.z_dim))
+    eps = rs.normal(size=(2, steps, n, 1, ocfg.z_dim))
+    u = np.zeros((2, steps, n, 1))
+    # oracle: two runs chained the reference's way; uniforms placed away from the oracle's ratios
+    zs, runs = z0, []
+    for r in range(2):
+        z = zs
+        for i in range(steps):
+            _, _, _, ratio = O.mala_step(ocfg, params, z, eps[r, i], np.zeros((n, 1)), alpha)
+            acc = ((np.arange(n) + i + r) % 3 != 0)[:, None] | (ratio > 0.97)
+            u[r, i] = np.where(acc, ratio * 0.5, np.minimum(ratio + 0.5 * (1 - ratio) + 1e-3, 0.999))
+            z, _, _, _ = O.mala_step(ocfg, params, z, eps[r, i], u[r, i], alpha)
+        o = O.mala_sample(ocfg, params, zs, eps[r], u[r], alpha=alpha)
+        runs.append(o)
+        zs = o['history_z'][-1]                                  # batch_z = batch_history_z[-1]  (:1061)
+    zg = z0
+    for r in range(2):
+        out = m.mala(zg, steps, alpha=alpha, eps=eps[r], u=u[r], history_z=True)
+        hz = out['history_z'].cpu().numpy().astype(np.float64)
+        assert hz.shape == (steps, n, 1, ocfg.z_dim)
+        assert np.abs(hz - runs[r]['history_z']).max() < ENERGY_ATOL
+        assert np.abs(out['z'].cpu().numpy() - runs[r]['z']).max() < ENERGY_ATOL
+        np.testing.assert_array_equal(hz[0], np.asarray(zg, dtype=np.float32).reshape(hz[0].shape))     # history_z[0] is the input
+        zg = out['history_z'][-1]
+    # the Script surface carries it too
+    from apvae.dmm import Script
+    t = Script(m).p_net(n_z=n, mcmc_iterator=steps, initial_z=z0, mcmc_alpha=alpha)['z']
+    assert tuple(t.history_z.shape) == (steps, n, 1, ocfg.z_dim)
+    m.close()
+
+
+def test_p_net_prior_samples_like_test_pn_net():
+    """test_pn_net = p_net(n_z=config.test_n_pz, mcmc_iterator=0, ...) (dmm_cifar10.py:883): z ~ N(0, I) drawn by the
+    net itself; 'z'.log_prob() carries .energy / .log_energy_prob / .pure_energy and 'x'.distribution.mean = G(z),
+    which is all the pd / pn / kl metric ops read (:915-927)."""
+    from apvae.dmm import Script
+    arch, kw, _, _ = CASES['Bcifar']
+    ocfg, params, cfg, m = _make(arch, kw)
+    m.set_scalars(0.2, 0.0, 3.0)
+    s = Script(m)
+    net = s.p_net(n_z=10, mcmc_iterator=0, beta=0.0, log_Z=3.0, seed=4)
+    z = net['z'].tensor.cpu().numpy().astype(np.float64)
+    assert z.shape == (10, 1, ocfg.z_dim) and abs(z.std() - 1) < 0.15
+    lp = net['z'].log_prob()
+    pb = O.prior_branch(ocfg, params, z, xi_raw=0.2, log_Z=3.0)
+    npf = lambda t: t.cpu().numpy().astype(np.float64)
+    _energy_close(npf(lp.pure_energy), pb['d_g'])
+    w_xi = ocfg.pull_back_energy_weight * O.sigmoid(0.2)
+    e_o, lep_o = O.energy_terms(ocfg, z, pb['d_g'], 0.2, 3.0)
+    assert np.abs(npf(lp.energy) - e_o).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(e_o).max()
+    assert np.abs(npf(lp.log_energy_prob) - lep_o).max() < w_xi * ENERGY_ATOL + 1e-4 * np.abs(e_o).max()
+    xm = npf(net['x'].distribution.mean)
+    assert np.abs(xm - O.G_theta(ocfg, params, z)).max() < ENERGY_ATOL
+    with pytest.raises(ValueError):
+        s.p_net()                                                  # neither observed z, initial_z nor n_z
+    m.close()
+
+
+@pytest.mark.parametrize('case', ['A128', 'Bceleba'])
+def test_bf16_operand_format(case):
+    """operand_dtype='bf16' (fp32's exponent range, 8 significant bits): the same path with bf16 tensors.  NLL within
+    north_star's 1e-3; energies sit at ~1e-2 in this format (0.6e-2 .. 2.1e-2 measured over the cases — which is why
+    fp16 is the default), bounded here at 3e-2, and fp16 must be closer to the oracle than bf16 on the same inputs."""
+    arch, kw, B, K = CASES[case]
+    ocfg, params, cfg16, m16 = _make(arch, kw)
+    _, _, _, mbf = _make(arch, kw, operand_dtype='bf16')
+    x, x_origin, eps = _inputs(ocfg, B, K)
+    want = O.eval_batch(ocfg, params, x, x_origin, eps)
+    errs = {}
+    for name, m in (('fp16', m16), ('bf16', mbf)):
+        g = {k: v.cpu().numpy().astype(np.float64) for k, v in m.is_nll(x, K, x_origin=x_origin, eps=eps, per_sample=True).items()}
+        for key in ('ele_test_ll', 'ele_adv_test_ll'):
+            assert (np.abs(g[key] - want[key]) / np.abs(want[key])).max() < NLL_RTOL, (name, key)
+        errs[name] = np.abs(g['d_g'] - want['d_g'])
+        m.close()
+    assert errs['fp16'].max() < ENERGY_ATOL and errs['bf16'].max() < 3e-2, (errs['fp16'].max(), errs['bf16'].max())
+    assert errs['fp16'].mean() < 0.5 * errs['bf16'].mean(), (errs['fp16'].mean(), errs['bf16'].mean())

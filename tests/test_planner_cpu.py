@@ -6,7 +6,7 @@ import pytest
 
 import oracle as O
 from apvae.plan import Plan, pad16
-from helpers import bf16_round, emulate_plan, pad_channels
+from helpers import bf16_round, exact16, emulate_plan, pad_channels
 
 CASES = [
     # transpose, k, stride, H, W, cin, cout
@@ -31,9 +31,9 @@ CASES = [
 def test_plan_matches_oracle(transpose, k, stride, H, W, cin, cout):
     rs = np.random.RandomState(k * 100 + stride * 10 + cin)
     n = 3
-    x = bf16_round(rs.normal(size=(n, H, W, cin)))
+    x = exact16(rs.normal(size=(n, H, W, cin)))
     shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
-    kern = bf16_round(rs.normal(size=shp) * 0.2)
+    kern = exact16(rs.normal(size=shp) * 0.2)
     bias = rs.normal(size=(cout,)).astype(np.float32)
     plan = Plan([dict(src=0, transpose=transpose, stride=stride, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
     got = emulate_plan(plan, [pad_channels(x, pad16(cin))], n)[..., :cout]
@@ -49,10 +49,10 @@ def test_fused_shortcut_terms():
     (resnet.py:225-265)."""
     rs = np.random.RandomState(7)
     n, H, cin, cout = 2, 8, 32, 64
-    r = bf16_round(rs.normal(size=(n, H, H, cin)))
-    x = bf16_round(rs.normal(size=(n, H, H, cin)))
-    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.1)
-    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.1)
+    r = exact16(rs.normal(size=(n, H, H, cin)))
+    x = exact16(rs.normal(size=(n, H, H, cin)))
+    k1 = exact16(rs.normal(size=(3, 3, cin, cout)) * 0.1)
+    ks = exact16(rs.normal(size=(1, 1, cin, cout)) * 0.1)
     b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
     plan = Plan([dict(src=0, stride=2, in_h=H, in_w=H, kernel=k1, bias=b1),
                  dict(src=1, stride=2, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
@@ -67,8 +67,8 @@ def test_dense_as_1x1():
     """dense == np.dot(x, k) + b (reference tests/layers/core/test_dense.py)."""
     rs = np.random.RandomState(3)
     n, fin, fout = 5, 4096, 64
-    x = bf16_round(rs.normal(size=(n, 1, 1, fin)))
-    k = bf16_round(rs.normal(size=(fin, fout)) * 0.05)
+    x = exact16(rs.normal(size=(n, 1, 1, fin)))
+    k = exact16(rs.normal(size=(fin, fout)) * 0.05)
     b = rs.normal(size=fout).astype(np.float32)
     plan = Plan([dict(src=0, in_h=1, in_w=1, kernel=k.reshape(1, 1, fin, fout), bias=b)], n)
     assert plan.info.bn == 128 and plan.info.kc == 64
@@ -115,9 +115,9 @@ def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc, monkeypa
     monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
     rs = np.random.RandomState(k * 100 + cin + cout)
     n = 2
-    x = bf16_round(rs.normal(size=(n, H, W, cin)))
+    x = exact16(rs.normal(size=(n, H, W, cin)))
     shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
-    kern = bf16_round(rs.normal(size=shp) * 0.2)
+    kern = exact16(rs.normal(size=shp) * 0.2)
     bias = rs.normal(size=(cout,)).astype(np.float32)
     plan = Plan([dict(src=0, transpose=transpose, stride=1, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
     assert plan.info.patch == 1
@@ -147,15 +147,15 @@ def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut, mo
     monkeypatch.setenv('APVAE_PATCH', '1')
     rs = np.random.RandomState(k * 100 + cin + cout)
     n = 2
-    x = bf16_round(rs.normal(size=(n, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(k, k, cin, cout)) * 0.2)
+    x = exact16(rs.normal(size=(n, H, W, cin)))
+    kern = exact16(rs.normal(size=(k, k, cin, cout)) * 0.2)
     bias = rs.normal(size=(cout,)).astype(np.float32)
     terms = [dict(src=0, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)]
     srcs = [pad_channels(x, pad16(cin))]
     want = O.conv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
     if shortcut:
-        x2 = bf16_round(rs.normal(size=(n, H, W, cin)))
-        ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.2)
+        x2 = exact16(rs.normal(size=(n, H, W, cin)))
+        ks = exact16(rs.normal(size=(1, 1, cin, cout)) * 0.2)
         bs = rs.normal(size=(cout,)).astype(np.float32)
         terms.append(dict(src=1, stride=2, in_h=H, in_w=W, kernel=ks, bias=bs))
         srcs.append(pad_channels(x2, pad16(cin)))
@@ -187,8 +187,8 @@ def test_stride2_deconv_phase_plans_match_oracle(k, H, W, cin, cout, monkeypatch
     monkeypatch.setenv('APVAE_PATCH', '1')
     rs = np.random.RandomState(k * 100 + cin + cout)
     n = 2
-    x = bf16_round(rs.normal(size=(n, H, W, cin)))
-    kern = bf16_round(rs.normal(size=(k, k, cout, cin)) * 0.2)
+    x = exact16(rs.normal(size=(n, H, W, cin)))
+    kern = exact16(rs.normal(size=(k, k, cout, cin)) * 0.2)
     bias = rs.normal(size=(cout,)).astype(np.float32)
     plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
     want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
@@ -217,10 +217,10 @@ def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     monkeypatch.setenv('APVAE_PATCH', '1')
     rs = np.random.RandomState(11)
     n, H, cin, cout = 2, 16, 32, 64
-    r = bf16_round(rs.normal(size=(n, H, H, cin)))
-    x = bf16_round(rs.normal(size=(n, H, H, cin)))
-    k1 = bf16_round(rs.normal(size=(3, 3, cin, cout)) * 0.1)
-    ks = bf16_round(rs.normal(size=(1, 1, cin, cout)) * 0.1)
+    r = exact16(rs.normal(size=(n, H, H, cin)))
+    x = exact16(rs.normal(size=(n, H, H, cin)))
+    k1 = exact16(rs.normal(size=(3, 3, cin, cout)) * 0.1)
+    ks = exact16(rs.normal(size=(1, 1, cin, cout)) * 0.1)
     b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
     plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
     assert plan.info.patch == 1 and plan.info.patch_prow[1] == plan.info.patch_rows_tile
