@@ -22,6 +22,7 @@ ACCUM_WEIGHT, ACCUM_BATCHES, ACCUM_MSE = 9, 10, 11
 ACCUM_PN_ENERGY, ACCUM_PD_ENERGY, ACCUM_KL_ADV, ACCUM_LOG_Z_OP, ACCUM_PRIOR_WEIGHT = 12, 13, 14, 15, 16
 ACCUM_SLOTS = 20
 PRIOR_PN_ENERGY, PRIOR_PD_ENERGY, PRIOR_KL_ADV, PRIOR_LOG_Z_OP = range(4)
+AUX_COUNT = 11
 
 
 class ApvaeError(RuntimeError):
@@ -120,6 +121,8 @@ _SYMBOLS = [
     ('apvae_op_count', C.c_int, [_P, C.c_int, C.POINTER(C.c_int)]),
     ('apvae_op_time', C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int,
                                 C.POINTER(C.c_double), C.POINTER(C.c_float), _P]),
+    ('apvae_aux_time', C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double),
+                                 C.POINTER(C.c_float), _P]),
     ('apvae_plan_create', C.c_int, [C.POINTER(ConvTerm), C.c_int, C.c_int, C.c_int, C.POINTER(_P)]),
     ('apvae_plan_get_info', C.c_int, [_P, C.POINTER(PlanInfo)]),
     ('apvae_plan_copy_steps', C.c_int, [_P, C.POINTER(C.c_int32)]),

@@ -458,6 +458,98 @@ int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* na
     return APVAE_OK;
 }
 
+int apvae_aux_time(apvae_handle* h, int which, int n, int B, int reps, char* name, int name_cap, double* bytes_per_launch,
+                   float* ms_per_launch, void* stream) {
+    REQUIRE_BUILT(h);
+    if (which < 0 || which >= APVAE_AUX_COUNT || n <= 0 || reps <= 0) { m.err = "aux_time: bad arguments"; return APVAE_ERR_INVALID; }
+    if (B <= 0) B = 1;
+    const int d = m.cfg.z_dim;
+    const bool sampler = which >= APVAE_AUX_MALA_PROPOSE && which <= APVAE_AUX_TANH_BACKWARD;
+    if (sampler && !m.cfg.enable_grad) { m.err = "aux_time: the sampler's kernels need enable_grad"; return APVAE_ERR_STATE; }
+    if (n > m.cfg.max_chunk && which != APVAE_AUX_IS_REDUCE && which != APVAE_AUX_FILL_NORMAL) { m.err = "aux_time: n exceeds max_chunk"; return APVAE_ERR_INVALID; }
+    if (!m.ensure_sample_buffers((size_t)std::max(n, m.cfg.max_chunk))) return APVAE_ERR_CUDA;
+    if (sampler && (size_t)n > m.mala_cap) {           // sizes the sampler's state buffers (a zero-step run)
+        if (!m.mala(m.z_tmp, std::min(n, m.cfg.max_chunk), 0, 1e-3f, nullptr, nullptr, 0, nullptr, nullptr, nullptr, nullptr, stream)) return APVAE_ERR_CUDA;
+    }
+    const long long px = (long long)n * m.HW();
+    const int C3 = m.C();
+    const char* nm = "";
+    double bytes = 0;
+    auto launch = [&]() -> int {
+        switch (which) {
+            case APVAE_AUX_SAMPLE_Z:          // eps in; z as raw + act operand tensors out (+ log q, log N)
+                nm = "sample_z";
+                bytes = (double)n * (d * 4.0 + 2.0 * m.z_stride() * 2.0 + 8.0);
+                return launch_sample_z(m.q_mu, m.q_logstd, m.eps_buf, n, 0, std::min(B, m.cfg.max_batch), d, m.cfg.min_logstd_of_q,
+                                       m.cfg.use_truncated, nullptr, m.g_in.raw.ptr, m.g_in.act.ptr, m.z_stride(), m.z_group(),
+                                       m.z_cpad(), 0.2f, m.log_q, m.log_pn, m.f16(), stream);
+            case APVAE_AUX_IS_REDUCE: {       // five [K, B] rows in (second pass from L2), ten floats per image out
+                nm = "is_reduce";
+                const int K = std::max(1, n / B);
+                bytes = (double)K * B * 5 * 4.0 + (double)B * kPerImageRows * 4.0;
+                return launch_is_reduce(m.log_px, m.log_q, m.log_pn, m.d_g, m.sq_err, K, B, d, m.w_xi(), m.log_Z, m.eps_buf, stream);
+            }
+            case APVAE_AUX_SUM_TILES: {
+                nm = "sum_tiles";
+                const int tpi = heads_tiles_per_image(m.HW());
+                if (!m.lik_part) return (int)cudaErrorInvalidValue;
+                bytes = (double)n * (tpi * 8.0 + 8.0);
+                return launch_sum_tiles(m.lik_part, tpi, n, m.log_px, m.sq_err, stream);
+            }
+            case APVAE_AUX_PACK_IMAGE:        // fp32 image in; raw + act operand rows out
+                nm = "pack_image";
+                bytes = (double)px * (C3 * 4.0 + 2.0 * m.d_in.raw.cp * 2.0);
+                return launch_pack_image(m.head_f32, px, C3, m.d_in.raw.cp, m.d_in.raw.ptr, m.d_in.act.ptr, 0.2f, m.f16(), stream);
+            case APVAE_AUX_ROWDOT:
+                nm = "rowdot";
+                bytes = (double)n * (64 * 4.0 + 4.0);
+                return launch_rowdot(m.d64, 64, m.d_last_w, m.d_last_b, 64, n, m.d_g, stream);
+            case APVAE_AUX_FILL_NORMAL:
+                nm = "fill_normal";
+                bytes = (double)n * d * 4.0;
+                return launch_fill_normal(m.eps_buf, (long long)n * d, 1234, 0, m.cfg.use_truncated, stream);
+            case APVAE_AUX_MALA_PROPOSE:      // z, grad, eps in; z' out
+                nm = "mala_propose";
+                bytes = (double)n * d * 4.0 * 4;
+                return launch_mala_propose(m.z_tmp, m.mg, m.eps_buf, n, d, 1e-3f, m.mzp, stream);
+            case APVAE_AUX_MALA_ACCEPT:       // z, z', grad, grad' in; z, grad out for the accepted chains (counted in full)
+                nm = "mala_accept";
+                bytes = (double)n * (d * 4.0 * 6 + 4.0 * 8);
+                return launch_mala_accept(m.z_tmp, m.me, m.mg, m.mp, m.mzp, m.mep, m.mgp, m.mpp, m.log_q, n, d, 1e-3f,
+                                          m.log_px, m.log_pn, m.d_g, stream);
+            case APVAE_AUX_ENERGY_COMBINE:    // d D/dz, z in; grad out
+                nm = "energy_combine";
+                bytes = (double)n * (d * 4.0 * 3 + 8.0);
+                return launch_energy_combine(m.d_g, m.gz_f32, m.z_tmp, n, d, m.w_xi(), m.me, m.mg, stream);
+            case APVAE_AUX_TANH_BACKWARD:     // fp32 gradient + fp32 x_mean in; operand row out
+                nm = "tanh_backward_pack";
+                bytes = (double)px * (C3 * 4.0 * 2 + m.g_pre.cp * 2.0);
+                return launch_tanh_backward_pack(m.gx_f32, m.head_f32, m.head_ld(), px, C3, m.g_pre.cp, m.g_pre.ptr, m.f16(), stream);
+            case APVAE_AUX_QUANTIZE:
+                nm = "quantize_images";
+                bytes = (double)px * C3 * 5.0;
+                return launch_quantize_images(m.head_f32, m.head_ld(), px, C3, reinterpret_cast<uint8_t*>(m.d_in.act.ptr), stream);
+        }
+        return (int)cudaErrorInvalidValue;
+    };
+    cudaStream_t st = (cudaStream_t)stream;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    for (int i = 0; i < 2; ++i) LCHECK(launch(), "aux_time warm-up");
+    cudaEventRecord(e0, st);
+    for (int i = 0; i < reps; ++i) LCHECK(launch(), "aux_time");
+    cudaEventRecord(e1, st);
+    const cudaError_t e = cudaEventSynchronize(e1);
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (e != cudaSuccess) { m.err = std::string("aux_time: ") + cudaGetErrorString(e); return APVAE_ERR_CUDA; }
+    if (name && name_cap > 0) { strncpy(name, nm, name_cap - 1); name[name_cap - 1] = 0; }
+    if (bytes_per_launch) *bytes_per_launch = bytes;
+    if (ms_per_launch) *ms_per_launch = ms / reps;
+    return APVAE_OK;
+}
+
 // ---------------------------------------------------------------- layer-level interface
 int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, apvae_plan** out) {
     if (!terms || nterms <= 0 || !out || capacity_n <= 0) return set_global_err("plan_create: bad arguments", APVAE_ERR_INVALID);

@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(kTile) pixel_heads_kernel(const __grid_constan
 #pragma unroll
                     for (int c = 0; c < CC; ++c) {
                         const float xv = __ldg(xr + c);
-                        const float ls = HS ? acc[(HS ? CC : 0) + c] : p.lik_beta;
+                        const float ls = (HS && !p.lik_uniform) ? acc[(HS ? CC : 0) + c] : p.lik_beta;
                         lp_sum += element_log_prob(p.lik, xv, acc[c], ls);
                         se_sum += element_sq_err(p.lik.bernoulli, xv, acc[c]);
                     }

@@ -138,7 +138,8 @@ struct HeadsParams {
     // fused likelihood (set per call; lik_part == null: off): pixel p of local sample s scores x[(lik_s0 + s) % lik_B]
     const float* lik_x;                   // fp32 [lik_B, pixels_per_image * C]
     float* lik_part;                      // [samples * tiles_per_image][2]: per-tile sums of log p and of the squared pixel error
-    int lik_s0, lik_B, lik_has_std;       // lik_has_std: columns [C, 2C) are x_logstd; else log_scale = lik_beta
+    int lik_s0, lik_B, lik_has_std;       // lik_has_std: columns [C, 2C) hold x_logstd
+    int lik_uniform;                      // config.uniform_scale: log_scale = lik_beta whatever the columns hold (dmm_for_sampling.py:628)
     float lik_beta;
     LikelihoodSpec lik;
     float bias[8];

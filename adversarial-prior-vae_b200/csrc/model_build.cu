@@ -400,6 +400,7 @@ bool Model::run_decoder_chunk(int n, void* stream, bool want_f32, const LikArgs*
         if (lik) {
             hp.lik_x = lik->x; hp.lik_s0 = lik->s0; hp.lik_B = lik->B;
             hp.lik_has_std = head_ld() == 2 * C() ? 1 : 0;
+            hp.lik_uniform = cfg.uniform_scale ? 1 : 0;
             hp.lik_beta = beta;
             hp.lik = spec;
         }

@@ -215,6 +215,17 @@ int apvae_op_count(const apvae_handle* h, int net, int* count);
 int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* name, int name_cap,
                   double* macs_per_unit, float* ms_per_launch, void* stream);
 
+/* Device timing of the HBM-bound CUDA-core kernels of the estimator tail and the sampler (bench.py's "achieved HBM GB/s
+ * against peak" table): kernel `which` (APVAE_AUX_*) runs 2 + reps times on the handle's own scratch buffers for `n`
+ * units (samples / chains; B images of K samples for APVAE_AUX_IS_REDUCE with n = K * B) and the CUDA-event average of the
+ * last `reps` launches is returned together with the kernel's ALGORITHMIC bytes per launch (compulsory reads + writes,
+ * stated per kernel in DESIGN.md).  Buffer contents are unspecified afterwards.  The sampler's kernels need enable_grad. */
+enum { APVAE_AUX_SAMPLE_Z = 0, APVAE_AUX_IS_REDUCE = 1, APVAE_AUX_SUM_TILES = 2, APVAE_AUX_PACK_IMAGE = 3,
+       APVAE_AUX_ROWDOT = 4, APVAE_AUX_FILL_NORMAL = 5, APVAE_AUX_MALA_PROPOSE = 6, APVAE_AUX_MALA_ACCEPT = 7,
+       APVAE_AUX_ENERGY_COMBINE = 8, APVAE_AUX_TANH_BACKWARD = 9, APVAE_AUX_QUANTIZE = 10, APVAE_AUX_COUNT = 11 };
+int apvae_aux_time(apvae_handle* h, int which, int n, int B, int reps, char* name, int name_cap, double* bytes_per_launch,
+                   float* ms_per_launch, void* stream);
+
 /* ---- layer-level interface (tests; mirrors spt.layers.conv2d / deconv2d / dense) ---- */
 typedef struct apvae_conv_term {
     int src, transpose, k, stride, cin, cout, in_h, in_w, in_cp;

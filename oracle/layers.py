@@ -9,8 +9,46 @@ import numpy as np
 __all__ = [
     'same_padding', 'leaky_relu', 'leaky_relu_grad', 'conv2d', 'deconv2d',
     'dense', 'conv2d_input_grad', 'deconv2d_input_grad',
-    'resnet_conv2d_block', 'resnet_deconv2d_block',
+    'resnet_conv2d_block', 'resnet_deconv2d_block', 'set_conv_backend', 'get_conv_backend',
 ]
+
+# Which library evaluates the k > 1 convolutions.  'numpy': sliding-window + tensordot (the default: plain numpy,
+# any dtype).  'torch': torch-CPU conv2d / conv_transpose2d (oneDNN) on the SAME explicitly padded arithmetic — the
+# closest available stand-in for TensorFlow-CPU's Eigen / MKL-DNN kernels, used by bench.py's CPU baseline so that the
+# GPU / CPU ratio is not flattered by a slow numpy conv.  Both are cross-checked in tests/test_oracle_cpu.py.
+_BACKEND = 'numpy'
+
+
+def set_conv_backend(name):
+    global _BACKEND
+    if name not in ('numpy', 'torch'):
+        raise ValueError("backend must be 'numpy' or 'torch'")
+    old, _BACKEND = _BACKEND, name
+    return old
+
+
+def get_conv_backend():
+    return _BACKEND
+
+
+def _torch_conv(x4, kernel, s, pads):
+    """SAME cross-correlation of conv2d_.py:204-211 through torch: explicit asymmetric zero padding, then a VALID conv."""
+    import torch
+    import torch.nn.functional as F
+    (plo_h, phi_h), (plo_w, phi_w) = pads
+    xt = torch.from_numpy(np.ascontiguousarray(x4)).permute(0, 3, 1, 2)
+    xt = F.pad(xt, (plo_w, phi_w, plo_h, phi_h))
+    wt = torch.from_numpy(np.ascontiguousarray(kernel)).permute(3, 2, 0, 1)
+    return F.conv2d(xt, wt, stride=s).permute(0, 2, 3, 1).numpy()
+
+
+def _torch_deconv_full(x4, kernel, s):
+    """sum_{di,dj} x[i, j] K[di, dj]^T scattered to (i s + di, j s + dj): torch's conv_transpose2d without padding."""
+    import torch
+    import torch.nn.functional as F
+    xt = torch.from_numpy(np.ascontiguousarray(x4)).permute(0, 3, 1, 2)
+    wt = torch.from_numpy(np.ascontiguousarray(kernel)).permute(3, 2, 0, 1)      # [Cin, Cout, kh, kw]
+    return F.conv_transpose2d(xt, wt, stride=s).permute(0, 2, 3, 1).numpy()
 
 
 def same_padding(in_size, k, s):
@@ -56,11 +94,14 @@ def conv2d(x, kernel, bias=None, strides=1, activation_fn=None):
     else:
         ho, plo_h, phi_h = same_padding(h, kh, s)
         wo, plo_w, phi_w = same_padding(w, kw, s)
-        xp = np.pad(x4, ((0, 0), (plo_h, phi_h), (plo_w, phi_w), (0, 0)))
-        # windows: [n, Hp-kh+1, Wp-kw+1, c, kh, kw] -> stride subsample
-        win = np.lib.stride_tricks.sliding_window_view(xp, (kh, kw), axis=(1, 2))
-        win = win[:, ::s, ::s][:, :ho, :wo]
-        y = np.tensordot(win, kernel, axes=([4, 5, 3], [0, 1, 2]))
+        if _BACKEND == 'torch':
+            y = _torch_conv(x4, np.asarray(kernel, dtype=x4.dtype), s, ((plo_h, phi_h), (plo_w, phi_w)))[:, :ho, :wo]
+        else:
+            xp = np.pad(x4, ((0, 0), (plo_h, phi_h), (plo_w, phi_w), (0, 0)))
+            # windows: [n, Hp-kh+1, Wp-kw+1, c, kh, kw] -> stride subsample
+            win = np.lib.stride_tricks.sliding_window_view(xp, (kh, kw), axis=(1, 2))
+            win = win[:, ::s, ::s][:, :ho, :wo]
+            y = np.tensordot(win, kernel, axes=([4, 5, 3], [0, 1, 2]))
     if bias is not None:
         y = y + bias
     if activation_fn is not None:
@@ -86,10 +127,14 @@ def deconv2d(x, kernel, bias=None, strides=1, activation_fn=None):
     fh = max((h - 1) * s + kh, plo_h + oh)
     fw = max((w - 1) * s + kw, plo_w + ow)
     full = np.zeros((n, fh, fw, cout), dtype=x4.dtype)
-    for di in range(kh):
-        for dj in range(kw):
-            full[:, di:di + (h - 1) * s + 1:s, dj:dj + (w - 1) * s + 1:s, :] += \
-                x4 @ kernel[di, dj].T
+    if _BACKEND == 'torch' and (kh > 1 or kw > 1):
+        part = _torch_deconv_full(x4, np.asarray(kernel, dtype=x4.dtype), s)
+        full[:, :part.shape[1], :part.shape[2], :] = part
+    else:
+        for di in range(kh):
+            for dj in range(kw):
+                full[:, di:di + (h - 1) * s + 1:s, dj:dj + (w - 1) * s + 1:s, :] += \
+                    x4 @ kernel[di, dj].T
     y = full[:, plo_h:plo_h + oh, plo_w:plo_w + ow, :]
     if bias is not None:
         y = y + bias

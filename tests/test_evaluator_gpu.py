@@ -121,6 +121,14 @@ def test_benchmarked_shape_against_the_oracle():
     g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
     m.close()
     p32 = {k: v.astype(np.float32) for k, v in params.items()}
+    old_backend = O.set_conv_backend('torch')       # torch-CPU convs (cross-checked against the numpy ones on the CPU): 4x faster
+    try:
+        _check_images_against_oracle(ocfg, p32, x, eps, g, K, xi_raw, beta, log_Z)
+    finally:
+        O.set_conv_backend(old_backend)
+
+
+def _check_images_against_oracle(ocfg, p32, x, eps, g, K, xi_raw, beta, log_Z):
     for b in (0, 36):
         # the oracle in slices of 100 samples (the nets treat samples independently; bounds its memory), then the
         # reference's reductions over all K (variational/evaluation.py:9-39, objectives.py:9-42)

@@ -31,7 +31,7 @@ def _torch():
 
 def _td():
     import torch
-    return torch.float16 if DT == 'fp16' else _td()
+    return torch.float16 if DT == "fp16" else torch.bfloat16
 
 
 def _check(got, want, tol=2e-4):

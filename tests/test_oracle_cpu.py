@@ -306,3 +306,58 @@ def test_arch_m_latent_gan_oracle_shapes():
         h = O.leaky_relu(h @ O.weight_norm(params[p + 'kernel'], params[p + 'weight_norm/scale']) + params[p + 'bias'])
     last = h @ O.weight_norm(params[pre + 'kernel'], params[pre + 'weight_norm/scale']) + params[pre + 'bias']
     np.testing.assert_allclose(out, np.where(last > 0, last, 0.2 * last), rtol=1e-12)
+
+
+@pytest.mark.parametrize('k,s', KS)
+def test_torch_conv_backend_matches_the_numpy_one(k, s):
+    """oracle.set_conv_backend('torch') (the CPU baseline's oneDNN path) computes the same SAME conv / transposed conv."""
+    rs = np.random.RandomState(k * 10 + s + 2)
+    x = rs.normal(size=(2, 8, 10, 3))
+    kern = rs.normal(size=(k, k, 3, 4))
+    kd = rs.normal(size=(k, k, 4, 3))
+    bias = rs.normal(size=4)
+    want_c, want_d = O.conv2d(x, kern, bias, s), O.deconv2d(x, kd, bias, s)
+    old = O.set_conv_backend('torch')
+    try:
+        assert O.get_conv_backend() == 'torch'
+        np.testing.assert_allclose(O.conv2d(x, kern, bias, s), want_c, rtol=1e-10, atol=1e-10)
+        np.testing.assert_allclose(O.deconv2d(x, kd, bias, s), want_d, rtol=1e-10, atol=1e-10)
+    finally:
+        O.set_conv_backend(old)
+    with pytest.raises(ValueError):
+        O.set_conv_backend('cudnn')
+
+
+def test_torch_conv_backend_whole_graph():
+    """The whole test graph (arch B, CIFAR shape) through both conv backends, float32 as in the reference."""
+    cfg = O.OracleConfig('B', dataset='cifar10', z_dim=16)
+    params = O.init_weights(cfg, dtype=np.float32)
+    rs = np.random.RandomState(0)
+    x = ((rs.randint(0, 256, size=(2, 32, 32, 3)) - 127.5) / 128.0).astype(np.float32)
+    eps = rs.normal(size=(3, 2, 16)).astype(np.float32)
+    a = O.eval_batch(cfg, params, x, x, eps)
+    old = O.set_conv_backend('torch')
+    try:
+        b = O.eval_batch(cfg, params, x, x, eps)
+    finally:
+        O.set_conv_backend(old)
+    for key in ('ele_test_ll', 'ele_adv_test_ll', 'd_g', 'ele_test_mse'):
+        np.testing.assert_allclose(np.asarray(a[key], np.float64), np.asarray(b[key], np.float64), rtol=2e-4, atol=2e-4)
+
+
+def test_test_mse_definition():
+    """test_mse (dmm_cifar10.py:889-895): squared difference of the ROUNDED grey levels, summed over pixels, min over the
+    sample axis, mean over images; tf.round = round half to even."""
+    cfg = O.OracleConfig('A', z_dim=64)
+    x = np.array([[-1.0, 0.0], [0.5, 0.00390625]]).reshape(1, 2, 2, 1)              # grey levels -0.5, 127.5, 191.5, 128
+    xm = np.stack([x, x + 2.0 / 128.0, x * 0])                                        # K = 3: exact, two levels off, zero
+    se = O.rounded_pixel_sq_err(cfg, x, xm[:, None].reshape(3, 1, 2, 2, 1))
+    lv = np.round(x * 128 + 127.5).ravel()
+    assert lv.tolist() == [-0.0, 128.0, 192.0, 128.0]                                 # 127.5 -> 128, 191.5 -> 192 (half to even)
+    assert se.shape == (3, 1) and se[0, 0] == 0 and se[1, 0] == 4 * 2 ** 2
+    assert se[2, 0] == np.sum((np.round(127.5) - lv) ** 2)
+    cfg_m = O.OracleConfig('M')
+    xb = np.array([0.0, 1.0, 1.0, 0.0]).reshape(1, 2, 2, 1)
+    pm = np.array([-0.3, 0.999, 0.5, 0.2]).reshape(1, 1, 2, 2, 1)                      # clip(-0.3) -> 1e-7 -> level 0
+    se = O.rounded_pixel_sq_err(cfg_m, xb, pm)
+    assert se[0, 0] == (0 - 0) ** 2 + (255 - 255) ** 2 + (np.round(127.5) - 255) ** 2 + (51 - 0) ** 2
