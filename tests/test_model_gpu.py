@@ -542,11 +542,19 @@ def test_latent_gan_initial_z_matches_oracle(case):
 # ----------------------------------------------------------------------------- round-2 additions
 def test_arch_m_with_the_reference_tanh_head():
     """Arch M exactly as the script builds it (dmm_bernouli_fashion.py:517-521,619-626): the mean head is a zero-centred
-    tanh, so a large share of the pixels (9 % with these synthetic weights) sits on clip(x_mean, 1e-7, .) — the branch the recentred cases above never reach.
-    Where the clip is active log p is flat in x_mean; the whole-model sum is ill-conditioned only for the few pixels
-    whose mean lies within the x_mean error of the clip threshold with x = 1 (log p jumps from log(1e-7) to log(mean)),
-    hence the per-image gate is 5e-3 relative here; the clip arithmetic itself is pinned exactly by
-    test_kats_gpu.py::test_cuda_bernoulli_clip_branch."""
+    tanh, so a large share of the pixels (9 % with these synthetic weights) sits on clip(x_mean, 1e-7, .) — the branch the
+    recentred cases above never reach.  log(clip(m, 1e-7, .)) has slope 1/m next to the threshold: a pixel with x = 1 whose
+    mean the float64 oracle puts at +3e-4 and the 16-bit-operand decoder at -1e-4 moves the image's log-likelihood by 8
+    nats (the reference's own float32 TF graph has the same sensitivity).  So the whole-model sum is checked the way its
+    conditioning allows:
+      (1) x_mean itself within north_star's 1e-2 abs of the oracle, every pixel of every sample;
+      (2) the fused CUDA likelihood / estimator on the GPU's OWN x_mean: the oracle's Bernoulli log-prob and IS / ELBO
+          arithmetic fed with the GPU's decoded means must reproduce the GPU's per-sample log p(x|z) and per-image
+          rows to 1e-3 relative — this is where a wrong clip branch would show;
+      (3) the direct per-image comparison with the oracle at 1e-3 relative for every image that has no pixel inside the
+          ill-conditioned band (x = 1 and oracle mean within 1e-2 of the clip), and a bound from the band's worst-case
+          jump for the others.
+    The clip arithmetic alone is pinned exactly by test_kats_gpu.py::test_cuda_bernoulli_clip_branch."""
     from apvae.model import ExpConfig, Model
     ocfg = O.OracleConfig('M')
     params = O.init_weights(ocfg)
@@ -558,9 +566,28 @@ def test_arch_m_with_the_reference_tanh_head():
     assert (want['x_mean'] < 1e-7).mean() > 0.05                  # the clip IS active on a real share of the pixels
     got = m.is_nll(x, K, x_origin=x_origin, eps=eps, per_sample=True)
     g = {k: v.cpu().numpy().astype(np.float64) for k, v in got.items()}
+    # (1) decoded means
+    z_gpu, _, _ = m.sample_z(x_origin, K, eps=eps)
+    xm_gpu = m.decode(z_gpu).cpu().numpy().astype(np.float64)           # [K, B, H, W, C], pre-clip tanh output
+    xerr = np.abs(xm_gpu - want['x_mean'])
+    assert xerr.max() < ENERGY_ATOL, (xerr.max(), xerr.mean())
+    assert (xm_gpu < 1e-7).mean() > 0.05
+    # (2) the GPU's likelihood / estimator on its own means
+    lp_own = O.bernoulli_log_prob_from_mean(x, xm_gpu, 3)
+    assert np.abs(g['log_px'] - lp_own).max() < 1e-4 * np.abs(lp_own).max(), np.abs(g['log_px'] - lp_own).max()
+    lj = lp_own + g['log_pn']
+    ll_own = O.importance_sampling_log_likelihood(lj, g['log_q'], 0)
+    lb_own = O.elbo_objective(lj, g['log_q'], 0)
+    assert (np.abs(g['ele_test_ll'] - ll_own) / np.abs(ll_own)).max() < 1e-5
+    assert (np.abs(g['ele_test_lb'] - lb_own) / np.abs(lb_own)).max() < 1e-5
+    # (3) against the float64 oracle, per image
+    band = (x[None] > 0.5) & (np.abs(want['x_mean'] - 1e-7) < ENERGY_ATOL)                 # [K,B,H,W,C]
+    slack = (band * (np.log(np.maximum(want['x_mean'], 1e-7) + ENERGY_ATOL) - np.log(1e-7))).sum(axis=(2, 3, 4)).max(axis=0)
+    checked = 0
     for name in ('ele_test_ll', 'ele_test_lb', 'ele_adv_test_ll', 'ele_adv_test_lb'):
-        rel = np.abs(g[name] - want[name]) / np.abs(want[name])
-        assert rel.max() < 5e-3, (name, g[name], want[name])
+        err = np.abs(g[name] - want[name])
+        assert np.all(err < NLL_RTOL * np.abs(want[name]) + slack), (name, g[name], want[name], slack)
+        checked += int((slack == 0).sum())
     _energy_close(g['d_g'], want['d_g'])
     m.close()
 
