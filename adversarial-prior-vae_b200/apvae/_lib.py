@@ -23,6 +23,7 @@ ACCUM_PN_ENERGY, ACCUM_PD_ENERGY, ACCUM_KL_ADV, ACCUM_LOG_Z_OP, ACCUM_PRIOR_WEIG
 ACCUM_SLOTS = 20
 PRIOR_PN_ENERGY, PRIOR_PD_ENERGY, PRIOR_KL_ADV, PRIOR_LOG_Z_OP = range(4)
 AUX_COUNT = 11
+NOALLOC_MAX_SAMPLES = 65536
 
 
 class ApvaeError(RuntimeError):
@@ -114,6 +115,8 @@ _SYMBOLS = [
                                                       C.c_int, C.c_float, C.c_int, C.c_float, _P, _P]),
     ('apvae_bernoulli_log_prob', C.c_int, [_P, _P, C.c_int64, C.c_int64, _P, _P]),
     ('apvae_is_reduce', C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, _P, _P]),
+    ('apvae_is_ll_noalloc', C.c_int, [_P, _P, _P, C.c_int64, C.c_float, C.c_int, C.c_float, C.c_int, C.c_float, C.c_int,
+                                      C.c_float, _P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, _P, _P]),
     ('apvae_fill_normal', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, C.c_int, _P]),
     ('apvae_fill_uniform', C.c_int, [_P, C.c_int64, C.c_uint64, C.c_uint64, _P]),
     ('apvae_launch_count', C.c_int, [_P, C.POINTER(C.c_int64)]),

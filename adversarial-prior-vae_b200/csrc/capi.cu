@@ -41,6 +41,8 @@ static int set_global_err(const std::string& m, int code) {
     return code;
 }
 
+namespace apvae { int report_global_error(const std::string& m, int code) { return set_global_err(m, code); } }   // noalloc.cu
+
 static_assert((int)kPerImageRows == (int)APVAE_PER_IMAGE_ROWS && (int)ROW_REAL_E == (int)APVAE_ROW_REAL_E &&
               (int)ROW_MSE == (int)APVAE_ROW_MSE, "per-image row tables out of sync");
 static_assert((int)ACC_WEIGHT == APVAE_ACCUM_WEIGHT && (int)ACC_BATCHES == APVAE_ACCUM_BATCHES && (int)ACC_MSE == APVAE_ACCUM_MSE &&

@@ -198,6 +198,23 @@ int apvae_is_reduce(const float* log_px_dev, const float* log_q_dev, const float
                     const float* sq_err_dev, int K, int B, int z_dim, float w_xi, float log_Z, float* per_image_dev,
                     void* stream);
 
+/* NO COUNTERPART IN THE REFERENCE — added for callers that cannot call cudaMalloc
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).  The estimator tail on plain
+ * arrays in ONE call that allocates nothing: element log-probs of DiscretizedLogistic(mean, log_scale, bin_size, ...)
+ * summed over `group` consecutive elements per (sample, image) row s = k * B + b  (= apvae_discretized_logistic_log_prob),
+ * then the per-image reductions over K (= apvae_is_reduce with sq_err NULL) into per_image_dev [APVAE_PER_IMAGE_ROWS][B].
+ * The intermediate per-sample row log p(x|z) [K * B] lives in a fixed device array inside the library (256 KiB on every
+ * GPU that loads it, held until exit), so K * B <= APVAE_NOALLOC_MAX_SAMPLES — larger calls are refused with
+ * APVAE_ERR_INVALID.  No cudaMalloc / cudaFree / allocating library routine is called.  All calls on one GPU share that
+ * array and it keeps the previous call's contents (each call overwrites what it reads; nothing needs zeroing): calls that
+ * overlap on the GPU (different streams, unordered graph branches) race — serialise them.  x / mean / log_scale are
+ * caller-owned fp32 device arrays of K * B * group elements; the current device is used. */
+enum { APVAE_NOALLOC_MAX_SAMPLES = 65536 };
+int apvae_is_ll_noalloc(const float* x_dev, const float* mean_dev, const float* log_scale_dev, int64_t group,
+                        float bin_size, int has_min, float min_val, int has_max, float max_val, int biased_edges,
+                        float epsilon, const float* log_q_dev, const float* log_pn_dev, const float* d_g_dev,
+                        int K, int B, int z_dim, float w_xi, float log_Z, float* per_image_dev, void* stream);
+
 /* Philox normals / uniforms the NULL-noise paths use (so tests can reproduce them). */
 int apvae_fill_normal(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, int truncated, void* stream);
 int apvae_fill_uniform(float* out_dev, int64_t n, uint64_t seed, uint64_t offset, void* stream);
