@@ -32,6 +32,25 @@ class ApvaeError(RuntimeError):
         self.status = status
 
 
+TUNING_FIELDS = ('patch', 'patch_macc', 'patch_cluster', 'patch_max_n', 'patch_phases', 'patch_merge', 'patch_s2',
+                 'patch_fold', 'patch_tpi', 'patch_2cta', 'patch_2cta_min_k', 'patch_a_cap', 'patch_a_stages', 'patch_b_stages',
+                 'tap_2cta', 'fast_epi', 'fast_mask', 'tiny_conv', 'small_block', 'heads_gemm', 'patch_split', 'debug', 'trace')
+
+
+class Tuning(C.Structure):
+    """apvae_tuning: kernel-selection overrides; all-zero = defaults, switch fields -1 = off / +1 = on."""
+    _fields_ = [(n, C.c_int) for n in TUNING_FIELDS]
+
+    @classmethod
+    def make(cls, options=None):
+        t = cls()
+        for k, v in (options or {}).items():
+            if k not in TUNING_FIELDS:
+                raise AttributeError('apvae_tuning has no field %r' % (k,))
+            setattr(t, k, int(v))
+        return t
+
+
 class Config(C.Structure):
     _fields_ = [
         ('arch', C.c_int), ('x_h', C.c_int), ('x_w', C.c_int), ('x_c', C.c_int),
@@ -42,6 +61,7 @@ class Config(C.Structure):
         ('max_batch', C.c_int), ('max_chunk', C.c_int), ('enable_grad', C.c_int),
         ('smallest_step', C.c_float), ('len_train', C.c_int), ('precise', C.c_int),
         ('nf_layers', C.c_int), ('latent_gan', C.c_int), ('operand_bf16', C.c_int),
+        ('tuning', Tuning),
     ]
 
 
@@ -82,6 +102,7 @@ class Epilogue(C.Structure):
         ('res_dev', C.c_void_p), ('res_mode', C.c_int), ('ld_res', C.c_int),
         ('mask_dev', C.c_void_p), ('ld_mask', C.c_int),
         ('tanh_cols', C.c_int),
+        ('out_raw_lo_dev', C.c_void_p), ('out_act_lo_dev', C.c_void_p), ('res_lo_dev', C.c_void_p),
     ]
 
 
@@ -105,6 +126,8 @@ _SYMBOLS = [
     ('apvae_is_nll', C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P]),
     ('apvae_sample_z', C.c_int, [_P, _P, C.c_int, C.c_int, _P, C.c_uint64, _P, _P, _P, _P]),
     ('apvae_accumulate_metrics', C.c_int, [_P, _P, _P, C.c_int, C.c_int, _P, _P]),
+    ('apvae_allreduce_metrics', C.c_int, [_P, C.c_int, _P, _P, _P]),
+    ('apvae_merge_metrics', C.c_int, [_P, C.c_int, _P, _P]),
     ('apvae_prior_stats', C.c_int, [_P, C.c_int, _P, C.c_uint64, _P, _P, _P, _P]),
     ('apvae_mala', C.c_int, [_P, _P, C.c_int, C.c_int, C.c_float, _P, _P, C.c_uint64, _P, _P, _P, _P, _P]),
     ('apvae_energy_grad', C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),
@@ -126,7 +149,7 @@ _SYMBOLS = [
                                 C.POINTER(C.c_double), C.POINTER(C.c_float), _P]),
     ('apvae_aux_time', C.c_int, [_P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double),
                                  C.POINTER(C.c_float), _P]),
-    ('apvae_plan_create', C.c_int, [C.POINTER(ConvTerm), C.c_int, C.c_int, C.c_int, C.POINTER(_P)]),
+    ('apvae_plan_create', C.c_int, [C.POINTER(ConvTerm), C.c_int, C.c_int, C.c_int, C.POINTER(Tuning), C.POINTER(_P)]),
     ('apvae_plan_get_info', C.c_int, [_P, C.POINTER(PlanInfo)]),
     ('apvae_plan_copy_steps', C.c_int, [_P, C.POINTER(C.c_int32)]),
     ('apvae_plan_copy_weights', C.c_int, [_P, C.POINTER(C.c_uint16)]),

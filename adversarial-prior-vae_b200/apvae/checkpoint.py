@@ -11,7 +11,7 @@ experiment/dmm/dmm_cifar10.py:1105-1126).  A Saver checkpoint with prefix P is
     <dir>/checkpoint          text: model_checkpoint_path: "…"   (what tf.train.latest_checkpoint reads)
 
 Variable names are the TF variable names without ":0" — exactly the names `apvae_load_weights` takes
-(`q_net/level_0/residual/conv_0/kernel`, …, `p_net/xi`, `beta`, `log_Z`).  This module reads that format (and writes
+(`q_net/level_0/residual/conv_0/kernel`, …, `p_net/xi`, `beta`, `get_log_Z/log_Z`).  This module reads that format (and writes
 it, so that fixtures can be produced here, where TensorFlow cannot be installed); it is host-side only.
 
 Format parity is UNPINNED: there is no TensorFlow in this image and the reference ships no checkpoint file, so the
@@ -369,7 +369,14 @@ def latest_checkpoint(checkpoint_dir):
 def model_weights_from_checkpoint(prefix, config):
     """(weights, scalars) for `Model(config, weights)` / `Model.set_scalars(**scalars)` out of a reference checkpoint:
     every variable of the path's schema (KeyError names the first missing one), and xi / beta / log_Z when the
-    checkpoint holds them (`p_net/xi` dmm_cifar10.py:604, `beta` :860, `log_Z` :462)."""
+    checkpoint holds them.  Names follow the reference's scoping rules: `p_net/xi` (tf.get_variable inside the
+    @spt.global_reuse function p_net, dmm_cifar10.py:604), `beta` (a root-level tf.Variable, :860) and
+    `get_log_Z/log_Z` (spt.ScheduledVariable('log_Z') = tf.get_variable inside the @spt.global_reuse function get_log_Z,
+    :458-463, scaffold/scheduled_var.py:60; utils/reuse.py opens a variable scope named after the function); a bare
+    `log_Z` is accepted as a fallback.  A scalar the checkpoint does not hold is left out of `scalars` with a warning —
+    the caller's defaults (log_Z = 1.0, the variable's initial value) would otherwise shift adv_test_nll / pd_energy /
+    kl_adv_and_gaussian silently."""
+    import warnings
     from .model import weight_schema
     schema = weight_schema(config)
     w = load_checkpoint(prefix, [n for n, _ in schema])
@@ -380,7 +387,10 @@ def model_weights_from_checkpoint(prefix, config):
         w[name] = w[name].astype(np.float32)
     present = dict((n, s) for n, s, _ in list_variables(prefix))
     scalars = {}
-    for key, name in (('xi_raw', 'p_net/xi'), ('beta', 'beta'), ('log_Z', 'log_Z')):
-        if name in present:
-            scalars[key] = float(np.asarray(load_checkpoint(prefix, [name])[name]).reshape(-1)[0])
+    for key, names in (('xi_raw', ('p_net/xi',)), ('beta', ('beta',)), ('log_Z', ('get_log_Z/log_Z', 'log_Z'))):
+        name = next((n for n in names if n in present), None)
+        if name is None:
+            warnings.warn('checkpoint %r holds no %s: %s keeps its initial value' % (prefix, ' / '.join(names), key))
+            continue
+        scalars[key] = float(np.asarray(load_checkpoint(prefix, [name])[name]).reshape(-1)[0])
     return w, scalars

@@ -49,7 +49,11 @@ class ExpConfig(object):
         self.max_batch = 64
         self.max_chunk = 512
         self.enable_grad = False
-        self.precise = False       # split-precision G_theta / D_psi (fp32-class energies for the sampler, 3x MMA work)
+        self.precise = False       # split-precision forward of G_theta / D_psi for the sampler: True / 1 = activations AND kernels
+                                   # as hi + lo 16-bit pairs (3 tensor-core terms, fp32-class energies); 2 = activations only
+                                   # (2 terms: the kernels keep their 16-bit rounding, a fixed perturbation that cancels in
+                                   # E(z) - E(z'))
+        self.tuning = {}           # apvae_tuning overrides (kernel-variant selection for A-B runs and tests; {} = defaults)
         self.operand_dtype = 'fp16'  # 16-bit operand format of the tensor-core path: 'fp16' (11 significant bits; default)
                                      # or 'bf16' (8 bits, fp32's exponent range); fp32 accumulation either way
         for k, v in kw.items():
@@ -79,6 +83,7 @@ class ExpConfig(object):
         if self.operand_dtype not in ('fp16', 'bf16'):
             raise ValueError("operand_dtype must be 'fp16' or 'bf16'")
         c.operand_bf16 = int(self.operand_dtype == 'bf16')
+        c.tuning = _lib.Tuning.make(self.tuning)
         return c
 
 
@@ -301,6 +306,7 @@ class Model(object):
         z0 [n, z_dim] (or [n,1,z_dim]); eps [steps,n,z_dim], u [steps,n] optional fed-in noise.
         history_z=True also returns history_z [steps, ...z0.shape]: the state BEFORE each step (:200,235); the reference's
         plot_samples restarts its next run from history_z[-1] (:1061)."""
+        self._check_sampler_precision()
         z = self._f32(z0).clone()
         shape = tuple(z.shape)
         z2 = z.reshape(-1, self.config.z_dim)
@@ -318,6 +324,28 @@ class Model(object):
         if history_z:
             out['history_z'] = hz.reshape((steps,) + shape)
         return out
+
+    # absolute error of D(G(z)) a single-pass 16-bit forward leaves (measured maxima against the float64 oracle)
+    SINGLE_PASS_ENERGY_ERROR = {'fp16': 2e-3, 'bf16': 2e-2}
+
+    def _check_sampler_precision(self):
+        """The accept / reject exponent of MALA carries pull_back_energy_weight * sigmoid(xi) * D(G(z)): at the reference's
+        weight of 1000 a single-pass 16-bit forward puts ~1 nat (fp16) to ~10 nats (bf16) of rounding noise into it and
+        the chain silently walks away from the reference's.  Say so, once per model, unless the caller has chosen a
+        split-precision forward (config.precise = 1 or 2)."""
+        if int(self.config.precise) != 0 or getattr(self, '_precision_warned', False):
+            return
+        import math
+        import warnings
+        xi = 1.0 / (1.0 + math.exp(-self.xi_raw))
+        noise = self.config.pull_back_energy_weight * xi * self.SINGLE_PASS_ENERGY_ERROR[self.config.operand_dtype]
+        if noise > 0.1:
+            self._precision_warned = True
+            warnings.warn('MALA with a single-pass %s forward: pull_back_energy_weight * xi = %.0f turns the ~%.0e error of '
+                          'D(G(z)) into ~%.1f nats inside the acceptance ratio; build the model with ExpConfig(precise=2) '
+                          '(or precise=True) to sample the reference\'s chain' %
+                          (self.config.operand_dtype, self.config.pull_back_energy_weight * xi,
+                           self.SINGLE_PASS_ENERGY_ERROR[self.config.operand_dtype], noise), RuntimeWarning, stacklevel=3)
 
     def fill_normal(self, shape, seed=0, offset=0, truncated=False):
         """N(0, 1) draws (Philox, in-kernel) as tf.random_normal inside zd.Normal.sample; `truncated`: resampled

@@ -21,9 +21,9 @@ def pad16(c):
 class Plan(object):
     """A planned op: sum of conv terms sharing one output grid."""
 
-    def __init__(self, terms, capacity_n, dtype='fp16'):
+    def __init__(self, terms, capacity_n, dtype='fp16', tuning=None):
         """dtype: the 16-bit operand format ('fp16' default, 'bf16'): kernels are packed in it, sources and 16-bit
-        outputs hold it."""
+        outputs hold it.  tuning: dict of apvae_tuning overrides (kernel variant selection; None = defaults)."""
         if dtype not in ('fp16', 'bf16'):
             raise ValueError("dtype must be 'fp16' or 'bf16'")
         self.dtype = dtype
@@ -48,7 +48,9 @@ class Plan(object):
                 self._keep.append(b)
                 arr[i].bias = b.ctypes.data_as(C.POINTER(C.c_float))
         self._h = C.c_void_p()
-        check(lib.apvae_plan_create(arr, len(terms), int(capacity_n), int(dtype == 'bf16'), C.byref(self._h)))
+        self._tuning = _lib.Tuning.make(tuning)
+        check(lib.apvae_plan_create(arr, len(terms), int(capacity_n), int(dtype == 'bf16'), C.byref(self._tuning),
+                                    C.byref(self._h)))
         self.info = _lib.PlanInfo()
         check(lib.apvae_plan_get_info(self._h, C.byref(self.info)))
 
@@ -105,7 +107,7 @@ class Plan(object):
 
     def run(self, srcs, n_valid, out_raw=None, out_act=None, out_f32=None, f32_cols=0,
             res=None, res_mode=_lib.RES_NONE, mask=None, tanh_cols=0, bf16_zero_from=0,
-            device=0, bench_reps=0):
+            device=0, bench_reps=0, out_raw_lo=None, out_act_lo=None, res_lo=None):
         """srcs: bf16 CUDA tensors [capacity_n, H, W, Cp]; outputs are CUDA tensors
         whose last dim is the row pitch."""
         ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
@@ -122,6 +124,7 @@ class Plan(object):
         e.mask_dev = ptr(mask)
         e.ld_mask = int(mask.shape[-1]) if mask is not None else 0
         e.tanh_cols = int(tanh_cols)
+        e.out_raw_lo_dev, e.out_act_lo_dev, e.res_lo_dev = ptr(out_raw_lo), ptr(out_act_lo), ptr(res_lo)   # split precision
         arr = (C.c_void_p * len(srcs))(*[t.data_ptr() for t in srcs])
         if bench_reps > 0:
             ms = C.c_float()

@@ -8,6 +8,7 @@
 #include "../../include/apvae.h"
 #include "kernels.h"
 #include "model.h"
+#include "tuning.h"
 
 using namespace apvae;
 
@@ -22,16 +23,8 @@ struct apvae_plan {
     int sel = -1;                     // which patch plan the info / copy calls describe (apvae_plan_select_patch)
     std::vector<PatchPlan> row_phases;   // ... or two plans, one per output row phase, both column phases merged into N
     int f16 = 1;                         // operand format (op16.h)
+    apvae_tuning tuning = {};            // the options the plan was made with (also steer apvae_plan_run / _bench)
 };
-
-static int env_int(const char* name) {
-    const char* v = getenv(name);
-    return v ? atoi(v) : 0;
-}
-static bool patch_enabled() {
-    const char* v = getenv("APVAE_PATCH");
-    return !(v && v[0] == '0');
-}
 
 static std::string g_err;
 static std::mutex g_err_mu;
@@ -153,6 +146,7 @@ int apvae_load_weights(apvae_handle* h, int n, const char* const* names, const f
         if (it == m.weights.end()) { m.err = "missing variable '" + w.name + "'"; return APVAE_ERR_WEIGHTS; }
         if (it->second.shape != w.shape) { m.err = "variable '" + w.name + "' has the wrong shape"; return APVAE_ERR_WEIGHTS; }
     }
+    TuningScope tuning_scope(&m.cfg.tuning);          // kernel-selection overrides of this handle's config
     if (!m.build()) return APVAE_ERR_CUDA;
     return APVAE_OK;
 }
@@ -553,8 +547,10 @@ int apvae_aux_time(apvae_handle* h, int which, int n, int B, int reps, char* nam
 }
 
 // ---------------------------------------------------------------- layer-level interface
-int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, apvae_plan** out) {
+int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, const apvae_tuning* tune,
+                      apvae_plan** out) {
     if (!terms || nterms <= 0 || !out || capacity_n <= 0) return set_global_err("plan_create: bad arguments", APVAE_ERR_INVALID);
+    TuningScope tuning_scope(tune);
     std::vector<TermSpec> ts;
     for (int i = 0; i < nterms; ++i) {
         TermSpec t;
@@ -566,25 +562,27 @@ int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, 
     }
     apvae_plan* p = new apvae_plan();
     p->f16 = operand_bf16 ? 0 : 1;
+    if (tune) p->tuning = *tune;
+    const int force_macc = tuning().patch_macc, force_cluster = tuning().patch_cluster;
     std::string e;
     if (!plan_op(ts, capacity_n, &p->plan, &e)) { delete p; return set_global_err(e, APVAE_ERR_UNSUPPORTED); }
-    if (patch_enabled()) {
+    bool all_s2t = true;          // stride-2 transposed terms of one geometry: sub-pixel phase plans
+    for (const TermSpec& t : ts) all_s2t = all_s2t && t.transpose && t.stride == 2 && t.k == ts[0].k && t.cin == ts[0].cin;
+    if (switch_on(tuning().patch, true)) {
         std::string pe;
-        p->has_patch = plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->patch, &pe);
-        const char* eph = getenv("APVAE_PATCH_PHASES");
-        if (!p->has_patch && !(eph && eph[0] == '0') && ts.size() == 1 && ts[0].transpose && ts[0].stride == 2) {
+        p->has_patch = plan_patch_op(ts, capacity_n, force_macc, force_cluster, &p->patch, &pe);
+        if (!p->has_patch && switch_on(tuning().patch_phases, true) && all_s2t) {
             p->phases.resize(4);
             for (int ph = 0; ph < 4; ++ph)
-                if (!plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->phases[ph], &pe, ph)) {
+                if (!plan_patch_op(ts, capacity_n, force_macc, force_cluster, &p->phases[ph], &pe, ph)) {
                     p->phases.clear();
                     break;
                 }
             // both column phases per op (two ops); used by plan_run when the output rows are unpadded
-            const char* emg = getenv("APVAE_PATCH_MERGE");
-            if (!p->phases.empty() && !(emg && emg[0] == '0')) {
+            if (!p->phases.empty() && switch_on(tuning().patch_merge, true)) {
                 p->row_phases.resize(2);
                 for (int py = 0; py < 2; ++py)
-                    if (!plan_patch_op(ts, capacity_n, env_int("APVAE_PATCH_MACC"), env_int("APVAE_PATCH_CLUSTER"), &p->row_phases[py], &pe, 4 + py)) {
+                    if (!plan_patch_op(ts, capacity_n, force_macc, force_cluster, &p->row_phases[py], &pe, 4 + py)) {
                         p->row_phases.clear();
                         break;
                     }
@@ -688,6 +686,7 @@ int apvae_plan_run(const apvae_plan* p, int device, const void* const* src_dev, 
 int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev, int n_valid,
                      const apvae_epilogue* epi, int reps, float* ms_per_launch) {
     if (!p || !src_dev || !epi) return set_global_err("null argument", APVAE_ERR_INVALID);
+    TuningScope tuning_scope(&p->tuning);
     DeviceInfo dev;
     std::string e;
     if (!device_open(device, &dev, &e)) return set_global_err(e, APVAE_ERR_NO_DEVICE);
@@ -697,6 +696,7 @@ int apvae_plan_bench(const apvae_plan* p, int device, const void* const* src_dev
     ep.out_f32 = epi->out_f32_dev; ep.ld_f32 = epi->ld_f32; ep.f32_cols = epi->f32_cols;
     ep.res = epi->res_dev; ep.res_mode = epi->res_mode; ep.ld_res = epi->ld_res;
     ep.mask = epi->mask_dev; ep.ld_mask = epi->ld_mask; ep.tanh_cols = epi->tanh_cols;
+    ep.out_raw_lo = epi->out_raw_lo_dev; ep.out_act_lo = epi->out_act_lo_dev; ep.res_lo = epi->res_lo_dev;
     ep.f16 = p->f16;
     // the op, or the four phase ops of a stride-2 transposed conv (only with a bf16-only epilogue; else the tap-GEMM op)
     std::vector<std::unique_ptr<DevOp>> ops;

@@ -1,4 +1,5 @@
 #include "model.h"
+#include "tuning.h"
 
 #include <cuda_runtime.h>
 #include <stdlib.h>
@@ -61,11 +62,10 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     std::unique_ptr<DevOp> op(new DevOp());
     op->name = name;
     // <= 4 -> <= 4 channels, stride 1 (the first conv on the image channels and its adjoint): CUDA cores (tinyconv.cu);
-    // APVAE_TINY=0 keeps the tensor-core op (tuning / A-B only)
+    // tuning.tiny_conv = -1 keeps the tensor-core op (tuning / A-B only)
     {
-        const char* et = getenv("APVAE_TINY");
         const bool lo_parts = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;
-        if (!(et && et[0] == '0') && terms.size() == 1 && terms[0].stride == 1 && terms[0].cin <= kTinyMaxC && terms[0].cout <= kTinyMaxC &&
+        if (switch_on(tuning().tiny_conv, true) && terms.size() == 1 && terms[0].stride == 1 && terms[0].cin <= kTinyMaxC && terms[0].cout <= kTinyMaxC &&
             terms[0].k <= kTinyMaxK && (terms[0].k & 1) && !lo_parts && epi.tanh_cols == 0 && epi.bf16_zero_from >= terms[0].cout &&
             terms[0].in_cp % 8 == 0 && (epi.ldo % 8 == 0 || !(epi.out_raw || epi.out_act)) &&
             (!epi.out_f32 || epi.f32_cols == terms[0].cout) && (epi.res_mode == RES_NONE || epi.res)) {
@@ -101,35 +101,33 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
         }
     }
     // stride-1 convs on wide grids: the A-stationary kernel; everything else: the tap-GEMM kernel
-    const char* env = getenv("APVAE_PATCH");
+    const bool patch_on = switch_on(tuning().patch, true);
     PatchPlan pplan;
-    const char* em = getenv("APVAE_PATCH_MACC");
-    const char* ec = getenv("APVAE_PATCH_CLUSTER");
-    const char* emax = getenv("APVAE_PATCH_MAXN");            // widest output the A-stationary kernel takes (tuning)
-    const int patch_max_n = emax ? atoi(emax) : 256;
-    const bool split_epi = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;     // split precision: tap-GEMM only
+    const int force_macc = tuning().patch_macc, force_cluster = tuning().patch_cluster;
+    const int patch_max_n = tuning().patch_max_n > 0 ? tuning().patch_max_n : 256;    // widest output the A-stationary kernel takes
+    const bool split_epi = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;     // split precision: low-half outputs / residual (generic epilogue)
     // stride-2 transposed conv: four sub-pixel phases, each an A-stationary stride-1 op on the input grid
-    const char* eph = getenv("APVAE_PATCH_PHASES");
-    if (!(env && env[0] == '0') && !(eph && eph[0] == '0') && !split_epi && terms.size() == 1 && terms[0].transpose &&
-        terms[0].stride == 2) {
+    bool all_s2t = !terms.empty();
+    for (const TermSpec& t : terms) all_s2t = all_s2t && t.transpose && t.stride == 2 && t.k == terms[0].k && t.cin == terms[0].cin;
+    const bool split_on_patch = switch_on(tuning().patch_split, true);
+    if (patch_on && switch_on(tuning().patch_phases, true) && (split_epi ? split_on_patch : terms.size() == 1) && all_s2t) {
         std::vector<std::unique_ptr<DevOp>> ops;
         double m = 0;
         bool ok = true;
         // two ops, one per output row phase, each writing both column phases as one 2 * cout-wide row (needs unpadded
         // output rows and 2 * cout <= 256); else one op per sub-pixel phase.  APVAE_PATCH_MERGE=0: always four.
-        const char* emg = getenv("APVAE_PATCH_MERGE");
-        if (!(emg && emg[0] == '0')) {
+        if (switch_on(tuning().patch_merge, true)) {
             for (int py = 0; py < 2 && ok; ++py) {
                 PatchPlan pp;
                 std::string e2;
                 std::unique_ptr<DevOp> o(new DevOp());
                 o->name = name + "/rows" + std::to_string(py);
-                ok = plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pp, &e2, 4 + py) && pp.npad <= patch_max_n &&
+                ok = plan_patch_op(terms, cap, force_macc, force_cluster, &pp, &e2, 4 + py) && pp.npad <= patch_max_n &&
                      devop_create_patch(dev, pp, srcs.data(), epi, o.get(), &e2);
                 if (ok) { m += pp.macs_per_image; ops.push_back(std::move(o)); }
             }
             if (ok) {
-                if (macs) *macs += m;
+                if (macs) *macs += m / split_terms();
                 for (auto& o : ops) prog.push_back(std::move(o));
                 return true;
             }
@@ -141,24 +139,26 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
             std::string e2;
             std::unique_ptr<DevOp> o(new DevOp());
             o->name = name + "/phase" + std::to_string(ph);
-            ok = plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pp, &e2, ph) && pp.npad <= patch_max_n &&
+            ok = plan_patch_op(terms, cap, force_macc, force_cluster, &pp, &e2, ph) && pp.npad <= patch_max_n &&
                  devop_create_patch(dev, pp, srcs.data(), epi, o.get(), &e2);
             if (ok) { m += pp.macs_per_image; ops.push_back(std::move(o)); }
         }
         if (ok) {
-            if (macs) *macs += m;
+            if (macs) *macs += m / split_terms();
             for (auto& o : ops) prog.push_back(std::move(o));
             return true;
         }
         cudaGetLastError();
     }
-    if (!(env && env[0] == '0') && !split_epi &&
-        plan_patch_op(terms, cap, em ? atoi(em) : 0, ec ? atoi(ec) : 0, &pplan, &perr) && pplan.npad <= patch_max_n) {
+    // (a split-precision op fits when it has two terms, hi and lo activations on single kernels — precise = 2; its low
+    // halves leave through the generic epilogue)
+    if (patch_on && (!split_epi || split_on_patch) &&
+        plan_patch_op(terms, cap, force_macc, force_cluster, &pplan, &perr) && pplan.npad <= patch_max_n) {
         if ((int)srcs.size() != pplan.nsrc) return fail("plan " + name + ": source count mismatch");
         const bool made = devop_create_patch(dev, pplan, srcs.data(), epi, op.get(), &perr);
         if (!made && pplan.fold == 1) return fail(perr);
         if (made) {
-            if (macs) *macs += pplan.macs_per_image / (split_mode ? 3.0 : 1.0);
+            if (macs) *macs += pplan.macs_per_image / split_terms();
             prog.push_back(std::move(op));
             return true;
         }
@@ -171,7 +171,7 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     if (!plan_op(terms, cap, &plan, &perr)) return fail("plan " + name + ": " + perr);
     if ((int)srcs.size() != plan.nsrc) return fail("plan " + name + ": source count mismatch");
     if (!devop_create(dev, plan, srcs.data(), epi, op.get(), &perr)) return fail(perr);
-    if (macs) *macs += plan.macs_per_image / (split_mode ? 3.0 : 1.0);   // split precision: 3 tensor-core terms per algorithmic product
+    if (macs) *macs += plan.macs_per_image / split_terms();   // split precision: 3 (or 2) tensor-core terms per algorithmic product
     prog.push_back(std::move(op));
     return true;
 }
@@ -208,7 +208,10 @@ bool Model::push_terms(std::vector<TermSpec>& terms, std::vector<const void*>& s
     }
     terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, &whi, bias));
     terms.push_back(term(s0 + 1, transpose, k, stride, cin, cout, lo, &whi, nullptr));
-    terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, &wlo, nullptr));
+    // precise = 2 ("activation split"): kernels stay single 16-bit values (A_hi W + A_lo W).  Their rounding is a fixed,
+    // smooth perturbation of the energy that cancels in MALA's E(z) - E(z'); the per-element rounding of the ACTIVATIONS,
+    // which differs between z and z' and is what turns accept / reject into noise, is removed at 2x instead of 3x the MMAs.
+    if (cfg.precise != 2) terms.push_back(term(s0, transpose, k, stride, cin, cout, hi, &wlo, nullptr));
     srcs.push_back(hi.ptr);
     srcs.push_back(lo.ptr);
     return true;
@@ -232,9 +235,8 @@ bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& 
     if (!r.ptr) return false;
     if (sp) { r_lo = alloc_act(cap, H, Wd, cin); if (!r_lo.ptr) return false; }
     // <= 3 input channels (D_psi/level_0 of the CIFAR models: 3 -> 3 -> 16 at 32 x 32): the whole block is one HBM-bound
-    // CUDA-core kernel (block0.cu) with fp32 weights; APVAE_SMALL_BLOCK=0 keeps the two tensor-core ops (tuning / A-B only)
-    const char* esb = getenv("APVAE_SMALL_BLOCK");
-    if (!sp && !(esb && esb[0] == '0') && s == 1 && k == kSmallBlockMaxK && cin <= kSmallBlockMaxCin && cout == kSmallBlockMaxCout &&
+    // CUDA-core kernel (block0.cu) with fp32 weights; tuning.small_block = -1 keeps the two tensor-core ops (tuning / A-B only)
+    if (!sp && switch_on(tuning().small_block, true) && s == 1 && k == kSmallBlockMaxK && cin <= kSmallBlockMaxCin && cout == kSmallBlockMaxCout &&
         use_sc && H <= kSmallBlockMaxHW && Wd <= kSmallBlockMaxHW) {
         const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cin, cout}), *bs = W_(pre + "shortcut/bias", {cout});
         if (!ks || !bs) return false;

@@ -165,6 +165,7 @@ public:
                     const Tensor& lo, bool transpose, int k, int stride, int cin, int cout, const std::string& wname,
                     const HostArr* kernel, const HostArr* bias);
     bool split_mode = false;   // set while building G_theta / D_psi of a `precise` handle
+    double split_terms() const { return !split_mode ? 1.0 : cfg.precise == 2 ? 2.0 : 3.0; }   // tensor-core terms per algorithmic product
     bool add_op(Program& prog, const std::string& name, const std::vector<TermSpec>& terms,
                 const std::vector<const void*>& srcs, const Epilogue& epi, int cap, double* macs);
     bool conv_block(Program& prog, const std::string& root, const BlockSpec& b, const Pair& in, bool need_raw,

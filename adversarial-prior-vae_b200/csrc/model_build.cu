@@ -6,6 +6,7 @@
 #include <vector>
 #include "kernels.h"
 #include "model.h"
+#include "tuning.h"
 
 namespace apvae {
 
@@ -188,9 +189,8 @@ bool Model::build_g() {
     e.ldo = d_in.raw.cp; e.bf16_zero_from = Cx;
     e.out_f32 = head_f32; e.ld_f32 = nout; e.f32_cols = nout; e.tanh_cols = Cx;
     // nout <= 8 outputs per pixel: an HBM-bound stream, run on the CUDA cores (heads.cu) with fp32 weights;
-    // APVAE_HEADS_GEMM=1 keeps the 1x1 tensor-core op (tuning / A-B only)
-    const char* hg = getenv("APVAE_HEADS_GEMM");
-    if (!(hg && hg[0] == '1') && nout <= 8 && ((cg + 7) / 8) * 8 * nout <= kHeadsMaxW && d_in.raw.cp % 8 == 0) {
+    // tuning.heads_gemm = +1 keeps the 1x1 tensor-core op (tuning / A-B only)
+    if (!switch_on(tuning().heads_gemm, false) && nout <= 8 && ((cg + 7) / 8) * 8 * nout <= kHeadsMaxW && d_in.raw.cp % 8 == 0) {
         std::unique_ptr<DevOp> op(new DevOp());
         op->name = "G_theta/heads";
         op->is_heads = true;

@@ -31,7 +31,7 @@ constexpr int kMaxStages = 12;
 
 }  // namespace
 
-template <int KC, bool kTwo, bool kMask, bool kF16>
+template <int KC, bool kTwo, bool kMask, bool kF16, bool kSplit>
 __global__ void __launch_bounds__(kThreads, 1)
 patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -288,6 +288,28 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             }
             return true;
         };
+        // split precision: the residual of block s as a hi + lo pair into boxes 0 and 1 behind ONE barrier (single buffered)
+        auto issue_res_split = [&](const Seq& s) {
+            if (res_mode == RES_NONE || !seq_ok(s)) return false;
+            const int po = s.m * kTileM + q * 32;
+            const int gy = s.n * H + s.ty * rows_tile + (po >> lgW), x0 = po & (W - 1);
+            int rp0 = gy * W + x0;
+            if (res_mode == RES_EVEN) {
+                if (gy & 1) return false;
+                rp0 = (gy >> 1) * (W >> 1) + (x0 >> 1);
+            }
+            if (leader) {
+                mbar_expect_tx(resbar(q, 0), 2 * res_bytes);
+                if (fold) {
+                    tma_load_5d(wbase, &p.tm_res, resbar(q, 0), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                    tma_load_5d(wbase + kFastEpiBoxBytes, &p.tm_res_lo, resbar(q, 0), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                } else {
+                    tma_load_2d(wbase, &p.tm_res, resbar(q, 0), s.cb, rp0);
+                    tma_load_2d(wbase + kFastEpiBoxBytes, &p.tm_res_lo, resbar(q, 0), s.cb, rp0);
+                }
+            }
+            return true;
+        };
         // leaky-relu' mask (adjoint ops): the forward activation box of block s, one block ahead, into the act staging box
         // (such ops write no act output); returns whether one was issued (warp-uniform)
         constexpr bool has_mask = kMask;               // its own instantiation: the forward ops' epilogue carries none of this
@@ -324,7 +346,9 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         seq_next(mseq);
         uint32_t mph = 0;
         bool iss0 = false, iss1 = false;
-        if (!dbl) {
+        if constexpr (kSplit) {
+            iss0 = issue_res_split(pre); seq_next(pre);
+        } else if (!dbl) {
             iss0 = issue_res(pre, 0); seq_next(pre);
             iss1 = issue_res(pre, 1); seq_next(pre);
         }
@@ -444,6 +468,98 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             kb ^= 1;
         };
 
+        // Split-precision block: the value v = acc + bias + (res_hi + res_lo) leaves as v_hi = round16(v), v_lo = round16(v - v_hi)
+        // (and the same pair of leaky_relu(v)).  Two store passes through the ONE (raw, act) staging pair — hi, then lo; the
+        // value is recomputed per 8-column chunk in each pass (TMEM registers, bias row and residual boxes stay put), so
+        // the register footprint is that of the plain block.  The residual boxes are refilled when pass 2 has read them.
+        auto block_split = [&](auto bw_c, uint32_t taddr, bool last_of_tile) {
+            constexpr int BW = decltype(bw_c)::value;
+            constexpr int NCH = BW / 8;
+            uint32_t v[(BW + 31) / 32 * 32];
+            {
+                uint32_t (&v0)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[0]);
+                if constexpr (BW >= 32) tmem_ld32(taddr, v0);
+                else { uint32_t (&l0)[16] = *reinterpret_cast<uint32_t (*)[16]>(&v[0]); tmem_ld16(taddr, l0); }
+                if constexpr (BW == 64) { uint32_t (&v1)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[32]); tmem_ld32(taddr + 32, v1); }
+                if constexpr (BW == 48) { uint32_t (&l1)[16] = *reinterpret_cast<uint32_t (*)[16]>(&v[32]); tmem_ld16(taddr + 32, l1); }
+            }
+            const bool has_res = iss0;
+            if (has_res) { mbar_wait(resbar(q, 0), ph0); ph0 ^= 1; }
+            tmem_ld_wait();
+            if (last_of_tile) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
+            }
+            const uint32_t rbuf = wbase + res_off;
+            const uint32_t bias_b = bias_s + cur.cb * 4;
+            auto value = [&](int ch, float (&f)[8]) {
+                const float4 b0 = ld_shared_f4(bias_b + ch * 32);
+                const float4 b1 = ld_shared_f4(bias_b + ch * 32 + 16);
+                f[0] = __uint_as_float(v[ch * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[ch * 8 + 1]) + b0.y;
+                f[2] = __uint_as_float(v[ch * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[ch * 8 + 3]) + b0.w;
+                f[4] = __uint_as_float(v[ch * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[ch * 8 + 5]) + b1.y;
+                f[6] = __uint_as_float(v[ch * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[ch * 8 + 7]) + b1.w;
+                if (has_res) {
+                    const uint4 rh = ld_shared_v4(rbuf + (((uint32_t)ch ^ rsw) << 4));
+                    const uint4 rl = ld_shared_v4(rbuf + kFastEpiBoxBytes + (((uint32_t)ch ^ rsw) << 4));
+                    if (lane_res) {
+                        const uint32_t wh[4] = {rh.x, rh.y, rh.z, rh.w}, wl[4] = {rl.x, rl.y, rl.z, rl.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            const float2 a = op16::unpack<kF16>(wh[i]), b = op16::unpack<kF16>(wl[i]);
+                            f[2 * i] += a.x + b.x; f[2 * i + 1] += a.y + b.y;
+                        }
+                    }
+                }
+            };
+#pragma unroll
+            for (int pass = 0; pass < 2; ++pass) {
+                if (leader) tma_store_wait_read();         // the staging pair is free again (previous pass / previous block)
+                __syncwarp();
+#pragma unroll
+                for (int ch = 0; ch < NCH; ++ch) {
+                    float f[8];
+                    value(ch, f);
+                    uint32_t r4[4], a4[4];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const float a0 = fmaxf(f[2 * i], alpha * f[2 * i]), a1 = fmaxf(f[2 * i + 1], alpha * f[2 * i + 1]);
+                        const uint32_t rh = op16::pack<kF16>(f[2 * i], f[2 * i + 1]), ah = op16::pack<kF16>(a0, a1);
+                        if (pass == 0) { r4[i] = rh; a4[i] = ah; }
+                        else {
+                            r4[i] = op16::pack<kF16>(f[2 * i] - op16::lo<kF16>(rh), f[2 * i + 1] - op16::hi<kF16>(rh));
+                            a4[i] = op16::pack<kF16>(a0 - op16::lo<kF16>(ah), a1 - op16::hi<kF16>(ah));
+                        }
+                    }
+                    if (want_raw) st_shared_v4(rawbuf + st_off + (((uint32_t)ch ^ sw) << 4), r4[0], r4[1], r4[2], r4[3]);
+                    if (want_act) st_shared_v4(actbuf + st_off + (((uint32_t)ch ^ sw) << 4), a4[0], a4[1], a4[2], a4[3]);
+                }
+                if (pass == 1) {
+                    __syncwarp();                          // every lane has read the residual pair: fetch the next block's
+                    iss0 = issue_res_split(pre);
+                    seq_next(pre);
+                }
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (leader && do_store && cur.n < n_valid) {
+                    const int po = cur.m * kTileM + q * 32;
+                    const int oyy = cur.ty * rows_tile + (po >> lgW), ox0 = po & (W - 1);
+                    const CUtensorMap* mr = pass ? &p.tm_raw_lo : &p.tm_raw;
+                    const CUtensorMap* ma = pass ? &p.tm_act_lo : &p.tm_act;
+                    if (fold) {
+                        if (want_raw) tma_store_5d(mr, rawbuf, cur.cb, 0, 0, oyy, cur.n);
+                        if (want_act) tma_store_5d(ma, actbuf, cur.cb, 0, 0, oyy, cur.n);
+                    } else {
+                        if (want_raw) tma_store_4d(mr, rawbuf, cur.cb, ox0, oyy, cur.n);
+                        if (want_act) tma_store_4d(ma, actbuf, cur.cb, ox0, oyy, cur.n);
+                    }
+                    tma_store_commit();
+                }
+            }
+            ++tblk;
+        };
+
         const int bw_last = NT - ((NT - 1) & ~63);          // columns of the last block of an accumulator: 16, 32, 48 or 64
         for (int g = cluster_id; g < rounds_total; g += num_clusters, ++tit) {
             if (q == 0 && lane == 0) stamp(tit, 4);
@@ -458,10 +574,17 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                         const bool last_cb = cb + 64 >= NT;
                         const bool last = last_cb && (m + 1 == macc);
                         const int bw = last_cb ? bw_last : 64;
-                        if (bw == 64) block(std::integral_constant<int, 64>{}, tbase + cb, last);
-                        else if (bw == 32) block(std::integral_constant<int, 32>{}, tbase + cb, last);
-                        else if (bw == 16) block(std::integral_constant<int, 16>{}, tbase + cb, last);
-                        else block(std::integral_constant<int, 48>{}, tbase + cb, last);
+                        if constexpr (kSplit) {
+                            if (bw == 64) block_split(std::integral_constant<int, 64>{}, tbase + cb, last);
+                            else if (bw == 32) block_split(std::integral_constant<int, 32>{}, tbase + cb, last);
+                            else if (bw == 16) block_split(std::integral_constant<int, 16>{}, tbase + cb, last);
+                            else block_split(std::integral_constant<int, 48>{}, tbase + cb, last);
+                        } else {
+                            if (bw == 64) block(std::integral_constant<int, 64>{}, tbase + cb, last);
+                            else if (bw == 32) block(std::integral_constant<int, 32>{}, tbase + cb, last);
+                            else if (bw == 16) block(std::integral_constant<int, 16>{}, tbase + cb, last);
+                            else block(std::integral_constant<int, 48>{}, tbase + cb, last);
+                        }
                         seq_next(cur);
                     }
                 }
@@ -483,6 +606,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         epilogue_load_bias(p.epi, bias_s, p.NT, 0, lane);
         int acc = 0;
         uint32_t acc_phase = 0;
+        const bool split_epi = p.epi.out_raw_lo != nullptr || p.epi.out_act_lo != nullptr || p.epi.res_lo != nullptr;
         auto make_row = [&](int tile, int m) {
             const int n = tile / p.tiles_y;
             const int y0 = (tile % p.tiles_y) * p.rows_tile;
@@ -519,7 +643,9 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 const bool more = !last_m || (g + num_clusters < rounds_total);
                 const EpiRow nrow = last_m ? make_row((g + num_clusters) * csize + (int)rank, 0) : make_row(tile, m + 1);
                 const uint32_t taddr0 = tmem_base + acc * kAccColStride + m * p.NT + ((uint32_t)(q * 32) << 16);
-                pre = epilogue_block<false, kF16>(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
+                // split precision (hi + lo outputs / residual): the same block body with the low halves written from registers
+                pre = split_epi ? epilogue_block<true, kF16>(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0)
+                                : epilogue_block<false, kF16>(p.epi, taddr0, p.NT, 0, row, wsm, bias_s, lane, rv, pre, more ? &nrow : nullptr, 0);
                 row = nrow;
             }
             tc_fence_before();
@@ -552,11 +678,15 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     if (two && c != 2) return (int)cudaErrorInvalidValue;
     const bool mk = p.fast_epi && p.fast_mask;
     const bool f16 = p.epi.f16 != 0;
-#define APVAE_PATCH_PICK2(KC, TWO, MK) kern = f16 ? patchgemm_kernel<KC, TWO, MK, true> : patchgemm_kernel<KC, TWO, MK, false>
-#define APVAE_PATCH_PICK(KC)                                                                              \
-    do {                                                                                                  \
-        if (two) { if (mk) APVAE_PATCH_PICK2(KC, true, true); else APVAE_PATCH_PICK2(KC, true, false); }  \
-        else { if (mk) APVAE_PATCH_PICK2(KC, false, true); else APVAE_PATCH_PICK2(KC, false, false); }    \
+    const bool sp = p.fast_epi && p.split;
+    if (sp && mk) return (int)cudaErrorInvalidValue;          // the split-precision TMA epilogue carries no mask
+#define APVAE_PATCH_PICK2(KC, TWO, MK, SP) kern = f16 ? patchgemm_kernel<KC, TWO, MK, true, SP> : patchgemm_kernel<KC, TWO, MK, false, SP>
+#define APVAE_PATCH_PICK(KC)                                                                                           \
+    do {                                                                                                               \
+        if (two) { if (sp) APVAE_PATCH_PICK2(KC, true, false, true); else if (mk) APVAE_PATCH_PICK2(KC, true, true, false);     \
+                   else APVAE_PATCH_PICK2(KC, true, false, false); }                                                   \
+        else { if (sp) APVAE_PATCH_PICK2(KC, false, false, true); else if (mk) APVAE_PATCH_PICK2(KC, false, true, false);       \
+               else APVAE_PATCH_PICK2(KC, false, false, false); }                                                      \
     } while (0)
     switch (p.kc) {
         case 16: APVAE_PATCH_PICK(16); break;
@@ -583,8 +713,8 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     // one persistent cluster per co-resident slot (GPC boundaries can leave a few SMs without a full cluster)
     int max_clusters = num_sms / c;
     if (c > 1) {
-        static int cached[24][5] = {{0}};                     // [kc index, pair mode][cluster] -> max active clusters
-        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (mk ? 6 : 0) + (f16 ? 12 : 0);
+        static int cached[36][5] = {{0}};                     // [kc index, pair mode, epilogue variant, format][cluster] -> max active clusters
+        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (mk ? 6 : sp ? 12 : 0) + (f16 ? 18 : 0);
         if (cached[ki][c] == 0) {
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki][c] = nc;

@@ -75,7 +75,11 @@ struct alignas(64) PatchGemmParams {
                                      // one block ahead into the (unused) act staging box
     int fast_mask;                   // 1: tm_mask is valid and the TMA epilogue multiplies by leaky-relu'(mask); 2: tm_mask is the
                                      // 4-D strided view of a sub-pixel phase, loaded at the store's coordinates
-    int debug;                       // tuning only (APVAE_PATCH_DEBUG): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
+    int split;                       // 1 (fast_epi, no mask): split-precision epilogue — every output is written as a hi + lo
+                                     // pair (tm_raw / tm_act and tm_raw_lo / tm_act_lo, two store passes through the same
+                                     // staging boxes) and the residual is read as hi + lo (tm_res / tm_res_lo, one box each)
+    CUtensorMap tm_raw_lo, tm_act_lo, tm_res_lo;
+    int debug;                       // tuning only (apvae_tuning.debug): 1 = no loads, 2 = no weight loads, 3 = no patch loads, 4 = no epilogue work, 5 = no output stores, 1x = x plus no loads (results are garbage)
     unsigned long long* trace;       // tuning only (APVAE_PATCH_TRACE): per-tile clock64 stamps of CTA 0, 16 slots per tile, 64 tiles
     EpilogueArgs epi;
 };

@@ -1,4 +1,5 @@
 #include "planner.h"
+#include "tuning.h"
 #include "op16.h"
 
 #include <stdlib.h>
@@ -6,6 +7,15 @@
 #include <algorithm>
 
 namespace apvae {
+
+namespace {
+const apvae_tuning kDefaultTuning = {};
+thread_local const apvae_tuning* t_tuning = nullptr;
+}  // namespace
+const apvae_tuning& tuning() { return t_tuning ? *t_tuning : kDefaultTuning; }
+TuningScope::TuningScope(const apvae_tuning* t) : prev_(t_tuning), copy_(t ? *t : kDefaultTuning) { t_tuning = &copy_; }
+TuningScope::~TuningScope() { t_tuning = prev_; }
+
 
 void same_padding(int in, int k, int s, int* out, int* lo, int* hi) {
     const int o = (in + s - 1) / s;
@@ -210,7 +220,9 @@ bool plan_op(const std::vector<TermSpec>& terms, int capacity_n, OpPlan* plan, s
 bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force_macc, int force_cluster,
                    PatchPlan* plan, std::string* err, int phase) {
     auto fail = [&](const char* m) { if (err) *err = m; return false; };
-    if (terms.empty() || terms.size() > (size_t)kPatchMaxSrc) return fail("patch: 1..2 terms");
+    // up to kPatchMaxMaps terms over at most kPatchMaxSrc sources: conv + fused shortcut (two sources), or the products of
+    // a split-precision op (A_hi W_hi, A_lo W_hi[, A_hi W_lo]: sources hi and lo, one activation map per term)
+    if (terms.empty() || terms.size() > (size_t)kPatchMaxMaps) return fail("patch: 1..4 terms");
     PatchPlan& P = *plan;
     P = PatchPlan();
     P.capacity_n = capacity_n;
@@ -219,24 +231,25 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // (row phase = one tensor map each, column phase folded into the channel coordinate)
     bool s2c = (phase < 0);
     for (const TermSpec& t : terms) s2c = s2c && !t.transpose && t.stride == 2;
-    if (s2c) { const char* e = getenv("APVAE_PATCH_S2"); if (e && e[0] == '0') return fail("patch: stride-2 convs disabled (APVAE_PATCH_S2=0)"); }
+    if (s2c && !switch_on(tuning().patch_s2, true)) return fail("patch: stride-2 convs disabled (tuning.patch_s2 = -1)");
     if (s2c && ((t0.in_w | t0.in_h) & 1)) return fail("patch: stride-2 conv needs an even input size");
     const int W = s2c ? t0.in_w / 2 : t0.in_w, H = s2c ? t0.in_h / 2 : t0.in_h, cp = t0.in_cp;
     if (W != 8 && W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 8, 16, 32, 64 or 128");
     // 8-wide images: two images side by side per tile row (PatchGemmParams::fold); needs whole pairs in the buffers
     const int fold = (W == 8) ? 2 : 1;
     if (fold > 1 && (capacity_n & 1)) return fail("patch: 8-wide images need an even capacity");
-    if (fold > 1) { const char* e = getenv("APVAE_PATCH_FOLD"); if (e && e[0] == '0') return fail("patch: 8-wide images disabled (APVAE_PATCH_FOLD=0)"); }
+    if (fold > 1 && !switch_on(tuning().patch_fold, true)) return fail("patch: 8-wide images disabled (tuning.patch_fold = -1)");
     const int Wt = W * fold;
     for (size_t i = 0; i < terms.size(); ++i) {
         const TermSpec& t = terms[i];
         if (phase < 0 && !s2c && t.stride != 1) return fail("patch: every term stride 1, or every term a stride-2 conv2d");
-        if (phase >= 0 && (terms.size() != 1 || !t.transpose || t.stride != 2)) return fail("patch: phases are for one stride-2 transposed term");
+        // sub-pixel phases: stride-2 transposed terms of ONE geometry (one term, or the hi / lo products of a split-precision op)
+        if (phase >= 0 && (!t.transpose || t.stride != 2 || t.k != t0.k || t.cin != t0.cin)) return fail("patch: phases are for stride-2 transposed terms of one geometry");
         if (!(t.k & 1)) return fail("patch: odd kernel sizes only");
         if (t.in_w != t0.in_w || t.in_h != t0.in_h) return fail("patch: terms disagree on the grid");
         if (t.in_cp != cp || cp % 16 || cp < t.cin) return fail("patch: bad channel padding");
         if (t.cout != t0.cout) return fail("patch: terms disagree on cout");
-        if (t.src != (int)i) return fail("patch: term i must read source i");
+        if (t.src < 0 || t.src >= kPatchMaxSrc) return fail("patch: at most two sources");
     }
     P.w = W; P.h = H; P.in_cp = cp; P.fold = fold; P.s2d = s2c ? 1 : 0;
     P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
@@ -247,7 +260,8 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.cout = merged ? 2 * t0.cout : t0.cout;
     P.npad = pad16(P.cout);
     if (P.npad > 256) return fail("patch: cout > 256");
-    P.nsrc = (int)terms.size();
+    P.nsrc = 0;
+    for (const TermSpec& t : terms) P.nsrc = std::max(P.nsrc, t.src + 1);
     const int rows128 = kTileM / Wt;
     if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
     int kmax = 1;
@@ -284,16 +298,16 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.tap_bytes = (uint32_t)P.npad * P.kc * 2;
     // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
     int tpi_want = std::max(1, std::min(kmax, (int)(32768u / P.tap_bytes)));
-    if (const char* e = getenv("APVAE_PATCH_TPI")) { const int v = atoi(e); if (v >= 1 && v <= kmax) tpi_want = v; }
-    // CTA pairs (cta_group::2): APVAE_PATCH_2CTA=1/0 overrides the default; APVAE_PATCH_2CTA_MINK moves the threshold.
+    { const int v = tuning().patch_tpi; if (v >= 1 && v <= kmax) tpi_want = v; }
+    // CTA pairs (cta_group::2): tuning.patch_2cta = +1 / -1 overrides the default; tuning.patch_2cta_min_k moves the threshold.
     // Measured on B200 (1000 samples, TFLOP/s single -> pair): 96->96 5x5 @32^2 1121 -> 1436, 192->192 3x3 @16^2
     // 1073 -> 1214, 128->128 3x3 @16^2 967 -> 1170, 64->64 3x3 @32^2 697 -> 786, 96->96 3x3 @32^2 778 -> 808; the
     // 16- and 32-channel layers (K < 500 per output) sit on the A-operand fetch floor either way and the whole step
     // was best with the threshold at 500 (sweep 1 / 100 / 250 / 500 / 1500 in one call: profiles/r1_notes.md).
     int two_min_k = 500;
-    if (const char* e = getenv("APVAE_PATCH_2CTA_MINK")) two_min_k = atoi(e);
+    if (tuning().patch_2cta_min_k > 0) two_min_k = tuning().patch_2cta_min_k;
     int two = ((long long)(phase >= 0 ? ph_nv * ph_nh : ktot) * cp >= two_min_k) ? 1 : 0;
-    if (const char* e = getenv("APVAE_PATCH_2CTA")) two = atoi(e) != 0;
+    if (tuning().patch_2cta != 0) two = tuning().patch_2cta > 0;
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;
     auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * (P.tap_bytes / (two ? 2 : 1)) + 1023u) & ~1023u; };
@@ -322,11 +336,11 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     while (P.b_stages > 2 && 2 * P.a_slot_bytes + P.b_stages * P.b_slot_bytes > budget) --P.b_stages;
     P.a_stages = 2;
     int a_cap = 4;
-    if (const char* e = getenv("APVAE_PATCH_ACAP")) { const int v = atoi(e); if (v >= 2 && v <= 12) a_cap = v; }
+    { const int v = tuning().patch_a_cap; if (v >= 2 && v <= 12) a_cap = v; }
     while (P.a_stages < a_cap && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
     while (P.b_stages < 12 && P.a_stages * P.a_slot_bytes + (P.b_stages + 1) * P.b_slot_bytes <= budget) ++P.b_stages;
-    if (const char* e = getenv("APVAE_PATCH_ASTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.a_stages) P.a_stages = v; }
-    if (const char* e = getenv("APVAE_PATCH_BSTAGES")) { const int v = atoi(e); if (v >= 1 && v <= P.b_stages) P.b_stages = v; }
+    { const int v = tuning().patch_a_stages; if (v >= 1 && v <= P.a_stages) P.a_stages = v; }
+    { const int v = tuning().patch_b_stages; if (v >= 1 && v <= P.b_stages) P.b_stages = v; }
     // cluster: weight-stream multicast across 2 / 4 CTAs is available (force_cluster) but measured slower
     // than independent CTAs on B200 for every layer of the reference models (the weights live in L2 anyway
     // and the cluster-wide slot release adds a round trip), so the default is 1.
@@ -398,6 +412,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         same_padding(W, t.k, 1, &o, &lo_w, &hi);
         const int nv = phase >= 0 ? ph_nv : t.k, nh = phase >= 0 ? ph_nh : t.k;
         const int dy0 = phase >= 0 ? ph_dy0 : -lo_h, dx0 = phase >= 0 ? ph_dx0 : -lo_w;
+        if (P.nmaps >= kPatchMaxMaps) return fail("patch: too many activation maps");
         P.map_src[P.nmaps] = t.src; P.map_ph[P.nmaps] = 0;
         P.prow[P.nmaps] = P.rows_tile + nv - 1;
         const int map = P.nmaps++;

@@ -1,4 +1,5 @@
 #include "runtime.h"
+#include "tuning.h"
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -146,8 +147,8 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.a_slot_bytes = plan.a_slot_bytes; p.b_slot_bytes = plan.b_slot_bytes;
     p.cluster = plan.cluster;
     p.two_cta = (plan.two_cta && plan.cluster == 2) ? 1 : 0;
-    { const char* dbg = getenv("APVAE_PATCH_DEBUG"); p.debug = dbg ? atoi(dbg) : 0; }
-    if (getenv("APVAE_PATCH_TRACE")) {        // tuning only: clock stamps of CTA 0 (read back by apvae_plan_bench)
+    p.debug = tuning().debug;
+    if (switch_on(tuning().trace, false)) {        // tuning only: clock stamps of CTA 0 (read back by apvae_plan_bench)
         APVAE_CUDA_OK(cudaMalloc(&op->d_trace, 64 * 16 * sizeof(unsigned long long)), err);
         APVAE_CUDA_OK(cudaMemset(op->d_trace, 0, 64 * 16 * sizeof(unsigned long long)), err);
         p.trace = op->d_trace;
@@ -157,14 +158,18 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     p.fast_epi = 0;
     p.res_rows = 32;
     {
-        const char* fe = getenv("APVAE_FAST_EPI");
         // a leaky-relu' mask (adjoint ops) rides along when the op writes no act output: its box takes the act staging box
-        const char* fm = getenv("APVAE_FAST_MASK");
         // (a merged-column-phase op needs unpadded mask rows, like its output rows)
-        const bool mask_ok = !epi.mask || ((plan.phase < 4 || epi.ld_mask * 2 == plan.npad) && !epi.out_act && epi.out_raw && !(fm && fm[0] == '0'));
-        const bool plain = mask_ok && !epi.out_f32 && !epi.out_raw_lo && !epi.out_act_lo && !epi.res_lo && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
+        const bool mask_ok = !epi.mask || ((plan.phase < 4 || epi.ld_mask * 2 == plan.npad) && !epi.out_act && epi.out_raw && switch_on(tuning().fast_mask, true));
+        // split precision (hi + lo outputs, hi + lo residual): its own epilogue variant, when every output and the residual
+        // come as complete pairs and there is no mask
+        const bool any_lo = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;
+        const bool split_ok = !any_lo || ((!epi.out_raw == !epi.out_raw_lo) && (!epi.out_act == !epi.out_act_lo) &&
+                                          (epi.res_mode == RES_NONE ? !epi.res_lo : epi.res_lo != nullptr) && !epi.mask &&
+                                          switch_on(tuning().patch_split, true));
+        const bool plain = mask_ok && !epi.out_f32 && split_ok && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
                            (epi.out_raw || epi.out_act) && (epi.res_mode == RES_NONE || epi.res != nullptr);
-        if (plain && !(fe && fe[0] == '0')) {
+        if (plain && switch_on(tuning().fast_epi, true)) {
             const cuuint64_t pixels = (cuuint64_t)plan.capacity_n * H * W;
             bool ok = true;
             auto map2d = [&](CUtensorMap* tm, const void* ptr, cuuint64_t rows, int ld, cuuint32_t box_rows) {
@@ -211,22 +216,34 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             const void* any_out = epi.out_raw ? epi.out_raw : epi.out_act;
             map_out(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out, epi.ldo);
             map_out(&p.tm_act, epi.out_act ? epi.out_act : any_out, epi.ldo);
-            if (epi.res_mode == RES_EVEN) {
-                p.res_rows = (plan.w >= 32) ? 16 : 8;
-                map2d(&p.tm_res, epi.res, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
-            } else if (epi.res_mode == RES_SAME && fold) {
-                const cuuint64_t ld = (cuuint64_t)epi.ld_res * 2;
-                cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
-                cuuint64_t strides4[4] = {ld, H * W * ld, W * ld, 2 * H * W * ld};
-                cuuint32_t box5[5] = {64, 8, 2, 2, 1};
-                const CUresult r = encode(&p.tm_res, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(epi.res), dims5, strides4,
-                                          box5, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                          CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-                if (r != CUDA_SUCCESS) ok = false;
-            } else if (epi.res_mode == RES_SAME) {
-                map2d(&p.tm_res, epi.res, pixels, epi.ld_res, 32);
+            auto map_res = [&](CUtensorMap* tm, const void* ptr) {
+                if (epi.res_mode == RES_EVEN) {
+                    p.res_rows = (plan.w >= 32) ? 16 : 8;
+                    map2d(tm, ptr, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
+                } else if (epi.res_mode == RES_SAME && fold) {
+                    const cuuint64_t ld = (cuuint64_t)epi.ld_res * 2;
+                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
+                    cuuint64_t strides4[4] = {ld, H * W * ld, W * ld, 2 * H * W * ld};
+                    cuuint32_t box5[5] = {64, 8, 2, 2, 1};
+                    const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), dims5, strides4,
+                                              box5, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    if (r != CUDA_SUCCESS) ok = false;
+                } else if (epi.res_mode == RES_SAME) {
+                    map2d(tm, ptr, pixels, epi.ld_res, 32);
+                } else {
+                    *tm = p.tm_raw;
+                }
+            };
+            map_res(&p.tm_res, epi.res);
+            p.split = any_lo ? 1 : 0;
+            if (any_lo) {
+                const void* any_lo_out = epi.out_raw_lo ? epi.out_raw_lo : epi.out_act_lo;
+                map_out(&p.tm_raw_lo, epi.out_raw_lo ? epi.out_raw_lo : any_lo_out, epi.ldo);
+                map_out(&p.tm_act_lo, epi.out_act_lo ? epi.out_act_lo : any_lo_out, epi.ldo);
+                map_res(&p.tm_res_lo, epi.res_lo);
             } else {
-                p.tm_res = p.tm_raw;
+                p.tm_raw_lo = p.tm_raw; p.tm_act_lo = p.tm_act; p.tm_res_lo = p.tm_res;
             }
             p.fast_mask = 0;
             if (epi.mask && plan.phase >= 0) {            // the mask of a sub-pixel phase: the same strided view as its output
@@ -296,11 +313,11 @@ bool devop_create(const DeviceInfo& dev, const OpPlan& plan, const void* const* 
         cuuint64_t dims[2] = {(cuuint64_t)plan.kc, (cuuint64_t)nsteps * plan.npad};
         cuuint64_t strides[1] = {(cuuint64_t)plan.kc * 2};
         // CTA pairs (cta_group::2): each CTA keeps half of every weight tile.  Pays off once the weight tile is wide
-        // enough for the shared-memory traffic to matter; APVAE_TAP_2CTA=0/1 overrides.
+        // enough for the shared-memory traffic to matter; tuning.tap_2cta = -1 / +1 overrides.
         const bool split_epi = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;
         bool two = false;    // measured: no gain for this kernel (1062 vs 1070 TFLOP/s at 192 wide, slower for short K): it is bound by the
                              // per-stage barrier round trip and the epilogue, not by shared-memory traffic; kept for experiments
-        if (const char* e = getenv("APVAE_TAP_2CTA")) two = atoi(e) != 0 && !split_epi;
+        if (tuning().tap_2cta != 0) two = tuning().tap_2cta > 0 && !split_epi;
         p.two_cta = two ? 1 : 0;
         cuuint32_t box[2] = {(cuuint32_t)plan.kc, (cuuint32_t)(two ? plan.nt / 2 : plan.nt)};
         CUresult r = encode(&p.tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, op->d_w, dims, strides, box, ones,

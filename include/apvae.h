@@ -36,6 +36,33 @@ typedef enum { APVAE_ARCH_A = 0, APVAE_ARCH_B = 1, APVAE_ARCH_M = 2 } apvae_arch
 /* Mirrors the ExpConfig fields the path reads
  * (experiment/dmm/dmm_cifar10.py:27-91, dmm_for_sampling.py:28-92,
  * dmm_bernouli_fashion.py ExpConfig). */
+/* Kernel-selection / tuning overrides (A-B comparisons, profiling probes, the layer tests' kernel variants).  All-zero =
+ * the library's defaults; "switch" fields: 0 = default, -1 = off, +1 = on.  The library reads NO environment variables:
+ * these travel in apvae_config.tuning (model handles) and with apvae_plan_create (layer plans). */
+typedef struct apvae_tuning {
+    int patch;              /* switch (default on): the A-stationary ("patch") tcgen05 kernel; off: every op on the tap-GEMM kernel */
+    int patch_macc;         /* accumulators sharing a weight tile: 1, 2 or 4 (0: planner's choice) */
+    int patch_cluster;      /* weight-stream multicast across a cluster of 2 / 4 CTAs (0: none) */
+    int patch_max_n;        /* widest output (padded cout) the patch kernel takes (0: 256) */
+    int patch_phases;       /* switch (default on): stride-2 transposed convs as sub-pixel phase ops */
+    int patch_merge;        /* switch (default on): both column phases of a row phase merged into N */
+    int patch_s2;           /* switch (default on): stride-2 convs through space-to-depth maps */
+    int patch_fold;         /* switch (default on): 8-wide grids as image pairs */
+    int patch_tpi;          /* vertical taps per weight item (0: up to 32 KB per item) */
+    int patch_2cta;         /* switch (default: by K per output): CTA pairs, tcgen05 cta_group::2 */
+    int patch_2cta_min_k;   /* K elements per output from which CTA pairs are used (0: 500) */
+    int patch_a_cap, patch_a_stages, patch_b_stages;   /* ring depths (0: planner's choice) */
+    int tap_2cta;           /* switch (default off): CTA pairs in the tap-GEMM kernel */
+    int fast_epi;           /* switch (default on): TMA-in / TMA-out epilogue of the patch kernel */
+    int fast_mask;          /* switch (default on): leaky-relu' mask through that epilogue (adjoint ops) */
+    int tiny_conv;          /* switch (default on): <= 4 -> <= 4 channel convs on the CUDA cores (tinyconv.cu) */
+    int small_block;        /* switch (default on): D_psi/level_0 as one fused CUDA-core block (block0.cu) */
+    int heads_gemm;         /* switch (default off): G_theta's 1x1 heads as a tensor-core op instead of heads.cu */
+    int patch_split;        /* switch (default on): two-term split-precision ops (precise = 2) on the patch kernel */
+    int debug;              /* patch kernel probe modes (skip loads / MMAs / epilogue / stores); 0 in any real run */
+    int trace;              /* switch (default off): clock stamps of CTA 0, read back by apvae_plan_bench */
+} apvae_tuning;
+
 typedef struct apvae_config {
     int arch;                       /* apvae_arch */
     int x_h, x_w, x_c;              /* config.x_shape */
@@ -52,9 +79,12 @@ typedef struct apvae_config {
     int enable_grad;                /* build the input-gradient programs (MALA, grad norms) */
     float smallest_step;            /* config.smallest_step (default MALA alpha) */
     int len_train;                  /* config.len_train (log-Z offset) */
-    int precise;                    /* 1: split-precision G_theta / D_psi (activations and kernels as hi + lo bf16 pairs,
+    int precise;                    /* 1: split-precision G_theta / D_psi (activations and kernels as hi + lo 16-bit pairs,
                                      * three tensor-core products per term, fp32 accumulate): fp32-class energies for the
-                                     * sampler at 3x the MMA work.  0: plain bf16 operands (evaluation default). */
+                                     * sampler at 3x the MMA work.  2: activations as hi + lo pairs, kernels single (two
+                                     * products per term): removes the per-element activation rounding, which differs between
+                                     * a MALA state and its proposal; the kernels' rounding stays (a fixed perturbation of D
+                                     * that cancels in E(z) - E(z')).  0: plain 16-bit operands (evaluation default). */
     int nf_layers;                  /* config.nf_layers when config.use_flow (dmm_bernouli_fashion.py:48,69,468-474): q(z|x) is
                                      * a FlowDistribution, the base Normal / TruncatedNormal draw pushed through that many planar
                                      * normalizing-flow layers (layers/flows/planar_nf.py); weights `posterior_flow/_i/{w,b,u}`
@@ -66,6 +96,7 @@ typedef struct apvae_config {
                                      * 0 (default): fp16 — 11 significant bits, D(G(z)) within 2e-3 of the float64 oracle;
                                      * 1: bf16 — 8 significant bits, fp32's exponent range (for activations beyond +-65504);
                                      * same tcgen05 rate either way (kind::f16). */
+    apvae_tuning tuning;            /* kernel-selection overrides, all-zero = defaults (see apvae_tuning) */
 } apvae_config;
 
 typedef struct apvae_handle apvae_handle;
@@ -147,6 +178,18 @@ enum { APVAE_ACCUM_WEIGHT = 9, APVAE_ACCUM_BATCHES = 10, APVAE_ACCUM_MSE = 11, A
        APVAE_ACCUM_SLOTS = 20 };
 int apvae_accumulate_metrics(apvae_handle* h, const float* per_image_dev, const float* prior4_dev, int B, int K,
                              double* accum_dev, void* stream);
+
+/* The one collective of a sharded evaluation (BASELINE north_star: "per-shard NLL/energy statistics are combined with a
+ * single NCCL allreduce over NVLink"): every rank passes the accumulator apvae_accumulate_metrics filled for its image
+ * shard (the reference combines on the host: np.average, trainer/evaluator.py:249-254; logsumexp, dmm_cifar10.py:1221-1222).
+ * ONE ncclAllGather of APVAE_ACCUM_SLOTS doubles per rank into gather_dev (caller-owned, double[nranks * APVAE_ACCUM_SLOTS]),
+ * then a device-side merge into accum_dev on every rank: additive slots summed, the log-Z (max, sum-exp) pair (slots 6, 7)
+ * rescaled to the common max.  nccl_comm: the caller's ncclComm_t; NCCL is bound at run time (dlopen of the libnccl.so.2
+ * already in the process), APVAE_ERR_UNSUPPORTED if there is none.  nranks == 1: no-op.  Asynchronous on `stream`. */
+int apvae_allreduce_metrics(void* nccl_comm, int nranks, double* accum_dev, double* gather_dev, void* stream);
+/* The merge alone, for accumulators gathered by another transport (MPI, torch.distributed): gathered_dev
+ * double[nranks][APVAE_ACCUM_SLOTS] -> accum_dev double[APVAE_ACCUM_SLOTS]. */
+int apvae_merge_metrics(const double* gathered_dev, int nranks, double* accum_dev, void* stream);
 
 /* test_pn_net branch (:883,915-927): Kp prior draws z ~ N(0, I) through G_theta and D_psi.
  * d_g_dev / log_pn_dev [Kp]: D(G(z)) and log N(z) per draw (either may be NULL);
@@ -272,13 +315,17 @@ typedef struct apvae_epilogue {
     const void* res_dev; int res_mode; int ld_res;
     const void* mask_dev; int ld_mask;
     int tanh_cols;
+    /* split precision (apvae_config.precise): low halves v - round16(v) of the 16-bit outputs and of the residual, same
+     * layouts as their high halves; NULL = a plain op */
+    void* out_raw_lo_dev;  void* out_act_lo_dev;  const void* res_lo_dev;
 } apvae_epilogue;
 
-/* Host-only planning (no GPU needed): step table, packed bf16 weights, TMA view geometry.
- * Environment (read at plan / model build time): APVAE_PATCH=0 disables the A-stationary kernel,
- * APVAE_PATCH_MACC / APVAE_PATCH_CLUSTER force its accumulator count / cluster size. */
-/* operand_bf16: the 16-bit format the kernels are packed in and the sources / outputs hold (see apvae_config). */
-int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, apvae_plan** out);
+/* Host-only planning (no GPU needed): step table, packed 16-bit weights, TMA view geometry.
+ * operand_bf16: the 16-bit format the kernels are packed in and the sources / outputs hold (see apvae_config).
+ * tuning: kernel-selection overrides (NULL = defaults), e.g. patch = -1 disables the A-stationary kernel, patch_macc /
+ * patch_cluster force its accumulator count / cluster size; kept with the plan and applied by apvae_plan_run / _bench. */
+int apvae_plan_create(const apvae_conv_term* terms, int nterms, int capacity_n, int operand_bf16, const apvae_tuning* tuning,
+                      apvae_plan** out);
 int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info);
 int apvae_plan_copy_steps(const apvae_plan* p, int32_t* out /* [total_steps][5]: src,dx,dy,ph,c0 */);
 int apvae_plan_copy_weights(const apvae_plan* p, uint16_t* out /* bf16 [total_steps][npad][kc] */);

@@ -24,7 +24,7 @@ def test_crc32c_known_answers():
 def test_round_trip_with_a_multi_block_index(tmp_path):
     rs = np.random.RandomState(0)
     arrays = {'p_net/xi': np.float32(0.25).reshape(()), 'beta': np.array(-1.5, dtype=np.float32),
-              'log_Z': np.array(3.0, dtype=np.float32), 'global_step': np.array(390000, dtype=np.int64),
+              'get_log_Z/log_Z': np.array(3.0, dtype=np.float32), 'global_step': np.array(390000, dtype=np.int64),
               'some/double': rs.normal(size=(3, 2)), 'flags': np.array([True, False])}
     for i in range(300):                       # > 4096 bytes of index entries: several data blocks + a real index block
         arrays['net/level_%d/residual/conv_0/kernel' % i] = rs.normal(size=(3, 3, 2, 4)).astype(np.float32)
@@ -91,11 +91,23 @@ def test_model_weights_from_a_reference_style_checkpoint(tmp_path):
     extra = {'G_omega/level_0/kernel': np.zeros((8, 4), np.float32), 'q_net/level_0/residual/conv_0/kernel/Adam': np.zeros(1, np.float32),
              'global_step': np.array(7, dtype=np.int64), 'p_net/xi': np.array(0.4, np.float32), 'beta': np.array(-0.7, np.float32)}
     prefix = ck.save_checkpoint(str(tmp_path / 'ckpt' / 'checkpoint.dat-7'), dict(params, **extra))
-    w, scalars = ck.model_weights_from_checkpoint(prefix, cfg)
+    with pytest.warns(UserWarning, match='get_log_Z/log_Z'):              # no log_Z in the file: said, not silently defaulted
+        w, scalars = ck.model_weights_from_checkpoint(prefix, cfg)
     assert [n for n, _ in weight_schema(cfg)] == list(w)
     for k in w:
         np.testing.assert_array_equal(w[k], params[k])
     assert scalars == {'xi_raw': pytest.approx(0.4), 'beta': pytest.approx(-0.7)}
+    # log_Z under the name the reference's graph gives it: spt.ScheduledVariable('log_Z') inside the @spt.global_reuse
+    # function get_log_Z (dmm_cifar10.py:458-463) -> 'get_log_Z/log_Z'; a bare 'log_Z' is the fallback
+    import warnings
+    for name in ('get_log_Z/log_Z', 'log_Z'):
+        p2 = ck.save_checkpoint(str(tmp_path / name.replace('/', '_') / 'c'), dict(params, **extra, **{name: np.array(2.5, np.float32)}))
+        with warnings.catch_warnings():
+            warnings.simplefilter('error')
+            _, sc = ck.model_weights_from_checkpoint(p2, cfg)
+        assert sc == {'xi_raw': pytest.approx(0.4), 'beta': pytest.approx(-0.7), 'log_Z': pytest.approx(2.5)}
+    both = dict(params, **extra, **{'get_log_Z/log_Z': np.array(2.5, np.float32), 'log_Z': np.array(9.0, np.float32)})
+    assert ck.model_weights_from_checkpoint(ck.save_checkpoint(str(tmp_path / 'both' / 'c'), both), cfg)[1]['log_Z'] == pytest.approx(2.5)
     bad = dict(params)
     bad['D_psi/level_-1/kernel'] = np.zeros((64, 2), np.float32)
     with pytest.raises(ck.CheckpointError):

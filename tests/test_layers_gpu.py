@@ -193,7 +193,7 @@ PATCH_GPU_CASES = [
 @pytest.mark.parametrize('cluster', [1, 2, 4])
 @pytest.mark.parametrize('macc', [1, 2, 4])
 @pytest.mark.parametrize('transpose,k,N,H,W,cin,cout', PATCH_GPU_CASES)
-def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster, monkeypatch):
+def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster):
     """A-stationary kernel (patchgemm.cu) for every accumulator count / cluster size it supports."""
     torch = _torch()
     import apvae
@@ -201,15 +201,15 @@ def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster, monkeypat
     Wt = 16 if W == 8 else W                   # 8-wide images: two side by side per tile row
     if macc * pad16(cout) > 256 or H % (macc * 128 // Wt) or (pad16(cout) // cluster) % 8:
         pytest.skip('combination not supported by the planner')
-    monkeypatch.setenv('APVAE_PATCH', '1')
-    monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
-    monkeypatch.setenv('APVAE_PATCH_CLUSTER', str(cluster))
+    tuning = dict(patch=1)
+    tuning['patch_macc'] = macc
+    tuning['patch_cluster'] = cluster
     rs = np.random.RandomState(k + cin + cout + N)
     x = exact16(rs.normal(size=(N, H, W, cin)))
     shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
     kern = exact16(rs.normal(size=shp) / np.sqrt(k * k * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, transpose=transpose, in_h=H, in_w=W, kernel=kern, bias=bias)], N, dtype=DT)
+    plan = Plan([dict(src=0, transpose=transpose, in_h=H, in_w=W, kernel=kern, bias=bias)], N, dtype=DT, tuning=tuning)
     if plan.info.patch != 1:
         pytest.skip('forced accumulator count does not fit the shared-memory rings')
     assert plan.info.patch_macc == macc and plan.info.patch_cluster == cluster
@@ -221,7 +221,7 @@ def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster, monkeypat
     _check(out.cpu().numpy(), want)
 
 
-def test_patch_kernel_matches_tap_kernel_bitwise_inputs(monkeypatch):
+def test_patch_kernel_matches_tap_kernel_bitwise_inputs():
     """Both kernels on the same op (fused 1x1 shortcut + residual-free epilogue, bf16 outputs)."""
     torch = _torch()
     from apvae.plan import Plan
@@ -235,8 +235,8 @@ def test_patch_kernel_matches_tap_kernel_bitwise_inputs(monkeypatch):
     t = lambda a: torch.tensor(a, device='cuda').to(_td())
     outs = {}
     for mode in ('0', '1'):
-        monkeypatch.setenv('APVAE_PATCH', mode)
-        plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n, dtype=DT)
+        tuning = dict(patch=(1 if int(mode) else -1))
+        plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n, dtype=DT, tuning=tuning)
         assert plan.info.patch == int(mode)
         o32 = torch.zeros((n, H, H, cout), dtype=torch.float32, device='cuda')
         oact = torch.zeros((n, H, H, cout), dtype=_td(), device='cuda')
@@ -275,22 +275,22 @@ TMA_EPI_CASES = [
 @pytest.mark.parametrize('two_cta', [0, 1])
 @pytest.mark.parametrize('macc', [0, 1])
 @pytest.mark.parametrize('H,W,cin,cout,res,n_valid,cap', TMA_EPI_CASES)
-def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two_cta, monkeypatch):
+def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two_cta):
     """bf16-only epilogue of the A-stationary kernel (bulk tensor loads of the residual, bulk tensor stores of
     out_raw / out_act): v = acc + bias (+ res on every / on even pixels); raw = bf16(v), act = bf16(lrelu(v));
     images >= n_valid stay untouched (a folded 8-wide op may also write the second image of its last pair)."""
     torch = _torch()
     from apvae import _lib
     from apvae.plan import Plan, pad16
-    monkeypatch.setenv('APVAE_PATCH', '1')
-    monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))     # cta_group::2 pairs: one 256-row MMA per two tiles
+    tuning = dict(patch=1)
+    tuning['patch_2cta'] = (1 if int(two_cta) else -1)     # cta_group::2 pairs: one 256-row MMA per two tiles
     if macc:
-        monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
+        tuning['patch_macc'] = macc
     rs = np.random.RandomState(H + cin + cout + len(res))
     x = exact16(rs.normal(size=(cap, H, W, cin)))
     kern = exact16(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT)
+    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT, tuning=tuning)
     assert plan.info.patch == 1
     npad = pad16(cout)
     t = lambda a: torch.tensor(a, device='cuda').to(_td())
@@ -318,6 +318,85 @@ def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two
     assert np.all(raw[keep:] == 7.0) and np.all(act[keep:] == 7.0)
 
 
+SPLIT_EPI_CASES = [
+    # transpose, k, stride, H, W (input), cin, cout, res, outs, n_valid, cap
+    (False, 3, 1, 16, 16, 64, 64, 'same', 'raw+act', 3, 4),     # arch B block output with identity shortcut
+    (False, 3, 1, 32, 32, 32, 32, 'none', 'act', 2, 3),         # conv_0 of a block
+    (True, 5, 1, 64, 64, 32, 32, 'same', 'raw', 1, 2),          # arch B celebA G_theta/level_9/conv_1
+    (True, 3, 1, 32, 32, 32, 32, 'even', 'raw+act', 2, 2),      # stride-2 block: half-resolution shortcut on even pixels
+    (False, 3, 1, 8, 8, 64, 48, 'same', 'raw+act', 3, 4),       # 8-wide images as pairs, 48 columns
+    (False, 3, 1, 8, 8, 64, 64, 'none', 'act', 4, 4),
+    (False, 3, 2, 32, 32, 32, 64, 'none', 'act', 2, 2),         # stride-2 conv through the space-to-depth maps
+    (True, 3, 2, 16, 16, 64, 32, 'none', 'act', 3, 4),          # stride-2 transposed conv: merged row-phase ops
+    (True, 5, 2, 32, 32, 32, 32, 'none', 'act', 2, 2),          # arch B celebA G_theta/level_9/conv_0
+    (True, 3, 2, 8, 8, 64, 64, 'none', 'act', 4, 4),            # 8-wide input grid, phases on image pairs
+]
+
+
+@pytest.mark.parametrize('nterms', [2, 3])
+@pytest.mark.parametrize('transpose,k,stride,H,W,cin,cout,res,outs,n_valid,cap', SPLIT_EPI_CASES)
+def test_split_precision_ops_on_the_patch_kernel(transpose, k, stride, H, W, cin, cout, res, outs, n_valid, cap, nterms):
+    """A split-precision op (apvae_config.precise): activations as hi + lo 16-bit pairs, kernels single (two terms,
+    precise = 2) or hi + lo as well (three terms, precise = 1), outputs and residual as hi + lo pairs — on the
+    A-stationary kernel with its split TMA epilogue (two store passes, hi then lo).  hi + lo of every output must
+    reproduce the float64 result to ~fp32 accuracy (2^-20 of the scale: 22 significant bits less accumulation noise)."""
+    torch = _torch()
+    from apvae import _lib
+    from apvae.plan import Plan, pad16
+    from helpers import op16_round
+    rs = np.random.RandomState(H + cin + cout + k + nterms)
+    a = rs.normal(size=(cap, H, W, cin)).astype(np.float32)
+    a_hi = op16_round(a, DT); a_lo = op16_round(a - a_hi, DT)
+    shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
+    w = (rs.normal(size=shp) / np.sqrt(k * k * cin)).astype(np.float32)
+    w_hi = op16_round(w, DT); w_lo = op16_round(w - w_hi, DT)
+    bias = rs.normal(size=(cout,)).astype(np.float32)
+    geo = dict(transpose=transpose, stride=stride, in_h=H, in_w=W)
+    terms = [dict(src=0, kernel=w_hi, bias=bias, **geo), dict(src=1, kernel=w_hi, **geo)]
+    if nterms == 3:
+        terms.append(dict(src=0, kernel=w_lo, **geo))
+    plan = Plan(terms, cap, dtype=DT, tuning=dict(patch=1))
+    Ho, Wo = plan.info.ho, plan.info.wo
+    npad = pad16(cout)
+    t = lambda x: torch.tensor(np.ascontiguousarray(x), device='cuda').to(_td())
+    ofn = O.deconv2d if transpose else O.conv2d
+    act64 = a_hi.astype(np.float64) + a_lo
+    want = ofn(act64, w_hi.astype(np.float64), bias.astype(np.float64), stride)
+    if nterms == 3:
+        want = want + ofn(a_hi.astype(np.float64), w_lo.astype(np.float64), None, stride)
+    kw = {}
+    if res != 'none':
+        rshape = (cap, Ho, Wo, npad) if res == 'same' else (cap, Ho // 2, Wo // 2, npad)
+        r = rs.normal(size=rshape).astype(np.float32)
+        r[..., cout:] = 0
+        r_hi = op16_round(r, DT); r_lo = op16_round(r - r_hi, DT)
+        r64 = r_hi.astype(np.float64) + r_lo
+        if res == 'same':
+            want = want + r64[..., :cout]
+        else:
+            want[:, ::2, ::2, :] += r64[..., :cout]
+        kw = dict(res=t(r_hi), res_lo=t(r_lo), res_mode=_lib.RES_SAME if res == 'same' else _lib.RES_EVEN)
+    bufs = {}
+    for name in ('raw', 'act'):
+        if name in outs:
+            bufs['out_' + name] = torch.full((cap, Ho, Wo, npad), 7.0, dtype=_td(), device='cuda')
+            bufs['out_' + name + '_lo'] = torch.full((cap, Ho, Wo, npad), 7.0, dtype=_td(), device='cuda')
+    plan.run([t(pad_channels(a_hi, pad16(cin))), t(pad_channels(a_lo, pad16(cin)))], n_valid, **bufs, **kw)
+    torch.cuda.synchronize()
+    scale = max(1.0, float(np.abs(want).max()))
+    for name, ref in (('raw', want), ('act', O.leaky_relu(want))):
+        if name not in outs:
+            continue
+        hi = bufs['out_' + name].float().cpu().numpy().astype(np.float64)
+        lo = bufs['out_' + name + '_lo'].float().cpu().numpy().astype(np.float64)
+        tol = (2.0 ** -20 if DT == 'fp16' else 2.0 ** -14) * scale
+        assert np.abs((hi + lo)[:n_valid, ..., :cout] - ref[:n_valid]).max() <= tol, (name, np.abs((hi + lo)[:n_valid, ..., :cout] - ref[:n_valid]).max(), tol)
+        assert np.abs(hi[:n_valid, ..., :cout] - ref[:n_valid]).max() <= 2.0 ** -7 * scale
+        assert np.all(hi[:n_valid, ..., cout:] == 0) and np.all(lo[:n_valid, ..., cout:] == 0)
+        keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 or W == 8 else 0)
+        assert np.all(hi[keep:] == 7.0) and np.all(lo[keep:] == 7.0)
+
+
 PHASE_CASES = [
     # k, H, W, cin, cout, n_valid, cap
     (3, 16, 16, 192, 96, 3, 4),        # arch A G_theta/level_8/conv_0
@@ -335,20 +414,20 @@ PHASE_CASES = [
 @pytest.mark.parametrize('merge', ['1', '0'])
 @pytest.mark.parametrize('outs', ['act', 'raw+act'])
 @pytest.mark.parametrize('k,H,W,cin,cout,n_valid,cap', PHASE_CASES)
-def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, outs, merge, monkeypatch):
+def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, outs, merge):
     """conv2d_transpose(stride 2, SAME) (conv2d_.py:464-471) as four sub-pixel phase ops of the A-stationary kernel:
     phase (py, px) is a stride-1 correlation on the input grid written to output pixels (2y + py, 2x + px) by strided
     bulk tensor stores.  merge=1: two ops, one per output row phase, whose N = [px 0 | px 1] x cout is the pair of
     adjacent output pixels (2x, 2x + 1) written as one contiguous row (when 2 * cout <= 256)."""
     torch = _torch()
     from apvae.plan import Plan, pad16
-    monkeypatch.setenv('APVAE_PATCH', '1')
-    monkeypatch.setenv('APVAE_PATCH_MERGE', merge)
+    tuning = dict(patch=1)
+    tuning['patch_merge'] = (1 if int(merge) else -1)
     rs = np.random.RandomState(k + H + cin + cout)
     x = exact16(rs.normal(size=(cap, H, W, cin)))
     kern = exact16(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT, tuning=tuning)
     npad = pad16(cout)
     t = lambda a: torch.tensor(a, device='cuda').to(_td())
     out_act = torch.full((cap, 2 * H, 2 * W, npad), 7.0, dtype=_td(), device='cuda')
@@ -380,14 +459,14 @@ S2_CASES = [
 
 @pytest.mark.parametrize('two_cta', [0, 1])
 @pytest.mark.parametrize('k,H,W,cin,cout,shortcut,n_valid,cap', S2_CASES)
-def test_stride2_conv_on_patch_kernel(k, H, W, cin, cout, shortcut, n_valid, cap, two_cta, monkeypatch):
+def test_stride2_conv_on_patch_kernel(k, H, W, cin, cout, shortcut, n_valid, cap, two_cta):
     """conv2d(stride 2, SAME) (conv2d_.py:204-211) on the A-stationary kernel through the space-to-depth view of the
     input (one tensor map per row phase), optionally with the block's 1x1 stride-2 shortcut as a second term
     (resnet.py:234-241); bf16 raw + act outputs through the TMA epilogue."""
     torch = _torch()
     from apvae.plan import Plan, pad16
-    monkeypatch.setenv('APVAE_PATCH', '1')
-    monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))
+    tuning = dict(patch=1)
+    tuning['patch_2cta'] = (1 if int(two_cta) else -1)
     rs = np.random.RandomState(k + H + cin + cout)
     t = lambda a: torch.tensor(a, device='cuda').to(_td())
     x = exact16(rs.normal(size=(cap, H, W, cin)))
@@ -403,7 +482,7 @@ def test_stride2_conv_on_patch_kernel(k, H, W, cin, cout, shortcut, n_valid, cap
         terms.append(dict(src=1, stride=2, in_h=H, in_w=W, kernel=ks, bias=bs))
         srcs.append(t(pad_channels(x2, pad16(cin))))
         want = want + O.conv2d(x2.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
-    plan = Plan(terms, cap, dtype=DT)
+    plan = Plan(terms, cap, dtype=DT, tuning=tuning)
     assert plan.info.patch == 1 and plan.info.patch_s2d == 1
     npad = pad16(cout)
     out_raw = torch.full((cap, H // 2, W // 2, npad), 7.0, dtype=_td(), device='cuda')
@@ -437,20 +516,20 @@ MASK_CASES = [
 
 @pytest.mark.parametrize('two_cta', [0, 1])
 @pytest.mark.parametrize('H,W,cin,cout,res,n_valid,cap', MASK_CASES)
-def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_cta, monkeypatch):
+def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_cta):
     """Adjoint ops (model_grad.cu): v = (acc + bias) * leaky_relu'(mask) (+ res), raw bf16 output only, through the TMA
     epilogue of the A-stationary kernel: the mask (the forward activation, dmm_cifar10.py:241-247 via tf.gradients of
     tf.nn.leaky_relu) is fetched one block ahead into the unused act staging box."""
     torch = _torch()
     from apvae import _lib
     from apvae.plan import Plan, pad16
-    monkeypatch.setenv('APVAE_PATCH', '1')
-    monkeypatch.setenv('APVAE_PATCH_2CTA', str(two_cta))
+    tuning = dict(patch=1)
+    tuning['patch_2cta'] = (1 if int(two_cta) else -1)
     rs = np.random.RandomState(H + cin + cout + len(res))
     x = exact16(rs.normal(size=(cap, H, W, cin)))
     kern = exact16(rs.normal(size=(3, 3, cin, cout)) / np.sqrt(9 * cin))
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT)
+    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT, tuning=tuning)
     assert plan.info.patch == 1
     npad = pad16(cout)
     t = lambda a: torch.tensor(a, device='cuda').to(_td())
@@ -475,8 +554,8 @@ def test_patch_kernel_tma_epilogue_mask(H, W, cin, cout, res, n_valid, cap, two_
     assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
     keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 else 0)
     assert np.all(raw[keep:] == 7.0)
-    # same op through the generic epilogue (APVAE_FAST_MASK=0): same values up to the bf16 rounding of the output
-    monkeypatch.setenv('APVAE_FAST_MASK', '0')
+    # same op through the generic epilogue (tuning.fast_mask = -1): same values up to the 16-bit rounding of the output
+    plan = Plan([dict(src=0, in_h=H, in_w=W, kernel=kern, bias=bias)], cap, dtype=DT, tuning=dict(tuning, fast_mask=-1))
     out2 = torch.full((cap, H, W, npad), 7.0, dtype=_td(), device='cuda')
     plan.run([t(pad_channels(x, pad16(cin)))], n_valid, out_raw=out2, mask=t(mask), **kw)
     torch.cuda.synchronize()
@@ -493,17 +572,17 @@ PHASE_MASK_CASES = [
 
 
 @pytest.mark.parametrize('k,H,W,cin,cout,n_valid,cap', PHASE_MASK_CASES)
-def test_stride2_deconv_phases_with_mask(k, H, W, cin, cout, n_valid, cap, monkeypatch):
+def test_stride2_deconv_phases_with_mask(k, H, W, cin, cout, n_valid, cap):
     """The adjoint of a stride-2 conv (model_grad.cu: conv_1^T of a D_psi block) = conv2d_transpose(stride 2) whose
     epilogue multiplies by leaky_relu'(forward activation): sub-pixel phase ops whose mask is the same strided view as
     their output, fetched by 4-D bulk tensor loads."""
     torch = _torch()
     from apvae.plan import Plan, pad16
-    monkeypatch.setenv('APVAE_PATCH', '1')
+    tuning = dict(patch=1)
     rs = np.random.RandomState(k + H + cin + cout)
     x = exact16(rs.normal(size=(cap, H, W, cin)))
     kern = exact16(rs.normal(size=(k, k, cout, cin)) / np.sqrt(k * k * cin / 4.0))
-    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=None)], cap, dtype=DT)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=None)], cap, dtype=DT, tuning=tuning)
     npad = pad16(cout)
     t = lambda a: torch.tensor(a, device='cuda').to(_td())
     mask = exact16(rs.normal(size=(cap, 2 * H, 2 * W, npad)))

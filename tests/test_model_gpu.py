@@ -367,6 +367,71 @@ def test_precise_mala_at_the_reference_energy_weight(case):
     m.close()
 
 
+@pytest.mark.parametrize('case', ['A128', 'Bceleba'])
+def test_activation_split_mala_at_the_reference_energy_weight(case):
+    """ExpConfig.precise = 2: activations as hi + lo 16-bit pairs, kernels single (A_hi W + A_lo W, two tensor-core terms
+    instead of three).  What is left is the kernels' own 16-bit rounding, i.e. the library computes the energy of the
+    model whose conv / dense kernels are the fp16-rounded ones — so against the float64 oracle ON THOSE KERNELS the
+    energies are fp32-class (1e-4), and MALA at pull_back_energy_weight = 1000 takes the same accept / reject decisions
+    and lands on the same samples.  Against the full-precision oracle the energies differ by the (smooth) perturbation,
+    which cancels in E(z) - E(z'): the acceptance ratios still agree."""
+    from helpers import fp16_round
+    arch, kw, _ = GRAD_CASES[case]
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=4, enable_grad=True, precise=2)
+    # the heads run on the CUDA cores with fp32 weights (heads.cu); every other kernel is a 16-bit tensor-core operand
+    # so does D_psi's last 64 -> 1 dense (rowdot)
+    heads = ('G_theta/x_mean/kernel', 'G_theta/x_logstd/kernel', 'G_theta/feature_map_mean_to_pixel/kernel', 'D_psi/level_-1/kernel')
+    params_r = {k: (fp16_round(v).astype(np.float64) if k.endswith('/kernel') and k not in heads else v) for k, v in params.items()}
+    n, steps, alpha, xi_raw = 6, 3, ocfg.smallest_step, 0.0
+    rs = np.random.RandomState(5)
+    z0 = rs.normal(size=(n, 1, ocfg.z_dim))
+    dg = m.energy_of_latents(z0[:, 0]).cpu().numpy()
+    dg_r = O.D_psi(ocfg, params_r, O.G_theta(ocfg, params_r, z0[:, 0]))
+    assert np.abs(dg - dg_r).max() < PRECISE_ATOL, np.abs(dg - dg_r).max()
+    assert np.abs(dg - O.D_psi(ocfg, params, O.G_theta(ocfg, params, z0[:, 0]))).max() < ENERGY_ATOL
+    eps = rs.normal(size=(steps, n, 1, ocfg.z_dim))
+    u = np.zeros((steps, n, 1))
+    z, zf = z0, z0
+    he, hp, hr, hr_full = [], [], [], []
+    for i in range(steps):
+        _, _, _, ratio = O.mala_step(ocfg, params_r, z, eps[i], np.zeros((n, 1)), alpha, xi_raw)
+        want_accept = ((np.arange(n) + i) % 3 != 0)[:, None] | (ratio > 0.8)
+        u[i] = np.where(want_accept, ratio * 0.5, np.minimum(ratio + 0.5 * (1 - ratio), 0.999))
+        _, _, _, rf = O.mala_step(ocfg, params, z, eps[i], u[i], alpha, xi_raw)       # full-precision kernels, same state
+        hr_full.append(rf)
+        z, e_z, pure, ratio = O.mala_step(ocfg, params_r, z, eps[i], u[i], alpha, xi_raw)
+        he.append(e_z), hp.append(pure), hr.append(ratio)
+    out = m.mala(z0, steps, alpha=alpha, eps=eps, u=u)
+    got_z = out['z'].cpu().numpy().reshape(z.shape)
+    assert np.abs(got_z - z).max() < 1e-3, np.abs(got_z - z).max()
+    gp = out['history_pure_e_z'].cpu().numpy().reshape(steps, n)
+    ge = out['history_e_z'].cpu().numpy().reshape(steps, n)
+    gr = out['history_ratio'].cpu().numpy().reshape(steps, n)
+    assert np.abs(gp - np.stack(hp).reshape(steps, n)).max() < PRECISE_ATOL
+    assert np.abs(ge - np.stack(he).reshape(steps, n)).max() < 500 * PRECISE_ATOL + 1e-5 * np.abs(np.stack(he)).max()
+    assert np.abs(gr - np.stack(hr).reshape(steps, n)).max() < 0.25, (gr, np.stack(hr).reshape(steps, n))
+    # the kernels' rounding cancels in the energy difference: ratios of the rounded-kernel and full-precision models agree
+    assert np.abs(np.stack(hr).reshape(steps, n) - np.stack(hr_full).reshape(steps, n)).max() < 0.25
+    m.close()
+
+
+def test_single_pass_sampler_at_the_reference_weight_warns():
+    """At pull_back_energy_weight = 1000 a single-pass 16-bit forward puts ~1 nat of rounding noise into MALA's acceptance
+    exponent: Model.mala says so (RuntimeWarning) unless the model was built with a split-precision forward."""
+    import warnings
+    arch, kw, _ = GRAD_CASES['Bcifar']
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=4, enable_grad=True)
+    z0 = np.random.RandomState(1).normal(size=(3, ocfg.z_dim))
+    with pytest.warns(RuntimeWarning, match='precise'):
+        m.mala(z0, 1, seed=1)
+    m.close()
+    ocfg, params, cfg, m = _make(arch, kw, max_chunk=4, enable_grad=True, precise=2)
+    with warnings.catch_warnings():
+        warnings.simplefilter('error')
+        m.mala(z0, 1, seed=1)
+    m.close()
+
+
 # ----------------------------------------------------------------------------- the scripts' call surface
 def test_script_call_surface_reads_like_the_reference():
     """apvae.dmm.Script: the test section of dmm_cifar10.py (:880-927) written with the reference's own names

@@ -1,6 +1,8 @@
 """Host planner vs the oracle: the step table + TMA view geometry + packed
 weights must reproduce conv2d / deconv2d / dense for every (k, stride) the
 scripts use.  Runs without a GPU (planning is host-only)."""
+import os
+
 import numpy as np
 import pytest
 
@@ -107,19 +109,19 @@ PATCH_CASES = [
 
 @pytest.mark.parametrize('transpose,k,H,W,cin,cout', PATCH_CASES)
 @pytest.mark.parametrize('macc', [0, 1])
-def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc, monkeypatch):
+def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc):
     """The A-stationary plan (patchgemm.h): groups, packed weights and patch geometry reproduce
     conv2d / deconv2d (stride 1)."""
     from helpers import emulate_patch_plan
-    monkeypatch.setenv('APVAE_PATCH', '1')
-    monkeypatch.setenv('APVAE_PATCH_MACC', str(macc))
+    tuning = dict(patch=1)
+    tuning['patch_macc'] = macc
     rs = np.random.RandomState(k * 100 + cin + cout)
     n = 2
     x = exact16(rs.normal(size=(n, H, W, cin)))
     shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
     kern = exact16(rs.normal(size=shp) * 0.2)
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, transpose=transpose, stride=1, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
+    plan = Plan([dict(src=0, transpose=transpose, stride=1, in_h=H, in_w=W, kernel=kern, bias=bias)], n, tuning=tuning)
     assert plan.info.patch == 1
     assert plan.info.patch_macc * plan.info.npad <= 256
     assert plan.info.patch_fold == (2 if W == 8 else 1)
@@ -140,11 +142,11 @@ S2_PATCH_CASES = [
 
 
 @pytest.mark.parametrize('k,H,W,cin,cout,shortcut', S2_PATCH_CASES)
-def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut, monkeypatch):
+def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut):
     """Stride-2 conv2d on the A-stationary kernel: the input is read through its space-to-depth view, one tensor map
     per row phase, column phase folded into the channel coordinate; vertical taps of one row phase share a patch."""
     from helpers import emulate_patch_plan
-    monkeypatch.setenv('APVAE_PATCH', '1')
+    tuning = dict(patch=1)
     rs = np.random.RandomState(k * 100 + cin + cout)
     n = 2
     x = exact16(rs.normal(size=(n, H, W, cin)))
@@ -160,7 +162,7 @@ def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut, mo
         terms.append(dict(src=1, stride=2, in_h=H, in_w=W, kernel=ks, bias=bs))
         srcs.append(pad_channels(x2, pad16(cin)))
         want = want + O.conv2d(x2.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
-    plan = Plan(terms, n)
+    plan = Plan(terms, n, tuning=tuning)
     assert plan.info.patch == 1 and plan.info.patch_s2d == 1
     assert plan.info.patch_fold == (2 if W == 16 else 1)
     assert plan.info.patch_nmaps == (1 if k == 1 else 2) + (1 if shortcut else 0)
@@ -180,17 +182,17 @@ PHASE_PLAN_CASES = [
 
 
 @pytest.mark.parametrize('k,H,W,cin,cout', PHASE_PLAN_CASES)
-def test_stride2_deconv_phase_plans_match_oracle(k, H, W, cin, cout, monkeypatch):
+def test_stride2_deconv_phase_plans_match_oracle(k, H, W, cin, cout):
     """conv2d_transpose(stride 2, SAME) (conv2d_.py:464-471) assembled from its sub-pixel phase plans: four plans (py, px),
     or two row-phase plans whose N is [px 0 | px 1] x cout — each emulated exactly as the kernel walks it."""
     from helpers import emulate_patch_plan
-    monkeypatch.setenv('APVAE_PATCH', '1')
+    tuning = dict(patch=1)
     rs = np.random.RandomState(k * 100 + cin + cout)
     n = 2
     x = exact16(rs.normal(size=(n, H, W, cin)))
     kern = exact16(rs.normal(size=(k, k, cout, cin)) * 0.2)
     bias = rs.normal(size=(cout,)).astype(np.float32)
-    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], n)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=W, kernel=kern, bias=bias)], n, tuning=tuning)
     want = O.deconv2d(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 2)
     src = [pad_channels(x, pad16(cin))]
     got = np.zeros_like(want)
@@ -212,9 +214,9 @@ def test_stride2_deconv_phase_plans_match_oracle(k, H, W, cin, cout, monkeypatch
             plan.select_patch(4)
 
 
-def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
+def test_patch_plan_fused_shortcut_and_eligibility():
     from helpers import emulate_patch_plan
-    monkeypatch.setenv('APVAE_PATCH', '1')
+    tuning = dict(patch=1)
     rs = np.random.RandomState(11)
     n, H, cin, cout = 2, 16, 32, 64
     r = exact16(rs.normal(size=(n, H, H, cin)))
@@ -222,7 +224,7 @@ def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     k1 = exact16(rs.normal(size=(3, 3, cin, cout)) * 0.1)
     ks = exact16(rs.normal(size=(1, 1, cin, cout)) * 0.1)
     b1, bs = rs.normal(size=cout).astype(np.float32), rs.normal(size=cout).astype(np.float32)
-    plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n)
+    plan = Plan([dict(src=0, in_h=H, in_w=H, kernel=k1, bias=b1), dict(src=1, in_h=H, in_w=H, kernel=ks, bias=bs)], n, tuning=tuning)
     assert plan.info.patch == 1 and plan.info.patch_prow[1] == plan.info.patch_rows_tile
     got = emulate_patch_plan(plan, [r, x], n)[..., :cout]
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
@@ -231,8 +233,66 @@ def test_patch_plan_fused_shortcut_and_eligibility(monkeypatch):
     # not eligible: stride 2 onto a 4x4 grid, 8x8 grids with an odd capacity (they run as image pairs), arch-M widths
     assert Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), in_h=8, in_w=8)], 4).info.patch_fold == 2
     for kw in (dict(stride=2, in_h=8, in_w=8), dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=28, in_w=28)):
-        p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1)
+        p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1, tuning=tuning)
         assert p.info.patch == 0
-    monkeypatch.setenv('APVAE_PATCH', '0')
-    p = Plan([dict(src=0, in_h=16, in_w=16, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1)
+    tuning['patch'] = -1
+    p = Plan([dict(src=0, in_h=16, in_w=16, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1, tuning=tuning)
     assert p.info.patch == 0
+
+
+def test_patch_plan_takes_the_products_of_a_split_precision_op():
+    """A split-precision op is two or three terms over TWO sources (hi and lo activations): A_hi W_hi + A_lo W_hi
+    [+ A_hi W_lo] (model.cu push_terms).  The A-stationary plan gives every term its own activation map (up to four),
+    also for the sub-pixel phases of a stride-2 transposed conv."""
+    from helpers import emulate_patch_plan, fp16_round
+    tuning = dict(patch=1)
+    rs = np.random.RandomState(17)
+    n, H, cin, cout = 2, 16, 32, 48
+    a = rs.normal(size=(n, H, H, cin)).astype(np.float32)
+    a_hi = fp16_round(a)
+    a_lo = fp16_round(a - a_hi)
+    w = (rs.normal(size=(3, 3, cin, cout)) * 0.1).astype(np.float32)
+    w_hi = fp16_round(w)
+    w_lo = fp16_round(w - w_hi)
+    b = rs.normal(size=cout).astype(np.float32)
+    for nterms in (2, 3):
+        terms = [dict(src=0, in_h=H, in_w=H, kernel=w_hi, bias=b), dict(src=1, in_h=H, in_w=H, kernel=w_hi)]
+        if nterms == 3:
+            terms.append(dict(src=0, in_h=H, in_w=H, kernel=w_lo))
+        plan = Plan(terms, n, tuning=tuning)
+        assert plan.info.patch == 1 and plan.info.patch_nmaps == nterms and plan.info.nsrc == 2
+        assert list(plan.info.patch_map_src)[:nterms] == [0, 1, 0][:nterms]
+        got = emulate_patch_plan(plan, [a_hi, a_lo], n)[..., :cout]
+        act = (a_hi.astype(np.float64) + a_lo)
+        want = O.conv2d(act, w_hi.astype(np.float64), b.astype(np.float64), 1)
+        if nterms == 3:
+            want = want + O.conv2d(a_hi.astype(np.float64), w_lo.astype(np.float64), None, 1)
+        np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+    # stride-2 transposed conv: the phase plans take both products as well
+    wt = (rs.normal(size=(3, 3, cout, cin)) * 0.1).astype(np.float32)
+    wt_hi = fp16_round(wt)
+    plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=H, kernel=wt_hi, bias=b),
+                 dict(src=1, transpose=True, stride=2, in_h=H, in_w=H, kernel=wt_hi)], n, tuning=tuning)
+    want = O.deconv2d(a_hi.astype(np.float64) + a_lo, wt_hi.astype(np.float64), b.astype(np.float64), 2)
+    got = np.zeros_like(want)
+    for ph in range(4):
+        plan.select_patch(ph)
+        assert plan.info.patch_nmaps == 2
+        got += emulate_patch_plan(plan, [a_hi, a_lo], n)[..., :cout]
+    np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
+
+
+def test_python_tuning_struct_matches_the_header():
+    """apvae/_lib.py's Tuning fields, in order, are the int fields of `struct apvae_tuning` in include/apvae.h."""
+    import re
+    from apvae import _lib
+    text = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), 'include', 'apvae.h')).read()
+    body = re.search(r'typedef struct apvae_tuning \{(.*?)\} apvae_tuning;', text, re.S).group(1)
+    body = re.sub(r'/\*.*?\*/', '', body, flags=re.S)
+    fields = []
+    for decl in re.findall(r'int\s+([^;]+);', body):
+        fields += [f.strip() for f in decl.split(',')]
+    assert tuple(fields) == tuple(_lib.TUNING_FIELDS)
+    assert _lib.Tuning.make(dict(patch=-1, patch_split=1)).patch == -1
+    with pytest.raises(AttributeError):
+        _lib.Tuning.make(dict(no_such_knob=1))

@@ -1,7 +1,7 @@
 """Times ONE conv / deconv layer on the GPU through the C ABI (apvae_plan_bench): kernel tuning and
 ncu profiling of a single op in isolation.
   python tools/bench_layer.py [--transpose] --k 3 --stride 1 --h 16 --w 16 --cin 192 --cout 192 --n 256
-Environment: APVAE_PATCH=0/1, APVAE_PATCH_MACC, APVAE_PATCH_CLUSTER select the kernel variant."""
+--tuning patch=-1,patch_macc=2,... (apvae_tuning fields; the old APVAE_* variable names are still read, by the TOOLS only) selects the kernel variant."""
 import argparse
 import os
 import sys
@@ -13,6 +13,8 @@ sys.path.insert(0, os.path.join(ROOT, 'adversarial-prior-vae_b200'))
 import torch  # noqa: E402
 
 from apvae.plan import Plan, pad16  # noqa: E402
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+import _tuning  # noqa: E402
 
 
 def main(argv=None):
@@ -28,12 +30,13 @@ def main(argv=None):
     ap.add_argument('--reps', type=int, default=10)
     ap.add_argument('--outs', default='raw,act', help='comma list of raw, act, f32')
     ap.add_argument('--res', default='none', help='none | same | even (residual added in the epilogue)')
+    ap.add_argument('--tuning', default='', help='apvae_tuning overrides, e.g. patch_2cta=-1,patch_macc=2')
     a = ap.parse_args(argv)
     rs = np.random.RandomState(0)
     shp = (a.k, a.k, a.cout, a.cin) if a.transpose else (a.k, a.k, a.cin, a.cout)
     kern = (rs.normal(size=shp) / np.sqrt(a.k * a.k * a.cin)).astype(np.float32)
     plan = Plan([dict(src=0, transpose=a.transpose, stride=a.stride, in_h=a.h, in_w=a.w, kernel=kern,
-                      bias=np.zeros(a.cout, np.float32))], a.n)
+                      bias=np.zeros(a.cout, np.float32))], a.n, dtype='bf16', tuning=_tuning.parse(a.tuning))
     i = plan.info
     src = torch.randn((a.n, a.h, a.w, pad16(a.cin)), device='cuda').to(torch.bfloat16)
     kw = {}

@@ -26,7 +26,9 @@ def main():
     ap.add_argument('--chains', type=int, default=1024)
     ap.add_argument('--steps', type=int, default=100)
     ap.add_argument('--chunk', type=int, default=1024)
-    ap.add_argument('--precise', action='store_true')
+    ap.add_argument('--precise', type=int, nargs='?', const=1, default=0,
+                    help='split-precision forward: 1 = activations and kernels hi + lo (3 terms), 2 = activations only (2 terms)')
+    ap.add_argument('--operand-dtype', default='fp16', choices=('fp16', 'bf16'))
     ap.add_argument('--op-times', action='store_true', help='also print per-op timings of the forward and adjoint programs')
     a = ap.parse_args()
     rank, world, local = (int(os.environ.get(k, d)) for k, d in (('RANK', '0'), ('WORLD_SIZE', '1'), ('LOCAL_RANK', '0')))
@@ -36,7 +38,7 @@ def main():
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=torch.device('cuda', local))
     cfg = ExpConfig(a.arch, dataset=a.dataset if a.arch == 'B' else None, z_dim=a.z_dim, max_batch=8, max_chunk=a.chunk,
-                    enable_grad=True, precise=a.precise)
+                    enable_grad=True, precise=a.precise, operand_dtype=a.operand_dtype)
     m = Model(cfg, synthetic_weights(weight_schema(cfg)), device=local)
     z0 = torch.from_numpy(np.random.RandomState(2 + rank).normal(size=(a.chains, cfg.z_dim)).astype(np.float32)).cuda()
     m.mala(z0, 2, seed=1, history=False)                      # warm-up
@@ -76,9 +78,9 @@ def main():
     print(json.dumps({
         'metric': 'MALA chain-steps/sec (%s %s, d=%d, %d chains x %d steps)' % (a.arch, a.dataset, cfg.z_dim, a.chains, a.steps),
         'value': world * a.chains * a.steps / (ms / 1e3), 'unit': 'chain-steps/s', 'n_gpus': world, 'ms_total': ms,
-        'algorithmic_tflops': flops / (ms / 1e3) / 1e12, 'precise': bool(a.precise),
+        'algorithmic_tflops': flops / (ms / 1e3) / 1e12, 'precise': int(a.precise),
         'mean_accept_ratio': float(out['history_ratio'].mean()), 'frac_ratio_gt_half': acc,
-        'images': list(img.shape), 'dtype': 'bf16x3 (split precision)' if a.precise else 'bf16'}))
+        'images': list(img.shape), 'dtype': a.operand_dtype + ('' if not a.precise else ' x3 (split precision)' if a.precise == 1 else ' x2 (activation split)')}))
 
 
 if __name__ == '__main__':
