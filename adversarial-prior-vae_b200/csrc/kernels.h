@@ -192,6 +192,10 @@ struct TinyConvParams {
     const void* mask;  int ld_mask;                                      // bf16 [N, H, W, ld_mask]
     float alpha;
     int f16;                                                             // operand format (op16.h)
+    // split precision (apvae_config.precise): the input and the residual are hi + lo pairs (summed in fp32 on load), every
+    // 16-bit output leaves as a pair (v_hi = round16(v), v_lo = round16(v - v_hi)); null = a plain op.  The weights are fp32
+    // here anyway (the sum of the hi and lo kernels when both exist).
+    const void* in_lo;  const void* res_lo;  void* out_raw_lo;  void* out_act_lo;
 };
 int launch_tiny_conv(const TinyConvParams& p, int n, void* stream);
 

