@@ -441,6 +441,34 @@ __global__ void tanh_backward_pack_kernel(const float* __restrict__ g, const flo
     }
 }
 
+// one thread per (pixel, 8 output channels): 16-byte stores, the pixel's three gradients re-read through L1
+template <bool F16>
+__global__ void tanh_backward_head_kernel(const __grid_constant__ HeadGradParams p) {
+    const int groups = p.cp_out >> 3;
+    const long long total = p.pixels * groups;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const long long px = i / groups;
+        const int c0 = (int)(i - px * groups) * 8;
+        float gp[kHeadGradMaxC] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < kHeadGradMaxC; ++c)
+            if (c < p.C) { const float t = p.head[px * p.ld + c]; gp[c] = p.g[px * p.C + c] * (1.f - t * t); }
+        float v[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int co = c0 + j;
+            float a = 0.f;
+            if (co < p.cg) {
+                const float* w = p.w + co * kHeadGradMaxC;
+                a = gp[0] * w[0] + gp[1] * w[1] + gp[2] * w[2] + gp[3] * w[3];
+            }
+            v[j] = a;
+        }
+        uint4* d = reinterpret_cast<uint4*>(static_cast<uint16_t*>(p.out) + px * p.cp_out + c0);
+        *d = make_uint4(op16::pack<F16>(v[0], v[1]), op16::pack<F16>(v[2], v[3]), op16::pack<F16>(v[4], v[5]), op16::pack<F16>(v[6], v[7]));
+    }
+}
+
 // one block per row
 __global__ void row_sqnorm_kernel(const float* __restrict__ v, long long len, float* __restrict__ out) {
     const float* p = v + (size_t)blockIdx.x * len;
@@ -684,6 +712,15 @@ int launch_tanh_backward_pack(const float* g, const float* head, int ld, long lo
     if (pixels <= 0) return 0;
     tanh_backward_pack_kernel<<<grid_for(pixels * cp, 256), 256, 0, st(stream)>>>(g, head, ld, pixels, C, cp,
                                                                                (uint16_t*)out_bf16, f16);
+    return (int)cudaGetLastError();
+}
+int launch_tanh_backward_head(const HeadGradParams& p, void* stream) {
+    if (p.pixels <= 0) return 0;
+    if (p.C < 1 || p.C > kHeadGradMaxC || p.cg < 1 || p.cg > kHeadGradMaxCg || p.cp_out % 8 || p.cp_out < p.cg || !p.g || !p.head || !p.out)
+        return (int)cudaErrorInvalidValue;
+    const long long total = p.pixels * (p.cp_out >> 3);
+    if (p.f16) tanh_backward_head_kernel<true><<<grid_for(total, 256), 256, 0, st(stream)>>>(p);
+    else tanh_backward_head_kernel<false><<<grid_for(total, 256), 256, 0, st(stream)>>>(p);
     return (int)cudaGetLastError();
 }
 int launch_row_sqnorm(const float* v, long long len, int rows, float* out, void* stream) {

@@ -104,6 +104,20 @@ int launch_energy_combine(const float* d_g, const float* gz, const float* z, int
 int launch_tanh_backward_pack(const float* g, const float* head, int ld, long long pixels, int C, int cp,
                               void* out_bf16, int f16, void* stream);
 
+// The same backward step fused with the adjoint of the 1x1 mean head (x_mean = tanh(conv 1x1(h)), dmm_cifar10.py:489-492):
+//   g_h[p, co] = sum_c g[p, c] (1 - head[p*ld + c]^2) W[co][c],   co < cg, as a 16-bit row of cp_out channels (padding zero).
+// C <= 4 image channels, cg <= kHeadGradMaxCg trunk channels: a K = C "GEMM" that is pure HBM streaming (12 B in per pixel,
+// cp_out * 2 B out), so it runs on the CUDA cores with the weights in the parameter block.
+constexpr int kHeadGradMaxCg = 128, kHeadGradMaxC = 4;
+struct HeadGradParams {
+    const float* g;  const float* head;  int ld;      // fp32 [pixels, C] and [pixels, ld]
+    long long pixels;
+    int C, cg, cp_out, f16;
+    void* out;                                         // 16-bit [pixels, cp_out]
+    float w[kHeadGradMaxCg * kHeadGradMaxC];           // [cg][4]: the head kernel [1,1,cg,C] transposed, zero padded
+};
+int launch_tanh_backward_head(const HeadGradParams& p, void* stream);
+
 // out[r] = sum_j v[r, j]^2 over `len` contiguous floats per row (ele_grad_norm, evaluation/dmm_cifar.py:958-959)
 int launch_row_sqnorm(const float* v, long long len, int rows, float* out, void* stream);
 
@@ -156,14 +170,20 @@ int launch_sum_tiles(const float* part, int tpi, int n, float* log_px, float* sq
 // to 16 per tap and sit on the tensor pipe's per-instruction floor (3 and 18 TFLOP/s measured); here one CTA takes one
 // image through shared memory:  r = lrelu(conv_k(lrelu(x)) + b0);  out = conv_k(r) + b1 + x W_s + b_s.
 // r is rounded to bf16 (it is stored for the backward pass and that is what the unfused ops fed to conv_1).
-constexpr int kSmallBlockMaxCin = 3, kSmallBlockMaxCout = 16, kSmallBlockMaxK = 3, kSmallBlockMaxHW = 32;
+// Two kernels: the CIFAR models' block (cout = 16, stride 1, <= 32 x 32: static shared memory, several CTAs per SM) and
+// a wider one (cout = 16 or 32, stride 1 or 2 at the block's exit like resnet.py's resize_at_exit, <= 64 x 64, dynamic shared
+// memory: arch B's D_psi/level_0 on CIFAR and CelebA shapes), which also takes split-precision tensors (hi + lo pairs).
+constexpr int kSmallBlockMaxCin = 3, kSmallBlockMaxCout = 32, kSmallBlockMaxK = 3, kSmallBlockMaxHW = 32, kSmallBlockWideMaxHW = 64;
 struct SmallBlockParams {
     const void* in_raw;                   // bf16 [N, H, W, cp_in]
     void* r_act;                          // bf16 [N, H, W, cp_in]: lrelu(conv_0 + b0), padding channels zero
     void* out_raw;  void* out_act;        // bf16 [N, H, W, ldo]: padding channels zero (either may be null)
     int H, W, cp_in, cin, cout, ldo, k;
+    int stride;                           // of conv_1 and the shortcut (1 or 2); outputs are [N, ceil(H/stride), ceil(W/stride), ldo]
     float alpha;
     int f16;                              // operand format (op16.h)
+    // split precision (wide kernel only): low halves of the input and of every 16-bit output; null = a plain block
+    const void* in_raw_lo;  void* r_act_lo;  void* out_raw_lo;  void* out_act_lo;
     float b0[kSmallBlockMaxCin];
     float b1[kSmallBlockMaxCout];         // conv_1 bias + shortcut bias
     float w0[kSmallBlockMaxK * kSmallBlockMaxK * kSmallBlockMaxCin * kSmallBlockMaxCin];      // [k][k][cin][cin]

@@ -245,36 +245,44 @@ bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& 
     Tensor r = alloc_act(cap, H, Wd, cin), r_lo;
     if (!r.ptr) return false;
     if (sp) { r_lo = alloc_act(cap, H, Wd, cin); if (!r_lo.ptr) return false; }
-    // <= 3 input channels (D_psi/level_0 of the CIFAR models: 3 -> 3 -> 16 at 32 x 32): the whole block is one HBM-bound
-    // CUDA-core kernel (block0.cu) with fp32 weights; tuning.small_block = -1 keeps the two tensor-core ops (tuning / A-B only)
-    if (!sp && switch_on(tuning().small_block, true) && s == 1 && k == kSmallBlockMaxK && cin <= kSmallBlockMaxCin && cout == kSmallBlockMaxCout &&
-        use_sc && H <= kSmallBlockMaxHW && Wd <= kSmallBlockMaxHW) {
+    // <= 3 input channels (D_psi/level_0: 3 -> 3 -> 16 at 32 x 32 in the CIFAR models, 3 -> 3 -> 32 with a stride-1 / stride-2
+    // exit at 32 x 32 / 64 x 64 in arch B): the whole block is one HBM-bound CUDA-core kernel (block0.cu) with fp32 weights,
+    // also for split-precision tensors; tuning.small_block = -1 keeps the tensor-core ops (tuning / A-B only)
+    if (switch_on(tuning().small_block, true) && (s == 1 || s == 2) && k == kSmallBlockMaxK && cin <= kSmallBlockMaxCin &&
+        (cout == 16 || cout == 32) && use_sc && H <= kSmallBlockWideMaxHW && Wd <= kSmallBlockWideMaxHW && !(H % s) && !(Wd % s)) {
         const HostArr *ks = W_(pre + "shortcut/kernel", {1, 1, cin, cout}), *bs = W_(pre + "shortcut/bias", {cout});
         if (!ks || !bs) return false;
+        const int Ho = H / s, Wo = Wd / s;
         Pair o;
-        if (need_raw) { o.raw = alloc_act(cap, H, Wd, cout); if (!o.raw.ptr) return false; }
-        if (need_act) { o.act = alloc_act(cap, H, Wd, cout); if (!o.act.ptr) return false; }
+        if (need_raw) { o.raw = alloc_act(cap, Ho, Wo, cout); if (!o.raw.ptr) return false; }
+        if (need_act) { o.act = alloc_act(cap, Ho, Wo, cout); if (!o.act.ptr) return false; }
+        if (sp && need_raw) { o.raw_lo = alloc_act(cap, Ho, Wo, cout); if (!o.raw_lo.ptr) return false; }
+        if (sp && need_act) { o.act_lo = alloc_act(cap, Ho, Wo, cout); if (!o.act_lo.ptr) return false; }
+        if (sp && !in.raw_lo.ptr) return fail("split-precision block " + pre + " has no low-half input");
         std::unique_ptr<DevOp> op(new DevOp());
         op->name = pre + "block";
         op->is_small_block = true;
         op->capacity_n = cap;
-        op->macs_per_image = ((double)k * k * cin * cin + (double)k * k * cin * cout + (double)cin * cout) * H * Wd;
+        op->macs_per_image = (double)k * k * cin * cin * H * Wd + ((double)k * k * cin * cout + (double)cin * cout) * Ho * Wo;
         SmallBlockParams& sb = op->sblock;
         memset(&sb, 0, sizeof(sb));
         sb.in_raw = in.raw.ptr; sb.r_act = r.ptr; sb.out_raw = o.raw.ptr; sb.out_act = o.act.ptr;
-        sb.H = H; sb.W = Wd; sb.cp_in = in.raw.cp; sb.cin = cin; sb.cout = cout; sb.ldo = pad16(cout); sb.k = k;
+        if (sp) { sb.in_raw_lo = in.raw_lo.ptr; sb.r_act_lo = r_lo.ptr; sb.out_raw_lo = o.raw_lo.ptr; sb.out_act_lo = o.act_lo.ptr; }
+        sb.H = H; sb.W = Wd; sb.cp_in = in.raw.cp; sb.cin = cin; sb.cout = cout; sb.ldo = pad16(cout); sb.k = k; sb.stride = s;
         sb.alpha = 0.2f;
         sb.f16 = f16();
+        // precise = 2 keeps the kernels at their 16-bit values (the model whose energy the sampler walks, model.h)
+        auto wv = [&](float v) { return cfg.precise == 2 && sp ? op16::host_round(v, f16() != 0) : v; };
         for (int c = 0; c < cin; ++c) sb.b0[c] = b0->v[c];
         for (int c = 0; c < cout; ++c) sb.b1[c] = b1->v[c] + bs->v[c];
         // kernel template is instantiated on cin (weights packed [tap][cin][cout] with that cin)
         for (int tp = 0; tp < k * k; ++tp)
             for (int ci = 0; ci < cin; ++ci) {
-                for (int co = 0; co < cin; ++co) sb.w0[(tp * cin + ci) * cin + co] = k0->v[((size_t)tp * cin + ci) * cin + co];
-                for (int co = 0; co < cout; ++co) sb.w1[(tp * cin + ci) * cout + co] = k1->v[((size_t)tp * cin + ci) * cout + co];
+                for (int co = 0; co < cin; ++co) sb.w0[(tp * cin + ci) * cin + co] = wv(k0->v[((size_t)tp * cin + ci) * cin + co]);
+                for (int co = 0; co < cout; ++co) sb.w1[(tp * cin + ci) * cout + co] = wv(k1->v[((size_t)tp * cin + ci) * cout + co]);
             }
         for (int ci = 0; ci < cin; ++ci)
-            for (int co = 0; co < cout; ++co) sb.ws[ci * cout + co] = ks->v[(size_t)ci * cout + co];
+            for (int co = 0; co < cout; ++co) sb.ws[ci * cout + co] = wv(ks->v[(size_t)ci * cout + co]);
         if (macs) *macs += op->macs_per_image;
         prog.push_back(std::move(op));
         if (tape) {

@@ -124,6 +124,8 @@ public:
     Tensor d_seed;             // dD/d(flatten) = W64 w_last, one copy per sample (constant)
     float* gx_f32 = nullptr;   // [max_chunk*HW, C] gradient w.r.t. x_mean
     Tensor g_pre;              // gradient w.r.t. the x_mean head's pre-activation, bf16 [max_chunk,H,W,16]
+    bool head_grad_fused = false;   // tanh' and the mean head's adjoint as ONE CUDA-core kernel (kernels.h: HeadGradParams)
+    HeadGradParams head_grad;
     float* gz_f32 = nullptr;   // [max_chunk, z_dim] d D(G(z)) / d z
     // MALA state (grow-only): current / proposed z, energy, gradient, pure energy, noise
     size_t mala_cap = 0;

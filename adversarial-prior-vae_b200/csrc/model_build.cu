@@ -353,6 +353,7 @@ bool Model::build() {
     // the heads kernel then skips the activated copy (32 B per pixel)
     if (heads_op && !d_prog.empty() && d_prog[0]->is_small_block) {
         heads_op->heads.act = nullptr;
+        heads_op->heads.act_lo = nullptr;
         if (!d_tape.empty()) d_tape[0].in.act = Tensor();      // the adjoint's leaky-relu' mask then reads the raw input (same signs)
     }
     prior4 = alloc_f32(4);

@@ -16,9 +16,11 @@
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cmath>
+#include <cstring>
 #include "kernels.h"
 #include "model.h"
 #include "op16.h"
+#include "tuning.h"
 
 namespace apvae {
 
@@ -143,7 +145,18 @@ bool Model::build_grad() {
     if (!km) return false;
     Tensor g_h = alloc_act(cap, H(), W(), cg);
     if (!g_h.ptr) return false;
-    {
+    // C <= 4 -> cg channels: tanh' and this 1x1 transpose are one HBM-streaming CUDA-core kernel (as a GEMM it pads K from
+    // 3 to 16 and runs at 4 TFLOP/s); tuning.tiny_conv = -1 keeps the elementwise pass + the tensor-core op
+    if (switch_on(tuning().tiny_conv, true) && C() <= kHeadGradMaxC && cg <= kHeadGradMaxCg && g_h.cp % 8 == 0) {
+        head_grad_fused = true;
+        memset(&head_grad, 0, sizeof(head_grad));
+        head_grad.g = gx_f32; head_grad.head = head_f32; head_grad.ld = head_ld();
+        head_grad.C = C(); head_grad.cg = cg; head_grad.cp_out = g_h.cp; head_grad.f16 = f16();
+        head_grad.out = g_h.ptr;
+        for (int co = 0; co < cg; ++co)
+            for (int c = 0; c < C(); ++c) head_grad.w[co * kHeadGradMaxC + c] = km->v[(size_t)co * C() + c];
+        macs_grad += (double)cg * C() * HW();
+    } else {
         Epilogue e; e.out_raw = g_h.ptr; e.ldo = g_h.cp;
         if (!add_op(gg_prog, mean_name + "^T", {gterm(true, 1, 1, C(), cg, g_pre, km)}, {g_pre.ptr}, e, cap, &macs_grad)) return false;
     }
@@ -193,8 +206,13 @@ bool Model::energy_grad_chunk(const float* z_dev, int n, float* energy, float* g
     if (!run_critic_chunk(n, d_out, stream)) return false;
     if (grad) {
         if (!run_program(gd_prog, n, stream)) return false;
-        GCHECK(launch_tanh_backward_pack(gx_f32, head_f32, head_ld(), (long long)n * HW(), C(), g_pre.cp, g_pre.ptr, f16(), stream),
-               "tanh_backward");
+        if (head_grad_fused) {
+            head_grad.pixels = (long long)n * HW();
+            GCHECK(launch_tanh_backward_head(head_grad, stream), "tanh_backward_head");
+        } else {
+            GCHECK(launch_tanh_backward_pack(gx_f32, head_f32, head_ld(), (long long)n * HW(), C(), g_pre.cp, g_pre.ptr, f16(), stream),
+                   "tanh_backward");
+        }
         if (!run_program(gg_prog, n, stream)) return false;
     }
     if (energy || grad)

@@ -814,4 +814,6 @@ def test_bf16_operand_format(case):
         errs[name] = np.abs(g['d_g'] - want['d_g'])
         m.close()
     assert errs['fp16'].max() < ENERGY_ATOL and errs['bf16'].max() < 3e-2, (errs['fp16'].max(), errs['bf16'].max())
-    assert errs['fp16'].mean() < 0.5 * errs['bf16'].mean(), (errs['fp16'].mean(), errs['bf16'].mean())
+    # (how much closer depends on how many layers run on the tensor cores at all: D_psi's first block is a CUDA-core kernel
+    # with fp32 weights in both formats)
+    assert errs['fp16'].mean() < 0.8 * errs['bf16'].mean(), (errs['fp16'].mean(), errs['bf16'].mean())
