@@ -248,6 +248,119 @@ void (*pick_wide(int cin, bool f16))(SmallBlockParams, int) {
     }
 }
 
+
+// Adjoint of the block (kernels.h: SmallBlockGradParams).  One image per CTA; g_u on a zero-bordered fp32 grid in dynamic
+// shared memory.  Pixels are walked as [row][column parity][column / 2], so that with stride 2 the taps a warp needs
+// (di = y mod 2 (+2), dj = x mod 2 (+2)) are warp-uniform and the weights stay uniform constant-bank loads.
+template <int CIN, int COUT, bool F16>
+__global__ void __launch_bounds__(kWideThreads) small_block_grad_kernel(const __grid_constant__ SmallBlockGradParams p, int n_images) {
+    extern __shared__ float sm[];
+    const int H = p.H, W = p.W, HW = H * W, PW = W + 2, plane = (H + 2) * PW, s = p.stride;
+    const int Ho = H / s, Wo = W / s, HWo = Ho * Wo, halfW = W >> 1;
+    float* const gu = sm;                                       // [CIN][plane]
+    const int t = threadIdx.x;
+    const int p1 = (s == 1) ? 1 : 0;                            // pad_lo of conv_1 (TF SAME)
+    auto load_row = [&](const uint8_t* row, float (&g)[COUT]) {
+#pragma unroll
+        for (int c = 0; c < COUT / 8; ++c) {
+            const uint4 v = *reinterpret_cast<const uint4*>(row + c * 16);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { g[c * 8 + 2 * j] = op16::lo<F16>(w[j]); g[c * 8 + 2 * j + 1] = op16::hi<F16>(w[j]); }
+        }
+    };
+    for (int img = blockIdx.x; img < n_images; img += gridDim.x) {
+        for (int i = t; i < CIN * plane; i += kWideThreads) gu[i] = 0.f;
+        __syncthreads();
+        const uint8_t* go = static_cast<const uint8_t*>(p.g_out) + (size_t)img * HWo * p.ldg * 2;
+        const uint8_t* rm = static_cast<const uint8_t*>(p.r_act) + (size_t)img * HW * p.cp_in * 2;
+        const uint8_t* xm = static_cast<const uint8_t*>(p.x_in) + (size_t)img * HW * p.cp_in * 2;
+        // g_u = conv_1^T(g_out) * lrelu'(r)
+        for (int q = t; q < HW; q += kWideThreads) {
+            const int y = q / W, rem = q - y * W, par = rem / halfW, x = 2 * (rem - par * halfW) + par;
+            float acc[CIN];
+#pragma unroll
+            for (int ci = 0; ci < CIN; ++ci) acc[ci] = 0.f;
+            // output (oy, ox) reads input (s oy + di - p1, s ox + dj - p1): this pixel receives from the taps with
+            // (y + p1 - di) and (x + p1 - dj) divisible by s
+            for (int di = (s == 1) ? 0 : ((y + p1) & 1); di < 3; di += s) {
+                const int ty = y + p1 - di;
+                if (ty < 0 || ty >= H) continue;
+                for (int dj = (s == 1) ? 0 : ((x + p1) & 1); dj < 3; dj += s) {
+                    const int tx = x + p1 - dj;
+                    if (tx < 0 || tx >= W) continue;
+                    float g[COUT];
+                    load_row(go + ((size_t)(ty / s) * Wo + tx / s) * p.ldg * 2, g);
+                    const float* w = p.w1 + (di * 3 + dj) * CIN * COUT;
+#pragma unroll
+                    for (int ci = 0; ci < CIN; ++ci)
+#pragma unroll
+                        for (int co = 0; co < COUT; ++co) acc[ci] = fmaf(g[co], w[ci * COUT + co], acc[ci]);
+                }
+            }
+            const uint2 m = *reinterpret_cast<const uint2*>(rm + ((size_t)y * W + x) * p.cp_in * 2);
+            const bool pos[4] = {op16::pos_lo(m.x), op16::pos_hi(m.x), op16::pos_lo(m.y), op16::pos_hi(m.y)};
+#pragma unroll
+            for (int ci = 0; ci < CIN; ++ci) gu[ci * plane + (y + 1) * PW + x + 1] = acc[ci] * (pos[ci] ? 1.f : p.alpha);
+        }
+        __syncthreads();
+        // g_x = conv_0^T(g_u) * lrelu'(x) + shortcut^T(g_out)
+        const int och = p.ldo >> 3;
+        for (int q = t; q < HW; q += kWideThreads) {
+            const int y = q / W, x = q - y * W;
+            float acc[CIN];
+#pragma unroll
+            for (int ci = 0; ci < CIN; ++ci) acc[ci] = 0.f;
+            // u(y', x', co) reads a(y' + di - 1, x' + dj - 1, ci): a(y, x) receives from u(y - di + 1, x - dj + 1)
+#pragma unroll
+            for (int di = 0; di < 3; ++di)
+#pragma unroll
+                for (int dj = 0; dj < 3; ++dj)
+#pragma unroll
+                    for (int co = 0; co < CIN; ++co) {
+                        const float g = gu[co * plane + (y - di + 2) * PW + x - dj + 2];
+#pragma unroll
+                        for (int ci = 0; ci < CIN; ++ci) acc[ci] = fmaf(g, p.w0[((di * 3 + dj) * CIN + ci) * CIN + co], acc[ci]);
+                    }
+            const uint2 m = *reinterpret_cast<const uint2*>(xm + ((size_t)y * W + x) * p.cp_in * 2);
+            const bool pos[4] = {op16::pos_lo(m.x), op16::pos_hi(m.x), op16::pos_lo(m.y), op16::pos_hi(m.y)};
+#pragma unroll
+            for (int ci = 0; ci < CIN; ++ci) acc[ci] *= pos[ci] ? 1.f : p.alpha;
+            if (!(y % s) && !(x % s)) {
+                float g[COUT];
+                load_row(go + ((size_t)(y / s) * Wo + x / s) * p.ldg * 2, g);
+#pragma unroll
+                for (int ci = 0; ci < CIN; ++ci)
+#pragma unroll
+                    for (int co = 0; co < COUT; ++co) acc[ci] = fmaf(g[co], p.ws[ci * COUT + co], acc[ci]);
+            }
+            const size_t pix = (size_t)img * HW + q;
+            if (p.gx_f32) {
+#pragma unroll
+                for (int ci = 0; ci < CIN; ++ci) p.gx_f32[pix * p.ld_f32 + ci] = acc[ci];
+            }
+            if (p.gx_raw) {
+                float v[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                for (int ci = 0; ci < CIN; ++ci) v[ci] = acc[ci];
+                uint4* d = reinterpret_cast<uint4*>(static_cast<uint8_t*>(p.gx_raw) + pix * p.ldo * 2);
+                d[0] = make_uint4(op16::pack<F16>(v[0], v[1]), op16::pack<F16>(v[2], v[3]), 0u, 0u);
+                for (int c = 1; c < och; ++c) d[c] = make_uint4(0u, 0u, 0u, 0u);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+template <int COUT>
+void (*pick_grad(int cin, bool f16))(SmallBlockGradParams, int) {
+    switch (cin) {
+        case 1: return f16 ? small_block_grad_kernel<1, COUT, true> : small_block_grad_kernel<1, COUT, false>;
+        case 2: return f16 ? small_block_grad_kernel<2, COUT, true> : small_block_grad_kernel<2, COUT, false>;
+        default: return f16 ? small_block_grad_kernel<3, COUT, true> : small_block_grad_kernel<3, COUT, false>;
+    }
+}
+
 }  // namespace
 
 int launch_small_block(const SmallBlockParams& p, int n, void* stream) {
@@ -281,6 +394,25 @@ int launch_small_block(const SmallBlockParams& p, int n, void* stream) {
     const int per_sm = smem > 110 * 1024 ? 1 : smem > 72 * 1024 ? 2 : smem > 54 * 1024 ? 3 : 4;
     const int cap = sms * per_sm;
     kern<<<n < cap ? n : cap, kWideThreads, smem, static_cast<cudaStream_t>(stream)>>>(q, n);
+    return (int)cudaGetLastError();
+}
+
+int launch_small_block_grad(const SmallBlockGradParams& p, int n, void* stream) {
+    if (n <= 0) return 0;
+    if (p.cp_in % 8 || p.ldg % 8 || p.cin < 1 || p.cin > kSmallBlockMaxCin || (p.cout != 16 && p.cout != 32) || p.ldg < p.cout ||
+        !p.g_out || !p.r_act || !p.x_in || (p.stride != 1 && p.stride != 2) || p.H > kSmallBlockWideMaxHW || p.W > kSmallBlockWideMaxHW ||
+        (p.H % p.stride) || (p.W % 2) || (p.gx_raw && p.ldo % 8) || (!p.gx_f32 && !p.gx_raw))
+        return (int)cudaErrorInvalidValue;
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    void (*kern)(SmallBlockGradParams, int) = p.cout == 16 ? pick_grad<16>(p.cin, p.f16 != 0) : pick_grad<32>(p.cin, p.f16 != 0);
+    const size_t smem = (size_t)p.cin * (p.H + 2) * (p.W + 2) * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    const int per_sm = smem > 110 * 1024 ? 1 : smem > 72 * 1024 ? 2 : smem > 54 * 1024 ? 3 : 4;
+    const int cap = sms * per_sm;
+    kern<<<n < cap ? n : cap, kWideThreads, smem, static_cast<cudaStream_t>(stream)>>>(p, n);
     return (int)cudaGetLastError();
 }
 

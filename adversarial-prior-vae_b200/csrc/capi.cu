@@ -434,7 +434,7 @@ int apvae_op_time(apvae_handle* h, int net, int index, int n, int reps, char* na
     DevOp& op = *(*p)[index];
     if (n <= 0 || n > op.capacity_n) { m.err = "op_time: n exceeds the op's capacity"; return APVAE_ERR_INVALID; }
     if (name && name_cap > 0) {      // op name + which kernel runs it
-        const std::string full = op.name + (op.is_tiny ? " [tiny conv, CUDA cores]" : op.is_small_block ? " [fused block, CUDA cores]" : op.is_heads ? " [heads, CUDA cores]" : op.is_patch ? (op.pparams.fast_epi ? " [patchgemm, TMA epilogue]" : " [patchgemm]") : " [tapgemm]");
+        const std::string full = op.name + (op.is_tiny ? " [tiny conv, CUDA cores]" : op.is_small_block ? " [fused block, CUDA cores]" : op.is_small_block_grad ? " [fused block adjoint, CUDA cores]" : op.is_heads ? " [heads, CUDA cores]" : op.is_patch ? (op.pparams.fast_epi ? " [patchgemm, TMA epilogue]" : " [patchgemm]") : " [tapgemm]");
         strncpy(name, full.c_str(), name_cap - 1); name[name_cap - 1] = 0;
     }
     if (macs_per_unit) *macs_per_unit = op.macs_per_image;

@@ -192,6 +192,27 @@ struct SmallBlockParams {
 };
 int launch_small_block(const SmallBlockParams& p, int n, void* stream);
 
+// The adjoint of that block (what tf.gradients(energy, [z]) walks through D_psi/level_0 in get_sgld_proposal,
+// dmm_cifar10.py:241-247; model_grad.cu states the algebra): from g_out = dE/d(out) to g_x = dE/dx in one kernel,
+//   g_u = conv_1^T(g_out) * lrelu'(r)          (stride-s transpose; kept in shared memory, fp32)
+//   g_x = conv_0^T(g_u) * lrelu'(x) + shortcut^T(g_out)   (the 1x1 stride-s transpose lands on pixels (s y, s x))
+// with the SAME packed kernels as the forward block.  Replaces 3 (stride 1) or 6 (stride 2: four sub-pixel phases)
+// tensor-core ops whose K or N is 3 padded to 16.
+struct SmallBlockGradParams {
+    const void* g_out;                    // 16-bit [N, H/stride, W/stride, ldg]
+    const void* r_act;                    // 16-bit [N, H, W, cp_in]: sign = lrelu'(conv_0 output)
+    const void* x_in;                     // 16-bit [N, H, W, cp_in]: the block input (raw or activated: same signs)
+    float* gx_f32;  int ld_f32;           // fp32 [N*H*W, ld_f32], cin columns (may be null)
+    void* gx_raw;   int ldo;              // 16-bit [N, H, W, ldo], channels >= cin zero (may be null)
+    int H, W, cp_in, cin, cout, ldg, stride;
+    float alpha;
+    int f16;
+    float w0[kSmallBlockMaxK * kSmallBlockMaxK * kSmallBlockMaxCin * kSmallBlockMaxCin];      // as SmallBlockParams
+    float w1[kSmallBlockMaxK * kSmallBlockMaxK * kSmallBlockMaxCin * kSmallBlockMaxCout];
+    float ws[kSmallBlockMaxCin * kSmallBlockMaxCout];
+};
+int launch_small_block_grad(const SmallBlockGradParams& p, int n, void* stream);
+
 
 // Stride-1 conv2d / conv2d_transpose with <= 4 input AND <= 4 output channels on the CUDA cores: the first conv of a
 // block on the raw image channels (3 -> 3, 1 -> 1) and its adjoint in the sampler's backward pass.  As implicit GEMMs

@@ -287,7 +287,7 @@ bool Model::conv_block(Program& prog, const std::string& root, const BlockSpec& 
         prog.push_back(std::move(op));
         if (tape) {
             BlockTape t; t.scope = pre; t.deconv = false; t.use_shortcut = use_sc; t.k = k; t.stride = s;
-            t.cin = cin; t.cout = cout; t.in = in; t.r_act = r; t.out = o;
+            t.cin = cin; t.cout = cout; t.in = in; t.r_act = r; t.out = o; t.fused = true;
             tape->push_back(t);
         }
         *out = o;

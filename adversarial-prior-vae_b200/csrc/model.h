@@ -58,6 +58,7 @@ struct BlockTape {
     Pair in;        // block input (raw + act)
     Tensor r_act;   // leaky_relu(conv_0 output)
     Pair out;
+    bool fused = false;   // the forward block is ONE CUDA-core kernel (block0.cu): its adjoint can be one too
 };
 
 typedef std::vector<std::unique_ptr<DevOp>> Program;

@@ -42,6 +42,40 @@ bool Model::grad_conv_block(const BlockTape& t, const Tensor& g_out, float* out_
     const HostArr* k0 = W_(t.scope + "residual/conv_0/kernel", {k, k, cin, cin});
     const HostArr* k1 = W_(t.scope + "residual/conv_1/kernel", {k, k, cin, cout});
     if (!k0 || !k1) return false;
+    // the block whose forward is one CUDA-core kernel (<= 3 input channels): its adjoint as one kernel too (block0.cu)
+    if (t.fused && t.use_shortcut && switch_on(tuning().small_block, true) && k == kSmallBlockMaxK && cin <= kSmallBlockMaxCin &&
+        (cout == 16 || cout == 32) && g_out.cp % 8 == 0 && !(Wd & 1) && !(H % s)) {
+        const HostArr* ks = W_(t.scope + "shortcut/kernel", {1, 1, cin, cout});
+        if (!ks) return false;
+        Tensor g_x = alloc_act(cap, H, Wd, cin);
+        if (!g_x.ptr) return false;
+        std::unique_ptr<DevOp> op(new DevOp());
+        op->name = t.scope + "block^T";
+        op->is_small_block_grad = true;
+        op->capacity_n = cap;
+        op->macs_per_image = (double)k * k * cin * cin * H * Wd + ((double)k * k * cin * cout + (double)cin * cout) * (H / s) * (Wd / s);
+        SmallBlockGradParams& sg = op->sbgrad;
+        memset(&sg, 0, sizeof(sg));
+        sg.g_out = g_out.ptr; sg.ldg = g_out.cp;
+        sg.r_act = t.r_act.ptr;
+        sg.x_in = t.in.act.ptr ? t.in.act.ptr : t.in.raw.ptr;
+        sg.gx_f32 = out_f32; sg.ld_f32 = f32_ld;
+        sg.gx_raw = out_f32 ? nullptr : g_x.ptr; sg.ldo = g_x.cp;      // the first block's gradient is only wanted in fp32
+        sg.H = H; sg.W = Wd; sg.cp_in = t.r_act.cp; sg.cin = cin; sg.cout = cout; sg.stride = s;
+        sg.alpha = 0.2f; sg.f16 = f16();
+        if ((t.in.act.ptr ? t.in.act.cp : t.in.raw.cp) != t.r_act.cp) return fail("fused block adjoint: input and r disagree on the channel padding");
+        for (int tp = 0; tp < k * k; ++tp)
+            for (int ci = 0; ci < cin; ++ci) {
+                for (int co = 0; co < cin; ++co) sg.w0[(tp * cin + ci) * cin + co] = k0->v[((size_t)tp * cin + ci) * cin + co];
+                for (int co = 0; co < cout; ++co) sg.w1[(tp * cin + ci) * cout + co] = k1->v[((size_t)tp * cin + ci) * cout + co];
+            }
+        for (int ci = 0; ci < cin; ++ci)
+            for (int co = 0; co < cout; ++co) sg.ws[ci * cout + co] = ks->v[(size_t)ci * cout + co];
+        macs_grad += op->macs_per_image;
+        gd_prog.push_back(std::move(op));
+        *g_x_out = g_x;
+        return true;
+    }
     Tensor g_r = alloc_act(cap, H, Wd, cin);
     if (!g_r.ptr) return false;
     {   // g_r = conv_1^T(g_out) * act'(r)

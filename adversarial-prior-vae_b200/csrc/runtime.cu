@@ -357,6 +357,7 @@ int devop_launch(const DeviceInfo& dev, DevOp& op, int n_valid, void* stream) {
     if (n_valid > op.capacity_n) return (int)cudaErrorInvalidValue;
     if (op.is_tiny) return launch_tiny_conv(op.tiny, n_valid, stream);
     if (op.is_small_block) return launch_small_block(op.sblock, n_valid, stream);
+    if (op.is_small_block_grad) return launch_small_block_grad(op.sbgrad, n_valid, stream);
     if (op.is_heads) return launch_pixel_heads(op.heads, n_valid, stream);
     if (op.is_patch) {
         op.pparams.n_real = n_valid;

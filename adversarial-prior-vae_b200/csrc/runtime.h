@@ -55,6 +55,8 @@ struct DevOp {
     TinyConvParams tiny;
     bool is_small_block = false;    // true: a whole <= 3-channel-input resnet block on the CUDA cores (kernels.h: SmallBlockParams)
     SmallBlockParams sblock;
+    bool is_small_block_grad = false;   // true: the adjoint of such a block (kernels.h: SmallBlockGradParams)
+    SmallBlockGradParams sbgrad;
     double macs_per_image = 0;
     int capacity_n = 0;
     ~DevOp();

@@ -274,6 +274,7 @@ def workload_config(args, world):
     return {'workload': 'BASELINE %s: arch %s (%s-shape) ResNet VAE + energy prior, z_dim=%d, K=%d '
                         'importance-sampled NLL' % (which, args.arch, ds, args.z_dim, args.n_z),
             'arch': args.arch, 'z_dim': args.z_dim, 'n_z': args.n_z, 'images_per_step_per_gpu': args.batch,
+            'scalars': 'p_net/xi = -6 (pre-sigmoid), beta = 0, log_Z = (z_dim / 2) log 2 pi',
             'chunk': args.chunk,
             'operands': '%s operands, fp32 accumulation (tcgen05 kind::f16)' % args.operand_dtype,
             'prior_branch': (not args.no_prior_branch),
@@ -427,6 +428,11 @@ def main():
                     max_batch=max(args.batch, 1), max_chunk=args.chunk, operand_dtype=args.operand_dtype,
                     tuning={k.strip(): int(v) for k, v in (kv.split('=') for kv in args.tuning.split(',') if kv.strip())}, **kw)
     model = Model(cfg, synthetic_weights(weight_schema(cfg)), device=local)
+    # scalars of a trained-like model so that every printed metric is finite in float32 (pd_energy averages
+    # D exp(-w xi D - log_Z + (d/2) log 2 pi): with the initial xi = 0.5 and log_Z = 1 the exponent overflows on random
+    # weights, exactly as the reference's graph would): xi = sigmoid(-6), log_Z = (d/2) log 2 pi.  No effect on the timing.
+    scalars = {'xi_raw': -6.0, 'beta': 0.0, 'log_Z': round(0.5 * cfg.z_dim * float(np.log(2 * np.pi)), 3)}
+    model.set_scalars(scalars['xi_raw'], scalars['beta'], scalars['log_Z'])
     B, K, W, S = args.batch, args.n_z, args.warmup, args.steps
     prior = not args.no_prior_branch
     Kp = cfg.test_n_pz if prior else 0
