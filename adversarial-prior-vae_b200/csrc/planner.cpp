@@ -298,7 +298,6 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.tap_bytes = (uint32_t)P.npad * P.kc * 2;
     // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
     int tpi_want = std::max(1, std::min(kmax, (int)(32768u / P.tap_bytes)));
-    { const int v = tuning().patch_tpi; if (v >= 1 && v <= kmax) tpi_want = v; }
     // CTA pairs (cta_group::2): tuning.patch_2cta = +1 / -1 overrides the default; tuning.patch_2cta_min_k moves the threshold.
     // Measured on B200 (1000 samples, TFLOP/s single -> pair): 96->96 5x5 @32^2 1121 -> 1436, 192->192 3x3 @16^2
     // 1073 -> 1214, 128->128 3x3 @16^2 967 -> 1170, 64->64 3x3 @32^2 697 -> 786, 96->96 3x3 @32^2 778 -> 808; the
@@ -310,6 +309,13 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     if (tuning().patch_2cta != 0) two = tuning().patch_2cta > 0;
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;
+    // in a pair each CTA holds half of every tap tile: a 24 KB tap (192 wide, kc = 64) that would travel alone takes a
+    // second tap along (24 KB per CTA and item).  With three weight slots of that size the patch ring gets a third stage,
+    // which is what the 192-wide layers were short of: measured in one call (per-op table, 7400 samples) 192->192 3x3
+    // @16^2 1.12 -> 0.97 / 1.23 -> 1.11 ms, @8^2 0.31 -> 0.23 / 0.28 -> 0.25 ms; the 256-wide layers (16 KB per CTA and tap)
+    // lose 3 % with two taps and keep one (profiles/r2_notes.md).
+    if (two && tpi_want == 1 && kmax >= 2 && P.tap_bytes <= 24576u) tpi_want = 2;
+    { const int v = tuning().patch_tpi; if (v >= 1 && v <= kmax) tpi_want = v; }
     auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * (P.tap_bytes / (two ? 2 : 1)) + 1023u) & ~1023u; };
     auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * Wt * P.kc * 2 + 1023u) & ~1023u; };
     int macc = 0;
