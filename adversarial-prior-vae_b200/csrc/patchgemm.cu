@@ -31,8 +31,8 @@ constexpr int kMaxStages = 12;
 
 }  // namespace
 
-template <int KC, bool kTwo, bool kMask, bool kF16, bool kSplit>
-__global__ void __launch_bounds__(kThreads, 1)
+template <int KC, bool kTwo, bool kMask, bool kF16, bool kSplit, bool kEpi2>
+__global__ void __launch_bounds__(kEpi2 ? kThreads + 128 : kThreads, 1)
 patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // identical offset in every CTA of the cluster (same kernel, same static layout)
@@ -40,7 +40,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     const uint32_t a_base = smem_base;
     const uint32_t b_base = a_base + p.a_stages * p.a_slot_bytes;
     const uint32_t epi_base = b_base + p.b_stages * p.b_slot_bytes;
-    const uint32_t bar_base = epi_base + (kPatchFixedSmem - 2048u);
+    const uint32_t bar_base = epi_base + ((kEpi2 ? kPatchFixedSmem2 : kPatchFixedSmem) - 2048u);
     auto fullA = [&](int s) { return bar_base + 8u * s; };
     auto emptyA = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
     auto fullB = [&](int s) { return bar_base + 8u * (2 * kMaxStages + s); };
@@ -50,6 +50,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     const uint32_t tmem_ptr_smem = bar_base + 8u * (4 * kMaxStages + 2 * kAccStages);
     auto resbar = [&](int q, int b) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 2 * q + b); };
     auto maskbar = [&](int q) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 8 + q); };
+    auto resbar2 = [&](int e) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 8 + 4 + e); };   // kEpi2: one per epilogue warp
+    auto maskbar2 = [&](int e) { return bar_base + 8u * (4 * kMaxStages + 2 * kAccStages + 1 + 8 + 4 + 8 + e); };
 
     const int warp = uniform_warp_idx();
     const int lane = threadIdx.x & 31;
@@ -68,7 +70,8 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
     if (warp == 1 && elect_one_sync()) {
         for (int s = 0; s < p.a_stages; ++s) { mbar_init(fullA(s), 1); mbar_init(emptyA(s), 1); }
         for (int s = 0; s < p.b_stages; ++s) { mbar_init(fullB(s), 1); mbar_init(emptyB(s), two ? 1 : csize); }
-        for (int a = 0; a < kAccStages; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), two ? 8 : 4); }
+        for (int a = 0; a < kAccStages; ++a) { mbar_init(tfull(a), 1); mbar_init(tempty(a), (two ? 8 : 4) * (kEpi2 ? 2 : 1)); }
+        if constexpr (kEpi2) { for (int e = 0; e < 8; ++e) { mbar_init(resbar2(e), 1); mbar_init(maskbar2(e), 1); } }
         for (int q = 0; q < 4; ++q) { mbar_init(resbar(q, 0), 1); mbar_init(resbar(q, 1), 1); mbar_init(maskbar(q), 1); }
         fence_barrier_init();
     }
@@ -234,7 +237,195 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             __syncwarp();
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
-    } else if (warp >= 4 && p.fast_epi) {
+    } else if (kEpi2 && warp >= 4) {
+        // ===================== epilogue, TMA in / TMA out, TWO warpgroups =====================
+        // Warps 4..7 (grp 0) take the even 64-column blocks of a tile, warps 8..11 (grp 1) the odd ones; both warps of a
+        // lane quarter q read the same TMEM lanes.  Per warp: one residual box (fetched one of ITS blocks ahead), one
+        // (raw, act) staging pair; the value goes chunk by chunk from the TMEM registers to the staging boxes.
+        const int e = warp - 4, q = e & 3, grp = e >> 2;
+        const uint32_t wbase = epi_base + e * kFastEpi2WarpBytes;
+        const uint32_t rawbuf = wbase + kFastEpiBoxBytes, actbuf = wbase + 2 * kFastEpiBoxBytes, bias_s = wbase + 3 * kFastEpiBoxBytes;
+        epilogue_load_bias(p.epi, bias_s, p.NT, 0, lane);
+        const bool leader = elect_one_sync();
+        const bool want_raw = p.epi.out_raw != nullptr, want_act = p.epi.out_act != nullptr;
+        const int res_mode = p.epi.res_mode;
+        const bool do_store = (p.debug != 5 && p.debug != 15), do_work = (p.debug != 4 && p.debug != 14);
+        const uint32_t res_bytes = (uint32_t)p.res_rows * 128u;
+        const float alpha = p.epi.lrelu_alpha;
+        const uint32_t sw = (uint32_t)(lane & 7);
+        const int W = p.W, H = p.H, NT = p.NT, macc = p.macc, tiles_y = p.tiles_y, rows_tile = p.rows_tile, n_valid = p.n_valid;
+        const int lgW = 31 - __clz(W);
+        const bool fold = p.fold > 1;
+        const int tile_step = num_clusters * csize;
+        const int dn = tile_step / tiles_y, dty = tile_step - dn * tiles_y;
+        const int nb_acc = (NT + 63) >> 6, nb_tile = macc * nb_acc;      // 64-column blocks per accumulator / per tile
+        const bool any_mine = nb_tile > grp;                             // a one-block tile leaves grp 1 without work
+        const int bw_last = NT - ((NT - 1) & ~63);
+        struct Pos { int g, n, ty, bi; };                                // a block of mine: round, image, row tile, block in tile
+        auto advance = [&](Pos& s) {
+            s.bi += 2;
+            if (s.bi >= nb_tile) {
+                s.bi = grp; s.g += num_clusters; s.n += dn; s.ty += dty;
+                if (s.ty >= tiles_y) { s.ty -= tiles_y; ++s.n; }
+            }
+        };
+        auto pos_ok = [&](const Pos& s) { return s.g < rounds_total && s.n < n_valid; };
+        auto issue_res = [&](const Pos& s) {
+            if (res_mode == RES_NONE || !pos_ok(s)) return false;
+            const int m = s.bi / nb_acc, cb = (s.bi - m * nb_acc) << 6;
+            const int po = m * kTileM + q * 32;
+            const int gy = s.n * H + s.ty * rows_tile + (po >> lgW), x0 = po & (W - 1);
+            int rp0 = gy * W + x0;
+            if (res_mode == RES_EVEN) {
+                if (gy & 1) return false;
+                rp0 = (gy >> 1) * (W >> 1) + (x0 >> 1);
+            }
+            if (leader) {
+                mbar_expect_tx(resbar2(e), res_bytes);
+                if (fold) tma_load_5d(wbase, &p.tm_res, resbar2(e), cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else tma_load_2d(wbase, &p.tm_res, resbar2(e), cb, rp0);
+            }
+            return true;
+        };
+        // leaky-relu' mask (adjoint ops, raw output only): the forward activation box of one of MY blocks, into the act box
+        auto issue_mask = [&](const Pos& s) {
+            if (!kMask || !pos_ok(s)) return false;
+            const int m = s.bi / nb_acc, cb = (s.bi - m * nb_acc) << 6;
+            const int po = m * kTileM + q * 32;
+            if (leader) {
+                mbar_expect_tx(maskbar2(e), 32u * 128u);
+                if (fold) tma_load_5d(actbuf, &p.tm_mask, maskbar2(e), cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else if (p.fast_mask == 2) tma_load_4d(actbuf, &p.tm_mask, maskbar2(e), cb, po & (W - 1), s.ty * rows_tile + (po >> lgW), s.n);
+                else tma_load_2d(actbuf, &p.tm_mask, maskbar2(e), cb, (s.n * H + s.ty * rows_tile + (po >> lgW)) * W + (po & (W - 1)));
+            }
+            return true;
+        };
+        int rrow = lane;
+        bool lane_res = true;
+        if (res_mode == RES_EVEN) {
+            const int pix = q * 32 + lane;
+            const int x = pix & (W - 1);
+            lane_res = !(x & 1) && !((pix >> lgW) & 1);
+            rrow = (W >= 32) ? (lane >> 1) : ((lane & 15) >> 1);
+        }
+        const uint32_t res_off = (uint32_t)rrow * 128u, rsw = (uint32_t)(rrow & 7);
+        const uint32_t st_off = (uint32_t)lane * 128u;
+        Pos cur;
+        {
+            const int tile0 = cluster_id * csize + (int)rank;
+            cur.g = cluster_id; cur.n = tile0 / tiles_y; cur.ty = tile0 - cur.n * tiles_y; cur.bi = grp;
+        }
+        Pos pre = cur;
+        bool iss = any_mine && issue_res(pre);
+        bool miss = any_mine && issue_mask(pre);
+        if (any_mine) advance(pre);
+        uint32_t rph = 0, mph = 0;
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        auto release_acc = [&]() {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) { if constexpr (two) mbar_arrive_cluster(mapa_shared(tempty(acc), 0)); else mbar_arrive(tempty(acc)); }
+        };
+        auto block2 = [&](auto bw_c, uint32_t taddr, int cb, int m, bool last_of_tile) {
+            constexpr int BW = decltype(bw_c)::value;
+            constexpr int NCH = BW / 8;
+            uint32_t v[(BW + 31) / 32 * 32];
+            {
+                uint32_t (&v0)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[0]);
+                if constexpr (BW >= 32) tmem_ld32(taddr, v0);
+                else { uint32_t (&l0)[16] = *reinterpret_cast<uint32_t (*)[16]>(&v[0]); tmem_ld16(taddr, l0); }
+                if constexpr (BW == 64) { uint32_t (&v1)[32] = *reinterpret_cast<uint32_t (*)[32]>(&v[32]); tmem_ld32(taddr + 32, v1); }
+                if constexpr (BW == 48) { uint32_t (&l1)[16] = *reinterpret_cast<uint32_t (*)[16]>(&v[32]); tmem_ld16(taddr + 32, l1); }
+            }
+            const bool has_res = iss;
+            if (has_res) { mbar_wait(resbar2(e), rph); rph ^= 1; }
+            const bool use_mask = kMask && miss;
+            if (use_mask) { mbar_wait(maskbar2(e), mph); mph ^= 1; }
+            if (leader) tma_store_wait_read();             // my previous block's stores have left the staging pair
+            tmem_ld_wait();
+            if (last_of_tile) release_acc();               // my part of the accumulator is in registers
+            __syncwarp();
+            const uint32_t rbuf = wbase + res_off;
+            const uint32_t bias_b = bias_s + cb * 4;
+#pragma unroll
+            for (int ch = 0; ch < NCH; ++ch) {
+                float f[8];
+                const float4 b0 = ld_shared_f4(bias_b + ch * 32);
+                const float4 b1 = ld_shared_f4(bias_b + ch * 32 + 16);
+                f[0] = __uint_as_float(v[ch * 8 + 0]) + b0.x; f[1] = __uint_as_float(v[ch * 8 + 1]) + b0.y;
+                f[2] = __uint_as_float(v[ch * 8 + 2]) + b0.z; f[3] = __uint_as_float(v[ch * 8 + 3]) + b0.w;
+                f[4] = __uint_as_float(v[ch * 8 + 4]) + b1.x; f[5] = __uint_as_float(v[ch * 8 + 5]) + b1.y;
+                f[6] = __uint_as_float(v[ch * 8 + 6]) + b1.z; f[7] = __uint_as_float(v[ch * 8 + 7]) + b1.w;
+                if (use_mask) {                            // v *= leaky-relu'(forward activation)
+                    const uint4 mv = ld_shared_v4(actbuf + st_off + (((uint32_t)ch ^ sw) << 4));
+                    f[0] *= op16::pos_lo(mv.x) ? 1.f : alpha; f[1] *= op16::pos_hi(mv.x) ? 1.f : alpha;
+                    f[2] *= op16::pos_lo(mv.y) ? 1.f : alpha; f[3] *= op16::pos_hi(mv.y) ? 1.f : alpha;
+                    f[4] *= op16::pos_lo(mv.z) ? 1.f : alpha; f[5] *= op16::pos_hi(mv.z) ? 1.f : alpha;
+                    f[6] *= op16::pos_lo(mv.w) ? 1.f : alpha; f[7] *= op16::pos_hi(mv.w) ? 1.f : alpha;
+                }
+                if (has_res) {
+                    const uint4 rv = ld_shared_v4(rbuf + (((uint32_t)ch ^ rsw) << 4));
+                    if (lane_res) {
+                        const float2 r0 = op16::unpack<kF16>(rv.x), r1 = op16::unpack<kF16>(rv.y), r2 = op16::unpack<kF16>(rv.z), r3 = op16::unpack<kF16>(rv.w);
+                        f[0] += r0.x; f[1] += r0.y; f[2] += r1.x; f[3] += r1.y;
+                        f[4] += r2.x; f[5] += r2.y; f[6] += r3.x; f[7] += r3.y;
+                    }
+                }
+                if (want_raw)
+                    st_shared_v4(rawbuf + st_off + (((uint32_t)ch ^ sw) << 4), op16::pack<kF16>(f[0], f[1]), op16::pack<kF16>(f[2], f[3]),
+                                 op16::pack<kF16>(f[4], f[5]), op16::pack<kF16>(f[6], f[7]));
+                if (want_act)
+                    st_shared_v4(actbuf + st_off + (((uint32_t)ch ^ sw) << 4),
+                                 op16::pack<kF16>(fmaxf(f[0], alpha * f[0]), fmaxf(f[1], alpha * f[1])),
+                                 op16::pack<kF16>(fmaxf(f[2], alpha * f[2]), fmaxf(f[3], alpha * f[3])),
+                                 op16::pack<kF16>(fmaxf(f[4], alpha * f[4]), fmaxf(f[5], alpha * f[5])),
+                                 op16::pack<kF16>(fmaxf(f[6], alpha * f[6]), fmaxf(f[7], alpha * f[7])));
+            }
+            __syncwarp();                                  // every lane has read the residual (and mask) box: fetch my next block's
+            iss = issue_res(pre);
+            miss = issue_mask(pre);
+            advance(pre);
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (leader && do_store && cur.n < n_valid) {
+                const int po = m * kTileM + q * 32;
+                const int oyy = cur.ty * rows_tile + (po >> lgW), ox0 = po & (W - 1);
+                if (fold) {
+                    if (want_raw) tma_store_5d(&p.tm_raw, rawbuf, cb, 0, 0, oyy, cur.n);
+                    if (want_act) tma_store_5d(&p.tm_act, actbuf, cb, 0, 0, oyy, cur.n);
+                } else {
+                    if (want_raw) tma_store_4d(&p.tm_raw, rawbuf, cb, ox0, oyy, cur.n);
+                    if (want_act) tma_store_4d(&p.tm_act, actbuf, cb, ox0, oyy, cur.n);
+                }
+                tma_store_commit();
+            }
+        };
+        for (int g = cluster_id; g < rounds_total; g += num_clusters) {
+            mbar_wait(tfull(acc), acc_phase);
+            tc_fence_after();
+            if (!any_mine || !do_work) {
+                release_acc();
+            } else {
+                for (int bi = grp; bi < nb_tile; bi += 2) {
+                    const int m = bi / nb_acc, cbi = bi - m * nb_acc, cb = cbi << 6;
+                    const bool last = bi + 2 >= nb_tile;
+                    const int bw = (cbi + 1 == nb_acc) ? bw_last : 64;
+                    const uint32_t taddr = tmem_base + acc * kAccColStride + m * NT + cb + ((uint32_t)(q * 32) << 16);
+                    if (bw == 64) block2(std::integral_constant<int, 64>{}, taddr, cb, m, last);
+                    else if (bw == 32) block2(std::integral_constant<int, 32>{}, taddr, cb, m, last);
+                    else if (bw == 16) block2(std::integral_constant<int, 16>{}, taddr, cb, m, last);
+                    else block2(std::integral_constant<int, 48>{}, taddr, cb, m, last);
+                }
+            }
+            // my next tile
+            cur.g += num_clusters; cur.n += dn; cur.ty += dty;
+            if (cur.ty >= tiles_y) { cur.ty -= tiles_y; ++cur.n; }
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (leader) tma_store_wait_all();
+        __syncwarp();
+    } else if (warp >= 4 && warp < 8 && p.fast_epi) {
         // ===================== epilogue, TMA in / TMA out =====================
         // Work unit = "block": 32 rows (this warp's TMEM lane quarter) x up to 64 columns of one accumulator.
         // Everything that positions a block is warp-uniform and advances by adds / shifts (W is a power of two);
@@ -597,7 +788,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         }
         if (leader) tma_store_wait_all();
         __syncwarp();
-    } else if (warp >= 4) {
+    } else if (warp >= 4 && warp < 8) {
         // ===================== epilogue =====================
         const int q = warp & 3;
         const int r = q * 32 + lane;
@@ -662,7 +853,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
 }
 
 uint32_t patchgemm_smem_bytes(const PatchGemmParams& p) {
-    return p.a_stages * p.a_slot_bytes + p.b_stages * p.b_slot_bytes + kPatchFixedSmem;
+    return p.a_stages * p.a_slot_bytes + p.b_stages * p.b_slot_bytes + (p.epi2 && p.fast_epi ? kPatchFixedSmem2 : kPatchFixedSmem);
 }
 
 int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
@@ -680,10 +871,15 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     const bool f16 = p.epi.f16 != 0;
     const bool sp = p.fast_epi && p.split;
     if (sp && mk) return (int)cudaErrorInvalidValue;          // the split-precision TMA epilogue carries no mask
-#define APVAE_PATCH_PICK2(KC, TWO, MK, SP) kern = f16 ? patchgemm_kernel<KC, TWO, MK, true, SP> : patchgemm_kernel<KC, TWO, MK, false, SP>
+    const bool e2 = p.fast_epi && p.epi2;
+    if (e2 && sp) return (int)cudaErrorInvalidValue;          // two epilogue warpgroups: 16-bit epilogue, with or without mask
+#define APVAE_PATCH_PICK2(KC, TWO, MK, SP) kern = f16 ? patchgemm_kernel<KC, TWO, MK, true, SP, false> : patchgemm_kernel<KC, TWO, MK, false, SP, false>
+#define APVAE_PATCH_PICK_E2(KC, TWO, MK) kern = f16 ? patchgemm_kernel<KC, TWO, MK, true, false, true> : patchgemm_kernel<KC, TWO, MK, false, false, true>
 #define APVAE_PATCH_PICK(KC)                                                                                           \
     do {                                                                                                               \
-        if (two) { if (sp) APVAE_PATCH_PICK2(KC, true, false, true); else if (mk) APVAE_PATCH_PICK2(KC, true, true, false);     \
+        if (e2) { if (two) { if (mk) APVAE_PATCH_PICK_E2(KC, true, true); else APVAE_PATCH_PICK_E2(KC, true, false); }  \
+                  else { if (mk) APVAE_PATCH_PICK_E2(KC, false, true); else APVAE_PATCH_PICK_E2(KC, false, false); } }  \
+        else if (two) { if (sp) APVAE_PATCH_PICK2(KC, true, false, true); else if (mk) APVAE_PATCH_PICK2(KC, true, true, false);     \
                    else APVAE_PATCH_PICK2(KC, true, false, false); }                                                   \
         else { if (sp) APVAE_PATCH_PICK2(KC, false, false, true); else if (mk) APVAE_PATCH_PICK2(KC, false, true, false);       \
                else APVAE_PATCH_PICK2(KC, false, false, false); }                                                      \
@@ -696,11 +892,12 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     }
 #undef APVAE_PATCH_PICK
 #undef APVAE_PATCH_PICK2
+#undef APVAE_PATCH_PICK_E2
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return (int)err;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((num_sms / c) * c);
-    cfg.blockDim = dim3(kThreads);
+    cfg.blockDim = dim3(e2 ? kThreads + 128 : kThreads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = static_cast<cudaStream_t>(stream);
     cudaLaunchAttribute attr[1];
@@ -713,8 +910,8 @@ int launch_patchgemm(const PatchGemmParams& p, int num_sms, void* stream) {
     // one persistent cluster per co-resident slot (GPC boundaries can leave a few SMs without a full cluster)
     int max_clusters = num_sms / c;
     if (c > 1) {
-        static int cached[36][5] = {{0}};                     // [kc index, pair mode, epilogue variant, format][cluster] -> max active clusters
-        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (mk ? 6 : sp ? 12 : 0) + (f16 ? 18 : 0);
+        static int cached[72][5] = {{0}};                     // [kc index, pair mode, epilogue variant, format][cluster] -> max active clusters
+        const int ki = (p.kc == 16 ? 0 : p.kc == 32 ? 1 : 2) + (two ? 3 : 0) + (e2 ? (mk ? 24 : 18) : mk ? 6 : sp ? 12 : 0) + (f16 ? 30 : 0);
         if (cached[ki][c] == 0) {
             int nc = 0;
             if (cudaOccupancyMaxActiveClusters(&nc, kern, &cfg) == cudaSuccess && nc > 0) cached[ki][c] = nc;

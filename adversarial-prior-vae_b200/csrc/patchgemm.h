@@ -40,6 +40,12 @@ constexpr int kPatchMaxGroups = 48;
 constexpr uint32_t kFastEpiBoxBytes = 32u * 128u;
 constexpr uint32_t kFastEpiWarpBytes = 4u * kFastEpiBoxBytes + 1024u;
 constexpr uint32_t kFastEpiSmemBytes = 4u * kFastEpiWarpBytes;
+// Two epilogue warpgroups (PatchGemmParams::epi2: warps 4..7 take the even 64-column blocks of a tile, warps 8..11 the odd
+// ones; 384 threads): per warp ONE residual box, one raw and one act staging box and the bias row.  For ops whose tile
+// costs the epilogue more than the MMAs (few K-elements per output: 3x3 96-wide layers, 1x1 shortcuts, sub-pixel phases,
+// everything narrow).
+constexpr uint32_t kFastEpi2WarpBytes = 3u * kFastEpiBoxBytes + 1024u;
+constexpr uint32_t kPatchFixedSmem2 = 1024u + 1024u + 8u * kFastEpi2WarpBytes;
 // shared memory the kernel needs besides the two rings: barriers, realignment slack, epilogue staging
 constexpr uint32_t kPatchFixedSmem = 1024u + 1024u + (kFastEpiSmemBytes > kEpiSmemBytes ? kFastEpiSmemBytes : kEpiSmemBytes);
 
@@ -75,6 +81,7 @@ struct alignas(64) PatchGemmParams {
                                      // one block ahead into the (unused) act staging box
     int fast_mask;                   // 1: tm_mask is valid and the TMA epilogue multiplies by leaky-relu'(mask); 2: tm_mask is the
                                      // 4-D strided view of a sub-pixel phase, loaded at the store's coordinates
+    int epi2;                        // 1 (fast_epi, no mask, no split): two epilogue warpgroups, 384 threads, kPatchFixedSmem2
     int split;                       // 1 (fast_epi, no mask): split-precision epilogue — every output is written as a hi + lo
                                      // pair (tm_raw / tm_act and tm_raw_lo / tm_act_lo, two store passes through the same
                                      // staging boxes) and the residual is read as hi + lo (tm_res / tm_res_lo, one box each)

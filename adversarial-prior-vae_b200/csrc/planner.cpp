@@ -294,7 +294,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         kmax = ph_nv;
         P.phase = phase; P.out_scale = 2;
     }
-    const uint32_t budget = 227u * 1024u - kPatchFixedSmem;
+    uint32_t budget = 227u * 1024u - kPatchFixedSmem;
     P.tap_bytes = (uint32_t)P.npad * P.kc * 2;
     // weight item = `tpi` vertical taps behind one barrier: up to 32 KB, fewer when the rings would not fit
     int tpi_want = std::max(1, std::min(kmax, (int)(32768u / P.tap_bytes)));
@@ -316,35 +316,73 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     // lose 3 % with two taps and keep one (profiles/r2_notes.md).
     if (two && tpi_want == 1 && kmax >= 2 && P.tap_bytes <= 24576u) tpi_want = 2;
     { const int v = tuning().patch_tpi; if (v >= 1 && v <= kmax) tpi_want = v; }
+    // Two epilogue warpgroups when a tile costs the epilogue more than the MMAs.  Measured (clock stamps of CTA 0, 96->96 3x3
+    // @32^2): a 64-column block takes one epilogue warp ~2.8 k cycles, a 16-column one ~1.0 k (~400 + 37 per column); an MMA
+    // of M = 128 per CTA takes max(N / 2, 32) cycles at best (the 4 KB A-operand read from shared memory).  The wider
+    // staging costs 39 KB of ring space, so it is only taken when the tile is clearly epilogue-bound.
+    {
+        const int nb_acc = (P.npad + 63) / 64;
+        const int last_cols = P.npad - (nb_acc - 1) * 64;
+        long long taps = 0;                                    // (tap, 16-channel slice) MMAs per accumulator and tile
+        if (phase >= 0) taps = (long long)ph_nv * ph_nh * ((t0.cin + P.kc - 1) / P.kc) * (P.kc / 16) * (long long)terms.size();
+        else for (const TermSpec& t : terms) taps += (long long)(s2c ? t.k * t.k : t.k * t.k) * ((t.cin + P.kc - 1) / P.kc) * (P.kc / 16);
+        const double mma_cyc = (double)taps * std::max(P.npad / 2, 32);
+        const double epi_cyc = (nb_acc - 1) * 2800.0 + (400.0 + 37.0 * last_cols);
+        const bool want = epi_cyc > 1.25 * mma_cyc;
+        const int sw = tuning().patch_epi2;
+        P.epi2 = (sw != 0 ? sw > 0 : want) ? 1 : 0;
+        if (P.epi2) budget = 227u * 1024u - kPatchFixedSmem2;
+    }
     auto b_slot_for = [&](int tpi) { return ((uint32_t)tpi * (P.tap_bytes / (two ? 2 : 1)) + 1023u) & ~1023u; };
     auto a_slot_for = [&](int macc) { return ((uint32_t)(macc * rows128 + kmax - 1) * Wt * P.kc * 2 + 1023u) & ~1023u; };
-    int macc = 0;
-    for (int cand : {4, 2, 1}) {
-        if (force_macc && cand != force_macc) continue;
-        if (cand * P.npad > 256) continue;
-        const int rt = cand * rows128;
-        if (rt > H || H % rt) continue;
-        int tpi = tpi_want;
-        while (tpi > 1 && 2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > budget) --tpi;
-        if (2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > budget) continue;
-        macc = cand;
-        P.tpi = tpi;
-        break;
+    // accumulator count, taps per item and ring depths for a given ring budget
+    struct Rings { int macc = 0, tpi = 1, a_stages = 0, b_stages = 0; };
+    int a_cap = 4;
+    { const int v = tuning().patch_a_cap; if (v >= 2 && v <= 12) a_cap = v; }
+    auto size_rings = [&](uint32_t bud) {
+        Rings r;
+        for (int cand : {4, 2, 1}) {
+            if (force_macc && cand != force_macc) continue;
+            if (cand * P.npad > 256) continue;
+            const int rt = cand * rows128;
+            if (rt > H || H % rt) continue;
+            int tpi = tpi_want;
+            while (tpi > 1 && 2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > bud) --tpi;
+            if (2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > bud) continue;
+            r.macc = cand;
+            r.tpi = tpi;
+            break;
+        }
+        if (!r.macc) return r;
+        const uint32_t as = a_slot_for(r.macc), bs = b_slot_for(r.tpi);
+        // ring depths: weights first (k+2 tiles keep one dx group ahead), then patches, then more weights
+        r.b_stages = std::min(12, (kmax + r.tpi - 1) / r.tpi + 2);
+        while (r.b_stages > 2 && 2 * as + r.b_stages * bs > bud) --r.b_stages;
+        r.a_stages = 2;
+        while (r.a_stages < a_cap && (r.a_stages + 1) * as + r.b_stages * bs <= bud) ++r.a_stages;
+        while (r.b_stages < 12 && r.a_stages * as + (r.b_stages + 1) * bs <= bud) ++r.b_stages;
+        return r;
+    };
+    Rings R = size_rings(budget);
+    if (P.epi2 && tuning().patch_epi2 == 0) {
+        // the wider staging must not cost the op what it was short of: same accumulator count, and a patch ring as deep as
+        // without it unless the patches are small (kc <= 32) or the op is a 1x1 (three groups per tile).  Measured layer by
+        // layer (tools/r2_epi2_layers.sh): 64->64 3x3 @32^2 +16 % with macc 4 -> 2, 64->128 stride 2 +20 % with 3 -> 2 patch stages,
+        // against -7 .. -22 % for the 16- / 32-channel layers, -13 .. -17 % for the 1x1 shortcuts, -6 % for 96->96 3x3.
+        const Rings R1 = size_rings(227u * 1024u - kPatchFixedSmem);
+        const bool ok = R.macc && R.macc == R1.macc && (R.a_stages >= R1.a_stages || P.kc <= 32 || ktot == 1);
+        if (!ok) { P.epi2 = 0; budget = 227u * 1024u - kPatchFixedSmem; R = R1; }
     }
-    if (!macc) return fail("patch: no accumulator count fits");
+    if (!R.macc) return fail("patch: no accumulator count fits");
+    const int macc = R.macc;
+    P.tpi = R.tpi;
     P.macc = macc;
     P.rows_tile = macc * rows128;
     P.tiles_y = (H + P.rows_tile - 1) / P.rows_tile;
     P.a_slot_bytes = a_slot_for(macc);
     P.b_slot_bytes = b_slot_for(P.tpi);
-    // ring depths: weights first (k+2 tiles keep one dx group ahead), then patches, then more weights
-    P.b_stages = std::min(12, (kmax + P.tpi - 1) / P.tpi + 2);
-    while (P.b_stages > 2 && 2 * P.a_slot_bytes + P.b_stages * P.b_slot_bytes > budget) --P.b_stages;
-    P.a_stages = 2;
-    int a_cap = 4;
-    { const int v = tuning().patch_a_cap; if (v >= 2 && v <= 12) a_cap = v; }
-    while (P.a_stages < a_cap && (P.a_stages + 1) * P.a_slot_bytes + P.b_stages * P.b_slot_bytes <= budget) ++P.a_stages;
-    while (P.b_stages < 12 && P.a_stages * P.a_slot_bytes + (P.b_stages + 1) * P.b_slot_bytes <= budget) ++P.b_stages;
+    P.a_stages = R.a_stages;
+    P.b_stages = R.b_stages;
     { const int v = tuning().patch_a_stages; if (v >= 1 && v <= P.a_stages) P.a_stages = v; }
     { const int v = tuning().patch_b_stages; if (v >= 1 && v <= P.b_stages) P.b_stages = v; }
     // cluster: weight-stream multicast across 2 / 4 CTAs is available (force_cluster) but measured slower

@@ -75,6 +75,7 @@ struct PatchPlan {
     uint32_t a_slot_bytes = 0, b_slot_bytes = 0;
     int cluster = 1;
     int two_cta = 0;               // cta_group::2 pairs (cluster == 2): each CTA stores half of every weight tile
+    int epi2 = 0;                  // two epilogue warpgroups (patchgemm.h): the rings are sized for kPatchFixedSmem2
     // sub-pixel phase of a stride-2 transposed conv (-1: ordinary stride-1 op).  Phase (py, px) = (phase >> 1, phase & 1)
     // is a stride-1 correlation over the INPUT grid whose results land on output pixels (2y + py, 2x + px).
     int phase = -1;                // 4 + py: both column phases of output rows 2y + py (N = [px 0 | px 1] x cout, see planner.cpp)

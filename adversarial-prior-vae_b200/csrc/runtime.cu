@@ -237,6 +237,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             };
             map_res(&p.tm_res, epi.res);
             p.split = any_lo ? 1 : 0;
+            p.epi2 = (plan.epi2 && !any_lo) ? 1 : 0;                   // two epilogue warpgroups: 16-bit epilogue (mask allowed)
             if (any_lo) {
                 const void* any_lo_out = epi.out_raw_lo ? epi.out_raw_lo : epi.out_act_lo;
                 map_out(&p.tm_raw_lo, epi.out_raw_lo ? epi.out_raw_lo : any_lo_out, epi.ldo);

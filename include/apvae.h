@@ -58,6 +58,7 @@ typedef struct apvae_tuning {
     int tiny_conv;          /* switch (default on): <= 4 -> <= 4 channel convs on the CUDA cores (tinyconv.cu) */
     int small_block;        /* switch (default on): D_psi/level_0 as one fused CUDA-core block (block0.cu) */
     int heads_gemm;         /* switch (default off): G_theta's 1x1 heads as a tensor-core op instead of heads.cu */
+    int patch_epi2;         /* switch (default: when a tile is epilogue-bound): two epilogue warpgroups in the patch kernel */
     int patch_split;        /* switch (default on): two-term split-precision ops (precise = 2) on the patch kernel */
     int debug;              /* patch kernel probe modes (skip loads / MMAs / epilogue / stores); 0 in any real run */
     int trace;              /* switch (default off): clock stamps of CTA 0, read back by apvae_plan_bench */
@@ -307,6 +308,7 @@ typedef struct apvae_plan_info {
     int patch_s2d, patch_nmaps, patch_map_src[4], patch_map_ph[4], patch_map_prow[4];
     int patch_phase, patch_out_scale, patch_npad;   /* of the selected patch plan (apvae_plan_select_patch): sub-pixel phase 0..3, row phase 4..5, -1 none */
     int patch_fold;   /* 2: 8-pixel-wide images are processed in pairs, side by side in one 16-wide tile row (even capacity) */
+    int patch_epi2;   /* 1: the selected patch plan asks for two epilogue warpgroups (epilogue-bound tiles) */
 } apvae_plan_info;
 
 typedef struct apvae_epilogue {

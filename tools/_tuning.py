@@ -11,7 +11,7 @@ _ENV = {  # variable -> (field, kind)
     'APVAE_PATCH_ACAP': ('patch_a_cap', 'int'), 'APVAE_PATCH_ASTAGES': ('patch_a_stages', 'int'), 'APVAE_PATCH_BSTAGES': ('patch_b_stages', 'int'),
     'APVAE_TAP_2CTA': ('tap_2cta', 'switch'), 'APVAE_FAST_EPI': ('fast_epi', 'switch'), 'APVAE_FAST_MASK': ('fast_mask', 'switch'),
     'APVAE_TINY': ('tiny_conv', 'switch'), 'APVAE_SMALL_BLOCK': ('small_block', 'switch'), 'APVAE_HEADS_GEMM': ('heads_gemm', 'switch'),
-    'APVAE_PATCH_DEBUG': ('debug', 'int'), 'APVAE_PATCH_TRACE': ('trace', 'switch'),
+    'APVAE_PATCH_EPI2': ('patch_epi2', 'switch'), 'APVAE_PATCH_DEBUG': ('debug', 'int'), 'APVAE_PATCH_TRACE': ('trace', 'switch'),
 }
 
 
