@@ -310,8 +310,8 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     if (force_cluster && force_cluster != 2) two = 0;
     P.two_cta = two;
     // in a pair each CTA holds half of every tap tile: a 24 KB tap (192 wide, kc = 64) that would travel alone takes a
-    // second tap along (24 KB per CTA and item).  With three weight slots of that size the patch ring gets a third stage,
-    // which is what the 192-wide layers were short of: measured in one call (per-op table, 7400 samples) 192->192 3x3
+    // second tap along (24 KB per CTA and item): the MMA warp then crosses a weight barrier every 8 MMAs instead of every 4
+    // (the same effect that made the 96-wide layers need all their taps in one item).  Measured in one call (per-op table, 7400 samples) 192->192 3x3
     // @16^2 1.12 -> 0.97 / 1.23 -> 1.11 ms, @8^2 0.31 -> 0.23 / 0.28 -> 0.25 ms; the 256-wide layers (16 KB per CTA and tap)
     // lose 3 % with two taps and keep one (profiles/r2_notes.md).
     if (two && tpi_want == 1 && kmax >= 2 && P.tap_bytes <= 24576u) tpi_want = 2;

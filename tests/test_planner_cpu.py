@@ -296,3 +296,31 @@ def test_python_tuning_struct_matches_the_header():
     assert _lib.Tuning.make(dict(patch=-1, patch_split=1)).patch == -1
     with pytest.raises(AttributeError):
         _lib.Tuning.make(dict(no_such_knob=1))
+
+
+def test_planner_picks_the_second_epilogue_warpgroup_for_epilogue_bound_tiles():
+    """PatchPlan::epi2 (planner.cpp): two epilogue warpgroups when the estimated epilogue cycles of a tile exceed its MMA
+    cycles, unless the wider staging would cost the op an accumulator or (large patches) a patch stage; tuning.patch_epi2
+    forces it either way.  Also the weight-item rule of the 192-wide pair layers: two taps per item (four 24 KB weight slots
+    and three patch stages instead of six one-tap slots and four)."""
+    def plan(transpose, k, H, W, cin, cout, stride=1, tuning=None, which=None):
+        shp = (k, k, cout, cin) if transpose else (k, k, cin, cout)
+        p = Plan([dict(src=0, transpose=transpose, stride=stride, in_h=H, in_w=W, kernel=np.zeros(shp, np.float32))], 7400, tuning=tuning)
+        if which is not None:
+            p.select_patch(which)
+        return p.info
+    # epilogue-bound: narrow layers, 1x1 shortcuts, the 96-wide 3x3
+    for args in ((False, 3, 32, 32, 16, 16), (False, 3, 32, 32, 16, 32), (False, 3, 32, 32, 32, 32), (True, 1, 16, 16, 192, 96),
+                 (True, 3, 32, 32, 96, 96), (True, 3, 8, 8, 2, 192)):
+        assert plan(*args).patch_epi2 == 1, args
+        assert plan(*args, tuning=dict(patch_epi2=-1)).patch_epi2 == 0
+    # MMA-bound, or not worth an accumulator / a patch stage: one warpgroup
+    for args in ((True, 3, 16, 16, 192, 192), (True, 5, 32, 32, 96, 96), (False, 3, 32, 32, 64, 64), (False, 3, 32, 32, 64, 128, 2),
+                 (False, 3, 16, 16, 128, 128), (True, 5, 64, 64, 32, 32)):
+        assert plan(*args).patch_epi2 == 0, args
+    assert plan(False, 3, 32, 32, 64, 64).patch_macc == 4 and plan(False, 3, 32, 32, 64, 64, tuning=dict(patch_epi2=1)).patch_macc == 2
+    # 192-wide pair layers: four two-tap weight slots
+    i = plan(True, 3, 16, 16, 192, 192)
+    assert (i.patch_cluster, i.patch_a_stages, i.patch_b_stages) == (2, 3, 4)
+    j = plan(True, 3, 16, 16, 192, 192, tuning=dict(patch_tpi=1))
+    assert (j.patch_a_stages, j.patch_b_stages) == (4, 6)
