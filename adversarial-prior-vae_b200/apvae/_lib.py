@@ -34,7 +34,7 @@ class ApvaeError(RuntimeError):
 
 TUNING_FIELDS = ('patch', 'patch_macc', 'patch_cluster', 'patch_max_n', 'patch_phases', 'patch_merge', 'patch_s2',
                  'patch_fold', 'patch_tpi', 'patch_2cta', 'patch_2cta_min_k', 'patch_a_cap', 'patch_a_stages', 'patch_b_stages',
-                 'tap_2cta', 'fast_epi', 'fast_mask', 'tiny_conv', 'small_block', 'heads_gemm', 'patch_epi2', 'patch_split', 'debug', 'trace')
+                 'tap_2cta', 'fast_epi', 'fast_mask', 'tiny_conv', 'small_block', 'heads_gemm', 'patch_epi2', 'patch_split', 'debug', 'trace', 'patch_virtual')
 
 
 class Tuning(C.Structure):
@@ -90,7 +90,7 @@ class PlanInfo(C.Structure):
         ('patch_a_stages', C.c_int), ('patch_b_stages', C.c_int), ('patch_prow', C.c_int * 2),
         ('patch_s2d', C.c_int), ('patch_nmaps', C.c_int), ('patch_map_src', C.c_int * 4), ('patch_map_ph', C.c_int * 4),
         ('patch_map_prow', C.c_int * 4), ('patch_phase', C.c_int), ('patch_out_scale', C.c_int), ('patch_npad', C.c_int),
-        ('patch_fold', C.c_int), ('patch_epi2', C.c_int),
+        ('patch_fold', C.c_int), ('patch_epi2', C.c_int), ('patch_wv', C.c_int),
     ]
 
 

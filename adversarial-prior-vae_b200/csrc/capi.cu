@@ -632,6 +632,7 @@ int apvae_plan_get_info(const apvae_plan* p, apvae_plan_info* info) {
         info->patch_prow[0] = Q.prow[0]; info->patch_prow[1] = Q.prow[1];
         info->patch_fold = Q.fold;
         info->patch_epi2 = Q.epi2;
+        info->patch_wv = Q.w;
         info->patch_s2d = Q.s2d; info->patch_nmaps = Q.nmaps;
         for (int i = 0; i < 4; ++i) { info->patch_map_src[i] = Q.map_src[i]; info->patch_map_ph[i] = Q.map_ph[i]; info->patch_map_prow[i] = Q.prow[i]; }
     }

@@ -256,6 +256,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         const int W = p.W, H = p.H, NT = p.NT, macc = p.macc, tiles_y = p.tiles_y, rows_tile = p.rows_tile, n_valid = p.n_valid;
         const int lgW = 31 - __clz(W);
         const bool fold = p.fold > 1;
+        const int rsh = (res_mode == RES_EVEN) ? 1 : 0;      // 4-D residual view (virtual widths): half-resolution coordinates
         const int tile_step = num_clusters * csize;
         const int dn = tile_step / tiles_y, dty = tile_step - dn * tiles_y;
         const int nb_acc = (NT + 63) >> 6, nb_tile = macc * nb_acc;      // 64-column blocks per accumulator / per tile
@@ -283,6 +284,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             if (leader) {
                 mbar_expect_tx(resbar2(e), res_bytes);
                 if (fold) tma_load_5d(wbase, &p.tm_res, resbar2(e), cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else if (p.res4d) tma_load_4d(wbase, &p.tm_res, resbar2(e), cb, x0 >> rsh, (s.ty * rows_tile + (po >> lgW)) >> rsh, s.n);
                 else tma_load_2d(wbase, &p.tm_res, resbar2(e), cb, rp0);
             }
             return true;
@@ -446,6 +448,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
         const int W = p.W, H = p.H, NT = p.NT, macc = p.macc, tiles_y = p.tiles_y, rows_tile = p.rows_tile, n_valid = p.n_valid;
         const int lgW = 31 - __clz(W);
         const bool fold = p.fold > 1;                      // two 8-wide images per tile row (tiles_y == 1): 5-D epilogue maps
+        const int rsh = (res_mode == RES_EVEN) ? 1 : 0;    // 4-D residual view (virtual widths): half-resolution coordinates
         const int tile_step = num_clusters * csize;
         const int dn = tile_step / tiles_y, dty = tile_step - dn * tiles_y;
         // a block's place in the work sequence: round g, accumulator m, first column cb; (n, ty) = image and row-tile of
@@ -475,6 +478,7 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             if (leader) {
                 mbar_expect_tx(resbar(q, b), res_bytes);
                 if (fold) tma_load_5d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                else if (p.res4d) tma_load_4d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, x0 >> rsh, (s.ty * rows_tile + (po >> lgW)) >> rsh, s.n);
                 else tma_load_2d(wbase + b * kFastEpiBoxBytes, &p.tm_res, resbar(q, b), s.cb, rp0);
             }
             return true;
@@ -494,6 +498,9 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
                 if (fold) {
                     tma_load_5d(wbase, &p.tm_res, resbar(q, 0), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
                     tma_load_5d(wbase + kFastEpiBoxBytes, &p.tm_res_lo, resbar(q, 0), s.cb, 0, 0, s.ty * rows_tile + (po >> lgW), s.n);
+                } else if (p.res4d) {
+                    tma_load_4d(wbase, &p.tm_res, resbar(q, 0), s.cb, x0 >> rsh, (s.ty * rows_tile + (po >> lgW)) >> rsh, s.n);
+                    tma_load_4d(wbase + kFastEpiBoxBytes, &p.tm_res_lo, resbar(q, 0), s.cb, x0 >> rsh, (s.ty * rows_tile + (po >> lgW)) >> rsh, s.n);
                 } else {
                     tma_load_2d(wbase, &p.tm_res, resbar(q, 0), s.cb, rp0);
                     tma_load_2d(wbase + kFastEpiBoxBytes, &p.tm_res_lo, resbar(q, 0), s.cb, rp0);
@@ -803,11 +810,12 @@ patchgemm_kernel(const __grid_constant__ PatchGemmParams p) {
             const int y0 = (tile % p.tiles_y) * p.rows_tile;
             const int pix = m * kTileM + r;
             int y = y0 + pix / p.W, x = pix % p.W;
-            int ni = n, wr = p.W;                       // image and row width in memory
-            bool valid = (n < p.n_valid) && (y < p.H);
-            if (p.fold > 1) {                           // x = (image of the pair, pixel): image 2 n + x / 8, 8 pixels per row
-                ni = 2 * n + (x >> 3); x &= 7; wr = 8;
-                valid = (ni < p.n_real) && (y < p.H);
+            int ni = n;
+            const int wr = p.Wr;                        // row width in memory (< the tile-row width for the virtual widths)
+            bool valid = (n < p.n_valid) && (y < p.H) && (x < wr);
+            if (p.fold > 1) {                           // x = (image of the pair, pixel): image 2 n + x / 8, <= 8 pixels per row
+                ni = 2 * n + (x >> 3); x &= 7;
+                valid = (ni < p.n_real) && (y < p.H) && (x < wr);
             }
             const size_t opix = ((size_t)ni * p.H + y) * wr + x;
             EpiRow row;

@@ -55,7 +55,10 @@ struct alignas(64) PatchGemmParams {
     CUtensorMap tm_b;                // 2-D (kc, items*Npad), box (kc, NT / cluster)
     PatchGroup groups[kPatchMaxGroups];   // in the kernel parameters: read through the constant bank (uniform loads)
     int num_groups, num_items;
-    int W, H;                        // image size (stride 1: input grid == output grid)
+    int W, H;                        // tile-row width (a power of two; per image pair when folded) and image height
+    int Wr;                          // image width in memory; < W / fold for the virtual widths (28 in 32, 14 in 16, 7 in 8): the TMA
+                                     // unit zero-fills / clips what hangs over, the generic epilogue skips those pixels
+    int res4d;                       // 1: tm_res is the 4-D view (Npad, Wr, H, N) of a virtual-width grid (RES_EVEN: of its half-resolution grid)
     int rows_tile, macc;             // output rows per tile = macc * 128 / W
     int tiles_y;
     int n_valid;                     // images to process (folded ops: image PAIRS, see `fold`)

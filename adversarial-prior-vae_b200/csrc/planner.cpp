@@ -233,8 +233,15 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     for (const TermSpec& t : terms) s2c = s2c && !t.transpose && t.stride == 2;
     if (s2c && !switch_on(tuning().patch_s2, true)) return fail("patch: stride-2 convs disabled (tuning.patch_s2 = -1)");
     if (s2c && ((t0.in_w | t0.in_h) & 1)) return fail("patch: stride-2 conv needs an even input size");
-    const int W = s2c ? t0.in_w / 2 : t0.in_w, H = s2c ? t0.in_h / 2 : t0.in_h, cp = t0.in_cp;
-    if (W != 8 && W != 16 && W != 32 && W != 64 && W != 128) return fail("patch: width must be 8, 16, 32, 64 or 128");
+    const int Wreal = s2c ? t0.in_w / 2 : t0.in_w, H = s2c ? t0.in_h / 2 : t0.in_h, cp = t0.in_cp;
+    // tile rows are a power of two wide.  A grid up to 1/8 narrower (28, 14, 7: arch M) runs as tiles of the next power of
+    // two: the activation / residual / mask boxes are zero-filled and the output boxes clipped by the TMA unit at the image's
+    // real width and height, so the memory layout stays the dense [N, H, Wreal, C] and only tile rows are wasted
+    int W = 8;
+    while (W < Wreal) W <<= 1;
+    const bool virt = (W != Wreal);
+    if (W > 128 || Wreal * 8 < W * 7) return fail("patch: width must be 8, 16, 32, 64 or 128, or at most 1/8 below one of them");
+    if (virt && !switch_on(tuning().patch_virtual, true)) return fail("patch: widths below a power of two disabled (tuning.patch_virtual = -1)");
     // 8-wide images: two images side by side per tile row (PatchGemmParams::fold); needs whole pairs in the buffers
     const int fold = (W == 8) ? 2 : 1;
     if (fold > 1 && (capacity_n & 1)) return fail("patch: 8-wide images need an even capacity");
@@ -251,7 +258,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
         if (t.cout != t0.cout) return fail("patch: terms disagree on cout");
         if (t.src < 0 || t.src >= kPatchMaxSrc) return fail("patch: at most two sources");
     }
-    P.w = W; P.h = H; P.in_cp = cp; P.fold = fold; P.s2d = s2c ? 1 : 0;
+    P.w = W; P.w_real = Wreal; P.h = H; P.in_cp = cp; P.fold = fold; P.s2d = s2c ? 1 : 0;
     P.kc = (cp % 64 == 0) ? 64 : (cp % 32 == 0) ? 32 : 16;
     // phase 4 + py: both column phases of output rows 2y + py in ONE op.  Its N is [px = 0 | px = 1] x cout, i.e. the two
     // adjacent output pixels (2x, 2x + 1) of input pixel x as one contiguous 2 * cout row (no channel padding allowed)
@@ -263,7 +270,8 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     P.nsrc = 0;
     for (const TermSpec& t : terms) P.nsrc = std::max(P.nsrc, t.src + 1);
     const int rows128 = kTileM / Wt;
-    if (H < rows128) return fail("patch: image smaller than one 128-pixel tile");
+    if (!virt && H < rows128) return fail("patch: image smaller than one 128-pixel tile");
+    const int Hv = virt ? round_up(H, rows128) : H;     // a virtual-width grid may also end inside its last row tile
     int kmax = 1;
     for (const TermSpec& t : terms) kmax = std::max(kmax, s2c ? (t.k + 1) / 2 : t.k);     // vertical taps that share one patch
     int ktot = 1;                                                                       // taps per output (pair-mode rule)
@@ -345,7 +353,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
             if (force_macc && cand != force_macc) continue;
             if (cand * P.npad > 256) continue;
             const int rt = cand * rows128;
-            if (rt > H || H % rt) continue;
+            if (rt > Hv || Hv % rt) continue;
             int tpi = tpi_want;
             while (tpi > 1 && 2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > bud) --tpi;
             if (2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > bud) continue;
@@ -448,12 +456,12 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                             for (int j = 0; j < nv[ph]; ++j) pack_tap(t, c0, col[j]->di, col[j]->dj);
                         }
                 }
-            P.macs_per_image += (double)t.k * t.k * t.cin * t.cout * H * W;
+            P.macs_per_image += (double)t.k * t.k * t.cin * t.cout * H * Wreal;
             continue;
         }
         int o, lo_h, lo_w, hi;
         same_padding(H, t.k, 1, &o, &lo_h, &hi);
-        same_padding(W, t.k, 1, &o, &lo_w, &hi);
+        same_padding(Wreal, t.k, 1, &o, &lo_w, &hi);
         const int nv = phase >= 0 ? ph_nv : t.k, nh = phase >= 0 ? ph_nh : t.k;
         const int dy0 = phase >= 0 ? ph_dy0 : -lo_h, dx0 = phase >= 0 ? ph_dx0 : -lo_w;
         if (P.nmaps >= kPatchMaxMaps) return fail("patch: too many activation maps");
@@ -488,7 +496,7 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
                 }
             }
         }
-        P.macs_per_image += (merged ? (double)(ph_taps.size() + ph_taps1.size()) : (double)nv * nh) * t.cin * t.cout * H * W;
+        P.macs_per_image += (merged ? (double)(ph_taps.size() + ph_taps1.size()) : (double)nv * nh) * t.cin * t.cout * H * Wreal;
     }
     if ((int)P.groups.size() > kPatchMaxGroups) return fail("patch: too many groups");
     return true;

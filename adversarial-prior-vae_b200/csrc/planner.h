@@ -55,6 +55,8 @@ struct OpPlan {
 struct PatchPlan {
     int kc = 0, npad = 0, cout = 0;
     int w = 0, h = 0, rows_tile = 0, macc = 1, tiles_y = 0;
+    int w_real = 0;                // grid width in memory; w is the tile-row width per image: w_real, or the next power of two above it
+                                   // (28 -> 32, 14 -> 16, 7 -> 8: TMA zero-fills / clips columns >= w_real and rows >= h)
     int fold = 1;                  // 2: 8-pixel-wide images, two per tile row (the kernel sees a 16-wide "image" per pair)
     int nsrc = 0;
     // activation tensor maps: one per source, or (stride-2 conv through the space-to-depth view, `s2d`) one per

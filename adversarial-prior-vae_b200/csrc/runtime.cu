@@ -101,7 +101,11 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     PatchGemmParams& p = op->pparams;
     memset(&p, 0, sizeof(p));
     const cuuint32_t ones[5] = {1, 1, 1, 1, 1};
-    const cuuint64_t C = plan.in_cp, W = plan.w, H = plan.h;
+    // W: tile-row width per image (box widths); Wr: the grid width in memory (tensor-map dims and strides).  They differ for
+    // the virtual widths of planner.cpp (28 -> 32 ...): every box then hangs over the image's right / bottom edge, where
+    // the TMA unit zero-fills loads and clips stores
+    const cuuint64_t C = plan.in_cp, W = plan.w, Wr = plan.w_real > 0 ? plan.w_real : plan.w, H = plan.h;
+    const bool virt = (Wr != W);
     const bool fold = plan.fold > 1;        // 8-wide images in pairs: dim 2 is the image inside the pair, dim 4 the pair
     if (fold && (plan.fold != 2 || W != 8 || (plan.capacity_n & 1))) { if (err) *err = "patch: bad fold geometry for op " + op->name; return false; }
     if (fold && epi.res_mode == RES_EVEN) { if (err) *err = "patch: folded ops take no half-resolution residual (op " + op->name + ")"; return false; }
@@ -109,13 +113,13 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     // one map per (source, row phase): a stride-2 conv reads the space-to-depth view of its 2H x 2W input, column phase
     // folded into the channel dim (2C), row phase selected by the map's base address (planner.h: PatchPlan::s2d)
     const cuuint64_t cs = plan.s2d ? 2 : 1;
-    const cuuint64_t row_b = cs * cs * W * C * 2, img_b = H * row_b;      // bytes per grid row (cs input rows) and per image
+    const cuuint64_t row_b = cs * cs * Wr * C * 2, img_b = H * row_b;      // bytes per grid row (cs input rows) and per image
     if (plan.nmaps < 1 || plan.nmaps > kPatchMaxMaps) { if (err) *err = "patch: bad map count for op " + op->name; return false; }
     for (int s = 0; s < plan.nmaps; ++s) {
-        cuuint64_t dims[5] = {cs * C, W, fold ? 2u : 1u, H, NP};
+        cuuint64_t dims[5] = {cs * C, Wr, fold ? 2u : 1u, H, NP};
         cuuint64_t strides[4] = {cs * C * 2, fold ? img_b : row_b, row_b, (fold ? 2 : 1) * img_b};
         cuuint32_t box[5] = {(cuuint32_t)plan.kc, (cuuint32_t)W, fold ? 2u : 1u, (cuuint32_t)plan.prow[s], 1};
-        char* base = static_cast<char*>(const_cast<void*>(src_ptrs[plan.map_src[s]])) + (size_t)plan.map_ph[s] * (cs * W * C * 2);
+        char* base = static_cast<char*>(const_cast<void*>(src_ptrs[plan.map_src[s]])) + (size_t)plan.map_ph[s] * (cs * Wr * C * 2);
         CUresult r = encode(&p.tm_a[s], CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims, strides,
                             box, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle_for(plan.kc),
                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -139,7 +143,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
     }
     for (size_t i = 0; i < ngroups; ++i) p.groups[i] = plan.groups[i];
     p.num_groups = (int)ngroups; p.num_items = plan.num_items;
-    p.W = plan.w * plan.fold; p.H = plan.h; p.fold = plan.fold; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
+    p.W = plan.w * plan.fold; p.Wr = (int)Wr; p.H = plan.h; p.fold = plan.fold; p.rows_tile = plan.rows_tile; p.macc = plan.macc; p.tiles_y = plan.tiles_y;
     p.n_valid = 0;
     p.Npad = plan.npad; p.NT = plan.npad; p.kc = plan.kc;
     p.tpi = plan.tpi; p.tap_bytes = plan.tap_bytes;
@@ -170,7 +174,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
         const bool plain = mask_ok && !epi.out_f32 && split_ok && epi.tanh_cols == 0 && epi.bf16_zero_from >= plan.npad &&
                            (epi.out_raw || epi.out_act) && (epi.res_mode == RES_NONE || epi.res != nullptr);
         if (plain && switch_on(tuning().fast_epi, true)) {
-            const cuuint64_t pixels = (cuuint64_t)plan.capacity_n * H * W;
+            const cuuint64_t pixels = (cuuint64_t)plan.capacity_n * H * Wr;
             bool ok = true;
             auto map2d = [&](CUtensorMap* tm, const void* ptr, cuuint64_t rows, int ld, cuuint32_t box_rows) {
                 cuuint64_t dims[2] = {(cuuint64_t)plan.npad, rows};
@@ -189,12 +193,12 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             const bool merged = plan.phase >= 4;
             if (merged && epi.ldo * 2 != plan.npad) { if (err) *err = "patch: merged column phases need ldo == cout (op " + op->name + ")"; return false; }
             const int py = merged ? plan.phase - 4 : plan.phase >= 0 ? (plan.phase >> 1) : 0, px = (plan.phase >= 0 && !merged) ? (plan.phase & 1) : 0;
-            auto map_out = [&](CUtensorMap* tm, const void* ptr, int ld_elems) {
+            auto map_grid = [&](CUtensorMap* tm, const void* ptr, int ld_elems, int osc, int py, int px) {
                 const cuuint64_t ld = (cuuint64_t)ld_elems * 2;                      // bytes per output pixel
-                const cuuint64_t Wo = (cuuint64_t)osc * W, Ho = (cuuint64_t)osc * H;
+                const cuuint64_t Wo = (cuuint64_t)osc * Wr, Ho = (cuuint64_t)osc * H;
                 char* base = static_cast<char*>(const_cast<void*>(ptr)) + ((size_t)py * Wo + px) * ld;
                 if (fold) {                 // (C, 8 pixels, 2 images, H, pairs): a block's 32 rows are [2 rows][2 images][8 pixels]
-                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
+                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, Wr, 2, H, NP};
                     cuuint64_t strides4[4] = {osc * ld, Ho * Wo * ld, osc * Wo * ld, 2 * Ho * Wo * ld};
                     cuuint32_t box5[5] = {64, 8, 2, 2, 1};
                     const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, base, dims5, strides4, box5, ones,
@@ -203,7 +207,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                     if (r != CUDA_SUCCESS) ok = false;
                     return;
                 }
-                cuuint64_t dims[4] = {(cuuint64_t)plan.npad, W, H, (cuuint64_t)plan.capacity_n};
+                cuuint64_t dims[4] = {(cuuint64_t)plan.npad, Wr, H, (cuuint64_t)plan.capacity_n};
                 cuuint64_t strides[3] = {osc * ld, osc * Wo * ld, Ho * Wo * ld};
                 const cuuint32_t bx = (cuuint32_t)std::min<cuuint64_t>(W, 32);
                 cuuint32_t box[4] = {64, bx, 32 / bx, 1};
@@ -213,22 +217,37 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                                           CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                 if (r != CUDA_SUCCESS) ok = false;
             };
+            auto map_out = [&](CUtensorMap* tm, const void* ptr, int ld_elems) { map_grid(tm, ptr, ld_elems, osc, py, px); };
             const void* any_out = epi.out_raw ? epi.out_raw : epi.out_act;
             map_out(&p.tm_raw, epi.out_raw ? epi.out_raw : any_out, epi.ldo);
             map_out(&p.tm_act, epi.out_act ? epi.out_act : any_out, epi.ldo);
             auto map_res = [&](CUtensorMap* tm, const void* ptr) {
-                if (epi.res_mode == RES_EVEN) {
+                if (epi.res_mode == RES_EVEN && virt) {
+                    // half-resolution residual of a virtual-width grid: (C, Wr / 2, H / 2, N), one (partial) row of it per block
+                    p.res_rows = (plan.w >= 32) ? 16 : 8;
+                    const cuuint64_t ld = (cuuint64_t)epi.ld_res * 2;
+                    cuuint64_t dims[4] = {(cuuint64_t)plan.npad, Wr / 2, H / 2, (cuuint64_t)plan.capacity_n};
+                    cuuint64_t strides[3] = {ld, (Wr / 2) * ld, (H / 2) * (Wr / 2) * ld};
+                    cuuint32_t box[4] = {64, (cuuint32_t)p.res_rows, 1, 1};
+                    const cuuint32_t ones4[4] = {1, 1, 1, 1};
+                    const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), dims, strides, box, ones4,
+                                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                    if (r != CUDA_SUCCESS || (Wr & 1) || (H & 1)) ok = false;
+                } else if (epi.res_mode == RES_EVEN) {
                     p.res_rows = (plan.w >= 32) ? 16 : 8;
                     map2d(tm, ptr, pixels / 4, epi.ld_res, (cuuint32_t)p.res_rows);
                 } else if (epi.res_mode == RES_SAME && fold) {
                     const cuuint64_t ld = (cuuint64_t)epi.ld_res * 2;
-                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
-                    cuuint64_t strides4[4] = {ld, H * W * ld, W * ld, 2 * H * W * ld};
+                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, Wr, 2, H, NP};
+                    cuuint64_t strides4[4] = {ld, H * Wr * ld, Wr * ld, 2 * H * Wr * ld};
                     cuuint32_t box5[5] = {64, 8, 2, 2, 1};
                     const CUresult r = encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(ptr), dims5, strides4,
                                               box5, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                                               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
                     if (r != CUDA_SUCCESS) ok = false;
+                } else if (epi.res_mode == RES_SAME && virt) {
+                    map_grid(tm, ptr, epi.ld_res, 1, 0, 0);              // the output's 4-D view: loaded at the store's coordinates
                 } else if (epi.res_mode == RES_SAME) {
                     map2d(tm, ptr, pixels, epi.ld_res, 32);
                 } else {
@@ -236,6 +255,7 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
                 }
             };
             map_res(&p.tm_res, epi.res);
+            p.res4d = (virt && !fold) ? 1 : 0;
             p.split = any_lo ? 1 : 0;
             p.epi2 = (plan.epi2 && !any_lo) ? 1 : 0;                   // two epilogue warpgroups: 16-bit epilogue (mask allowed)
             if (any_lo) {
@@ -250,11 +270,14 @@ bool devop_create_patch(const DeviceInfo& dev, const PatchPlan& plan, const void
             if (epi.mask && plan.phase >= 0) {            // the mask of a sub-pixel phase: the same strided view as its output
                 map_out(&p.tm_mask, epi.mask, epi.ld_mask);
                 p.fast_mask = ok ? (fold ? 1 : 2) : 0;     // 2: 4-D load at the store's coordinates
+            } else if (epi.mask && virt && !fold) {
+                map_grid(&p.tm_mask, epi.mask, epi.ld_mask, 1, 0, 0);
+                p.fast_mask = ok ? 2 : 0;
             } else if (epi.mask) {
                 if (fold) {
                     const cuuint64_t ld = (cuuint64_t)epi.ld_mask * 2;
-                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, W, 2, H, NP};
-                    cuuint64_t strides4[4] = {ld, H * W * ld, W * ld, 2 * H * W * ld};
+                    cuuint64_t dims5[5] = {(cuuint64_t)plan.npad, Wr, 2, H, NP};
+                    cuuint64_t strides4[4] = {ld, H * Wr * ld, Wr * ld, 2 * H * Wr * ld};
                     cuuint32_t box5[5] = {64, 8, 2, 2, 1};
                     const CUresult r = encode(&p.tm_mask, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(epi.mask), dims5, strides4,
                                               box5, ones, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,

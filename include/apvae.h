@@ -62,6 +62,8 @@ typedef struct apvae_tuning {
     int patch_split;        /* switch (default on): two-term split-precision ops (precise = 2) on the patch kernel */
     int debug;              /* patch kernel probe modes (skip loads / MMAs / epilogue / stores); 0 in any real run */
     int trace;              /* switch (default off): clock stamps of CTA 0, read back by apvae_plan_bench */
+    int patch_virtual;      /* switch (default on): grids whose width is within 1/8 below a power of two (7, 14, 28: arch M) on the patch kernel
+                             * as tiles of the next power of two (TMA zero-fills / clips the columns and rows past the image) */
 } apvae_tuning;
 
 typedef struct apvae_config {
@@ -301,7 +303,7 @@ typedef struct apvae_plan_info {
     uint64_t src_strides[3][4];
     uint32_t src_box[3][5];
     double macs_per_image;
-    /* A-stationary ("patch") plan, when the op is eligible (stride 1, width 8..128) and not disabled */
+    /* A-stationary ("patch") plan, when the op is eligible (width 7..128 within 1/8 below a power of two) and not disabled */
     int patch, patch_macc, patch_cluster, patch_rows_tile, patch_groups, patch_items, patch_a_stages, patch_b_stages;
     int patch_prow[2];
     /* activation maps of the patch plan: (source, row phase); patch_s2d = 1: stride-2 conv through the space-to-depth view */
@@ -309,6 +311,7 @@ typedef struct apvae_plan_info {
     int patch_phase, patch_out_scale, patch_npad;   /* of the selected patch plan (apvae_plan_select_patch): sub-pixel phase 0..3, row phase 4..5, -1 none */
     int patch_fold;   /* 2: 8-pixel-wide images are processed in pairs, side by side in one 16-wide tile row (even capacity) */
     int patch_epi2;   /* 1: the selected patch plan asks for two epilogue warpgroups (epilogue-bound tiles) */
+    int patch_wv;     /* tile-row width per image of the patch plan: the grid width, or the next power of two above it (28 -> 32, 14 -> 16, 7 -> 8) */
 } apvae_plan_info;
 
 typedef struct apvae_epilogue {

@@ -112,8 +112,9 @@ def emulate_patch_plan(plan, srcs, n_valid):
     """Evaluate the A-stationary ("patch") plan on the CPU exactly as patchgemm.cu would: per tile and
     group, one zero-filled patch [prow, W, kc]; tap j reads the patch advanced by j*W rows, accumulator
     m by 128 rows.  Stride-2 convs (patch_s2d) read the space-to-depth view of the input.  Folded plans (8-wide images, patch_fold == 2) lay two images side by side: the patch
-    is [prow, 2 images, 8, kc] and a tile row is 16 pixels.  srcs: float arrays [N, H, W, Cp].
-    Returns [n_valid, H, W, npad]."""
+    is [prow, 2 images, 8, kc] and a tile row is 16 pixels.  Virtual widths (patch_wv > W: 28 in 32, 14 in 16, 7 in 8):
+    the tile rows are patch_wv wide, what hangs over the image's right / bottom edge is zero on load and dropped on
+    store.  srcs: float arrays [N, H, W, Cp].  Returns [n_valid, H, W, npad]."""
     i = plan.info
     assert i.patch
     groups = plan.patch_groups
@@ -122,7 +123,8 @@ def emulate_patch_plan(plan, srcs, n_valid):
     bias = plan.patch_bias if i.patch_npad else plan.bias
     H, W, kc, macc, rt = i.hg, i.wg, i.kc, i.patch_macc, i.patch_rows_tile
     fold = max(1, i.patch_fold)
-    Wt = W * fold
+    Wv = i.patch_wv or W                 # tile-row width per image
+    Wt = Wv * fold
     # a sub-pixel phase plan (Plan.select_patch) writes output pixels (2y + py, 2x + px) of a 2H x 2W image; a row-phase
     # plan (phase 4 + py) carries both column phases side by side in N
     ph = i.patch_phase
@@ -139,7 +141,7 @@ def emulate_patch_plan(plan, srcs, n_valid):
                 if i.patch_s2d:      # space-to-depth view of the 2H x 2W input: [N, H, row phase, W, 2 Cp], one row phase per map
                     nn, hh, ww, cc = x.shape
                     x = x.reshape(nn, hh // 2, 2, ww // 2, 2 * cc)[:, :, i.patch_map_ph[mp]]
-                patch = np.zeros((prow, fold, W, kc))
+                patch = np.zeros((prow, fold, Wv, kc))
                 for py in range(prow):
                     y = y0 + py0 + py
                     if not 0 <= y < H:
@@ -147,7 +149,7 @@ def emulate_patch_plan(plan, srcs, n_valid):
                     for f in range(fold):
                         if n0 + f >= x.shape[0]:
                             continue
-                        for px in range(W):
+                        for px in range(Wv):
                             xx = px + dx
                             if 0 <= xx < W:
                                 patch[py, f, px, :] = x[n0 + f, y, xx, c0:c0 + kc]
@@ -162,8 +164,8 @@ def emulate_patch_plan(plan, srcs, n_valid):
             acc += bias
             for pix in range(macc * 128):
                 y, xt = y0 + pix // Wt, pix % Wt
-                f, xx = xt // W, xt % W
-                if y < H and n0 + f < n_valid:
+                f, xx = xt // Wv, xt % Wv
+                if y < H and xx < W and n0 + f < n_valid:
                     if ph < 0:
                         out[n0 + f, y, xx] = acc[pix]
                     elif ph < 4:

@@ -187,7 +187,13 @@ PATCH_GPU_CASES = [
     (False, 3, 6, 8, 8, 192, 192),         # 8-wide images run as pairs (fold): even capacity
     (True, 3, 4, 8, 8, 64, 64),
     (True, 1, 130, 8, 8, 2, 192),
+    (False, 3, 5, 28, 28, 32, 32),         # arch M: virtual widths (28 in 32, 14 in 16, 7 in 8 as pairs), fp32 output
+    (True, 3, 4, 14, 14, 64, 64),          # through the generic epilogue, which skips the pixels past the image
+    (False, 3, 6, 7, 7, 64, 64),
+    (False, 5, 3, 14, 28, 16, 48),
 ]
+
+VIRTUAL_W = {7: 8, 14: 16, 28: 32}         # grid width -> tile-row width of the A-stationary kernel (planner.cpp)
 
 
 @pytest.mark.parametrize('cluster', [1, 2, 4])
@@ -198,8 +204,10 @@ def test_patch_kernel(transpose, k, N, H, W, cin, cout, macc, cluster):
     torch = _torch()
     import apvae
     from apvae.plan import Plan, pad16
-    Wt = 16 if W == 8 else W                   # 8-wide images: two side by side per tile row
-    if macc * pad16(cout) > 256 or H % (macc * 128 // Wt) or (pad16(cout) // cluster) % 8:
+    Wv = VIRTUAL_W.get(W, W)
+    Wt = 16 if Wv == 8 else Wv                 # 8-wide images: two side by side per tile row
+    Hv = -(-H // (128 // Wt)) * (128 // Wt) if Wv != W else H      # virtual widths: the last row tile may hang over
+    if macc * pad16(cout) > 256 or Hv % (macc * 128 // Wt) or (pad16(cout) // cluster) % 8:
         pytest.skip('combination not supported by the planner')
     tuning = dict(patch=1)
     tuning['patch_macc'] = macc
@@ -269,6 +277,14 @@ TMA_EPI_CASES = [
     (8, 8, 64, 48, 'same', 2, 2),
     (8, 8, 64, 64, 'even', 3, 4),          # half-resolution residual: falls back to the tap-GEMM kernel
     (16, 8, 32, 32, 'same', 3, 4),         # 8 wide, 16 high: two row tiles per pair
+    (28, 28, 32, 32, 'same', 3, 4),        # arch M (virtual widths): residual through its 4-D view, stores clipped by the TMA unit
+    (28, 28, 16, 32, 'none', 2, 2),
+    (28, 28, 32, 16, 'even', 2, 3),        # G_theta/level_5/conv_1: half-resolution residual from the 14 x 14 grid
+    (14, 14, 64, 64, 'same', 3, 3),        # one 16-row tile of two accumulators (macc = 1: two tiles, the second 6 rows)
+    (14, 14, 64, 64, 'even', 2, 3),        # G_theta/level_3/conv_1: residual from the 7 x 7 grid
+    (7, 7, 64, 64, 'same', 3, 4),          # image pairs, row 7 and column 7 of every tile hang over
+    (7, 7, 64, 48, 'none', 4, 4),
+    (14, 28, 32, 96, 'same', 2, 2),
 ]
 
 
@@ -326,6 +342,11 @@ def test_patch_kernel_tma_epilogue(H, W, cin, cout, res, n_valid, cap, macc, two
 SPLIT_EPI_CASES = [
     # transpose, k, stride, H, W (input), cin, cout, res, outs, n_valid, cap
     (False, 3, 1, 16, 16, 64, 64, 'same', 'raw+act', 3, 4),     # arch B block output with identity shortcut
+    (False, 3, 1, 28, 28, 32, 32, 'same', 'raw+act', 2, 3),     # arch M widths: 4-D residual views, clipped stores
+    (True, 3, 1, 14, 14, 64, 64, 'even', 'raw+act', 2, 2),
+    (False, 3, 1, 7, 7, 64, 64, 'same', 'raw+act', 3, 4),
+    (False, 3, 2, 28, 28, 32, 32, 'none', 'act', 2, 2),
+    (True, 3, 2, 7, 7, 64, 64, 'none', 'act', 4, 4),
     (False, 3, 1, 32, 32, 32, 32, 'none', 'act', 2, 3),         # conv_0 of a block
     (True, 5, 1, 64, 64, 32, 32, 'same', 'raw', 1, 2),          # arch B celebA G_theta/level_9/conv_1
     (True, 3, 1, 32, 32, 32, 32, 'even', 'raw+act', 2, 2),      # stride-2 block: half-resolution shortcut on even pixels
@@ -399,7 +420,7 @@ def test_split_precision_ops_on_the_patch_kernel(transpose, k, stride, H, W, cin
         assert np.abs((hi + lo)[:n_valid, ..., :cout] - ref[:n_valid]).max() <= tol, (name, np.abs((hi + lo)[:n_valid, ..., :cout] - ref[:n_valid]).max(), tol)
         assert np.abs(hi[:n_valid, ..., :cout] - ref[:n_valid]).max() <= 2.0 ** -7 * scale
         assert np.all(hi[:n_valid, ..., cout:] == 0) and np.all(lo[:n_valid, ..., cout:] == 0)
-        keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 or W == 8 else 0)
+        keep = n_valid + (n_valid & 1 if plan.info.patch_fold == 2 or W in (7, 8) else 0)
         assert np.all(hi[keep:] == 7.0) and np.all(lo[keep:] == 7.0)
 
 
@@ -414,6 +435,8 @@ PHASE_CASES = [
     (3, 8, 8, 192, 192, 3, 4),         # arch A G_theta/level_3/conv_0: 8-wide inputs run as pairs
     (3, 8, 8, 64, 32, 4, 4),
     (5, 8, 8, 32, 32, 2, 2),
+    (3, 7, 7, 64, 64, 3, 4),           # arch M G_theta/level_3/conv_0: 7 -> 14, pairs of 7-wide images in 8-wide tile rows
+    (3, 14, 14, 64, 32, 2, 3),         # G_theta/level_5/conv_0: 14 -> 28
 ]
 
 
@@ -444,7 +467,7 @@ def test_stride2_deconv_as_four_patch_phases(k, H, W, cin, cout, n_valid, cap, o
     scale = max(1.0, float(np.abs(want).max()))
     act = out_act.float().cpu().numpy()
     assert np.abs(act[:n_valid, ..., :cout] - O.leaky_relu(want[:n_valid])).max() <= 2 ** -7 * scale
-    keep = n_valid + (n_valid & 1 if W == 8 else 0)      # pairs of 8-wide images: the last pair is written whole
+    keep = n_valid + (n_valid & 1 if W in (7, 8) else 0)      # pairs of 8-wide images: the last pair is written whole
     assert np.all(act[keep:] == 7.0)
     if out_raw is not None:
         raw = out_raw.float().cpu().numpy()
@@ -460,6 +483,8 @@ S2_CASES = [
     (5, 64, 64, 3, 32, False, 2, 3),       # celebA first block
     (3, 64, 64, 32, 64, True, 1, 2),
     (1, 32, 32, 16, 16, False, 3, 3),
+    (3, 28, 28, 32, 32, True, 3, 4),       # arch M level_4/conv_1: 28 -> 14 (14 in 16-wide tile rows)
+    (3, 14, 14, 32, 64, True, 3, 4),       # level_6/conv_1: 14 -> 7 (image pairs)
 ]
 
 
@@ -517,6 +542,10 @@ MASK_CASES = [
     (64, 64, 32, 32, 'none', 1, 2),
     (8, 8, 192, 192, 'same', 5, 6),        # image pairs
     (8, 8, 64, 48, 'none', 4, 4),
+    (28, 28, 32, 32, 'same', 2, 3),        # arch M widths: mask and residual through 4-D views
+    (28, 28, 32, 16, 'none', 3, 3),
+    (14, 14, 64, 64, 'even', 2, 2),
+    (7, 7, 64, 64, 'same', 3, 4),
 ]
 
 
@@ -577,6 +606,8 @@ PHASE_MASK_CASES = [
     (5, 32, 32, 32, 3, 2, 2),          # arch B D_psi/level_0/conv_1^T: 3 output channels, four phases
     (3, 8, 8, 192, 192, 3, 4),         # image pairs, four phases
     (3, 32, 32, 64, 48, 2, 3),
+    (3, 14, 14, 32, 32, 2, 3),         # arch M level_4/conv_1^T: 14 -> 28
+    (3, 7, 7, 64, 32, 3, 4),           # level_6/conv_1^T: 7 -> 14, image pairs
 ]
 
 
@@ -602,5 +633,5 @@ def test_stride2_deconv_phases_with_mask(k, H, W, cin, cout, n_valid, cap):
     scale = max(1.0, float(np.abs(want).max()))
     raw = out_raw.float().cpu().numpy()
     assert np.abs(raw[:n_valid, ..., :cout] - want[:n_valid]).max() <= 2 ** -7 * scale
-    keep = n_valid + (n_valid & 1 if W == 8 else 0)
+    keep = n_valid + (n_valid & 1 if W in (7, 8) else 0)
     assert np.all(raw[keep:] == 7.0)

@@ -104,6 +104,11 @@ PATCH_CASES = [
     (False, 3, 8, 8, 32, 48),        # 8-wide images: two per tile row (fold)
     (True, 3, 8, 8, 16, 200),
     (False, 1, 16, 8, 16, 16),       # 8 wide, two row tiles per pair
+    (False, 3, 28, 28, 16, 32),      # arch M: 28 wide in 32-wide tile rows (seven 4-row tiles)
+    (True, 3, 28, 28, 32, 16),
+    (False, 3, 14, 14, 32, 32),      # 14 in 16: one 16-row tile of two accumulators, rows 14 and 15 hang over
+    (True, 3, 7, 7, 64, 64),         # 7 in 8, as image pairs: one 8-row tile per pair
+    (False, 5, 14, 28, 16, 16),      # non-square, 5x5
 ]
 
 
@@ -124,7 +129,8 @@ def test_patch_plan_matches_oracle(transpose, k, H, W, cin, cout, macc):
     plan = Plan([dict(src=0, transpose=transpose, stride=1, in_h=H, in_w=W, kernel=kern, bias=bias)], n, tuning=tuning)
     assert plan.info.patch == 1
     assert plan.info.patch_macc * plan.info.npad <= 256
-    assert plan.info.patch_fold == (2 if W == 8 else 1)
+    assert plan.info.patch_fold == (2 if W in (7, 8) else 1)
+    assert plan.info.patch_wv == {7: 8, 14: 16, 28: 32}.get(W, W)
     got = emulate_patch_plan(plan, [pad_channels(x, pad16(cin))], n)[..., :cout]
     fn = O.deconv2d if transpose else O.conv2d
     want = fn(x.astype(np.float64), kern.astype(np.float64), bias.astype(np.float64), 1)
@@ -138,6 +144,8 @@ S2_PATCH_CASES = [
     (5, 64, 64, 3, 32, False),       # celebA first block
     (1, 32, 32, 16, 16, False),
     (3, 32, 64, 16, 24, False),      # non-square
+    (3, 28, 28, 32, 32, True),       # arch M level_4: 28 -> 14 (14 in 16-wide tile rows)
+    (3, 14, 14, 32, 64, True),       # arch M level_6: 14 -> 7 (7 in 8, image pairs)
 ]
 
 
@@ -164,7 +172,7 @@ def test_patch_plan_stride2_conv_matches_oracle(k, H, W, cin, cout, shortcut):
         want = want + O.conv2d(x2.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 2)
     plan = Plan(terms, n, tuning=tuning)
     assert plan.info.patch == 1 and plan.info.patch_s2d == 1
-    assert plan.info.patch_fold == (2 if W == 16 else 1)
+    assert plan.info.patch_fold == (2 if W in (14, 16) else 1)
     assert plan.info.patch_nmaps == (1 if k == 1 else 2) + (1 if shortcut else 0)
     got = emulate_patch_plan(plan, srcs, n)[..., :cout]
     assert got.shape == want.shape
@@ -178,6 +186,8 @@ PHASE_PLAN_CASES = [
     (3, 8, 8, 32, 32),         # 8-wide input: image pairs
     (3, 16, 16, 16, 3),        # cout % 16 != 0: four sub-pixel phases only
     (3, 16, 32, 16, 192),      # 2 * cout > 256: four sub-pixel phases only
+    (3, 7, 7, 64, 64),         # arch M G_theta/level_3: 7 -> 14 (7 in 8, image pairs)
+    (3, 14, 14, 64, 32),       # arch M G_theta/level_5: 14 -> 28
 ]
 
 
@@ -230,10 +240,16 @@ def test_patch_plan_fused_shortcut_and_eligibility():
     want = O.conv2d(r.astype(np.float64), k1.astype(np.float64), b1.astype(np.float64), 1) + \
         O.conv2d(x.astype(np.float64), ks.astype(np.float64), bs.astype(np.float64), 1)
     np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6)
-    # not eligible: stride 2 onto a 4x4 grid, 8x8 grids with an odd capacity (they run as image pairs), arch-M widths
+    # not eligible: stride 2 onto a 4x4 grid, 8x8 grids with an odd capacity (they run as image pairs), widths more than
+    # 1/8 below a power of two, and the arch-M widths with tuning.patch_virtual = -1
     assert Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), in_h=8, in_w=8)], 4).info.patch_fold == 2
-    for kw in (dict(stride=2, in_h=8, in_w=8), dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=28, in_w=28)):
-        p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1, tuning=tuning)
+    assert Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), in_h=28, in_w=28)], 1, tuning=tuning).info.patch_wv == 32
+    for kw in (dict(stride=2, in_h=8, in_w=8), dict(stride=2, in_h=16, in_w=16), dict(in_h=8, in_w=8), dict(in_h=24, in_w=24),
+               dict(in_h=7, in_w=7), dict(in_h=28, in_w=28, virt=-1)):
+        tn = dict(tuning)
+        if kw.pop('virt', 0):
+            tn['patch_virtual'] = -1
+        p = Plan([dict(src=0, kernel=np.zeros((3, 3, 16, 16), np.float32), **kw)], 1, tuning=tn)
         assert p.info.patch == 0
     tuning['patch'] = -1
     p = Plan([dict(src=0, in_h=16, in_w=16, kernel=np.zeros((3, 3, 16, 16), np.float32))], 1, tuning=tuning)
