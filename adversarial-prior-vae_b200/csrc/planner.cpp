@@ -271,7 +271,10 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
     for (const TermSpec& t : terms) P.nsrc = std::max(P.nsrc, t.src + 1);
     const int rows128 = kTileM / Wt;
     if (!virt && H < rows128) return fail("patch: image smaller than one 128-pixel tile");
-    const int Hv = virt ? round_up(H, rows128) : H;     // a virtual-width grid may also end inside its last row tile
+    // a virtual-width grid may also end inside its last row tile: up to 1/7 more rows than the image has (28 rows as two
+    // 16-row tiles of four accumulators instead of seven 4-row tiles of one: the per-tile costs and the patch halo are paid
+    // twice instead of seven times per image)
+    auto rows_for = [&](int rt) { return virt ? round_up(H, rt) : H; };
     int kmax = 1;
     for (const TermSpec& t : terms) kmax = std::max(kmax, s2c ? (t.k + 1) / 2 : t.k);     // vertical taps that share one patch
     int ktot = 1;                                                                       // taps per output (pair-mode rule)
@@ -353,7 +356,8 @@ bool plan_patch_op(const std::vector<TermSpec>& terms, int capacity_n, int force
             if (force_macc && cand != force_macc) continue;
             if (cand * P.npad > 256) continue;
             const int rt = cand * rows128;
-            if (rt > Hv || Hv % rt) continue;
+            const int Hv = rows_for(rt);
+            if (rt > Hv || Hv % rt || (Hv - H) * 7 > H) continue;
             int tpi = tpi_want;
             while (tpi > 1 && 2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > bud) --tpi;
             if (2 * a_slot_for(cand) + 2u * b_slot_for(tpi) > bud) continue;

@@ -104,7 +104,7 @@ PATCH_CASES = [
     (False, 3, 8, 8, 32, 48),        # 8-wide images: two per tile row (fold)
     (True, 3, 8, 8, 16, 200),
     (False, 1, 16, 8, 16, 16),       # 8 wide, two row tiles per pair
-    (False, 3, 28, 28, 16, 32),      # arch M: 28 wide in 32-wide tile rows (seven 4-row tiles)
+    (False, 3, 28, 28, 16, 32),      # arch M: 28 wide in 32-wide tile rows (two 16-row tiles, the second hangs over by 4 rows)
     (True, 3, 28, 28, 32, 16),
     (False, 3, 14, 14, 32, 32),      # 14 in 16: one 16-row tile of two accumulators, rows 14 and 15 hang over
     (True, 3, 7, 7, 64, 64),         # 7 in 8, as image pairs: one 8-row tile per pair
