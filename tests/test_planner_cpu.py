@@ -340,3 +340,38 @@ def test_planner_picks_the_second_epilogue_warpgroup_for_epilogue_bound_tiles():
     assert (i.patch_cluster, i.patch_a_stages, i.patch_b_stages) == (2, 3, 4)
     j = plan(True, 3, 16, 16, 192, 192, tuning=dict(patch_tpi=1))
     assert (j.patch_a_stages, j.patch_b_stages) == (4, 6)
+
+
+def test_every_arch_m_conv_plans_onto_the_patch_kernel():
+    """dmm_bernouli_fashion.py:444-448, 510-514, 561-565: every conv / deconv of arch M's q_net, G_theta and D_psi
+    (28 / 14 / 7-wide grids, 16 - 64 channels) has an A-stationary plan through the virtual widths (even capacity: the
+    7-wide grids run as image pairs); stride-2 transposed convs as merged row-phase plans."""
+    z = lambda *s: np.zeros(s, np.float32)
+    convs = [
+        # transpose, k, stride, H (= W), cin, cout, with a 1x1 shortcut term of the same stride
+        (False, 3, 1, 28, 16, 16, False), (False, 3, 1, 28, 16, 32, True),        # level_2
+        (False, 3, 1, 28, 32, 32, False),                                         # level_3, level_4/conv_0
+        (False, 3, 2, 28, 32, 32, True),                                          # level_4/conv_1: 28 -> 14
+        (False, 3, 1, 14, 32, 32, False), (False, 3, 2, 14, 32, 64, True),        # level_6: 14 -> 7
+        (True, 3, 1, 14, 64, 64, False),                                          # G level_3/conv_1
+        (True, 3, 1, 28, 32, 32, False),                                          # G level_5/conv_1, level_6, level_7
+        (True, 3, 1, 28, 32, 16, False), (True, 3, 1, 28, 16, 16, False),         # G level_8
+        (True, 1, 1, 28, 32, 16, False),                                          # G level_8/shortcut
+        (True, 1, 1, 7, 64, 64, False), (True, 1, 1, 14, 64, 32, False),          # half-resolution shortcuts of level_3 / level_5
+    ]
+    for tr, k, s, H, cin, cout, sc in convs:
+        shp = (k, k, cout, cin) if tr else (k, k, cin, cout)
+        terms = [dict(src=0, transpose=tr, stride=s, in_h=H, in_w=H, kernel=z(*shp))]
+        if sc:
+            terms.append(dict(src=1, stride=s, in_h=H, in_w=H, kernel=z(1, 1, cin, cout)))
+        i = Plan(terms, 64).info
+        Wg = H // s
+        assert i.patch == 1 and i.patch_wv == {7: 8, 14: 16, 28: 32}[Wg], (tr, k, s, H, cin, cout)
+        assert i.patch_fold == (2 if Wg == 7 else 1)
+        assert i.patch_rows_tile * i.patch_wv * i.patch_fold == 128 * i.patch_macc
+    for H, cin, cout in ((7, 64, 64), (14, 64, 32)):                              # G level_3 / level_5 conv_0: stride-2 transposed
+        plan = Plan([dict(src=0, transpose=True, stride=2, in_h=H, in_w=H, kernel=z(3, 3, cout, cin))], 64)
+        plan.select_patch(4)
+        assert plan.info.patch_phase == 4 and plan.info.patch_npad == 2 * cout and plan.info.patch_wv == {7: 8, 14: 16}[H]
+    # an odd capacity keeps the 7-wide grids on the tap-GEMM kernel (pairs need whole pairs in the buffers)
+    assert Plan([dict(src=0, in_h=7, in_w=7, kernel=z(3, 3, 64, 64))], 5).info.patch == 0
